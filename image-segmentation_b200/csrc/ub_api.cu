@@ -1,0 +1,755 @@
+// ub_api.cu — host side of libunetb200.so: context, weight folding/packing, the per-resolution
+// execution plan (buffers + TMA descriptors) and the C ABI declared in include/unet_b200.h.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/unet_b200.h"
+#include "ub_aux.cuh"
+#include "ub_conv_tc.cuh"
+#include "ub_perturb.cuh"
+
+namespace {
+
+using ub::ConvParams;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+std::string g_create_error;
+
+struct HostTensor {
+  std::vector<float> data;
+  std::vector<int64_t> shape;
+};
+
+// One tensor-core GEMM layer (conv3x3+BN+ReLU, or ConvTranspose2d k2 s2).
+struct GemmLayer {
+  std::string key;  // state_dict prefix of the conv / up module
+  int cin = 0, cout = 0, n_total = 0, ksize = 3, block_n = 0, swz = 128, relu = 1;
+  bool is_convt = false;
+  __nv_bfloat16* w = nullptr;  // [n_total][ksize*ksize*cin] bf16, BN folded
+  float* bias = nullptr;       // [cout]
+};
+
+struct Step {
+  enum Kind { GEMM, RESAMPLE } kind = GEMM;
+  int layer = -1;
+  ConvParams cp;   // GEMM: tensor maps + static params (B patched per launch)
+  // RESAMPLE
+  const __nv_bfloat16* rs_in = nullptr;
+  __nv_bfloat16* rs_out = nullptr;
+  int hi = 0, wi = 0, ho = 0, wo = 0, c = 0, out_cstride = 0, out_choff = 0;
+};
+
+struct Plan {
+  int H = 0, W = 0;
+  void* arena = nullptr;
+  size_t arena_bytes = 0;
+  __nv_bfloat16* stem_out = nullptr;
+  int stem_cstride = 0, stem_choff = 0;
+  float* pert_f32 = nullptr;   // [MB,3,H,W] perturbed image (blur families / perturbed_out staging)
+  void* blur_a = nullptr;      // ping-pong planes (fp32-sized)
+  void* blur_b = nullptr;
+  std::vector<Step> steps;
+};
+
+}  // namespace
+
+struct ub_ctx {
+  int device = 0, arch = 0, in_ch = 3, n_classes = 3, max_mb = 16, num_sms = 148, n_enc = 3;
+  std::string err;
+  std::map<std::string, HostTensor> sd;
+  std::vector<GemmLayer> layers;
+  std::map<std::string, int> layer_by_key;
+  ub::StemWeights stem;
+  float* head_w = nullptr;  // device [C][32]
+  float* head_b = nullptr;
+  bool weights_ready = false;
+  std::map<std::pair<int, int>, std::unique_ptr<Plan>> plans;
+  EncodeTiledFn encode = nullptr;
+  int64_t launches = 0;
+  std::vector<void*> owned;  // device allocations freed in ub_destroy
+};
+
+namespace {
+
+int fail(ub_ctx* ctx, int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->err = buf; else g_create_error = buf;
+  return code;
+}
+
+#define UB_CUDA(ctx, call)                                                                      \
+  do {                                                                                          \
+    cudaError_t e__ = (call);                                                                   \
+    if (e__ != cudaSuccess)                                                                     \
+      return fail(ctx, UB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__),   \
+                  __FILE__, __LINE__);                                                          \
+  } while (0)
+
+int dev_alloc(ub_ctx* ctx, void** p, size_t bytes) {
+  UB_CUDA(ctx, cudaMalloc(p, bytes));
+  ctx->owned.push_back(*p);
+  return UB_OK;
+}
+
+const HostTensor* find(ub_ctx* ctx, const std::string& k) {
+  auto it = ctx->sd.find(k);
+  return it == ctx->sd.end() ? nullptr : &it->second;
+}
+
+int pick_block_n(int n_total) { return n_total >= 256 ? 256 : n_total; }
+
+// conv3x3 + BatchNorm(eval) folded:  w' = w*g/sqrt(var+eps),  b' = (b-mean)*g/sqrt(var+eps)+beta
+// (processing_blocks.py:43-44).  Packed K order = (ky*3+kx)*Cin + ci, K contiguous per output channel.
+int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_key) {
+  const HostTensor* w = find(ctx, conv_key + ".weight");
+  const HostTensor* b = find(ctx, conv_key + ".bias");
+  const HostTensor* g = find(ctx, bn_key + ".weight");
+  const HostTensor* be = find(ctx, bn_key + ".bias");
+  const HostTensor* mu = find(ctx, bn_key + ".running_mean");
+  const HostTensor* var = find(ctx, bn_key + ".running_var");
+  if (!w || !b || !g || !be || !mu || !var)
+    return fail(ctx, UB_ERR_INVALID, "missing state_dict entries for %s / %s", conv_key.c_str(), bn_key.c_str());
+  if (w->shape.size() != 4 || w->shape[2] != 3 || w->shape[3] != 3)
+    return fail(ctx, UB_ERR_INVALID, "%s.weight is not [Cout,Cin,3,3]", conv_key.c_str());
+  GemmLayer L;
+  L.key = conv_key;
+  L.cout = static_cast<int>(w->shape[0]);
+  L.cin = static_cast<int>(w->shape[1]);
+  L.n_total = L.cout;
+  L.ksize = 3;
+  L.block_n = pick_block_n(L.n_total);
+  L.swz = (L.cin % 64 == 0) ? 128 : 64;
+  if (L.cin % 32 != 0 || L.cout % 32 != 0)
+    return fail(ctx, UB_ERR_UNSUPPORTED, "%s: channel counts must be multiples of 32", conv_key.c_str());
+  const size_t K = static_cast<size_t>(9) * L.cin;
+  std::vector<__nv_bfloat16> packed(static_cast<size_t>(L.cout) * K);
+  std::vector<float> bias(L.cout);
+  for (int co = 0; co < L.cout; ++co) {
+    const double s = static_cast<double>(g->data[co]) / std::sqrt(static_cast<double>(var->data[co]) + 1e-5);
+    bias[co] = static_cast<float>((static_cast<double>(b->data[co]) - mu->data[co]) * s + be->data[co]);
+    for (int ci = 0; ci < L.cin; ++ci)
+      for (int t = 0; t < 9; ++t)
+        packed[co * K + static_cast<size_t>(t) * L.cin + ci] =
+            __float2bfloat16(static_cast<float>(w->data[(static_cast<size_t>(co) * L.cin + ci) * 9 + t] * s));
+  }
+  int rc;
+  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.w), packed.size() * 2))) return rc;
+  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), bias.size() * 4))) return rc;
+  UB_CUDA(ctx, cudaMemcpy(L.w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
+  UB_CUDA(ctx, cudaMemcpy(L.bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
+  ctx->layer_by_key[L.key] = static_cast<int>(ctx->layers.size());
+  ctx->layers.push_back(L);
+  return UB_OK;
+}
+
+// ConvTranspose2d(k2,s2) weight [Cin,Cout,2,2] (processing_blocks.py:102) as GEMM B operand
+// W2[(a*2+b)*Cout + co][ci]: out[2i+a,2j+b,co] = sum_ci x[i,j,ci]*W[ci,co,a,b] + bias[co].
+int pack_convt(ub_ctx* ctx, const std::string& key) {
+  const HostTensor* w = find(ctx, key + ".weight");
+  const HostTensor* b = find(ctx, key + ".bias");
+  if (!w || !b) return fail(ctx, UB_ERR_INVALID, "missing state_dict entries for %s", key.c_str());
+  if (w->shape.size() != 4 || w->shape[2] != 2 || w->shape[3] != 2)
+    return fail(ctx, UB_ERR_INVALID, "%s.weight is not [Cin,Cout,2,2]", key.c_str());
+  GemmLayer L;
+  L.key = key;
+  L.is_convt = true;
+  L.cin = static_cast<int>(w->shape[0]);
+  L.cout = static_cast<int>(w->shape[1]);
+  L.n_total = 4 * L.cout;
+  L.ksize = 1;
+  L.relu = 0;
+  L.block_n = pick_block_n(L.n_total);
+  L.swz = (L.cin % 64 == 0) ? 128 : 64;
+  if (L.cin % 32 != 0 || L.cout % 32 != 0)
+    return fail(ctx, UB_ERR_UNSUPPORTED, "%s: channel counts must be multiples of 32", key.c_str());
+  std::vector<__nv_bfloat16> packed(static_cast<size_t>(L.n_total) * L.cin);
+  for (int ci = 0; ci < L.cin; ++ci)
+    for (int co = 0; co < L.cout; ++co)
+      for (int q = 0; q < 4; ++q)
+        packed[(static_cast<size_t>(q) * L.cout + co) * L.cin + ci] =
+            __float2bfloat16(w->data[(static_cast<size_t>(ci) * L.cout + co) * 4 + q]);
+  int rc;
+  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.w), packed.size() * 2))) return rc;
+  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), b->data.size() * 4))) return rc;
+  UB_CUDA(ctx, cudaMemcpy(L.w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
+  UB_CUDA(ctx, cudaMemcpy(L.bias, b->data.data(), b->data.size() * 4, cudaMemcpyHostToDevice));
+  ctx->layer_by_key[L.key] = static_cast<int>(ctx->layers.size());
+  ctx->layers.push_back(L);
+  return UB_OK;
+}
+
+int pack_all(ub_ctx* ctx) {
+  int rc;
+  const HostTensor* sw = find(ctx, "input.weight");
+  const HostTensor* sb = find(ctx, "input.bias");
+  const HostTensor* ow = find(ctx, "out.weight");
+  const HostTensor* ob = find(ctx, "out.bias");
+  if (!sw || !sb || !ow || !ob) return fail(ctx, UB_ERR_INVALID, "missing input.* / out.* entries");
+  if (sw->data.size() != 32 * 3 || sb->data.size() != 32)
+    return fail(ctx, UB_ERR_UNSUPPORTED, "stem must be Conv2d(3,32,1)");
+  if (static_cast<int>(ow->shape[0]) != ctx->n_classes || ow->shape[1] != 32)
+    return fail(ctx, UB_ERR_INVALID, "out.weight must be [%d,32,1,1]", ctx->n_classes);
+  memcpy(ctx->stem.w, sw->data.data(), sizeof(ctx->stem.w));
+  memcpy(ctx->stem.b, sb->data.data(), sizeof(ctx->stem.b));
+  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->head_w), ow->data.size() * 4))) return rc;
+  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->head_b), ob->data.size() * 4))) return rc;
+  UB_CUDA(ctx, cudaMemcpy(ctx->head_w, ow->data.data(), ow->data.size() * 4, cudaMemcpyHostToDevice));
+  UB_CUDA(ctx, cudaMemcpy(ctx->head_b, ob->data.data(), ob->data.size() * 4, cudaMemcpyHostToDevice));
+  char k[128];
+  for (int i = 1; i <= ctx->n_enc; ++i) {
+    snprintf(k, sizeof(k), "enc%d.block.0.conv", i);
+    if ((rc = pack_conv(ctx, std::string(k) + ".0", std::string(k) + ".1"))) return rc;
+    if ((rc = pack_conv(ctx, std::string(k) + ".3", std::string(k) + ".4"))) return rc;
+  }
+  if ((rc = pack_conv(ctx, "bottleneck.conv.0", "bottleneck.conv.1"))) return rc;
+  if ((rc = pack_conv(ctx, "bottleneck.conv.3", "bottleneck.conv.4"))) return rc;
+  for (int j = 1; j <= ctx->n_enc + 1; ++j) {
+    snprintf(k, sizeof(k), "dec%d", j);
+    if ((rc = pack_convt(ctx, std::string(k) + ".up"))) return rc;
+    if ((rc = pack_conv(ctx, std::string(k) + ".conv.conv.0", std::string(k) + ".conv.conv.1"))) return rc;
+    if ((rc = pack_conv(ctx, std::string(k) + ".conv.conv.3", std::string(k) + ".conv.conv.4"))) return rc;
+  }
+  ctx->weights_ready = true;
+  return UB_OK;
+}
+
+// ------------------------------------------------------------------ TMA descriptors
+int make_tm_act(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int c_view, int cstride, int W,
+                int H, int B, int box_rows, int swz) {
+  const cuuint64_t dims[4] = {static_cast<cuuint64_t>(c_view), static_cast<cuuint64_t>(W),
+                              static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(B)};
+  const cuuint64_t strides[3] = {static_cast<cuuint64_t>(cstride) * 2, static_cast<cuuint64_t>(W) * cstride * 2,
+                                 static_cast<cuuint64_t>(H) * W * cstride * 2};
+  const cuuint32_t box[4] = {static_cast<cuuint32_t>(swz / 2), ub::kTileCols, static_cast<cuuint32_t>(box_rows), 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<__nv_bfloat16*>(base), dims,
+                                 strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 swz == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ctx, UB_ERR_CUDA, "cuTensorMapEncodeTiled(activation) failed: %d", static_cast<int>(r));
+  return UB_OK;
+}
+int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total, int n_total, int block_n, int swz) {
+  const cuuint64_t dims[2] = {static_cast<cuuint64_t>(k_total), static_cast<cuuint64_t>(n_total)};
+  const cuuint64_t strides[1] = {static_cast<cuuint64_t>(k_total) * 2};
+  const cuuint32_t box[2] = {static_cast<cuuint32_t>(swz / 2), static_cast<cuuint32_t>(block_n)};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(w), dims, strides,
+                                 box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 swz == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ctx, UB_ERR_CUDA, "cuTensorMapEncodeTiled(weights) failed: %d", static_cast<int>(r));
+  return UB_OK;
+}
+
+// Static part of a GEMM step: descriptors over (src view) and the layer's packed weights.
+int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat16* src, int src_cstride,
+              int B, int H, int W, int mode, __nv_bfloat16* out, int out_cstride, int out_choff) {
+  memset(cp, 0, sizeof(*cp));
+  int rc;
+  const int pad = L.ksize / 2;
+  if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin, src_cstride, W, H, B, ub::kTileRows + 2 * pad, L.swz))) return rc;
+  if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, L.block_n, L.swz))) return rc;
+  cp->B = B; cp->H = H; cp->W = W;
+  cp->cin = L.cin; cp->ksize = L.ksize; cp->n_total = L.n_total;
+  cp->mode = mode; cp->relu = L.relu;
+  cp->bias = L.bias; cp->n_bias = L.cout;
+  cp->out = out; cp->out_cstride = out_cstride; cp->out_choff = out_choff; cp->cout = L.cout;
+  cp->head_w = ctx->head_w; cp->head_b = ctx->head_b; cp->n_classes = ctx->n_classes;
+  cp->ref_batch = 1;
+  return UB_OK;
+}
+
+template <int N, int S>
+int launch_inst(ub_ctx* ctx, const ConvParams& cp, cudaStream_t st) {
+  using Cfg = ub::ConvCfg<N, S>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  const int tiles = cp.B * ((cp.H + ub::kTileRows - 1) / ub::kTileRows) * ((cp.W + ub::kTileCols - 1) / ub::kTileCols) *
+                    (cp.n_total / N);
+  const int grid = tiles < ctx->num_sms ? tiles : ctx->num_sms;
+  ub::conv_tc_kernel<N, S><<<grid, ub::kConvThreads, Cfg::SMEM_BYTES, st>>>(cp);
+  UB_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return UB_OK;
+}
+
+int launch_gemm(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cudaStream_t st) {
+  if (cp.mode == ub::EPI_HEAD && block_n != 32) return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs 32 channels");
+  if (swz == 128) {
+    switch (block_n) {
+      case 32: return launch_inst<32, 128>(ctx, cp, st);
+      case 64: return launch_inst<64, 128>(ctx, cp, st);
+      case 128: return launch_inst<128, 128>(ctx, cp, st);
+      case 256: return launch_inst<256, 128>(ctx, cp, st);
+    }
+  } else {
+    switch (block_n) {
+      case 32: return launch_inst<32, 64>(ctx, cp, st);
+      case 64: return launch_inst<64, 64>(ctx, cp, st);
+      case 128: return launch_inst<128, 64>(ctx, cp, st);
+      case 256: return launch_inst<256, 64>(ctx, cp, st);
+    }
+  }
+  return fail(ctx, UB_ERR_UNSUPPORTED, "no kernel for BLOCK_N=%d swizzle=%d", block_n, swz);
+}
+
+// ------------------------------------------------------------------ execution plan for one resolution
+int skip_width(int level) { return level == 0 ? 32 : (32 << level); }
+
+int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
+  auto key = std::make_pair(H, W);
+  auto it = ctx->plans.find(key);
+  if (it != ctx->plans.end()) { *out = it->second.get(); return UB_OK; }
+  const int n = ctx->n_enc, MB = ctx->max_mb;
+  if (H % (1 << n) || W % (1 << n) || H < (2 << n) || W < (2 << n))
+    return fail(ctx, UB_ERR_UNSUPPORTED, "H and W must be multiples of %d and at least %d", 1 << n, 2 << n);
+  std::unique_ptr<Plan> pl(new Plan());
+  pl->H = H; pl->W = W;
+  std::vector<size_t> sizes;
+  auto want = [&](size_t bytes) { sizes.push_back((bytes + 1023) & ~static_cast<size_t>(1023)); return sizes.size() - 1; };
+  auto hl = [&](int l) { return H >> l; };
+  auto wl = [&](int l) { return W >> l; };
+  std::vector<size_t> i_cat(n + 1), i_enc(n + 1), i_da(n + 2), i_db(n + 2);
+  for (int l = 0; l <= n; ++l) i_cat[l] = want(static_cast<size_t>(MB) * hl(l) * wl(l) * 2 * skip_width(l) * 2);
+  for (int i = 1; i <= n; ++i) i_enc[i] = want(static_cast<size_t>(MB) * hl(i - 1) * wl(i - 1) * skip_width(i) * 2);
+  const int cb = 2 * skip_width(n);
+  const size_t i_ba = want(static_cast<size_t>(MB) * hl(n) * wl(n) * cb * 2);
+  const size_t i_bb = want(static_cast<size_t>(MB) * hl(n) * wl(n) * cb * 2);
+  const size_t i_up = want(static_cast<size_t>(MB) * 4 * hl(n) * wl(n) * skip_width(n) * 2);
+  for (int j = 1; j <= n + 1; ++j) {
+    const int l = n + 1 - j;
+    i_da[j] = want(static_cast<size_t>(MB) * hl(l) * wl(l) * skip_width(l) * 2);
+    i_db[j] = want(static_cast<size_t>(MB) * hl(l) * wl(l) * skip_width(l) * 2);
+  }
+  const size_t img_bytes = static_cast<size_t>(MB) * 3 * H * W * 4;
+  const size_t i_pert = want(img_bytes), i_bla = want(img_bytes), i_blb = want(img_bytes);
+  size_t total = 0;
+  std::vector<size_t> offs(sizes.size());
+  for (size_t i = 0; i < sizes.size(); ++i) { offs[i] = total; total += sizes[i]; }
+  int rc;
+  if ((rc = dev_alloc(ctx, &pl->arena, total))) return rc;
+  pl->arena_bytes = total;
+  UB_CUDA(ctx, cudaMemset(pl->arena, 0, total));
+  auto bufp = [&](size_t idx) { return reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(pl->arena) + offs[idx]); };
+  pl->pert_f32 = reinterpret_cast<float*>(bufp(i_pert));
+  pl->blur_a = bufp(i_bla);
+  pl->blur_b = bufp(i_blb);
+  pl->stem_out = bufp(i_cat[0]);
+  pl->stem_cstride = 2 * skip_width(0);
+  pl->stem_choff = skip_width(0);
+
+  auto add_gemm = [&](const std::string& lkey, const __nv_bfloat16* src, int src_cstride, int h, int w, int mode,
+                      __nv_bfloat16* dst, int dst_cstride, int dst_choff) -> int {
+    auto li = ctx->layer_by_key.find(lkey);
+    if (li == ctx->layer_by_key.end()) return fail(ctx, UB_ERR_STATE, "layer %s not packed", lkey.c_str());
+    Step s;
+    s.kind = Step::GEMM;
+    s.layer = li->second;
+    int r2 = fill_gemm(ctx, &s.cp, ctx->layers[s.layer], src, src_cstride, MB, h, w, mode, dst, dst_cstride, dst_choff);
+    if (r2) return r2;
+    pl->steps.push_back(s);
+    return UB_OK;
+  };
+  char k[128];
+  // encoder (models/UNet.py:63-65): conv.0 -> conv.3 + MaxPool into the skip half of the next concat buffer
+  for (int i = 1; i <= n; ++i) {
+    snprintf(k, sizeof(k), "enc%d.block.0.conv", i);
+    const int cs = 2 * skip_width(i - 1);
+    if ((rc = add_gemm(std::string(k) + ".0", bufp(i_cat[i - 1]) + skip_width(i - 1), cs, hl(i - 1), wl(i - 1),
+                       ub::EPI_STORE, bufp(i_enc[i]), skip_width(i), 0))) return rc;
+    if ((rc = add_gemm(std::string(k) + ".3", bufp(i_enc[i]), skip_width(i), hl(i - 1), wl(i - 1), ub::EPI_POOL,
+                       bufp(i_cat[i]), 2 * skip_width(i), skip_width(i)))) return rc;
+  }
+  // bottleneck (UNet.py:67), not pooled
+  if ((rc = add_gemm("bottleneck.conv.0", bufp(i_cat[n]) + skip_width(n), 2 * skip_width(n), hl(n), wl(n), ub::EPI_STORE,
+                     bufp(i_ba), cb, 0))) return rc;
+  if ((rc = add_gemm("bottleneck.conv.3", bufp(i_ba), cb, hl(n), wl(n), ub::EPI_STORE, bufp(i_bb), cb, 0))) return rc;
+  // decoder (UNet.py:69-72, processing_blocks.py:105-109)
+  const __nv_bfloat16* x = bufp(i_bb);
+  int xc = cb, xh = hl(n), xw = wl(n);
+  for (int j = 1; j <= n + 1; ++j) {
+    const int l = n + 1 - j;
+    snprintf(k, sizeof(k), "dec%d", j);
+    const int sw = skip_width(l);
+    (void)xc;
+    if (2 * xh == hl(l) && 2 * xw == wl(l)) {
+      // F.interpolate is the identity: ConvT scatters straight into channels [0,sw) of the concat buffer
+      if ((rc = add_gemm(std::string(k) + ".up", x, ctx->layers[ctx->layer_by_key[std::string(k) + ".up"]].cin, xh, xw,
+                         ub::EPI_CONVT, bufp(i_cat[l]), 2 * sw, 0))) return rc;
+    } else {
+      if ((rc = add_gemm(std::string(k) + ".up", x, ctx->layers[ctx->layer_by_key[std::string(k) + ".up"]].cin, xh, xw,
+                         ub::EPI_CONVT, bufp(i_up), sw, 0))) return rc;
+      Step s;
+      s.kind = Step::RESAMPLE;
+      s.rs_in = bufp(i_up); s.rs_out = bufp(i_cat[l]);
+      s.hi = 2 * xh; s.wi = 2 * xw; s.ho = hl(l); s.wo = wl(l); s.c = sw; s.out_cstride = 2 * sw; s.out_choff = 0;
+      pl->steps.push_back(s);
+    }
+    if ((rc = add_gemm(std::string(k) + ".conv.conv.0", bufp(i_cat[l]), 2 * sw, hl(l), wl(l), ub::EPI_STORE,
+                       bufp(i_da[j]), sw, 0))) return rc;
+    const bool last = (j == n + 1);
+    if ((rc = add_gemm(std::string(k) + ".conv.conv.3", bufp(i_da[j]), sw, hl(l), wl(l), last ? ub::EPI_HEAD : ub::EPI_STORE,
+                       bufp(i_db[j]), sw, 0))) return rc;
+    x = bufp(i_db[j]); xc = sw; xh = hl(l); xw = wl(l);
+  }
+  *out = pl.get();
+  ctx->plans[key] = std::move(pl);
+  return UB_OK;
+}
+}  // namespace
+namespace {
+
+int to_dev_perturb(ub_ctx* ctx, const ub_perturb* p, const void* aux, ub::PerturbDev* d) {
+  memset(d, 0, sizeof(*d));
+  if (!p) { d->kind = UB_P_NONE; return UB_OK; }
+  if (p->kind < UB_P_NONE || p->kind > UB_P_F_SALT_PEPPER) return fail(ctx, UB_ERR_INVALID, "unknown perturbation kind %d", p->kind);
+  if ((p->kind == UB_P_U8_BLUR || p->kind == UB_P_F_BLUR) && (p->iparam < 0 || p->iparam > 64))
+    return fail(ctx, UB_ERR_INVALID, "blur passes out of range: %d", p->iparam);
+  d->kind = p->kind; d->iparam = p->iparam; d->fparam = p->fparam; d->fparam2 = p->fparam2;
+  d->seed = p->seed; d->aux = aux;
+  memcpy(d->lut, p->lut, 256);
+  return UB_OK;
+}
+
+inline unsigned blocks_for(size_t n, int bs) { return static_cast<unsigned>((n + bs - 1) / bs); }
+
+// Blur families: quantise/load -> passes (ping-pong) -> fp32 NCHW in pl->pert_f32.
+int run_blur(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* img, int fmt, int n, float* dst, cudaStream_t st) {
+  const int H = pl->H, W = pl->W;
+  const size_t count = static_cast<size_t>(n) * 3 * H * W;
+  const unsigned g = blocks_for(count, 256);
+  if (P.kind == UB_P_U8_BLUR) {
+    uint8_t* a = static_cast<uint8_t*>(pl->blur_a);
+    uint8_t* b = static_cast<uint8_t*>(pl->blur_b);
+    ub::blur_u8_quantise_kernel<<<g, 256, 0, st>>>(img, fmt, n, H, W, a);
+    ctx->launches++;
+    for (int i = 0; i < P.iparam; ++i) {
+      ub::blur_u8_pass_kernel<<<g, 256, 0, st>>>(a, b, n * 3, H, W);
+      ctx->launches++;
+      std::swap(a, b);
+    }
+    ub::u8_planar_to_f32_kernel<<<g, 256, 0, st>>>(a, dst, count);
+    ctx->launches++;
+  } else {
+    float* a = static_cast<float*>(pl->blur_a);
+    float* b = static_cast<float*>(pl->blur_b);
+    if (P.iparam == 0) a = dst;
+    ub::blur_f_load_kernel<<<g, 256, 0, st>>>(img, fmt, n, H, W, a);
+    ctx->launches++;
+    for (int i = 0; i < P.iparam; ++i) {
+      float* o = (i == P.iparam - 1) ? dst : b;
+      ub::blur_f_pass_kernel<<<g, 256, 0, st>>>(a, o, n * 3, H, W);
+      ctx->launches++;
+      b = a; a = o;
+    }
+  }
+  UB_CUDA(ctx, cudaGetLastError());
+  return UB_OK;
+}
+
+struct HeadArgs {
+  const void* targets = nullptr; int target_fmt = 0; int ref_batch = 1; int img_base = 0;
+  unsigned long long* cm = nullptr; double* dice = nullptr; uint8_t* pred = nullptr; float* logits = nullptr;
+};
+
+// One micro-batch: perturb+stem, then every planned step.
+int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* img, int fmt, int nb,
+                   const HeadArgs& ha, float* perturbed_out, cudaStream_t st) {
+  const int H = pl->H, W = pl->W;
+  const size_t px = static_cast<size_t>(nb) * H * W;
+  int rc;
+  if (P.kind == UB_P_U8_BLUR || P.kind == UB_P_F_BLUR) {
+    float* dst = perturbed_out ? perturbed_out : pl->pert_f32;
+    if ((rc = run_blur(ctx, pl, P, img, fmt, nb, dst, st))) return rc;
+    ub::PerturbDev none;
+    memset(&none, 0, sizeof(none));
+    ub::stem_kernel<<<blocks_for(px, 256), 256, 0, st>>>(none, ctx->stem, dst, UB_IMG_F32_NCHW, nb, H, W, pl->stem_out,
+                                                        pl->stem_cstride, pl->stem_choff, nullptr);
+  } else {
+    ub::stem_kernel<<<blocks_for(px, 256), 256, 0, st>>>(P, ctx->stem, img, fmt, nb, H, W, pl->stem_out, pl->stem_cstride,
+                                                        pl->stem_choff, perturbed_out);
+  }
+  UB_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  for (Step& s : pl->steps) {
+    if (s.kind == Step::RESAMPLE) {
+      const size_t total = static_cast<size_t>(nb) * s.ho * s.wo * (s.c / 8);
+      ub::resample_bilinear_kernel<<<blocks_for(total, 256), 256, 0, st>>>(s.rs_in, nb, s.hi, s.wi, s.c, s.rs_out, s.ho, s.wo,
+                                                                           s.out_cstride, s.out_choff);
+      UB_CUDA(ctx, cudaGetLastError());
+      ctx->launches++;
+      continue;
+    }
+    ConvParams cp = s.cp;
+    cp.B = nb;
+    if (cp.mode == ub::EPI_HEAD) {
+      cp.targets = ha.targets; cp.target_fmt = ha.target_fmt; cp.ref_batch = ha.ref_batch; cp.img_base = ha.img_base;
+      cp.cm = ha.cm; cp.dice = ha.dice; cp.pred_out = ha.pred; cp.logits_out = ha.logits;
+    }
+    const GemmLayer& L = ctx->layers[s.layer];
+    if ((rc = launch_gemm(ctx, cp, L.block_n, L.swz, st))) return rc;
+  }
+  return UB_OK;
+}
+
+int check_ready(ub_ctx* ctx) {
+  if (!ctx) return UB_ERR_INVALID;
+  if (!ctx->weights_ready) return fail(ctx, UB_ERR_STATE, "ub_load_weights has not been called");
+  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  return UB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ub_abi_version(void) { return UB_ABI_VERSION; }
+
+int ub_make_lut(ub_perturb* p, int lut_kind, double param) {
+  if (!p) return UB_ERR_INVALID;
+  const float f = static_cast<float>(param);
+  for (int u = 0; u < 256; ++u) {
+    float v;
+    const float uf = static_cast<float>(u);
+    switch (lut_kind) {
+      case UB_LUT_CONTRAST: v = fminf(fmaxf(rintf(uf * f), 0.0f), 255.0f); break;
+      case UB_LUT_BRIGHTNESS_INCREASE: v = rintf(fminf(fmaxf(uf + f, 0.0f), 255.0f)); break;
+      case UB_LUT_BRIGHTNESS_DECREASE: v = fminf(fmaxf(rintf(uf - f), 0.0f), 255.0f); break;
+      default: return UB_ERR_INVALID;
+    }
+    p->lut[u] = static_cast<uint8_t>(v);
+  }
+  p->kind = UB_P_U8_LUT;
+  return UB_OK;
+}
+
+int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes, int max_microbatch) {
+  if (!out) return UB_ERR_INVALID;
+  *out = nullptr;
+  if (arch != UB_ARCH_UNET && arch != UB_ARCH_LARGE_UNET) return fail(nullptr, UB_ERR_INVALID, "unknown arch %d", arch);
+  if (in_channels != 3) return fail(nullptr, UB_ERR_UNSUPPORTED, "only in_channels=3 is supported");
+  if (n_classes < 1 || n_classes > ub::kMaxClasses) return fail(nullptr, UB_ERR_UNSUPPORTED, "n_classes must be 1..%d", ub::kMaxClasses);
+  if (max_microbatch < 1 || max_microbatch > 4096) return fail(nullptr, UB_ERR_INVALID, "max_microbatch out of range");
+  cudaDeviceProp prop;
+  cudaError_t e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) return fail(nullptr, UB_ERR_CUDA, "cudaGetDeviceProperties(%d): %s", device, cudaGetErrorString(e));
+  if (prop.major != 10)
+    return fail(nullptr, UB_ERR_UNSUPPORTED, "device %d is sm_%d%d; this library contains sm_100a code only (no fallback)",
+                device, prop.major, prop.minor);
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(nullptr, UB_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+  std::unique_ptr<ub_ctx> ctx(new ub_ctx());
+  ctx->device = device; ctx->arch = arch; ctx->in_ch = in_channels; ctx->n_classes = n_classes;
+  ctx->max_mb = max_microbatch; ctx->num_sms = prop.multiProcessorCount;
+  ctx->n_enc = arch == UB_ARCH_LARGE_UNET ? 4 : 3;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+    return fail(nullptr, UB_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  ctx->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  *out = ctx.release();
+  return UB_OK;
+}
+
+void ub_destroy(ub_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  for (void* p : ctx->owned) cudaFree(p);
+  delete ctx;
+}
+
+const char* ub_last_error(const ub_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+int64_t ub_launch_count(const ub_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int ub_load_weights(ub_ctx* ctx, int n, const char* const* names, const void* const* host_ptrs,
+                    const int64_t* const* shapes, const int* ndims) {
+  if (!ctx || n <= 0 || !names || !host_ptrs || !shapes || !ndims) return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  if (ctx->weights_ready) return fail(ctx, UB_ERR_STATE, "weights already loaded; create a new context");
+  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  for (int i = 0; i < n; ++i) {
+    std::string k(names[i]);
+    const std::string pre = "_orig_mod.";  // torch.compile prefix stripped by every reference loader
+    if (k.compare(0, pre.size(), pre) == 0) k = k.substr(pre.size());
+    if (k.size() > 19 && k.compare(k.size() - 19, 19, "num_batches_tracked") == 0) continue;
+    HostTensor t;
+    size_t cnt = 1;
+    for (int d = 0; d < ndims[i]; ++d) { t.shape.push_back(shapes[i][d]); cnt *= static_cast<size_t>(shapes[i][d]); }
+    t.data.assign(static_cast<const float*>(host_ptrs[i]), static_cast<const float*>(host_ptrs[i]) + cnt);
+    ctx->sd[k] = std::move(t);
+  }
+  const int rc = pack_all(ctx);
+  ctx->sd.clear();
+  return rc;
+}
+
+int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, const void* targets,
+                    int target_format, const void* aux, int n, int h, int w, int ref_batch, int64_t* cm,
+                    double* dice_sums, uint8_t* pred_out, float* logits_out, float* perturbed_out, void* stream) {
+  int rc;
+  if ((rc = check_ready(ctx))) return rc;
+  if (!images || n <= 0 || ref_batch <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  if (image_format != UB_IMG_F32_NCHW && image_format != UB_IMG_U8_NHWC) return fail(ctx, UB_ERR_INVALID, "bad image_format");
+  if (targets && !cm) return fail(ctx, UB_ERR_INVALID, "targets given without a confusion-matrix buffer");
+  if (dice_sums && !targets) return fail(ctx, UB_ERR_INVALID, "dice_sums needs targets");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Plan* pl;
+  if ((rc = build_plan(ctx, h, w, &pl))) return rc;
+  ub::PerturbDev P;
+  if ((rc = to_dev_perturb(ctx, p, aux, &P))) return rc;
+  const int C = ctx->n_classes;
+  const int n_batches = (n + ref_batch - 1) / ref_batch;
+  if (cm) UB_CUDA(ctx, cudaMemsetAsync(cm, 0, sizeof(int64_t) * n_batches * C * C, st));
+  if (dice_sums) UB_CUDA(ctx, cudaMemsetAsync(dice_sums, 0, sizeof(double) * n_batches * C * 3, st));
+  const size_t hw = static_cast<size_t>(h) * w;
+  const size_t img_stride = image_format == UB_IMG_U8_NHWC ? hw * 3 : hw * 3 * 4;
+  const size_t tgt_stride = target_format == UB_TGT_U8 ? hw : hw * 8;
+  for (int i0 = 0; i0 < n; i0 += ctx->max_mb) {
+    const int nb = (n - i0) < ctx->max_mb ? (n - i0) : ctx->max_mb;
+    ub::PerturbDev Pm = P;
+    if (aux) {
+      size_t per_img = 0;
+      switch (P.kind) {
+        case UB_P_U8_NOISE: case UB_P_F_NOISE: per_img = hw * 3 * 4; break;
+        case UB_P_U8_OCCLUSION: case UB_P_F_OCCLUSION: per_img = 8; break;
+        case UB_P_U8_SALT_PEPPER: per_img = hw; break;
+        case UB_P_F_SALT_PEPPER: per_img = hw * 4; break;
+        default: break;
+      }
+      Pm.aux = static_cast<const uint8_t*>(aux) + per_img * i0;
+    }
+    // device RNG: decorrelate micro-batches
+    Pm.seed = P.seed + 0x9E3779B97F4A7C15ull * static_cast<unsigned long long>(i0);
+    HeadArgs ha;
+    ha.targets = targets ? static_cast<const uint8_t*>(targets) + tgt_stride * i0 : nullptr;
+    ha.target_fmt = target_format; ha.ref_batch = ref_batch; ha.img_base = i0;
+    ha.cm = reinterpret_cast<unsigned long long*>(cm);
+    ha.dice = dice_sums;
+    ha.pred = pred_out ? pred_out + hw * i0 : nullptr;
+    ha.logits = logits_out ? logits_out + hw * C * i0 : nullptr;
+    if ((rc = run_microbatch(ctx, pl, Pm, static_cast<const uint8_t*>(images) + img_stride * i0, image_format, nb, ha,
+                             perturbed_out ? perturbed_out + hw * 3 * i0 : nullptr, st)))
+      return rc;
+  }
+  if (dice_sums) {
+    ub::dice_tsum_kernel<<<blocks_for(static_cast<size_t>(n_batches) * C, 128), 128, 0, st>>>(
+        reinterpret_cast<const unsigned long long*>(cm), dice_sums, n_batches, C);
+    UB_CUDA(ctx, cudaGetLastError());
+    ctx->launches++;
+  }
+  return UB_OK;
+}
+
+int ub_forward(ub_ctx* ctx, const float* x_nchw, float* logits_nchw, int n, int h, int w, void* stream) {
+  if (!logits_nchw) return fail(ctx, UB_ERR_INVALID, "logits buffer is null");
+  return ub_eval_batches(ctx, nullptr, x_nchw, UB_IMG_F32_NCHW, nullptr, UB_TGT_I64, nullptr, n, h, w, 1, nullptr, nullptr,
+                         nullptr, logits_nchw, nullptr, stream);
+}
+
+int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, const void* aux, int n,
+                      int h, int w, float* out_nchw, void* stream) {
+  if (!ctx) return UB_ERR_INVALID;
+  if (!images || !out_nchw || n <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ub::PerturbDev P;
+  int rc;
+  if ((rc = to_dev_perturb(ctx, p, aux, &P))) return rc;
+  const size_t hw = static_cast<size_t>(h) * w;
+  if (P.kind == UB_P_U8_BLUR || P.kind == UB_P_F_BLUR) {
+    // needs ping-pong planes: allocate per call on the stream (not on the evaluation hot path)
+    void *a = nullptr, *b = nullptr;
+    const size_t bytes = static_cast<size_t>(n) * 3 * hw * 4;
+    UB_CUDA(ctx, cudaMallocAsync(&a, bytes, st));
+    UB_CUDA(ctx, cudaMallocAsync(&b, bytes, st));
+    Plan tmp;
+    tmp.H = h; tmp.W = w; tmp.blur_a = a; tmp.blur_b = b;
+    rc = run_blur(ctx, &tmp, P, images, image_format, n, out_nchw, st);
+    cudaFreeAsync(a, st);
+    cudaFreeAsync(b, st);
+    return rc;
+  }
+  ub::perturb_kernel<<<blocks_for(hw * n, 256), 256, 0, st>>>(P, images, image_format, n, h, w, out_nchw);
+  UB_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return UB_OK;
+}
+
+int ub_metrics(ub_ctx* ctx, const float* logits_nchw, const void* targets, int target_format, int n, int n_classes,
+               int h, int w, int ref_batch, int64_t* cm, double* dice_sums, void* stream) {
+  if (!ctx) return UB_ERR_INVALID;
+  if (!logits_nchw || !targets || !cm || n <= 0 || ref_batch <= 0 || n_classes < 1 || n_classes > ub::kMaxClasses)
+    return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int n_batches = (n + ref_batch - 1) / ref_batch;
+  UB_CUDA(ctx, cudaMemsetAsync(cm, 0, sizeof(int64_t) * n_batches * n_classes * n_classes, st));
+  if (dice_sums) UB_CUDA(ctx, cudaMemsetAsync(dice_sums, 0, sizeof(double) * n_batches * n_classes * 3, st));
+  dim3 grid(blocks_for(static_cast<size_t>(h) * w, 256), n);
+  ub::metrics_kernel<<<grid, 256, 0, st>>>(logits_nchw, targets, target_format, n_classes, h, w, ref_batch,
+                                           reinterpret_cast<unsigned long long*>(cm), dice_sums);
+  UB_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  if (dice_sums) {
+    ub::dice_tsum_kernel<<<blocks_for(static_cast<size_t>(n_batches) * n_classes, 128), 128, 0, st>>>(
+        reinterpret_cast<const unsigned long long*>(cm), dice_sums, n_batches, n_classes);
+    UB_CUDA(ctx, cudaGetLastError());
+    ctx->launches++;
+  }
+  return UB_OK;
+}
+
+static int debug_layer(ub_ctx* ctx, const char* key, const void* in, void* out, int n, int h, int w, int mode, void* stream) {
+  int rc;
+  if ((rc = check_ready(ctx))) return rc;
+  if (!key || !in || !out || n <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  auto it = ctx->layer_by_key.find(key);
+  if (it == ctx->layer_by_key.end()) return fail(ctx, UB_ERR_INVALID, "no such layer: %s", key);
+  const GemmLayer& L = ctx->layers[it->second];
+  ConvParams cp;
+  if ((rc = fill_gemm(ctx, &cp, L, static_cast<const __nv_bfloat16*>(in), L.cin, n, h, w, mode,
+                      static_cast<__nv_bfloat16*>(out), L.cout, 0)))
+    return rc;
+  return launch_gemm(ctx, cp, L.block_n, L.swz, static_cast<cudaStream_t>(stream));
+}
+
+int ub_debug_conv3x3(ub_ctx* ctx, const char* conv_key, const void* in_bf16_nhwc, void* out_bf16_nhwc, int n, int h,
+                     int w, int pool, void* stream) {
+  if (ctx && conv_key) {
+    auto it = ctx->layer_by_key.find(conv_key);
+    if (it != ctx->layer_by_key.end() && ctx->layers[it->second].is_convt) return fail(ctx, UB_ERR_INVALID, "%s is a ConvTranspose", conv_key);
+  }
+  return debug_layer(ctx, conv_key, in_bf16_nhwc, out_bf16_nhwc, n, h, w, pool ? ub::EPI_POOL : ub::EPI_STORE, stream);
+}
+
+int ub_debug_convt2x2(ub_ctx* ctx, const char* up_key, const void* in_bf16_nhwc, void* out_bf16_nhwc, int n, int h,
+                      int w, void* stream) {
+  if (ctx && up_key) {
+    auto it = ctx->layer_by_key.find(up_key);
+    if (it != ctx->layer_by_key.end() && !ctx->layers[it->second].is_convt) return fail(ctx, UB_ERR_INVALID, "%s is not a ConvTranspose", up_key);
+  }
+  return debug_layer(ctx, up_key, in_bf16_nhwc, out_bf16_nhwc, n, h, w, ub::EPI_CONVT, stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,140 @@
+// ub_aux.cuh — the small HBM-bound kernels around the tensor-core GEMMs.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ub {
+
+// F.interpolate(mode="bilinear", align_corners=True), models/processing_blocks.py:107.  Only dec1
+// needs it for real (ConvT doubles the un-pooled bottleneck to 2x the skip size; this brings it
+// back); elsewhere input and output sizes agree and the ConvT epilogue writes the concat buffer
+// directly.  NHWC bf16; one thread per (output pixel, 8 channels) -> 16-byte loads and stores.
+__global__ void resample_bilinear_kernel(const __nv_bfloat16* __restrict__ in, int n, int Hi, int Wi,
+                                         int C, __nv_bfloat16* __restrict__ out, int Ho, int Wo,
+                                         int out_cstride, int out_choff) {
+  const int groups = C / 8;
+  const size_t total = static_cast<size_t>(n) * Ho * Wo * groups;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int g = static_cast<int>(i % groups);
+  size_t r = i / groups;
+  const int ox = static_cast<int>(r % Wo);
+  r /= Wo;
+  const int oy = static_cast<int>(r % Ho);
+  const int b = static_cast<int>(r / Ho);
+  const float sy = Ho > 1 ? static_cast<float>(Hi - 1) / static_cast<float>(Ho - 1) : 0.0f;
+  const float sx = Wo > 1 ? static_cast<float>(Wi - 1) / static_cast<float>(Wo - 1) : 0.0f;
+  const float fy = sy * oy, fx = sx * ox;
+  const int y0 = static_cast<int>(fy), x0 = static_cast<int>(fx);
+  const int y1 = y0 + (y0 < Hi - 1 ? 1 : 0), x1 = x0 + (x0 < Wi - 1 ? 1 : 0);
+  const float ly = fy - y0, lx = fx - x0;
+  const float hy = 1.0f - ly, hx = 1.0f - lx;
+  auto ld = [&](int yy, int xx) {
+    return *reinterpret_cast<const uint4*>(in + ((static_cast<size_t>(b) * Hi + yy) * Wi + xx) * C + g * 8);
+  };
+  const uint4 v00 = ld(y0, x0), v01 = ld(y0, x1), v10 = ld(y1, x0), v11 = ld(y1, x1);
+  const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&v00);
+  const __nv_bfloat162* bq = reinterpret_cast<const __nv_bfloat162*>(&v01);
+  const __nv_bfloat162* c = reinterpret_cast<const __nv_bfloat162*>(&v10);
+  const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(&v11);
+  uint4 o;
+  __nv_bfloat162* op = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 fa = __bfloat1622float2(a[k]), fb = __bfloat1622float2(bq[k]);
+    const float2 fc = __bfloat1622float2(c[k]), fd = __bfloat1622float2(d[k]);
+    const float r0 = hy * (hx * fa.x + lx * fb.x) + ly * (hx * fc.x + lx * fd.x);
+    const float r1 = hy * (hx * fa.y + lx * fb.y) + ly * (hx * fc.y + lx * fd.y);
+    op[k] = __floats2bfloat162_rn(r0, r1);
+  }
+  *reinterpret_cast<uint4*>(out + ((static_cast<size_t>(b) * Ho + oy) * Wo + ox) * out_cstride + out_choff + g * 8) = o;
+}
+
+// Layout converters for the test hooks (NCHW fp32 <-> NHWC bf16 are done by the caller in torch);
+// nothing needed here.
+
+// Metrics from materialised logits (models/losses.py:43-63, :133-154, :98-100): softmax -> argmax ->
+// warp-aggregated counts into a shared-memory int64 histogram -> one global atomic per cell per block.
+// grid = (ceil(H*W/256), n); image b belongs to reference batch b / ref_batch.
+__global__ void __launch_bounds__(256)
+metrics_kernel(const float* __restrict__ logits, const void* __restrict__ targets, int target_fmt, int C,
+               int H, int W, int ref_batch, unsigned long long* cm, double* dice) {
+  __shared__ unsigned long long s_cm[16];
+  __shared__ double s_dice[8];
+  if (threadIdx.x < 16) s_cm[threadIdx.x] = 0ull;
+  if (threadIdx.x < 8) s_dice[threadIdx.x] = 0.0;
+  __syncthreads();
+  const int b = blockIdx.y;
+  const size_t hw = static_cast<size_t>(H) * W;
+  const size_t pix = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const bool inb = pix < hw;
+  const int lane = threadIdx.x & 31;
+  float z[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  int tgt = -1;
+  if (inb) {
+    for (int c = 0; c < C; ++c) z[c] = logits[(static_cast<size_t>(b) * C + c) * hw + pix];
+    tgt = target_fmt == 1 ? static_cast<int>(reinterpret_cast<const uint8_t*>(targets)[b * hw + pix])
+                          : static_cast<int>(reinterpret_cast<const long long*>(targets)[b * hw + pix]);
+    if (tgt < 0 || tgt >= C) tgt = -1;
+  }
+  float zmax = fmaxf(fmaxf(z[0], z[1]), fmaxf(z[2], z[3]));
+  float pr[4], psum = 0.0f;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) { pr[c] = (inb && c < C) ? expf(z[c] - zmax) : 0.0f; psum += pr[c]; }
+  int pred = 0;
+  float best = -1.0f;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    pr[c] = inb ? pr[c] / psum : 0.0f;
+    if (c < C && pr[c] > best) { best = pr[c]; pred = c; }
+  }
+  const int cell = tgt >= 0 ? tgt * C + pred : -1;
+  for (int i = 0; i < C * C; ++i) {
+    const unsigned bal = __ballot_sync(0xffffffffu, cell == i);
+    if (lane == 0 && bal) atomicAdd(&s_cm[i], static_cast<unsigned long long>(__popc(bal)));
+  }
+  if (dice) {
+    float qmax = pr[0];
+#pragma unroll
+    for (int c = 1; c < 4; ++c) if (c < C) qmax = fmaxf(qmax, pr[c]);
+    float q[4], qsum = 0.0f;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { q[c] = c < C ? expf(pr[c] - qmax) : 0.0f; qsum += q[c]; }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float pc = (inb && c < C) ? q[c] / qsum : 0.0f;
+      float ic = tgt == c ? pc : 0.0f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        pc += __shfl_xor_sync(0xffffffffu, pc, o);
+        ic += __shfl_xor_sync(0xffffffffu, ic, o);
+      }
+      if (lane == 0 && c < C) {
+        atomicAdd(&s_dice[c * 2], static_cast<double>(ic));
+        atomicAdd(&s_dice[c * 2 + 1], static_cast<double>(pc));
+      }
+    }
+  }
+  __syncthreads();
+  const int batch = b / ref_batch;
+  if (threadIdx.x < C * C) {
+    const unsigned long long v = s_cm[threadIdx.x];
+    if (v) atomicAdd(&cm[static_cast<size_t>(batch) * C * C + threadIdx.x], v);
+  } else if (dice && threadIdx.x >= 32 && threadIdx.x < 32 + 2 * C) {
+    const int i = threadIdx.x - 32;
+    atomicAdd(&dice[(static_cast<size_t>(batch) * C + (i >> 1)) * 3 + (i & 1)], s_dice[i]);
+  }
+}
+
+// dice_sums[..][2] = sum 1[t=c] = row sums of the confusion matrix (exact integers).
+__global__ void dice_tsum_kernel(const unsigned long long* cm, double* dice, int n_batches, int C) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_batches * C) return;
+  const int bt = i / C, c = i % C;
+  unsigned long long s = 0;
+  for (int pcol = 0; pcol < C; ++pcol) s += cm[(static_cast<size_t>(bt) * C + c) * C + pcol];
+  dice[static_cast<size_t>(i) * 3 + 2] = static_cast<double>(s);
+}
+
+}  // namespace ub

@@ -1,0 +1,235 @@
+// ub_conv_tc.cuh — the tensor-core kernel of the path: conv3x3(pad 1)+foldedBN+ReLU as an implicit
+// GEMM on tcgen05 with TMEM accumulators, fed by TMA from NHWC bf16 activations.  The same kernel
+// (taps = 1) is the ConvTranspose2d(k2,s2) GEMM with a pixel-shuffle scatter epilogue, and with
+// the HEAD epilogue it fuses the final 1x1 conv, softmax/argmax and the confusion-matrix histogram.
+//
+// Replaces: models/processing_blocks.py:43-48 (Conv2d+BatchNorm2d+ReLU), :73 (MaxPool2d, POOL
+// epilogue), :102 (ConvTranspose2d), :108 (cat: operands live in one concat buffer), models/UNet.py:73
+// (out 1x1) and models/losses.py:48-58 (softmax/argmax/counts).
+//
+// GEMM view:  D[M = 128 pixels (8 rows x 16 cols of one image)][N = BLOCK_N output channels]
+//             K = taps * Cin, walked as (channel chunk c) x (kx) x (ky) x (BK/16 MMAs).
+// A operand:  one TMA box {BK ch, 16 px, 8+2 rows} per (c, kx) — the three ky taps reuse it by
+//             moving the UMMA descriptor start address down one tile row (16 px * BK * 2 bytes, a
+//             multiple of the swizzle atom), so activations are fetched 3.75x instead of 9x.
+//             Out-of-image halo pixels are zero-filled by TMA = the conv's zero padding.
+// B operand:  weights W2[N][K] (K contiguous), one TMA box {BK, BLOCK_N} per (c, kx, ky).
+// Warp roles (256 threads): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-7 epilogue.
+// Two TMEM accumulators so the epilogue of tile i overlaps the MMAs of tile i+1 (persistent CTAs).
+#pragma once
+#include "ub_ptx.cuh"
+
+namespace ub {
+
+enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_CONVT = 2, EPI_HEAD = 3 };
+
+constexpr int kTileRows = 8;
+constexpr int kTileCols = 16;
+constexpr int kTileM = 128;
+constexpr int kConvThreads = 256;
+constexpr int kMaxClasses = 4;
+
+struct ConvParams {
+  CUtensorMap tmA;  // activations: dims {C, W, H, B}, box {BK, 16, 8 + 2*pad, 1}
+  CUtensorMap tmB;  // weights:     dims {Ktot, Ntot}, box {BK, BLOCK_N}
+  int B, H, W;      // input extent (= output extent for conv; output is 2H x 2W for ConvT)
+  int cin;          // channels of the A source = K per tap
+  int ksize;        // 3 or 1
+  int n_total;      // GEMM N (Cout, or 4*Cout for ConvT)
+  int mode;         // EpiMode
+  int relu;
+  const float* bias;  // [n_total] (conv) / [cout] (ConvT)
+  int n_bias;
+  __nv_bfloat16* out;  // NHWC bf16
+  int out_cstride;     // channels per pixel of the output buffer (concat buffers are wider)
+  int out_choff;       // first channel written
+  int cout;            // ConvT: channels per 2x2 quadrant
+  // HEAD epilogue
+  const float* head_w;  // [n_classes][32]
+  const float* head_b;  // [n_classes]
+  int n_classes;
+  const void* targets;  // uint8 or int64 [B,H,W], may be null (no counts)
+  int target_fmt;       // 0 = int64, 1 = uint8
+  int ref_batch;        // images per reference batch
+  int img_base;         // index (within the whole call) of image 0 of this micro-batch
+  unsigned long long* cm;  // [n_batches][C][C]
+  double* dice;            // [n_batches][C][3] or null
+  uint8_t* pred_out;       // [B,H,W] or null
+  float* logits_out;       // [B,C,H,W] or null
+};
+
+template <int BLOCK_N, int SWZ>
+struct ConvCfg {
+  static constexpr int BK = SWZ / 2;  // bf16 channels per K chunk
+  static constexpr int A_ROW_BYTES = kTileCols * SWZ;                 // one tile row of pixels
+  static constexpr int A_STAGE_BYTES = (kTileRows + 2) * A_ROW_BYTES; // 10 rows
+  static constexpr int B_STAGE_BYTES = BLOCK_N * SWZ;
+  static constexpr int SA = 3;
+  static constexpr int RING_BUDGET = 222 * 1024;
+  static constexpr int SB_RAW = (RING_BUDGET - SA * A_STAGE_BYTES) / B_STAGE_BYTES;
+  static constexpr int SB = SB_RAW > 8 ? 8 : SB_RAW;
+  static constexpr int TMEM_COLS = (2 * BLOCK_N) < 32 ? 32 : (2 * BLOCK_N);
+  static constexpr int OFF_B = SA * A_STAGE_BYTES;
+  static constexpr int OFF_BIAS = OFF_B + SB * B_STAGE_BYTES;
+  static constexpr int OFF_HEAD = OFF_BIAS + 1024 * 4;
+  static constexpr int OFF_BAR = OFF_HEAD + (kMaxClasses * 32 + kMaxClasses) * 4;
+  static constexpr int N_BARS = 2 * SA + 2 * SB + 4;
+  static constexpr int OFF_CM = OFF_BAR + N_BARS * 8;
+  static constexpr int OFF_DICE = OFF_CM + kMaxClasses * kMaxClasses * 8;
+  static constexpr int OFF_TMEM = OFF_DICE + kMaxClasses * 2 * 8;
+  static constexpr int SMEM_BYTES = OFF_TMEM + 16 + 1024;  // + slack for 1024B alignment
+  static_assert(SB >= 2, "B ring too shallow");
+  static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns");
+  static_assert(A_STAGE_BYTES % 1024 == 0 && B_STAGE_BYTES % 1024 == 0, "swizzle atom alignment");
+};
+
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <int BLOCK_N, int SWZ>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_tc_kernel(const __grid_constant__ ConvParams p) {
+  using Cfg = ConvCfg<BLOCK_N, SWZ>;
+  constexpr int BK = Cfg::BK;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* a_ring = smem;
+  uint8_t* b_ring = smem + Cfg::OFF_B;
+  float* s_bias = reinterpret_cast<float*>(smem + Cfg::OFF_BIAS);
+  float* s_head = reinterpret_cast<float*>(smem + Cfg::OFF_HEAD);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  uint64_t* a_full = bars;
+  uint64_t* a_empty = bars + Cfg::SA;
+  uint64_t* b_full = bars + 2 * Cfg::SA;
+  uint64_t* b_empty = bars + 2 * Cfg::SA + Cfg::SB;
+  uint64_t* t_full = bars + 2 * Cfg::SA + 2 * Cfg::SB;
+  uint64_t* t_empty = t_full + 2;
+  unsigned long long* s_cm = reinterpret_cast<unsigned long long*>(smem + Cfg::OFF_CM);
+  double* s_dice = reinterpret_cast<double*>(smem + Cfg::OFF_DICE);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_TMEM);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int pad = p.ksize >> 1;
+  const int tiles_x = (p.W + kTileCols - 1) / kTileCols;
+  const int tiles_y = (p.H + kTileRows - 1) / kTileRows;
+  const int n_tiles = p.n_total / BLOCK_N;
+  const int total_tiles = p.B * tiles_x * tiles_y * n_tiles;
+  const int k_chunks = p.cin / BK;
+  const uint32_t a_bytes = static_cast<uint32_t>((kTileRows + 2 * pad) * Cfg::A_ROW_BYTES);
+
+  // ---------------- one-time setup
+  for (int i = threadIdx.x; i < p.n_bias; i += kConvThreads) s_bias[i] = p.bias[i];
+  if (p.mode == EPI_HEAD) {
+    for (int i = threadIdx.x; i < p.n_classes * 32; i += kConvThreads) s_head[i] = p.head_w[i];
+    if (threadIdx.x < p.n_classes) s_head[kMaxClasses * 32 + threadIdx.x] = p.head_b[threadIdx.x];
+    if (threadIdx.x < kMaxClasses * kMaxClasses) s_cm[threadIdx.x] = 0ull;
+    if (threadIdx.x < kMaxClasses * 2) s_dice[threadIdx.x] = 0.0;
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmA);
+    tma_prefetch_desc(&p.tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < Cfg::SA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < Cfg::SB; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 128); }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(s_tmem, Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0 && lane == 0) {
+    // ================= TMA producer =================
+    int sa = 0, sb = 0;
+    uint32_t pa = 0, pb = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int nt = t % n_tiles;
+      int m = t / n_tiles;
+      const int x0 = (m % tiles_x) * kTileCols;
+      m /= tiles_x;
+      const int y0 = (m % tiles_y) * kTileRows;
+      const int b = m / tiles_y;
+      for (int c = 0; c < k_chunks; ++c) {
+        for (int kx = 0; kx < p.ksize; ++kx) {
+          mbar_wait(&a_empty[sa], pa ^ 1u);
+          mbar_arrive_expect_tx(&a_full[sa], a_bytes);
+          tma_load_4d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], c * BK, x0 + kx - pad,
+                      y0 - pad, b);
+          if (++sa == Cfg::SA) { sa = 0; pa ^= 1u; }
+          for (int ky = 0; ky < p.ksize; ++ky) {
+            mbar_wait(&b_empty[sb], pb ^ 1u);
+            mbar_arrive_expect_tx(&b_full[sb], Cfg::B_STAGE_BYTES);
+            tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb],
+                        (ky * p.ksize + kx) * p.cin + c * BK, nt * BLOCK_N);
+            if (++sb == Cfg::SB) { sb = 0; pb ^= 1u; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ================= MMA issuer (single thread) =================
+    constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
+    int sa = 0, sb = 0;
+    uint32_t pa = 0, pb = 0;
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t use = static_cast<uint32_t>(it >> 1);
+      mbar_wait(&t_empty[acc], (use & 1u) ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BLOCK_N);
+      uint32_t accumulate = 0;
+      for (int c = 0; c < k_chunks; ++c) {
+        for (int kx = 0; kx < p.ksize; ++kx) {
+          mbar_wait(&a_full[sa], pa);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(a_ring + sa * Cfg::A_STAGE_BYTES);
+          for (int ky = 0; ky < p.ksize; ++ky) {
+            mbar_wait(&b_full[sb], pb);
+            tc_fence_after();
+            const uint32_t a_addr = a_base + static_cast<uint32_t>(ky * Cfg::A_ROW_BYTES);
+            const uint32_t b_addr = smem_u32(b_ring + sb * Cfg::B_STAGE_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              umma_bf16(d_tmem, umma_smem_desc<SWZ>(a_addr + k * 32), umma_smem_desc<SWZ>(b_addr + k * 32),
+                        idesc, accumulate);
+              accumulate = 1;
+            }
+            umma_commit(&b_empty[sb]);
+            if (++sb == Cfg::SB) { sb = 0; pb ^= 1u; }
+          }
+          umma_commit(&a_empty[sa]);
+          if (++sa == Cfg::SA) { sa = 0; pa ^= 1u; }
+        }
+      }
+      umma_commit(&t_full[acc]);
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue (128 threads; warp w owns TMEM lanes 32*(w-4)..) =================
+#include "ub_conv_epilogue.inl"
+  }
+
+  // ---------------- teardown
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+}  // namespace ub

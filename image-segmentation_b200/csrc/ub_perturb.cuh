@@ -1,0 +1,274 @@
+// ub_perturb.cuh — perturbations (both reference families) + the 1x1 stem conv that consumes them.
+//   uint8-space Dataset wrappers : customDatasets/perturbations.py  (exact integer arithmetic)
+//   float-space nn.Modules       : models/processing_blocks.py:454-592 (fp32, no FMA contraction)
+//   stem                         : models/UNet.py:39,62  nn.Conv2d(3,32,1)
+// Pointwise families are evaluated inside the stem's input load (no intermediate image in HBM);
+// the two blur families need neighbours and run as short ping-pong passes first.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/unet_b200.h"
+
+namespace ub {
+
+struct PerturbDev {
+  int kind;
+  int iparam;
+  float fparam;
+  float fparam2;
+  unsigned long long seed;
+  const void* aux;
+  uint8_t lut[256];
+};
+
+// ---- counter-based RNG (Philox4x32-10) for throughput mode (aux == NULL)
+__device__ __forceinline__ uint4 philox4x32(uint4 c, uint2 k) {
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+__device__ __forceinline__ uint4 rng4(unsigned long long seed, uint32_t a, uint32_t b, uint32_t c) {
+  return philox4x32(make_uint4(a, b, c, 0x5eed5eedu),
+                    make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32)));
+}
+__device__ __forceinline__ float u01(uint32_t r) { return (static_cast<float>(r >> 8) + 0.5f) * (1.0f / 16777216.0f); }
+__device__ __forceinline__ float normal_from(uint32_t r0, uint32_t r1) {
+  return sqrtf(-2.0f * logf(u01(r0))) * cospif(2.0f * u01(r1));
+}
+
+__device__ __forceinline__ float clamp01(float v) { return fminf(fmaxf(v, 0.0f), 1.0f); }
+
+// Raw pixel channel as the dataset would hand it over: fp32 in [0,1].
+__device__ __forceinline__ float load_f(const void* img, int fmt, int b, int c, int y, int x, int H, int W) {
+  if (fmt == UB_IMG_F32_NCHW)
+    return reinterpret_cast<const float*>(img)[((static_cast<size_t>(b) * 3 + c) * H + y) * W + x];
+  const uint8_t u = reinterpret_cast<const uint8_t*>(img)[((static_cast<size_t>(b) * H + y) * W + x) * 3 + c];
+  return static_cast<float>(u) / 255.0f;
+}
+// (image*255).round().clamp(0,255).to(uint8)  — perturbations.py:34 etc.
+__device__ __forceinline__ int load_u8(const void* img, int fmt, int b, int c, int y, int x, int H, int W) {
+  if (fmt == UB_IMG_U8_NHWC)
+    return reinterpret_cast<const uint8_t*>(img)[((static_cast<size_t>(b) * H + y) * W + x) * 3 + c];
+  const float v = reinterpret_cast<const float*>(img)[((static_cast<size_t>(b) * 3 + c) * H + y) * W + x];
+  return static_cast<int>(fminf(fmaxf(rintf(__fmul_rn(v, 255.0f)), 0.0f), 255.0f));
+}
+
+// One pixel (all 3 channels) of the perturbed network input, for every family except the blurs.
+__device__ __forceinline__ void perturbed_pixel(const PerturbDev& P, const void* img, int fmt, int b,
+                                                int y, int x, int H, int W, float (&out)[3]) {
+  const size_t hw = static_cast<size_t>(H) * W;
+  const size_t pix = static_cast<size_t>(y) * W + x;
+  switch (P.kind) {
+    default:
+    case UB_P_NONE:
+#pragma unroll
+      for (int c = 0; c < 3; ++c) out[c] = load_f(img, fmt, b, c, y, x, H, W);
+      break;
+    case UB_P_U8_NOISE: {
+      uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
+      if (!P.aux) { r0 = rng4(P.seed, static_cast<uint32_t>(pix), b, 1); r1 = rng4(P.seed, static_cast<uint32_t>(pix), b, 2); }
+      const uint32_t rr[6] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y};
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float nz = P.aux ? reinterpret_cast<const float*>(P.aux)[(static_cast<size_t>(b) * 3 + c) * hw + pix]
+                               : __fmul_rn(P.fparam, normal_from(rr[2 * c], rr[2 * c + 1]));
+        const float v = __fadd_rn(static_cast<float>(load_u8(img, fmt, b, c, y, x, H, W)), nz);
+        out[c] = rintf(fminf(fmaxf(v, 0.0f), 255.0f)) / 255.0f;  // clamp then round, :45
+      }
+    } break;
+    case UB_P_U8_LUT:
+#pragma unroll
+      for (int c = 0; c < 3; ++c) out[c] = static_cast<float>(P.lut[load_u8(img, fmt, b, c, y, x, H, W)]) / 255.0f;
+      break;
+    case UB_P_U8_OCCLUSION:
+    case UB_P_F_OCCLUSION: {
+      const int s = P.iparam;
+      int y0, x0;
+      if (P.aux) {
+        y0 = reinterpret_cast<const int*>(P.aux)[2 * b];
+        x0 = reinterpret_cast<const int*>(P.aux)[2 * b + 1];
+      } else {
+        const uint4 r = rng4(P.seed, 0u, b, 3);
+        const bool draw = P.kind == UB_P_F_OCCLUSION ? true : (s > 0 && H - s > 0 && W - s > 0);
+        y0 = draw ? (H > s ? static_cast<int>(r.x % static_cast<uint32_t>(H - s + 1)) : 0) : -1;
+        x0 = draw ? (W > s ? static_cast<int>(r.y % static_cast<uint32_t>(W - s + 1)) : 0) : -1;
+      }
+      const bool hit = s > 0 && y0 >= 0 && x0 >= 0 && y >= y0 && y < y0 + s && x >= x0 && x < x0 + s;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float v = P.kind == UB_P_U8_OCCLUSION
+                            ? static_cast<float>(load_u8(img, fmt, b, c, y, x, H, W)) / 255.0f
+                            : load_f(img, fmt, b, c, y, x, H, W);
+        out[c] = hit ? 0.0f : v;
+      }
+    } break;
+    case UB_P_U8_SALT_PEPPER: {
+      int code;
+      if (P.aux) {
+        code = reinterpret_cast<const uint8_t*>(P.aux)[static_cast<size_t>(b) * hw + pix];
+      } else {
+        // fparam2 = P(pixel hit at least once by the reference's n draws with replacement)
+        const uint4 r = rng4(P.seed, static_cast<uint32_t>(pix), b, 4);
+        code = (u01(r.x) < P.fparam2) ? ((r.y & 1u) ? 2 : 1) : 0;
+      }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int u = code == 1 ? 0 : (code == 2 ? 255 : load_u8(img, fmt, b, c, y, x, H, W));
+        out[c] = static_cast<float>(u) / 255.0f;
+      }
+    } break;
+    case UB_P_F_NOISE: {
+      uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0;
+      if (!P.aux) { r0 = rng4(P.seed, static_cast<uint32_t>(pix), b, 5); r1 = rng4(P.seed, static_cast<uint32_t>(pix), b, 6); }
+      const uint32_t rr[6] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y};
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float g = P.aux ? reinterpret_cast<const float*>(P.aux)[(static_cast<size_t>(b) * 3 + c) * hw + pix]
+                              : normal_from(rr[2 * c], rr[2 * c + 1]);
+        // randn * fl32(std/255.0), then img + noise (separate roundings, :472-473)
+        out[c] = clamp01(__fadd_rn(load_f(img, fmt, b, c, y, x, H, W), __fmul_rn(g, P.fparam2)));
+      }
+    } break;
+    case UB_P_F_CONTRAST:
+#pragma unroll
+      for (int c = 0; c < 3; ++c) out[c] = clamp01(__fmul_rn(load_f(img, fmt, b, c, y, x, H, W), P.fparam));
+      break;
+    case UB_P_F_BRIGHTNESS:
+#pragma unroll
+      for (int c = 0; c < 3; ++c) out[c] = clamp01(__fadd_rn(load_f(img, fmt, b, c, y, x, H, W), P.fparam));
+      break;
+    case UB_P_F_SALT_PEPPER: {
+      // fparam = fl32(amount/2), fparam2 = fl32(1-amount/2); one draw per pixel, shared by channels
+      const float r = P.aux ? reinterpret_cast<const float*>(P.aux)[static_cast<size_t>(b) * hw + pix]
+                            : u01(rng4(P.seed, static_cast<uint32_t>(pix), b, 7).x);
+      const float salt = r < P.fparam ? 1.0f : 0.0f;
+      const float pepper = r > P.fparam2 ? 1.0f : 0.0f;
+      const float mask = __fsub_rn(__fsub_rn(1.0f, salt), pepper);
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        out[c] = __fadd_rn(__fmul_rn(load_f(img, fmt, b, c, y, x, H, W), mask), salt);
+    } break;
+  }
+}
+
+// Perturbation alone -> fp32 NCHW (ub_perturb_images; also feeds perturbed_out).
+__global__ void perturb_kernel(PerturbDev P, const void* img, int fmt, int n, int H, int W, float* out) {
+  const size_t hw = static_cast<size_t>(H) * W;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= hw * n) return;
+  const int b = static_cast<int>(i / hw);
+  const int y = static_cast<int>((i % hw) / W), x = static_cast<int>(i % W);
+  float v[3];
+  perturbed_pixel(P, img, fmt, b, y, x, H, W, v);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) out[(static_cast<size_t>(b) * 3 + c) * hw + static_cast<size_t>(y) * W + x] = v[c];
+}
+
+// ---- blur passes
+// uint8 family (perturbations.py:97-121): zero-padded 3x3 sum S -> floor((S+4)/9); planar u8 [n*3,H,W].
+__global__ void blur_u8_quantise_kernel(const void* img, int fmt, int n, int H, int W, uint8_t* out) {
+  const size_t hw = static_cast<size_t>(H) * W;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= hw * n * 3) return;
+  const int pl = static_cast<int>(i / hw);
+  const int y = static_cast<int>((i % hw) / W), x = static_cast<int>(i % W);
+  out[i] = static_cast<uint8_t>(load_u8(img, fmt, pl / 3, pl % 3, y, x, H, W));
+}
+__global__ void blur_u8_pass_kernel(const uint8_t* in, uint8_t* out, int planes, int H, int W) {
+  const size_t hw = static_cast<size_t>(H) * W;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= hw * planes) return;
+  const uint8_t* pl = in + (i / hw) * hw;
+  const int y = static_cast<int>((i % hw) / W), x = static_cast<int>(i % W);
+  int s = 0;
+#pragma unroll
+  for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+    for (int dx = -1; dx <= 1; ++dx) {
+      const int yy = y + dy, xx = x + dx;
+      if (yy >= 0 && yy < H && xx >= 0 && xx < W) s += pl[static_cast<size_t>(yy) * W + xx];
+    }
+  out[i] = static_cast<uint8_t>((s + 4) / 9);
+}
+__global__ void u8_planar_to_f32_kernel(const uint8_t* in, float* out, size_t count) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < count) out[i] = static_cast<float>(in[i]) / 255.0f;
+}
+// float family (processing_blocks.py:493-496 -> kornia box_blur, reflect border; fp32 planar).
+__global__ void blur_f_load_kernel(const void* img, int fmt, int n, int H, int W, float* out) {
+  const size_t hw = static_cast<size_t>(H) * W;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= hw * n * 3) return;
+  const int pl = static_cast<int>(i / hw);
+  out[i] = load_f(img, fmt, pl / 3, pl % 3, static_cast<int>((i % hw) / W), static_cast<int>(i % W), H, W);
+}
+__global__ void blur_f_pass_kernel(const float* in, float* out, int planes, int H, int W) {
+  const size_t hw = static_cast<size_t>(H) * W;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= hw * planes) return;
+  const float* pl = in + (i / hw) * hw;
+  const int y = static_cast<int>((i % hw) / W), x = static_cast<int>(i % W);
+  const float ninth = 1.0f / 9.0f;
+  float acc = 0.0f;
+#pragma unroll
+  for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+    for (int dx = -1; dx <= 1; ++dx) {
+      int yy = y + dy, xx = x + dx;
+      yy = yy < 0 ? -yy : (yy >= H ? 2 * H - 2 - yy : yy);
+      xx = xx < 0 ? -xx : (xx >= W ? 2 * W - 2 - xx : xx);
+      acc = __fadd_rn(acc, __fmul_rn(pl[static_cast<size_t>(yy) * W + xx], ninth));
+    }
+  out[i] = acc;
+}
+
+// ---- stem: perturbed pixel -> Conv2d(3,32,1) -> bf16, written into channels [choff, choff+32) of the
+// level-0 concat buffer (NHWC, cstride channels per pixel).  One thread per pixel, 4 x 16-byte stores.
+struct StemWeights {
+  float w[32 * 3];
+  float b[32];
+};
+__global__ void __launch_bounds__(256)
+stem_kernel(PerturbDev P, StemWeights sw, const void* img, int fmt, int n, int H, int W,
+            __nv_bfloat16* out, int cstride, int choff, float* perturbed_out) {
+  __shared__ float s_w[32 * 3 + 32];
+  for (int i = threadIdx.x; i < 32 * 3; i += blockDim.x) s_w[i] = sw.w[i];
+  if (threadIdx.x < 32) s_w[96 + threadIdx.x] = sw.b[threadIdx.x];
+  __syncthreads();
+  const size_t hw = static_cast<size_t>(H) * W;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= hw * n) return;
+  const int b = static_cast<int>(i / hw);
+  const int y = static_cast<int>((i % hw) / W), x = static_cast<int>(i % W);
+  float v[3];
+  perturbed_pixel(P, img, fmt, b, y, x, H, W, v);
+  if (perturbed_out) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) perturbed_out[(static_cast<size_t>(b) * 3 + c) * hw + static_cast<size_t>(y) * W + x] = v[c];
+  }
+  uint32_t packed[16];
+#pragma unroll
+  for (int o = 0; o < 32; o += 2) {
+    float a0 = s_w[96 + o], a1 = s_w[96 + o + 1];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      a0 = fmaf(s_w[o * 3 + c], v[c], a0);
+      a1 = fmaf(s_w[(o + 1) * 3 + c], v[c], a1);
+    }
+    __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
+    packed[o >> 1] = *reinterpret_cast<uint32_t*>(&h);
+  }
+  uint4* dst = reinterpret_cast<uint4*>(out + i * cstride + choff);
+#pragma unroll
+  for (int g = 0; g < 4; ++g) dst[g] = make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+}
+
+}  // namespace ub

@@ -1,0 +1,250 @@
+"""Host-side handle on one ub_ctx (one per device per process).  PyTorch supplies device memory and the
+stream; every computation is a call into libunetb200.so through the C ABI (include/unet_b200.h)."""
+from __future__ import annotations
+
+import ctypes
+import math
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+
+
+class Perturbation:
+    """Host description of one (family, level): the ub_perturb struct plus an optional aux tensor
+    (reference-generated noise / corners / code map in parity mode; None = device RNG)."""
+
+    def __init__(self, kind: int = L.UB_P_NONE, iparam: int = 0, fparam: float = 0.0, fparam2: float = 0.0,
+                 seed: int = 0, aux: Optional[torch.Tensor] = None, lut=None, name: str = "none"):
+        self.struct = L.ub_perturb()
+        self.struct.kind = kind
+        self.struct.iparam = int(iparam)
+        self.struct.fparam = float(fparam)
+        self.struct.fparam2 = float(fparam2)
+        self.struct.seed = int(seed) & (2 ** 64 - 1)
+        if lut is not None:
+            lib = L.load()
+            rc = lib.ub_make_lut(ctypes.byref(self.struct), int(lut[0]), float(lut[1]))
+            if rc != 0:
+                raise ValueError(f"ub_make_lut failed ({rc})")
+        self.aux = aux
+        self.name = name
+
+    # ---- uint8-space Dataset-wrapper families (customDatasets/perturbations.py)
+    @staticmethod
+    def u8_noise(std, aux=None, seed=0):
+        return Perturbation(L.UB_P_U8_NOISE, fparam=float(std), aux=aux, seed=seed, name="gaussian_noise")
+
+    @staticmethod
+    def u8_blur(passes):
+        return Perturbation(L.UB_P_U8_BLUR, iparam=int(passes), name="gaussian_blur")
+
+    @staticmethod
+    def u8_contrast(scale):
+        return Perturbation(lut=(L.UB_LUT_CONTRAST, scale), name="contrast")
+
+    @staticmethod
+    def u8_brightness(offset, increase=True):
+        return Perturbation(lut=(L.UB_LUT_BRIGHTNESS_INCREASE if increase else L.UB_LUT_BRIGHTNESS_DECREASE, offset),
+                            name="brightness")
+
+    @staticmethod
+    def u8_occlusion(size, aux=None, seed=0):
+        return Perturbation(L.UB_P_U8_OCCLUSION, iparam=int(size), aux=aux, seed=seed, name="occlusion")
+
+    @staticmethod
+    def u8_salt_pepper(amount, aux=None, seed=0, hw=256 * 256):
+        n = int(round(amount * hw))
+        p_hit = 1.0 - (1.0 - 1.0 / hw) ** n  # P(pixel drawn at least once), perturbations.py:366-377
+        return Perturbation(L.UB_P_U8_SALT_PEPPER, fparam=float(amount), fparam2=p_hit, aux=aux, seed=seed,
+                            name="salt_pepper_noise")
+
+    # ---- float-space nn.Module families (models/processing_blocks.py:454-592)
+    @staticmethod
+    def f_noise(std, aux=None, seed=0):
+        return Perturbation(L.UB_P_F_NOISE, fparam=float(std), fparam2=std / 255.0, aux=aux, seed=seed,
+                            name="GaussianPixelNoise")
+
+    @staticmethod
+    def f_blur(times):
+        return Perturbation(L.UB_P_F_BLUR, iparam=int(times), name="RepeatedBlur")
+
+    @staticmethod
+    def f_contrast(factor):
+        return Perturbation(L.UB_P_F_CONTRAST, fparam=float(factor), name="ContrastChange")
+
+    @staticmethod
+    def f_brightness(offset):
+        return Perturbation(L.UB_P_F_BRIGHTNESS, fparam=offset / 255.0, name="BrightnessChange")
+
+    @staticmethod
+    def f_occlusion(size, aux=None, seed=0):
+        return Perturbation(L.UB_P_F_OCCLUSION, iparam=int(size), aux=aux, seed=seed, name="Occlusion")
+
+    @staticmethod
+    def f_salt_pepper(amount, aux=None, seed=0):
+        return Perturbation(L.UB_P_F_SALT_PEPPER, fparam=amount / 2, fparam2=1 - amount / 2, aux=aux, seed=seed,
+                            name="SaltAndPepper")
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _stream(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+class Engine:
+    """Owns one ub_ctx.  arch: 'unet' | 'large'."""
+
+    def __init__(self, device, arch: str = "unet", in_channels: int = 3, n_classes: int = 3,
+                 max_microbatch: int = 32):
+        self.lib = L.load()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("unet-b200 runs on CUDA sm_100a devices only (no CPU fallback)")
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", idx)
+        self.n_classes = n_classes
+        self.max_microbatch = max_microbatch
+        h = ctypes.c_void_p()
+        rc = self.lib.ub_create(ctypes.byref(h), idx, L.UB_ARCH_LARGE_UNET if arch == "large" else L.UB_ARCH_UNET,
+                                in_channels, n_classes, max_microbatch)
+        if rc != 0:
+            raise RuntimeError(f"ub_create failed ({rc}): {self.lib.ub_last_error(None).decode()}")
+        self.h = h
+        self.loaded = False
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ub_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise RuntimeError(f"{what} failed ({rc}): {self.lib.ub_last_error(self.h).decode()}")
+
+    def load_state_dict(self, state_dict):
+        items = [(k, v.detach().to("cpu", torch.float32).contiguous()) for k, v in state_dict.items()
+                 if torch.is_tensor(v) and v.is_floating_point()]
+        n = len(items)
+        names = (ctypes.c_char_p * n)(*[k.encode() for k, _ in items])
+        ptrs = (ctypes.c_void_p * n)(*[v.data_ptr() for _, v in items])
+        shape_arrays = [(ctypes.c_int64 * max(v.dim(), 1))(*(list(v.shape) or [1])) for _, v in items]
+        shapes = (ctypes.POINTER(ctypes.c_int64) * n)(*[ctypes.cast(a, ctypes.POINTER(ctypes.c_int64))
+                                                        for a in shape_arrays])
+        ndims = (ctypes.c_int * n)(*[v.dim() for _, v in items])
+        self._check(self.lib.ub_load_weights(self.h, n, names, ptrs, shapes, ndims), "ub_load_weights")
+        self.loaded = True
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = x.to(self.device, torch.float32).contiguous()
+        n, c, h, w = x.shape
+        out = torch.empty((n, self.n_classes, h, w), device=self.device, dtype=torch.float32)
+        self._check(self.lib.ub_forward(self.h, _ptr(x), _ptr(out), n, h, w, _stream(self.device)), "ub_forward")
+        return out
+
+    def eval_batches(self, images: torch.Tensor, targets: Optional[torch.Tensor], perturbation: Optional[Perturbation],
+                     ref_batch: int, want_dice: bool = False, want_pred: bool = False, want_logits: bool = False,
+                     want_perturbed: bool = False, out_cm: Optional[torch.Tensor] = None,
+                     out_dice: Optional[torch.Tensor] = None):
+        """images: uint8 [n,H,W,3] or fp32 [n,3,H,W]; targets: uint8 or int64 [n,H,W] (device tensors).
+        Returns dict(cm=int64 [nb,C,C], dice=f64 [nb,C,3], pred=u8 [n,H,W], logits, perturbed)."""
+        assert images.is_cuda and images.is_contiguous()
+        if images.dtype == torch.uint8:
+            fmt = L.UB_IMG_U8_NHWC
+            n, h, w, _ = images.shape
+        elif images.dtype == torch.float32:
+            fmt = L.UB_IMG_F32_NCHW
+            n, _, h, w = images.shape
+        else:
+            raise TypeError("images must be uint8 NHWC or float32 NCHW")
+        C = self.n_classes
+        nb = math.ceil(n / ref_batch)
+        tfmt = L.UB_TGT_I64
+        cm = dice = None
+        if targets is not None:
+            assert targets.is_cuda and targets.is_contiguous() and tuple(targets.shape) == (n, h, w)
+            if targets.dtype == torch.uint8:
+                tfmt = L.UB_TGT_U8
+            elif targets.dtype != torch.int64:
+                raise TypeError("targets must be uint8 or int64")
+            cm = out_cm if out_cm is not None else torch.empty((nb, C, C), device=self.device, dtype=torch.int64)
+            if want_dice:
+                dice = out_dice if out_dice is not None else torch.empty((nb, C, 3), device=self.device,
+                                                                         dtype=torch.float64)
+        pred = torch.empty((n, h, w), device=self.device, dtype=torch.uint8) if want_pred else None
+        logits = torch.empty((n, C, h, w), device=self.device, dtype=torch.float32) if want_logits else None
+        pert = torch.empty((n, 3, h, w), device=self.device, dtype=torch.float32) if want_perturbed else None
+        p = perturbation
+        aux = None
+        if p is not None and p.aux is not None:
+            aux = p.aux.to(self.device).contiguous()
+        self._check(self.lib.ub_eval_batches(self.h, ctypes.byref(p.struct) if p is not None else None, _ptr(images),
+                                             fmt, _ptr(targets), tfmt, _ptr(aux), n, h, w, int(ref_batch), _ptr(cm),
+                                             _ptr(dice), _ptr(pred), _ptr(logits), _ptr(pert),
+                                             _stream(self.device)), "ub_eval_batches")
+        return dict(cm=cm, dice=dice, pred=pred, logits=logits, perturbed=pert)
+
+    def perturb(self, images: torch.Tensor, perturbation: Perturbation) -> torch.Tensor:
+        assert images.is_cuda and images.is_contiguous()
+        if images.dtype == torch.uint8:
+            fmt = L.UB_IMG_U8_NHWC
+            n, h, w, _ = images.shape
+        else:
+            fmt = L.UB_IMG_F32_NCHW
+            n, _, h, w = images.shape
+        out = torch.empty((n, 3, h, w), device=self.device, dtype=torch.float32)
+        aux = perturbation.aux.to(self.device).contiguous() if perturbation.aux is not None else None
+        self._check(self.lib.ub_perturb_images(self.h, ctypes.byref(perturbation.struct), _ptr(images), fmt, _ptr(aux),
+                                               n, h, w, _ptr(out), _stream(self.device)), "ub_perturb_images")
+        return out
+
+    def metrics(self, logits: torch.Tensor, targets: torch.Tensor, ref_batch: int, want_dice: bool = False):
+        logits = logits.to(self.device, torch.float32).contiguous()
+        targets = targets.to(self.device).contiguous()
+        n, C, h, w = logits.shape
+        tfmt = L.UB_TGT_U8 if targets.dtype == torch.uint8 else L.UB_TGT_I64
+        if tfmt == L.UB_TGT_I64 and targets.dtype != torch.int64:
+            targets = targets.long()
+        nb = math.ceil(n / ref_batch)
+        cm = torch.empty((nb, C, C), device=self.device, dtype=torch.int64)
+        dice = torch.empty((nb, C, 3), device=self.device, dtype=torch.float64) if want_dice else None
+        self._check(self.lib.ub_metrics(self.h, _ptr(logits), _ptr(targets), tfmt, n, C, h, w, int(ref_batch), _ptr(cm),
+                                        _ptr(dice), _stream(self.device)), "ub_metrics")
+        return cm, dice
+
+    def debug_conv3x3(self, key: str, x_nhwc_bf16: torch.Tensor, pool: bool = False) -> torch.Tensor:
+        n, h, w, _ = x_nhwc_bf16.shape
+        cout = self._layer_cout(key)
+        oh, ow = (h // 2, w // 2) if pool else (h, w)
+        out = torch.zeros((n, oh, ow, cout), device=self.device, dtype=torch.bfloat16)
+        self._check(self.lib.ub_debug_conv3x3(self.h, key.encode(), _ptr(x_nhwc_bf16.contiguous()), _ptr(out), n, h, w,
+                                              int(pool), _stream(self.device)), "ub_debug_conv3x3")
+        return out
+
+    def debug_convt2x2(self, key: str, x_nhwc_bf16: torch.Tensor) -> torch.Tensor:
+        n, h, w, _ = x_nhwc_bf16.shape
+        cout = self._layer_cout(key)
+        out = torch.zeros((n, 2 * h, 2 * w, cout), device=self.device, dtype=torch.bfloat16)
+        self._check(self.lib.ub_debug_convt2x2(self.h, key.encode(), _ptr(x_nhwc_bf16.contiguous()), _ptr(out), n, h, w,
+                                               _stream(self.device)), "ub_debug_convt2x2")
+        return out
+
+    def _layer_cout(self, key):
+        return self._couts[key]
+
+    def set_layer_couts(self, couts):
+        self._couts = dict(couts)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.ub_launch_count(self.h))

@@ -1,0 +1,135 @@
+/* unet_b200.h — C ABI of libunetb200.so, the sm_100a (B200) implementation of the robustness-
+ * evaluation hot path of MattiDeBeer/image-segmentation:
+ *
+ *   perturbation -> U-Net forward -> per-pixel argmax -> per-reference-batch confusion counts
+ *
+ * Nothing like this interface exists in the reference (it is pure Python); each entry point names
+ * the reference code it replaces (paths relative to the reference root).  Plain pointers and sizes
+ * only: no torch / C++ types cross this boundary.  All device pointers are owned by the caller; the
+ * library owns the packed weights and its workspace inside ub_ctx.  Every call is asynchronous on
+ * the passed stream (a cudaStream_t / CUstream handle passed as void*), never synchronises, and
+ * returns 0 or a negative ub_status; ub_last_error() gives the message.  One ctx per device per
+ * process; a ctx is not thread-safe (the reference's callers are single-threaded).
+ * There is no CPU fallback: ub_create fails on a device that is not compute capability 10.x.
+ */
+#ifndef UNET_B200_H_
+#define UNET_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UB_ABI_VERSION 1
+
+typedef struct ub_ctx ub_ctx;
+
+enum ub_status {
+  UB_OK = 0,
+  UB_ERR_INVALID = -1,     /* bad argument / shape / missing weight */
+  UB_ERR_CUDA = -2,        /* a CUDA call failed; see ub_last_error */
+  UB_ERR_UNSUPPORTED = -3, /* wrong GPU architecture, unsupported size */
+  UB_ERR_STATE = -4        /* weights not loaded yet */
+};
+
+/* models/UNet.py:7-76 (UNet) and :78-148 (LargeUNet) */
+enum ub_arch { UB_ARCH_UNET = 0, UB_ARCH_LARGE_UNET = 1 };
+
+/* Input image container. */
+enum ub_image_format {
+  UB_IMG_F32_NCHW = 0, /* fp32 [n,3,H,W] in [0,1] — what customDatasets/datasets.py:157-158 yields */
+  UB_IMG_U8_NHWC = 1   /* uint8 [n,H,W,3] — the decoded bytes before datasets.py:115 divides by 255 */
+};
+enum ub_target_format { UB_TGT_I64 = 0 /* int64 [n,H,W], datasets.py:118-131 */, UB_TGT_U8 = 1 };
+
+/* Perturbation families.
+ * UB_P_U8_*: uint8-space Dataset wrappers, customDatasets/perturbations.py (image is quantised with
+ *            rint(x*255) first, result is k/255.0f) — exact integer arithmetic.
+ * UB_P_F_* : float-space nn.Modules, models/processing_blocks.py:454-592. */
+enum ub_perturb_kind {
+  UB_P_NONE = 0,
+  UB_P_U8_NOISE = 1,       /* perturbations.py:31-50;   fparam = std; aux = fp32 [n,3,H,W] N(0,std) or NULL */
+  UB_P_U8_BLUR = 2,        /* perturbations.py:85-124;  iparam = passes (0..16) */
+  UB_P_U8_LUT = 3,         /* perturbations.py:140-156,182-198,222-235,262-275; lut[] filled by ub_make_lut */
+  UB_P_U8_OCCLUSION = 4,   /* perturbations.py:301-327; iparam = size; aux = int32 [n,2] (y0,x0), <0 = none, or NULL */
+  UB_P_U8_SALT_PEPPER = 5, /* perturbations.py:354-382; fparam = amount; aux = uint8 [n,H,W] 0 keep/1 pepper/2 salt, or NULL */
+  UB_P_F_NOISE = 6,        /* processing_blocks.py:471-474; fparam = std; aux = fp32 [n,3,H,W] randn or NULL */
+  UB_P_F_BLUR = 7,         /* processing_blocks.py:493-496 (kornia box_blur, reflect); iparam = times (0..16) */
+  UB_P_F_CONTRAST = 8,     /* processing_blocks.py:516-518; fparam = factor */
+  UB_P_F_BRIGHTNESS = 9,   /* processing_blocks.py:535-539; fparam = fl32(offset/255.0) computed by the caller in double */
+  UB_P_F_OCCLUSION = 10,   /* processing_blocks.py:557-563; iparam = size; aux = int32 [n,2] (y,x) or NULL */
+  UB_P_F_SALT_PEPPER = 11  /* processing_blocks.py:586-592; fparam = amount; aux = fp32 [n,1,H,W] rand or NULL */
+};
+
+typedef struct ub_perturb {
+  int32_t kind;      /* ub_perturb_kind */
+  int32_t iparam;
+  float fparam;
+  float fparam2;     /* reserved */
+  uint64_t seed;     /* device RNG seed, used only when the family is random and aux == NULL */
+  uint8_t lut[256];  /* UB_P_U8_LUT */
+} ub_perturb;
+
+enum ub_lut_kind {
+  UB_LUT_CONTRAST = 0,            /* clamp(rint(fl32(u*fl32(param))),0,255)   perturbations.py:146-150 */
+  UB_LUT_BRIGHTNESS_INCREASE = 1, /* rint(clamp(u+param,0,255))               perturbations.py:228-230 */
+  UB_LUT_BRIGHTNESS_DECREASE = 2  /* clamp(rint(u-param),0,255)               perturbations.py:268-270 */
+};
+
+/* Host-only helper: fills p->lut and sets p->kind = UB_P_U8_LUT. */
+int ub_make_lut(ub_perturb* p, int lut_kind, double param);
+
+int ub_abi_version(void);
+
+/* Replaces nn.Module construction + .to(device) (models/model_wrappers.py:335-338).
+ * max_microbatch: images processed per internal pass (workspace ~45 MB per image at 256x256). */
+int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes, int max_microbatch);
+void ub_destroy(ub_ctx* ctx);
+const char* ub_last_error(const ub_ctx* ctx); /* ctx may be NULL: returns the last creation error */
+
+/* Replaces load_state_dict (models/model_wrappers.py:323-332, scripts/robustness_evaluation.py:39-46).
+ * names[i] are reference state_dict keys ("enc1.block.0.conv.0.weight", ...), host_ptrs[i] fp32 host
+ * tensors in PyTorch layout, shapes[i]/ndims[i] their shapes.  BatchNorm (eval) is folded into the
+ * conv weights here; "num_batches_tracked" and unknown keys are ignored; a missing key is an error. */
+int ub_load_weights(ub_ctx* ctx, int n, const char* const* names, const void* const* host_ptrs,
+                    const int64_t* const* shapes, const int* ndims);
+
+/* Replaces UNet.forward (models/UNet.py:60-76): x fp32 NCHW device -> logits fp32 NCHW device. */
+int ub_forward(ub_ctx* ctx, const float* x_nchw, float* logits_nchw, int n, int h, int w, void* stream);
+
+/* Replaces the body of the evaluation hot loop, models/model_wrappers.py:440-463 and
+ * scripts/robustness_evaluation.py:116-122, for n images at once: perturb -> forward -> argmax
+ * (first index on ties) -> confusion counts.  Image i belongs to reference batch i / ref_batch.
+ *   cm        int64  [ceil(n/ref_batch), C, C]   rows = target, cols = prediction; zeroed by the callee
+ *   dice_sums double [ceil(n/ref_batch), C, 3]   (sum p*1[t=c], sum p, sum 1[t=c]), p = softmax(softmax(z))
+ *                                                — the sums smp DiceLoss needs (models/losses.py:98-100); may be NULL
+ *   pred_out  uint8  [n,H,W] argmax map, may be NULL;  logits_out fp32 [n,C,H,W], may be NULL
+ *   perturbed_out fp32 [n,3,H,W] the perturbed network input, may be NULL */
+int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,
+                    const void* targets, int target_format, const void* aux, int n, int h, int w,
+                    int ref_batch, int64_t* cm, double* dice_sums, uint8_t* pred_out,
+                    float* logits_out, float* perturbed_out, void* stream);
+
+/* Perturbation alone (the Dataset wrappers' __getitem__ / the nn.Modules' forward): out fp32 [n,3,H,W]. */
+int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,
+                      const void* aux, int n, int h, int w, float* out_nchw, void* stream);
+
+/* Metrics alone (models/losses.py:43-63,133-154 from materialised logits): fills cm / dice_sums as above. */
+int ub_metrics(ub_ctx* ctx, const float* logits_nchw, const void* targets, int target_format, int n,
+               int n_classes, int h, int w, int ref_batch, int64_t* cm, double* dice_sums, void* stream);
+
+/* Test / profiling hook: one conv3x3+BN(folded)+ReLU layer (processing_blocks.py:43-45) by its
+ * state_dict prefix, e.g. "enc2.block.0.conv.conv.3"; bf16 NHWC in and out; pool = fuse MaxPool2d(2,2). */
+int ub_debug_conv3x3(ub_ctx* ctx, const char* conv_key, const void* in_bf16_nhwc, void* out_bf16_nhwc,
+                     int n, int h, int w, int pool, void* stream);
+/* Test hook: ConvTranspose2d(k2,s2) (processing_blocks.py:102,106) by prefix, e.g. "dec2.up". */
+int ub_debug_convt2x2(ub_ctx* ctx, const char* up_key, const void* in_bf16_nhwc, void* out_bf16_nhwc,
+                      int n, int h, int w, void* stream);
+/* Number of kernel launches issued by this ctx so far (bench.py's gpu_launches claim). */
+int64_t ub_launch_count(const ub_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UNET_B200_H_ */

@@ -1,0 +1,79 @@
+"""ORACLE (test infrastructure, not product): CPU fp32 restatement of the reference U-Net forward.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this.  It restates, as one flat functional pass over a reference-format state_dict:
+
+  models/UNet.py:60-76 (UNet.forward) and :129-148 (LargeUNet.forward)
+  models/processing_blocks.py:42-52  ConvBlock  (conv3x3 pad1 + BatchNorm eval + ReLU, twice)
+  models/processing_blocks.py:71-77  ConvBlockDownsample (ConvBlock + MaxPool2d(2,2))
+  models/processing_blocks.py:102-109 ConvBlockUpsampleSkip
+        (ConvTranspose2d k2 s2 -> F.interpolate bilinear align_corners=True to skip size ->
+         cat([up, skip]) -> ConvBlock)
+
+Pinned: tests/test_oracle_pinned.py compares it with the real reference modules (imported from
+/root/reference in the build container) and with tests/golden/unet_small.npz made by
+oracle/make_golden.py.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+BN_EPS = 1e-5  # nn.BatchNorm2d default, processing_blocks.py:44,47
+
+
+def arch_of(state_dict) -> str:
+    """'unet' (3 encoder stages) or 'large' (4), from the keys present."""
+    return "large" if any(k.startswith("enc4.") for k in state_dict) else "unet"
+
+
+def _conv_bn_relu(x, sd, prefix, i_conv, i_bn):
+    x = F.conv2d(x, sd[f"{prefix}.{i_conv}.weight"], sd[f"{prefix}.{i_conv}.bias"], padding=1)
+    x = F.batch_norm(x, sd[f"{prefix}.{i_bn}.running_mean"], sd[f"{prefix}.{i_bn}.running_var"],
+                     sd[f"{prefix}.{i_bn}.weight"], sd[f"{prefix}.{i_bn}.bias"],
+                     training=False, eps=BN_EPS)
+    return F.relu(x)
+
+
+def _double_conv(x, sd, prefix):
+    x = _conv_bn_relu(x, sd, prefix, 0, 1)
+    return _conv_bn_relu(x, sd, prefix, 3, 4)
+
+
+def _up_skip(x, skip, sd, name):
+    x = F.conv_transpose2d(x, sd[f"{name}.up.weight"], sd[f"{name}.up.bias"], stride=2)
+    x = F.interpolate(x, size=skip.shape[2:], mode="bilinear", align_corners=True)
+    return _double_conv(torch.cat([x, skip], dim=1), sd, f"{name}.conv.conv")
+
+
+def forward_impl(state_dict, x: torch.Tensor, return_intermediates: bool = False):
+    """x: fp32 [B,3,H,W] -> logits fp32 [B,C,H,W] (activation = Identity).  Differentiable."""
+    sd = {k.replace("_orig_mod.", ""): v.float() for k, v in state_dict.items()
+          if v.is_floating_point()}
+    n_enc = 4 if arch_of(sd) == "large" else 3
+    acts = {}
+    stem = F.conv2d(x.float(), sd["input.weight"], sd["input.bias"])
+    acts["input"] = stem
+    skips = [stem]
+    h = stem
+    for i in range(1, n_enc + 1):
+        h = F.max_pool2d(_double_conv(h, sd, f"enc{i}.block.0.conv"), 2, 2)
+        acts[f"enc{i}"] = h
+        skips.append(h)
+    h = _double_conv(h, sd, "bottleneck.conv")
+    acts["bottleneck"] = h
+    for j in range(1, n_enc + 2):
+        h = _up_skip(h, skips[n_enc + 1 - j], sd, f"dec{j}")
+        acts[f"dec{j}"] = h
+    logits = F.conv2d(h, sd["out.weight"], sd["out.bias"])
+    return (logits, acts) if return_intermediates else logits
+
+
+@torch.no_grad()
+def forward(state_dict, x: torch.Tensor, return_intermediates: bool = False):
+    return forward_impl(state_dict, x, return_intermediates)
+
+
+def hard_prediction(logits: torch.Tensor) -> torch.Tensor:
+    """models/losses.py:48-50 — argmax taken AFTER softmax, first index on ties."""
+    return torch.argmax(F.softmax(logits, dim=1), dim=1)
