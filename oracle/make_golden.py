@@ -1,0 +1,157 @@
+"""Generates tests/golden/*.npz by RUNNING THE REFERENCE'S OWN CODE (imported from /root/reference
+through oracle/refload.py).  Run in the build container only:  python -m oracle.make_golden
+
+  perturb_u8.npz   customDatasets/perturbations.py wrappers, all 8 families x the 10 script levels
+                   (scripts/robustness_evaluation.py:59-92) on 2 synthetic 3x24x40 images, with the RNG
+                   artefacts (noise tensors, occlusion corners, salt-pepper code maps) captured by
+                   replaying random.seed(42)/torch.manual_seed(42) (robustness_evaluation.py:32-34).
+  perturb_f.npz    models/processing_blocks.py float-space modules (all but RepeatedBlur, which needs
+                   kornia) on a [2,3,24,40] batch, 3 levels per family.
+  unet_small.npz   reference UNet (seed 42 + randomised BatchNorm) logits on a [2,3,32,64] input, the
+                   reference IoU / PixelAccuracy on them, and a checksum of the seeded state_dict.
+"""
+import hashlib
+import os
+import random
+
+import numpy as np
+import torch
+
+from oracle import refload
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+SCRIPT_LEVELS = {  # scripts/robustness_evaluation.py:59-92
+    "gaussian_noise": ("GaussianPixelNoise", [0, 2, 4, 6, 8, 10, 12, 14, 16, 18]),
+    "gaussian_blur": ("GaussianBlur", [0, 1, 2, 3, 4, 5, 6, 7, 8, 9]),
+    "contrast_increase": ("ContrastIncrease", [1.0, 1.01, 1.02, 1.03, 1.04, 1.05, 1.1, 1.15, 1.2, 1.25]),
+    "contrast_decrease": ("ContrastDecrease", [1.0, 0.95, 0.9, 0.85, 0.8, 0.6, 0.4, 0.3, 0.2, 0.1]),
+    "brightness_increase": ("BrightnessIncrease", [0, 5, 10, 15, 20, 25, 30, 35, 40, 45]),
+    "brightness_decrease": ("BrightnessDecrease", [0, 5, 10, 15, 20, 25, 30, 35, 40, 45]),
+    "occlusion": ("OcclusionIncrease", [0, 5, 10, 15, 20, 25, 30, 35, 40, 45]),
+    "salt_pepper_noise": ("SaltPepperNoise", [0.00, 0.02, 0.04, 0.06, 0.08, 0.10, 0.12, 0.14, 0.16, 0.18]),
+}
+
+
+class _Base(torch.utils.data.Dataset):
+    def __init__(self, imgs):
+        self.imgs = imgs
+
+    def __len__(self):
+        return len(self.imgs)
+
+    def __getitem__(self, i):
+        return self.imgs[i], torch.zeros(self.imgs[i].shape[1:], dtype=torch.long)
+
+
+def small_images(n=2, h=24, w=40, seed=11):
+    g = torch.Generator().manual_seed(seed)
+    u8 = torch.randint(0, 256, (n, 3, h, w), generator=g, dtype=torch.uint8)
+    return u8, u8.float() / 255.0
+
+
+def state_checksum(sd):
+    hsh = hashlib.sha256()
+    for k in sorted(sd):
+        if sd[k].is_floating_point():
+            hsh.update(k.encode())
+            hsh.update(sd[k].detach().cpu().float().numpy().tobytes())
+    return hsh.hexdigest()
+
+
+def golden_perturb_u8(ns):
+    from oracle import perturb_oracle as po
+    u8, imgs = small_images()
+    out = {"images_u8": u8.numpy()}
+    _, h, w = imgs[0].shape
+    for fam, (cls_name, levels) in SCRIPT_LEVELS.items():
+        cls = getattr(ns.perturbations, cls_name)
+        for li, level in enumerate(levels):
+            # reference run
+            random.seed(42); torch.manual_seed(42)
+            ds = cls(_Base(imgs), level)
+            ref = torch.stack([ds[i][0] for i in range(len(ds))])
+            ref_u8 = (ref * 255.0).round().to(torch.uint8)
+            assert torch.equal(ref_u8.float() / 255.0, ref), (fam, level)  # outputs are exactly k/255
+            out[f"{fam}/{li}/out"] = ref_u8.numpy()
+            # RNG artefacts, replayed in the same order
+            random.seed(42); torch.manual_seed(42)
+            if fam == "gaussian_noise":
+                out[f"{fam}/{li}/aux"] = np.stack([
+                    torch.normal(mean=0.0, std=float(level), size=imgs[0].shape, dtype=torch.float).numpy()
+                    for _ in range(len(imgs))])
+            elif fam == "occlusion":
+                out[f"{fam}/{li}/aux"] = np.array([po.replay_occlusion_corner(level, h, w) for _ in range(len(imgs))],
+                                                 dtype=np.int32)
+            elif fam == "salt_pepper_noise":
+                out[f"{fam}/{li}/aux"] = np.stack([po.replay_salt_pepper_code(level, h, w) for _ in range(len(imgs))])
+    np.savez_compressed(os.path.join(OUT, "perturb_u8.npz"), **out)
+    return out
+
+
+def golden_perturb_f(ns):
+    from oracle import perturb_oracle as po
+    u8, imgs = small_images(seed=12)
+    out = {"images_u8": u8.numpy()}
+    b, _, h, w = imgs.shape
+    fams = {
+        "GaussianPixelNoise": [1e-6, 8, 18],
+        "ContrastChange": [1.05, 1.25, 0.3],
+        "BrightnessChange": [15, 45, -30],
+        "Occlusion": [0, 15, 45],
+        "SaltAndPepper": [0.0, 0.06, 0.16],
+    }
+    for fam, levels in fams.items():
+        for li, level in enumerate(levels):
+            random.seed(42); torch.manual_seed(42)
+            mod = getattr(ns.blocks, fam)(level)
+            ref = mod(imgs.clone())
+            out[f"{fam}/{li}/out"] = ref.numpy()
+            random.seed(42); torch.manual_seed(42)
+            if fam == "GaussianPixelNoise":
+                out[f"{fam}/{li}/aux"] = torch.randn_like(imgs).numpy()
+            elif fam == "Occlusion":
+                out[f"{fam}/{li}/aux"] = np.array(po.replay_f_occlusion_corners(b, level, h, w), dtype=np.int32)
+            elif fam == "SaltAndPepper":
+                out[f"{fam}/{li}/aux"] = torch.rand((b, 1, h, w)).numpy()
+            out[f"{fam}/{li}/level"] = np.float64(level)
+    np.savez_compressed(os.path.join(OUT, "perturb_f.npz"), **out)
+    return out
+
+
+def golden_unet(ns):
+    from image_segmentation_b200 import synthetic
+    torch.manual_seed(42)
+    m = ns.UNet().eval()
+    base_sum = state_checksum(m.state_dict())
+    sd = synthetic.randomize_batchnorm(m.state_dict(), seed=7)
+    m.load_state_dict(sd)
+    imgs, masks = synthetic.make_dataset(2, 32, 64, seed=5)
+    x = synthetic.to_float_nchw(imgs)
+    with torch.no_grad():
+        logits = m(x)
+        # centre the head so that all three classes occur, then re-run
+        sd["out.bias"] = sd["out.bias"] - logits.mean(dim=(0, 2, 3))
+        m.load_state_dict(sd)
+        logits = m(x)
+        iou = ns.losses.IoU()(logits, masks.long())
+        pa = ns.losses.PixelAccuracy()(logits, masks.long())
+    out = dict(images_u8=imgs.numpy(), masks_u8=masks.numpy(), logits=logits.numpy(), iou=iou.numpy(),
+               pixel_accuracy=pa.numpy(), out_bias=sd["out.bias"].numpy(),
+               seed42_state_sha256=np.array(base_sum), final_state_sha256=np.array(state_checksum(sd)))
+    np.savez_compressed(os.path.join(OUT, "unet_small.npz"), **out)
+    return out
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    ns = refload.load()
+    golden_perturb_u8(ns)
+    golden_perturb_f(ns)
+    golden_unet(ns)
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    main()
