@@ -80,6 +80,11 @@ struct ub_ctx {
   std::map<std::pair<int, int>, std::unique_ptr<Plan>> plans;
   EncodeTiledFn encode = nullptr;
   int64_t launches = 0;
+  // optional per-launch timing (ub_profile_begin/end): event pairs around every GEMM launch
+  bool profiling = false;
+  struct ProfRec { int layer; cudaEvent_t a, b; };
+  std::vector<ProfRec> prof;
+  std::vector<cudaEvent_t> event_pool;
   std::vector<void*> owned;  // device allocations freed in ub_destroy
 };
 
@@ -295,7 +300,26 @@ int launch_inst(ub_ctx* ctx, const ConvParams& cp, cudaStream_t st) {
   return UB_OK;
 }
 
-int launch_gemm(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cudaStream_t st) {
+int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cudaStream_t st);
+
+cudaEvent_t take_event(ub_ctx* ctx) {
+  if (!ctx->event_pool.empty()) { cudaEvent_t e = ctx->event_pool.back(); ctx->event_pool.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+
+int launch_gemm(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cudaStream_t st, int layer = -1) {
+  if (!ctx->profiling) return launch_gemm_raw(ctx, cp, block_n, swz, st);
+  ub_ctx::ProfRec r{layer, take_event(ctx), take_event(ctx)};
+  cudaEventRecord(r.a, st);
+  const int rc = launch_gemm_raw(ctx, cp, block_n, swz, st);
+  cudaEventRecord(r.b, st);
+  ctx->prof.push_back(r);
+  return rc;
+}
+
+int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cudaStream_t st) {
   if (cp.mode == ub::EPI_HEAD && block_n != 32) return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs 32 channels");
   if (swz == 128) {
     switch (block_n) {
@@ -509,7 +533,7 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
       cp.cm = ha.cm; cp.dice = ha.dice; cp.pred_out = ha.pred; cp.logits_out = ha.logits;
     }
     const GemmLayer& L = ctx->layers[s.layer];
-    if ((rc = launch_gemm(ctx, cp, L.block_n, L.swz, st))) return rc;
+    if ((rc = launch_gemm(ctx, cp, L.block_n, L.swz, st, s.layer))) return rc;
   }
   return UB_OK;
 }
@@ -577,11 +601,48 @@ void ub_destroy(ub_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   for (void* p : ctx->owned) cudaFree(p);
+  for (auto& r : ctx->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
   delete ctx;
 }
 
 const char* ub_last_error(const ub_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 int64_t ub_launch_count(const ub_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int ub_profile_begin(ub_ctx* ctx) {
+  if (!ctx) return UB_ERR_INVALID;
+  for (auto& r : ctx->prof) { ctx->event_pool.push_back(r.a); ctx->event_pool.push_back(r.b); }
+  ctx->prof.clear();
+  ctx->profiling = true;
+  return UB_OK;
+}
+
+int ub_profile_end(ub_ctx* ctx, double* gemm_ms_total, int64_t* gemm_launches, char* report, int report_len) {
+  if (!ctx) return UB_ERR_INVALID;
+  ctx->profiling = false;
+  UB_CUDA(ctx, cudaDeviceSynchronize());
+  std::vector<double> ms(ctx->layers.size(), 0.0);
+  std::vector<int64_t> cnt(ctx->layers.size(), 0);
+  double total = 0.0;
+  for (auto& r : ctx->prof) {
+    float t = 0.f;
+    UB_CUDA(ctx, cudaEventElapsedTime(&t, r.a, r.b));
+    total += t;
+    if (r.layer >= 0) { ms[r.layer] += t; cnt[r.layer]++; }
+  }
+  if (gemm_ms_total) *gemm_ms_total = total;
+  if (gemm_launches) *gemm_launches = static_cast<int64_t>(ctx->prof.size());
+  if (report && report_len > 0) {
+    int off = 0;
+    report[0] = 0;
+    for (size_t i = 0; i < ctx->layers.size() && off < report_len - 96; ++i)
+      off += snprintf(report + off, report_len - off, "%s %d %d %d %lld %.4f\n", ctx->layers[i].key.c_str(), ctx->layers[i].cin,
+                      ctx->layers[i].n_total, ctx->layers[i].ksize, static_cast<long long>(cnt[i]), ms[i]);
+  }
+  for (auto& r : ctx->prof) { ctx->event_pool.push_back(r.a); ctx->event_pool.push_back(r.b); }
+  ctx->prof.clear();
+  return UB_OK;
+}
 
 int ub_load_weights(ub_ctx* ctx, int n, const char* const* names, const void* const* host_ptrs,
                     const int64_t* const* shapes, const int* ndims) {
@@ -731,7 +792,7 @@ static int debug_layer(ub_ctx* ctx, const char* key, const void* in, void* out, 
   if ((rc = fill_gemm(ctx, &cp, L, static_cast<const __nv_bfloat16*>(in), L.cin, n, h, w, mode,
                       static_cast<__nv_bfloat16*>(out), L.cout, 0)))
     return rc;
-  return launch_gemm(ctx, cp, L.block_n, L.swz, static_cast<cudaStream_t>(stream));
+  return launch_gemm(ctx, cp, L.block_n, L.swz, static_cast<cudaStream_t>(stream), it->second);
 }
 
 int ub_debug_conv3x3(ub_ctx* ctx, const char* conv_key, const void* in_bf16_nhwc, void* out_bf16_nhwc, int n, int h,

@@ -245,6 +245,20 @@ class Engine:
     def set_layer_couts(self, couts):
         self._couts = dict(couts)
 
+    def profile_begin(self):
+        self._check(self.lib.ub_profile_begin(self.h), "ub_profile_begin")
+
+    def profile_end(self):
+        """-> (gemm_ms_total, gemm_launches, [(key, cin, n_total, ksize, launches, ms), ...])"""
+        ms, cnt = ctypes.c_double(), ctypes.c_int64()
+        buf = ctypes.create_string_buffer(16384)
+        self._check(self.lib.ub_profile_end(self.h, ctypes.byref(ms), ctypes.byref(cnt), buf, len(buf)), "ub_profile_end")
+        rows = []
+        for line in buf.value.decode().splitlines():
+            k, cin, nt, ks, n, t = line.split()
+            rows.append((k, int(cin), int(nt), int(ks), int(n), float(t)))
+        return ms.value, cnt.value, rows
+
     @property
     def launch_count(self) -> int:
         return int(self.lib.ub_launch_count(self.h))

@@ -126,6 +126,12 @@ int ub_debug_conv3x3(ub_ctx* ctx, const char* conv_key, const void* in_bf16_nhwc
 /* Test hook: ConvTranspose2d(k2,s2) (processing_blocks.py:102,106) by prefix, e.g. "dec2.up". */
 int ub_debug_convt2x2(ub_ctx* ctx, const char* up_key, const void* in_bf16_nhwc, void* out_bf16_nhwc,
                       int n, int h, int w, void* stream);
+/* Measurement hooks (bench.py's roofline leg): between begin and end every tensor-core GEMM launch is
+ * bracketed by CUDA events on its own stream.  end() synchronises the device and returns the summed
+ * GEMM time, the number of GEMM launches, and (optionally) one text line per layer:
+ * "<state_dict key> <cin> <n_total> <ksize> <launches> <ms>". */
+int ub_profile_begin(ub_ctx* ctx);
+int ub_profile_end(ub_ctx* ctx, double* gemm_ms_total, int64_t* gemm_launches, char* report, int report_len);
 /* Number of kernel launches issued by this ctx so far (bench.py's gpu_launches claim). */
 int64_t ub_launch_count(const ub_ctx* ctx);
 

@@ -1,0 +1,269 @@
+"""Parity tests proper (B200 only): the CUDA path, called through the C ABI, against the oracle and the
+golden vectors.  Tolerances are the north_star's: counts bit-exact, deterministic perturbations
+bit-exact (<= 1 ulp asked), logits within 1e-2 relative (bf16), argmax agreement >= 99.9 % on weights
+with real margins, IoU/Dice within 0.1 point."""
+import os
+import random
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import metrics_oracle as mo
+from oracle import perturb_oracle as po
+from oracle import unet_oracle
+from oracle.make_golden import SCRIPT_LEVELS
+from tests import util
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "GPU tests need a B200"
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def base_model(dev):
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.UNet import UNet
+    torch.manual_seed(42)
+    m = UNet().eval()
+    sd = synthetic.randomize_batchnorm(m.state_dict(), seed=7)
+    m.load_state_dict(sd)
+    return m.to(dev), sd
+
+
+@pytest.fixture(scope="module")
+def trained(dev):
+    """UNet with decision margins: a few Adam steps on the learnable synthetic task (checker side)."""
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.UNet import UNet
+    torch.manual_seed(42)
+    m = UNet().eval()
+    sd = synthetic.randomize_batchnorm(m.state_dict(), seed=7)
+    imgs, masks = synthetic.make_dataset(48, 128, 128, seed=21)
+    sd = util.train_like(sd, synthetic.to_float_nchw(imgs), masks, steps=300, lr=1e-3, batch=8, crop=128)
+    m.load_state_dict(sd)
+    return m.to(dev), sd
+
+
+def folded(sd, conv_key):
+    base, idx = conv_key.rsplit(".", 1)
+    bn = f"{base}.{int(idx) + 1}"
+    s = sd[bn + ".weight"].double() / torch.sqrt(sd[bn + ".running_var"].double() + 1e-5)
+    w = (sd[conv_key + ".weight"].double() * s[:, None, None, None]).float()
+    b = ((sd[conv_key + ".bias"].double() - sd[bn + ".running_mean"].double()) * s + sd[bn + ".bias"].double()).float()
+    return w, b
+
+
+# ------------------------------------------------------------------ layers (tcgen05 implicit GEMM)
+def test_every_conv_layer(base_model, dev):
+    m, sd = base_model
+    eng = m.engine()
+    g = torch.Generator().manual_seed(3)
+    for key in m.layer_couts():
+        if key.endswith(".up"):
+            continue
+        wf, bf = folded(sd, key)
+        for (n, h, w) in [(2, 24, 40), (1, 64, 64)]:  # ragged tiles and full tiles
+            x = torch.randn((n, wf.shape[1], h, w), generator=g)
+            ref = F.relu(F.conv2d(util.bf16_round(x).to(dev), util.bf16_round(wf).to(dev), bf.to(dev), padding=1))
+            for pool in (False, True):
+                got = util.nhwc_to_nchw_f32(eng.debug_conv3x3(key, util.nchw_to_nhwc_bf16(x).to(dev), pool=pool))
+                want = F.max_pool2d(ref, 2, 2) if pool else ref
+                assert util.rel_err(got, want) < 6e-3, (key, n, h, w, pool)  # one bf16 output rounding
+
+
+def test_every_transposed_conv(base_model, dev):
+    m, sd = base_model
+    eng = m.engine()
+    g = torch.Generator().manual_seed(4)
+    for key in m.layer_couts():
+        if not key.endswith(".up"):
+            continue
+        cin = sd[key + ".weight"].shape[0]
+        x = torch.randn((2, cin, 24, 40), generator=g)
+        ref = F.conv_transpose2d(util.bf16_round(x).to(dev), util.bf16_round(sd[key + ".weight"]).to(dev),
+                                 sd[key + ".bias"].to(dev), stride=2)
+        got = util.nhwc_to_nchw_f32(eng.debug_convt2x2(key, util.nchw_to_nhwc_bf16(x).to(dev)))
+        assert util.rel_err(got, ref) < 6e-3, key
+
+
+# ------------------------------------------------------------------ whole network
+def test_forward_logits_and_argmax(trained, dev):
+    from image_segmentation_b200 import synthetic
+    m, sd = trained
+    imgs, masks = synthetic.make_dataset(6, 256, 256, seed=5)
+    x = synthetic.to_float_nchw(imgs)
+    ref = unet_oracle.forward({k: v.to(dev) for k, v in sd.items()}, x.to(dev)).cpu()
+    got = m(x.to(dev)).cpu()
+    assert got.shape == ref.shape and got.dtype == torch.float32
+    rel = util.rel_err(got, ref)
+    agree = float((unet_oracle.hard_prediction(ref) == unet_oracle.hard_prediction(got)).float().mean())
+    top2 = ref.topk(2, dim=1).values
+    thin = float(((top2[:, 0] - top2[:, 1]) < 1e-2 * ref.abs().max()).float().mean())
+    print(f"logits rel err {rel:.3e}; argmax agreement {agree:.5f}; pixels with margin < 1e-2*max|z|: {thin:.5f}")
+    assert rel < 1e-2
+    assert agree >= 0.999
+    acc = float((unet_oracle.hard_prediction(ref) == masks.long()).float().mean())
+    assert acc > 0.8  # the checker-side training did give the net real decisions
+
+
+def test_random_init_noise_floor(base_model, dev):
+    """Random-init weights have near-zero margins; report (not gate at 99.9 %) and bound loosely."""
+    from image_segmentation_b200 import synthetic
+    m, sd = base_model
+    imgs, _ = synthetic.make_dataset(2, 128, 128, seed=6)
+    x = synthetic.to_float_nchw(imgs)
+    ref = unet_oracle.forward(sd, x)
+    got = m(x.to(dev)).cpu()
+    assert util.rel_err(got, ref) < 3e-2
+
+
+def test_large_unet_forward(dev):
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.UNet import LargeUNet
+    torch.manual_seed(1)
+    m = LargeUNet().eval()
+    sd = synthetic.randomize_batchnorm(m.state_dict(), seed=8)
+    m.load_state_dict(sd)
+    imgs, _ = synthetic.make_dataset(2, 128, 128, seed=7)
+    x = synthetic.to_float_nchw(imgs)
+    ref = unet_oracle.forward({k: v.to(dev) for k, v in sd.items()}, x.to(dev)).cpu()
+    got = m.to(dev)(x.to(dev)).cpu()
+    assert util.rel_err(got, ref) < 3e-2
+
+
+# ------------------------------------------------------------------ head: argmax + confusion counts
+@pytest.mark.parametrize("ref_batch,n", [(8, 19), (10, 10), (16, 5)])
+def test_confusion_counts_bit_exact(trained, dev, ref_batch, n):
+    from image_segmentation_b200 import synthetic
+    m, sd = trained
+    imgs, masks = synthetic.make_dataset(n, 64, 128, seed=9)
+    eng = m.engine(max_microbatch=4)  # forces several micro-batches per reference batch
+    for tgt in (masks.to(dev), masks.long().to(dev)):  # uint8 and int64 targets
+        res = eng.eval_batches(imgs.to(dev), tgt, None, ref_batch, want_dice=True, want_pred=True, want_logits=True)
+        pred = res["pred"].cpu()
+        assert torch.equal(pred.long(), unet_oracle.hard_prediction(res["logits"].cpu()))  # first-max tie rule
+        nb = -(-n // ref_batch)
+        assert res["cm"].shape == (nb, 3, 3)
+        for b in range(nb):
+            sl = slice(b * ref_batch, min((b + 1) * ref_batch, n))
+            cm = mo.confusion_matrix(pred[sl].numpy(), masks[sl].numpy())
+            assert np.array_equal(res["cm"][b].cpu().numpy(), cm)
+            ds = mo.dice_sums(res["logits"][sl].cpu(), masks[sl].long()).numpy()
+            assert np.allclose(res["dice"][b].cpu().numpy(), ds, rtol=1e-5, atol=1e-3)
+        assert int(res["cm"].sum()) == n * 64 * 128  # checksum of checksums
+
+
+def test_metric_modules_match_oracle(dev):
+    from image_segmentation_b200.models import losses
+    g = torch.Generator().manual_seed(1)
+    for b in (1, 8, 10, 16):
+        z = torch.randn((b, 3, 40, 56), generator=g) * 3
+        t = torch.randint(0, 3, (b, 40, 56), generator=g)
+        if b == 1:
+            t[t == 2] = 0
+        assert float(losses.IoU()(z.to(dev), t.to(dev))) == float(mo.iou_direct(z, t))
+        assert float(losses.PixelAccuracy()(z.to(dev), t.to(dev))) == float(mo.pixel_accuracy_direct(z, t))
+        assert abs(float(losses.Dice()(z.to(dev), t.to(dev))) - mo.dice_smp(z, t)) < 1e-5
+
+
+# ------------------------------------------------------------------ perturbations
+def _spec_u8(fam, level, aux):
+    from image_segmentation_b200.engine import Perturbation as P
+    t = None if aux is None else torch.from_numpy(aux)
+    return {"gaussian_noise": lambda: P.u8_noise(level, aux=t), "gaussian_blur": lambda: P.u8_blur(level),
+            "contrast_increase": lambda: P.u8_contrast(level), "contrast_decrease": lambda: P.u8_contrast(level),
+            "brightness_increase": lambda: P.u8_brightness(level, True),
+            "brightness_decrease": lambda: P.u8_brightness(level, False),
+            "occlusion": lambda: P.u8_occlusion(level, aux=t), "salt_pepper_noise": lambda: P.u8_salt_pepper(level, aux=t)}[fam]()
+
+
+@pytest.mark.parametrize("fam", list(SCRIPT_LEVELS))
+def test_u8_perturbations_golden_bit_exact(dev, fam):
+    """All 80 script levels against the outputs of the reference's own wrappers (tests/golden)."""
+    from image_segmentation_b200 import runtime
+    g = np.load(os.path.join(GOLD, "perturb_u8.npz"))
+    eng = runtime.engine_for(dev)
+    u8 = torch.from_numpy(g["images_u8"])
+    for li, level in enumerate(SCRIPT_LEVELS[fam][1]):
+        aux = g[f"{fam}/{li}/aux"] if f"{fam}/{li}/aux" in g.files else None
+        want = g[f"{fam}/{li}/out"].astype(np.float32) / np.float32(255.0)
+        for src in (u8.permute(0, 2, 3, 1).contiguous().to(dev), (u8.float() / 255.0).to(dev)):  # u8 NHWC and fp32 NCHW
+            got = eng.perturb(src, _spec_u8(fam, level, aux)).cpu().numpy()
+            assert np.array_equal(got, want), (fam, level)
+
+
+def test_float_perturbations_golden_bit_exact(dev):
+    from image_segmentation_b200 import runtime
+    from image_segmentation_b200.engine import Perturbation as P
+    g = np.load(os.path.join(GOLD, "perturb_f.npz"))
+    eng = runtime.engine_for(dev)
+    x = (torch.from_numpy(g["images_u8"]).float() / 255.0).to(dev)
+    mk = {"GaussianPixelNoise": lambda lv, a: P.f_noise(lv, aux=a), "ContrastChange": lambda lv, a: P.f_contrast(lv),
+          "BrightnessChange": lambda lv, a: P.f_brightness(lv), "Occlusion": lambda lv, a: P.f_occlusion(int(lv), aux=a),
+          "SaltAndPepper": lambda lv, a: P.f_salt_pepper(lv, aux=a)}
+    for fam, make in mk.items():
+        for li in range(3):
+            lv = float(g[f"{fam}/{li}/level"])
+            aux = torch.from_numpy(g[f"{fam}/{li}/aux"]) if f"{fam}/{li}/aux" in g.files else None
+            got = eng.perturb(x, make(lv, aux)).cpu().numpy()
+            assert np.array_equal(got, g[f"{fam}/{li}/out"]), (fam, lv)
+
+
+def test_float_blur_matches_restatement(dev):
+    """RepeatedBlur (kornia) is PARITY UNPINNED: compared with the oracle's restatement only."""
+    from image_segmentation_b200.models.processing_blocks import RepeatedBlur
+    x = torch.rand((2, 3, 24, 40), generator=torch.Generator().manual_seed(3))
+    for times in (0, 1, 4, 9):
+        got = RepeatedBlur(times)(x.to(dev)).cpu().numpy()
+        assert np.array_equal(got, po.f_box_blur(x.numpy(), times))
+
+
+def test_dropin_modules_replay_reference_rng(dev):
+    """Seeded host draws + CUDA arithmetic == oracle with the same draws (Dataset wrappers)."""
+    from image_segmentation_b200.customDatasets import perturbations as P
+    from image_segmentation_b200.customDatasets.datasets import CustomImageDataset
+    base = CustomImageDataset(split="test", n=3, h=32, w=48, seed=4)
+    u8 = po.quantise(torch.stack([base[i][0] for i in range(3)]).numpy())
+    random.seed(42); torch.manual_seed(42)
+    ds = P.SaltPepperNoise(base, 0.06)
+    got = np.stack([ds[i][0].numpy() for i in range(3)])
+    random.seed(42); torch.manual_seed(42)
+    want = np.stack([po.dequantise(po.u8_salt_pepper(u8[i], po.replay_salt_pepper_code(0.06, 32, 48))) for i in range(3)])
+    assert np.array_equal(got, want)
+    random.seed(1); torch.manual_seed(1)
+    ds = P.GaussianPixelNoise(base, 8)
+    got = np.stack([ds[i][0].numpy() for i in range(3)])
+    random.seed(1); torch.manual_seed(1)
+    want = np.stack([po.dequantise(po.u8_gaussian_noise(u8[i], torch.normal(0.0, 8.0, size=(3, 32, 48)).numpy())) for i in range(3)])
+    assert np.array_equal(got, want)
+    assert len(ds) == 3 and ds[0][1].dtype == torch.int64
+
+
+def test_full_size_properties(trained, dev):
+    """Size-independent properties at the benchmark's image size: identity levels agree with no
+    perturbation, counts sum to the pixel count, device-RNG families hit the expected fraction."""
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.engine import Perturbation as P
+    m, sd = trained
+    eng = m.engine()
+    imgs, masks = synthetic.make_dataset(16, 256, 256, seed=11)
+    di, dm = imgs.to(dev), masks.to(dev)
+    base = eng.eval_batches(di, dm, None, 8)["cm"].clone()
+    for spec in (P.u8_contrast(1.0), P.u8_brightness(0, True), P.u8_blur(0), P.u8_noise(0), P.u8_occlusion(0),
+                 P.u8_salt_pepper(0.0), P.f_contrast(1.0), P.f_brightness(0)):
+        assert torch.equal(eng.eval_batches(di, dm, spec, 8)["cm"], base), spec.name
+    assert int(base.sum()) == 16 * 256 * 256
+    a = eng.eval_batches(di, dm, P.u8_salt_pepper(0.1, seed=3), 8, want_perturbed=True)["perturbed"]
+    x = synthetic.to_float_nchw(imgs).to(dev)
+    frac = float(((a != x).any(dim=1)).float().mean())
+    assert 0.085 < frac < 0.1  # 1-exp(-0.1) = 0.0952 of pixels hit, minus salt-on-white/pepper-on-black
+    b = eng.eval_batches(di, dm, P.u8_noise(10, seed=5), 8, want_perturbed=True)["perturbed"]
+    d = (b - x)[(x > 0.2) & (x < 0.8)] * 255
+    assert abs(float(d.mean())) < 0.05 and abs(float(d.std()) - 10.0) < 0.2

@@ -1,0 +1,131 @@
+"""CPU-only checks of the host side: C-ABI library loads and exports what include/unet_b200.h declares,
+LUT construction, metric formulas, sharding arithmetic, drop-in module surface, loud failure on CPU."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import metrics_oracle as mo
+from oracle import perturb_oracle as po
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import __graft_entry__ as ge
+    ge.build()
+    from image_segmentation_b200 import _lib
+    return _lib.load()
+
+
+def test_library_exports_every_declared_symbol(lib):
+    header = open(os.path.join(ROOT, "include", "unet_b200.h")).read()
+    declared = set(re.findall(r"\b(ub_[a-z0-9_]+)\s*\(", header))
+    assert {"ub_create", "ub_eval_batches", "ub_forward", "ub_load_weights"} <= declared
+    from image_segmentation_b200 import _lib
+    assert declared == set(_lib.SIGNATURES)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.ub_abi_version() == 1
+
+
+def test_create_fails_loudly_without_gpu(lib):
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    h = ctypes.c_void_p()
+    rc = lib.ub_create(ctypes.byref(h), 0, 0, 3, 3, 8)
+    assert rc < 0 and not h.value and len(lib.ub_last_error(None)) > 0
+
+
+@pytest.mark.parametrize("kind,param,increase", [(0, 1.25, None), (0, 0.1, None), (0, 1.01, None), (1, 45, True),
+                                                 (2, 45, False), (1, 0, True), (2, 5, False)])
+def test_lut_matches_oracle(lib, kind, param, increase):
+    from image_segmentation_b200 import _lib
+    p = _lib.ub_perturb()
+    assert lib.ub_make_lut(ctypes.byref(p), kind, float(param)) == 0
+    want = po.contrast_lut(param) if kind == 0 else po.brightness_lut(param, increase)
+    assert np.array_equal(np.array(list(p.lut), dtype=np.uint8), want)
+    assert p.kind == _lib.UB_P_U8_LUT
+
+
+def test_all_script_luts(lib):
+    from image_segmentation_b200 import _lib
+    from oracle.make_golden import SCRIPT_LEVELS
+    for fam in ("contrast_increase", "contrast_decrease"):
+        for s in SCRIPT_LEVELS[fam][1]:
+            p = _lib.ub_perturb()
+            lib.ub_make_lut(ctypes.byref(p), 0, float(s))
+            assert np.array_equal(np.array(list(p.lut), dtype=np.uint8), po.contrast_lut(s)), s
+
+
+def test_metric_formulas_match_oracle():
+    from image_segmentation_b200 import metrics
+    rng = np.random.default_rng(0)
+    cms = rng.integers(0, 70000, (64, 3, 3))
+    cms[5, 1, :] = 0
+    cms[6, :, :] = 0
+    cms[6, 0, 0] = 10
+    t = torch.from_numpy(cms)
+    iou = metrics.iou_from_cm(t).numpy()
+    pa = metrics.pixel_accuracy_from_cm(t).numpy()
+    for i in range(64):
+        assert iou[i] == mo.iou_from_cm(cms[i])
+        assert pa[i] == mo.pixel_accuracy_from_cm(cms[i])
+        assert metrics.wrapper_dice(torch.tensor(iou[i])).numpy() == mo.wrapper_dice_from_iou(iou[i])
+    sums = torch.rand((7, 3, 3), dtype=torch.float64) * 100
+    sums[2, 1, 2] = 0
+    d = metrics.dice_from_sums(sums)
+    for i in range(7):
+        assert abs(float(d[i]) - mo.dice_from_sums(sums[i].numpy())) < 1e-12
+
+
+@pytest.mark.parametrize("nb,world", [(460, 8), (368, 8), (7, 4), (3, 8), (1, 2), (460, 1)])
+def test_batch_range_partitions(nb, world):
+    from image_segmentation_b200.evaluator import batch_range
+    spans = [batch_range(nb, r, world) for r in range(world)]
+    assert spans[0][0] == 0 and spans[-1][1] == nb
+    for a, b in zip(spans, spans[1:]):
+        assert a[1] == b[0]
+    sizes = [b - a for a, b in spans]
+    assert max(sizes) - min(sizes) <= 1
+
+
+def test_dropin_surface_and_cpu_refusal():
+    from image_segmentation_b200.models import UNet as U
+    from image_segmentation_b200.models import losses, processing_blocks as pb
+    m = U.UNet().eval()
+    assert len(m.state_dict()) == 124 and sum(p.numel() for p in m.parameters()) == 7755907
+    assert sum(p.numel() for p in U.LargeUNet().parameters()) == 31096451
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(1, 3, 64, 64))  # no CPU fallback
+    with pytest.raises(RuntimeError):
+        pb.ContrastChange(1.1)(torch.zeros(1, 3, 8, 8))
+    with pytest.raises(RuntimeError):
+        losses.IoU()(torch.zeros(1, 3, 8, 8), torch.zeros(1, 8, 8, dtype=torch.long))
+    from image_segmentation_b200.customDatasets.datasets import CustomImageDataset
+    with pytest.raises(ValueError):
+        CustomImageDataset(split="bogus")
+    ds = CustomImageDataset(split="test", n=2, h=32, w=32)
+    x, t = ds[0]
+    assert x.dtype == torch.float32 and x.shape == (3, 32, 32) and t.dtype == torch.int64
+    assert torch.equal((x * 255).round() / 255.0, x)
+
+
+def test_rng_replay_helpers_follow_reference_order():
+    """Host draws of the drop-in wrappers == oracle replay (same `random` stream consumption)."""
+    import random
+    from image_segmentation_b200.customDatasets import perturbations as P
+    random.seed(42)
+    a = [P.OcclusionIncrease(None, 15).draw_corner(40, 56) for _ in range(5)]
+    random.seed(42)
+    b = [po.replay_occlusion_corner(15, 40, 56) for _ in range(5)]
+    assert a == b
+    random.seed(7)
+    c = P.SaltPepperNoise(None, 0.1).draw_code(24, 24)
+    random.seed(7)
+    d = po.replay_salt_pepper_code(0.1, 24, 24)
+    assert np.array_equal(c, d)

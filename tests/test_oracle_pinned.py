@@ -1,0 +1,165 @@
+"""Pins the oracle: (a) against the golden vectors produced by the reference's own code
+(tests/golden/*.npz, made by oracle/make_golden.py), always; (b) against the live reference modules
+when /root/reference is present (build container only)."""
+import os
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import metrics_oracle as mo
+from oracle import perturb_oracle as po
+from oracle import refload, unet_oracle
+from oracle.make_golden import SCRIPT_LEVELS, state_checksum
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def g_u8():
+    return np.load(os.path.join(GOLD, "perturb_u8.npz"))
+
+
+@pytest.fixture(scope="module")
+def g_f():
+    return np.load(os.path.join(GOLD, "perturb_f.npz"))
+
+
+def oracle_u8(fam, level, u8, aux):
+    if fam == "gaussian_noise":
+        return po.u8_gaussian_noise(u8, aux)
+    if fam == "gaussian_blur":
+        return po.u8_blur(u8, level)
+    if fam in ("contrast_increase", "contrast_decrease"):
+        return po.u8_contrast(u8, level)
+    if fam == "brightness_increase":
+        return po.u8_brightness(u8, level, True)
+    if fam == "brightness_decrease":
+        return po.u8_brightness(u8, level, False)
+    if fam == "occlusion":
+        return np.stack([po.u8_occlusion(u8[i], level, int(aux[i][0]), int(aux[i][1])) for i in range(len(u8))])
+    if fam == "salt_pepper_noise":
+        return np.stack([po.u8_salt_pepper(u8[i], aux[i]) for i in range(len(u8))])
+    raise KeyError(fam)
+
+
+@pytest.mark.parametrize("fam", list(SCRIPT_LEVELS))
+def test_u8_perturbations_match_golden(g_u8, fam):
+    u8 = g_u8["images_u8"]
+    for li, level in enumerate(SCRIPT_LEVELS[fam][1]):
+        aux = g_u8[f"{fam}/{li}/aux"] if f"{fam}/{li}/aux" in g_u8.files else None
+        got = oracle_u8(fam, level, u8, aux)
+        assert np.array_equal(got, g_u8[f"{fam}/{li}/out"]), (fam, level)
+
+
+def oracle_f(fam, level, x, aux):
+    if fam == "GaussianPixelNoise":
+        return po.f_gaussian_noise(x, aux, level)
+    if fam == "ContrastChange":
+        return po.f_contrast(x, level)
+    if fam == "BrightnessChange":
+        return po.f_brightness(x, level)
+    if fam == "Occlusion":
+        return po.f_occlusion(x, int(level), [tuple(int(v) for v in c) for c in aux])
+    if fam == "SaltAndPepper":
+        return po.f_salt_pepper(x, aux, level)
+    raise KeyError(fam)
+
+
+def test_float_perturbations_match_golden(g_f):
+    x = g_f["images_u8"].astype(np.float32) / np.float32(255.0)
+    fams = sorted({k.split("/")[0] for k in g_f.files if "/" in k})
+    assert fams == ["BrightnessChange", "ContrastChange", "GaussianPixelNoise", "Occlusion", "SaltAndPepper"]
+    for fam in fams:
+        for li in range(3):
+            level = float(g_f[f"{fam}/{li}/level"])
+            aux = g_f[f"{fam}/{li}/aux"] if f"{fam}/{li}/aux" in g_f.files else None
+            got = oracle_f(fam, level, x, aux)
+            assert np.array_equal(got, g_f[f"{fam}/{li}/out"]), (fam, level)  # bit-exact fp32
+
+
+def test_unet_and_metrics_match_golden():
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.UNet import UNet
+    g = np.load(os.path.join(GOLD, "unet_small.npz"))
+    torch.manual_seed(42)
+    m = UNet()
+    assert state_checksum(m.state_dict()) == str(g["seed42_state_sha256"])  # same init as the reference
+    sd = synthetic.randomize_batchnorm(m.state_dict(), seed=7)
+    sd["out.bias"] = torch.from_numpy(g["out_bias"])
+    assert state_checksum(sd) == str(g["final_state_sha256"])
+    imgs, masks = synthetic.make_dataset(2, 32, 64, seed=5)
+    assert np.array_equal(imgs.numpy(), g["images_u8"]) and np.array_equal(masks.numpy(), g["masks_u8"])
+    logits = unet_oracle.forward(sd, synthetic.to_float_nchw(imgs))
+    ref = torch.from_numpy(g["logits"])
+    assert float((logits - ref).abs().max()) <= 2e-5 * float(ref.abs().max())  # fp32, thread-count noise only
+    pred = unet_oracle.hard_prediction(ref).numpy()
+    cm = mo.confusion_matrix(pred, masks.numpy())
+    assert mo.iou_from_cm(cm) == g["iou"][()]
+    assert mo.pixel_accuracy_from_cm(cm) == g["pixel_accuracy"][()]
+    assert float(mo.iou_direct(ref, masks.long())) == float(g["iou"])
+    assert float(mo.pixel_accuracy_direct(ref, masks.long())) == float(g["pixel_accuracy"])
+
+
+def test_dice_restatement_is_self_consistent():
+    """Dice is PARITY UNPINNED (smp absent): only internal consistency can be checked."""
+    g = torch.Generator().manual_seed(0)
+    z = torch.randn((2, 3, 16, 16), generator=g)
+    t = torch.randint(0, 3, (2, 16, 16), generator=g)
+    d = mo.dice_smp(z, t)
+    assert 0.0 < d < 1.0
+    t2 = torch.zeros_like(t)  # classes 1,2 absent -> masked out of the loss
+    s = mo.dice_sums(z, t2).numpy()
+    assert s[1, 2] == 0 and s[2, 2] == 0 and mo.dice_from_sums(s) > 2.0 / 3.0
+
+
+# ------------------------------------------------------------------ live reference (build container)
+@pytest.mark.reference
+def test_live_reference_unet_forward():
+    ns = refload.load()
+    for cls, hw in ((ns.UNet, (32, 64)), (ns.LargeUNet, (32, 32))):
+        torch.manual_seed(3)
+        m = cls().eval()
+        x = torch.rand(2, 3, *hw)
+        with torch.no_grad():
+            ref = m(x)
+        assert torch.equal(unet_oracle.forward(m.state_dict(), x), ref)
+
+
+@pytest.mark.reference
+def test_live_reference_metrics():
+    ns = refload.load()
+    g = torch.Generator().manual_seed(1)
+    for b in (1, 8, 10, 16):
+        z = torch.randn((b, 3, 32, 32), generator=g)
+        t = torch.randint(0, 3, (b, 32, 32), generator=g)
+        if b == 1:
+            t[t == 2] = 0  # a class absent from the targets
+        cm = mo.confusion_matrix(unet_oracle.hard_prediction(z).numpy(), t.numpy())
+        assert float(ns.losses.IoU()(z, t)) == float(mo.iou_from_cm(cm))
+        assert float(ns.losses.PixelAccuracy()(z, t)) == float(mo.pixel_accuracy_from_cm(cm))
+
+
+@pytest.mark.reference
+def test_live_reference_wrapper_levels():
+    """All 79 TestWrapper levels (model_wrappers.py:743-764) of the float-space modules, bit-exact."""
+    ns = refload.load()
+    x = torch.rand((3, 3, 20, 28), generator=torch.Generator().manual_seed(2))
+    xn = x.numpy()
+    for std in [1e-6, 2, 4, 6, 8, 10, 12, 14, 16, 18]:
+        torch.manual_seed(5); ref = ns.blocks.GaussianPixelNoise(std)(x.clone())
+        torch.manual_seed(5); aux = torch.randn_like(x).numpy()
+        assert np.array_equal(po.f_gaussian_noise(xn, aux, std), ref.numpy())
+    for f in [1.0, 1.01, 1.02, 1.03, 1.04, 1.05, 1.1, 1.15, 1.20, 1.25, 0.95, 0.90, 0.85, 0.80, 0.60, 0.40, 0.30, 0.20, 0.10]:
+        assert np.array_equal(po.f_contrast(xn, f), ns.blocks.ContrastChange(f)(x.clone()).numpy())
+    for o in [0, 5, 10, 15, 20, 25, 30, 35, 40, 45, -5, -10, -15, -20, -25, -30, -35, -40, -45]:
+        assert np.array_equal(po.f_brightness(xn, o), ns.blocks.BrightnessChange(o)(x.clone()).numpy())
+    for s in [0, 5, 10, 15, 20, 25, 30, 35, 40, 45]:
+        random.seed(9); ref = ns.blocks.Occlusion(s)(x.clone())
+        random.seed(9); corners = po.replay_f_occlusion_corners(3, s, 20, 28)
+        assert np.array_equal(po.f_occlusion(xn, s, corners), ref.numpy())
+    for a in [0.00, 0.02, 0.04, 0.06, 0.08, 0.10, 0.12, 0.14, 0.16]:
+        torch.manual_seed(6); ref = ns.blocks.SaltAndPepper(a)(x.clone())
+        torch.manual_seed(6); r = torch.rand((3, 1, 20, 28)).numpy()
+        assert np.array_equal(po.f_salt_pepper(xn, r, a), ref.numpy())
