@@ -57,6 +57,12 @@ class RobustnessEvaluator:
     def n_local(self) -> int:
         return self.i1 - self.i0
 
+    def upload(self, images_u8: torch.Tensor, masks_u8: torch.Tensor):
+        """Host -> device copy of this rank's slice into the resident buffers (async on the current stream
+        when the host tensors are pinned).  Used when the evaluation set changes between levels."""
+        self.images.copy_(images_u8[self.i0:self.i1], non_blocking=True)
+        self.masks.copy_(masks_u8[self.i0:self.i1], non_blocking=True)
+
     def local_aux(self, perturbation: Optional[Perturbation]):
         """Parity mode hands aux for the whole dataset; keep this rank's rows."""
         if perturbation is None or perturbation.aux is None:
