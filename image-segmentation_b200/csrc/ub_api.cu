@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -81,6 +82,7 @@ struct ub_ctx {
   EncodeTiledFn encode = nullptr;
   int64_t launches = 0;
   // optional per-launch timing (ub_profile_begin/end): event pairs around every GEMM launch
+  bool force_stream = false;  // UB_FORCE_STREAM=1: never use the weight-stationary pipeline (tests)
   bool profiling = false;
   struct ProfRec { int layer; cudaEvent_t a, b; };
   std::vector<ProfRec> prof;
@@ -283,21 +285,65 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   return UB_OK;
 }
 
+// Pipeline shape for one launch: weight-stationary when every tap of an n-tile fits beside >= 3 A stages
+// (and the persistent grid keeps each CTA on one n-tile), else A ring of 3 + as many B stages as fit.
 template <int N, int S>
-int launch_inst(ub_ctx* ctx, const ConvParams& cp, cudaStream_t st) {
+void choose_pipeline(ConvParams* cp, int grid, int* smem_bytes) {
   using Cfg = ub::ConvCfg<N, S>;
+  const int n_tiles = cp->n_total / N;
+  const int n_taps = (cp->cin / Cfg::BK) * cp->ksize * cp->ksize;
+  const int w_bytes = n_taps * Cfg::B_STAGE_BYTES;
+  const int budget = Cfg::OPERAND_BUDGET;
+  if (w_bytes + 3 * Cfg::A_STAGE_BYTES <= budget && grid % n_tiles == 0) {
+    cp->ws = 1;
+    int sa = (budget - w_bytes) / Cfg::A_STAGE_BYTES;
+    cp->sa = sa > ub::kMaxSA ? ub::kMaxSA : sa;
+    cp->sb = 0;
+    *smem_bytes = cp->sa * Cfg::A_STAGE_BYTES + w_bytes + Cfg::TAIL_BYTES + 1024;
+  } else {
+    cp->ws = 0;
+    cp->sa = 3;
+    int sb = (budget - 3 * Cfg::A_STAGE_BYTES) / Cfg::B_STAGE_BYTES;
+    cp->sb = sb > ub::kMaxSB ? ub::kMaxSB : sb;
+    *smem_bytes = cp->sa * Cfg::A_STAGE_BYTES + cp->sb * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES + 1024;
+  }
+}
+
+template <int N, int S, int KS>
+int launch_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, S, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      ub::kSmemLimit));
     attr_set = true;
   }
+  ConvParams cp = cp_in;
   const int tiles = cp.B * ((cp.H + ub::kTileRows - 1) / ub::kTileRows) * ((cp.W + ub::kTileCols - 1) / ub::kTileCols) *
                     (cp.n_total / N);
   const int grid = tiles < ctx->num_sms ? tiles : ctx->num_sms;
-  ub::conv_tc_kernel<N, S><<<grid, ub::kConvThreads, Cfg::SMEM_BYTES, st>>>(cp);
+  int smem = 0;
+  choose_pipeline<N, S>(&cp, grid, &smem);
+  if (ctx->force_stream) {  // test hook: exercise the streaming path on layers that would be stationary
+    cp.ws = 1 << 30;        // make the ws test fail below
+  }
+  if (cp.ws == (1 << 30)) {
+    using Cfg = ub::ConvCfg<N, S>;
+    cp.ws = 0; cp.sa = 3;
+    int sb = (Cfg::OPERAND_BUDGET - 3 * Cfg::A_STAGE_BYTES) / Cfg::B_STAGE_BYTES;
+    cp.sb = sb > ub::kMaxSB ? ub::kMaxSB : sb;
+    smem = cp.sa * Cfg::A_STAGE_BYTES + cp.sb * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES + 1024;
+  }
+  ub::conv_tc_kernel<N, S, KS><<<grid, ub::kConvThreads, smem, st>>>(cp);
   UB_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
   return UB_OK;
+}
+
+template <int N, int S>
+int launch_ks(ub_ctx* ctx, const ConvParams& cp, cudaStream_t st) {
+  if (cp.ksize == 3) return launch_inst<N, S, 3>(ctx, cp, st);
+  if (cp.ksize == 1) return launch_inst<N, S, 1>(ctx, cp, st);
+  return fail(ctx, UB_ERR_UNSUPPORTED, "kernel size %d", cp.ksize);
 }
 
 int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cudaStream_t st);
@@ -323,17 +369,17 @@ int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cud
   if (cp.mode == ub::EPI_HEAD && block_n != 32) return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs 32 channels");
   if (swz == 128) {
     switch (block_n) {
-      case 32: return launch_inst<32, 128>(ctx, cp, st);
-      case 64: return launch_inst<64, 128>(ctx, cp, st);
-      case 128: return launch_inst<128, 128>(ctx, cp, st);
-      case 256: return launch_inst<256, 128>(ctx, cp, st);
+      case 32: return launch_ks<32, 128>(ctx, cp, st);
+      case 64: return launch_ks<64, 128>(ctx, cp, st);
+      case 128: return launch_ks<128, 128>(ctx, cp, st);
+      case 256: return launch_ks<256, 128>(ctx, cp, st);
     }
   } else {
     switch (block_n) {
-      case 32: return launch_inst<32, 64>(ctx, cp, st);
-      case 64: return launch_inst<64, 64>(ctx, cp, st);
-      case 128: return launch_inst<128, 64>(ctx, cp, st);
-      case 256: return launch_inst<256, 64>(ctx, cp, st);
+      case 32: return launch_ks<32, 64>(ctx, cp, st);
+      case 64: return launch_ks<64, 64>(ctx, cp, st);
+      case 128: return launch_ks<128, 64>(ctx, cp, st);
+      case 256: return launch_ks<256, 64>(ctx, cp, st);
     }
   }
   return fail(ctx, UB_ERR_UNSUPPORTED, "no kernel for BLOCK_N=%d swizzle=%d", block_n, swz);
@@ -593,6 +639,8 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
     return fail(nullptr, UB_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
   ctx->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  const char* fs = getenv("UB_FORCE_STREAM");
+  ctx->force_stream = fs && fs[0] == '1';
   *out = ctx.release();
   return UB_OK;
 }

@@ -7,6 +7,21 @@
   const int tx = lane & 15;
   const int et = threadIdx.x - 128;  // 0..127
   int it = 0;
+  int cur_batch = -1;
+  auto flush_counts = [&](int batch) {
+    const int C = p.n_classes;
+    epi_bar_sync();  // every warp's shared-memory atomics of the finished batch are done
+    if (et < C * C) {
+      const unsigned long long v = atomicExch(&s_cm[et], 0ull);
+      if (v) atomicAdd(&p.cm[static_cast<size_t>(batch) * C * C + et], v);
+    } else if (p.dice && et >= 32 && et < 32 + 2 * C) {
+      const int i = et - 32;
+      const double v = s_dice[i];
+      s_dice[i] = 0.0;
+      atomicAdd(&p.dice[(static_cast<size_t>(batch) * C + (i >> 1)) * 3 + (i & 1)], v);
+    }
+    epi_bar_sync();  // counters are zero again before anyone adds the next batch
+  };
   for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
     const int acc = it & 1;
     const uint32_t use = static_cast<uint32_t>(it >> 1);
@@ -18,6 +33,16 @@
     const int b = mm / tiles_y;
     const bool inb = (y < p.H) && (x < p.W);
     const int n0 = nt * BLOCK_N;
+
+    if (p.mode == EPI_HEAD && p.targets) {
+      // counts accumulate in shared memory across tiles and go to HBM only when the reference batch
+      // changes (and once at the end): <= C*C global atomics per batch per CTA instead of per tile
+      const int batch = (p.img_base + b) / p.ref_batch;
+      if (batch != cur_batch) {
+        if (cur_batch >= 0) flush_counts(cur_batch);
+        cur_batch = batch;
+      }
+    }
 
     mbar_wait(&t_full[acc], use & 1u);
     tc_fence_after();
@@ -61,8 +86,9 @@
       if (inb) {
         if (p.pred_out) p.pred_out[pix] = static_cast<uint8_t>(pred);
         if (p.logits_out) {
-          for (int c = 0; c < C; ++c)
-            p.logits_out[((static_cast<size_t>(b) * C + c) * p.H + y) * p.W + x] = z[c];
+#pragma unroll
+          for (int c = 0; c < kMaxClasses; ++c)
+            if (c < C) p.logits_out[((static_cast<size_t>(b) * C + c) * p.H + y) * p.W + x] = z[c];
         }
       }
       if (p.targets) {
@@ -99,18 +125,6 @@
             }
           }
         }
-        epi_bar_sync();
-        const int batch = (p.img_base + b) / p.ref_batch;
-        if (et < C * C) {
-          const unsigned long long v = atomicExch(&s_cm[et], 0ull);
-          if (v) atomicAdd(&p.cm[static_cast<size_t>(batch) * C * C + et], v);
-        } else if (p.dice && et >= 32 && et < 32 + 2 * C) {
-          const int i = et - 32;
-          const double v = s_dice[i];
-          s_dice[i] = 0.0;
-          atomicAdd(&p.dice[(static_cast<size_t>(batch) * C + (i >> 1)) * 3 + (i & 1)], v);
-        }
-        epi_bar_sync();
       }
     } else {
       // ---- STORE / POOL / CONVT: bias (+ReLU) -> bf16 -> NHWC global store, 32 channels at a time
@@ -172,4 +186,5 @@
       }
     }
   }
+  if (p.mode == EPI_HEAD && p.targets && cur_batch >= 0) flush_counts(cur_batch);
 }

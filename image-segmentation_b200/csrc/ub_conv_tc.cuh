@@ -13,7 +13,9 @@
 //             moving the UMMA descriptor start address down one tile row (16 px * BK * 2 bytes, a
 //             multiple of the swizzle atom), so activations are fetched 3.75x instead of 9x.
 //             Out-of-image halo pixels are zero-filled by TMA = the conv's zero padding.
-// B operand:  weights W2[N][K] (K contiguous), one TMA box {BK, BLOCK_N} per (c, kx, ky).
+// B operand:  weights W2[N][K] (K contiguous), one TMA box {BK, BLOCK_N} per (c, kx, ky): either streamed
+//             through a ring, or — when all taps of an n-tile fit beside the A ring (the thin, high-
+//             resolution layers) — loaded ONCE per persistent CTA and kept resident (ws mode).
 // Warp roles (256 threads): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-7 epilogue.
 // Two TMEM accumulators so the epilogue of tile i overlaps the MMAs of tile i+1 (persistent CTAs).
 #pragma once
@@ -56,7 +58,15 @@ struct ConvParams {
   double* dice;            // [n_batches][C][3] or null
   uint8_t* pred_out;       // [B,H,W] or null
   float* logits_out;       // [B,C,H,W] or null
+  // pipeline shape chosen by the host (ub_api.cu: choose_pipeline)
+  int sa;  // A stages (activation boxes)
+  int sb;  // B stages when streaming weights; unused when ws != 0
+  int ws;  // 1 = weight-stationary: all taps of this CTA's n-tile stay resident in shared memory
 };
+
+constexpr int kMaxSA = 12;
+constexpr int kMaxSB = 8;
+constexpr int kSmemLimit = 232448;  // 227 KB, the sm_100 per-block maximum
 
 template <int BLOCK_N, int SWZ>
 struct ConvCfg {
@@ -64,21 +74,17 @@ struct ConvCfg {
   static constexpr int A_ROW_BYTES = kTileCols * SWZ;                 // one tile row of pixels
   static constexpr int A_STAGE_BYTES = (kTileRows + 2) * A_ROW_BYTES; // 10 rows
   static constexpr int B_STAGE_BYTES = BLOCK_N * SWZ;
-  static constexpr int SA = 3;
-  static constexpr int RING_BUDGET = 222 * 1024;
-  static constexpr int SB_RAW = (RING_BUDGET - SA * A_STAGE_BYTES) / B_STAGE_BYTES;
-  static constexpr int SB = SB_RAW > 8 ? 8 : SB_RAW;
   static constexpr int TMEM_COLS = (2 * BLOCK_N) < 32 ? 32 : (2 * BLOCK_N);
-  static constexpr int OFF_B = SA * A_STAGE_BYTES;
-  static constexpr int OFF_BIAS = OFF_B + SB * B_STAGE_BYTES;
-  static constexpr int OFF_HEAD = OFF_BIAS + 1024 * 4;
-  static constexpr int OFF_BAR = OFF_HEAD + (kMaxClasses * 32 + kMaxClasses) * 4;
-  static constexpr int N_BARS = 2 * SA + 2 * SB + 4;
-  static constexpr int OFF_CM = OFF_BAR + N_BARS * 8;
-  static constexpr int OFF_DICE = OFF_CM + kMaxClasses * kMaxClasses * 8;
-  static constexpr int OFF_TMEM = OFF_DICE + kMaxClasses * 2 * 8;
-  static constexpr int SMEM_BYTES = OFF_TMEM + 16 + 1024;  // + slack for 1024B alignment
-  static_assert(SB >= 2, "B ring too shallow");
+  // fixed-size tail after the two operand regions
+  static constexpr int TAIL_BIAS = 0;
+  static constexpr int TAIL_HEAD = TAIL_BIAS + 1024 * 4;
+  static constexpr int TAIL_BAR = TAIL_HEAD + (kMaxClasses * 32 + kMaxClasses) * 4;
+  static constexpr int N_BARS = 2 * kMaxSA + 2 * kMaxSB + 4 + 1;
+  static constexpr int TAIL_CM = TAIL_BAR + N_BARS * 8;
+  static constexpr int TAIL_DICE = TAIL_CM + kMaxClasses * kMaxClasses * 8;
+  static constexpr int TAIL_TMEM = TAIL_DICE + kMaxClasses * 2 * 8;
+  static constexpr int TAIL_BYTES = TAIL_TMEM + 16;
+  static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;  // 1024 = alignment slack
   static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns");
   static_assert(A_STAGE_BYTES % 1024 == 0 && B_STAGE_BYTES % 1024 == 0, "swizzle atom alignment");
 };
@@ -90,39 +96,44 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <int BLOCK_N, int SWZ>
+template <int BLOCK_N, int SWZ, int KSIZE>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_tc_kernel(const __grid_constant__ ConvParams p) {
   using Cfg = ConvCfg<BLOCK_N, SWZ>;
   constexpr int BK = Cfg::BK;
+  constexpr int PAD = KSIZE / 2;
+  constexpr uint32_t A_BYTES = static_cast<uint32_t>((kTileRows + 2 * PAD) * Cfg::A_ROW_BYTES);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
+  const int k_chunks = p.cin / BK;
+  const int n_taps = k_chunks * KSIZE * KSIZE;       // B tiles per output tile
+  const int b_slots = p.ws ? n_taps : p.sb;          // resident taps, or ring depth
   uint8_t* a_ring = smem;
-  uint8_t* b_ring = smem + Cfg::OFF_B;
-  float* s_bias = reinterpret_cast<float*>(smem + Cfg::OFF_BIAS);
-  float* s_head = reinterpret_cast<float*>(smem + Cfg::OFF_HEAD);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  uint8_t* b_ring = smem + p.sa * Cfg::A_STAGE_BYTES;
+  uint8_t* tail = b_ring + b_slots * Cfg::B_STAGE_BYTES;
+  float* s_bias = reinterpret_cast<float*>(tail + Cfg::TAIL_BIAS);
+  float* s_head = reinterpret_cast<float*>(tail + Cfg::TAIL_HEAD);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail + Cfg::TAIL_BAR);
   uint64_t* a_full = bars;
-  uint64_t* a_empty = bars + Cfg::SA;
-  uint64_t* b_full = bars + 2 * Cfg::SA;
-  uint64_t* b_empty = bars + 2 * Cfg::SA + Cfg::SB;
-  uint64_t* t_full = bars + 2 * Cfg::SA + 2 * Cfg::SB;
+  uint64_t* a_empty = bars + kMaxSA;
+  uint64_t* b_full = bars + 2 * kMaxSA;
+  uint64_t* b_empty = b_full + kMaxSB;
+  uint64_t* t_full = b_empty + kMaxSB;
   uint64_t* t_empty = t_full + 2;
-  unsigned long long* s_cm = reinterpret_cast<unsigned long long*>(smem + Cfg::OFF_CM);
-  double* s_dice = reinterpret_cast<double*>(smem + Cfg::OFF_DICE);
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + Cfg::OFF_TMEM);
+  uint64_t* w_full = t_empty + 2;  // ws mode: all resident weights have landed
+  unsigned long long* s_cm = reinterpret_cast<unsigned long long*>(tail + Cfg::TAIL_CM);
+  double* s_dice = reinterpret_cast<double*>(tail + Cfg::TAIL_DICE);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(tail + Cfg::TAIL_TMEM);
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle so the compiler treats the role branches as warp-uniform
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
-  const int pad = p.ksize >> 1;
   const int tiles_x = (p.W + kTileCols - 1) / kTileCols;
   const int tiles_y = (p.H + kTileRows - 1) / kTileRows;
   const int n_tiles = p.n_total / BLOCK_N;
   const int total_tiles = p.B * tiles_x * tiles_y * n_tiles;
-  const int k_chunks = p.cin / BK;
-  const uint32_t a_bytes = static_cast<uint32_t>((kTileRows + 2 * pad) * Cfg::A_ROW_BYTES);
 
   // ---------------- one-time setup
   for (int i = threadIdx.x; i < p.n_bias; i += kConvThreads) s_bias[i] = p.bias[i];
@@ -137,9 +148,10 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     tma_prefetch_desc(&p.tmB);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < Cfg::SA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-    for (int i = 0; i < Cfg::SB; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
+    for (int i = 0; i < kMaxSA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < kMaxSB; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 128); }
+    mbar_init(w_full, 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -151,10 +163,27 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
 
-  if (warp == 0 && lane == 0) {
-    // ================= TMA producer =================
+  if (warp == 0) {
+    // ================= TMA producer (whole warp runs the loop; one elected lane issues) =================
+    const bool leader = elect_one();
+    if (p.ws) {
+      // weight-stationary: with gridDim a multiple of n_tiles every tile of this CTA has the same n-tile
+      const int nt = blockIdx.x % n_tiles;
+      if (leader) {
+        mbar_arrive_expect_tx(w_full, static_cast<uint32_t>(n_taps * Cfg::B_STAGE_BYTES));
+#pragma unroll 1
+        for (int j = 0; j < n_taps; ++j) {  // consumption order: c outer, kx, ky inner
+          const int c = j / (KSIZE * KSIZE), r = j % (KSIZE * KSIZE);
+          const int kx = r / KSIZE, ky = r % KSIZE;
+          tma_load_2d(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, (ky * KSIZE + kx) * p.cin + c * BK,
+                      nt * BLOCK_N);
+        }
+      }
+      __syncwarp();
+    }
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
+#pragma unroll 1
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int nt = t % n_tiles;
       int m = t / n_tiles;
@@ -162,60 +191,94 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
       m /= tiles_x;
       const int y0 = (m % tiles_y) * kTileRows;
       const int b = m / tiles_y;
+#pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
-        for (int kx = 0; kx < p.ksize; ++kx) {
+#pragma unroll
+        for (int kx = 0; kx < KSIZE; ++kx) {
           mbar_wait(&a_empty[sa], pa ^ 1u);
-          mbar_arrive_expect_tx(&a_full[sa], a_bytes);
-          tma_load_4d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], c * BK, x0 + kx - pad,
-                      y0 - pad, b);
-          if (++sa == Cfg::SA) { sa = 0; pa ^= 1u; }
-          for (int ky = 0; ky < p.ksize; ++ky) {
-            mbar_wait(&b_empty[sb], pb ^ 1u);
-            mbar_arrive_expect_tx(&b_full[sb], Cfg::B_STAGE_BYTES);
-            tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb],
-                        (ky * p.ksize + kx) * p.cin + c * BK, nt * BLOCK_N);
-            if (++sb == Cfg::SB) { sb = 0; pb ^= 1u; }
+          if (leader) {
+            mbar_arrive_expect_tx(&a_full[sa], A_BYTES);
+            tma_load_4d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], c * BK, x0 + kx - PAD, y0 - PAD, b);
+          }
+          __syncwarp();
+          if (++sa == p.sa) { sa = 0; pa ^= 1u; }
+          if (!p.ws) {
+#pragma unroll
+            for (int ky = 0; ky < KSIZE; ++ky) {
+              mbar_wait(&b_empty[sb], pb ^ 1u);
+              if (leader) {
+                mbar_arrive_expect_tx(&b_full[sb], Cfg::B_STAGE_BYTES);
+                tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb],
+                            (ky * KSIZE + kx) * p.cin + c * BK, nt * BLOCK_N);
+              }
+              __syncwarp();
+              if (++sb == p.sb) { sb = 0; pb ^= 1u; }
+            }
           }
         }
       }
     }
-  } else if (warp == 1 && lane == 0) {
-    // ================= MMA issuer (single thread) =================
+  } else if (warp == 1) {
+    // ================= MMA issuer (whole warp runs the loop; ONE fixed lane issues and commits) =================
+    const bool leader = elect_one();
     constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t a_desc_ring = umma_smem_desc<SWZ>(smem_u32(a_ring));
+    const uint64_t b_desc_ring = umma_smem_desc<SWZ>(smem_u32(b_ring));
+    if (p.ws) {
+      mbar_wait(w_full, 0);
+      tc_fence_after();
+    }
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
     int it = 0;
+#pragma unroll 1
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
       const int acc = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
       mbar_wait(&t_empty[acc], (use & 1u) ^ 1u);
       tc_fence_after();
-      const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BLOCK_N);
+      const uint32_t d_tmem = tmem_u + static_cast<uint32_t>(acc * BLOCK_N);
       uint32_t accumulate = 0;
+      int j = 0;  // resident tap index (ws)
+#pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
-        for (int kx = 0; kx < p.ksize; ++kx) {
+#pragma unroll
+        for (int kx = 0; kx < KSIZE; ++kx) {
           mbar_wait(&a_full[sa], pa);
           tc_fence_after();
-          const uint32_t a_base = smem_u32(a_ring + sa * Cfg::A_STAGE_BYTES);
-          for (int ky = 0; ky < p.ksize; ++ky) {
-            mbar_wait(&b_full[sb], pb);
-            tc_fence_after();
-            const uint32_t a_addr = a_base + static_cast<uint32_t>(ky * Cfg::A_ROW_BYTES);
-            const uint32_t b_addr = smem_u32(b_ring + sb * Cfg::B_STAGE_BYTES);
+          const uint64_t a_desc0 = a_desc_ring + static_cast<uint64_t>(sa * (Cfg::A_STAGE_BYTES >> 4));
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k) {
-              umma_bf16(d_tmem, umma_smem_desc<SWZ>(a_addr + k * 32), umma_smem_desc<SWZ>(b_addr + k * 32),
-                        idesc, accumulate);
-              accumulate = 1;
+          for (int ky = 0; ky < KSIZE; ++ky, ++j) {
+            uint64_t b_desc;
+            if (p.ws) {
+              b_desc = b_desc_ring + static_cast<uint64_t>(j * (Cfg::B_STAGE_BYTES >> 4));
+            } else {
+              mbar_wait(&b_full[sb], pb);
+              tc_fence_after();
+              b_desc = b_desc_ring + static_cast<uint64_t>(sb * (Cfg::B_STAGE_BYTES >> 4));
             }
-            umma_commit(&b_empty[sb]);
-            if (++sb == Cfg::SB) { sb = 0; pb ^= 1u; }
+            const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((ky * Cfg::A_ROW_BYTES) >> 4);
+            if (leader) {
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k) {
+                umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, accumulate);
+                accumulate = 1;
+              }
+              if (!p.ws) umma_commit(&b_empty[sb]);
+            }
+            __syncwarp();
+            if (!p.ws) {
+              if (++sb == p.sb) { sb = 0; pb ^= 1u; }
+            }
           }
-          umma_commit(&a_empty[sa]);
-          if (++sa == Cfg::SA) { sa = 0; pa ^= 1u; }
+          if (leader) umma_commit(&a_empty[sa]);
+          __syncwarp();
+          if (++sa == p.sa) { sa = 0; pa ^= 1u; }
         }
       }
-      umma_commit(&t_full[acc]);
+      if (leader) umma_commit(&t_full[acc]);
+      __syncwarp();
     }
   } else if (warp >= 4) {
     // ================= epilogue (128 threads; warp w owns TMEM lanes 32*(w-4)..) =================

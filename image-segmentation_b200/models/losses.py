@@ -16,7 +16,9 @@ def _counts(preds, targets, want_dice=False):
         raise RuntimeError("unet-b200 metrics run on CUDA only (no CPU fallback)")
     eng = runtime.engine_for(preds.device)
     cm, dice = eng.metrics(preds, targets, ref_batch=preds.shape[0], want_dice=want_dice)
-    return cm[0], (dice[0] if dice is not None else None)
+    # the ratios are evaluated on the host in the reference's fp32 arithmetic (bit-reproducible); the
+    # reference syncs here too (.item() per batch, model_wrappers.py:461-463)
+    return cm[0].cpu(), (dice[0].cpu() if dice is not None else None)
 
 
 class IoU(nn.Module):
@@ -26,13 +28,13 @@ class IoU(nn.Module):
 
     def forward(self, preds, targets):
         cm, _ = _counts(preds, targets)
-        return metrics.iou_from_cm(cm, self.eps)
+        return metrics.iou_from_cm(cm, self.eps).to(preds.device)
 
 
 class PixelAccuracy(nn.Module):
     def forward(self, preds, targets):
         cm, _ = _counts(preds, targets)
-        return metrics.pixel_accuracy_from_cm(cm)
+        return metrics.pixel_accuracy_from_cm(cm).to(preds.device)
 
 
 class Dice(nn.Module):
@@ -41,4 +43,4 @@ class Dice(nn.Module):
 
     def forward(self, preds, targets):
         _, sums = _counts(preds, targets, want_dice=True)
-        return metrics.dice_from_sums(sums).to(torch.float32)
+        return metrics.dice_from_sums(sums).to(torch.float32).to(preds.device)
