@@ -3,16 +3,50 @@
 // of the tile and reads its BLOCK_N fp32 columns from TMEM 32 at a time.
 {
   const int wq = warp & 3;
+  const int grp = (warp - 4) >> 2;             // 0: even tiles of this CTA / accumulator 0, 1: odd / accumulator 1
   const int ty = 2 * wq + (lane >> 4);
   const int tx = lane & 15;
-  const int et = threadIdx.x - 128;  // 0..127
+  const int et = (threadIdx.x - 128) & 127;    // 0..127 within the group
+  unsigned long long* s_cm = s_cm_all + grp * (kMaxClasses * kMaxClasses);
+  double* s_dice = s_dice_all + grp * (2 * kMaxClasses);
   int it = 0;
   int cur_batch = -1;
+  // HEAD: every thread counts its own pixels in registers (cell = target*C + prediction, and the
+  // soft-Dice partial sums); they are reduced (warp shuffle -> shared memory -> global atomics) only
+  // when the reference batch changes, every kFlushTiles tiles, and once at the end.
+  constexpr int kCells = kMaxClasses * kMaxClasses;
+  constexpr int kFlushTiles = 4096;
+  uint32_t cnt[kCells];
+  float dsum[2 * kMaxClasses];
+#pragma unroll
+  for (int i = 0; i < kCells; ++i) cnt[i] = 0u;
+#pragma unroll
+  for (int i = 0; i < 2 * kMaxClasses; ++i) dsum[i] = 0.0f;
+  int tiles_since_flush = 0;
   auto flush_counts = [&](int batch) {
     const int C = p.n_classes;
-    epi_bar_sync();  // every warp's shared-memory atomics of the finished batch are done
+#pragma unroll
+    for (int i = 0; i < kCells; ++i) {
+      uint32_t v = cnt[i];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0 && v) atomicAdd(&s_cm[i], static_cast<unsigned long long>(v));
+      cnt[i] = 0u;
+    }
+    if (p.dice) {
+#pragma unroll
+      for (int i = 0; i < 2 * kMaxClasses; ++i) {
+        float v = dsum[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) atomicAdd(&s_dice[i], static_cast<double>(v));
+        dsum[i] = 0.0f;
+      }
+    }
+    epi_bar_sync(grp);  // all four warps of the group have added their share
     if (et < C * C) {
-      const unsigned long long v = atomicExch(&s_cm[et], 0ull);
+      const int tc = et / C, pc = et % C;
+      const unsigned long long v = atomicExch(&s_cm[tc * kMaxClasses + pc], 0ull);
       if (v) atomicAdd(&p.cm[static_cast<size_t>(batch) * C * C + et], v);
     } else if (p.dice && et >= 32 && et < 32 + 2 * C) {
       const int i = et - 32;
@@ -20,10 +54,12 @@
       s_dice[i] = 0.0;
       atomicAdd(&p.dice[(static_cast<size_t>(batch) * C + (i >> 1)) * 3 + (i & 1)], v);
     }
-    epi_bar_sync();  // counters are zero again before anyone adds the next batch
+    epi_bar_sync(grp);  // shared counters are zero again before the next batch is added
+    tiles_since_flush = 0;
   };
   for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-    const int acc = it & 1;
+    if ((it & 1) != grp) continue;
+    const int acc = grp;
     const uint32_t use = static_cast<uint32_t>(it >> 1);
     const int nt = t % n_tiles;
     int mm = t / n_tiles;
@@ -33,14 +69,22 @@
     const int b = mm / tiles_y;
     const bool inb = (y < p.H) && (x < p.W);
     const int n0 = nt * BLOCK_N;
+    int tgt_pre = -1;
 
     if (p.mode == EPI_HEAD && p.targets) {
       // counts accumulate in shared memory across tiles and go to HBM only when the reference batch
       // changes (and once at the end): <= C*C global atomics per batch per CTA instead of per tile
       const int batch = (p.img_base + b) / p.ref_batch;
-      if (batch != cur_batch) {
+      if (batch != cur_batch || tiles_since_flush >= kFlushTiles) {
         if (cur_batch >= 0) flush_counts(cur_batch);
         cur_batch = batch;
+      }
+      ++tiles_since_flush;
+      // the target is fetched before waiting for the accumulator so its latency hides behind the MMAs
+      if (inb) {
+        const size_t tp = (static_cast<size_t>(b) * p.H + y) * p.W + x;
+        tgt_pre = p.target_fmt == 1 ? static_cast<int>(reinterpret_cast<const uint8_t*>(p.targets)[tp])
+                                    : static_cast<int>(reinterpret_cast<const long long*>(p.targets)[tp]);
       }
     }
 
@@ -92,17 +136,11 @@
         }
       }
       if (p.targets) {
-        int tgt = -1;
-        if (inb) {
-          tgt = p.target_fmt == 1 ? static_cast<int>(reinterpret_cast<const uint8_t*>(p.targets)[pix])
-                                  : static_cast<int>(reinterpret_cast<const long long*>(p.targets)[pix]);
-          if (tgt < 0 || tgt >= C) tgt = -1;
-        }
-        const int cell = (tgt >= 0) ? tgt * C + pred : -1;
-        for (int i = 0; i < C * C; ++i) {
-          const unsigned bal = __ballot_sync(0xffffffffu, cell == i);
-          if (lane == 0 && bal) atomicAdd(&s_cm[i], static_cast<unsigned long long>(__popc(bal)));
-        }
+        const int tgt = (tgt_pre >= 0 && tgt_pre < C) ? tgt_pre : -1;
+#pragma unroll
+        for (int tc = 0; tc < kMaxClasses; ++tc)
+#pragma unroll
+          for (int pc = 0; pc < kMaxClasses; ++pc) cnt[tc * kMaxClasses + pc] += (tgt == tc && pred == pc) ? 1u : 0u;
         if (p.dice) {
           // smp DiceLoss(from_logits=True) applies softmax again to the softmax output (losses.py:100)
           float q[kMaxClasses], qmax = pr[0], qsum = 0.0f;
@@ -112,17 +150,9 @@
           for (int c = 0; c < kMaxClasses; ++c) { q[c] = (c < C) ? expf(pr[c] - qmax) : 0.0f; qsum += q[c]; }
 #pragma unroll
           for (int c = 0; c < kMaxClasses; ++c) {
-            float pc = (inb && c < C) ? q[c] / qsum : 0.0f;
-            float ic = (tgt == c) ? pc : 0.0f;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-              pc += __shfl_xor_sync(0xffffffffu, pc, o);
-              ic += __shfl_xor_sync(0xffffffffu, ic, o);
-            }
-            if (lane == 0 && c < C) {
-              atomicAdd(&s_dice[c * 2 + 0], static_cast<double>(ic));
-              atomicAdd(&s_dice[c * 2 + 1], static_cast<double>(pc));
-            }
+            const float pc = (inb && c < C) ? q[c] / qsum : 0.0f;
+            dsum[2 * c + 0] += (tgt == c) ? pc : 0.0f;
+            dsum[2 * c + 1] += pc;
           }
         }
       }

@@ -16,8 +16,9 @@
 // B operand:  weights W2[N][K] (K contiguous), one TMA box {BK, BLOCK_N} per (c, kx, ky): either streamed
 //             through a ring, or — when all taps of an n-tile fit beside the A ring (the thin, high-
 //             resolution layers) — loaded ONCE per persistent CTA and kept resident (ws mode).
-// Warp roles (256 threads): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-7 epilogue.
-// Two TMEM accumulators so the epilogue of tile i overlaps the MMAs of tile i+1 (persistent CTAs).
+// Warp roles (384 threads): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-7 / w8-11 two epilogue
+// groups.  Two TMEM accumulators: group g drains accumulator g (even / odd tiles of this CTA) while the
+// MMA warp fills the other one, so two epilogues and one main loop are in flight per SM.
 #pragma once
 #include "ub_ptx.cuh"
 
@@ -28,7 +29,7 @@ enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_CONVT = 2, EPI_HEAD = 3 };
 constexpr int kTileRows = 8;
 constexpr int kTileCols = 16;
 constexpr int kTileM = 128;
-constexpr int kConvThreads = 256;
+constexpr int kConvThreads = 384;  // 4 control warps + 2 epilogue groups of 4 warps
 constexpr int kMaxClasses = 4;
 
 struct ConvParams {
@@ -80,16 +81,18 @@ struct ConvCfg {
   static constexpr int TAIL_HEAD = TAIL_BIAS + 1024 * 4;
   static constexpr int TAIL_BAR = TAIL_HEAD + (kMaxClasses * 32 + kMaxClasses) * 4;
   static constexpr int N_BARS = 2 * kMaxSA + 2 * kMaxSB + 4 + 1;
-  static constexpr int TAIL_CM = TAIL_BAR + N_BARS * 8;
-  static constexpr int TAIL_DICE = TAIL_CM + kMaxClasses * kMaxClasses * 8;
-  static constexpr int TAIL_TMEM = TAIL_DICE + kMaxClasses * 2 * 8;
-  static constexpr int TAIL_BYTES = TAIL_TMEM + 16;
+  static constexpr int TAIL_CM = TAIL_BAR + N_BARS * 8;                          // 2 groups x C*C counters
+  static constexpr int TAIL_DICE = TAIL_CM + 2 * kMaxClasses * kMaxClasses * 8;  // 2 groups x 2C sums
+  static constexpr int TAIL_TMEM = TAIL_DICE + 2 * kMaxClasses * 2 * 8;
+  static constexpr int TAIL_BYTES = ((TAIL_TMEM + 16 + 1023) / 1024) * 1024;     // keeps the rings 1024B aligned
   static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;  // 1024 = alignment slack
   static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns");
   static_assert(A_STAGE_BYTES % 1024 == 0 && B_STAGE_BYTES % 1024 == 0, "swizzle atom alignment");
 };
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync(int grp) {  // named barrier 1 or 2: the 128 threads of one epilogue group
+  asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
+}
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -103,18 +106,16 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   constexpr int BK = Cfg::BK;
   constexpr int PAD = KSIZE / 2;
   constexpr uint32_t A_BYTES = static_cast<uint32_t>((kTileRows + 2 * PAD) * Cfg::A_ROW_BYTES);
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // pad to 1024 B with pointer arithmetic on the __shared__ array (keeps the address space known to
+  // the compiler: LDS/STS/ATOMS instead of generic accesses)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int k_chunks = p.cin / BK;
   const int n_taps = k_chunks * KSIZE * KSIZE;       // B tiles per output tile
-  const int b_slots = p.ws ? n_taps : p.sb;          // resident taps, or ring depth
-  uint8_t* a_ring = smem;
-  uint8_t* b_ring = smem + p.sa * Cfg::A_STAGE_BYTES;
-  uint8_t* tail = b_ring + b_slots * Cfg::B_STAGE_BYTES;
-  float* s_bias = reinterpret_cast<float*>(tail + Cfg::TAIL_BIAS);
-  float* s_head = reinterpret_cast<float*>(tail + Cfg::TAIL_HEAD);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(tail + Cfg::TAIL_BAR);
+  // [fixed-size tail: bias, head weights, barriers, counters][A ring][B ring or resident weights]
+  float* s_bias = reinterpret_cast<float*>(smem + Cfg::TAIL_BIAS);
+  float* s_head = reinterpret_cast<float*>(smem + Cfg::TAIL_HEAD);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::TAIL_BAR);
   uint64_t* a_full = bars;
   uint64_t* a_empty = bars + kMaxSA;
   uint64_t* b_full = bars + 2 * kMaxSA;
@@ -122,9 +123,11 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   uint64_t* t_full = b_empty + kMaxSB;
   uint64_t* t_empty = t_full + 2;
   uint64_t* w_full = t_empty + 2;  // ws mode: all resident weights have landed
-  unsigned long long* s_cm = reinterpret_cast<unsigned long long*>(tail + Cfg::TAIL_CM);
-  double* s_dice = reinterpret_cast<double*>(tail + Cfg::TAIL_DICE);
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(tail + Cfg::TAIL_TMEM);
+  unsigned long long* s_cm_all = reinterpret_cast<unsigned long long*>(smem + Cfg::TAIL_CM);
+  double* s_dice_all = reinterpret_cast<double*>(smem + Cfg::TAIL_DICE);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + Cfg::TAIL_TMEM);
+  uint8_t* a_ring = smem + Cfg::TAIL_BYTES;
+  uint8_t* b_ring = a_ring + p.sa * Cfg::A_STAGE_BYTES;
 
   // warp index through a shuffle so the compiler treats the role branches as warp-uniform
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
@@ -140,8 +143,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   if (p.mode == EPI_HEAD) {
     for (int i = threadIdx.x; i < p.n_classes * 32; i += kConvThreads) s_head[i] = p.head_w[i];
     if (threadIdx.x < p.n_classes) s_head[kMaxClasses * 32 + threadIdx.x] = p.head_b[threadIdx.x];
-    if (threadIdx.x < kMaxClasses * kMaxClasses) s_cm[threadIdx.x] = 0ull;
-    if (threadIdx.x < kMaxClasses * 2) s_dice[threadIdx.x] = 0.0;
+    if (threadIdx.x < 2 * kMaxClasses * kMaxClasses) s_cm_all[threadIdx.x] = 0ull;
+    if (threadIdx.x < 2 * kMaxClasses * 2) s_dice_all[threadIdx.x] = 0.0;
   }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
@@ -281,7 +284,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
       __syncwarp();
     }
   } else if (warp >= 4) {
-    // ================= epilogue (128 threads; warp w owns TMEM lanes 32*(w-4)..) =================
+    // ================= epilogue (2 groups x 128 threads; warp w owns TMEM lanes 32*(w%4)..) =================
 #include "ub_conv_epilogue.inl"
   }
 
