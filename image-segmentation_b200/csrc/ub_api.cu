@@ -309,14 +309,22 @@ void choose_pipeline(ConvParams* cp, int grid, int* smem_bytes) {
   }
 }
 
-template <int N, int S, int KS>
-int launch_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
+template <int N, int S, int KS, bool WS>
+int launch_kernel(ub_ctx* ctx, const ConvParams& cp, int grid, int smem, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, S, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, S, KS, WS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       ub::kSmemLimit));
     attr_set = true;
   }
+  ub::conv_tc_kernel<N, S, KS, WS><<<grid, ub::kConvThreads, smem, st>>>(cp);
+  UB_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return UB_OK;
+}
+
+template <int N, int S, int KS>
+int launch_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   ConvParams cp = cp_in;
   const int tiles = cp.B * ((cp.H + ub::kTileRows - 1) / ub::kTileRows) * ((cp.W + ub::kTileCols - 1) / ub::kTileCols) *
                     (cp.n_total / N);
@@ -333,10 +341,8 @@ int launch_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
     cp.sb = sb > ub::kMaxSB ? ub::kMaxSB : sb;
     smem = cp.sa * Cfg::A_STAGE_BYTES + cp.sb * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES + 1024;
   }
-  ub::conv_tc_kernel<N, S, KS><<<grid, ub::kConvThreads, smem, st>>>(cp);
-  UB_CUDA(ctx, cudaGetLastError());
-  ctx->launches++;
-  return UB_OK;
+  return cp.ws ? launch_kernel<N, S, KS, true>(ctx, cp, grid, smem, st)
+               : launch_kernel<N, S, KS, false>(ctx, cp, grid, smem, st);
 }
 
 template <int N, int S>

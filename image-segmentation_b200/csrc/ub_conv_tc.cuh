@@ -99,7 +99,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <int BLOCK_N, int SWZ, int KSIZE>
+template <int BLOCK_N, int SWZ, int KSIZE, bool WS>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_tc_kernel(const __grid_constant__ ConvParams p) {
   using Cfg = ConvCfg<BLOCK_N, SWZ>;
@@ -169,7 +169,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   if (warp == 0) {
     // ================= TMA producer (whole warp runs the loop; one elected lane issues) =================
     const bool leader = elect_one();
-    if (p.ws) {
+    if constexpr (WS) {
       // weight-stationary: with gridDim a multiple of n_tiles every tile of this CTA has the same n-tile
       const int nt = blockIdx.x % n_tiles;
       if (leader) {
@@ -205,7 +205,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
           }
           __syncwarp();
           if (++sa == p.sa) { sa = 0; pa ^= 1u; }
-          if (!p.ws) {
+          if constexpr (!WS) {
 #pragma unroll
             for (int ky = 0; ky < KSIZE; ++ky) {
               mbar_wait(&b_empty[sb], pb ^ 1u);
@@ -226,9 +226,14 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     const bool leader = elect_one();
     constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint64_t a_desc_ring = umma_smem_desc<SWZ>(smem_u32(a_ring));
-    const uint64_t b_desc_ring = umma_smem_desc<SWZ>(smem_u32(b_ring));
-    if (p.ws) {
+    // descriptors advance by plain 32-bit adds on the low word ((address >> 4) field); high word is constant
+    const uint64_t desc_a_ring = umma_smem_desc<SWZ>(smem_u32(a_ring));
+    const uint32_t desc_hi = static_cast<uint32_t>(desc_a_ring >> 32);
+    const uint32_t a_lo_ring = static_cast<uint32_t>(desc_a_ring);
+    const uint32_t b_lo_ring = static_cast<uint32_t>(umma_smem_desc<SWZ>(smem_u32(b_ring)));
+    constexpr uint32_t A_STAGE_U = Cfg::A_STAGE_BYTES >> 4, A_ROW_U = Cfg::A_ROW_BYTES >> 4;
+    constexpr uint32_t B_STAGE_U = Cfg::B_STAGE_BYTES >> 4;
+    if constexpr (WS) {
       mbar_wait(w_full, 0);
       tc_fence_after();
     }
@@ -242,41 +247,57 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
       mbar_wait(&t_empty[acc], (use & 1u) ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_u + static_cast<uint32_t>(acc * BLOCK_N);
-      uint32_t accumulate = 0;
-      int j = 0;  // resident tap index (ws)
 #pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
 #pragma unroll
         for (int kx = 0; kx < KSIZE; ++kx) {
           mbar_wait(&a_full[sa], pa);
           tc_fence_after();
-          const uint64_t a_desc0 = a_desc_ring + static_cast<uint64_t>(sa * (Cfg::A_STAGE_BYTES >> 4));
-#pragma unroll
-          for (int ky = 0; ky < KSIZE; ++ky, ++j) {
-            uint64_t b_desc;
-            if (p.ws) {
-              b_desc = b_desc_ring + static_cast<uint64_t>(j * (Cfg::B_STAGE_BYTES >> 4));
-            } else {
-              mbar_wait(&b_full[sb], pb);
-              tc_fence_after();
-              b_desc = b_desc_ring + static_cast<uint64_t>(sb * (Cfg::B_STAGE_BYTES >> 4));
-            }
-            const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((ky * Cfg::A_ROW_BYTES) >> 4);
+          const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(sa) * A_STAGE_U;
+          if constexpr (WS) {
+            // resident weights: tap j = (c*KSIZE + kx)*KSIZE + ky sits at a fixed offset -> one issue region per box
+            const uint32_t b_lo = b_lo_ring + static_cast<uint32_t>((c * KSIZE + kx) * KSIZE) * B_STAGE_U;
             if (leader) {
 #pragma unroll
-              for (int k = 0; k < BK / 16; ++k) {
-                umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, accumulate);
-                accumulate = 1;
+              for (int ky = 0; ky < KSIZE; ++ky) {
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                  const uint32_t al = a_lo + ky * A_ROW_U + 2 * k, bl = b_lo + ky * B_STAGE_U + 2 * k;
+                  if (kx == 0 && ky == 0 && k == 0) {
+                    if (c == 0) umma_bf16_lo<false>(d_tmem, al, bl, desc_hi, idesc);
+                    else umma_bf16_lo<true>(d_tmem, al, bl, desc_hi, idesc);
+                  } else {
+                    umma_bf16_lo<true>(d_tmem, al, bl, desc_hi, idesc);
+                  }
+                }
               }
-              if (!p.ws) umma_commit(&b_empty[sb]);
+              umma_commit(&a_empty[sa]);
             }
             __syncwarp();
-            if (!p.ws) {
+          } else {
+#pragma unroll
+            for (int ky = 0; ky < KSIZE; ++ky) {
+              mbar_wait(&b_full[sb], pb);
+              tc_fence_after();
+              const uint32_t b_lo = b_lo_ring + static_cast<uint32_t>(sb) * B_STAGE_U;
+              if (leader) {
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                  const uint32_t al = a_lo + ky * A_ROW_U + 2 * k, bl = b_lo + 2 * k;
+                  if (kx == 0 && ky == 0 && k == 0) {
+                    if (c == 0) umma_bf16_lo<false>(d_tmem, al, bl, desc_hi, idesc);
+                    else umma_bf16_lo<true>(d_tmem, al, bl, desc_hi, idesc);
+                  } else {
+                    umma_bf16_lo<true>(d_tmem, al, bl, desc_hi, idesc);
+                  }
+                }
+                umma_commit(&b_empty[sb]);
+                if (ky == KSIZE - 1) umma_commit(&a_empty[sa]);
+              }
+              __syncwarp();
               if (++sb == p.sb) { sb = 0; pb ^= 1u; }
             }
           }
-          if (leader) umma_commit(&a_empty[sa]);
-          __syncwarp();
           if (++sa == p.sa) { sa = 0; pa ^= 1u; }
         }
       }
