@@ -38,7 +38,7 @@ struct HostTensor {
 // One tensor-core GEMM layer (conv3x3+BN+ReLU, or ConvTranspose2d k2 s2).
 struct GemmLayer {
   std::string key;  // state_dict prefix of the conv / up module
-  int cin = 0, cout = 0, n_total = 0, ksize = 3, block_n = 0, swz = 128, relu = 1;
+  int cin = 0, cout = 0, n_total = 0, ksize = 3, block_n = 0, bk = 64, relu = 1;
   bool is_convt = false;
   __nv_bfloat16* w = nullptr;  // [n_total][ksize*ksize*cin] bf16, BN folded
   float* bias = nullptr;       // [cout]
@@ -51,15 +51,15 @@ struct Step {
   // RESAMPLE
   const __nv_bfloat16* rs_in = nullptr;
   __nv_bfloat16* rs_out = nullptr;
-  int hi = 0, wi = 0, ho = 0, wo = 0, c = 0, out_cstride = 0, out_choff = 0;
+  int hi = 0, wi = 0, ho = 0, wo = 0, c = 0, out_cgs = 0, out_cg0 = 0;
 };
 
 struct Plan {
   int H = 0, W = 0;
   void* arena = nullptr;
   size_t arena_bytes = 0;
-  __nv_bfloat16* stem_out = nullptr;
-  int stem_cstride = 0, stem_choff = 0;
+  __nv_bfloat16* stem_out = nullptr;  // level-0 concat buffer, channel-blocked
+  int stem_cgs = 0, stem_cg0 = 0;
   float* pert_f32 = nullptr;   // [MB,3,H,W] perturbed image (blur families / perturbed_out staging)
   void* blur_a = nullptr;      // ping-pong planes (fp32-sized)
   void* blur_b = nullptr;
@@ -83,6 +83,7 @@ struct ub_ctx {
   int64_t launches = 0;
   // optional per-launch timing (ub_profile_begin/end): event pairs around every GEMM launch
   bool force_stream = false;  // UB_FORCE_STREAM=1: never use the weight-stationary pipeline (tests)
+  bool use_pdl = true;        // UB_NO_PDL=1: plain stream-ordered launches
   bool profiling = false;
   struct ProfRec { int layer; cudaEvent_t a, b; };
   std::vector<ProfRec> prof;
@@ -143,7 +144,7 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   L.n_total = L.cout;
   L.ksize = 3;
   L.block_n = pick_block_n(L.n_total);
-  L.swz = (L.cin % 64 == 0) ? 128 : 64;
+  L.bk = (L.cin % 64 == 0) ? 64 : 32;
   if (L.cin % 32 != 0 || L.cout % 32 != 0)
     return fail(ctx, UB_ERR_UNSUPPORTED, "%s: channel counts must be multiples of 32", conv_key.c_str());
   const size_t K = static_cast<size_t>(9) * L.cin;
@@ -184,7 +185,7 @@ int pack_convt(ub_ctx* ctx, const std::string& key) {
   L.ksize = 1;
   L.relu = 0;
   L.block_n = pick_block_n(L.n_total);
-  L.swz = (L.cin % 64 == 0) ? 128 : 64;
+  L.bk = (L.cin % 64 == 0) ? 64 : 32;
   if (L.cin % 32 != 0 || L.cout % 32 != 0)
     return fail(ctx, UB_ERR_UNSUPPORTED, "%s: channel counts must be multiples of 32", key.c_str());
   std::vector<__nv_bfloat16> packed(static_cast<size_t>(L.n_total) * L.cin);
@@ -239,120 +240,124 @@ int pack_all(ub_ctx* ctx) {
 }
 
 // ------------------------------------------------------------------ TMA descriptors
-int make_tm_act(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int c_view, int cstride, int W,
-                int H, int B, int box_rows, int swz) {
-  const cuuint64_t dims[4] = {static_cast<cuuint64_t>(c_view), static_cast<cuuint64_t>(W),
-                              static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(B)};
-  const cuuint64_t strides[3] = {static_cast<cuuint64_t>(cstride) * 2, static_cast<cuuint64_t>(W) * cstride * 2,
-                                 static_cast<cuuint64_t>(H) * W * cstride * 2};
-  const cuuint32_t box[4] = {static_cast<cuuint32_t>(swz / 2), ub::kTileCols, static_cast<cuuint32_t>(box_rows), 1};
+// Activations are channel-blocked: [B][cgs][H][W][8] bf16.  The map views `cin/8` consecutive planes starting at
+// `base`: dims {8*W, H, cin/8, B}; one box = {8*(8+2*pad) elements, 16+2*pad rows, bk/8 planes} (ub_conv_tc.cuh).
+int make_tm_act(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int cin, int cgs_total, int W, int H, int B,
+                int ksize, int bk) {
+  const int pad = ksize / 2;
+  const cuuint64_t dims[4] = {static_cast<cuuint64_t>(8) * W, static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(cin / 8),
+                              static_cast<cuuint64_t>(B)};
+  const cuuint64_t strides[3] = {static_cast<cuuint64_t>(W) * 16, static_cast<cuuint64_t>(H) * W * 16,
+                                 static_cast<cuuint64_t>(cgs_total) * H * W * 16};
+  const cuuint32_t box[4] = {static_cast<cuuint32_t>(8 * (ub::kTileCols + 2 * pad)), static_cast<cuuint32_t>(ub::kTileRows + 2 * pad),
+                             static_cast<cuuint32_t>(bk / 8), 1};
   const cuuint32_t estr[4] = {1, 1, 1, 1};
   const CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<__nv_bfloat16*>(base), dims,
-                                 strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                 swz == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                                 strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(ctx, UB_ERR_CUDA, "cuTensorMapEncodeTiled(activation) failed: %d", static_cast<int>(r));
   return UB_OK;
 }
-int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total, int n_total, int block_n, int swz) {
+int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total, int n_total, int block_n, int bk) {
   const cuuint64_t dims[2] = {static_cast<cuuint64_t>(k_total), static_cast<cuuint64_t>(n_total)};
   const cuuint64_t strides[1] = {static_cast<cuuint64_t>(k_total) * 2};
-  const cuuint32_t box[2] = {static_cast<cuuint32_t>(swz / 2), static_cast<cuuint32_t>(block_n)};
+  const cuuint32_t box[2] = {static_cast<cuuint32_t>(bk), static_cast<cuuint32_t>(block_n)};
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(w), dims, strides,
                                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                 swz == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                                 bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(ctx, UB_ERR_CUDA, "cuTensorMapEncodeTiled(weights) failed: %d", static_cast<int>(r));
   return UB_OK;
 }
 
-// Static part of a GEMM step: descriptors over (src view) and the layer's packed weights.
-int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat16* src, int src_cstride,
-              int B, int H, int W, int mode, __nv_bfloat16* out, int out_cstride, int out_choff) {
+// Static part of a GEMM step: descriptors over (src view) and the layer's packed weights.  `src` points at the
+// first channel-group plane the layer reads; `src_cgs` / `out_cgs` are the planes per image of the two buffers.
+int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat16* src, int src_cgs,
+              int B, int H, int W, int mode, __nv_bfloat16* out, int out_cgs, int out_cg0) {
   memset(cp, 0, sizeof(*cp));
   int rc;
-  const int pad = L.ksize / 2;
-  if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin, src_cstride, W, H, B, ub::kTileRows + 2 * pad, L.swz))) return rc;
-  if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, L.block_n, L.swz))) return rc;
+  if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin, src_cgs, W, H, B, L.ksize, L.bk))) return rc;
+  if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, L.block_n, L.bk))) return rc;
   cp->B = B; cp->H = H; cp->W = W;
   cp->cin = L.cin; cp->ksize = L.ksize; cp->n_total = L.n_total;
   cp->mode = mode; cp->relu = L.relu;
   cp->bias = L.bias; cp->n_bias = L.cout;
-  cp->out = out; cp->out_cstride = out_cstride; cp->out_choff = out_choff; cp->cout = L.cout;
+  cp->out = out; cp->out_cgs = out_cgs; cp->out_cg0 = out_cg0; cp->cout = L.cout;
   cp->head_w = ctx->head_w; cp->head_b = ctx->head_b; cp->n_classes = ctx->n_classes;
   cp->ref_batch = 1;
   return UB_OK;
 }
 
-// Pipeline shape for one launch: weight-stationary when every tap of an n-tile fits beside >= 3 A stages
-// (and the persistent grid keeps each CTA on one n-tile), else A ring of 3 + as many B stages as fit.
-template <int N, int S>
-void choose_pipeline(ConvParams* cp, int grid, int* smem_bytes) {
-  using Cfg = ub::ConvCfg<N, S>;
+// Pipeline shape for one launch: weight-stationary when every tap of an n-tile fits beside >= 2 A stages
+// (and the persistent grid keeps each CTA on one n-tile), else a short A ring + as many B stages as fit.
+template <int N, int BK, int KS>
+bool choose_pipeline(ConvParams* cp, int grid, bool allow_ws, int* smem_bytes) {
+  using Cfg = ub::ConvCfg<N, BK, KS>;
   const int n_tiles = cp->n_total / N;
-  const int n_taps = (cp->cin / Cfg::BK) * cp->ksize * cp->ksize;
+  const int n_taps = (cp->cin / BK) * KS * KS;
   const int w_bytes = n_taps * Cfg::B_STAGE_BYTES;
   const int budget = Cfg::OPERAND_BUDGET;
-  if (w_bytes + 3 * Cfg::A_STAGE_BYTES <= budget && grid % n_tiles == 0) {
-    cp->ws = 1;
+  if (allow_ws && w_bytes + 2 * Cfg::A_STAGE_BYTES <= budget && grid % n_tiles == 0) {
     int sa = (budget - w_bytes) / Cfg::A_STAGE_BYTES;
     cp->sa = sa > ub::kMaxSA ? ub::kMaxSA : sa;
     cp->sb = 0;
     *smem_bytes = cp->sa * Cfg::A_STAGE_BYTES + w_bytes + Cfg::TAIL_BYTES + 1024;
-  } else {
-    cp->ws = 0;
-    cp->sa = 3;
-    int sb = (budget - 3 * Cfg::A_STAGE_BYTES) / Cfg::B_STAGE_BYTES;
-    cp->sb = sb > ub::kMaxSB ? ub::kMaxSB : sb;
-    *smem_bytes = cp->sa * Cfg::A_STAGE_BYTES + cp->sb * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES + 1024;
+    return true;
   }
+  cp->sa = Cfg::A_STAGE_BYTES >= 16384 ? 2 : 3;
+  if (N <= 128) cp->sa += 1;
+  int sb = (budget - cp->sa * Cfg::A_STAGE_BYTES) / Cfg::B_STAGE_BYTES;
+  cp->sb = sb > ub::kMaxSB ? ub::kMaxSB : sb;
+  *smem_bytes = cp->sa * Cfg::A_STAGE_BYTES + cp->sb * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES + 1024;
+  return false;
 }
 
-template <int N, int S, int KS, bool WS>
+template <int N, int BK, int KS, bool WS>
 int launch_kernel(ub_ctx* ctx, const ConvParams& cp, int grid, int smem, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, S, KS, WS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, BK, KS, WS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       ub::kSmemLimit));
     attr_set = true;
   }
-  ub::conv_tc_kernel<N, S, KS, WS><<<grid, ub::kConvThreads, smem, st>>>(cp);
-  UB_CUDA(ctx, cudaGetLastError());
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(ub::kConvThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = ctx->use_pdl ? 1 : 0;
+  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_tc_kernel<N, BK, KS, WS>, cp));
   ctx->launches++;
   return UB_OK;
 }
 
-template <int N, int S, int KS>
+template <int N, int BK, int KS>
 int launch_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   ConvParams cp = cp_in;
   const int tiles = cp.B * ((cp.H + ub::kTileRows - 1) / ub::kTileRows) * ((cp.W + ub::kTileCols - 1) / ub::kTileCols) *
                     (cp.n_total / N);
   const int grid = tiles < ctx->num_sms ? tiles : ctx->num_sms;
   int smem = 0;
-  choose_pipeline<N, S>(&cp, grid, &smem);
-  if (ctx->force_stream) {  // test hook: exercise the streaming path on layers that would be stationary
-    cp.ws = 1 << 30;        // make the ws test fail below
-  }
-  if (cp.ws == (1 << 30)) {
-    using Cfg = ub::ConvCfg<N, S>;
-    cp.ws = 0; cp.sa = 3;
-    int sb = (Cfg::OPERAND_BUDGET - 3 * Cfg::A_STAGE_BYTES) / Cfg::B_STAGE_BYTES;
-    cp.sb = sb > ub::kMaxSB ? ub::kMaxSB : sb;
-    smem = cp.sa * Cfg::A_STAGE_BYTES + cp.sb * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES + 1024;
-  }
-  return cp.ws ? launch_kernel<N, S, KS, true>(ctx, cp, grid, smem, st)
-               : launch_kernel<N, S, KS, false>(ctx, cp, grid, smem, st);
+  // UB_FORCE_STREAM=1 (test hook): exercise the streaming path on layers that would be weight-stationary
+  const bool ws = choose_pipeline<N, BK, KS>(&cp, grid, !ctx->force_stream, &smem);
+  return ws ? launch_kernel<N, BK, KS, true>(ctx, cp, grid, smem, st)
+            : launch_kernel<N, BK, KS, false>(ctx, cp, grid, smem, st);
 }
 
-template <int N, int S>
+template <int N, int BK>
 int launch_ks(ub_ctx* ctx, const ConvParams& cp, cudaStream_t st) {
-  if (cp.ksize == 3) return launch_inst<N, S, 3>(ctx, cp, st);
-  if (cp.ksize == 1) return launch_inst<N, S, 1>(ctx, cp, st);
+  if (cp.ksize == 3) return launch_inst<N, BK, 3>(ctx, cp, st);
+  if (cp.ksize == 1) return launch_inst<N, BK, 1>(ctx, cp, st);
   return fail(ctx, UB_ERR_UNSUPPORTED, "kernel size %d", cp.ksize);
 }
 
-int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cudaStream_t st);
+int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStream_t st);
 
 cudaEvent_t take_event(ub_ctx* ctx) {
   if (!ctx->event_pool.empty()) { cudaEvent_t e = ctx->event_pool.back(); ctx->event_pool.pop_back(); return e; }
@@ -361,34 +366,32 @@ cudaEvent_t take_event(ub_ctx* ctx) {
   return e;
 }
 
-int launch_gemm(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cudaStream_t st, int layer = -1) {
-  if (!ctx->profiling) return launch_gemm_raw(ctx, cp, block_n, swz, st);
+int launch_gemm(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStream_t st, int layer = -1) {
+  if (!ctx->profiling) return launch_gemm_raw(ctx, cp, block_n, bk, st);
   ub_ctx::ProfRec r{layer, take_event(ctx), take_event(ctx)};
   cudaEventRecord(r.a, st);
-  const int rc = launch_gemm_raw(ctx, cp, block_n, swz, st);
+  const int rc = launch_gemm_raw(ctx, cp, block_n, bk, st);
   cudaEventRecord(r.b, st);
   ctx->prof.push_back(r);
   return rc;
 }
 
-int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int swz, cudaStream_t st) {
+int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStream_t st) {
   if (cp.mode == ub::EPI_HEAD && block_n != 32) return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs 32 channels");
-  if (swz == 128) {
-    switch (block_n) {
-      case 32: return launch_ks<32, 128>(ctx, cp, st);
-      case 64: return launch_ks<64, 128>(ctx, cp, st);
-      case 128: return launch_ks<128, 128>(ctx, cp, st);
-      case 256: return launch_ks<256, 128>(ctx, cp, st);
-    }
-  } else {
+  if (bk == 64) {
     switch (block_n) {
       case 32: return launch_ks<32, 64>(ctx, cp, st);
       case 64: return launch_ks<64, 64>(ctx, cp, st);
       case 128: return launch_ks<128, 64>(ctx, cp, st);
       case 256: return launch_ks<256, 64>(ctx, cp, st);
     }
+  } else if (cp.ksize == 3) {  // the two Cin = 32 layers (enc1.conv.0, dec4.conv.3)
+    switch (block_n) {
+      case 32: return launch_inst<32, 32, 3>(ctx, cp, st);
+      case 64: return launch_inst<64, 32, 3>(ctx, cp, st);
+    }
   }
-  return fail(ctx, UB_ERR_UNSUPPORTED, "no kernel for BLOCK_N=%d swizzle=%d", block_n, swz);
+  return fail(ctx, UB_ERR_UNSUPPORTED, "no kernel for BLOCK_N=%d BK=%d ksize=%d", block_n, bk, cp.ksize);
 }
 
 // ------------------------------------------------------------------ execution plan for one resolution
@@ -432,36 +435,38 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
   pl->pert_f32 = reinterpret_cast<float*>(bufp(i_pert));
   pl->blur_a = bufp(i_bla);
   pl->blur_b = bufp(i_blb);
+  // every activation buffer is channel-blocked [MB][cgs][h][w][8]; plane(l) = elements of one channel group
+  auto plane = [&](int l) { return static_cast<size_t>(hl(l)) * wl(l) * 8; };
+  auto skip_half = [&](int l) { return bufp(i_cat[l]) + static_cast<size_t>(skip_width(l) / 8) * plane(l); };
   pl->stem_out = bufp(i_cat[0]);
-  pl->stem_cstride = 2 * skip_width(0);
-  pl->stem_choff = skip_width(0);
+  pl->stem_cgs = 2 * skip_width(0) / 8;
+  pl->stem_cg0 = skip_width(0) / 8;
 
-  auto add_gemm = [&](const std::string& lkey, const __nv_bfloat16* src, int src_cstride, int h, int w, int mode,
-                      __nv_bfloat16* dst, int dst_cstride, int dst_choff) -> int {
+  auto add_gemm = [&](const std::string& lkey, const __nv_bfloat16* src, int src_cgs, int h, int w, int mode,
+                      __nv_bfloat16* dst, int dst_cgs, int dst_cg0) -> int {
     auto li = ctx->layer_by_key.find(lkey);
     if (li == ctx->layer_by_key.end()) return fail(ctx, UB_ERR_STATE, "layer %s not packed", lkey.c_str());
     Step s;
     s.kind = Step::GEMM;
     s.layer = li->second;
-    int r2 = fill_gemm(ctx, &s.cp, ctx->layers[s.layer], src, src_cstride, MB, h, w, mode, dst, dst_cstride, dst_choff);
+    int r2 = fill_gemm(ctx, &s.cp, ctx->layers[s.layer], src, src_cgs, MB, h, w, mode, dst, dst_cgs, dst_cg0);
     if (r2) return r2;
     pl->steps.push_back(s);
     return UB_OK;
   };
   char k[128];
-  // encoder (models/UNet.py:63-65): conv.0 -> conv.3 + MaxPool into the skip half of the next concat buffer
+  // encoder (models/UNet.py:63-65): conv.0 -> conv.3 + MaxPool into the skip planes of the next concat buffer
   for (int i = 1; i <= n; ++i) {
     snprintf(k, sizeof(k), "enc%d.block.0.conv", i);
-    const int cs = 2 * skip_width(i - 1);
-    if ((rc = add_gemm(std::string(k) + ".0", bufp(i_cat[i - 1]) + skip_width(i - 1), cs, hl(i - 1), wl(i - 1),
-                       ub::EPI_STORE, bufp(i_enc[i]), skip_width(i), 0))) return rc;
-    if ((rc = add_gemm(std::string(k) + ".3", bufp(i_enc[i]), skip_width(i), hl(i - 1), wl(i - 1), ub::EPI_POOL,
-                       bufp(i_cat[i]), 2 * skip_width(i), skip_width(i)))) return rc;
+    if ((rc = add_gemm(std::string(k) + ".0", skip_half(i - 1), 2 * skip_width(i - 1) / 8, hl(i - 1), wl(i - 1),
+                       ub::EPI_STORE, bufp(i_enc[i]), skip_width(i) / 8, 0))) return rc;
+    if ((rc = add_gemm(std::string(k) + ".3", bufp(i_enc[i]), skip_width(i) / 8, hl(i - 1), wl(i - 1), ub::EPI_POOL,
+                       bufp(i_cat[i]), 2 * skip_width(i) / 8, skip_width(i) / 8))) return rc;
   }
   // bottleneck (UNet.py:67), not pooled
-  if ((rc = add_gemm("bottleneck.conv.0", bufp(i_cat[n]) + skip_width(n), 2 * skip_width(n), hl(n), wl(n), ub::EPI_STORE,
-                     bufp(i_ba), cb, 0))) return rc;
-  if ((rc = add_gemm("bottleneck.conv.3", bufp(i_ba), cb, hl(n), wl(n), ub::EPI_STORE, bufp(i_bb), cb, 0))) return rc;
+  if ((rc = add_gemm("bottleneck.conv.0", skip_half(n), 2 * skip_width(n) / 8, hl(n), wl(n), ub::EPI_STORE,
+                     bufp(i_ba), cb / 8, 0))) return rc;
+  if ((rc = add_gemm("bottleneck.conv.3", bufp(i_ba), cb / 8, hl(n), wl(n), ub::EPI_STORE, bufp(i_bb), cb / 8, 0))) return rc;
   // decoder (UNet.py:69-72, processing_blocks.py:105-109)
   const __nv_bfloat16* x = bufp(i_bb);
   int xc = cb, xh = hl(n), xw = wl(n);
@@ -469,25 +474,22 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
     const int l = n + 1 - j;
     snprintf(k, sizeof(k), "dec%d", j);
     const int sw = skip_width(l);
-    (void)xc;
     if (2 * xh == hl(l) && 2 * xw == wl(l)) {
-      // F.interpolate is the identity: ConvT scatters straight into channels [0,sw) of the concat buffer
-      if ((rc = add_gemm(std::string(k) + ".up", x, ctx->layers[ctx->layer_by_key[std::string(k) + ".up"]].cin, xh, xw,
-                         ub::EPI_CONVT, bufp(i_cat[l]), 2 * sw, 0))) return rc;
+      // F.interpolate is the identity: ConvT scatters straight into planes [0, sw/8) of the concat buffer
+      if ((rc = add_gemm(std::string(k) + ".up", x, xc / 8, xh, xw, ub::EPI_CONVT, bufp(i_cat[l]), 2 * sw / 8, 0))) return rc;
     } else {
-      if ((rc = add_gemm(std::string(k) + ".up", x, ctx->layers[ctx->layer_by_key[std::string(k) + ".up"]].cin, xh, xw,
-                         ub::EPI_CONVT, bufp(i_up), sw, 0))) return rc;
+      if ((rc = add_gemm(std::string(k) + ".up", x, xc / 8, xh, xw, ub::EPI_CONVT, bufp(i_up), sw / 8, 0))) return rc;
       Step s;
       s.kind = Step::RESAMPLE;
       s.rs_in = bufp(i_up); s.rs_out = bufp(i_cat[l]);
-      s.hi = 2 * xh; s.wi = 2 * xw; s.ho = hl(l); s.wo = wl(l); s.c = sw; s.out_cstride = 2 * sw; s.out_choff = 0;
+      s.hi = 2 * xh; s.wi = 2 * xw; s.ho = hl(l); s.wo = wl(l); s.c = sw; s.out_cgs = 2 * sw / 8; s.out_cg0 = 0;
       pl->steps.push_back(s);
     }
-    if ((rc = add_gemm(std::string(k) + ".conv.conv.0", bufp(i_cat[l]), 2 * sw, hl(l), wl(l), ub::EPI_STORE,
-                       bufp(i_da[j]), sw, 0))) return rc;
+    if ((rc = add_gemm(std::string(k) + ".conv.conv.0", bufp(i_cat[l]), 2 * sw / 8, hl(l), wl(l), ub::EPI_STORE,
+                       bufp(i_da[j]), sw / 8, 0))) return rc;
     const bool last = (j == n + 1);
-    if ((rc = add_gemm(std::string(k) + ".conv.conv.3", bufp(i_da[j]), sw, hl(l), wl(l), last ? ub::EPI_HEAD : ub::EPI_STORE,
-                       bufp(i_db[j]), sw, 0))) return rc;
+    if ((rc = add_gemm(std::string(k) + ".conv.conv.3", bufp(i_da[j]), sw / 8, hl(l), wl(l), last ? ub::EPI_HEAD : ub::EPI_STORE,
+                       bufp(i_db[j]), sw / 8, 0))) return rc;
     x = bufp(i_db[j]); xc = sw; xh = hl(l); xw = wl(l);
   }
   *out = pl.get();
@@ -562,10 +564,10 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
     ub::PerturbDev none;
     memset(&none, 0, sizeof(none));
     ub::stem_kernel<<<blocks_for(px, 256), 256, 0, st>>>(none, ctx->stem, dst, UB_IMG_F32_NCHW, nb, H, W, pl->stem_out,
-                                                        pl->stem_cstride, pl->stem_choff, nullptr);
+                                                        pl->stem_cgs, pl->stem_cg0, nullptr);
   } else {
-    ub::stem_kernel<<<blocks_for(px, 256), 256, 0, st>>>(P, ctx->stem, img, fmt, nb, H, W, pl->stem_out, pl->stem_cstride,
-                                                        pl->stem_choff, perturbed_out);
+    ub::stem_kernel<<<blocks_for(px, 256), 256, 0, st>>>(P, ctx->stem, img, fmt, nb, H, W, pl->stem_out, pl->stem_cgs,
+                                                        pl->stem_cg0, perturbed_out);
   }
   UB_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
@@ -573,7 +575,7 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
     if (s.kind == Step::RESAMPLE) {
       const size_t total = static_cast<size_t>(nb) * s.ho * s.wo * (s.c / 8);
       ub::resample_bilinear_kernel<<<blocks_for(total, 256), 256, 0, st>>>(s.rs_in, nb, s.hi, s.wi, s.c, s.rs_out, s.ho, s.wo,
-                                                                           s.out_cstride, s.out_choff);
+                                                                           s.out_cgs, s.out_cg0);
       UB_CUDA(ctx, cudaGetLastError());
       ctx->launches++;
       continue;
@@ -585,7 +587,7 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
       cp.cm = ha.cm; cp.dice = ha.dice; cp.pred_out = ha.pred; cp.logits_out = ha.logits;
     }
     const GemmLayer& L = ctx->layers[s.layer];
-    if ((rc = launch_gemm(ctx, cp, L.block_n, L.swz, st, s.layer))) return rc;
+    if ((rc = launch_gemm(ctx, cp, L.block_n, L.bk, st, s.layer))) return rc;
   }
   return UB_OK;
 }
@@ -647,6 +649,8 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   ctx->encode = reinterpret_cast<EncodeTiledFn>(fn);
   const char* fs = getenv("UB_FORCE_STREAM");
   ctx->force_stream = fs && fs[0] == '1';
+  const char* np = getenv("UB_NO_PDL");
+  ctx->use_pdl = !(np && np[0] == '1');
   *out = ctx.release();
   return UB_OK;
 }
@@ -843,28 +847,28 @@ static int debug_layer(ub_ctx* ctx, const char* key, const void* in, void* out, 
   if (it == ctx->layer_by_key.end()) return fail(ctx, UB_ERR_INVALID, "no such layer: %s", key);
   const GemmLayer& L = ctx->layers[it->second];
   ConvParams cp;
-  if ((rc = fill_gemm(ctx, &cp, L, static_cast<const __nv_bfloat16*>(in), L.cin, n, h, w, mode,
-                      static_cast<__nv_bfloat16*>(out), L.cout, 0)))
+  if ((rc = fill_gemm(ctx, &cp, L, static_cast<const __nv_bfloat16*>(in), L.cin / 8, n, h, w, mode,
+                      static_cast<__nv_bfloat16*>(out), L.cout / 8, 0)))
     return rc;
-  return launch_gemm(ctx, cp, L.block_n, L.swz, static_cast<cudaStream_t>(stream), it->second);
+  return launch_gemm(ctx, cp, L.block_n, L.bk, static_cast<cudaStream_t>(stream), it->second);
 }
 
-int ub_debug_conv3x3(ub_ctx* ctx, const char* conv_key, const void* in_bf16_nhwc, void* out_bf16_nhwc, int n, int h,
+int ub_debug_conv3x3(ub_ctx* ctx, const char* conv_key, const void* in_bf16_cg8, void* out_bf16_cg8, int n, int h,
                      int w, int pool, void* stream) {
   if (ctx && conv_key) {
     auto it = ctx->layer_by_key.find(conv_key);
     if (it != ctx->layer_by_key.end() && ctx->layers[it->second].is_convt) return fail(ctx, UB_ERR_INVALID, "%s is a ConvTranspose", conv_key);
   }
-  return debug_layer(ctx, conv_key, in_bf16_nhwc, out_bf16_nhwc, n, h, w, pool ? ub::EPI_POOL : ub::EPI_STORE, stream);
+  return debug_layer(ctx, conv_key, in_bf16_cg8, out_bf16_cg8, n, h, w, pool ? ub::EPI_POOL : ub::EPI_STORE, stream);
 }
 
-int ub_debug_convt2x2(ub_ctx* ctx, const char* up_key, const void* in_bf16_nhwc, void* out_bf16_nhwc, int n, int h,
+int ub_debug_convt2x2(ub_ctx* ctx, const char* up_key, const void* in_bf16_cg8, void* out_bf16_cg8, int n, int h,
                       int w, void* stream) {
   if (ctx && up_key) {
     auto it = ctx->layer_by_key.find(up_key);
     if (it != ctx->layer_by_key.end() && !ctx->layers[it->second].is_convt) return fail(ctx, UB_ERR_INVALID, "%s is not a ConvTranspose", up_key);
   }
-  return debug_layer(ctx, up_key, in_bf16_nhwc, out_bf16_nhwc, n, h, w, ub::EPI_CONVT, stream);
+  return debug_layer(ctx, up_key, in_bf16_cg8, out_bf16_cg8, n, h, w, ub::EPI_CONVT, stream);
 }
 
 }  // extern "C"

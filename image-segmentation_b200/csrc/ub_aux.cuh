@@ -9,20 +9,21 @@ namespace ub {
 // F.interpolate(mode="bilinear", align_corners=True), models/processing_blocks.py:107.  Only dec1
 // needs it for real (ConvT doubles the un-pooled bottleneck to 2x the skip size; this brings it
 // back); elsewhere input and output sizes agree and the ConvT epilogue writes the concat buffer
-// directly.  NHWC bf16; one thread per (output pixel, 8 channels) -> 16-byte loads and stores.
+// directly.  Channel-blocked bf16 [n][cgs][H][W][8]; one thread per (channel group, output pixel) ->
+// 16-byte loads and stores, consecutive threads on consecutive pixels of one plane.
 __global__ void resample_bilinear_kernel(const __nv_bfloat16* __restrict__ in, int n, int Hi, int Wi,
                                          int C, __nv_bfloat16* __restrict__ out, int Ho, int Wo,
-                                         int out_cstride, int out_choff) {
+                                         int out_cgs, int out_cg0) {
   const int groups = C / 8;
   const size_t total = static_cast<size_t>(n) * Ho * Wo * groups;
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= total) return;
-  const int g = static_cast<int>(i % groups);
-  size_t r = i / groups;
-  const int ox = static_cast<int>(r % Wo);
-  r /= Wo;
+  const int ox = static_cast<int>(i % Wo);
+  size_t r = i / Wo;
   const int oy = static_cast<int>(r % Ho);
-  const int b = static_cast<int>(r / Ho);
+  r /= Ho;
+  const int g = static_cast<int>(r % groups);
+  const int b = static_cast<int>(r / groups);
   const float sy = Ho > 1 ? static_cast<float>(Hi - 1) / static_cast<float>(Ho - 1) : 0.0f;
   const float sx = Wo > 1 ? static_cast<float>(Wi - 1) / static_cast<float>(Wo - 1) : 0.0f;
   const float fy = sy * oy, fx = sx * ox;
@@ -31,7 +32,7 @@ __global__ void resample_bilinear_kernel(const __nv_bfloat16* __restrict__ in, i
   const float ly = fy - y0, lx = fx - x0;
   const float hy = 1.0f - ly, hx = 1.0f - lx;
   auto ld = [&](int yy, int xx) {
-    return *reinterpret_cast<const uint4*>(in + ((static_cast<size_t>(b) * Hi + yy) * Wi + xx) * C + g * 8);
+    return reinterpret_cast<const uint4*>(in)[((static_cast<size_t>(b) * groups + g) * Hi + yy) * Wi + xx];
   };
   const uint4 v00 = ld(y0, x0), v01 = ld(y0, x1), v10 = ld(y1, x0), v11 = ld(y1, x1);
   const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&v00);
@@ -48,7 +49,7 @@ __global__ void resample_bilinear_kernel(const __nv_bfloat16* __restrict__ in, i
     const float r1 = hy * (hx * fa.y + lx * fb.y) + ly * (hx * fc.y + lx * fd.y);
     op[k] = __floats2bfloat162_rn(r0, r1);
   }
-  *reinterpret_cast<uint4*>(out + ((static_cast<size_t>(b) * Ho + oy) * Wo + ox) * out_cstride + out_choff + g * 8) = o;
+  reinterpret_cast<uint4*>(out)[((static_cast<size_t>(b) * out_cgs + out_cg0 + g) * Ho + oy) * Wo + ox] = o;
 }
 
 // Layout converters for the test hooks (NCHW fp32 <-> NHWC bf16 are done by the caller in torch);

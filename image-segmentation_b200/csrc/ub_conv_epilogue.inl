@@ -1,15 +1,15 @@
 // Epilogue body of conv_tc_kernel (included inside the `warp >= 4` branch).
-// Thread (wq, lane) owns accumulator row m = 32*wq + lane = pixel (ty = 2*wq + lane/16, tx = lane%16)
-// of the tile and reads its BLOCK_N fp32 columns from TMEM 32 at a time.
+// Thread (wq, lane) owns accumulator row m = 32*wq + lane = pixel (ty = 4*wq + lane/8, tx = lane%8)
+// of the 16x8 tile and reads its BLOCK_N fp32 columns from TMEM 32 at a time (double-buffered: the
+// next tcgen05.ld is in flight while the current 32 channels are converted and stored).
 {
   const int wq = warp & 3;
-  const int grp = (warp - 4) >> 2;             // 0: even tiles of this CTA / accumulator 0, 1: odd / accumulator 1
-  const int ty = 2 * wq + (lane >> 4);
-  const int tx = lane & 15;
+  const int grp = (warp - 4) >> 2;             // tiles it with it % kEpiGroups == grp
+  const int ty = 4 * wq + (lane >> 3);
+  const int tx = lane & 7;
   const int et = (threadIdx.x - 128) & 127;    // 0..127 within the group
   unsigned long long* s_cm = s_cm_all + grp * (kMaxClasses * kMaxClasses);
   double* s_dice = s_dice_all + grp * (2 * kMaxClasses);
-  int it = 0;
   int cur_batch = -1;
   // HEAD: every thread counts its own pixels in registers (cell = target*C + prediction, and the
   // soft-Dice partial sums); they are reduced (warp shuffle -> shared memory -> global atomics) only
@@ -57,10 +57,12 @@
     epi_bar_sync(grp);  // shared counters are zero again before the next batch is added
     tiles_since_flush = 0;
   };
-  for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-    if ((it & 1) != grp) continue;
-    const int acc = grp;
-    const uint32_t use = static_cast<uint32_t>(it >> 1);
+
+  int it = grp;
+#pragma unroll 1
+  for (int t = blockIdx.x + grp * gridDim.x; t < total_tiles; t += kEpiGroups * gridDim.x, it += kEpiGroups) {
+    const int acc = it % ACC;
+    const uint32_t use = static_cast<uint32_t>(it / ACC);
     const int nt = t % n_tiles;
     int mm = t / n_tiles;
     const int x = (mm % tiles_x) * kTileCols + tx;
@@ -72,7 +74,7 @@
     int tgt_pre = -1;
 
     if (p.mode == EPI_HEAD && p.targets) {
-      // counts accumulate in shared memory across tiles and go to HBM only when the reference batch
+      // counts accumulate in registers across tiles and go to HBM only when the reference batch
       // changes (and once at the end): <= C*C global atomics per batch per CTA instead of per tile
       const int batch = (p.img_base + b) / p.ref_batch;
       if (batch != cur_batch || tiles_since_flush >= kFlushTiles) {
@@ -92,25 +94,42 @@
     tc_fence_after();
     const uint32_t t_addr =
         tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + static_cast<uint32_t>(acc * BLOCK_N);
+    auto release_acc = [&]() {  // every column of this accumulator is in registers: hand it back to the MMA warp
+      tc_fence_before();
+      mbar_arrive(&t_empty[acc]);
+    };
 
     if (p.mode == EPI_HEAD) {
       // ---- dec4.conv.3 epilogue: bias+ReLU (fp32) -> 1x1 head -> softmax -> argmax -> counts
       uint32_t r[32];
       tmem_ld_32x32(t_addr, r);
       tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(&t_empty[acc]);
+      release_acc();
       const int C = p.n_classes;
       float z[kMaxClasses];
 #pragma unroll
       for (int c = 0; c < kMaxClasses; ++c) z[c] = (c < C) ? s_head[kMaxClasses * 32 + c] : -INFINITY;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        float v = __uint_as_float(r[j]) + s_bias[j];
-        v = p.relu ? fmaxf(v, 0.0f) : v;
+      for (int j4 = 0; j4 < 8; ++j4) {
+        const float4 bz = reinterpret_cast<const float4*>(s_bias)[j4];
+        const float bb[4] = {bz.x, bz.y, bz.z, bz.w};
+        float v[4];
 #pragma unroll
-        for (int c = 0; c < kMaxClasses; ++c)
-          if (c < C) z[c] = fmaf(s_head[c * 32 + j], v, z[c]);
+        for (int q = 0; q < 4; ++q) {
+          v[q] = __uint_as_float(r[4 * j4 + q]) + bb[q];
+          v[q] = p.relu ? fmaxf(v[q], 0.0f) : v[q];
+        }
+#pragma unroll
+        for (int c = 0; c < kMaxClasses; ++c) {
+          if (c < C) {
+            const float4 hw = reinterpret_cast<const float4*>(s_head + c * 32)[j4];
+            // same accumulation order as before: channel by channel
+            z[c] = fmaf(hw.x, v[0], z[c]);
+            z[c] = fmaf(hw.y, v[1], z[c]);
+            z[c] = fmaf(hw.z, v[2], z[c]);
+            z[c] = fmaf(hw.w, v[3], z[c]);
+          }
+        }
       }
       // softmax (models/losses.py:48), then first-index argmax (:50)
       float zmax = z[0];
@@ -157,52 +176,50 @@
         }
       }
     } else {
-      // ---- STORE / POOL / CONVT: bias (+ReLU) -> bf16 -> NHWC global store, 32 channels at a time
-#pragma unroll 1
-      for (int cb = 0; cb < BLOCK_N; cb += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(t_addr + static_cast<uint32_t>(cb), r);
-        tmem_ld_wait();
-        if (cb + 32 >= BLOCK_N) {  // last read of this accumulator: hand it back to the MMA warp
-          tc_fence_before();
-          mbar_arrive(&t_empty[acc]);
-        }
+      // ---- STORE / POOL / CONVT: bias (+ReLU) -> bf16 -> channel-blocked global store, 32 channels at a time
+      // geometry of this thread's output pixel (fixed per tile)
+      int oy = y, ox = x, oh = p.H, ow = p.W;
+      bool writer = inb;
+      if (p.mode == EPI_POOL) {
+        writer = inb && ((lane & 9) == 0);  // MaxPool2d(2,2): partners are lane^1 (x) and lane^8 (y)
+        oy = y >> 1; ox = x >> 1; oh = p.H >> 1; ow = p.W >> 1;
+      } else if (p.mode == EPI_CONVT) {
+        oh = 2 * p.H; ow = 2 * p.W;
+      }
+      const size_t plane = static_cast<size_t>(oh) * ow;  // pixels per channel-group plane
+      auto store_chunk = [&](const uint32_t (&r)[32], int cb) {
         const int n = n0 + cb;
-        int bias_off = n;
-        int oy = y, ox = x, oh = p.H, ow = p.W, och = p.out_choff + n;
+        int bias_off = n, cg = p.out_cg0 + (n >> 3), py = oy, px = ox;
         if (p.mode == EPI_CONVT) {
           const int q = n / p.cout;
           bias_off = n - q * p.cout;
-          oy = 2 * y + (q >> 1);
-          ox = 2 * x + (q & 1);
-          oh = 2 * p.H;
-          ow = 2 * p.W;
-          och = p.out_choff + bias_off;
+          py = 2 * y + (q >> 1);
+          px = 2 * x + (q & 1);
+          cg = p.out_cg0 + (bias_off >> 3);
         }
         float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          v[j] = __uint_as_float(r[j]) + s_bias[bias_off + j];
-          if (p.relu) v[j] = fmaxf(v[j], 0.0f);
+        for (int j4 = 0; j4 < 8; ++j4) {
+          const float4 bz = *reinterpret_cast<const float4*>(s_bias + bias_off + 4 * j4);
+          v[4 * j4 + 0] = __uint_as_float(r[4 * j4 + 0]) + bz.x;
+          v[4 * j4 + 1] = __uint_as_float(r[4 * j4 + 1]) + bz.y;
+          v[4 * j4 + 2] = __uint_as_float(r[4 * j4 + 2]) + bz.z;
+          v[4 * j4 + 3] = __uint_as_float(r[4 * j4 + 3]) + bz.w;
         }
-        bool writer = inb;
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+        }
         if (p.mode == EPI_POOL) {
-          // MaxPool2d(2,2): partners are lane^1 (x) and lane^16 (y) of the same warp
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             v[j] = fmaxf(v[j], __shfl_xor_sync(0xffffffffu, v[j], 1));
-            v[j] = fmaxf(v[j], __shfl_xor_sync(0xffffffffu, v[j], 16));
+            v[j] = fmaxf(v[j], __shfl_xor_sync(0xffffffffu, v[j], 8));
           }
-          writer = inb && ((lane & 17) == 0);
-          oy = y >> 1;
-          ox = x >> 1;
-          oh = p.H >> 1;
-          ow = p.W >> 1;
         }
         if (writer) {
-          __nv_bfloat16* dst =
-              p.out + ((static_cast<size_t>(b) * oh + oy) * ow + ox) * p.out_cstride + och;
-          uint4* d4 = reinterpret_cast<uint4*>(dst);
+          uint4* dst = reinterpret_cast<uint4*>(p.out) +
+                       ((static_cast<size_t>(b) * p.out_cgs + cg) * plane + static_cast<size_t>(py) * ow + px);
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             uint4 o;
@@ -210,8 +227,23 @@
             o.y = pack_bf16(v[8 * g + 2], v[8 * g + 3]);
             o.z = pack_bf16(v[8 * g + 4], v[8 * g + 5]);
             o.w = pack_bf16(v[8 * g + 6], v[8 * g + 7]);
-            d4[g] = o;
+            dst[static_cast<size_t>(g) * plane] = o;
           }
+        }
+      };
+      uint32_t ra[32], rb[32];
+      tmem_ld_32x32(t_addr, ra);
+#pragma unroll 1
+      for (int cb = 0; cb < BLOCK_N; cb += 64) {
+        tmem_ld_wait();
+        if (cb + 32 < BLOCK_N) tmem_ld_32x32(t_addr + static_cast<uint32_t>(cb + 32), rb);
+        else release_acc();
+        store_chunk(ra, cb);
+        if (cb + 32 < BLOCK_N) {
+          tmem_ld_wait();
+          if (cb + 64 < BLOCK_N) tmem_ld_32x32(t_addr + static_cast<uint32_t>(cb + 64), ra);
+          else release_acc();
+          store_chunk(rb, cb + 32);
         }
       }
     }

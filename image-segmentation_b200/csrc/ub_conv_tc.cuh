@@ -1,24 +1,33 @@
 // ub_conv_tc.cuh — the tensor-core kernel of the path: conv3x3(pad 1)+foldedBN+ReLU as an implicit
-// GEMM on tcgen05 with TMEM accumulators, fed by TMA from NHWC bf16 activations.  The same kernel
-// (taps = 1) is the ConvTranspose2d(k2,s2) GEMM with a pixel-shuffle scatter epilogue, and with
+// GEMM on tcgen05 with TMEM accumulators, fed by TMA from channel-blocked bf16 activations.  The same
+// kernel (taps = 1) is the ConvTranspose2d(k2,s2) GEMM with a pixel-shuffle scatter epilogue, and with
 // the HEAD epilogue it fuses the final 1x1 conv, softmax/argmax and the confusion-matrix histogram.
 //
 // Replaces: models/processing_blocks.py:43-48 (Conv2d+BatchNorm2d+ReLU), :73 (MaxPool2d, POOL
 // epilogue), :102 (ConvTranspose2d), :108 (cat: operands live in one concat buffer), models/UNet.py:73
 // (out 1x1) and models/losses.py:48-58 (softmax/argmax/counts).
 //
-// GEMM view:  D[M = 128 pixels (8 rows x 16 cols of one image)][N = BLOCK_N output channels]
-//             K = taps * Cin, walked as (channel chunk c) x (kx) x (ky) x (BK/16 MMAs).
-// A operand:  one TMA box {BK ch, 16 px, 8+2 rows} per (c, kx) — the three ky taps reuse it by
-//             moving the UMMA descriptor start address down one tile row (16 px * BK * 2 bytes, a
-//             multiple of the swizzle atom), so activations are fetched 3.75x instead of 9x.
-//             Out-of-image halo pixels are zero-filled by TMA = the conv's zero padding.
-// B operand:  weights W2[N][K] (K contiguous), one TMA box {BK, BLOCK_N} per (c, kx, ky): either streamed
-//             through a ring, or — when all taps of an n-tile fit beside the A ring (the thin, high-
-//             resolution layers) — loaded ONCE per persistent CTA and kept resident (ws mode).
-// Warp roles (384 threads): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-7 / w8-11 two epilogue
-// groups.  Two TMEM accumulators: group g drains accumulator g (even / odd tiles of this CTA) while the
-// MMA warp fills the other one, so two epilogues and one main loop are in flight per SM.
+// Activation layout in HBM: [B][C/8][H][W][8] bf16 ("channel groups" cg of 8 channels = 16 bytes).
+//   * a concat along channels is a concat of cg planes: a consumer reads any contiguous cg range of a
+//     buffer through one tensor map, two producers fill disjoint plane ranges of the same buffer;
+//   * a warp of the epilogue (32 pixels = 4 tile rows x 8 columns) stores 4 x 128 contiguous bytes per
+//     16-byte store instruction instead of 32 separate lines (NHWC): the store path stays off the
+//     critical path.
+//
+// GEMM view:  D[M = 128 pixels (16 rows x 8 cols of one image)][N = BLOCK_N output channels]
+//             K = taps * Cin, walked as (channel chunk c of BK) x (tap ky,kx) x (BK/16 MMAs).
+// A operand:  ONE TMA box per channel chunk: {8*(8+2) elements, 16+2 rows, BK/8 cg} (halo included, image
+//             border = TMA out-of-bounds zero fill = the conv's zero padding).  In shared memory it is the
+//             no-swizzle K-major "interleaved" UMMA layout: pixel rows 16 bytes apart, 8-pixel groups
+//             (one tile row) SBO = 10*16 bytes apart, the two K halves of an MMA LBO = one cg plane apart.
+//             Because pixels are linear in memory, tap (ky,kx) is just the descriptor start address moved
+//             by (ky*10 + kx) * 16 bytes: all nine taps read the same box — activations are fetched
+//             1.4x (halo) instead of 9x, and written to shared memory once.
+// B operand:  weights W2[N][K] (K contiguous, 128B/64B swizzle), one TMA box {BK, BLOCK_N} per (c, tap):
+//             either streamed through a ring, or — when all taps of an n-tile fit beside the A ring (the
+//             thin, high-resolution layers) — loaded ONCE per persistent CTA and kept resident (WS).
+// Warp roles: w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, then kEpiGroups groups of 4 epilogue
+// warps.  kAcc TMEM accumulators (up to 4): the MMA warp runs ahead of the epilogues by kAcc tiles.
 #pragma once
 #include "ub_ptx.cuh"
 
@@ -26,14 +35,15 @@ namespace ub {
 
 enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_CONVT = 2, EPI_HEAD = 3 };
 
-constexpr int kTileRows = 8;
-constexpr int kTileCols = 16;
+constexpr int kTileRows = 16;
+constexpr int kTileCols = 8;
 constexpr int kTileM = 128;
-constexpr int kConvThreads = 384;  // 4 control warps + 2 epilogue groups of 4 warps
+constexpr int kEpiGroups = 2;
+constexpr int kConvThreads = 128 + 128 * kEpiGroups;  // 4 control warps + epilogue groups of 4 warps
 constexpr int kMaxClasses = 4;
 
 struct ConvParams {
-  CUtensorMap tmA;  // activations: dims {C, W, H, B}, box {BK, 16, 8 + 2*pad, 1}
+  CUtensorMap tmA;  // activations: dims {8*W, H, Cin/8, B}, box {8*(8+2*pad), 16+2*pad, BK/8, 1}
   CUtensorMap tmB;  // weights:     dims {Ktot, Ntot}, box {BK, BLOCK_N}
   int B, H, W;      // input extent (= output extent for conv; output is 2H x 2W for ConvT)
   int cin;          // channels of the A source = K per tap
@@ -43,9 +53,9 @@ struct ConvParams {
   int relu;
   const float* bias;  // [n_total] (conv) / [cout] (ConvT)
   int n_bias;
-  __nv_bfloat16* out;  // NHWC bf16
-  int out_cstride;     // channels per pixel of the output buffer (concat buffers are wider)
-  int out_choff;       // first channel written
+  __nv_bfloat16* out;  // [B][out_cgs][Ho][Wo][8] bf16
+  int out_cgs;         // channel groups per image of the output buffer (concat buffers are wider)
+  int out_cg0;         // first channel group written
   int cout;            // ConvT: channels per 2x2 quadrant
   // HEAD epilogue
   const float* head_w;  // [n_classes][32]
@@ -61,36 +71,42 @@ struct ConvParams {
   float* logits_out;       // [B,C,H,W] or null
   // pipeline shape chosen by the host (ub_api.cu: choose_pipeline)
   int sa;  // A stages (activation boxes)
-  int sb;  // B stages when streaming weights; unused when ws != 0
-  int ws;  // 1 = weight-stationary: all taps of this CTA's n-tile stay resident in shared memory
+  int sb;  // B stages when streaming weights; unused when the kernel is the WS instantiation
 };
 
-constexpr int kMaxSA = 12;
+constexpr int kMaxSA = 8;
 constexpr int kMaxSB = 8;
+constexpr int kMaxAcc = 4;
 constexpr int kSmemLimit = 232448;  // 227 KB, the sm_100 per-block maximum
 
-template <int BLOCK_N, int SWZ>
+template <int BLOCK_N, int BK, int KSIZE>
 struct ConvCfg {
-  static constexpr int BK = SWZ / 2;  // bf16 channels per K chunk
-  static constexpr int A_ROW_BYTES = kTileCols * SWZ;                 // one tile row of pixels
-  static constexpr int A_STAGE_BYTES = (kTileRows + 2) * A_ROW_BYTES; // 10 rows
-  static constexpr int B_STAGE_BYTES = BLOCK_N * SWZ;
-  static constexpr int TMEM_COLS = (2 * BLOCK_N) < 32 ? 32 : (2 * BLOCK_N);
-  // fixed-size tail after the two operand regions
+  static constexpr int PAD = KSIZE / 2;
+  static constexpr int PXW = kTileCols + 2 * PAD;        // pixels per box row
+  static constexpr int ROWS_IN = kTileRows + 2 * PAD;    // box rows
+  static constexpr int A_PLANE_BYTES = ROWS_IN * PXW * 16;            // one channel group of the box = LBO
+  static constexpr int A_BOX_BYTES = (BK / 8) * A_PLANE_BYTES;        // what one TMA load delivers
+  static constexpr int A_STAGE_BYTES = ((A_BOX_BYTES + 1023) / 1024) * 1024;
+  static constexpr int SWZ_B = 2 * BK;                                // weight rows: 128 B or 64 B swizzle
+  static constexpr int B_STAGE_BYTES = BLOCK_N * SWZ_B;
+  static constexpr int ACC = (512 / BLOCK_N) < kMaxAcc ? (512 / BLOCK_N) : kMaxAcc;
+  static constexpr int TMEM_COLS = ACC * BLOCK_N;
+  // fixed-size tail in front of the two operand regions
   static constexpr int TAIL_BIAS = 0;
   static constexpr int TAIL_HEAD = TAIL_BIAS + 1024 * 4;
   static constexpr int TAIL_BAR = TAIL_HEAD + (kMaxClasses * 32 + kMaxClasses) * 4;
-  static constexpr int N_BARS = 2 * kMaxSA + 2 * kMaxSB + 4 + 1;
-  static constexpr int TAIL_CM = TAIL_BAR + N_BARS * 8;                          // 2 groups x C*C counters
-  static constexpr int TAIL_DICE = TAIL_CM + 2 * kMaxClasses * kMaxClasses * 8;  // 2 groups x 2C sums
-  static constexpr int TAIL_TMEM = TAIL_DICE + 2 * kMaxClasses * 2 * 8;
-  static constexpr int TAIL_BYTES = ((TAIL_TMEM + 16 + 1023) / 1024) * 1024;     // keeps the rings 1024B aligned
-  static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;  // 1024 = alignment slack
-  static_assert((TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns");
-  static_assert(A_STAGE_BYTES % 1024 == 0 && B_STAGE_BYTES % 1024 == 0, "swizzle atom alignment");
+  static constexpr int N_BARS = 2 * kMaxSA + 2 * kMaxSB + 2 * kMaxAcc + 1;
+  static constexpr int TAIL_CM = TAIL_BAR + N_BARS * 8;
+  static constexpr int TAIL_DICE = TAIL_CM + kEpiGroups * kMaxClasses * kMaxClasses * 8;
+  static constexpr int TAIL_TMEM = TAIL_DICE + kEpiGroups * kMaxClasses * 2 * 8;
+  static constexpr int TAIL_BYTES = ((TAIL_TMEM + 16 + 1023) / 1024) * 1024;  // keeps the rings 1024B aligned
+  static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;       // 1024 = alignment slack
+  static_assert(BK == 64 || BK == 32, "channel chunk");
+  static_assert(TMEM_COLS >= 32 && (TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns");
+  static_assert(B_STAGE_BYTES % 1024 == 0, "swizzle atom alignment");
 };
 
-__device__ __forceinline__ void epi_bar_sync(int grp) {  // named barrier 1 or 2: the 128 threads of one epilogue group
+__device__ __forceinline__ void epi_bar_sync(int grp) {  // named barrier 1..: the 128 threads of one epilogue group
   asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
 }
 
@@ -99,19 +115,19 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <int BLOCK_N, int SWZ, int KSIZE, bool WS>
+template <int BLOCK_N, int BK, int KSIZE, bool WS>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_tc_kernel(const __grid_constant__ ConvParams p) {
-  using Cfg = ConvCfg<BLOCK_N, SWZ>;
-  constexpr int BK = Cfg::BK;
-  constexpr int PAD = KSIZE / 2;
-  constexpr uint32_t A_BYTES = static_cast<uint32_t>((kTileRows + 2 * PAD) * Cfg::A_ROW_BYTES);
+  using Cfg = ConvCfg<BLOCK_N, BK, KSIZE>;
+  constexpr int PAD = Cfg::PAD;
+  constexpr int TAPS = KSIZE * KSIZE;
+  constexpr int ACC = Cfg::ACC;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // pad to 1024 B with pointer arithmetic on the __shared__ array (keeps the address space known to
   // the compiler: LDS/STS/ATOMS instead of generic accesses)
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int k_chunks = p.cin / BK;
-  const int n_taps = k_chunks * KSIZE * KSIZE;       // B tiles per output tile
+  const int n_taps = k_chunks * TAPS;  // B tiles per output tile
   // [fixed-size tail: bias, head weights, barriers, counters][A ring][B ring or resident weights]
   float* s_bias = reinterpret_cast<float*>(smem + Cfg::TAIL_BIAS);
   float* s_head = reinterpret_cast<float*>(smem + Cfg::TAIL_HEAD);
@@ -121,8 +137,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   uint64_t* b_full = bars + 2 * kMaxSA;
   uint64_t* b_empty = b_full + kMaxSB;
   uint64_t* t_full = b_empty + kMaxSB;
-  uint64_t* t_empty = t_full + 2;
-  uint64_t* w_full = t_empty + 2;  // ws mode: all resident weights have landed
+  uint64_t* t_empty = t_full + kMaxAcc;
+  uint64_t* w_full = t_empty + kMaxAcc;  // WS: all resident weights have landed
   unsigned long long* s_cm_all = reinterpret_cast<unsigned long long*>(smem + Cfg::TAIL_CM);
   double* s_dice_all = reinterpret_cast<double*>(smem + Cfg::TAIL_DICE);
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + Cfg::TAIL_TMEM);
@@ -138,13 +154,13 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   const int n_tiles = p.n_total / BLOCK_N;
   const int total_tiles = p.B * tiles_x * tiles_y * n_tiles;
 
-  // ---------------- one-time setup
+  // ---------------- one-time setup (nothing here depends on the previous kernel's output)
   for (int i = threadIdx.x; i < p.n_bias; i += kConvThreads) s_bias[i] = p.bias[i];
   if (p.mode == EPI_HEAD) {
     for (int i = threadIdx.x; i < p.n_classes * 32; i += kConvThreads) s_head[i] = p.head_w[i];
     if (threadIdx.x < p.n_classes) s_head[kMaxClasses * 32 + threadIdx.x] = p.head_b[threadIdx.x];
-    if (threadIdx.x < 2 * kMaxClasses * kMaxClasses) s_cm_all[threadIdx.x] = 0ull;
-    if (threadIdx.x < 2 * kMaxClasses * 2) s_dice_all[threadIdx.x] = 0.0;
+    if (threadIdx.x < kEpiGroups * kMaxClasses * kMaxClasses) s_cm_all[threadIdx.x] = 0ull;
+    if (threadIdx.x < kEpiGroups * kMaxClasses * 2) s_dice_all[threadIdx.x] = 0.0;
   }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
@@ -153,7 +169,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kMaxSA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < kMaxSB; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 128); }
+    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 128); }
     mbar_init(w_full, 1);
     fence_barrier_init();
   }
@@ -170,20 +186,20 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     // ================= TMA producer (whole warp runs the loop; one elected lane issues) =================
     const bool leader = elect_one();
     if constexpr (WS) {
-      // weight-stationary: with gridDim a multiple of n_tiles every tile of this CTA has the same n-tile
+      // weight-stationary: with gridDim a multiple of n_tiles every tile of this CTA has the same n-tile.
+      // Weights are constants of the layer: their loads may precede the wait on the previous kernel.
       const int nt = blockIdx.x % n_tiles;
       if (leader) {
         mbar_arrive_expect_tx(w_full, static_cast<uint32_t>(n_taps * Cfg::B_STAGE_BYTES));
 #pragma unroll 1
-        for (int j = 0; j < n_taps; ++j) {  // consumption order: c outer, kx, ky inner
-          const int c = j / (KSIZE * KSIZE), r = j % (KSIZE * KSIZE);
-          const int kx = r / KSIZE, ky = r % KSIZE;
-          tma_load_2d(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, (ky * KSIZE + kx) * p.cin + c * BK,
-                      nt * BLOCK_N);
+        for (int j = 0; j < n_taps; ++j) {  // consumption order: c outer, tap inner
+          const int c = j / TAPS, tap = j % TAPS;
+          tma_load_2d(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, tap * p.cin + c * BK, nt * BLOCK_N);
         }
       }
       __syncwarp();
     }
+    pdl_wait_prior_grid();  // activations of the previous layer are complete and visible from here on
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
 #pragma unroll 1
@@ -196,27 +212,23 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
       const int b = m / tiles_y;
 #pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
+        mbar_wait(&a_empty[sa], pa ^ 1u);
+        if (leader) {
+          mbar_arrive_expect_tx(&a_full[sa], static_cast<uint32_t>(Cfg::A_BOX_BYTES));
+          tma_load_4d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], (x0 - PAD) * 8, y0 - PAD, c * (BK / 8), b);
+        }
+        __syncwarp();
+        if (++sa == p.sa) { sa = 0; pa ^= 1u; }
+        if constexpr (!WS) {
 #pragma unroll
-        for (int kx = 0; kx < KSIZE; ++kx) {
-          mbar_wait(&a_empty[sa], pa ^ 1u);
-          if (leader) {
-            mbar_arrive_expect_tx(&a_full[sa], A_BYTES);
-            tma_load_4d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], c * BK, x0 + kx - PAD, y0 - PAD, b);
-          }
-          __syncwarp();
-          if (++sa == p.sa) { sa = 0; pa ^= 1u; }
-          if constexpr (!WS) {
-#pragma unroll
-            for (int ky = 0; ky < KSIZE; ++ky) {
-              mbar_wait(&b_empty[sb], pb ^ 1u);
-              if (leader) {
-                mbar_arrive_expect_tx(&b_full[sb], Cfg::B_STAGE_BYTES);
-                tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb],
-                            (ky * KSIZE + kx) * p.cin + c * BK, nt * BLOCK_N);
-              }
-              __syncwarp();
-              if (++sb == p.sb) { sb = 0; pb ^= 1u; }
+          for (int tap = 0; tap < TAPS; ++tap) {
+            mbar_wait(&b_empty[sb], pb ^ 1u);
+            if (leader) {
+              mbar_arrive_expect_tx(&b_full[sb], Cfg::B_STAGE_BYTES);
+              tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb], tap * p.cin + c * BK, nt * BLOCK_N);
             }
+            __syncwarp();
+            if (++sb == p.sb) { sb = 0; pb ^= 1u; }
           }
         }
       }
@@ -226,12 +238,13 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     const bool leader = elect_one();
     constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    // descriptors advance by plain 32-bit adds on the low word ((address >> 4) field); high word is constant
-    const uint64_t desc_a_ring = umma_smem_desc<SWZ>(smem_u32(a_ring));
-    const uint32_t desc_hi = static_cast<uint32_t>(desc_a_ring >> 32);
-    const uint32_t a_lo_ring = static_cast<uint32_t>(desc_a_ring);
-    const uint32_t b_lo_ring = static_cast<uint32_t>(umma_smem_desc<SWZ>(smem_u32(b_ring)));
-    constexpr uint32_t A_STAGE_U = Cfg::A_STAGE_BYTES >> 4, A_ROW_U = Cfg::A_ROW_BYTES >> 4;
+    // descriptors advance by plain 32-bit adds on the low word ((address >> 4) field); high words are constant
+    const uint64_t desc_a = umma_smem_desc_interleaved(smem_u32(a_ring), Cfg::A_PLANE_BYTES, Cfg::PXW * 16);
+    const uint64_t desc_b = umma_smem_desc<Cfg::SWZ_B>(smem_u32(b_ring));
+    const uint32_t a_hi = static_cast<uint32_t>(desc_a >> 32), b_hi = static_cast<uint32_t>(desc_b >> 32);
+    const uint32_t a_lo_ring = static_cast<uint32_t>(desc_a), b_lo_ring = static_cast<uint32_t>(desc_b);
+    constexpr uint32_t A_STAGE_U = Cfg::A_STAGE_BYTES >> 4;
+    constexpr uint32_t A_KSTEP_U = (2 * Cfg::A_PLANE_BYTES) >> 4;  // one MMA = 16 channels = 2 cg planes
     constexpr uint32_t B_STAGE_U = Cfg::B_STAGE_BYTES >> 4;
     if constexpr (WS) {
       mbar_wait(w_full, 0);
@@ -242,70 +255,55 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     int it = 0;
 #pragma unroll 1
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-      const int acc = it & 1;
-      const uint32_t use = static_cast<uint32_t>(it >> 1);
+      const int acc = it % ACC;
+      const uint32_t use = static_cast<uint32_t>(it / ACC);
       mbar_wait(&t_empty[acc], (use & 1u) ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_u + static_cast<uint32_t>(acc * BLOCK_N);
 #pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
+        mbar_wait(&a_full[sa], pa);
+        tc_fence_after();
+        const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(sa) * A_STAGE_U;
 #pragma unroll
-        for (int kx = 0; kx < KSIZE; ++kx) {
-          mbar_wait(&a_full[sa], pa);
-          tc_fence_after();
-          const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(sa) * A_STAGE_U;
+        for (int tap = 0; tap < TAPS; ++tap) {
+          constexpr int dummy = 0;
+          (void)dummy;
+          const uint32_t a_tap = a_lo + static_cast<uint32_t>((tap / KSIZE) * Cfg::PXW + (tap % KSIZE));
+          uint32_t b_lo;
           if constexpr (WS) {
-            // resident weights: tap j = (c*KSIZE + kx)*KSIZE + ky sits at a fixed offset -> one issue region per box
-            const uint32_t b_lo = b_lo_ring + static_cast<uint32_t>((c * KSIZE + kx) * KSIZE) * B_STAGE_U;
-            if (leader) {
-#pragma unroll
-              for (int ky = 0; ky < KSIZE; ++ky) {
-#pragma unroll
-                for (int k = 0; k < BK / 16; ++k) {
-                  const uint32_t al = a_lo + ky * A_ROW_U + 2 * k, bl = b_lo + ky * B_STAGE_U + 2 * k;
-                  if (kx == 0 && ky == 0 && k == 0) {
-                    if (c == 0) umma_bf16_lo<false>(d_tmem, al, bl, desc_hi, idesc);
-                    else umma_bf16_lo<true>(d_tmem, al, bl, desc_hi, idesc);
-                  } else {
-                    umma_bf16_lo<true>(d_tmem, al, bl, desc_hi, idesc);
-                  }
-                }
-              }
-              umma_commit(&a_empty[sa]);
-            }
-            __syncwarp();
+            b_lo = b_lo_ring + static_cast<uint32_t>(c * TAPS + tap) * B_STAGE_U;
           } else {
-#pragma unroll
-            for (int ky = 0; ky < KSIZE; ++ky) {
-              mbar_wait(&b_full[sb], pb);
-              tc_fence_after();
-              const uint32_t b_lo = b_lo_ring + static_cast<uint32_t>(sb) * B_STAGE_U;
-              if (leader) {
-#pragma unroll
-                for (int k = 0; k < BK / 16; ++k) {
-                  const uint32_t al = a_lo + ky * A_ROW_U + 2 * k, bl = b_lo + 2 * k;
-                  if (kx == 0 && ky == 0 && k == 0) {
-                    if (c == 0) umma_bf16_lo<false>(d_tmem, al, bl, desc_hi, idesc);
-                    else umma_bf16_lo<true>(d_tmem, al, bl, desc_hi, idesc);
-                  } else {
-                    umma_bf16_lo<true>(d_tmem, al, bl, desc_hi, idesc);
-                  }
-                }
-                umma_commit(&b_empty[sb]);
-                if (ky == KSIZE - 1) umma_commit(&a_empty[sa]);
-              }
-              __syncwarp();
-              if (++sb == p.sb) { sb = 0; pb ^= 1u; }
-            }
+            mbar_wait(&b_full[sb], pb);
+            tc_fence_after();
+            b_lo = b_lo_ring + static_cast<uint32_t>(sb) * B_STAGE_U;
           }
-          if (++sa == p.sa) { sa = 0; pa ^= 1u; }
+          if (leader) {
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint32_t al = a_tap + k * A_KSTEP_U, bl = b_lo + 2 * k;
+              if (tap == 0 && k == 0) {
+                if (c == 0) umma_bf16_lo<false>(d_tmem, al, a_hi, bl, b_hi, idesc);
+                else umma_bf16_lo<true>(d_tmem, al, a_hi, bl, b_hi, idesc);
+              } else {
+                umma_bf16_lo<true>(d_tmem, al, a_hi, bl, b_hi, idesc);
+              }
+            }
+            if constexpr (!WS) umma_commit(&b_empty[sb]);
+            if (tap == TAPS - 1) umma_commit(&a_empty[sa]);
+          }
+          __syncwarp();
+          if constexpr (!WS) {
+            if (++sb == p.sb) { sb = 0; pb ^= 1u; }
+          }
         }
+        if (++sa == p.sa) { sa = 0; pa ^= 1u; }
       }
       if (leader) umma_commit(&t_full[acc]);
       __syncwarp();
     }
   } else if (warp >= 4) {
-    // ================= epilogue (2 groups x 128 threads; warp w owns TMEM lanes 32*(w%4)..) =================
+    // ================= epilogue (kEpiGroups x 128 threads; warp w owns TMEM lanes 32*(w%4)..) =================
 #include "ub_conv_epilogue.inl"
   }
 

@@ -230,15 +230,16 @@ __global__ void blur_f_pass_kernel(const float* in, float* out, int planes, int 
   out[i] = acc;
 }
 
-// ---- stem: perturbed pixel -> Conv2d(3,32,1) -> bf16, written into channels [choff, choff+32) of the
-// level-0 concat buffer (NHWC, cstride channels per pixel).  One thread per pixel, 4 x 16-byte stores.
+// ---- stem: perturbed pixel -> Conv2d(3,32,1) -> bf16, written into channel groups [cg0, cg0+4) of the
+// level-0 concat buffer (channel-blocked [n][cgs][H][W][8]).  One thread per pixel, 4 x 16-byte stores; a warp
+// stores 512 contiguous bytes per instruction.
 struct StemWeights {
   float w[32 * 3];
   float b[32];
 };
 __global__ void __launch_bounds__(256)
 stem_kernel(PerturbDev P, StemWeights sw, const void* img, int fmt, int n, int H, int W,
-            __nv_bfloat16* out, int cstride, int choff, float* perturbed_out) {
+            __nv_bfloat16* out, int cgs, int cg0, float* perturbed_out) {
   __shared__ float s_w[32 * 3 + 32];
   for (int i = threadIdx.x; i < 32 * 3; i += blockDim.x) s_w[i] = sw.w[i];
   if (threadIdx.x < 32) s_w[96 + threadIdx.x] = sw.b[threadIdx.x];
@@ -266,9 +267,9 @@ stem_kernel(PerturbDev P, StemWeights sw, const void* img, int fmt, int n, int H
     __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
     packed[o >> 1] = *reinterpret_cast<uint32_t*>(&h);
   }
-  uint4* dst = reinterpret_cast<uint4*>(out + i * cstride + choff);
+  uint4* dst = reinterpret_cast<uint4*>(out) + (static_cast<size_t>(b) * cgs + cg0) * hw + (i - static_cast<size_t>(b) * hw);
 #pragma unroll
-  for (int g = 0; g < 4; ++g) dst[g] = make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+  for (int g = 0; g < 4; ++g) dst[g * hw] = make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
 }
 
 }  // namespace ub

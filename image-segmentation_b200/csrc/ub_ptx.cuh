@@ -55,6 +55,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// ------------------------------------------------------------------ programmatic dependent launch
+__device__ __forceinline__ void pdl_wait_prior_grid() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ------------------------------------------------------------------ TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
@@ -105,24 +109,25 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-// Same, with the descriptors given as (low word, constant high word) and a compile-time accumulate flag:
-// the issue loop then needs one 32-bit uniform add per operand per MMA.
+// Same, with each descriptor given as (low word, constant high word) and a compile-time accumulate flag:
+// the issue loop then needs one 32-bit uniform add per operand per MMA.  A and B have different high
+// words (A: no-swizzle interleaved activations, B: swizzled weights).
 template <bool kAccumulate>
-__device__ __forceinline__ void umma_bf16_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi,
-                                             uint32_t idesc) {
+__device__ __forceinline__ void umma_bf16_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                             uint32_t b_hi, uint32_t idesc) {
   if constexpr (kAccumulate) {
     asm volatile(
         "{\n\t.reg .b64 da, db;\n\t.reg .pred p;\n\tsetp.eq.b32 p, 1, 1;\n\t"
-        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}\n" ::"r"(tmem_d),
-        "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc)
+        "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}\n" ::"r"(tmem_d),
+        "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc)
         : "memory");
   } else {
     asm volatile(
         "{\n\t.reg .b64 da, db;\n\t.reg .pred p;\n\tsetp.ne.b32 p, 1, 1;\n\t"
-        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}\n" ::"r"(tmem_d),
-        "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc)
+        "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}\n" ::"r"(tmem_d),
+        "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc)
         : "memory");
   }
 }
@@ -163,6 +168,15 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr) {
   constexpr uint64_t sbo = (8u * kSwizzleBytes) >> 4;
   return static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (sbo << 32) |
          (1ull << 46) | (layout << 61);
+}
+// K-major operand WITHOUT swizzle ("interleaved": core matrices of 8 rows x 16 bytes, rows 16 bytes apart).
+// In 16-byte units the canonical layout is ((8,m),2):((1,SBO),LBO) (cute/atom/mma_traits_sm100.hpp,
+// make_umma_desc<Major::K>): SBO = distance between 8-row groups, LBO = distance between the two 8-element
+// K halves of one MMA.  Rows are linear in memory, so the start address may sit on any 16-byte boundary.
+__device__ __forceinline__ uint64_t umma_smem_desc_interleaved(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                               uint32_t sbo_bytes) {
+  return static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4) | (static_cast<uint64_t>(lbo_bytes >> 4) << 16) |
+         (static_cast<uint64_t>(sbo_bytes >> 4) << 32) | (1ull << 46);
 }
 // Instruction descriptor, kind::f16: D=F32, A=B=BF16, both K-major, M x N.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t m, uint32_t n) {

@@ -222,22 +222,36 @@ class Engine:
                                         _ptr(dice), _stream(self.device)), "ub_metrics")
         return cm, dice
 
+    @staticmethod
+    def _to_blocked(x_nhwc: torch.Tensor) -> torch.Tensor:
+        """NHWC -> the library's activation layout [n][C/8][h][w][8] (channel groups of 8 = 16 bytes)."""
+        n, h, w, c = x_nhwc.shape
+        return x_nhwc.view(n, h, w, c // 8, 8).permute(0, 3, 1, 2, 4).contiguous()
+
+    @staticmethod
+    def _from_blocked(x: torch.Tensor) -> torch.Tensor:
+        n, g, h, w, _ = x.shape
+        return x.permute(0, 2, 3, 1, 4).reshape(n, h, w, g * 8).contiguous()
+
     def debug_conv3x3(self, key: str, x_nhwc_bf16: torch.Tensor, pool: bool = False) -> torch.Tensor:
+        """One conv3x3+BN+ReLU layer on NHWC bf16 data (converted to / from the blocked layout here)."""
         n, h, w, _ = x_nhwc_bf16.shape
         cout = self._layer_cout(key)
         oh, ow = (h // 2, w // 2) if pool else (h, w)
-        out = torch.zeros((n, oh, ow, cout), device=self.device, dtype=torch.bfloat16)
-        self._check(self.lib.ub_debug_conv3x3(self.h, key.encode(), _ptr(x_nhwc_bf16.contiguous()), _ptr(out), n, h, w,
+        out = torch.zeros((n, cout // 8, oh, ow, 8), device=self.device, dtype=torch.bfloat16)
+        xb = self._to_blocked(x_nhwc_bf16)
+        self._check(self.lib.ub_debug_conv3x3(self.h, key.encode(), _ptr(xb), _ptr(out), n, h, w,
                                               int(pool), _stream(self.device)), "ub_debug_conv3x3")
-        return out
+        return self._from_blocked(out)
 
     def debug_convt2x2(self, key: str, x_nhwc_bf16: torch.Tensor) -> torch.Tensor:
         n, h, w, _ = x_nhwc_bf16.shape
         cout = self._layer_cout(key)
-        out = torch.zeros((n, 2 * h, 2 * w, cout), device=self.device, dtype=torch.bfloat16)
-        self._check(self.lib.ub_debug_convt2x2(self.h, key.encode(), _ptr(x_nhwc_bf16.contiguous()), _ptr(out), n, h, w,
+        out = torch.zeros((n, cout // 8, 2 * h, 2 * w, 8), device=self.device, dtype=torch.bfloat16)
+        xb = self._to_blocked(x_nhwc_bf16)
+        self._check(self.lib.ub_debug_convt2x2(self.h, key.encode(), _ptr(xb), _ptr(out), n, h, w,
                                                _stream(self.device)), "ub_debug_convt2x2")
-        return out
+        return self._from_blocked(out)
 
     def _layer_cout(self, key):
         return self._couts[key]

@@ -120,11 +120,11 @@ int ub_metrics(ub_ctx* ctx, const float* logits_nchw, const void* targets, int t
                int n_classes, int h, int w, int ref_batch, int64_t* cm, double* dice_sums, void* stream);
 
 /* Test / profiling hook: one conv3x3+BN(folded)+ReLU layer (processing_blocks.py:43-45) by its
- * state_dict prefix, e.g. "enc2.block.0.conv.conv.3"; bf16 NHWC in and out; pool = fuse MaxPool2d(2,2). */
-int ub_debug_conv3x3(ub_ctx* ctx, const char* conv_key, const void* in_bf16_nhwc, void* out_bf16_nhwc,
+ * state_dict prefix, e.g. "enc2.block.0.conv.conv.3"; bf16 channel-blocked [n][C/8][h][w][8] in and out (the library's activation layout); pool = fuse MaxPool2d(2,2). */
+int ub_debug_conv3x3(ub_ctx* ctx, const char* conv_key, const void* in_bf16_cg8, void* out_bf16_cg8,
                      int n, int h, int w, int pool, void* stream);
 /* Test hook: ConvTranspose2d(k2,s2) (processing_blocks.py:102,106) by prefix, e.g. "dec2.up". */
-int ub_debug_convt2x2(ub_ctx* ctx, const char* up_key, const void* in_bf16_nhwc, void* out_bf16_nhwc,
+int ub_debug_convt2x2(ub_ctx* ctx, const char* up_key, const void* in_bf16_cg8, void* out_bf16_cg8,
                       int n, int h, int w, void* stream);
 /* Measurement hooks (bench.py's roofline leg): between begin and end every tensor-core GEMM launch is
  * bracketed by CUDA events on its own stream.  end() synchronises the device and returns the summed
