@@ -42,6 +42,7 @@ struct GemmLayer {
   bool is_convt = false;
   __nv_bfloat16* w = nullptr;  // [n_total][ksize*ksize*cin] bf16, BN folded
   float* bias = nullptr;       // [cout]
+  std::vector<float> h_bias;   // host copy (the HEAD layer passes its 32 biases by value)
 };
 
 struct Step {
@@ -77,6 +78,7 @@ struct ub_ctx {
   ub::StemWeights stem;
   float* head_w = nullptr;  // device [C][32]
   float* head_b = nullptr;
+  std::vector<float> h_head_w, h_head_b;  // host copies, passed by value to the HEAD epilogue
   bool weights_ready = false;
   std::map<std::pair<int, int>, std::unique_ptr<Plan>> plans;
   EncodeTiledFn encode = nullptr;
@@ -163,6 +165,7 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), bias.size() * 4))) return rc;
   UB_CUDA(ctx, cudaMemcpy(L.w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
   UB_CUDA(ctx, cudaMemcpy(L.bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
+  L.h_bias = bias;
   ctx->layer_by_key[L.key] = static_cast<int>(ctx->layers.size());
   ctx->layers.push_back(L);
   return UB_OK;
@@ -221,6 +224,8 @@ int pack_all(ub_ctx* ctx) {
   if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->head_b), ob->data.size() * 4))) return rc;
   UB_CUDA(ctx, cudaMemcpy(ctx->head_w, ow->data.data(), ow->data.size() * 4, cudaMemcpyHostToDevice));
   UB_CUDA(ctx, cudaMemcpy(ctx->head_b, ob->data.data(), ob->data.size() * 4, cudaMemcpyHostToDevice));
+  ctx->h_head_w = ow->data;
+  ctx->h_head_b = ob->data;
   char k[128];
   for (int i = 1; i <= ctx->n_enc; ++i) {
     snprintf(k, sizeof(k), "enc%d.block.0.conv", i);
@@ -284,7 +289,18 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   cp->mode = mode; cp->relu = L.relu;
   cp->bias = L.bias; cp->n_bias = L.cout;
   cp->out = out; cp->out_cgs = out_cgs; cp->out_cg0 = out_cg0; cp->cout = L.cout;
-  cp->head_w = ctx->head_w; cp->head_b = ctx->head_b; cp->n_classes = ctx->n_classes;
+  cp->n_classes = ctx->n_classes;
+  cp->cout_shift = 0;
+  while ((1 << cp->cout_shift) < L.cout) cp->cout_shift++;
+  if (mode == ub::EPI_CONVT && (1 << cp->cout_shift) != L.cout)
+    return fail(ctx, UB_ERR_UNSUPPORTED, "%s: ConvTranspose output channels must be a power of two", L.key.c_str());
+  if (mode == ub::EPI_HEAD) {
+    if (L.cout != 32 || ctx->h_head_w.size() != static_cast<size_t>(ctx->n_classes) * 32)
+      return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs a 32-channel layer");
+    memcpy(cp->head_w, ctx->h_head_w.data(), ctx->h_head_w.size() * 4);
+    memcpy(cp->head_b, ctx->h_head_b.data(), ctx->h_head_b.size() * 4);
+    memcpy(cp->bias32, L.h_bias.data(), 32 * 4);
+  }
   cp->ref_batch = 1;
   return UB_OK;
 }
@@ -324,7 +340,7 @@ int launch_kernel(ub_ctx* ctx, const ConvParams& cp, int grid, int smem, cudaStr
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(ub::kConvThreads);
+  cfg.blockDim = dim3(ub::conv_threads(N));
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];

@@ -3,6 +3,7 @@
 // of the 16x8 tile and reads its BLOCK_N fp32 columns from TMEM 32 at a time (double-buffered: the
 // next tcgen05.ld is in flight while the current 32 channels are converted and stored).
 {
+  constexpr bool kHead = (BLOCK_N == 32);  // the fused head exists only in the 32-channel instantiations
   const int wq = warp & 3;
   const int grp = (warp - 4) >> 2;             // tiles it with it % kEpiGroups == grp
   const int ty = 4 * wq + (lane >> 3);
@@ -73,7 +74,7 @@
     const int n0 = nt * BLOCK_N;
     int tgt_pre = -1;
 
-    if (p.mode == EPI_HEAD && p.targets) {
+    if (kHead && p.mode == EPI_HEAD && p.targets) {
       // counts accumulate in registers across tiles and go to HBM only when the reference batch
       // changes (and once at the end): <= C*C global atomics per batch per CTA instead of per tile
       const int batch = (p.img_base + b) / p.ref_batch;
@@ -99,7 +100,7 @@
       mbar_arrive(&t_empty[acc]);
     };
 
-    if (p.mode == EPI_HEAD) {
+    if (kHead && p.mode == EPI_HEAD) {
       // ---- dec4.conv.3 epilogue: bias+ReLU (fp32) -> 1x1 head -> softmax -> argmax -> counts
       uint32_t r[32];
       tmem_ld_32x32(t_addr, r);
@@ -108,28 +109,14 @@
       const int C = p.n_classes;
       float z[kMaxClasses];
 #pragma unroll
-      for (int c = 0; c < kMaxClasses; ++c) z[c] = (c < C) ? s_head[kMaxClasses * 32 + c] : -INFINITY;
+      for (int c = 0; c < kMaxClasses; ++c) z[c] = (c < C) ? p.head_b[c] : -INFINITY;
 #pragma unroll
-      for (int j4 = 0; j4 < 8; ++j4) {
-        const float4 bz = reinterpret_cast<const float4*>(s_bias)[j4];
-        const float bb[4] = {bz.x, bz.y, bz.z, bz.w};
-        float v[4];
+      for (int j = 0; j < 32; ++j) {
+        float v = __uint_as_float(r[j]) + p.bias32[j];
+        v = p.relu ? fmaxf(v, 0.0f) : v;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          v[q] = __uint_as_float(r[4 * j4 + q]) + bb[q];
-          v[q] = p.relu ? fmaxf(v[q], 0.0f) : v[q];
-        }
-#pragma unroll
-        for (int c = 0; c < kMaxClasses; ++c) {
-          if (c < C) {
-            const float4 hw = reinterpret_cast<const float4*>(s_head + c * 32)[j4];
-            // same accumulation order as before: channel by channel
-            z[c] = fmaf(hw.x, v[0], z[c]);
-            z[c] = fmaf(hw.y, v[1], z[c]);
-            z[c] = fmaf(hw.z, v[2], z[c]);
-            z[c] = fmaf(hw.w, v[3], z[c]);
-          }
-        }
+        for (int c = 0; c < kMaxClasses; ++c)
+          if (c < C) z[c] = fmaf(p.head_w[c * 32 + j], v, z[c]);
       }
       // softmax (models/losses.py:48), then first-index argmax (:50)
       float zmax = z[0];
@@ -191,8 +178,8 @@
         const int n = n0 + cb;
         int bias_off = n, cg = p.out_cg0 + (n >> 3), py = oy, px = ox;
         if (p.mode == EPI_CONVT) {
-          const int q = n / p.cout;
-          bias_off = n - q * p.cout;
+          const int q = n >> p.cout_shift;
+          bias_off = n - (q << p.cout_shift);
           py = 2 * y + (q >> 1);
           px = 2 * x + (q & 1);
           cg = p.out_cg0 + (bias_off >> 3);
@@ -248,5 +235,5 @@
       }
     }
   }
-  if (p.mode == EPI_HEAD && p.targets && cur_batch >= 0) flush_counts(cur_batch);
+  if (kHead && p.mode == EPI_HEAD && p.targets && cur_batch >= 0) flush_counts(cur_batch);
 }

@@ -38,8 +38,11 @@ enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_CONVT = 2, EPI_HEAD = 3 };
 constexpr int kTileRows = 16;
 constexpr int kTileCols = 8;
 constexpr int kTileM = 128;
-constexpr int kEpiGroups = 2;
-constexpr int kConvThreads = 128 + 128 * kEpiGroups;  // 4 control warps + epilogue groups of 4 warps
+constexpr int kMaxEpiGroups = 4;
+// epilogue groups of 4 warps: the thin layers (N <= 64) have short main loops and long per-pixel epilogues
+// (latency-bound single warps), so they get 4 groups; the wide ones have 2 accumulators anyway
+__host__ __device__ constexpr int epi_groups(int block_n) { return block_n <= 64 ? 4 : 2; }
+__host__ __device__ constexpr int conv_threads(int block_n) { return 128 + 128 * epi_groups(block_n); }  // 4 control warps + groups
 constexpr int kMaxClasses = 4;
 
 struct ConvParams {
@@ -57,9 +60,12 @@ struct ConvParams {
   int out_cgs;         // channel groups per image of the output buffer (concat buffers are wider)
   int out_cg0;         // first channel group written
   int cout;            // ConvT: channels per 2x2 quadrant
-  // HEAD epilogue
-  const float* head_w;  // [n_classes][32]
-  const float* head_b;  // [n_classes]
+  int cout_shift;      // log2(cout) (ConvT quadrant = n >> cout_shift)
+  // HEAD epilogue: the 1x1 head and this layer's 32 biases travel by value in the kernel parameters, so the
+  // epilogue reads them as constant-bank operands (no shared-memory traffic beside the MMA operand reads)
+  float head_w[kMaxClasses * 32];  // [n_classes][32]
+  float head_b[kMaxClasses];
+  float bias32[32];
   int n_classes;
   const void* targets;  // uint8 or int64 [B,H,W], may be null (no counts)
   int target_fmt;       // 0 = int64, 1 = uint8
@@ -97,8 +103,8 @@ struct ConvCfg {
   static constexpr int TAIL_BAR = TAIL_HEAD + (kMaxClasses * 32 + kMaxClasses) * 4;
   static constexpr int N_BARS = 2 * kMaxSA + 2 * kMaxSB + 2 * kMaxAcc + 1;
   static constexpr int TAIL_CM = TAIL_BAR + N_BARS * 8;
-  static constexpr int TAIL_DICE = TAIL_CM + kEpiGroups * kMaxClasses * kMaxClasses * 8;
-  static constexpr int TAIL_TMEM = TAIL_DICE + kEpiGroups * kMaxClasses * 2 * 8;
+  static constexpr int TAIL_DICE = TAIL_CM + kMaxEpiGroups * kMaxClasses * kMaxClasses * 8;
+  static constexpr int TAIL_TMEM = TAIL_DICE + kMaxEpiGroups * kMaxClasses * 2 * 8;
   static constexpr int TAIL_BYTES = ((TAIL_TMEM + 16 + 1023) / 1024) * 1024;  // keeps the rings 1024B aligned
   static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;       // 1024 = alignment slack
   static_assert(BK == 64 || BK == 32, "channel chunk");
@@ -116,12 +122,14 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 }
 
 template <int BLOCK_N, int BK, int KSIZE, bool WS>
-__global__ void __launch_bounds__(kConvThreads, 1)
+__global__ void __launch_bounds__(conv_threads(BLOCK_N), 1)
 conv_tc_kernel(const __grid_constant__ ConvParams p) {
   using Cfg = ConvCfg<BLOCK_N, BK, KSIZE>;
   constexpr int PAD = Cfg::PAD;
   constexpr int TAPS = KSIZE * KSIZE;
   constexpr int ACC = Cfg::ACC;
+  constexpr int kEpiGroups = epi_groups(BLOCK_N);
+  constexpr int kConvThreads = conv_threads(BLOCK_N);
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // pad to 1024 B with pointer arithmetic on the __shared__ array (keeps the address space known to
   // the compiler: LDS/STS/ATOMS instead of generic accesses)
@@ -130,7 +138,6 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   const int n_taps = k_chunks * TAPS;  // B tiles per output tile
   // [fixed-size tail: bias, head weights, barriers, counters][A ring][B ring or resident weights]
   float* s_bias = reinterpret_cast<float*>(smem + Cfg::TAIL_BIAS);
-  float* s_head = reinterpret_cast<float*>(smem + Cfg::TAIL_HEAD);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::TAIL_BAR);
   uint64_t* a_full = bars;
   uint64_t* a_empty = bars + kMaxSA;
@@ -157,8 +164,6 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   // ---------------- one-time setup (nothing here depends on the previous kernel's output)
   for (int i = threadIdx.x; i < p.n_bias; i += kConvThreads) s_bias[i] = p.bias[i];
   if (p.mode == EPI_HEAD) {
-    for (int i = threadIdx.x; i < p.n_classes * 32; i += kConvThreads) s_head[i] = p.head_w[i];
-    if (threadIdx.x < p.n_classes) s_head[kMaxClasses * 32 + threadIdx.x] = p.head_b[threadIdx.x];
     if (threadIdx.x < kEpiGroups * kMaxClasses * kMaxClasses) s_cm_all[threadIdx.x] = 0ull;
     if (threadIdx.x < kEpiGroups * kMaxClasses * 2) s_dice_all[threadIdx.x] = 0.0;
   }

@@ -8,9 +8,9 @@ import sys
 rows = list(csv.reader(open(sys.argv[1])))
 nw = int(sys.argv[2]) if len(sys.argv) > 2 else 12
 starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
-BASE = 0x1210
-CLASSES = [("a_full", 0, 12), ("a_empty", 12, 24), ("b_full", 24, 32), ("b_empty", 32, 40), ("t_full", 40, 42),
-           ("t_empty", 42, 44), ("w_full", 44, 45)]
+BASE = int(sys.argv[3], 16) if len(sys.argv) > 3 else 0x1210
+CLASSES = [("a_full", 0, 8), ("a_empty", 8, 16), ("b_full", 16, 24), ("b_empty", 24, 32), ("t_full", 32, 36),
+           ("t_empty", 36, 40), ("w_full", 40, 41)]  # ub_conv_tc.cuh: bars[] order (kMaxSA = kMaxSB = 8, kMaxAcc = 4)
 
 
 def classify(off):

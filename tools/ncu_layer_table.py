@@ -33,7 +33,13 @@ print(f"{'layer':8s} {'kernel':22s} {'t_us':>7s} {'TF/s':>6s} {'tensor%':>7s} {'
 for r, l in zip(data, layers):
     t = float(r[T]) * {'us': 1.0, 'ns': 1e-3, 'ms': 1e3}[units[T]]
     tf = GMAC[l] * 2 * mb / t * 1e3
-    tp = float(r[HM]) / 4 / float(r[CY]) * 100
-    rd, wr = float(r[RD]) * scale[units[RD]], float(r[WR]) * scale[units[WR]]
+    try:
+        tp = float(r[HM]) / 4 / float(r[CY]) * 100
+    except ValueError:
+        tp = float('nan')
+    try:
+        rd, wr = float(r[RD]) * scale[units[RD]], float(r[WR]) * scale[units[WR]]
+    except ValueError:
+        rd = wr = float('nan')
     k = r[KN].split('conv_tc_kernel')[-1].split('(')[0]
-    print(f"{l:8s} {k:22s} {t:7.1f} {tf:6.0f} {tp:7.1f} {rd:7.1f} {wr:7.1f} {(rd + wr) / t * 1e3:6.0f} {float(r[LT]):5.1f} {float(r[L1]):5.1f} {float(r[GH]):.2f}")
+    print(f"{l:8s} {k:22s} {t:7.1f} {tf:6.0f} {tp:7.1f} {rd:7.1f} {wr:7.1f} {(rd + wr) / t * 1e3:6.0f} {r[LT][:5]:>5s} {r[L1][:5]:>5s} {r[GH][:4]}")
