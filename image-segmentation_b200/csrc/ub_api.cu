@@ -41,6 +41,7 @@ struct GemmLayer {
   int cin = 0, cout = 0, n_total = 0, ksize = 3, block_n = 0, bk = 64, relu = 1;
   bool is_convt = false;
   __nv_bfloat16* w = nullptr;  // [n_total][ksize*ksize*cin] bf16, BN folded
+  __nv_bfloat16* w_kxs = nullptr;  // thin 3x3 layers: [(ky*3+kx)*cout + co][cin] for the kx-stacked kernel
   float* bias = nullptr;       // [cout]
   std::vector<float> h_bias;   // host copy (the HEAD layer passes its 32 biases by value)
 };
@@ -86,6 +87,7 @@ struct ub_ctx {
   // optional per-launch timing (ub_profile_begin/end): event pairs around every GEMM launch
   bool force_stream = false;  // UB_FORCE_STREAM=1: never use the weight-stationary pipeline (tests)
   bool use_pdl = true;        // UB_NO_PDL=1: plain stream-ordered launches
+  bool no_kxs = false;        // UB_NO_KXS=1: thin layers run the standard (9-tap) kernel
   bool profiling = false;
   struct ProfRec { int layer; cudaEvent_t a, b; };
   std::vector<ProfRec> prof;
@@ -166,6 +168,16 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   UB_CUDA(ctx, cudaMemcpy(L.w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
   UB_CUDA(ctx, cudaMemcpy(L.bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
   L.h_bias = bias;
+  if (L.cout <= 64 && L.cin % 64 == 0) {
+    // kx-stacked operand (ub_conv_tc.cuh): GEMM column n3 = kx*cout + co of the ky-th box, K = cin
+    std::vector<__nv_bfloat16> ks(packed.size());
+    for (int t = 0; t < 9; ++t)
+      for (int co = 0; co < L.cout; ++co)
+        for (int ci = 0; ci < L.cin; ++ci)
+          ks[(static_cast<size_t>(t) * L.cout + co) * L.cin + ci] = packed[co * K + static_cast<size_t>(t) * L.cin + ci];
+    if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.w_kxs), ks.size() * 2))) return rc;
+    UB_CUDA(ctx, cudaMemcpy(L.w_kxs, ks.data(), ks.size() * 2, cudaMemcpyHostToDevice));
+  }
   ctx->layer_by_key[L.key] = static_cast<int>(ctx->layers.size());
   ctx->layers.push_back(L);
   return UB_OK;
@@ -248,13 +260,13 @@ int pack_all(ub_ctx* ctx) {
 // Activations are channel-blocked: [B][cgs][H][W][8] bf16.  The map views `cin/8` consecutive planes starting at
 // `base`: dims {8*W, H, cin/8, B}; one box = {8*(8+2*pad) elements, 16+2*pad rows, bk/8 planes} (ub_conv_tc.cuh).
 int make_tm_act(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int cin, int cgs_total, int W, int H, int B,
-                int ksize, int bk) {
-  const int pad = ksize / 2;
+                int ksize, int bk, int tw) {
+  const int pady = ksize / 2, padx = ub::is_kxs(tw) ? 0 : pady;
   const cuuint64_t dims[4] = {static_cast<cuuint64_t>(8) * W, static_cast<cuuint64_t>(H), static_cast<cuuint64_t>(cin / 8),
                               static_cast<cuuint64_t>(B)};
   const cuuint64_t strides[3] = {static_cast<cuuint64_t>(W) * 16, static_cast<cuuint64_t>(H) * W * 16,
                                  static_cast<cuuint64_t>(cgs_total) * H * W * 16};
-  const cuuint32_t box[4] = {static_cast<cuuint32_t>(8 * (ub::kTileCols + 2 * pad)), static_cast<cuuint32_t>(ub::kTileRows + 2 * pad),
+  const cuuint32_t box[4] = {static_cast<cuuint32_t>(8 * (tw + 2 * padx)), static_cast<cuuint32_t>(ub::tile_rows(tw) + 2 * pady),
                              static_cast<cuuint32_t>(bk / 8), 1};
   const cuuint32_t estr[4] = {1, 1, 1, 1};
   const CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<__nv_bfloat16*>(base), dims,
@@ -278,12 +290,24 @@ int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total,
 
 // Static part of a GEMM step: descriptors over (src view) and the layer's packed weights.  `src` points at the
 // first channel-group plane the layer reads; `src_cgs` / `out_cgs` are the planes per image of the two buffers.
+// Tile geometry of a layer: the thin 3x3 layers run kx-stacked (32-pixel-wide tiles, 16 when the pool is fused).
+int pick_tw(const ub_ctx* ctx, const GemmLayer& L, int mode) {
+  if (ctx->no_kxs || !L.w_kxs || L.ksize != 3 || mode == ub::EPI_HEAD || mode == ub::EPI_CONVT) return 8;
+  return mode == ub::EPI_POOL ? 16 : 32;
+}
+
 int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat16* src, int src_cgs,
               int B, int H, int W, int mode, __nv_bfloat16* out, int out_cgs, int out_cg0) {
   memset(cp, 0, sizeof(*cp));
   int rc;
-  if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin, src_cgs, W, H, B, L.ksize, L.bk))) return rc;
-  if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, L.block_n, L.bk))) return rc;
+  const int tw = pick_tw(ctx, L, mode);
+  cp->tw = tw;
+  if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin, src_cgs, W, H, B, L.ksize, L.bk, tw))) return rc;
+  if (ub::is_kxs(tw)) {
+    if ((rc = make_tm_w(ctx, &cp->tmB, L.w_kxs, L.cin, 9 * L.cout, 3 * L.cout, L.bk))) return rc;
+  } else {
+    if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, L.block_n, L.bk))) return rc;
+  }
   cp->B = B; cp->H = H; cp->W = W;
   cp->cin = L.cin; cp->ksize = L.ksize; cp->n_total = L.n_total;
   cp->mode = mode; cp->relu = L.relu;
@@ -307,11 +331,11 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
 
 // Pipeline shape for one launch: weight-stationary when every tap of an n-tile fits beside >= 2 A stages
 // (and the persistent grid keeps each CTA on one n-tile), else a short A ring + as many B stages as fit.
-template <int N, int BK, int KS>
+template <int N, int BK, int KS, int TW>
 bool choose_pipeline(ConvParams* cp, int grid, bool allow_ws, int* smem_bytes) {
-  using Cfg = ub::ConvCfg<N, BK, KS>;
-  const int n_tiles = cp->n_total / N;
-  const int n_taps = (cp->cin / BK) * KS * KS;
+  using Cfg = ub::ConvCfg<N, BK, KS, TW>;
+  const int n_tiles = Cfg::KXS ? 1 : cp->n_total / N;
+  const int n_taps = (cp->cin / BK) * Cfg::TAPS;
   const int w_bytes = n_taps * Cfg::B_STAGE_BYTES;
   const int budget = Cfg::OPERAND_BUDGET;
   if (allow_ws && w_bytes + 2 * Cfg::A_STAGE_BYTES <= budget && grid % n_tiles == 0) {
@@ -329,18 +353,18 @@ bool choose_pipeline(ConvParams* cp, int grid, bool allow_ws, int* smem_bytes) {
   return false;
 }
 
-template <int N, int BK, int KS, bool WS>
+template <int N, int BK, int KS, bool WS, int TW>
 int launch_kernel(ub_ctx* ctx, const ConvParams& cp, int grid, int smem, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, BK, KS, WS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, BK, KS, WS, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       ub::kSmemLimit));
     attr_set = true;
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(ub::conv_threads(N));
+  cfg.blockDim = dim3(ub::conv_threads(N, TW));
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -348,22 +372,22 @@ int launch_kernel(ub_ctx* ctx, const ConvParams& cp, int grid, int smem, cudaStr
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = ctx->use_pdl ? 1 : 0;
-  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_tc_kernel<N, BK, KS, WS>, cp));
+  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_tc_kernel<N, BK, KS, WS, TW>, cp));
   ctx->launches++;
   return UB_OK;
 }
 
-template <int N, int BK, int KS>
+template <int N, int BK, int KS, int TW = 8>
 int launch_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   ConvParams cp = cp_in;
-  const int tiles = cp.B * ((cp.H + ub::kTileRows - 1) / ub::kTileRows) * ((cp.W + ub::kTileCols - 1) / ub::kTileCols) *
-                    (cp.n_total / N);
+  constexpr int TH = ub::tile_rows(TW), XS = ub::tile_xstep(TW);
+  const int tiles = cp.B * ((cp.H + TH - 1) / TH) * ((cp.W + XS - 1) / XS) * (ub::is_kxs(TW) ? 1 : cp.n_total / N);
   const int grid = tiles < ctx->num_sms ? tiles : ctx->num_sms;
   int smem = 0;
   // UB_FORCE_STREAM=1 (test hook): exercise the streaming path on layers that would be weight-stationary
-  const bool ws = choose_pipeline<N, BK, KS>(&cp, grid, !ctx->force_stream, &smem);
-  return ws ? launch_kernel<N, BK, KS, true>(ctx, cp, grid, smem, st)
-            : launch_kernel<N, BK, KS, false>(ctx, cp, grid, smem, st);
+  const bool ws = choose_pipeline<N, BK, KS, TW>(&cp, grid, !ctx->force_stream, &smem);
+  return ws ? launch_kernel<N, BK, KS, true, TW>(ctx, cp, grid, smem, st)
+            : launch_kernel<N, BK, KS, false, TW>(ctx, cp, grid, smem, st);
 }
 
 template <int N, int BK>
@@ -394,6 +418,13 @@ int launch_gemm(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStre
 
 int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStream_t st) {
   if (cp.mode == ub::EPI_HEAD && block_n != 32) return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs 32 channels");
+  if (ub::is_kxs(cp.tw)) {  // thin 3x3 layers, N = 3 * cout
+    if (cp.tw == 32 && cp.cout == 64) return launch_inst<192, 64, 3, 32>(ctx, cp, st);
+    if (cp.tw == 32 && cp.cout == 32) return launch_inst<96, 64, 3, 32>(ctx, cp, st);
+    if (cp.tw == 16 && cp.cout == 64) return launch_inst<192, 64, 3, 16>(ctx, cp, st);
+    if (cp.tw == 16 && cp.cout == 32) return launch_inst<96, 64, 3, 16>(ctx, cp, st);
+    return fail(ctx, UB_ERR_UNSUPPORTED, "no kx-stacked kernel for cout=%d tw=%d", cp.cout, cp.tw);
+  }
   if (bk == 64) {
     switch (block_n) {
       case 32: return launch_ks<32, 64>(ctx, cp, st);
@@ -667,6 +698,8 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   ctx->force_stream = fs && fs[0] == '1';
   const char* np = getenv("UB_NO_PDL");
   ctx->use_pdl = !(np && np[0] == '1');
+  const char* nk = getenv("UB_NO_KXS");
+  ctx->no_kxs = nk && nk[0] == '1';
   *out = ctx.release();
   return UB_OK;
 }

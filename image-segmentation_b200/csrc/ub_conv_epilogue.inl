@@ -1,13 +1,15 @@
 // Epilogue body of conv_tc_kernel (included inside the `warp >= 4` branch).
-// Thread (wq, lane) owns accumulator row m = 32*wq + lane = pixel (ty = 4*wq + lane/8, tx = lane%8)
-// of the 16x8 tile and reads its BLOCK_N fp32 columns from TMEM 32 at a time (double-buffered: the
-// next tcgen05.ld is in flight while the current 32 channels are converted and stored).
+// Thread (wq, lane) owns accumulator row m = 32*wq + lane = pixel (ty = m / TW, tx = m % TW) of the
+// (128/TW) x TW tile and reads its fp32 columns from TMEM 32 at a time (double-buffered: the next
+// tcgen05.ld is in flight while the current 32 channels are converted and stored).  In the kx-stacked
+// variants tx is an INPUT column: columns 0 and TW-1 are halo, and output channel co of column tx is
+// D[tx-1][co] + D[tx][Cout+co] + D[tx+1][2*Cout+co].
 {
   constexpr bool kHead = (BLOCK_N == 32);  // the fused head exists only in the 32-channel instantiations
   const int wq = warp & 3;
   const int grp = (warp - 4) >> 2;             // tiles it with it % kEpiGroups == grp
-  const int ty = 4 * wq + (lane >> 3);
-  const int tx = lane & 7;
+  const int ty = (32 * wq + lane) / TW;
+  const int tx = (32 * wq + lane) % TW;
   const int et = (threadIdx.x - 128) & 127;    // 0..127 within the group
   unsigned long long* s_cm = s_cm_all + grp * (kMaxClasses * kMaxClasses);
   double* s_dice = s_dice_all + grp * (2 * kMaxClasses);
@@ -66,11 +68,11 @@
     const uint32_t use = static_cast<uint32_t>(it / ACC);
     const int nt = t % n_tiles;
     int mm = t / n_tiles;
-    const int x = (mm % tiles_x) * kTileCols + tx;
+    const int x = (mm % tiles_x) * kXStep - (KXS ? 1 : 0) + tx;
     mm /= tiles_x;
     const int y = (mm % tiles_y) * kTileRows + ty;
     const int b = mm / tiles_y;
-    const bool inb = (y < p.H) && (x < p.W);
+    const bool inb = (y < p.H) && (x < p.W) && (!KXS || (tx >= 1 && tx <= TW - 2));
     const int n0 = nt * BLOCK_N;
     int tgt_pre = -1;
 
@@ -94,7 +96,7 @@
     mbar_wait(&t_full[acc], use & 1u);
     tc_fence_after();
     const uint32_t t_addr =
-        tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + static_cast<uint32_t>(acc * BLOCK_N);
+        tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + static_cast<uint32_t>(acc * Cfg::ACC_STRIDE);
     auto release_acc = [&]() {  // every column of this accumulator is in registers: hand it back to the MMA warp
       tc_fence_before();
       mbar_arrive(&t_empty[acc]);
@@ -168,7 +170,9 @@
       int oy = y, ox = x, oh = p.H, ow = p.W;
       bool writer = inb;
       if (p.mode == EPI_POOL) {
-        writer = inb && ((lane & 9) == 0);  // MaxPool2d(2,2): partners are lane^1 (x) and lane^8 (y)
+        // MaxPool2d(2,2).  Standard tile: partners are lane^1 (x) and lane^8 (y).  Kx-stacked TW = 16 tile:
+        // outputs start at an even x in tile column 1, so pairs are (odd tx, tx+1) and rows are lane^16.
+        writer = KXS ? (inb && (tx & 1) && lane < 16) : (inb && ((lane & 9) == 0));
         oy = y >> 1; ox = x >> 1; oh = p.H >> 1; ow = p.W >> 1;
       } else if (p.mode == EPI_CONVT) {
         oh = 2 * p.H; ow = 2 * p.W;
@@ -197,40 +201,70 @@
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
         }
+        // bf16 rounding is monotone, so max(bf16(a), bf16(b)) == bf16(max(a, b)): pack first, then pool the
+        // packed pairs (half the shuffles and half the max instructions of an fp32 pool, same result)
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
         if (p.mode == EPI_POOL) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            v[j] = fmaxf(v[j], __shfl_xor_sync(0xffffffffu, v[j], 1));
-            v[j] = fmaxf(v[j], __shfl_xor_sync(0xffffffffu, v[j], 8));
+          for (int j = 0; j < 16; ++j) {
+            if constexpr (KXS) {
+              pk[j] = bf16x2_max(pk[j], __shfl_down_sync(0xffffffffu, pk[j], 1));
+              pk[j] = bf16x2_max(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 16));
+            } else {
+              pk[j] = bf16x2_max(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 1));
+              pk[j] = bf16x2_max(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 8));
+            }
           }
         }
         if (writer) {
           uint4* dst = reinterpret_cast<uint4*>(p.out) +
                        ((static_cast<size_t>(b) * p.out_cgs + cg) * plane + static_cast<size_t>(py) * ow + px);
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            uint4 o;
-            o.x = pack_bf16(v[8 * g + 0], v[8 * g + 1]);
-            o.y = pack_bf16(v[8 * g + 2], v[8 * g + 3]);
-            o.z = pack_bf16(v[8 * g + 4], v[8 * g + 5]);
-            o.w = pack_bf16(v[8 * g + 6], v[8 * g + 7]);
-            dst[static_cast<size_t>(g) * plane] = o;
-          }
+          for (int g = 0; g < 4; ++g)
+            dst[static_cast<size_t>(g) * plane] = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
         }
       };
-      uint32_t ra[32], rb[32];
-      tmem_ld_32x32(t_addr, ra);
-#pragma unroll 1
-      for (int cb = 0; cb < BLOCK_N; cb += 64) {
-        tmem_ld_wait();
-        if (cb + 32 < BLOCK_N) tmem_ld_32x32(t_addr + static_cast<uint32_t>(cb + 32), rb);
-        else release_acc();
-        store_chunk(ra, cb);
-        if (cb + 32 < BLOCK_N) {
+      if constexpr (KXS) {
+        // phase 1 (needs TMEM): read the three kx blocks of every 32-channel chunk and add the neighbours'
+        // shares; the accumulator is released as soon as the last block is in registers.  phase 2: bias,
+        // ReLU, pool, store from registers while the MMA warp already refills the accumulator.
+        constexpr int CO = Cfg::COUT_T;
+        constexpr int NCH = CO / 32;
+        uint32_t sum[NCH][32];
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+          uint32_t d0[32], d1[32], d2[32];
+          tmem_ld_32x32(t_addr + static_cast<uint32_t>(32 * ch), d0);
+          tmem_ld_32x32(t_addr + static_cast<uint32_t>(CO + 32 * ch), d1);
+          tmem_ld_32x32(t_addr + static_cast<uint32_t>(2 * CO + 32 * ch), d2);
           tmem_ld_wait();
-          if (cb + 64 < BLOCK_N) tmem_ld_32x32(t_addr + static_cast<uint32_t>(cb + 64), ra);
+          if (ch == NCH - 1) release_acc();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float left = __shfl_up_sync(0xffffffffu, __uint_as_float(d0[j]), 1, TW);     // kx = 0 of column tx-1
+            const float right = __shfl_down_sync(0xffffffffu, __uint_as_float(d2[j]), 1, TW);  // kx = 2 of column tx+1
+            sum[ch][j] = __float_as_uint((left + __uint_as_float(d1[j])) + right);
+          }
+        }
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) store_chunk(sum[ch], 32 * ch);
+      } else {
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32(t_addr, ra);
+#pragma unroll 1
+        for (int cb = 0; cb < BLOCK_N; cb += 64) {
+          tmem_ld_wait();
+          if (cb + 32 < BLOCK_N) tmem_ld_32x32(t_addr + static_cast<uint32_t>(cb + 32), rb);
           else release_acc();
-          store_chunk(rb, cb + 32);
+          store_chunk(ra, cb);
+          if (cb + 32 < BLOCK_N) {
+            tmem_ld_wait();
+            if (cb + 64 < BLOCK_N) tmem_ld_32x32(t_addr + static_cast<uint32_t>(cb + 64), ra);
+            else release_acc();
+            store_chunk(rb, cb + 32);
+          }
         }
       }
     }

@@ -26,6 +26,13 @@
 // B operand:  weights W2[N][K] (K contiguous, 128B/64B swizzle), one TMA box {BK, BLOCK_N} per (c, tap):
 //             either streamed through a ring, or — when all taps of an n-tile fit beside the A ring (the
 //             thin, high-resolution layers) — loaded ONCE per persistent CTA and kept resident (WS).
+// KXS ("kx-stacked") variant for the thin 3x3 layers (Cout <= 64), where the 4 KB A read per MMA — not the
+//             tensor pipe — is the limit (shared-memory bandwidth): the three kx taps become GEMM columns,
+//             N = 3*Cout, D[p][kx*Cout+co] = sum_{ky,ci} X[y+ky-1][x'][ci] W[co][ci][ky][kx] over INPUT column
+//             x', and the epilogue adds the three column blocks of the neighbouring pixels (two warp
+//             shuffles per value): out[x] = D0[x-1] + D1[x] + D2[x+1].  One A read then feeds 3x the FLOPs.
+//             Tiles are TW = 32 (or 16 for the pooled layer) pixels wide with one halo column on each
+//             side (TW-2 outputs); the A box has no x halo, so 8-pixel groups stay 128 bytes apart.
 // Warp roles: w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, then kEpiGroups groups of 4 epilogue
 // warps.  kAcc TMEM accumulators (up to 4): the MMA warp runs ahead of the epilogues by kAcc tiles.
 #pragma once
@@ -35,18 +42,20 @@ namespace ub {
 
 enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_CONVT = 2, EPI_HEAD = 3 };
 
-constexpr int kTileRows = 16;
-constexpr int kTileCols = 8;
 constexpr int kTileM = 128;
 constexpr int kMaxEpiGroups = 4;
+constexpr int kMaxClasses = 4;
+// tile geometry: TW = 8 is the standard 16-row x 8-column tile; TW = 16 / 32 are the kx-stacked variants
+__host__ __device__ constexpr bool is_kxs(int tw) { return tw != 8; }
+__host__ __device__ constexpr int tile_rows(int tw) { return kTileM / tw; }
+__host__ __device__ constexpr int tile_xstep(int tw) { return is_kxs(tw) ? tw - 2 : tw; }  // output columns per tile
 // epilogue groups of 4 warps: the thin layers (N <= 64) have short main loops and long per-pixel epilogues
 // (latency-bound single warps), so they get 4 groups; the wide ones have 2 accumulators anyway
-__host__ __device__ constexpr int epi_groups(int block_n) { return block_n <= 64 ? 4 : 2; }
-__host__ __device__ constexpr int conv_threads(int block_n) { return 128 + 128 * epi_groups(block_n); }  // 4 control warps + groups
-constexpr int kMaxClasses = 4;
+__host__ __device__ constexpr int epi_groups(int block_n, int tw) { return is_kxs(tw) ? 2 : (block_n <= 64 ? 4 : 2); }
+__host__ __device__ constexpr int conv_threads(int block_n, int tw) { return 128 + 128 * epi_groups(block_n, tw); }
 
 struct ConvParams {
-  CUtensorMap tmA;  // activations: dims {8*W, H, Cin/8, B}, box {8*(8+2*pad), 16+2*pad, BK/8, 1}
+  CUtensorMap tmA;  // activations: dims {8*W, H, Cin/8, B}, box {8*PXW, ROWS_IN, BK/8, 1} (ConvCfg)
   CUtensorMap tmB;  // weights:     dims {Ktot, Ntot}, box {BK, BLOCK_N}
   int B, H, W;      // input extent (= output extent for conv; output is 2H x 2W for ConvT)
   int cin;          // channels of the A source = K per tap
@@ -76,6 +85,7 @@ struct ConvParams {
   uint8_t* pred_out;       // [B,H,W] or null
   float* logits_out;       // [B,C,H,W] or null
   // pipeline shape chosen by the host (ub_api.cu: choose_pipeline)
+  int tw;  // tile width chosen by the host (8 standard, 16/32 kx-stacked); the kernel has it as a template parameter
   int sa;  // A stages (activation boxes)
   int sb;  // B stages when streaming weights; unused when the kernel is the WS instantiation
 };
@@ -85,18 +95,25 @@ constexpr int kMaxSB = 8;
 constexpr int kMaxAcc = 4;
 constexpr int kSmemLimit = 232448;  // 227 KB, the sm_100 per-block maximum
 
-template <int BLOCK_N, int BK, int KSIZE>
+template <int BLOCK_N, int BK, int KSIZE, int TW>
 struct ConvCfg {
-  static constexpr int PAD = KSIZE / 2;
-  static constexpr int PXW = kTileCols + 2 * PAD;        // pixels per box row
-  static constexpr int ROWS_IN = kTileRows + 2 * PAD;    // box rows
+  static constexpr bool KXS = is_kxs(TW);
+  static constexpr int TH = tile_rows(TW);
+  static constexpr int PADY = KSIZE / 2;
+  static constexpr int PADX = KXS ? 0 : PADY;            // kx-stacked tiles carry their x halo inside the tile
+  static constexpr int PXW = TW + 2 * PADX;              // pixels per box row
+  static constexpr int ROWS_IN = TH + 2 * PADY;          // box rows
+  static constexpr int SBO_BYTES = KXS ? 128 : PXW * 16; // distance between 8-pixel groups of the A tile
+  static constexpr int TAPS = KXS ? KSIZE : KSIZE * KSIZE;            // B boxes per channel chunk
+  static constexpr int COUT_T = KXS ? BLOCK_N / 3 : BLOCK_N;          // output channels per tile
   static constexpr int A_PLANE_BYTES = ROWS_IN * PXW * 16;            // one channel group of the box = LBO
   static constexpr int A_BOX_BYTES = (BK / 8) * A_PLANE_BYTES;        // what one TMA load delivers
   static constexpr int A_STAGE_BYTES = ((A_BOX_BYTES + 1023) / 1024) * 1024;
   static constexpr int SWZ_B = 2 * BK;                                // weight rows: 128 B or 64 B swizzle
   static constexpr int B_STAGE_BYTES = BLOCK_N * SWZ_B;
-  static constexpr int ACC = (512 / BLOCK_N) < kMaxAcc ? (512 / BLOCK_N) : kMaxAcc;
-  static constexpr int TMEM_COLS = ACC * BLOCK_N;
+  static constexpr int ACC_STRIDE = BLOCK_N <= 32 ? 32 : BLOCK_N <= 64 ? 64 : BLOCK_N <= 128 ? 128 : 256;  // TMEM columns
+  static constexpr int ACC = (512 / ACC_STRIDE) < kMaxAcc ? (512 / ACC_STRIDE) : kMaxAcc;
+  static constexpr int TMEM_COLS = ACC * ACC_STRIDE;
   // fixed-size tail in front of the two operand regions
   static constexpr int TAIL_BIAS = 0;
   static constexpr int TAIL_HEAD = TAIL_BIAS + 1024 * 4;
@@ -108,6 +125,7 @@ struct ConvCfg {
   static constexpr int TAIL_BYTES = ((TAIL_TMEM + 16 + 1023) / 1024) * 1024;  // keeps the rings 1024B aligned
   static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;       // 1024 = alignment slack
   static_assert(BK == 64 || BK == 32, "channel chunk");
+  static_assert(!KXS || (KSIZE == 3 && BLOCK_N % 48 == 0 && (TW == 16 || TW == 32)), "kx-stacked geometry");
   static_assert(TMEM_COLS >= 32 && (TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns");
   static_assert(B_STAGE_BYTES % 1024 == 0, "swizzle atom alignment");
 };
@@ -121,15 +139,22 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <int BLOCK_N, int BK, int KSIZE, bool WS>
-__global__ void __launch_bounds__(conv_threads(BLOCK_N), 1)
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+  const __nv_bfloat162 r = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+  return *reinterpret_cast<const uint32_t*>(&r);
+}
+
+template <int BLOCK_N, int BK, int KSIZE, bool WS, int TW>
+__global__ void __launch_bounds__(conv_threads(BLOCK_N, TW), 1)
 conv_tc_kernel(const __grid_constant__ ConvParams p) {
-  using Cfg = ConvCfg<BLOCK_N, BK, KSIZE>;
-  constexpr int PAD = Cfg::PAD;
-  constexpr int TAPS = KSIZE * KSIZE;
+  using Cfg = ConvCfg<BLOCK_N, BK, KSIZE, TW>;
+  constexpr bool KXS = Cfg::KXS;
+  constexpr int TAPS = Cfg::TAPS;
   constexpr int ACC = Cfg::ACC;
-  constexpr int kEpiGroups = epi_groups(BLOCK_N);
-  constexpr int kConvThreads = conv_threads(BLOCK_N);
+  constexpr int kTileRows = Cfg::TH;
+  constexpr int kXStep = tile_xstep(TW);
+  constexpr int kEpiGroups = epi_groups(BLOCK_N, TW);
+  constexpr int kConvThreads = conv_threads(BLOCK_N, TW);
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // pad to 1024 B with pointer arithmetic on the __shared__ array (keeps the address space known to
   // the compiler: LDS/STS/ATOMS instead of generic accesses)
@@ -156,9 +181,9 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
-  const int tiles_x = (p.W + kTileCols - 1) / kTileCols;
+  const int tiles_x = (p.W + kXStep - 1) / kXStep;
   const int tiles_y = (p.H + kTileRows - 1) / kTileRows;
-  const int n_tiles = p.n_total / BLOCK_N;
+  const int n_tiles = KXS ? 1 : p.n_total / BLOCK_N;
   const int total_tiles = p.B * tiles_x * tiles_y * n_tiles;
 
   // ---------------- one-time setup (nothing here depends on the previous kernel's output)
@@ -199,7 +224,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
 #pragma unroll 1
         for (int j = 0; j < n_taps; ++j) {  // consumption order: c outer, tap inner
           const int c = j / TAPS, tap = j % TAPS;
-          tma_load_2d(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, tap * p.cin + c * BK, nt * BLOCK_N);
+          if constexpr (KXS) tma_load_2d(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, c * BK, tap * BLOCK_N);
+          else tma_load_2d(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, tap * p.cin + c * BK, nt * BLOCK_N);
         }
       }
       __syncwarp();
@@ -211,7 +237,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int nt = t % n_tiles;
       int m = t / n_tiles;
-      const int x0 = (m % tiles_x) * kTileCols;
+      const int x0 = (m % tiles_x) * kXStep - (KXS ? 1 : 0);  // input column of tile column 0
       m /= tiles_x;
       const int y0 = (m % tiles_y) * kTileRows;
       const int b = m / tiles_y;
@@ -220,7 +246,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
         mbar_wait(&a_empty[sa], pa ^ 1u);
         if (leader) {
           mbar_arrive_expect_tx(&a_full[sa], static_cast<uint32_t>(Cfg::A_BOX_BYTES));
-          tma_load_4d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], (x0 - PAD) * 8, y0 - PAD, c * (BK / 8), b);
+          tma_load_4d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], (x0 - Cfg::PADX) * 8, y0 - Cfg::PADY,
+                      c * (BK / 8), b);
         }
         __syncwarp();
         if (++sa == p.sa) { sa = 0; pa ^= 1u; }
@@ -230,7 +257,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
             mbar_wait(&b_empty[sb], pb ^ 1u);
             if (leader) {
               mbar_arrive_expect_tx(&b_full[sb], Cfg::B_STAGE_BYTES);
-              tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb], tap * p.cin + c * BK, nt * BLOCK_N);
+              if constexpr (KXS) tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb], c * BK, tap * BLOCK_N);
+              else tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb], tap * p.cin + c * BK, nt * BLOCK_N);
             }
             __syncwarp();
             if (++sb == p.sb) { sb = 0; pb ^= 1u; }
@@ -244,7 +272,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     // descriptors advance by plain 32-bit adds on the low word ((address >> 4) field); high words are constant
-    const uint64_t desc_a = umma_smem_desc_interleaved(smem_u32(a_ring), Cfg::A_PLANE_BYTES, Cfg::PXW * 16);
+    const uint64_t desc_a = umma_smem_desc_interleaved(smem_u32(a_ring), Cfg::A_PLANE_BYTES, Cfg::SBO_BYTES);
     const uint64_t desc_b = umma_smem_desc<Cfg::SWZ_B>(smem_u32(b_ring));
     const uint32_t a_hi = static_cast<uint32_t>(desc_a >> 32), b_hi = static_cast<uint32_t>(desc_b >> 32);
     const uint32_t a_lo_ring = static_cast<uint32_t>(desc_a), b_lo_ring = static_cast<uint32_t>(desc_b);
@@ -264,7 +292,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
       const uint32_t use = static_cast<uint32_t>(it / ACC);
       mbar_wait(&t_empty[acc], (use & 1u) ^ 1u);
       tc_fence_after();
-      const uint32_t d_tmem = tmem_u + static_cast<uint32_t>(acc * BLOCK_N);
+      const uint32_t d_tmem = tmem_u + static_cast<uint32_t>(acc * Cfg::ACC_STRIDE);
 #pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
         mbar_wait(&a_full[sa], pa);
@@ -272,9 +300,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
         const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(sa) * A_STAGE_U;
 #pragma unroll
         for (int tap = 0; tap < TAPS; ++tap) {
-          constexpr int dummy = 0;
-          (void)dummy;
-          const uint32_t a_tap = a_lo + static_cast<uint32_t>((tap / KSIZE) * Cfg::PXW + (tap % KSIZE));
+          // kx-stacked: tap = ky (one box row down); else tap = ky*3+kx (row down, pixel right)
+          const uint32_t a_tap = a_lo + static_cast<uint32_t>(KXS ? tap * Cfg::PXW : (tap / KSIZE) * Cfg::PXW + (tap % KSIZE));
           uint32_t b_lo;
           if constexpr (WS) {
             b_lo = b_lo_ring + static_cast<uint32_t>(c * TAPS + tap) * B_STAGE_U;
