@@ -62,16 +62,19 @@
   };
 
   int it = grp;
+  TileIter ti;
+  ti.init(blockIdx.x + grp * gridDim.x, kEpiGroups * gridDim.x, n_tiles, tiles_x, tiles_y);
+  // first image of the NEXT reference batch, relative to this micro-batch (HEAD): b only grows
+  int batch_now = (p.img_base + ti.b) / p.ref_batch;
+  int batch_end = (batch_now + 1) * p.ref_batch - p.img_base;
 #pragma unroll 1
-  for (int t = blockIdx.x + grp * gridDim.x; t < total_tiles; t += kEpiGroups * gridDim.x, it += kEpiGroups) {
+  for (int t = blockIdx.x + grp * gridDim.x; t < total_tiles; t += kEpiGroups * gridDim.x, it += kEpiGroups, ti.next()) {
     const int acc = it % ACC;
     const uint32_t use = static_cast<uint32_t>(it / ACC);
-    const int nt = t % n_tiles;
-    int mm = t / n_tiles;
-    const int x = (mm % tiles_x) * kXStep - (KXS ? 1 : 0) + tx;
-    mm /= tiles_x;
-    const int y = (mm % tiles_y) * kTileRows + ty;
-    const int b = mm / tiles_y;
+    const int nt = ti.nt;
+    const int x = ti.tx * kXStep - (KXS ? 1 : 0) + tx;
+    const int y = ti.ty * kTileRows + ty;
+    const int b = ti.b;
     const bool inb = (y < p.H) && (x < p.W) && (!KXS || (tx >= 1 && tx <= TW - 2));
     const int n0 = nt * BLOCK_N;
     int tgt_pre = -1;
@@ -79,7 +82,8 @@
     if (kHead && p.mode == EPI_HEAD && p.targets) {
       // counts accumulate in registers across tiles and go to HBM only when the reference batch
       // changes (and once at the end): <= C*C global atomics per batch per CTA instead of per tile
-      const int batch = (p.img_base + b) / p.ref_batch;
+      while (b >= batch_end) { ++batch_now; batch_end += p.ref_batch; }
+      const int batch = batch_now;
       if (batch != cur_batch || tiles_since_flush >= kFlushTiles) {
         if (cur_batch >= 0) flush_counts(cur_batch);
         cur_batch = batch;
@@ -108,62 +112,69 @@
       tmem_ld_32x32(t_addr, r);
       tmem_ld_wait();
       release_acc();
-      const int C = p.n_classes;
+      // the per-pixel head, specialised for the usual 3 classes (NC = 0: class count known at run time only)
+      auto head_pixel = [&](auto nc_tag) {
+        constexpr int NC = decltype(nc_tag)::value;
+        const int C = NC ? NC : p.n_classes;
       float z[kMaxClasses];
 #pragma unroll
-      for (int c = 0; c < kMaxClasses; ++c) z[c] = (c < C) ? p.head_b[c] : -INFINITY;
+        for (int c = 0; c < kMaxClasses; ++c) z[c] = (c < C) ? p.head_b[c] : -INFINITY;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        float v = __uint_as_float(r[j]) + p.bias32[j];
-        v = p.relu ? fmaxf(v, 0.0f) : v;
-#pragma unroll
-        for (int c = 0; c < kMaxClasses; ++c)
-          if (c < C) z[c] = fmaf(p.head_w[c * 32 + j], v, z[c]);
-      }
-      // softmax (models/losses.py:48), then first-index argmax (:50)
-      float zmax = z[0];
-#pragma unroll
-      for (int c = 1; c < kMaxClasses; ++c) zmax = fmaxf(zmax, z[c]);
-      float pr[kMaxClasses], psum = 0.0f;
-#pragma unroll
-      for (int c = 0; c < kMaxClasses; ++c) { pr[c] = (c < C) ? expf(z[c] - zmax) : 0.0f; psum += pr[c]; }
-      int pred = 0;
-      float best = -1.0f;
-#pragma unroll
-      for (int c = 0; c < kMaxClasses; ++c) {
-        pr[c] = pr[c] / psum;
-        if (c < C && pr[c] > best) { best = pr[c]; pred = c; }
-      }
-      const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
-      if (inb) {
-        if (p.pred_out) p.pred_out[pix] = static_cast<uint8_t>(pred);
-        if (p.logits_out) {
+        for (int j = 0; j < 32; ++j) {
+          float v = __uint_as_float(r[j]) + p.bias32[j];
+          v = p.relu ? fmaxf(v, 0.0f) : v;
 #pragma unroll
           for (int c = 0; c < kMaxClasses; ++c)
-            if (c < C) p.logits_out[((static_cast<size_t>(b) * C + c) * p.H + y) * p.W + x] = z[c];
+            if (c < C) z[c] = fmaf(p.head_w[c * 32 + j], v, z[c]);
         }
-      }
-      if (p.targets) {
-        const int tgt = (tgt_pre >= 0 && tgt_pre < C) ? tgt_pre : -1;
+        // softmax (models/losses.py:48), then first-index argmax (:50)
+        float zmax = z[0];
 #pragma unroll
-        for (int tc = 0; tc < kMaxClasses; ++tc)
+        for (int c = 1; c < kMaxClasses; ++c) zmax = fmaxf(zmax, z[c]);
+        float pr[kMaxClasses], psum = 0.0f;
 #pragma unroll
-          for (int pc = 0; pc < kMaxClasses; ++pc) cnt[tc * kMaxClasses + pc] += (tgt == tc && pred == pc) ? 1u : 0u;
-        if (p.dice) {
-          // smp DiceLoss(from_logits=True) applies softmax again to the softmax output (losses.py:100)
-          float q[kMaxClasses], qmax = pr[0], qsum = 0.0f;
+        for (int c = 0; c < kMaxClasses; ++c) { pr[c] = (c < C) ? expf(z[c] - zmax) : 0.0f; psum += pr[c]; }
+        int pred = 0;
+        float best = -1.0f;
 #pragma unroll
-          for (int c = 1; c < kMaxClasses; ++c) if (c < C) qmax = fmaxf(qmax, pr[c]);
+        for (int c = 0; c < kMaxClasses; ++c) {
+          pr[c] = pr[c] / psum;
+          if (c < C && pr[c] > best) { best = pr[c]; pred = c; }
+        }
+        const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
+        if (inb) {
+          if (p.pred_out) p.pred_out[pix] = static_cast<uint8_t>(pred);
+          if (p.logits_out) {
 #pragma unroll
-          for (int c = 0; c < kMaxClasses; ++c) { q[c] = (c < C) ? expf(pr[c] - qmax) : 0.0f; qsum += q[c]; }
-#pragma unroll
-          for (int c = 0; c < kMaxClasses; ++c) {
-            const float pc = (inb && c < C) ? q[c] / qsum : 0.0f;
-            dsum[2 * c + 0] += (tgt == c) ? pc : 0.0f;
-            dsum[2 * c + 1] += pc;
+            for (int c = 0; c < kMaxClasses; ++c)
+              if (c < C) p.logits_out[((static_cast<size_t>(b) * C + c) * p.H + y) * p.W + x] = z[c];
           }
         }
-      }
+        if (p.targets) {
+          const int tgt = (tgt_pre >= 0 && tgt_pre < C) ? tgt_pre : -1;
+#pragma unroll
+          for (int tc = 0; tc < kMaxClasses; ++tc)
+#pragma unroll
+            for (int pc = 0; pc < kMaxClasses; ++pc)
+              if (tc < C && pc < C) cnt[tc * kMaxClasses + pc] += (tgt == tc && pred == pc) ? 1u : 0u;
+          if (p.dice) {
+            // smp DiceLoss(from_logits=True) applies softmax again to the softmax output (losses.py:100)
+            float q[kMaxClasses], qmax = pr[0], qsum = 0.0f;
+#pragma unroll
+            for (int c = 1; c < kMaxClasses; ++c) if (c < C) qmax = fmaxf(qmax, pr[c]);
+#pragma unroll
+            for (int c = 0; c < kMaxClasses; ++c) { q[c] = (c < C) ? expf(pr[c] - qmax) : 0.0f; qsum += q[c]; }
+#pragma unroll
+            for (int c = 0; c < kMaxClasses; ++c) {
+              const float pc = (inb && c < C) ? q[c] / qsum : 0.0f;
+              dsum[2 * c + 0] += (tgt == c) ? pc : 0.0f;
+              dsum[2 * c + 1] += pc;
+            }
+          }
+        }
+      };
+      if (p.n_classes == 3) head_pixel(std::integral_constant<int, 3>{});
+      else head_pixel(std::integral_constant<int, 0>{});
     } else {
       // ---- STORE / POOL / CONVT: bias (+ReLU) -> bf16 -> channel-blocked global store, 32 channels at a time
       // geometry of this thread's output pixel (fixed per tile)

@@ -51,7 +51,7 @@ __host__ __device__ constexpr int tile_rows(int tw) { return kTileM / tw; }
 __host__ __device__ constexpr int tile_xstep(int tw) { return is_kxs(tw) ? tw - 2 : tw; }  // output columns per tile
 // epilogue groups of 4 warps: the thin layers (N <= 64) have short main loops and long per-pixel epilogues
 // (latency-bound single warps), so they get 4 groups; the wide ones have 2 accumulators anyway
-__host__ __device__ constexpr int epi_groups(int block_n, int tw) { return is_kxs(tw) ? 2 : (block_n <= 64 ? 4 : 2); }
+__host__ __device__ constexpr int epi_groups(int block_n, int tw) { return is_kxs(tw) ? 2 : (block_n <= 32 ? 4 : 2); }
 __host__ __device__ constexpr int conv_threads(int block_n, int tw) { return 128 + 128 * epi_groups(block_n, tw); }
 
 struct ConvParams {
@@ -128,6 +128,35 @@ struct ConvCfg {
   static_assert(!KXS || (KSIZE == 3 && BLOCK_N % 48 == 0 && (TW == 16 || TW == 32)), "kx-stacked geometry");
   static_assert(TMEM_COLS >= 32 && (TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns");
   static_assert(B_STAGE_BYTES % 1024 == 0, "swizzle atom alignment");
+};
+
+// Walks the tiles t0, t0 + stride, ... of one warp role without per-tile integer divisions: the tile index
+// is kept as mixed-radix digits (n-tile, tile column, tile row, image) and advanced by the pre-decomposed stride.
+struct TileIter {
+  int nt, tx, ty, b;
+  int inc_nt, inc_tx, inc_ty, inc_b;
+  int n_tiles, tiles_x, tiles_y;
+  __device__ __forceinline__ void init(int t0, int stride, int n_tiles_, int tiles_x_, int tiles_y_) {
+    n_tiles = n_tiles_; tiles_x = tiles_x_; tiles_y = tiles_y_;
+    nt = t0 % n_tiles; int m = t0 / n_tiles;
+    tx = m % tiles_x; m /= tiles_x;
+    ty = m % tiles_y; b = m / tiles_y;
+    inc_nt = stride % n_tiles; m = stride / n_tiles;
+    inc_tx = m % tiles_x; m /= tiles_x;
+    inc_ty = m % tiles_y; inc_b = m / tiles_y;
+  }
+  __device__ __forceinline__ void next() {
+    nt += inc_nt;
+    int c = nt >= n_tiles ? 1 : 0;
+    nt -= c ? n_tiles : 0;
+    tx += inc_tx + c;
+    c = tx >= tiles_x ? 1 : 0;
+    tx -= c ? tiles_x : 0;
+    ty += inc_ty + c;
+    c = ty >= tiles_y ? 1 : 0;
+    ty -= c ? tiles_y : 0;
+    b += inc_b + c;
+  }
 };
 
 __device__ __forceinline__ void epi_bar_sync(int grp) {  // named barrier 1..: the 128 threads of one epilogue group
@@ -233,14 +262,14 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     pdl_wait_prior_grid();  // activations of the previous layer are complete and visible from here on
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
+    TileIter ti;
+    ti.init(blockIdx.x, gridDim.x, n_tiles, tiles_x, tiles_y);
 #pragma unroll 1
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const int nt = t % n_tiles;
-      int m = t / n_tiles;
-      const int x0 = (m % tiles_x) * kXStep - (KXS ? 1 : 0);  // input column of tile column 0
-      m /= tiles_x;
-      const int y0 = (m % tiles_y) * kTileRows;
-      const int b = m / tiles_y;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ti.next()) {
+      const int nt = ti.nt;
+      const int x0 = ti.tx * kXStep - (KXS ? 1 : 0);  // input column of tile column 0
+      const int y0 = ti.ty * kTileRows;
+      const int b = ti.b;
 #pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
         mbar_wait(&a_empty[sa], pa ^ 1u);

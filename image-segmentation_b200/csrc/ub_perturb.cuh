@@ -62,7 +62,9 @@ __device__ __forceinline__ int load_u8(const void* img, int fmt, int b, int c, i
 }
 
 // One pixel (all 3 channels) of the perturbed network input, for every family except the blurs.
-__device__ __forceinline__ void perturbed_pixel(const PerturbDev& P, const void* img, int fmt, int b,
+// `lut` is the 256-entry table of the LUT families: per-thread indexed, so callers stage it in shared memory
+// (a data-dependent index into the constant bank would serialise the warp).
+__device__ __forceinline__ void perturbed_pixel(const PerturbDev& P, const uint8_t* lut, const void* img, int fmt, int b,
                                                 int y, int x, int H, int W, float (&out)[3]) {
   const size_t hw = static_cast<size_t>(H) * W;
   const size_t pix = static_cast<size_t>(y) * W + x;
@@ -86,7 +88,7 @@ __device__ __forceinline__ void perturbed_pixel(const PerturbDev& P, const void*
     } break;
     case UB_P_U8_LUT:
 #pragma unroll
-      for (int c = 0; c < 3; ++c) out[c] = static_cast<float>(P.lut[load_u8(img, fmt, b, c, y, x, H, W)]) / 255.0f;
+      for (int c = 0; c < 3; ++c) out[c] = static_cast<float>(lut[load_u8(img, fmt, b, c, y, x, H, W)]) / 255.0f;
       break;
     case UB_P_U8_OCCLUSION:
     case UB_P_F_OCCLUSION: {
@@ -161,13 +163,16 @@ __device__ __forceinline__ void perturbed_pixel(const PerturbDev& P, const void*
 
 // Perturbation alone -> fp32 NCHW (ub_perturb_images; also feeds perturbed_out).
 __global__ void perturb_kernel(PerturbDev P, const void* img, int fmt, int n, int H, int W, float* out) {
+  __shared__ uint8_t s_lut[256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) s_lut[i] = P.lut[i];
+  __syncthreads();
   const size_t hw = static_cast<size_t>(H) * W;
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= hw * n) return;
   const int b = static_cast<int>(i / hw);
   const int y = static_cast<int>((i % hw) / W), x = static_cast<int>(i % W);
   float v[3];
-  perturbed_pixel(P, img, fmt, b, y, x, H, W, v);
+  perturbed_pixel(P, s_lut, img, fmt, b, y, x, H, W, v);
 #pragma unroll
   for (int c = 0; c < 3; ++c) out[(static_cast<size_t>(b) * 3 + c) * hw + static_cast<size_t>(y) * W + x] = v[c];
 }
@@ -238,36 +243,39 @@ struct StemWeights {
   float b[32];
 };
 __global__ void __launch_bounds__(256)
-stem_kernel(PerturbDev P, StemWeights sw, const void* img, int fmt, int n, int H, int W,
-            __nv_bfloat16* out, int cgs, int cg0, float* perturbed_out) {
-  __shared__ float s_w[32 * 3 + 32];
-  for (int i = threadIdx.x; i < 32 * 3; i += blockDim.x) s_w[i] = sw.w[i];
-  if (threadIdx.x < 32) s_w[96 + threadIdx.x] = sw.b[threadIdx.x];
-  __syncthreads();
+stem_kernel(const __grid_constant__ PerturbDev P, const __grid_constant__ StemWeights sw, const void* img, int fmt, int n,
+            int H, int W, __nv_bfloat16* out, int cgs, int cg0, float* perturbed_out) {
+  __shared__ uint8_t s_lut[256];
+  if (P.kind == UB_P_U8_LUT) {
+    s_lut[threadIdx.x] = P.lut[threadIdx.x];  // blockDim.x == 256
+    __syncthreads();
+  }
   const size_t hw = static_cast<size_t>(H) * W;
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= hw * n) return;
   const int b = static_cast<int>(i / hw);
-  const int y = static_cast<int>((i % hw) / W), x = static_cast<int>(i % W);
+  const size_t pix = i - static_cast<size_t>(b) * hw;
+  const int y = static_cast<int>(pix / W), x = static_cast<int>(pix % W);
   float v[3];
-  perturbed_pixel(P, img, fmt, b, y, x, H, W, v);
+  perturbed_pixel(P, s_lut, img, fmt, b, y, x, H, W, v);
   if (perturbed_out) {
 #pragma unroll
-    for (int c = 0; c < 3; ++c) perturbed_out[(static_cast<size_t>(b) * 3 + c) * hw + static_cast<size_t>(y) * W + x] = v[c];
+    for (int c = 0; c < 3; ++c) perturbed_out[(static_cast<size_t>(b) * 3 + c) * hw + pix] = v[c];
   }
+  // the 32x3 weights and 32 biases are kernel parameters: FFMA reads them straight from the constant bank
   uint32_t packed[16];
 #pragma unroll
   for (int o = 0; o < 32; o += 2) {
-    float a0 = s_w[96 + o], a1 = s_w[96 + o + 1];
+    float a0 = sw.b[o], a1 = sw.b[o + 1];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      a0 = fmaf(s_w[o * 3 + c], v[c], a0);
-      a1 = fmaf(s_w[(o + 1) * 3 + c], v[c], a1);
+      a0 = fmaf(sw.w[o * 3 + c], v[c], a0);
+      a1 = fmaf(sw.w[(o + 1) * 3 + c], v[c], a1);
     }
     __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
     packed[o >> 1] = *reinterpret_cast<uint32_t*>(&h);
   }
-  uint4* dst = reinterpret_cast<uint4*>(out) + (static_cast<size_t>(b) * cgs + cg0) * hw + (i - static_cast<size_t>(b) * hw);
+  uint4* dst = reinterpret_cast<uint4*>(out) + (static_cast<size_t>(b) * cgs + cg0) * hw + pix;
 #pragma unroll
   for (int g = 0; g < 4; ++g) dst[g * hw] = make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
 }
