@@ -88,6 +88,7 @@ struct ub_ctx {
   bool force_stream = false;  // UB_FORCE_STREAM=1: never use the weight-stationary pipeline (tests)
   bool use_pdl = true;        // UB_NO_PDL=1: plain stream-ordered launches
   bool no_kxs = false;        // UB_NO_KXS=1: thin layers run the standard (9-tap) kernel
+  bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool profiling = false;
   struct ProfRec { int layer; cudaEvent_t a, b; };
   std::vector<ProfRec> prof;
@@ -303,10 +304,14 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   const int tw = pick_tw(ctx, L, mode);
   cp->tw = tw;
   if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin, src_cgs, W, H, B, L.ksize, L.bk, tw))) return rc;
+  // CTA pairs (cta_group::2) for the wide layers whose weights cannot stay resident in shared memory
+  const size_t w_tile_bytes = static_cast<size_t>(L.ksize) * L.ksize * L.cin * L.block_n * 2;
+  const bool resident = w_tile_bytes + 2 * 24576 <= 220 * 1024;  // mirrors choose_pipeline's weight-stationary test
+  cp->cg2 = (!ctx->no_cg2 && tw == 8 && L.bk == 64 && L.block_n >= 128 && mode != ub::EPI_HEAD && mode != ub::EPI_CONVT && !resident) ? 1 : 0;
   if (ub::is_kxs(tw)) {
     if ((rc = make_tm_w(ctx, &cp->tmB, L.w_kxs, L.cin, 9 * L.cout, 3 * L.cout, L.bk))) return rc;
   } else {
-    if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, L.block_n, L.bk))) return rc;
+    if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, cp->cg2 ? L.block_n / 2 : L.block_n, L.bk))) return rc;
   }
   cp->B = B; cp->H = H; cp->W = W;
   cp->cin = L.cin; cp->ksize = L.ksize; cp->n_total = L.n_total;
@@ -331,9 +336,9 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
 
 // Pipeline shape for one launch: weight-stationary when every tap of an n-tile fits beside >= 2 A stages
 // (and the persistent grid keeps each CTA on one n-tile), else a short A ring + as many B stages as fit.
-template <int N, int BK, int KS, int TW>
+template <int N, int BK, int KS, int TW, bool CG2 = false>
 bool choose_pipeline(ConvParams* cp, int grid, bool allow_ws, int* smem_bytes) {
-  using Cfg = ub::ConvCfg<N, BK, KS, TW>;
+  using Cfg = ub::ConvCfg<N, BK, KS, TW, CG2>;
   const int n_tiles = Cfg::KXS ? 1 : cp->n_total / N;
   const int n_taps = (cp->cin / BK) * Cfg::TAPS;
   const int w_bytes = n_taps * Cfg::B_STAGE_BYTES;
@@ -353,11 +358,11 @@ bool choose_pipeline(ConvParams* cp, int grid, bool allow_ws, int* smem_bytes) {
   return false;
 }
 
-template <int N, int BK, int KS, bool WS, int TW>
+template <int N, int BK, int KS, bool WS, int TW, bool CG2 = false>
 int launch_kernel(ub_ctx* ctx, const ConvParams& cp, int grid, int smem, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, BK, KS, WS, TW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, BK, KS, WS, TW, CG2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       ub::kSmemLimit));
     attr_set = true;
   }
@@ -367,12 +372,23 @@ int launch_kernel(ub_ctx* ctx, const ConvParams& cp, int grid, int smem, cudaStr
   cfg.blockDim = dim3(ub::conv_threads(N, TW));
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (ctx->use_pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (CG2) {  // the two CTAs of a pair are one cluster (adjacent SMs of a TPC)
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = ctx->use_pdl ? 1 : 0;
-  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_tc_kernel<N, BK, KS, WS, TW>, cp));
+  cfg.numAttrs = na;
+  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_tc_kernel<N, BK, KS, WS, TW, CG2>, cp));
   ctx->launches++;
   return UB_OK;
 }
@@ -388,6 +404,21 @@ int launch_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   const bool ws = choose_pipeline<N, BK, KS, TW>(&cp, grid, !ctx->force_stream, &smem);
   return ws ? launch_kernel<N, BK, KS, true, TW>(ctx, cp, grid, smem, st)
             : launch_kernel<N, BK, KS, false, TW>(ctx, cp, grid, smem, st);
+}
+
+// CTA-pair launch: tiles are enumerated (column, row, image, n-tile) over an even, padded image count
+// (ub_conv_tc.cuh), the grid is even and the weights always stream.
+template <int N, int KS>
+int launch_pair(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
+  ConvParams cp = cp_in;
+  const int per_img = ((cp.H + 15) / 16) * ((cp.W + 7) / 8);
+  const int b_pad = cp.B + ((per_img * cp.B) & 1);
+  const int tiles = per_img * b_pad * (cp.n_total / N);
+  const int max_grid = ctx->num_sms & ~1;
+  const int grid = tiles < max_grid ? tiles : max_grid;
+  int smem = 0;
+  choose_pipeline<N, 64, KS, 8, true>(&cp, grid, false, &smem);
+  return launch_kernel<N, 64, KS, false, 8, true>(ctx, cp, grid, smem, st);
 }
 
 template <int N, int BK>
@@ -424,6 +455,13 @@ int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cuda
     if (cp.tw == 16 && cp.cout == 64) return launch_inst<192, 64, 3, 16>(ctx, cp, st);
     if (cp.tw == 16 && cp.cout == 32) return launch_inst<96, 64, 3, 16>(ctx, cp, st);
     return fail(ctx, UB_ERR_UNSUPPORTED, "no kx-stacked kernel for cout=%d tw=%d", cp.cout, cp.tw);
+  }
+  if (cp.cg2) {
+    if (block_n == 256 && cp.ksize == 3) return launch_pair<256, 3>(ctx, cp, st);
+    if (block_n == 256 && cp.ksize == 1) return launch_pair<256, 1>(ctx, cp, st);
+    if (block_n == 128 && cp.ksize == 3) return launch_pair<128, 3>(ctx, cp, st);
+    if (block_n == 128 && cp.ksize == 1) return launch_pair<128, 1>(ctx, cp, st);
+    return fail(ctx, UB_ERR_UNSUPPORTED, "no CTA-pair kernel for BLOCK_N=%d ksize=%d", block_n, cp.ksize);
   }
   if (bk == 64) {
     switch (block_n) {
@@ -700,6 +738,8 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   ctx->use_pdl = !(np && np[0] == '1');
   const char* nk = getenv("UB_NO_KXS");
   ctx->no_kxs = nk && nk[0] == '1';
+  const char* nc = getenv("UB_NO_CG2");
+  ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();
   return UB_OK;
 }

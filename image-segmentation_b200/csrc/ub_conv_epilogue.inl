@@ -62,20 +62,19 @@
   };
 
   int it = grp;
-  TileIter ti;
-  ti.init(blockIdx.x + grp * gridDim.x, kEpiGroups * gridDim.x, n_tiles, tiles_x, tiles_y);
+  TileIter ti = tile_iter(blockIdx.x + grp * gridDim.x, kEpiGroups * gridDim.x);
   // first image of the NEXT reference batch, relative to this micro-batch (HEAD): b only grows
-  int batch_now = (p.img_base + ti.b) / p.ref_batch;
+  int batch_now = (p.img_base + ti.d3) / p.ref_batch;
   int batch_end = (batch_now + 1) * p.ref_batch - p.img_base;
 #pragma unroll 1
   for (int t = blockIdx.x + grp * gridDim.x; t < total_tiles; t += kEpiGroups * gridDim.x, it += kEpiGroups, ti.next()) {
     const int acc = it % ACC;
     const uint32_t use = static_cast<uint32_t>(it / ACC);
-    const int nt = ti.nt;
-    const int x = ti.tx * kXStep - (KXS ? 1 : 0) + tx;
-    const int y = ti.ty * kTileRows + ty;
-    const int b = ti.b;
-    const bool inb = (y < p.H) && (x < p.W) && (!KXS || (tx >= 1 && tx <= TW - 2));
+    const int nt = CG2 ? ti.d3 : ti.d0;
+    const int x = (CG2 ? ti.d0 : ti.d1) * kXStep - (KXS ? 1 : 0) + tx;
+    const int y = (CG2 ? ti.d1 : ti.d2) * kTileRows + ty;
+    const int b = CG2 ? ti.d2 : ti.d3;
+    const bool inb = (y < p.H) && (x < p.W) && (!KXS || (tx >= 1 && tx <= TW - 2)) && (!CG2 || b < p.B);
     const int n0 = nt * BLOCK_N;
     int tgt_pre = -1;
 
@@ -103,7 +102,8 @@
         tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + static_cast<uint32_t>(acc * Cfg::ACC_STRIDE);
     auto release_acc = [&]() {  // every column of this accumulator is in registers: hand it back to the MMA warp
       tc_fence_before();
-      mbar_arrive(&t_empty[acc]);
+      if constexpr (CG2) mbar_arrive_leader(&t_empty[acc]);  // the pair's MMA warp lives in the even CTA
+      else mbar_arrive(&t_empty[acc]);
     };
 
     if (kHead && p.mode == EPI_HEAD) {

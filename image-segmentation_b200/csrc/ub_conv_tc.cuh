@@ -33,6 +33,11 @@
 //             shuffles per value): out[x] = D0[x-1] + D1[x] + D2[x+1].  One A read then feeds 3x the FLOPs.
 //             Tiles are TW = 32 (or 16 for the pooled layer) pixels wide with one halo column on each
 //             side (TW-2 outputs); the A box has no x halo, so 8-pixel groups stay 128 bytes apart.
+// CG2 (CTA pair, tcgen05 cta_group::2) variant for the wide streaming layers (N >= 128): two CTAs of a cluster
+//             compute two 128-pixel tiles of the same n-tile with ONE M = 256 MMA stream issued by the even
+//             CTA.  Each CTA stages its own A box and HALF of every weight tile (N/2 rows); the tensor
+//             cores of both SMs read both halves.  Weight traffic from L2 and the shared-memory bytes
+//             written and read per MMA are halved — these layers were bound by exactly that.
 // Warp roles: w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, then kEpiGroups groups of 4 epilogue
 // warps.  kAcc TMEM accumulators (up to 4): the MMA warp runs ahead of the epilogues by kAcc tiles.
 #pragma once
@@ -85,6 +90,7 @@ struct ConvParams {
   uint8_t* pred_out;       // [B,H,W] or null
   float* logits_out;       // [B,C,H,W] or null
   // pipeline shape chosen by the host (ub_api.cu: choose_pipeline)
+  int cg2; // 1 = CTA-pair kernel (host: tmB box holds N/2 rows, even grid, cluster launch)
   int tw;  // tile width chosen by the host (8 standard, 16/32 kx-stacked); the kernel has it as a template parameter
   int sa;  // A stages (activation boxes)
   int sb;  // B stages when streaming weights; unused when the kernel is the WS instantiation
@@ -95,7 +101,7 @@ constexpr int kMaxSB = 8;
 constexpr int kMaxAcc = 4;
 constexpr int kSmemLimit = 232448;  // 227 KB, the sm_100 per-block maximum
 
-template <int BLOCK_N, int BK, int KSIZE, int TW>
+template <int BLOCK_N, int BK, int KSIZE, int TW, bool CG2 = false>
 struct ConvCfg {
   static constexpr bool KXS = is_kxs(TW);
   static constexpr int TH = tile_rows(TW);
@@ -110,7 +116,8 @@ struct ConvCfg {
   static constexpr int A_BOX_BYTES = (BK / 8) * A_PLANE_BYTES;        // what one TMA load delivers
   static constexpr int A_STAGE_BYTES = ((A_BOX_BYTES + 1023) / 1024) * 1024;
   static constexpr int SWZ_B = 2 * BK;                                // weight rows: 128 B or 64 B swizzle
-  static constexpr int B_STAGE_BYTES = BLOCK_N * SWZ_B;
+  static constexpr int B_ROWS = CG2 ? BLOCK_N / 2 : BLOCK_N;          // weight rows staged by one CTA
+  static constexpr int B_STAGE_BYTES = B_ROWS * SWZ_B;
   static constexpr int ACC_STRIDE = BLOCK_N <= 32 ? 32 : BLOCK_N <= 64 ? 64 : BLOCK_N <= 128 ? 128 : 256;  // TMEM columns
   static constexpr int ACC = (512 / ACC_STRIDE) < kMaxAcc ? (512 / ACC_STRIDE) : kMaxAcc;
   static constexpr int TMEM_COLS = ACC * ACC_STRIDE;
@@ -125,6 +132,7 @@ struct ConvCfg {
   static constexpr int TAIL_BYTES = ((TAIL_TMEM + 16 + 1023) / 1024) * 1024;  // keeps the rings 1024B aligned
   static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;       // 1024 = alignment slack
   static_assert(BK == 64 || BK == 32, "channel chunk");
+  static_assert(!CG2 || (TW == 8 && BLOCK_N >= 128), "CTA pairs are for the wide standard-geometry layers");
   static_assert(!KXS || (KSIZE == 3 && BLOCK_N % 48 == 0 && (TW == 16 || TW == 32)), "kx-stacked geometry");
   static_assert(TMEM_COLS >= 32 && (TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns");
   static_assert(B_STAGE_BYTES % 1024 == 0, "swizzle atom alignment");
@@ -133,29 +141,29 @@ struct ConvCfg {
 // Walks the tiles t0, t0 + stride, ... of one warp role without per-tile integer divisions: the tile index
 // is kept as mixed-radix digits (n-tile, tile column, tile row, image) and advanced by the pre-decomposed stride.
 struct TileIter {
-  int nt, tx, ty, b;
-  int inc_nt, inc_tx, inc_ty, inc_b;
-  int n_tiles, tiles_x, tiles_y;
-  __device__ __forceinline__ void init(int t0, int stride, int n_tiles_, int tiles_x_, int tiles_y_) {
-    n_tiles = n_tiles_; tiles_x = tiles_x_; tiles_y = tiles_y_;
-    nt = t0 % n_tiles; int m = t0 / n_tiles;
-    tx = m % tiles_x; m /= tiles_x;
-    ty = m % tiles_y; b = m / tiles_y;
-    inc_nt = stride % n_tiles; m = stride / n_tiles;
-    inc_tx = m % tiles_x; m /= tiles_x;
-    inc_ty = m % tiles_y; inc_b = m / tiles_y;
+  int d0, d1, d2, d3;      // digits, d0 fastest; radices r0, r1, r2 (d3 unbounded)
+  int i0, i1, i2, i3;      // the stride, decomposed the same way
+  int r0, r1, r2;
+  __device__ __forceinline__ void init(int t0, int stride, int r0_, int r1_, int r2_) {
+    r0 = r0_; r1 = r1_; r2 = r2_;
+    d0 = t0 % r0; int m = t0 / r0;
+    d1 = m % r1; m /= r1;
+    d2 = m % r2; d3 = m / r2;
+    i0 = stride % r0; m = stride / r0;
+    i1 = m % r1; m /= r1;
+    i2 = m % r2; i3 = m / r2;
   }
   __device__ __forceinline__ void next() {
-    nt += inc_nt;
-    int c = nt >= n_tiles ? 1 : 0;
-    nt -= c ? n_tiles : 0;
-    tx += inc_tx + c;
-    c = tx >= tiles_x ? 1 : 0;
-    tx -= c ? tiles_x : 0;
-    ty += inc_ty + c;
-    c = ty >= tiles_y ? 1 : 0;
-    ty -= c ? tiles_y : 0;
-    b += inc_b + c;
+    d0 += i0;
+    int c = d0 >= r0 ? 1 : 0;
+    d0 -= c ? r0 : 0;
+    d1 += i1 + c;
+    c = d1 >= r1 ? 1 : 0;
+    d1 -= c ? r1 : 0;
+    d2 += i2 + c;
+    c = d2 >= r2 ? 1 : 0;
+    d2 -= c ? r2 : 0;
+    d3 += i3 + c;
   }
 };
 
@@ -173,10 +181,11 @@ __device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
   return *reinterpret_cast<const uint32_t*>(&r);
 }
 
-template <int BLOCK_N, int BK, int KSIZE, bool WS, int TW>
+template <int BLOCK_N, int BK, int KSIZE, bool WS, int TW, bool CG2 = false>
 __global__ void __launch_bounds__(conv_threads(BLOCK_N, TW), 1)
 conv_tc_kernel(const __grid_constant__ ConvParams p) {
-  using Cfg = ConvCfg<BLOCK_N, BK, KSIZE, TW>;
+  using Cfg = ConvCfg<BLOCK_N, BK, KSIZE, TW, CG2>;
+  static_assert(!(CG2 && WS), "CTA pairs stream their weights");
   constexpr bool KXS = Cfg::KXS;
   constexpr int TAPS = Cfg::TAPS;
   constexpr int ACC = Cfg::ACC;
@@ -213,7 +222,17 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   const int tiles_x = (p.W + kXStep - 1) / kXStep;
   const int tiles_y = (p.H + kTileRows - 1) / kTileRows;
   const int n_tiles = KXS ? 1 : p.n_total / BLOCK_N;
-  const int total_tiles = p.B * tiles_x * tiles_y * n_tiles;
+  // Tile order.  Standard: (n-tile, column, row, image), n-tile fastest.  CTA pairs: (column, row, image, n-tile)
+  // with the image count padded so that tiles 2k and 2k+1 — the two CTAs of a pair — always share the n-tile.
+  const int b_pad = CG2 ? p.B + ((tiles_x * tiles_y * p.B) & 1) : p.B;
+  const int total_tiles = b_pad * tiles_x * tiles_y * n_tiles;
+  const uint32_t cta_rank = CG2 ? cluster_ctarank() : 0u;
+  auto tile_iter = [&](int t0, int stride) {
+    TileIter ti;
+    if constexpr (CG2) ti.init(t0, stride, tiles_x, tiles_y, b_pad);
+    else ti.init(t0, stride, n_tiles, tiles_x, tiles_y);
+    return ti;
+  };
 
   // ---------------- one-time setup (nothing here depends on the previous kernel's output)
   for (int i = threadIdx.x; i < p.n_bias; i += kConvThreads) s_bias[i] = p.bias[i];
@@ -228,16 +247,17 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kMaxSA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < kMaxSB; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
-    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 128); }
+    for (int i = 0; i < kMaxAcc; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], CG2 ? 256 : 128); }
     mbar_init(w_full, 1);
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(s_tmem, Cfg::TMEM_COLS);
-    tmem_relinquish();
+    if constexpr (CG2) { tmem_alloc_pair(s_tmem, Cfg::TMEM_COLS); tmem_relinquish_pair(); }
+    else { tmem_alloc(s_tmem, Cfg::TMEM_COLS); tmem_relinquish(); }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG2) cluster_sync_all();  // the peer's barriers are initialised before anything is signalled on them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
 
@@ -262,21 +282,27 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     pdl_wait_prior_grid();  // activations of the previous layer are complete and visible from here on
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
-    TileIter ti;
-    ti.init(blockIdx.x, gridDim.x, n_tiles, tiles_x, tiles_y);
+    TileIter ti = tile_iter(blockIdx.x, gridDim.x);
 #pragma unroll 1
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ti.next()) {
-      const int nt = ti.nt;
-      const int x0 = ti.tx * kXStep - (KXS ? 1 : 0);  // input column of tile column 0
-      const int y0 = ti.ty * kTileRows;
-      const int b = ti.b;
+      const int nt = CG2 ? ti.d3 : ti.d0;
+      const int x0 = (CG2 ? ti.d0 : ti.d1) * kXStep - (KXS ? 1 : 0);  // input column of tile column 0
+      const int y0 = (CG2 ? ti.d1 : ti.d2) * kTileRows;
+      const int b = CG2 ? ti.d2 : ti.d3;  // may be the padding image (== B) of a CTA pair: TMA zero-fills
 #pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
         mbar_wait(&a_empty[sa], pa ^ 1u);
         if (leader) {
-          mbar_arrive_expect_tx(&a_full[sa], static_cast<uint32_t>(Cfg::A_BOX_BYTES));
-          tma_load_4d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], (x0 - Cfg::PADX) * 8, y0 - Cfg::PADY,
-                      c * (BK / 8), b);
+          if constexpr (CG2) {
+            // both CTAs' boxes are counted on the leader's barrier; only the leader announces the bytes
+            if (cta_rank == 0) mbar_arrive_expect_tx(&a_full[sa], static_cast<uint32_t>(2 * Cfg::A_BOX_BYTES));
+            tma_load_4d_pair(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], (x0 - Cfg::PADX) * 8, y0 - Cfg::PADY,
+                             c * (BK / 8), b);
+          } else {
+            mbar_arrive_expect_tx(&a_full[sa], static_cast<uint32_t>(Cfg::A_BOX_BYTES));
+            tma_load_4d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], (x0 - Cfg::PADX) * 8, y0 - Cfg::PADY,
+                        c * (BK / 8), b);
+          }
         }
         __syncwarp();
         if (++sa == p.sa) { sa = 0; pa ^= 1u; }
@@ -285,9 +311,15 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
           for (int tap = 0; tap < TAPS; ++tap) {
             mbar_wait(&b_empty[sb], pb ^ 1u);
             if (leader) {
-              mbar_arrive_expect_tx(&b_full[sb], Cfg::B_STAGE_BYTES);
-              if constexpr (KXS) tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb], c * BK, tap * BLOCK_N);
-              else tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb], tap * p.cin + c * BK, nt * BLOCK_N);
+              if constexpr (CG2) {
+                if (cta_rank == 0) mbar_arrive_expect_tx(&b_full[sb], 2 * Cfg::B_STAGE_BYTES);
+                tma_load_2d_pair(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb], tap * p.cin + c * BK,
+                                 nt * BLOCK_N + static_cast<int>(cta_rank) * Cfg::B_ROWS);
+              } else {
+                mbar_arrive_expect_tx(&b_full[sb], Cfg::B_STAGE_BYTES);
+                if constexpr (KXS) tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb], c * BK, tap * BLOCK_N);
+                else tma_load_2d(b_ring + sb * Cfg::B_STAGE_BYTES, &p.tmB, &b_full[sb], tap * p.cin + c * BK, nt * BLOCK_N);
+              }
             }
             __syncwarp();
             if (++sb == p.sb) { sb = 0; pb ^= 1u; }
@@ -295,10 +327,20 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == 1 && cta_rank == 0) {
     // ================= MMA issuer (whole warp runs the loop; ONE fixed lane issues and commits) =================
+    // (CTA pairs: the even CTA issues M = 256 MMAs for both; the odd CTA's warp 1 has nothing to do)
     const bool leader = elect_one();
-    constexpr uint32_t idesc = umma_idesc_bf16(kTileM, BLOCK_N);
+    constexpr uint32_t idesc = umma_idesc_bf16(CG2 ? 2 * kTileM : kTileM, BLOCK_N);
+    auto mma = [&](auto acc_tag, uint32_t d, uint32_t al, uint32_t ah, uint32_t bl, uint32_t bh) {
+      constexpr bool kAcc = decltype(acc_tag)::value;
+      if constexpr (CG2) umma_bf16_lo_pair<kAcc>(d, al, ah, bl, bh, idesc);
+      else umma_bf16_lo<kAcc>(d, al, ah, bl, bh, idesc);
+    };
+    auto commit = [&](uint64_t* bar) {
+      if constexpr (CG2) umma_commit_pair(bar);
+      else umma_commit(bar);
+    };
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     // descriptors advance by plain 32-bit adds on the low word ((address >> 4) field); high words are constant
     const uint64_t desc_a = umma_smem_desc_interleaved(smem_u32(a_ring), Cfg::A_PLANE_BYTES, Cfg::SBO_BYTES);
@@ -344,14 +386,14 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
             for (int k = 0; k < BK / 16; ++k) {
               const uint32_t al = a_tap + k * A_KSTEP_U, bl = b_lo + 2 * k;
               if (tap == 0 && k == 0) {
-                if (c == 0) umma_bf16_lo<false>(d_tmem, al, a_hi, bl, b_hi, idesc);
-                else umma_bf16_lo<true>(d_tmem, al, a_hi, bl, b_hi, idesc);
+                if (c == 0) mma(std::false_type{}, d_tmem, al, a_hi, bl, b_hi);
+                else mma(std::true_type{}, d_tmem, al, a_hi, bl, b_hi);
               } else {
-                umma_bf16_lo<true>(d_tmem, al, a_hi, bl, b_hi, idesc);
+                mma(std::true_type{}, d_tmem, al, a_hi, bl, b_hi);
               }
             }
-            if constexpr (!WS) umma_commit(&b_empty[sb]);
-            if (tap == TAPS - 1) umma_commit(&a_empty[sa]);
+            if constexpr (!WS) commit(&b_empty[sb]);
+            if (tap == TAPS - 1) commit(&a_empty[sa]);
           }
           __syncwarp();
           if constexpr (!WS) {
@@ -360,7 +402,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
         }
         if (++sa == p.sa) { sa = 0; pa ^= 1u; }
       }
-      if (leader) umma_commit(&t_full[acc]);
+      if (leader) commit(&t_full[acc]);
       __syncwarp();
     }
   } else if (warp >= 4) {
@@ -371,10 +413,12 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   // ---------------- teardown
   __syncwarp();
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG2) cluster_sync_all();  // the peer may still signal our barriers / read our operands until here
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if constexpr (CG2) tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
+    else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
 }
 

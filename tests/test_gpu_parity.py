@@ -69,7 +69,7 @@ def test_every_conv_layer(base_model, dev):
         if key.endswith(".up"):
             continue
         wf, bf = folded(sd, key)
-        for (n, h, w) in [(2, 24, 40), (1, 64, 64)]:  # ragged tiles and full tiles
+        for (n, h, w) in [(2, 24, 40), (1, 64, 64), (3, 16, 8)]:  # ragged tiles, full tiles, odd tile count (CTA-pair padding)
             x = torch.randn((n, wf.shape[1], h, w), generator=g)
             ref = F.relu(F.conv2d(util.bf16_round(x).to(dev), util.bf16_round(wf).to(dev), bf.to(dev), padding=1))
             for pool in (False, True):
@@ -86,11 +86,12 @@ def test_every_transposed_conv(base_model, dev):
         if not key.endswith(".up"):
             continue
         cin = sd[key + ".weight"].shape[0]
-        x = torch.randn((2, cin, 24, 40), generator=g)
-        ref = F.conv_transpose2d(util.bf16_round(x).to(dev), util.bf16_round(sd[key + ".weight"]).to(dev),
-                                 sd[key + ".bias"].to(dev), stride=2)
-        got = util.nhwc_to_nchw_f32(eng.debug_convt2x2(key, util.nchw_to_nhwc_bf16(x).to(dev)))
-        assert util.rel_err(got, ref) < 6e-3, key
+        for (n, h, w) in [(2, 24, 40), (3, 16, 8)]:  # (3, 16, 8): odd tile count (CTA-pair padding)
+            x = torch.randn((n, cin, h, w), generator=g)
+            ref = F.conv_transpose2d(util.bf16_round(x).to(dev), util.bf16_round(sd[key + ".weight"]).to(dev),
+                                     sd[key + ".bias"].to(dev), stride=2)
+            got = util.nhwc_to_nchw_f32(eng.debug_convt2x2(key, util.nchw_to_nhwc_bf16(x).to(dev)))
+            assert util.rel_err(got, ref) < 6e-3, (key, n, h, w)
 
 
 # ------------------------------------------------------------------ whole network
