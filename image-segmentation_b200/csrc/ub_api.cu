@@ -169,7 +169,7 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   UB_CUDA(ctx, cudaMemcpy(L.w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
   UB_CUDA(ctx, cudaMemcpy(L.bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
   L.h_bias = bias;
-  if (L.cout <= 64 && L.cin % 64 == 0) {
+  if (L.cout <= 64) {
     // kx-stacked operand (ub_conv_tc.cuh): GEMM column n3 = kx*cout + co of the ky-th box, K = cin
     std::vector<__nv_bfloat16> ks(packed.size());
     for (int t = 0; t < 9; ++t)
@@ -293,7 +293,8 @@ int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total,
 // first channel-group plane the layer reads; `src_cgs` / `out_cgs` are the planes per image of the two buffers.
 // Tile geometry of a layer: the thin 3x3 layers run kx-stacked (32-pixel-wide tiles, 16 when the pool is fused).
 int pick_tw(const ub_ctx* ctx, const GemmLayer& L, int mode) {
-  if (ctx->no_kxs || !L.w_kxs || L.ksize != 3 || mode == ub::EPI_HEAD || mode == ub::EPI_CONVT) return 8;
+  if (ctx->no_kxs || !L.w_kxs || L.ksize != 3 || mode == ub::EPI_CONVT) return 8;
+  if (L.bk == 32 && mode != ub::EPI_HEAD) return 8;  // Cin = 32: only the head layer gains (enc1.conv.0 is write-bound)
   return mode == ub::EPI_POOL ? 16 : 32;
 }
 
@@ -307,6 +308,7 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   // CTA pairs (cta_group::2) for the wide layers whose weights cannot stay resident in shared memory
   const size_t w_tile_bytes = static_cast<size_t>(L.ksize) * L.ksize * L.cin * L.block_n * 2;
   const bool resident = w_tile_bytes + 2 * 24576 <= 220 * 1024;  // mirrors choose_pipeline's weight-stationary test
+  { const char* d = getenv("UB_DBG"); cp->dbg = d ? atoi(d) : 0; }
   cp->cg2 = (!ctx->no_cg2 && tw == 8 && L.bk == 64 && L.block_n >= 128 && mode != ub::EPI_HEAD && mode != ub::EPI_CONVT && !resident) ? 1 : 0;
   if (ub::is_kxs(tw)) {
     if ((rc = make_tm_w(ctx, &cp->tmB, L.w_kxs, L.cin, 9 * L.cout, 3 * L.cout, L.bk))) return rc;
@@ -369,7 +371,7 @@ int launch_kernel(ub_ctx* ctx, const ConvParams& cp, int grid, int smem, cudaStr
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(ub::conv_threads(N, TW));
+  cfg.blockDim = dim3(ub::conv_threads(N, TW, KS));
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
@@ -448,8 +450,11 @@ int launch_gemm(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStre
 }
 
 int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStream_t st) {
-  if (cp.mode == ub::EPI_HEAD && block_n != 32) return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs 32 channels");
+  if (cp.mode == ub::EPI_HEAD && cp.cout != 32) return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs 32 channels");
   if (ub::is_kxs(cp.tw)) {  // thin 3x3 layers, N = 3 * cout
+    if (bk == 32 && cp.tw == 32 && cp.cout == 64) return launch_inst<192, 32, 3, 32>(ctx, cp, st);
+    if (bk == 32 && cp.tw == 32 && cp.cout == 32) return launch_inst<96, 32, 3, 32>(ctx, cp, st);
+    if (bk != 64) return fail(ctx, UB_ERR_UNSUPPORTED, "no kx-stacked kernel for BK=%d tw=%d", bk, cp.tw);
     if (cp.tw == 32 && cp.cout == 64) return launch_inst<192, 64, 3, 32>(ctx, cp, st);
     if (cp.tw == 32 && cp.cout == 32) return launch_inst<96, 64, 3, 32>(ctx, cp, st);
     if (cp.tw == 16 && cp.cout == 64) return launch_inst<192, 64, 3, 16>(ctx, cp, st);

@@ -56,8 +56,11 @@ __host__ __device__ constexpr int tile_rows(int tw) { return kTileM / tw; }
 __host__ __device__ constexpr int tile_xstep(int tw) { return is_kxs(tw) ? tw - 2 : tw; }  // output columns per tile
 // epilogue groups of 4 warps: the thin layers (N <= 64) have short main loops and long per-pixel epilogues
 // (latency-bound single warps), so they get 4 groups; the wide ones have 2 accumulators anyway
-__host__ __device__ constexpr int epi_groups(int block_n, int tw) { return is_kxs(tw) ? 2 : (block_n <= 32 ? 4 : 2); }
-__host__ __device__ constexpr int conv_threads(int block_n, int tw) { return 128 + 128 * epi_groups(block_n, tw); }
+__host__ __device__ constexpr int epi_groups(int block_n, int tw, int ksize) {
+  // never more groups than TMEM accumulators (a group may only be one barrier phase ahead): N = 256 has 2
+  return (void)ksize, is_kxs(tw) ? (block_n <= 96 ? 4 : 2) : (block_n <= 32 ? 4 : 2);
+}
+__host__ __device__ constexpr int conv_threads(int block_n, int tw, int ksize) { return 128 + 128 * epi_groups(block_n, tw, ksize); }
 
 struct ConvParams {
   CUtensorMap tmA;  // activations: dims {8*W, H, Cin/8, B}, box {8*PXW, ROWS_IN, BK/8, 1} (ConvCfg)
@@ -90,6 +93,7 @@ struct ConvParams {
   uint8_t* pred_out;       // [B,H,W] or null
   float* logits_out;       // [B,C,H,W] or null
   // pipeline shape chosen by the host (ub_api.cu: choose_pipeline)
+  int dbg; // UB_DBG bit mask (experiments only): 1 = epilogue only drains, 2 = no MMAs issued
   int cg2; // 1 = CTA-pair kernel (host: tmB box holds N/2 rows, even grid, cluster launch)
   int tw;  // tile width chosen by the host (8 standard, 16/32 kx-stacked); the kernel has it as a template parameter
   int sa;  // A stages (activation boxes)
@@ -182,17 +186,18 @@ __device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
 }
 
 template <int BLOCK_N, int BK, int KSIZE, bool WS, int TW, bool CG2 = false>
-__global__ void __launch_bounds__(conv_threads(BLOCK_N, TW), 1)
+__global__ void __launch_bounds__(conv_threads(BLOCK_N, TW, KSIZE), 1)
 conv_tc_kernel(const __grid_constant__ ConvParams p) {
   using Cfg = ConvCfg<BLOCK_N, BK, KSIZE, TW, CG2>;
   static_assert(!(CG2 && WS), "CTA pairs stream their weights");
+  static_assert(epi_groups(BLOCK_N, TW, KSIZE) <= Cfg::ACC, "an epilogue group per accumulator at most");
   constexpr bool KXS = Cfg::KXS;
   constexpr int TAPS = Cfg::TAPS;
   constexpr int ACC = Cfg::ACC;
   constexpr int kTileRows = Cfg::TH;
   constexpr int kXStep = tile_xstep(TW);
-  constexpr int kEpiGroups = epi_groups(BLOCK_N, TW);
-  constexpr int kConvThreads = conv_threads(BLOCK_N, TW);
+  constexpr int kEpiGroups = epi_groups(BLOCK_N, TW, KSIZE);
+  constexpr int kConvThreads = conv_threads(BLOCK_N, TW, KSIZE);
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // pad to 1024 B with pointer arithmetic on the __shared__ array (keeps the address space known to
   // the compiler: LDS/STS/ATOMS instead of generic accesses)
@@ -384,6 +389,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
           if (leader) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
+              if (p.dbg & 2) continue;
               const uint32_t al = a_tap + k * A_KSTEP_U, bl = b_lo + 2 * k;
               if (tap == 0 && k == 0) {
                 if (c == 0) mma(std::false_type{}, d_tmem, al, a_hi, bl, b_hi);
