@@ -63,6 +63,30 @@ class RobustnessEvaluator:
         self.images.copy_(images_u8[self.i0:self.i1], non_blocking=True)
         self.masks.copy_(masks_u8[self.i0:self.i1], non_blocking=True)
 
+    def upload_async(self, images_u8: torch.Tensor, masks_u8: torch.Tensor):
+        """Double-buffered upload: copies this rank's slice of the NEXT evaluation set into the back buffers on a
+        side stream while the current level computes.  `swap()` makes them current (and orders the compute stream
+        after the copy).  Host tensors should be pinned."""
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream(self.device)
+            self._back = (torch.empty_like(self.images), torch.empty_like(self.masks))
+            self._copy_done = torch.cuda.Event()
+            self._front_free = torch.cuda.Event()
+            self._front_free.record(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self._copy_stream):
+            # the back buffers were the front buffers two swaps ago: their last reader has been recorded
+            self._copy_stream.wait_event(self._front_free)
+            self._back[0].copy_(images_u8[self.i0:self.i1], non_blocking=True)
+            self._back[1].copy_(masks_u8[self.i0:self.i1], non_blocking=True)
+            self._copy_done.record(self._copy_stream)
+
+    def swap(self):
+        """Make the buffers filled by `upload_async` the current evaluation set."""
+        cur = torch.cuda.current_stream(self.device)
+        self._front_free.record(cur)           # everything launched so far may still read the old front buffers
+        cur.wait_event(self._copy_done)
+        (self.images, self.masks), self._back = self._back, (self.images, self.masks)
+
     def local_aux(self, perturbation: Optional[Perturbation]):
         """Parity mode hands aux for the whole dataset; keep this rank's rows."""
         if perturbation is None or perturbation.aux is None:

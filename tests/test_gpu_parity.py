@@ -268,3 +268,26 @@ def test_full_size_properties(trained, dev):
     b = eng.eval_batches(di, dm, P.u8_noise(10, seed=5), 8, want_perturbed=True)["perturbed"]
     d = (b - x)[(x > 0.2) & (x < 0.8)] * 255
     assert abs(float(d.mean())) < 0.05 and abs(float(d.std()) - 10.0) < 0.2
+
+
+def test_double_buffered_upload_matches_plain(trained, dev):
+    """`upload_async` + `swap` (H2D on a side stream, overlapped with the previous level) must give the
+    counts of a plain upload of the same set, for alternating evaluation sets."""
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.evaluator import RobustnessEvaluator
+    m, sd = trained
+    sets = [synthetic.make_dataset(24, 64, 64, seed=s) for s in (3, 4)]
+    sets = [(a.pin_memory(), b.pin_memory()) for a, b in sets]
+    ev = RobustnessEvaluator(m, sets[0][0], sets[0][1], 8, device=dev, rank=0, world_size=1)
+    want = []
+    for a, b in sets:
+        ev.upload(a, b)
+        want.append(ev.run_level(None, reduce=False)[0].clone())
+    assert not torch.equal(want[0], want[1])
+    ev.upload_async(*sets[0])
+    for i in range(4):
+        ev.swap()
+        if i + 1 < 4:
+            ev.upload_async(*sets[(i + 1) % 2])
+        got = ev.run_level(None, reduce=False)[0].cpu()
+        assert torch.equal(got, want[i % 2].cpu()), i
