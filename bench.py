@@ -136,7 +136,33 @@ def cpu_time_sample(sd, images, masks, levels, n_sample, reps):
     return n_sample * reps / dt, cores, dt
 
 
+LARGE = False            # --workload large512: BASELINE.json configs[2] (LargeUNet, 512x512, 64 images per GPU)
+
+
+def use_large_workload(world):
+    """Secondary workload: LargeUNet @512^2, 64 images per GPU per step, no perturbation
+    (forward + metrics).  Not the headline; the default run is unchanged."""
+    global LARGE, N_IMAGES, REF_BATCH, H, W, GFLOP_PER_IMAGE, GEMM_GFLOP_PER_IMAGE
+    LARGE = True
+    N_IMAGES, REF_BATCH, H, W = 64 * world, 64, 512, 512
+    GFLOP_PER_IMAGE = 226.123                                       # SURVEY 8d config 3
+    GEMM_GFLOP_PER_IMAGE = 226.123 - 2 * (H * W * 3 * 32 * 2) / 1e9  # minus the two 1x1 convs
+
+
+def net_class():
+    from image_segmentation_b200.models.UNet import LargeUNet, UNet
+    return LargeUNet if LARGE else UNet
+
+
 def base_line(args, world):
+    if LARGE:
+        return {"metric": "LargeUNet 512x512 forward+metrics images/s", "unit": "images/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "data": "synthetic",
+                "config": {"workload": "LargeUNet random-init (seed 42), 64 synthetic 512x512 RGB images per GPU per step, "
+                                       "3 classes, forward + argmax + confusion counts, no perturbation",
+                           "images_per_step": N_IMAGES, "ref_batch": REF_BATCH,
+                           "l2": "activations_exceed_l2 (every layer's tensors are > 126 MB at 64 images)"}}
     return {"metric": "UNet 256x256 robustness-eval images/s", "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "data": "synthetic",
             "config": {"workload": "robustness_evaluation sweep levels (8 perturbations x 10 levels, visited round-robin) over "
@@ -148,10 +174,9 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     from image_segmentation_b200 import synthetic
-    from image_segmentation_b200.models.UNet import UNet
     torch.manual_seed(42)
-    sd = UNet().eval().state_dict()
-    n_sample = 16
+    sd = net_class()().eval().state_dict()
+    n_sample = 4 if LARGE else 16
     images, masks = synthetic.make_dataset(n_sample, H, W, seed=99)
     levels = level_list()
     cores = os.cpu_count() or 1
@@ -164,7 +189,7 @@ def run_reference(args, rank, world):
     dt = time.perf_counter() - t0
     v = n_sample * args.steps / dt
     line = base_line(args, world)
-    sample = f"each step = {n_sample} of the 3,680 images of one sweep level (oracle port of the reference path, torch CPU fp32)"
+    sample = f"each step = {n_sample} of the {N_IMAGES:,} images of one step (oracle port of the reference path, torch CPU fp32)"
     line.update({"impl": "reference", "value": v, "ms_per_step": dt / args.steps * 1e3, "dtype": "f32",
                  "cpu_baseline": {"value": v, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
                  "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -177,23 +202,26 @@ def run_gpu(args, rank, world, local_rank):
     import torch.distributed as dist
     from image_segmentation_b200 import synthetic
     from image_segmentation_b200.evaluator import RobustnessEvaluator
-    from image_segmentation_b200.models.UNet import UNet
     from image_segmentation_b200.scripts.robustness_evaluation import make_spec
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     torch.manual_seed(42)
-    model = UNet().eval()
+    model = net_class()().eval()
     sd_cpu = {k: v.clone() for k, v in model.state_dict().items()}
     model = model.to(dev)
-    base_i, base_m = synthetic.make_dataset(230, H, W, seed=99)
-    images = base_i.repeat(16, 1, 1, 1)[:N_IMAGES].contiguous().pin_memory()   # values do not affect throughput
-    masks = base_m.repeat(16, 1, 1)[:N_IMAGES].contiguous().pin_memory()
+    n_base = min(N_IMAGES, 64 if LARGE else 230)
+    base_i, base_m = synthetic.make_dataset(n_base, H, W, seed=99)
+    reps = -(-N_IMAGES // n_base)
+    images = base_i.repeat(reps, 1, 1, 1)[:N_IMAGES].contiguous().pin_memory()   # values do not affect throughput
+    masks = base_m.repeat(reps, 1, 1)[:N_IMAGES].contiguous().pin_memory()
     ev = RobustnessEvaluator(model, images, masks, REF_BATCH, dev, rank=rank, world_size=world,
                              max_microbatch=args.microbatch)
     eng = ev.engine
     levels = level_list()
 
     def step(i):
+        if LARGE:
+            return ev.run_level(None)
         name, lv = levels[i % len(levels)]
         return ev.run_level(make_spec(name, lv, H * W, seed=i))
 
@@ -274,9 +302,10 @@ def run_gpu(args, rank, world, local_rank):
                  "whole_net_tflops": value * GFLOP_PER_IMAGE / 1e3, "microbatch": eng.max_microbatch})
     if world == 1 and not args.no_cpu:
         lv = [("contrast_increase", 1.1), ("gaussian_blur", 5), ("gaussian_noise", 10), ("occlusion", 25)]
-        v, cores, dt = cpu_time_sample(sd_cpu, images[:64], masks[:64], lv, 64, 4)
+        n_cpu = 8 if LARGE else 64
+        v, cores, dt = cpu_time_sample(sd_cpu, images[:n_cpu], masks[:n_cpu], lv, n_cpu, 4)
         line["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
-                                "sample": f"4 levels (contrast 1.1, blur 5, noise 10, occlusion 25) x 64 images "
+                                "sample": f"4 levels (contrast 1.1, blur 5, noise 10, occlusion 25) x {n_cpu} images "
                                           f"through the oracle port, {dt:.1f} s"}
     else:
         line["cpu_baseline"] = None
@@ -292,11 +321,15 @@ def main():
     ap.add_argument("--microbatch", type=int, default=None)
     ap.add_argument("--layers", action="store_true", help="print the per-layer GEMM times to stderr")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--workload", default="unet256", choices=["unet256", "large512"],
+                    help="unet256 = the headline (BASELINE.json configs[1]); large512 = configs[2], secondary")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.workload == "large512":
+        use_large_workload(world)
     if args.impl == "reference":
         run_reference(args, rank, world)
         return

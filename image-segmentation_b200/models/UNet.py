@@ -37,14 +37,20 @@ class _B200Net(nn.Module):
             if self._engine is not None:
                 self._engine.close()
             self._engine = runtime.new_engine(dev, self._arch, 3, self._n_classes, mb)
-            self._engine.load_state_dict(self.state_dict())
+            self._engine.load_state_dict({self._flat_name(k): v for k, v in self.state_dict().items()})
             self._engine.set_layer_couts(self.layer_couts())
             self._engine_key = key
         return self._engine
 
+    @staticmethod
+    def _flat_name(key: str) -> str:
+        """state_dict key -> the library's layer name (the UNet key); identity for UNet/LargeUNet."""
+        return key
+
     def layer_couts(self):
         out = {}
         for name, m in self.named_modules():
+            name = self._flat_name(name)
             if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)) and name not in ("input", "out"):
                 out[name] = m.out_channels
         return out

@@ -9,6 +9,9 @@ through oracle/refload.py).  Run in the build container only:  python -m oracle.
                    kornia) on a [2,3,24,40] batch, 3 levels per family.
   unet_small.npz   reference UNet (seed 42 + randomised BatchNorm) logits on a [2,3,32,64] input, the
                    reference IoU / PixelAccuracy on them, and a checksum of the seeded state_dict.
+  segmodel_small.npz  reference SegmentationModel(Encoder(), SegmentationDecoderSkip(3)) (models/pre_trained.py:47-56,
+                   models/autoencoder.py:5-26), seed 42 + randomised BatchNorm: state_dict key list, checksums and
+                   logits on the same [2,3,32,64] input.
 """
 import hashlib
 import os
@@ -143,12 +146,35 @@ def golden_unet(ns):
     return out
 
 
+def golden_segmodel(ns):
+    from image_segmentation_b200 import synthetic
+    torch.manual_seed(42)
+    m = ns.pre_trained.SegmentationModel(ns.autoencoder.Encoder(), ns.pre_trained.SegmentationDecoderSkip(3)).eval()
+    base_sum = state_checksum(m.state_dict())
+    sd = synthetic.randomize_batchnorm(m.state_dict(), seed=7)
+    m.load_state_dict(sd)
+    imgs, masks = synthetic.make_dataset(2, 32, 64, seed=5)
+    x = synthetic.to_float_nchw(imgs)
+    with torch.no_grad():
+        logits = m(x)
+        sd["decoder.out.bias"] = sd["decoder.out.bias"] - logits.mean(dim=(0, 2, 3))
+        m.load_state_dict(sd)
+        logits = m(x)
+    keys = list(m.state_dict().keys())
+    out = dict(images_u8=imgs.numpy(), logits=logits.numpy(), out_bias=sd["decoder.out.bias"].numpy(),
+               keys=np.array(keys), shapes=np.array([str(tuple(m.state_dict()[k].shape)) for k in keys]),
+               seed42_state_sha256=np.array(base_sum), final_state_sha256=np.array(state_checksum(sd)))
+    np.savez_compressed(os.path.join(OUT, "segmodel_small.npz"), **out)
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = refload.load()
     golden_perturb_u8(ns)
     golden_perturb_f(ns)
     golden_unet(ns)
+    golden_segmodel(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -66,6 +66,8 @@ def load():
     ns.blocks = importlib.import_module("models.processing_blocks")
     ns.losses = importlib.import_module("models.losses")
     ns.perturbations = importlib.import_module("customDatasets.perturbations")
+    ns.autoencoder = importlib.import_module("models.autoencoder")
+    ns.pre_trained = importlib.import_module("models.pre_trained")
     ns.UNet = ns.UNet_mod.UNet
     ns.LargeUNet = ns.UNet_mod.LargeUNet
     return ns

@@ -125,18 +125,44 @@ def test_random_init_noise_floor(base_model, dev):
     assert util.rel_err(got, ref) < 3e-2
 
 
-def test_large_unet_forward(dev):
+@pytest.mark.parametrize("n,hw", [(2, 128), (1, 512)])
+def test_large_unet_forward(dev, n, hw):
     from image_segmentation_b200 import synthetic
     from image_segmentation_b200.models.UNet import LargeUNet
     torch.manual_seed(1)
     m = LargeUNet().eval()
     sd = synthetic.randomize_batchnorm(m.state_dict(), seed=8)
     m.load_state_dict(sd)
-    imgs, _ = synthetic.make_dataset(2, 128, 128, seed=7)
+    imgs, _ = synthetic.make_dataset(n, hw, hw, seed=7)
     x = synthetic.to_float_nchw(imgs)
     ref = unet_oracle.forward({k: v.to(dev) for k, v in sd.items()}, x.to(dev)).cpu()
     got = m.to(dev)(x.to(dev)).cpu()
+    print(f"LargeUNet {n}x{hw}x{hw}: logits rel err {util.rel_err(got, ref):.3e}")
     assert util.rel_err(got, ref) < 3e-2
+
+
+def test_segmentation_model_matches_reference_golden_and_unet(dev):
+    """Config 4: SegmentationModel(Encoder, SegmentationDecoderSkip) = the UNet's arithmetic behind a different
+    parameter tree.  Logits vs the reference's own (golden, fp32 CPU) within the bf16 tolerance, and
+    bit-identical to our UNet carrying the same weights."""
+    import os
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.autoencoder import Encoder
+    from image_segmentation_b200.models.pre_trained import SegmentationDecoderSkip, SegmentationModel
+    from image_segmentation_b200.models.UNet import UNet
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "segmodel_small.npz"))
+    torch.manual_seed(42)
+    m = SegmentationModel(Encoder(), SegmentationDecoderSkip(3)).eval()
+    sd = synthetic.randomize_batchnorm(m.state_dict(), seed=7)
+    sd["decoder.out.bias"] = torch.from_numpy(g["out_bias"])
+    m.load_state_dict(sd)
+    x = synthetic.to_float_nchw(torch.from_numpy(g["images_u8"])).to(dev)
+    got = m.to(dev)(x).cpu()
+    ref = torch.from_numpy(g["logits"])
+    assert util.rel_err(got, ref) < 1e-2
+    u = UNet().eval()
+    u.load_state_dict({m._flat_name(k): v for k, v in sd.items()})
+    assert torch.equal(u.to(dev)(x).cpu(), got)
 
 
 # ------------------------------------------------------------------ head: argmax + confusion counts

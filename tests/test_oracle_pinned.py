@@ -102,6 +102,32 @@ def test_unet_and_metrics_match_golden():
     assert float(mo.pixel_accuracy_direct(ref, masks.long())) == float(g["pixel_accuracy"])
 
 
+def test_segmentation_model_tree_and_oracle_against_reference_golden():
+    """SegmentationModel(Encoder, SegmentationDecoderSkip) (reference models/pre_trained.py:47-56): same key
+    list, shapes and seeded initialisation as the reference's, and the oracle network on the prefix-stripped
+    state_dict reproduces the reference's logits."""
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.autoencoder import Encoder
+    from image_segmentation_b200.models.pre_trained import SegmentationDecoderSkip, SegmentationModel
+    from oracle.make_golden import state_checksum
+    g = np.load(os.path.join(GOLD, "segmodel_small.npz"))
+    torch.manual_seed(42)
+    m = SegmentationModel(Encoder(), SegmentationDecoderSkip(3))
+    sd0 = m.state_dict()
+    assert list(sd0.keys()) == [str(k) for k in g["keys"]]
+    assert [str(tuple(v.shape)) for v in sd0.values()] == [str(s) for s in g["shapes"]]
+    assert state_checksum(sd0) == str(g["seed42_state_sha256"])
+    sd = synthetic.randomize_batchnorm(sd0, seed=7)
+    sd["decoder.out.bias"] = torch.from_numpy(g["out_bias"])
+    assert state_checksum(sd) == str(g["final_state_sha256"])
+    flat = {m._flat_name(k): v for k, v in sd.items()}
+    logits = unet_oracle.forward(flat, synthetic.to_float_nchw(torch.from_numpy(g["images_u8"])))
+    ref = torch.from_numpy(g["logits"])
+    assert float((logits - ref).abs().max()) <= 2e-5 * float(ref.abs().max())
+    with pytest.raises(RuntimeError):
+        m.encoder(torch.zeros(1, 3, 32, 32))  # parameter container, no per-half fallback
+
+
 def test_dice_restatement_is_self_consistent():
     """Dice is PARITY UNPINNED (smp absent): only internal consistency can be checked."""
     g = torch.Generator().manual_seed(0)
