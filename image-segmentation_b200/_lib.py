@@ -38,6 +38,8 @@ SIGNATURES = {
                                 c_void_p]),
     "ub_perturb_images": (c_int, [c_void_p, ctypes.POINTER(ub_perturb), c_void_p, c_int, c_void_p, c_int, c_int,
                                   c_int, c_void_p, c_void_p]),
+    "ub_decode_masks": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
+    "ub_pack_dataset": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "ub_metrics": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                            c_void_p, c_void_p]),
     "ub_debug_conv3x3": (c_int, [c_void_p, c_char_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),

@@ -909,6 +909,36 @@ int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int 
   return UB_OK;
 }
 
+int ub_decode_masks(ub_ctx* ctx, const uint8_t* raw_masks, uint8_t* masks_out, int n, int64_t pixels_per_image,
+                    void* stream) {
+  if (!ctx) return UB_ERR_INVALID;
+  if (n == 0) return UB_OK;  // empty set: nothing to read, pointers may be NULL
+  if (!raw_masks || !masks_out || n < 0 || pixels_per_image <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ub::decode_masks_kernel<<<n, 1024, 0, st>>>(raw_masks, masks_out, static_cast<size_t>(pixels_per_image));
+  UB_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return UB_OK;
+}
+
+int ub_pack_dataset(ub_ctx* ctx, const float* images_nchw, const int64_t* masks_i64, int n, int h, int w,
+                    uint8_t* images_u8_nhwc, uint8_t* masks_u8, void* stream) {
+  if (!ctx) return UB_ERR_INVALID;
+  if (n == 0) return UB_OK;
+  if (n < 0 || h <= 0 || w <= 0 || (images_nchw && !images_u8_nhwc) || (masks_i64 && !masks_u8) ||
+      (!images_nchw && !masks_i64))
+    return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t hw = static_cast<size_t>(h) * w;
+  ub::pack_dataset_kernel<<<blocks_for(hw * n, 256), 256, 0, st>>>(
+      images_nchw, reinterpret_cast<const long long*>(masks_i64), n, hw, images_u8_nhwc, masks_u8);
+  UB_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return UB_OK;
+}
+
 int ub_metrics(ub_ctx* ctx, const float* logits_nchw, const void* targets, int target_format, int n, int n_classes,
                int h, int w, int ref_batch, int64_t* cm, double* dice_sums, void* stream) {
   if (!ctx) return UB_ERR_INVALID;

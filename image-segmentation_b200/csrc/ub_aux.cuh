@@ -138,4 +138,69 @@ __global__ void dice_tsum_kernel(const unsigned long long* cm, double* dice, int
   dice[static_cast<size_t>(i) * 3 + 2] = static_cast<double>(s);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Dataset rows on the device (customDatasets/datasets.py:92-134, `_deserialize_datapoint`).
+//
+// decode_masks_kernel: the raw trimap bytes of the Oxford-IIIT-Pet rows (38 = cat, 75 = dog, 255 = uncertain
+// border, anything else = background) -> class ids.  The rule is per IMAGE (datasets.py:122-131): if the image
+// has any cat pixel, out = 1 where raw is 38 or 255; otherwise out = 2 where raw is 75 or 255; 0 elsewhere.
+// One CTA per image: pass 1 = block-wide "any 38" (16-byte loads, __syncthreads_or), pass 2 = remap (the re-read
+// of the 64 KB image hits L1/L2).  Algorithmic bytes: 2 per pixel (1 read + 1 write).
+__device__ __forceinline__ uint32_t bytes_eq(uint32_t v, uint32_t pat) {   // 0x01 in every byte lane where v == pat
+  return __vcmpeq4(v, pat) & 0x01010101u;
+}
+
+__global__ void decode_masks_kernel(const uint8_t* __restrict__ raw, uint8_t* __restrict__ out, size_t px) {
+  const uint8_t* src = raw + static_cast<size_t>(blockIdx.x) * px;
+  uint8_t* dst = out + static_cast<size_t>(blockIdx.x) * px;
+  const bool vec = (px % 16 == 0) && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) % 16 == 0);
+  int cat = 0;
+  if (vec) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    for (size_t i = threadIdx.x; i < px / 16; i += blockDim.x) {
+      const uint4 v = s4[i];
+      cat |= (__vcmpeq4(v.x, 0x26262626u) | __vcmpeq4(v.y, 0x26262626u) | __vcmpeq4(v.z, 0x26262626u) |
+              __vcmpeq4(v.w, 0x26262626u)) != 0u;
+    }
+  } else {
+    for (size_t i = threadIdx.x; i < px; i += blockDim.x) cat |= src[i] == 38;
+  }
+  cat = __syncthreads_or(cat);
+  const uint32_t body = cat ? 0x26262626u : 0x4B4B4B4Bu;   // 38 : 75
+  const uint32_t mul = cat ? 1u : 2u;
+  auto remap = [&](uint32_t v) { return (bytes_eq(v, body) | bytes_eq(v, 0xFFFFFFFFu)) * mul; };
+  if (vec) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    for (size_t i = threadIdx.x; i < px / 16; i += blockDim.x) {
+      const uint4 v = s4[i];
+      d4[i] = make_uint4(remap(v.x), remap(v.y), remap(v.z), remap(v.w));
+    }
+  } else {
+    for (size_t i = threadIdx.x; i < px; i += blockDim.x) {
+      const uint8_t v = src[i];
+      dst[i] = static_cast<uint8_t>(((v == (cat ? 38 : 75)) || v == 255) ? mul : 0u);
+    }
+  }
+}
+
+// pack_dataset_kernel: the `.pt` cache / `__getitem__` form (fp32 [n,3,H,W] in [0,1] = k/255, int64 [n,H,W])
+// back to the resident evaluation form (uint8 [n,H,W,3], uint8 [n,H,W]); datasets.py:64-86, :115.
+// round(x*255) recovers k exactly for every k/255 (|fl32(k/255)*255 - k| < 2^-15).  One thread per pixel.
+__global__ void pack_dataset_kernel(const float* __restrict__ img, const long long* __restrict__ mask, int n,
+                                    size_t hw, uint8_t* __restrict__ img_u8, uint8_t* __restrict__ mask_u8) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<size_t>(n) * hw) return;
+  const size_t b = i / hw, p = i - b * hw;
+  if (img) {
+    const float* s = img + b * 3 * hw + p;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float v = fminf(fmaxf(s[c * hw], 0.0f), 1.0f);
+      img_u8[i * 3 + c] = static_cast<uint8_t>(__float2int_rn(v * 255.0f));
+    }
+  }
+  if (mask) mask_u8[i] = static_cast<uint8_t>(mask[i]);
+}
+
 }  // namespace ub

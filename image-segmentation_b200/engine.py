@@ -222,6 +222,35 @@ class Engine:
                                         _ptr(dice), _stream(self.device)), "ub_metrics")
         return cm, dice
 
+    def decode_masks(self, raw: torch.Tensor) -> torch.Tensor:
+        """Raw trimap bytes uint8 [n, ...] (38 cat / 75 dog / 255 border) -> class ids uint8, same shape; the
+        per-image rule of customDatasets/datasets.py:118-131."""
+        if raw.dtype != torch.uint8 or raw.dim() < 2:
+            raise ValueError("decode_masks expects a uint8 tensor [n, ...]")
+        raw = raw.to(self.device).contiguous()
+        out = torch.empty_like(raw)
+        n = raw.shape[0]
+        px = raw[0].numel() if n else 1
+        self._check(self.lib.ub_decode_masks(self.h, _ptr(raw), _ptr(out), n, px, _stream(self.device)),
+                    "ub_decode_masks")
+        return out
+
+    def pack_dataset(self, images: Optional[torch.Tensor], masks: Optional[torch.Tensor]):
+        """(fp32 [n,3,H,W] in [0,1], int64 [n,H,W]) -> (uint8 [n,H,W,3], uint8 [n,H,W]) on the device; either may
+        be None.  Inverse of the reference's `/255` (datasets.py:115) for the k/255 values it yields."""
+        src = images if images is not None else masks
+        n, h, w = src.shape[0], src.shape[-2], src.shape[-1]
+        img_u8 = mask_u8 = None
+        if images is not None:
+            images = images.to(self.device, torch.float32).contiguous()
+            img_u8 = torch.empty((n, h, w, 3), device=self.device, dtype=torch.uint8)
+        if masks is not None:
+            masks = masks.to(self.device, torch.int64).contiguous()
+            mask_u8 = torch.empty((n, h, w), device=self.device, dtype=torch.uint8)
+        self._check(self.lib.ub_pack_dataset(self.h, _ptr(images), _ptr(masks), n, h, w, _ptr(img_u8), _ptr(mask_u8),
+                                             _stream(self.device)), "ub_pack_dataset")
+        return img_u8, mask_u8
+
     @staticmethod
     def _to_blocked(x_nhwc: torch.Tensor) -> torch.Tensor:
         """NHWC -> the library's activation layout [n][C/8][h][w][8] (channel groups of 8 = 16 bytes)."""

@@ -40,6 +40,10 @@ class TestWrapper:
 
     # ---- dataset made device-resident once (uint8 when the items are exact k/255, as the reference's are)
     def evaluator(self) -> RobustnessEvaluator:
+        if self._evaluator is None and hasattr(self.test_dataset, "resident_tensors"):
+            # customDatasets.datasets.DeviceResidentDataset: rows were decoded on the device already
+            u8, t = self.test_dataset.resident_tensors()
+            self._evaluator = RobustnessEvaluator(self.model, u8, t, self.batch_size, self.device)
         if self._evaluator is None:
             imgs, masks = [], []
             for x, t in DataLoader(self.test_dataset, batch_size=64, shuffle=False):

@@ -61,3 +61,22 @@ class SyntheticSegmentationDataset(torch.utils.data.Dataset):
 
     def __getitem__(self, i):
         return self.images_u8[i].permute(2, 0, 1).float() / 255.0, self.masks_u8[i].long()
+
+
+def make_raw_rows(n: int, h: int = 256, w: int = 256, seed: int = 99):
+    """Rows with the schema the reference reads from Oxford-IIIT-Pet-Augmented (customDatasets/datasets.py:107-110):
+    {'image': H*W*3 bytes (uint8 HWC), 'mask': H*W bytes (trimap: 38 = cat body, 75 = dog body, 255 = uncertain
+    border, 0 = background)}.  Even rows are cats, odd rows dogs; row 2 (if present) has no animal at all."""
+    images, cls = make_dataset(n, h, w, seed)
+    body = cls != 0
+    pad = F.max_pool2d(body.float().unsqueeze(1), 5, stride=1, padding=2).squeeze(1) > 0
+    core = -F.max_pool2d(-body.float().unsqueeze(1), 5, stride=1, padding=2).squeeze(1) > 0
+    rows = []
+    for i in range(n):
+        m = torch.zeros((h, w), dtype=torch.uint8)
+        m[pad[i]] = 255
+        m[core[i]] = 38 if i % 2 == 0 else 75
+        if i == 2:
+            m[m == 38] = 0
+        rows.append({"image": images[i].numpy().tobytes(), "mask": m.numpy().tobytes()})
+    return rows

@@ -115,6 +115,16 @@ int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int im
 int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,
                       const void* aux, int n, int h, int w, float* out_nchw, void* stream);
 
+/* Dataset rows on the device (replaces the per-sample CPU work of customDatasets/datasets.py:92-160).
+ * ub_decode_masks: raw trimap bytes [n, pixels] (38 cat / 75 dog / 255 border) -> class ids {0,1,2} with the
+ *   reference's per-image rule (`_deserialize_datapoint`, datasets.py:118-131).  In place is allowed.
+ * ub_pack_dataset: the `.pt` cache / `__getitem__` form (fp32 [n,3,H,W] = k/255, int64 [n,H,W]; datasets.py:64-86,
+ *   :115) -> the resident evaluation form (uint8 [n,H,W,3], uint8 [n,H,W]).  Either pair may be NULL. */
+int ub_decode_masks(ub_ctx* ctx, const uint8_t* raw_masks, uint8_t* masks_out, int n, int64_t pixels_per_image,
+                    void* stream);
+int ub_pack_dataset(ub_ctx* ctx, const float* images_nchw, const int64_t* masks_i64, int n, int h, int w,
+                    uint8_t* images_u8_nhwc, uint8_t* masks_u8, void* stream);
+
 /* Metrics alone (models/losses.py:43-63,133-154 from materialised logits): fills cm / dice_sums as above. */
 int ub_metrics(ub_ctx* ctx, const float* logits_nchw, const void* targets, int target_format, int n,
                int n_classes, int h, int w, int ref_batch, int64_t* cm, double* dice_sums, void* stream);

@@ -9,6 +9,8 @@ through oracle/refload.py).  Run in the build container only:  python -m oracle.
                    kornia) on a [2,3,24,40] batch, 3 levels per family.
   unet_small.npz   reference UNet (seed 42 + randomised BatchNorm) logits on a [2,3,32,64] input, the
                    reference IoU / PixelAccuracy on them, and a checksum of the seeded state_dict.
+  dataset_rows.npz reference CustomImageDataset._deserialize_datapoint on 6 synthetic rows (trimap remap), masks +
+                   a checksum of the decoded fp32 images.
   segmodel_small.npz  reference SegmentationModel(Encoder(), SegmentationDecoderSkip(3)) (models/pre_trained.py:47-56,
                    models/autoencoder.py:5-26), seed 42 + randomised BatchNorm: state_dict key list, checksums and
                    logits on the same [2,3,32,64] input.
@@ -168,6 +170,27 @@ def golden_segmodel(ns):
     return out
 
 
+def golden_dataset_rows(ns):
+    """The reference's own `_deserialize_datapoint` (customDatasets/datasets.py:92-131), called unbound on 6
+    synthetic rows (the HF download its __init__ does is not possible here; the method only uses
+    `self._deserialize_numpy`)."""
+    from image_segmentation_b200 import synthetic
+    ds_mod = __import__("customDatasets.datasets", fromlist=["CustomImageDataset"])
+    cls = ds_mod.CustomImageDataset
+    obj = cls.__new__(cls)
+    rows = synthetic.make_raw_rows(6, 256, 256, seed=21)
+    masks, img_sha = [], hashlib.sha256()
+    for r in rows:
+        image, mask = cls._deserialize_datapoint(obj, r)
+        assert image.dtype == torch.float32 and tuple(image.shape) == (3, 256, 256)
+        img_sha.update(image.numpy().tobytes())
+        masks.append(mask.numpy().astype(np.uint8))
+    out = dict(masks=np.stack(masks), images_sha256=np.array(img_sha.hexdigest()),
+               raw_sha256=np.array(hashlib.sha256(b"".join(r["image"] + r["mask"] for r in rows)).hexdigest()))
+    np.savez_compressed(os.path.join(OUT, "dataset_rows.npz"), **out)
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = refload.load()
@@ -175,6 +198,7 @@ def main():
     golden_perturb_f(ns)
     golden_unet(ns)
     golden_segmodel(ns)
+    golden_dataset_rows(ns)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

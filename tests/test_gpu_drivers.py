@@ -114,3 +114,33 @@ def test_testwrapper_csvs(setup, monkeypatch):
     tw.test_contrast_change([1.0], False)  # append mode: header written once
     rows2 = list(csv.reader(open(d / "augmentation-results" / "contrast_decrease_results.csv")))
     assert len(rows2) == 4 and rows2[0][0] == "Augmentation"
+
+
+def test_testwrapper_on_device_resident_rows(setup, monkeypatch):
+    """TestWrapper fed by DeviceResidentDataset (rows decoded on the GPU) gives the confusion counts of the generic
+    loader path on the same decoded data."""
+    from image_segmentation_b200.customDatasets.datasets import DeviceResidentDataset
+    from image_segmentation_b200.models.model_wrappers import TestWrapper
+    from image_segmentation_b200.models.UNet import UNet
+    from image_segmentation_b200 import synthetic
+    from oracle import dataset_oracle as do
+    sd, path, d = setup
+    monkeypatch.chdir(d)
+    rows = synthetic.make_raw_rows(7, 256, 256, seed=4)
+
+    class HostRows(torch.utils.data.Dataset):          # what the reference's CPU __getitem__ yields
+        def __init__(self):
+            self.items = [do.deserialize_datapoint(r) for r in rows]
+
+        def __len__(self):
+            return len(self.items)
+
+        def __getitem__(self, i):
+            return torch.from_numpy(self.items[i][0]), torch.from_numpy(self.items[i][1])
+
+    a = TestWrapper(UNet(), test_dataset_class=lambda: DeviceResidentDataset.from_rows(rows, "cuda:0"),
+                    test_dataset_args={}, batch_size=4, model_load_location=path)
+    b = TestWrapper(UNet(), test_dataset_class=HostRows, test_dataset_args={}, batch_size=4, model_load_location=path)
+    cm_a = a.evaluator().run_level(None)[0].clone()
+    cm_b = b.evaluator().run_level(None)[0].clone()
+    assert cm_a.shape == (2, 3, 3) and torch.equal(cm_a, cm_b) and int(cm_a.sum()) == 7 * 256 * 256

@@ -317,3 +317,35 @@ def test_double_buffered_upload_matches_plain(trained, dev):
             ev.upload_async(*sets[(i + 1) % 2])
         got = ev.run_level(None, reduce=False)[0].cpu()
         assert torch.equal(got, want[i % 2].cpu()), i
+
+
+def test_device_resident_dataset_rows_bit_exact(dev):
+    """Raw rows -> device-resident (images u8, masks u8): bit-exact against the reference's decoding (golden) and
+    the oracle, item contract kept, `.pt`-cache form packs back to the same bytes, ragged pixel counts work."""
+    import os
+    from image_segmentation_b200 import runtime, synthetic
+    from image_segmentation_b200.customDatasets.datasets import DeviceResidentDataset
+    from oracle import dataset_oracle as do
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "dataset_rows.npz"))
+    rows = synthetic.make_raw_rows(6, 256, 256, seed=21)
+    ds = DeviceResidentDataset.from_rows(rows, dev)
+    imgs, masks = ds.resident_tensors()
+    assert np.array_equal(masks.cpu().numpy(), g["masks"])
+    want = [do.deserialize_datapoint(r) for r in rows]
+    for i in (0, 1, 2, 5):
+        x, t = ds[i]
+        assert x.dtype == torch.float32 and t.dtype == torch.int64 and x.shape == (3, 256, 256)
+        assert np.array_equal(x.cpu().numpy(), want[i][0]) and np.array_equal(t.cpu().numpy(), want[i][1])
+    assert len(DeviceResidentDataset(imgs, masks, augmentations_per_datapoint=2)) == 18
+    # the reference's cache form: list of (fp32 CHW, int64 mask)
+    cache = [(torch.from_numpy(a), torch.from_numpy(b)) for a, b in want]
+    ds2 = DeviceResidentDataset.from_cache(cache, dev, chunk=4)
+    assert torch.equal(ds2.images_u8, imgs) and torch.equal(ds2.masks_u8, masks)
+    # ragged size (pixel count not a multiple of 16, unaligned rows) and an empty set
+    gen = torch.Generator().manual_seed(0)
+    raw = torch.tensor([0, 38, 75, 255, 7], dtype=torch.uint8)[torch.randint(0, 5, (5, 37, 23), generator=gen)]
+    raw[3][raw[3] == 38] = 0
+    got = runtime.engine_for(dev).decode_masks(raw.to(dev)).cpu().numpy()
+    for i in range(5):
+        assert np.array_equal(got[i], do.decode_mask(raw[i].numpy()))
+    assert runtime.engine_for(dev).decode_masks(torch.empty((0, 8, 8), dtype=torch.uint8)).shape == (0, 8, 8)

@@ -128,6 +128,24 @@ def test_segmentation_model_tree_and_oracle_against_reference_golden():
         m.encoder(torch.zeros(1, 3, 32, 32))  # parameter container, no per-half fallback
 
 
+def test_dataset_row_decoding_against_reference_golden():
+    """oracle.dataset_oracle vs the reference's CustomImageDataset._deserialize_datapoint (datasets.py:107-131)."""
+    import hashlib
+    from image_segmentation_b200 import synthetic
+    from oracle import dataset_oracle as do
+    g = np.load(os.path.join(GOLD, "dataset_rows.npz"))
+    rows = synthetic.make_raw_rows(6, 256, 256, seed=21)
+    assert hashlib.sha256(b"".join(r["image"] + r["mask"] for r in rows)).hexdigest() == str(g["raw_sha256"])
+    sha = hashlib.sha256()
+    for i, r in enumerate(rows):
+        image, mask = do.deserialize_datapoint(r)
+        assert mask.dtype == np.int64 and np.array_equal(mask, g["masks"][i])
+        sha.update(image.tobytes())
+    assert sha.hexdigest() == str(g["images_sha256"])
+    kinds = [set(np.unique(m)) for m in g["masks"]]
+    assert kinds[0] == {0, 1} and kinds[1] == {0, 2} and kinds[2] == {0, 2}  # cat, dog, border-only row
+
+
 def test_dice_restatement_is_self_consistent():
     """Dice is PARITY UNPINNED (smp absent): only internal consistency can be checked."""
     g = torch.Generator().manual_seed(0)
