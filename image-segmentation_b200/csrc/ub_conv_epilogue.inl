@@ -210,9 +210,9 @@
       int oy = y, ox = x, oh = p.H, ow = p.W;
       bool writer = inb;
       if (p.mode == EPI_POOL) {
-        // MaxPool2d(2,2).  Standard tile: partners are lane^1 (x) and lane^8 (y).  Kx-stacked TW = 16 tile:
-        // outputs start at an even x in tile column 1, so pairs are (odd tx, tx+1) and rows are lane^16.
-        writer = KXS ? (inb && (tx & 1) && lane < 16) : (inb && ((lane & 9) == 0));
+        // MaxPool2d(2,2), H and W even.  Standard tile: partners are lane^1 (x) and lane^8 (y).  Kx-stacked TW = 16
+        // tile: outputs start at an even x in tile column 1, so pairs are (odd tx, tx+1) and rows are lane^16.
+        // (every lane of a window writes its share of the pooled pixel, see store_chunk)
         oy = y >> 1; ox = x >> 1; oh = p.H >> 1; ow = p.W >> 1;
       } else if (p.mode == EPI_CONVT) {
         oh = 2 * p.H; ow = 2 * p.W;
@@ -247,16 +247,30 @@
 #pragma unroll
         for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
         if (p.mode == EPI_POOL) {
+          // 2x2 max as a reduce-scatter over the four lanes of a pooling window: stage 1 trades HALF of the packed
+          // registers with the x-partner, stage 2 a quarter with the y-partner; every lane ends with one channel
+          // group (8 channels, 16 B) of the pooled pixel and stores it.  12 shuffles per 32 channels instead of 32.
+          const bool sx = KXS ? !(tx & 1) : (lane & 1);    // keeps groups 2,3 in stage 1
+          const bool sy = KXS ? (lane >= 16) : (lane & 8);  // keeps the odd group in stage 2
+          const int partner = KXS ? ((tx & 1) ? lane + 1 : lane - 1) : (lane ^ 1);
+          uint32_t m[8], q[4];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            if constexpr (KXS) {
-              pk[j] = bf16x2_max(pk[j], __shfl_down_sync(0xffffffffu, pk[j], 1));
-              pk[j] = bf16x2_max(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 16));
-            } else {
-              pk[j] = bf16x2_max(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 1));
-              pk[j] = bf16x2_max(pk[j], __shfl_xor_sync(0xffffffffu, pk[j], 8));
-            }
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t send = sx ? pk[j] : pk[8 + j], keep = sx ? pk[8 + j] : pk[j];
+            m[j] = bf16x2_max(keep, __shfl_sync(0xffffffffu, send, partner));
           }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t send = sy ? m[j] : m[4 + j], keep = sy ? m[4 + j] : m[j];
+            q[j] = bf16x2_max(keep, __shfl_xor_sync(0xffffffffu, send, KXS ? 16 : 8));
+          }
+          if (writer) {
+            const int g = (sx ? 2 : 0) + (sy ? 1 : 0);
+            uint4* dst = reinterpret_cast<uint4*>(p.out) +
+                         ((static_cast<size_t>(b) * p.out_cgs + cg + g) * plane + static_cast<size_t>(py) * ow + px);
+            *dst = make_uint4(q[0], q[1], q[2], q[3]);
+          }
+          return;
         }
         if (writer) {
           uint4* dst = reinterpret_cast<uint4*>(p.out) +
