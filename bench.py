@@ -283,10 +283,21 @@ def run_gpu(args, rank, world, local_rank):
     roofline = {"bound": "tensor", "kernel": "ub::conv_tc_kernel (all conv3x3 + ConvTranspose launches)",
                 "achieved": gemm_tflops, "peak": peak, "unit": "TFLOP/s", "frac": gemm_tflops / peak,
                 "peak_source": pk_src + ", sustained figure (kernel timed inside a long step)",
-                "frac_of_burst_peak": gemm_tflops / pk["bf16_tflops"], "traffic": None,
+                "frac_of_burst_peak": gemm_tflops / pk["bf16_tflops"], "traffic": None, "traffic_unit": "bytes/launch",
                 "gemm_share_of_step": gemm_ms / 2 / (ms / args.steps),
                 "flops_per_launch": GEMM_GFLOP_PER_IMAGE * 1e9 * ev.n_local * 2 / max(gemm_launches, 1),
                 "avg_launch_ms": gemm_ms / max(gemm_launches, 1)}
+    # DRAM bytes per launch from the committed ncu --set full capture (same micro-batch, headline workload only)
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")) as f:
+            tr = json.load(f)
+        if not LARGE and tr["microbatch"] == eng.max_microbatch:
+            roofline["traffic"] = tr["dram_bytes_per_launch_avg"]
+            roofline["traffic_source"] = "profiles/r01_ncu_traffic.json (dram read+write, mean over the 20 GEMM launches of a micro-batch)"
+            # every layer's input read once + output written once, bf16 blocked tensors, per image
+            roofline["traffic_algorithmic"] = 93.4e6 * eng.max_microbatch / 20
+    except Exception:
+        pass
     if args.layers and rank == 0:
         for k, cin, nt, ks, n, t in rows:
             fl = 2.0 * ks * ks * cin * nt

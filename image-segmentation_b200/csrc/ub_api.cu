@@ -653,10 +653,10 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
     if ((rc = run_blur(ctx, pl, P, img, fmt, nb, dst, st))) return rc;
     ub::PerturbDev none;
     memset(&none, 0, sizeof(none));
-    ub::stem_kernel<<<blocks_for(px, 256), 256, 0, st>>>(none, ctx->stem, dst, UB_IMG_F32_NCHW, nb, H, W, pl->stem_out,
+    ub::stem_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(none, ctx->stem, dst, UB_IMG_F32_NCHW, nb, H, W, pl->stem_out,
                                                         pl->stem_cgs, pl->stem_cg0, nullptr);
   } else {
-    ub::stem_kernel<<<blocks_for(px, 256), 256, 0, st>>>(P, ctx->stem, img, fmt, nb, H, W, pl->stem_out, pl->stem_cgs,
+    ub::stem_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(P, ctx->stem, img, fmt, nb, H, W, pl->stem_out, pl->stem_cgs,
                                                         pl->stem_cg0, perturbed_out);
   }
   UB_CUDA(ctx, cudaGetLastError());

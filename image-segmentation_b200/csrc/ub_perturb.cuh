@@ -10,6 +10,7 @@
 #include <stdint.h>
 
 #include "../../include/unet_b200.h"
+#include "ub_ptx.cuh"
 
 namespace ub {
 
@@ -242,42 +243,60 @@ struct StemWeights {
   float w[32 * 3];
   float b[32];
 };
-__global__ void __launch_bounds__(256)
-stem_kernel(const __grid_constant__ PerturbDev P, const __grid_constant__ StemWeights sw, const void* img, int fmt, int n,
-            int H, int W, __nv_bfloat16* out, int cgs, int cg0, float* perturbed_out) {
+constexpr int kStemPx = 4;  // pixels per thread: four independent load->FMA->store chains, 64 contiguous bytes per plane
+__global__ void __launch_bounds__(256, 3)
+stem_kernel(const __grid_constant__ PerturbDev P, const __grid_constant__ StemWeights sw, const void* __restrict__ img,
+            int fmt, int n, int H, int W, __nv_bfloat16* __restrict__ out, int cgs, int cg0,
+            float* __restrict__ perturbed_out) {
   __shared__ uint8_t s_lut[256];
   if (P.kind == UB_P_U8_LUT) {
     s_lut[threadIdx.x] = P.lut[threadIdx.x];  // blockDim.x == 256
     __syncthreads();
   }
   const size_t hw = static_cast<size_t>(H) * W;
-  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= hw * n) return;
-  const int b = static_cast<int>(i / hw);
-  const size_t pix = i - static_cast<size_t>(b) * hw;
+  const size_t total = hw * n;
+  static_assert(kStemPx == 4, "float4 / paired 32-byte stores below");
+  const size_t i0 = (static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x) * kStemPx;
+  if (i0 >= total) return;
+  // W is a multiple of 8 (build_plan checks): the four pixels share image and row, and i0 + 3 < total
+  const int b = static_cast<int>(i0 / hw);
+  const size_t pix = i0 - static_cast<size_t>(b) * hw;
   const int y = static_cast<int>(pix / W), x = static_cast<int>(pix % W);
-  float v[3];
-  perturbed_pixel(P, s_lut, img, fmt, b, y, x, H, W, v);
+  float v[kStemPx][3];
+#pragma unroll
+  for (int k = 0; k < kStemPx; ++k) perturbed_pixel(P, s_lut, img, fmt, b, y, x + k, H, W, v[k]);
   if (perturbed_out) {
 #pragma unroll
-    for (int c = 0; c < 3; ++c) perturbed_out[(static_cast<size_t>(b) * 3 + c) * hw + pix] = v[c];
+    for (int c = 0; c < 3; ++c)
+      *reinterpret_cast<float4*>(perturbed_out + (static_cast<size_t>(b) * 3 + c) * hw + pix) =
+          make_float4(v[0][c], v[1][c], v[2][c], v[3][c]);
   }
-  // the 32x3 weights and 32 biases are kernel parameters: FFMA reads them straight from the constant bank
-  uint32_t packed[16];
+  // the 32x3 weights and 32 biases are kernel parameters: FFMA reads them straight from the constant bank.
+  // One channel group (8 outputs = 16 B per pixel) at a time, so only 16 packed registers are live.
 #pragma unroll
-  for (int o = 0; o < 32; o += 2) {
-    float a0 = sw.b[o], a1 = sw.b[o + 1];
+  for (int g = 0; g < 4; ++g) {
+    uint32_t packed[kStemPx][4];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      a0 = fmaf(sw.w[o * 3 + c], v[c], a0);
-      a1 = fmaf(sw.w[(o + 1) * 3 + c], v[c], a1);
+    for (int k = 0; k < kStemPx; ++k) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int o = 8 * g + 2 * j;
+        float a0 = sw.b[o], a1 = sw.b[o + 1];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          a0 = fmaf(sw.w[o * 3 + c], v[k][c], a0);
+          a1 = fmaf(sw.w[(o + 1) * 3 + c], v[k][c], a1);
+        }
+        __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
+        packed[k][j] = *reinterpret_cast<uint32_t*>(&h);
+      }
     }
-    __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
-    packed[o >> 1] = *reinterpret_cast<uint32_t*>(&h);
-  }
-  uint4* dst = reinterpret_cast<uint4*>(out) + (static_cast<size_t>(b) * cgs + cg0) * hw + pix;
+    uint4* dst = reinterpret_cast<uint4*>(out) + (static_cast<size_t>(b) * cgs + cg0 + g) * hw + pix;
 #pragma unroll
-  for (int g = 0; g < 4; ++g) dst[g * hw] = make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+    for (int k = 0; k < kStemPx; k += 2)
+      st_global_256(dst + k, make_uint4(packed[k][0], packed[k][1], packed[k][2], packed[k][3]),
+                    make_uint4(packed[k + 1][0], packed[k + 1][1], packed[k + 1][2], packed[k + 1][3]));
+  }
 }
 
 }  // namespace ub

@@ -119,4 +119,4 @@ if __name__ == "__main__":
     elif stage == "forward_large":
         stage_forward(large=True, hw=(128, 128), n=2)
     elif stage == "time":
-        stage_time(mb=int(sys.argv[2]) if len(sys.argv) > 2 else 32)
+        stage_time(mb=int(sys.argv[2]) if len(sys.argv) > 2 else 32, n=int(sys.argv[3]) if len(sys.argv) > 3 else 64)

@@ -18,8 +18,8 @@ sc = {'Mbyte': 1, 'Kbyte': 1e-3, 'Gbyte': 1e3, 'byte': 1e-6}
 print(f"# ncu --set full, one micro-batch of {mb} images (UB_NO_PDL=1, cold cache, serialised); tensor% = hmma subpipe cycles / elapsed")
 print(f"{'layer':9s} {'kernel <N,BK,KS,WS,TW,CG2>':30s} {'t_us':>7s} {'TF/s':>6s} {'tensor%':>7s} {'rdMB':>7s} {'wrMB':>7s} {'GB/s':>6s} {'lts%':>5s} GHz")
 tot = 0.0
-for r, n in zip(rows[2:], names):
-    t = float(r[T]); tot += t
+for i, (r, n) in enumerate(zip(rows[2:], names)):
+    t = float(r[T]); tot += t if i < len(ORDER) else 0.0   # one pass over the plan; later rows repeat layers
     k = r[ci('Kernel Name')]
     k = k.split('conv_tc_kernel')[-1].split('(')[0] if 'conv_tc' in k else k.split('(')[0]
     try: tp = float(r[HM]) / 4 / float(r[CY]) * 100
