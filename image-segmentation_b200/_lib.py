@@ -44,6 +44,7 @@ SIGNATURES = {
                            c_void_p, c_void_p]),
     "ub_debug_conv3x3": (c_int, [c_void_p, c_char_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "ub_debug_convt2x2": (c_int, [c_void_p, c_char_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "ub_debug_resample": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "ub_launch_count": (c_int64, [c_void_p]),
     "ub_profile_begin": (c_int, [c_void_p]),
     "ub_profile_end": (c_int, [c_void_p, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(c_int64), c_char_p, c_int]),

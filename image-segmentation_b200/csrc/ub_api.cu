@@ -995,4 +995,20 @@ int ub_debug_convt2x2(ub_ctx* ctx, const char* up_key, const void* in_bf16_cg8, 
   return debug_layer(ctx, up_key, in_bf16_cg8, out_bf16_cg8, n, h, w, ub::EPI_CONVT, stream);
 }
 
+int ub_debug_resample(ub_ctx* ctx, const void* in_bf16_cg8, void* out_bf16_cg8, int n, int c, int hi, int wi, int ho,
+                      int wo, void* stream) {
+  if (!ctx) return UB_ERR_INVALID;
+  if (!in_bf16_cg8 || !out_bf16_cg8 || n <= 0 || c <= 0 || c % 8 || hi <= 0 || wi <= 0 || ho <= 0 || wo <= 0)
+    return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t total = static_cast<size_t>(n) * ho * wo * (c / 8);
+  ub::resample_bilinear_kernel<<<blocks_for(total, 256), 256, 0, st>>>(
+      static_cast<const __nv_bfloat16*>(in_bf16_cg8), n, hi, wi, c, static_cast<__nv_bfloat16*>(out_bf16_cg8), ho, wo,
+      c / 8, 0);
+  UB_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return UB_OK;
+}
+
 }  // extern "C"

@@ -282,6 +282,15 @@ class Engine:
                                                _stream(self.device)), "ub_debug_convt2x2")
         return self._from_blocked(out)
 
+    def debug_resample(self, x_nhwc_bf16: torch.Tensor, ho: int, wo: int) -> torch.Tensor:
+        """The decoder's bilinear align_corners=True resize alone (processing_blocks.py:107); NHWC bf16 in and out."""
+        n, h, w, c = x_nhwc_bf16.shape
+        out = torch.zeros((n, c // 8, ho, wo, 8), device=self.device, dtype=torch.bfloat16)
+        xb = self._to_blocked(x_nhwc_bf16.to(self.device))
+        self._check(self.lib.ub_debug_resample(self.h, _ptr(xb), _ptr(out), n, c, h, w, ho, wo, _stream(self.device)),
+                    "ub_debug_resample")
+        return self._from_blocked(out)
+
     def _layer_cout(self, key):
         return self._couts[key]
 

@@ -136,6 +136,10 @@ int ub_debug_conv3x3(ub_ctx* ctx, const char* conv_key, const void* in_bf16_cg8,
 /* Test hook: ConvTranspose2d(k2,s2) (processing_blocks.py:102,106) by prefix, e.g. "dec2.up". */
 int ub_debug_convt2x2(ub_ctx* ctx, const char* up_key, const void* in_bf16_cg8, void* out_bf16_cg8,
                       int n, int h, int w, void* stream);
+/* The decoder's F.interpolate(mode="bilinear", align_corners=True) (models/processing_blocks.py:107) in isolation:
+ * blocked bf16 [n][c/8][hi][wi][8] -> [n][c/8][ho][wo][8]. */
+int ub_debug_resample(ub_ctx* ctx, const void* in_bf16_cg8, void* out_bf16_cg8, int n, int c, int hi, int wi,
+                      int ho, int wo, void* stream);
 /* Measurement hooks (bench.py's roofline leg): between begin and end every tensor-core GEMM launch is
  * bracketed by CUDA events on its own stream.  end() synchronises the device and returns the summed
  * GEMM time, the number of GEMM launches, and (optionally) one text line per layer:

@@ -94,6 +94,25 @@ def test_every_transposed_conv(base_model, dev):
             assert util.rel_err(got, ref) < 6e-3, (key, n, h, w)
 
 
+def test_decoder_resample_in_isolation(dev):
+    """SURVEY 8c fixture (iv): F.interpolate(bilinear, align_corners=True) 64x64 -> 32x32 (dec1) and the ragged /
+    identity shapes, against torch fp32 on the same bf16 inputs; the only difference allowed is the final bf16
+    rounding (and fp32 association inside the 2x2 lerp)."""
+    import torch.nn.functional as F
+    from image_segmentation_b200 import runtime
+    eng = runtime.engine_for(dev)
+    g = torch.Generator().manual_seed(12)
+    for (n, c, hi, wi, ho, wo) in [(2, 256, 64, 64, 32, 32), (1, 16, 10, 14, 5, 7), (1, 8, 6, 6, 6, 6), (3, 24, 8, 8, 16, 12)]:
+        x = torch.randn((n, hi, wi, c), generator=g).to(torch.bfloat16)
+        got = eng.debug_resample(x.to(dev), ho, wo).float().cpu()
+        ref = F.interpolate(x.float().permute(0, 3, 1, 2), size=(ho, wo), mode="bilinear", align_corners=True)
+        ref = ref.permute(0, 2, 3, 1)
+        err = (got - ref).abs()
+        assert float((err - ref.abs() * 2.0 ** -8).max()) <= 1e-6, (n, c, hi, wi, ho, wo, float(err.max()))
+        if (hi, wi) == (ho, wo):
+            assert torch.equal(got, x.float())  # identity resize is exact
+
+
 # ------------------------------------------------------------------ whole network
 def test_forward_logits_and_argmax(trained, dev):
     from image_segmentation_b200 import synthetic
