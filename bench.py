@@ -291,11 +291,14 @@ def run_gpu(args, rank, world, local_rank):
     try:
         with open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")) as f:
             tr = json.load(f)
-        if not LARGE and tr["microbatch"] == eng.max_microbatch:
-            roofline["traffic"] = tr["dram_bytes_per_launch_avg"]
-            roofline["traffic_source"] = "profiles/r01_ncu_traffic.json (dram read+write, mean over the 20 GEMM launches of a micro-batch)"
+        if not LARGE:
+            per_launch_images = ev.n_local * 2 / max(gemm_launches, 1) * 20   # images per micro-batch in this run
+            roofline["traffic"] = tr["dram_bytes_per_image"] * per_launch_images / 20
+            roofline["traffic_source"] = (f"profiles/r01_ncu_traffic.json: dram read+write per image from an ncu --set full "
+                                          f"capture at micro-batch {tr['microbatch']}, x images per launch here, mean over "
+                                          f"the 20 GEMM launches of a micro-batch")
             # every layer's input read once + output written once, bf16 blocked tensors, per image
-            roofline["traffic_algorithmic"] = 93.4e6 * eng.max_microbatch / 20
+            roofline["traffic_algorithmic"] = 93.4e6 * per_launch_images / 20
     except Exception:
         pass
     if args.layers and rank == 0:

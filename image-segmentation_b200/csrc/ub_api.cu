@@ -838,8 +838,11 @@ int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int im
   const size_t hw = static_cast<size_t>(h) * w;
   const size_t img_stride = image_format == UB_IMG_U8_NHWC ? hw * 3 : hw * 3 * 4;
   const size_t tgt_stride = target_format == UB_TGT_U8 ? hw : hw * 8;
-  for (int i0 = 0; i0 < n; i0 += ctx->max_mb) {
-    const int nb = (n - i0) < ctx->max_mb ? (n - i0) : ctx->max_mb;
+  // balanced micro-batches: ceil(n / max_mb) launches of (almost) equal size instead of a short last one
+  const int mb_count = (n + ctx->max_mb - 1) / ctx->max_mb;
+  const int mb_size = (n + mb_count - 1) / mb_count;
+  for (int i0 = 0; i0 < n; i0 += mb_size) {
+    const int nb = (n - i0) < mb_size ? (n - i0) : mb_size;
     ub::PerturbDev Pm = P;
     if (aux) {
       size_t per_img = 0;

@@ -100,7 +100,7 @@ class Engine:
     """Owns one ub_ctx.  arch: 'unet' | 'large'."""
 
     def __init__(self, device, arch: str = "unet", in_channels: int = 3, n_classes: int = 3,
-                 max_microbatch: int = 74):
+                 max_microbatch: int = 148):
         self.lib = L.load()
         self.device = torch.device(device)
         if self.device.type != "cuda":
