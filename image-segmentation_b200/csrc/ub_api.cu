@@ -419,7 +419,12 @@ int launch_pair(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   const int max_grid = ctx->num_sms & ~1;
   const int grid = tiles < max_grid ? tiles : max_grid;
   int smem = 0;
-  choose_pipeline<N, 64, KS, 8, true>(&cp, grid, false, &smem);
+  if constexpr (N == 128 && KS == 3) {  // one n-tile and the pair's halves fit: each CTA keeps its half of the weights resident
+    if (choose_pipeline<N, 64, KS, 8, true>(&cp, grid, cp.n_total == N && !ctx->force_stream, &smem))
+      return launch_kernel<N, 64, KS, true, 8, true>(ctx, cp, grid, smem, st);
+  } else {
+    choose_pipeline<N, 64, KS, 8, true>(&cp, grid, false, &smem);
+  }
   return launch_kernel<N, 64, KS, false, 8, true>(ctx, cp, grid, smem, st);
 }
 

@@ -189,7 +189,7 @@ template <int BLOCK_N, int BK, int KSIZE, bool WS, int TW, bool CG2 = false>
 __global__ void __launch_bounds__(conv_threads(BLOCK_N, TW, KSIZE), 1)
 conv_tc_kernel(const __grid_constant__ ConvParams p) {
   using Cfg = ConvCfg<BLOCK_N, BK, KSIZE, TW, CG2>;
-  static_assert(!(CG2 && WS), "CTA pairs stream their weights");
+  // CG2 && WS: each CTA of the pair keeps ITS half of every weight tile resident (single n-tile layers only)
   static_assert(epi_groups(BLOCK_N, TW, KSIZE) <= Cfg::ACC, "an epilogue group per accumulator at most");
   constexpr bool KXS = Cfg::KXS;
   constexpr int TAPS = Cfg::TAPS;
@@ -272,13 +272,21 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     if constexpr (WS) {
       // weight-stationary: with gridDim a multiple of n_tiles every tile of this CTA has the same n-tile.
       // Weights are constants of the layer: their loads may precede the wait on the previous kernel.
-      const int nt = blockIdx.x % n_tiles;
+      const int nt = CG2 ? 0 : blockIdx.x % n_tiles;  // pairs: the host allows WS only when there is one n-tile
       if (leader) {
-        mbar_arrive_expect_tx(w_full, static_cast<uint32_t>(n_taps * Cfg::B_STAGE_BYTES));
+        if constexpr (CG2) {
+          // both halves are counted on the even CTA's barrier (its MMA warp is the only reader)
+          if (cta_rank == 0) mbar_arrive_expect_tx(w_full, static_cast<uint32_t>(2 * n_taps * Cfg::B_STAGE_BYTES));
+        } else {
+          mbar_arrive_expect_tx(w_full, static_cast<uint32_t>(n_taps * Cfg::B_STAGE_BYTES));
+        }
 #pragma unroll 1
         for (int j = 0; j < n_taps; ++j) {  // consumption order: c outer, tap inner
           const int c = j / TAPS, tap = j % TAPS;
-          if constexpr (KXS) tma_load_2d(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, c * BK, tap * BLOCK_N);
+          if constexpr (CG2)
+            tma_load_2d_pair(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, tap * p.cin + c * BK,
+                             nt * BLOCK_N + static_cast<int>(cta_rank) * Cfg::B_ROWS);
+          else if constexpr (KXS) tma_load_2d(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, c * BK, tap * BLOCK_N);
           else tma_load_2d(b_ring + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, tap * p.cin + c * BK, nt * BLOCK_N);
         }
       }
