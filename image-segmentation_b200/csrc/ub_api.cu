@@ -47,7 +47,7 @@ struct GemmLayer {
 };
 
 struct Step {
-  enum Kind { GEMM, RESAMPLE } kind = GEMM;
+  enum Kind { GEMM, RESAMPLE, CLIP_FUSE } kind = GEMM;  // CLIP_FUSE reuses rs_out / ho / wo / c
   int layer = -1;
   ConvParams cp;   // GEMM: tensor maps + static params (B patched per launch)
   // RESAMPLE
@@ -78,6 +78,8 @@ struct ub_ctx {
   std::map<std::string, int> layer_by_key;
   ub::StemWeights stem;
   float* head_w = nullptr;  // device [C][32]
+  // UB_ARCH_CLIP_UNET: cross_attention_fusion.cross_attn value / output projections, transposed ([in][out]), fp32
+  float *fuse_wv_t = nullptr, *fuse_bv = nullptr, *fuse_wo_t = nullptr, *fuse_bo = nullptr;
   float* head_b = nullptr;
   std::vector<float> h_head_w, h_head_b;  // host copies, passed by value to the HEAD epilogue
   bool weights_ready = false;
@@ -245,8 +247,37 @@ int pack_all(ub_ctx* ctx) {
     if ((rc = pack_conv(ctx, std::string(k) + ".0", std::string(k) + ".1"))) return rc;
     if ((rc = pack_conv(ctx, std::string(k) + ".3", std::string(k) + ".4"))) return rc;
   }
-  if ((rc = pack_conv(ctx, "bottleneck.conv.0", "bottleneck.conv.1"))) return rc;
-  if ((rc = pack_conv(ctx, "bottleneck.conv.3", "bottleneck.conv.4"))) return rc;
+  if (ctx->arch == UB_ARCH_CLIP_UNET) {
+    // the bottleneck ConvBlock's output is dead in ClipUnet.forward (CLIP_models.py:124-126): its weights are not packed
+    const int E = 2 * 32 * (1 << ctx->n_enc);  // bottleneck width = embed_dim of the fusion (512)
+    const HostTensor* ipw = find(ctx, "cross_attention_fusion.cross_attn.in_proj_weight");
+    const HostTensor* ipb = find(ctx, "cross_attention_fusion.cross_attn.in_proj_bias");
+    const HostTensor* opw = find(ctx, "cross_attention_fusion.cross_attn.out_proj.weight");
+    const HostTensor* opb = find(ctx, "cross_attention_fusion.cross_attn.out_proj.bias");
+    if (!ipw || !ipb || !opw || !opb) return fail(ctx, UB_ERR_INVALID, "missing cross_attention_fusion.cross_attn.* entries");
+    if (ipw->data.size() != static_cast<size_t>(3) * E * E || ipb->data.size() != static_cast<size_t>(3) * E ||
+        opw->data.size() != static_cast<size_t>(E) * E || opb->data.size() != static_cast<size_t>(E))
+      return fail(ctx, UB_ERR_UNSUPPORTED, "cross-attention fusion must have embed_dim %d (in_proj [3E,E])", E);
+    // nn.MultiheadAttention packs q, k, v projections row-wise in in_proj_*: the value projection is rows [2E, 3E)
+    std::vector<float> wv_t(static_cast<size_t>(E) * E), wo_t(static_cast<size_t>(E) * E);
+    for (int o = 0; o < E; ++o)
+      for (int i = 0; i < E; ++i) {
+        wv_t[static_cast<size_t>(i) * E + o] = ipw->data[(static_cast<size_t>(2 * E + o)) * E + i];
+        wo_t[static_cast<size_t>(i) * E + o] = opw->data[static_cast<size_t>(o) * E + i];
+      }
+    const size_t mb = static_cast<size_t>(E) * E * 4, vb = static_cast<size_t>(E) * 4;
+    if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->fuse_wv_t), mb))) return rc;
+    if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->fuse_wo_t), mb))) return rc;
+    if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->fuse_bv), vb))) return rc;
+    if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->fuse_bo), vb))) return rc;
+    UB_CUDA(ctx, cudaMemcpy(ctx->fuse_wv_t, wv_t.data(), mb, cudaMemcpyHostToDevice));
+    UB_CUDA(ctx, cudaMemcpy(ctx->fuse_wo_t, wo_t.data(), mb, cudaMemcpyHostToDevice));
+    UB_CUDA(ctx, cudaMemcpy(ctx->fuse_bv, ipb->data.data() + 2 * E, vb, cudaMemcpyHostToDevice));
+    UB_CUDA(ctx, cudaMemcpy(ctx->fuse_bo, opb->data.data(), vb, cudaMemcpyHostToDevice));
+  } else {
+    if ((rc = pack_conv(ctx, "bottleneck.conv.0", "bottleneck.conv.1"))) return rc;
+    if ((rc = pack_conv(ctx, "bottleneck.conv.3", "bottleneck.conv.4"))) return rc;
+  }
   for (int j = 1; j <= ctx->n_enc + 1; ++j) {
     snprintf(k, sizeof(k), "dec%d", j);
     if ((rc = pack_convt(ctx, std::string(k) + ".up"))) return rc;
@@ -559,9 +590,17 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
                        bufp(i_cat[i]), 2 * skip_width(i) / 8, skip_width(i) / 8))) return rc;
   }
   // bottleneck (UNet.py:67), not pooled
-  if ((rc = add_gemm("bottleneck.conv.0", skip_half(n), 2 * skip_width(n) / 8, hl(n), wl(n), ub::EPI_STORE,
-                     bufp(i_ba), cb / 8, 0))) return rc;
-  if ((rc = add_gemm("bottleneck.conv.3", bufp(i_ba), cb / 8, hl(n), wl(n), ub::EPI_STORE, bufp(i_bb), cb / 8, 0))) return rc;
+  if (ctx->arch == UB_ARCH_CLIP_UNET) {
+    // ClipUnet: dec1's input is the cross-attention fusion of the CLIP embedding, broadcast over the grid
+    Step s;
+    s.kind = Step::CLIP_FUSE;
+    s.rs_out = bufp(i_bb); s.ho = hl(n); s.wo = wl(n); s.c = cb;
+    pl->steps.push_back(s);
+  } else {
+    if ((rc = add_gemm("bottleneck.conv.0", skip_half(n), 2 * skip_width(n) / 8, hl(n), wl(n), ub::EPI_STORE,
+                       bufp(i_ba), cb / 8, 0))) return rc;
+    if ((rc = add_gemm("bottleneck.conv.3", bufp(i_ba), cb / 8, hl(n), wl(n), ub::EPI_STORE, bufp(i_bb), cb / 8, 0))) return rc;
+  }
   // decoder (UNet.py:69-72, processing_blocks.py:105-109)
   const __nv_bfloat16* x = bufp(i_bb);
   int xc = cb, xh = hl(n), xw = wl(n);
@@ -645,6 +684,7 @@ int run_blur(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* img, in
 struct HeadArgs {
   const void* targets = nullptr; int target_fmt = 0; int ref_batch = 1; int img_base = 0;
   unsigned long long* cm = nullptr; double* dice = nullptr; uint8_t* pred = nullptr; float* logits = nullptr;
+  const float* clip = nullptr;  // UB_ARCH_CLIP_UNET: this micro-batch's CLIP embeddings [nb, 512]
 };
 
 // One micro-batch: perturb+stem, then every planned step.
@@ -667,6 +707,14 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
   UB_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
   for (Step& s : pl->steps) {
+    if (s.kind == Step::CLIP_FUSE) {
+      if (!ha.clip) return fail(ctx, UB_ERR_INVALID, "this model needs CLIP embeddings: call ub_eval_batches_clip");
+      ub::clip_fusion_broadcast_kernel<<<nb, 512, 2 * s.c * sizeof(float), st>>>(
+          ha.clip, ctx->fuse_wv_t, ctx->fuse_bv, ctx->fuse_wo_t, ctx->fuse_bo, s.rs_out, s.c, s.ho * s.wo);
+      UB_CUDA(ctx, cudaGetLastError());
+      ctx->launches++;
+      continue;
+    }
     if (s.kind == Step::RESAMPLE) {
       const size_t total = static_cast<size_t>(nb) * s.ho * s.wo * (s.c / 8);
       ub::resample_bilinear_kernel<<<blocks_for(total, 256), 256, 0, st>>>(s.rs_in, nb, s.hi, s.wi, s.c, s.rs_out, s.ho, s.wo,
@@ -721,7 +769,7 @@ int ub_make_lut(ub_perturb* p, int lut_kind, double param) {
 int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes, int max_microbatch) {
   if (!out) return UB_ERR_INVALID;
   *out = nullptr;
-  if (arch != UB_ARCH_UNET && arch != UB_ARCH_LARGE_UNET) return fail(nullptr, UB_ERR_INVALID, "unknown arch %d", arch);
+  if (arch != UB_ARCH_UNET && arch != UB_ARCH_LARGE_UNET && arch != UB_ARCH_CLIP_UNET) return fail(nullptr, UB_ERR_INVALID, "unknown arch %d", arch);
   if (in_channels != 3) return fail(nullptr, UB_ERR_UNSUPPORTED, "only in_channels=3 is supported");
   if (n_classes < 1 || n_classes > ub::kMaxClasses) return fail(nullptr, UB_ERR_UNSUPPORTED, "n_classes must be 1..%d", ub::kMaxClasses);
   if (max_microbatch < 1 || max_microbatch > 4096) return fail(nullptr, UB_ERR_INVALID, "max_microbatch out of range");
@@ -822,11 +870,18 @@ int ub_load_weights(ub_ctx* ctx, int n, const char* const* names, const void* co
   return rc;
 }
 
-int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, const void* targets,
-                    int target_format, const void* aux, int n, int h, int w, int ref_batch, int64_t* cm,
-                    double* dice_sums, uint8_t* pred_out, float* logits_out, float* perturbed_out, void* stream) {
+}  // extern "C"  (the shared body of the two evaluation entries follows)
+namespace {
+int eval_impl(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, const void* targets,
+              int target_format, const void* aux, const float* clip_feats, int n, int h, int w, int ref_batch,
+              int64_t* cm, double* dice_sums, uint8_t* pred_out, float* logits_out, float* perturbed_out,
+              void* stream) {
   int rc;
   if ((rc = check_ready(ctx))) return rc;
+  if (ctx->arch == UB_ARCH_CLIP_UNET && !clip_feats)
+    return fail(ctx, UB_ERR_INVALID, "UB_ARCH_CLIP_UNET needs the CLIP embeddings: call ub_eval_batches_clip");
+  if (ctx->arch != UB_ARCH_CLIP_UNET && clip_feats)
+    return fail(ctx, UB_ERR_INVALID, "clip_feats given to a model without a CLIP fusion");
   if (!images || n <= 0 || ref_batch <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
   if (image_format != UB_IMG_F32_NCHW && image_format != UB_IMG_U8_NHWC) return fail(ctx, UB_ERR_INVALID, "bad image_format");
   if (targets && !cm) return fail(ctx, UB_ERR_INVALID, "targets given without a confusion-matrix buffer");
@@ -869,6 +924,7 @@ int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int im
     ha.dice = dice_sums;
     ha.pred = pred_out ? pred_out + hw * i0 : nullptr;
     ha.logits = logits_out ? logits_out + hw * C * i0 : nullptr;
+    ha.clip = clip_feats ? clip_feats + static_cast<size_t>(2 * 32 * (1 << ctx->n_enc)) * i0 : nullptr;
     if ((rc = run_microbatch(ctx, pl, Pm, static_cast<const uint8_t*>(images) + img_stride * i0, image_format, nb, ha,
                              perturbed_out ? perturbed_out + hw * 3 * i0 : nullptr, st)))
       return rc;
@@ -880,6 +936,24 @@ int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int im
     ctx->launches++;
   }
   return UB_OK;
+}
+}  // namespace
+extern "C" {
+
+int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, const void* targets,
+                    int target_format, const void* aux, int n, int h, int w, int ref_batch, int64_t* cm,
+                    double* dice_sums, uint8_t* pred_out, float* logits_out, float* perturbed_out, void* stream) {
+  return eval_impl(ctx, p, images, image_format, targets, target_format, aux, nullptr, n, h, w, ref_batch, cm, dice_sums,
+                   pred_out, logits_out, perturbed_out, stream);
+}
+
+int ub_eval_batches_clip(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, const void* targets,
+                         int target_format, const void* aux, const float* clip_feats, int n, int h, int w,
+                         int ref_batch, int64_t* cm, double* dice_sums, uint8_t* pred_out, float* logits_out,
+                         float* perturbed_out, void* stream) {
+  if (!clip_feats) return fail(ctx, UB_ERR_INVALID, "clip_feats is null");
+  return eval_impl(ctx, p, images, image_format, targets, target_format, aux, clip_feats, n, h, w, ref_batch, cm,
+                   dice_sums, pred_out, logits_out, perturbed_out, stream);
 }
 
 int ub_forward(ub_ctx* ctx, const float* x_nchw, float* logits_nchw, int n, int h, int w, void* stream) {

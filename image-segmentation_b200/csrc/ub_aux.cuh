@@ -203,4 +203,46 @@ __global__ void pack_dataset_kernel(const float* __restrict__ img, const long lo
   if (mask) mask_u8[i] = static_cast<uint8_t>(mask[i]);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// ClipUnet bottleneck (models/CLIP_models.py:124-128, processing_blocks.py:310-322).  `CrossAttentionFusion` runs
+// nn.MultiheadAttention with the H*W bottleneck positions as queries and ONE key/value token per image (the CLIP
+// embedding, expanded H*W times).  With a single key the softmax over keys is identically 1, so every query
+// position receives   out_proj(v_proj(clip) + b_v) + b_o   — independent of the query: the fused map handed to
+// dec1 is that 512-vector broadcast over the bottleneck grid.  One CTA per image: two 512x512 fp32 GEMVs
+// (sequential sums, like the reference's fp32 linear layers up to association), then the broadcast store in the
+// channel-blocked layout [cgs = C/8][hw][8] bf16.
+__global__ void __launch_bounds__(512)
+clip_fusion_broadcast_kernel(const float* __restrict__ clip, const float* __restrict__ w_v_t, const float* __restrict__ b_v,
+                             const float* __restrict__ w_o_t, const float* __restrict__ b_o,
+                             __nv_bfloat16* __restrict__ out, int C, int hw) {
+  extern __shared__ float s_vec[];  // [2][C]
+  float* s_in = s_vec;
+  float* s_mid = s_vec + C;
+  const int b = blockIdx.x;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_in[i] = clip[static_cast<size_t>(b) * C + i];
+  __syncthreads();
+  for (int o = threadIdx.x; o < C; o += blockDim.x) {
+    float acc = b_v[o];  // weights are stored transposed ([in][out]) so that a warp reads consecutive floats
+    for (int i = 0; i < C; ++i) acc = fmaf(w_v_t[static_cast<size_t>(i) * C + o], s_in[i], acc);
+    s_mid[o] = acc;
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < C; o += blockDim.x) {
+    float acc = b_o[o];
+    for (int i = 0; i < C; ++i) acc = fmaf(w_o_t[static_cast<size_t>(i) * C + o], s_mid[i], acc);
+    s_in[o] = acc;  // s_in is free again
+  }
+  __syncthreads();
+  uint4* dst = reinterpret_cast<uint4*>(out) + static_cast<size_t>(b) * (C / 8) * hw;
+  for (int i = threadIdx.x; i < (C / 8) * hw; i += blockDim.x) {
+    const int g = i / hw;
+    __nv_bfloat162 h0 = __floats2bfloat162_rn(s_in[8 * g + 0], s_in[8 * g + 1]);
+    __nv_bfloat162 h1 = __floats2bfloat162_rn(s_in[8 * g + 2], s_in[8 * g + 3]);
+    __nv_bfloat162 h2 = __floats2bfloat162_rn(s_in[8 * g + 4], s_in[8 * g + 5]);
+    __nv_bfloat162 h3 = __floats2bfloat162_rn(s_in[8 * g + 6], s_in[8 * g + 7]);
+    dst[i] = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
+                        *reinterpret_cast<uint32_t*>(&h2), *reinterpret_cast<uint32_t*>(&h3));
+  }
+}
+
 }  // namespace ub

@@ -97,7 +97,8 @@ def _stream(device):
 
 
 class Engine:
-    """Owns one ub_ctx.  arch: 'unet' | 'large'."""
+    """Owns one ub_ctx.  arch: 'unet' | 'large' | 'clip' (ClipUnet: every evaluation call also takes the CLIP
+    image embeddings of the same images, `clip_feats` fp32 [n, 512])."""
 
     def __init__(self, device, arch: str = "unet", in_channels: int = 3, n_classes: int = 3,
                  max_microbatch: int = 148):
@@ -110,8 +111,11 @@ class Engine:
         self.n_classes = n_classes
         self.max_microbatch = max_microbatch
         h = ctypes.c_void_p()
-        rc = self.lib.ub_create(ctypes.byref(h), idx, L.UB_ARCH_LARGE_UNET if arch == "large" else L.UB_ARCH_UNET,
-                                in_channels, n_classes, max_microbatch)
+        archs = {"unet": L.UB_ARCH_UNET, "large": L.UB_ARCH_LARGE_UNET, "clip": L.UB_ARCH_CLIP_UNET}
+        if arch not in archs:
+            raise ValueError(f"unknown arch {arch!r}")
+        self.arch = arch
+        rc = self.lib.ub_create(ctypes.byref(h), idx, archs[arch], in_channels, n_classes, max_microbatch)
         if rc != 0:
             raise RuntimeError(f"ub_create failed ({rc}): {self.lib.ub_last_error(None).decode()}")
         self.h = h
@@ -145,9 +149,11 @@ class Engine:
         self._check(self.lib.ub_load_weights(self.h, n, names, ptrs, shapes, ndims), "ub_load_weights")
         self.loaded = True
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, clip_feats: Optional[torch.Tensor] = None) -> torch.Tensor:
         x = x.to(self.device, torch.float32).contiguous()
         n, c, h, w = x.shape
+        if self.arch == "clip":
+            return self.eval_batches(x, None, None, 1, want_logits=True, clip_feats=clip_feats)["logits"]
         out = torch.empty((n, self.n_classes, h, w), device=self.device, dtype=torch.float32)
         self._check(self.lib.ub_forward(self.h, _ptr(x), _ptr(out), n, h, w, _stream(self.device)), "ub_forward")
         return out
@@ -155,7 +161,7 @@ class Engine:
     def eval_batches(self, images: torch.Tensor, targets: Optional[torch.Tensor], perturbation: Optional[Perturbation],
                      ref_batch: int, want_dice: bool = False, want_pred: bool = False, want_logits: bool = False,
                      want_perturbed: bool = False, out_cm: Optional[torch.Tensor] = None,
-                     out_dice: Optional[torch.Tensor] = None):
+                     out_dice: Optional[torch.Tensor] = None, clip_feats: Optional[torch.Tensor] = None):
         """images: uint8 [n,H,W,3] or fp32 [n,3,H,W]; targets: uint8 or int64 [n,H,W] (device tensors).
         Returns dict(cm=int64 [nb,C,C], dice=f64 [nb,C,3], pred=u8 [n,H,W], logits, perturbed)."""
         assert images.is_cuda and images.is_contiguous()
@@ -188,6 +194,17 @@ class Engine:
         aux = None
         if p is not None and p.aux is not None:
             aux = p.aux.to(self.device).contiguous()
+        if self.arch == "clip":
+            if clip_feats is None:
+                raise ValueError("a ClipUnet engine needs clip_feats (fp32 [n, 512], the CLIP image embeddings)")
+            clip_feats = clip_feats.to(self.device, torch.float32).contiguous()
+            if tuple(clip_feats.shape) != (n, 512):
+                raise ValueError(f"clip_feats must be [n, 512], got {tuple(clip_feats.shape)}")
+            self._check(self.lib.ub_eval_batches_clip(
+                self.h, ctypes.byref(p.struct) if p is not None else None, _ptr(images), fmt, _ptr(targets), tfmt,
+                _ptr(aux), _ptr(clip_feats), n, h, w, int(ref_batch), _ptr(cm), _ptr(dice), _ptr(pred), _ptr(logits),
+                _ptr(pert), _stream(self.device)), "ub_eval_batches_clip")
+            return dict(cm=cm, dice=dice, pred=pred, logits=logits, perturbed=pert)
         self._check(self.lib.ub_eval_batches(self.h, ctypes.byref(p.struct) if p is not None else None, _ptr(images),
                                              fmt, _ptr(targets), tfmt, _ptr(aux), n, h, w, int(ref_batch), _ptr(cm),
                                              _ptr(dice), _ptr(pred), _ptr(logits), _ptr(pert),

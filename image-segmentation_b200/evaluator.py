@@ -99,15 +99,38 @@ class RobustnessEvaluator:
             return p
         return perturbation
 
+    def _eval(self, images, masks, spec: Optional[Perturbation], want_dice, out_cm, out_dice):
+        """One engine call over `images` (a whole number of reference batches, except possibly the last)."""
+        if self.engine.arch != "clip":
+            self.engine.eval_batches(images, masks, spec, self.ref_batch, want_dice=want_dice, out_cm=out_cm,
+                                     out_dice=out_dice)
+            return
+        # ClipUnet (models/CLIP_models.py:114-131): the CLIP embedding is taken from the image the network sees, i.e.
+        # AFTER the perturbation, so the perturbed batch is materialised, embedded, and then evaluated unperturbed.
+        step = max(1, self.engine.max_microbatch // self.ref_batch) * self.ref_batch
+        n = images.shape[0]
+        for i0 in range(0, n, step):
+            i1 = min(i0 + step, n)
+            sub = Perturbation()
+            if spec is not None:
+                sub.struct, sub.name = type(spec.struct).from_buffer_copy(spec.struct), spec.name
+                sub.aux = spec.aux[i0:i1] if spec.aux is not None else None
+                sub.struct.seed = (spec.struct.seed + 0x9E3779B97F4A7C15 * i0) & (2 ** 64 - 1)  # device RNG: new stream
+            x = self.engine.perturb(images[i0:i1].contiguous(), sub)
+            feats = self.model.clip_feature_extractor(x)
+            b0, b1 = i0 // self.ref_batch, math.ceil(i1 / self.ref_batch)
+            self.engine.eval_batches(x, masks[i0:i1].contiguous(), None, self.ref_batch, want_dice=want_dice,
+                                     out_cm=out_cm[b0:b1], out_dice=out_dice[b0:b1] if out_dice is not None else None,
+                                     clip_feats=feats)
+
     def run_level(self, perturbation: Optional[Perturbation], want_dice: bool = False, reduce: bool = True):
         """-> (cm int64 [n_batches,C,C], dice_sums f64 [n_batches,C,3] or None), complete on every rank."""
         self.cm.zero_()
         if want_dice:
             self.dice.zero_()
         if self.n_local > 0:
-            self.engine.eval_batches(self.images, self.masks, self.local_aux(perturbation), self.ref_batch,
-                                     want_dice=want_dice, out_cm=self.cm[self.b0:self.b1],
-                                     out_dice=self.dice[self.b0:self.b1] if want_dice else None)
+            self._eval(self.images, self.masks, self.local_aux(perturbation), want_dice, self.cm[self.b0:self.b1],
+                       self.dice[self.b0:self.b1] if want_dice else None)
         if reduce and self.world > 1:
             dist.all_reduce(self.cm, op=dist.ReduceOp.SUM)
             if want_dice:
@@ -136,8 +159,8 @@ class RobustnessEvaluator:
                 merged.struct, merged.name = spec.struct, spec.name
                 merged.aux = torch.cat([s.aux.to(self.device) for s in specs], dim=0)
                 spec = merged
-            self.engine.eval_batches(self.images[lo:hi], self.masks[lo:hi], spec, self.ref_batch, want_dice=want_dice,
-                                     out_cm=self.cm[cb0:cb1], out_dice=self.dice[cb0:cb1] if want_dice else None)
+            self._eval(self.images[lo:hi], self.masks[lo:hi], spec, want_dice, self.cm[cb0:cb1],
+                       self.dice[cb0:cb1] if want_dice else None)
         if self.world > 1:
             dist.all_reduce(self.cm, op=dist.ReduceOp.SUM)
             if want_dice:

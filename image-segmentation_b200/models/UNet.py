@@ -16,6 +16,7 @@ from .processing_blocks import ConvBlock, ConvBlockDownsample, ConvBlockUpsample
 
 class _B200Net(nn.Module):
     _arch = "unet"
+    _host_side_prefixes = ()  # sub-modules that compute outside the library (their weights are not handed to it)
 
     def _finish_init(self, out_channels, activation):
         self.activation = activation
@@ -37,7 +38,8 @@ class _B200Net(nn.Module):
             if self._engine is not None:
                 self._engine.close()
             self._engine = runtime.new_engine(dev, self._arch, 3, self._n_classes, mb)
-            self._engine.load_state_dict({self._flat_name(k): v for k, v in self.state_dict().items()})
+            self._engine.load_state_dict({self._flat_name(k): v for k, v in self.state_dict().items()
+                                          if not k.startswith(self._host_side_prefixes)})
             self._engine.set_layer_couts(self.layer_couts())
             self._engine_key = key
         return self._engine
@@ -50,6 +52,8 @@ class _B200Net(nn.Module):
     def layer_couts(self):
         out = {}
         for name, m in self.named_modules():
+            if name.startswith(self._host_side_prefixes):
+                continue
             name = self._flat_name(name)
             if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)) and name not in ("input", "out"):
                 out[name] = m.out_channels

@@ -180,3 +180,69 @@ class SaltAndPepper(_DevicePerturbation):
     def spec(self, img):
         b, _, h, w = img.shape
         return Perturbation.f_salt_pepper(self.amount, aux=torch.rand((b, 1, h, w), device=img.device))
+
+
+# --------------------------------------------------------------------------- ClipUnet blocks (reference :135-233, :286-322)
+class CustomClipPreprocessor(nn.Module):
+    """Resize to 224x224 and normalise with the CLIP statistics; reference :135-168.  The reference loops over the
+    images of the batch; torchvision's Resize / Normalize act on the trailing [C,H,W] dimensions, so one batched call
+    gives the same values."""
+
+    def __init__(self, mean, std, target_size=(224, 224)):
+        super().__init__()
+        from torchvision import transforms
+        self.resize = transforms.Resize(target_size)
+        self.normalize = transforms.Normalize(mean=mean, std=std)
+
+    def forward(self, images):
+        return self.normalize(self.resize(images))
+
+
+class ClipFeatureExtractor(nn.Module):
+    """CLIP ViT-B/32 image embedding [B,512]; reference :171-233.  This is the one part of ClipUnet that is NOT
+    unet-b200 code: it runs HuggingFace `transformers`' CLIPModel with PyTorch kernels, exactly as the reference does.
+    `clip_model` lets a caller supply an already constructed CLIPModel (e.g. random-init where the
+    `openai/clip-vit-base-patch32` checkpoint cannot be downloaded); the default loads the checkpoint like the
+    reference (:209)."""
+
+    def __init__(self, train=False, clip_model=None):
+        super().__init__()
+        self.device = torch.device('cuda' if torch.cuda.is_available() else 'cpu')
+        mean = [0.48145466, 0.4578275, 0.40821073]
+        std = [0.26862954, 0.26130258, 0.27577711]
+        self.custom_preprocessor = CustomClipPreprocessor(mean=mean, std=std)
+        if clip_model is None:
+            from transformers import CLIPModel
+            clip_model = CLIPModel.from_pretrained("openai/clip-vit-base-patch32")
+        self.clip_model = clip_model.to(self.device)
+        self.train_clip = train
+        self.set_train(train)
+
+    def set_train(self, value: bool):
+        assert isinstance(value, bool), "Value must be a boolean"
+        if value:
+            raise RuntimeError("unet-b200 is inference-only: the CLIP encoder stays frozen")
+        for param in self.clip_model.parameters():
+            param.requires_grad = value
+        self.train_clip = value
+
+    def forward(self, X):
+        inputs = self.custom_preprocessor(X)
+        with torch.no_grad():
+            feats = self.clip_model.get_image_features(pixel_values=inputs)
+        if not torch.is_tensor(feats):  # transformers >= 5 returns a ModelOutput; the projected embedding is its pooler_output
+            feats = feats.pooler_output
+        return feats
+
+
+class CrossAttentionFusion(nn.Module):
+    """nn.MultiheadAttention(query = bottleneck positions, key = value = the CLIP embedding); reference :286-322.
+    Parameter container: with one key per image the attention weights are identically 1, so the library evaluates
+    out_proj(v_proj(clip)) once per image and broadcasts it (csrc/ub_aux.cuh: clip_fusion_broadcast_kernel)."""
+
+    def __init__(self, resnet_channels, num_heads=4):
+        super().__init__()
+        self.cross_attn = nn.MultiheadAttention(embed_dim=resnet_channels, num_heads=num_heads)
+
+    def forward(self, resnet_feats, clip_feats):
+        _no_standalone("CrossAttentionFusion")

@@ -34,7 +34,12 @@ enum ub_status {
 };
 
 /* models/UNet.py:7-76 (UNet) and :78-148 (LargeUNet) */
-enum ub_arch { UB_ARCH_UNET = 0, UB_ARCH_LARGE_UNET = 1 };
+enum ub_arch {
+  UB_ARCH_UNET = 0,       /* models/UNet.py:7-76 */
+  UB_ARCH_LARGE_UNET = 1, /* models/UNet.py:78-148 */
+  UB_ARCH_CLIP_UNET = 2   /* models/CLIP_models.py:89-134: UNet encoder/decoder, bottleneck = cross-attention fusion of the
+                             CLIP image embedding (the embedding itself is computed by the caller) */
+};
 
 /* Input image container. */
 enum ub_image_format {
@@ -110,6 +115,16 @@ int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int im
                     const void* targets, int target_format, const void* aux, int n, int h, int w,
                     int ref_batch, int64_t* cm, double* dice_sums, uint8_t* pred_out,
                     float* logits_out, float* perturbed_out, void* stream);
+
+/* ub_eval_batches for UB_ARCH_CLIP_UNET: clip_feats fp32 [n, 512] (device) = `ClipFeatureExtractor.forward`'s output
+ * for the same n images (models/processing_blocks.py:216-233).  The library applies `CrossAttentionFusion`
+ * (processing_blocks.py:310-322; weights `cross_attention_fusion.cross_attn.*` from ub_load_weights) and feeds the
+ * result to dec1 with the encoder skips.  The reference's bottleneck ConvBlock output is never used by its forward
+ * (CLIP_models.py:124-126) and is not computed. */
+int ub_eval_batches_clip(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,
+                         const void* targets, int target_format, const void* aux, const float* clip_feats, int n,
+                         int h, int w, int ref_batch, int64_t* cm, double* dice_sums, uint8_t* pred_out,
+                         float* logits_out, float* perturbed_out, void* stream);
 
 /* Perturbation alone (the Dataset wrappers' __getitem__ / the nn.Modules' forward): out fp32 [n,3,H,W]. */
 int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,

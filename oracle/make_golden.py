@@ -11,6 +11,8 @@ through oracle/refload.py).  Run in the build container only:  python -m oracle.
                    reference IoU / PixelAccuracy on them, and a checksum of the seeded state_dict.
   dataset_rows.npz reference CustomImageDataset._deserialize_datapoint on 6 synthetic rows (trimap remap), masks +
                    a checksum of the decoded fp32 images.
+  clipunet_small.npz  reference ClipUnet with a seeded random-init CLIP encoder (the checkpoint needs the network): key
+                   list, CLIP embedding and logits on the [2,3,32,64] input.
   segmodel_small.npz  reference SegmentationModel(Encoder(), SegmentationDecoderSkip(3)) (models/pre_trained.py:47-56,
                    models/autoencoder.py:5-26), seed 42 + randomised BatchNorm: state_dict key list, checksums and
                    logits on the same [2,3,32,64] input.
@@ -191,6 +193,33 @@ def golden_dataset_rows(ns):
     return out
 
 
+def golden_clipunet():
+    """Reference ClipUnet (models/CLIP_models.py:65-134) with a seeded random-init CLIP ViT-B/32 (refload.load_clip_unet):
+    key list of the non-CLIP part, the CLIP embedding of the input and the logits."""
+    from image_segmentation_b200 import synthetic
+    ns = refload.load_clip_unet(clip_seed=0)
+    torch.manual_seed(42)
+    m = ns.ClipUnet().to("cpu").eval()
+    own = {k: v for k, v in m.state_dict().items() if not k.startswith("clip_feature_extractor.")}
+    base_sum = state_checksum(own)
+    sd = synthetic.randomize_batchnorm(own, seed=7)
+    m.load_state_dict(sd, strict=False)
+    imgs, _ = synthetic.make_dataset(2, 32, 64, seed=5)
+    x = synthetic.to_float_nchw(imgs)
+    with torch.no_grad():
+        feats = m.clip_feature_extractor(x.to(m.clip_feature_extractor.device)).cpu()
+        logits = m(x)
+        sd["out.bias"] = sd["out.bias"] - logits.mean(dim=(0, 2, 3))
+        m.load_state_dict(sd, strict=False)
+        logits = m(x)
+    keys = list(own.keys())
+    out = dict(images_u8=imgs.numpy(), clip_feats=feats.numpy(), logits=logits.numpy(), out_bias=sd["out.bias"].numpy(),
+               keys=np.array(keys), shapes=np.array([str(tuple(own[k].shape)) for k in keys]),
+               seed42_state_sha256=np.array(base_sum), final_state_sha256=np.array(state_checksum(sd)))
+    np.savez_compressed(os.path.join(OUT, "clipunet_small.npz"), **out)
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = refload.load()
@@ -199,6 +228,7 @@ def main():
     golden_unet(ns)
     golden_segmodel(ns)
     golden_dataset_rows(ns)
+    golden_clipunet()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

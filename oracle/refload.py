@@ -40,6 +40,9 @@ def _install_stubs():
         if "." in name:
             parent, child = name.rsplit(".", 1)
             setattr(sys.modules[parent], child, mod)
+    mp = sys.modules["matplotlib.patches"]
+    if getattr(mp, "__stub__", False) and not hasattr(mp, "Patch"):
+        mp.Patch = type("Patch", (), {})  # models/helperFunctions.py:6 imports the name; plotting is never called
     smp = sys.modules["segmentation_models_pytorch"]
     if getattr(smp, "__stub__", False):
         # models/losses.py:9,22,96,108 instantiate smp.losses.DiceLoss at construction time.
@@ -70,4 +73,32 @@ def load():
     ns.pre_trained = importlib.import_module("models.pre_trained")
     ns.UNet = ns.UNet_mod.UNet
     ns.LargeUNet = ns.UNet_mod.LargeUNet
+    return ns
+
+
+def load_clip_unet(clip_seed: int = 0):
+    """The reference's `ClipUnet` class (models/CLIP_models.py:65-134) with the ONE substitution this container forces:
+    `CLIPModel.from_pretrained("openai/clip-vit-base-patch32")` (models/processing_blocks.py:209) needs the network, so
+    the name `CLIPModel` inside the reference module is bound to a subclass whose `from_pretrained` builds the same
+    architecture (default CLIPConfig = ViT-B/32, projection 512) with seeded random weights, and whose
+    `get_image_features` returns the tensor the reference's pinned transformers 4.x returned (5.x wraps it in a
+    ModelOutput).  Everything else — preprocessing, fusion, U-Net — is the reference's unmodified code."""
+    import torch
+    import transformers
+    ns = load()
+
+    class SeededCLIPModel(transformers.CLIPModel):
+        @classmethod
+        def from_pretrained(cls, *args, **kwargs):
+            torch.manual_seed(clip_seed)
+            return cls(transformers.CLIPConfig()).eval()
+
+        def get_image_features(self, *args, **kwargs):
+            out = super().get_image_features(*args, **kwargs)
+            return out if torch.is_tensor(out) else out.pooler_output
+
+    ns.blocks.CLIPModel = SeededCLIPModel
+    ns.CLIP_models = importlib.import_module("models.CLIP_models")
+    ns.SeededCLIPModel = SeededCLIPModel
+    ns.ClipUnet = ns.CLIP_models.ClipUnet
     return ns

@@ -6,6 +6,8 @@ this.  It restates, as one flat functional pass over a reference-format state_di
   models/UNet.py:60-76 (UNet.forward) and :129-148 (LargeUNet.forward)
   models/processing_blocks.py:42-52  ConvBlock  (conv3x3 pad1 + BatchNorm eval + ReLU, twice)
   models/processing_blocks.py:71-77  ConvBlockDownsample (ConvBlock + MaxPool2d(2,2))
+  models/CLIP_models.py:114-131 (ClipUnet.forward, given the CLIP embedding) with
+  models/processing_blocks.py:310-322 (CrossAttentionFusion)
   models/processing_blocks.py:102-109 ConvBlockUpsampleSkip
         (ConvTranspose2d k2 s2 -> F.interpolate bilinear align_corners=True to skip size ->
          cat([up, skip]) -> ConvBlock)
@@ -46,8 +48,23 @@ def _up_skip(x, skip, sd, name):
     return _double_conv(torch.cat([x, skip], dim=1), sd, f"{name}.conv.conv")
 
 
-def forward_impl(state_dict, x: torch.Tensor, return_intermediates: bool = False):
-    """x: fp32 [B,3,H,W] -> logits fp32 [B,C,H,W] (activation = Identity).  Differentiable."""
+def clip_fusion(sd, clip_feats: torch.Tensor, h: int, w: int) -> torch.Tensor:
+    """models/processing_blocks.py:310-322 (CrossAttentionFusion.forward) restated for its actual shapes: every one of
+    the H*W queries attends to ONE key/value token per image, so softmax over the key axis is 1 and the output is
+    out_proj(v_proj(clip)) at every position, whatever the query.  -> [B, E, h, w].  (tests/test_oracle_pinned.py
+    checks this against nn.MultiheadAttention itself.)"""
+    e = sd["cross_attention_fusion.cross_attn.out_proj.weight"].shape[0]
+    w_v = sd["cross_attention_fusion.cross_attn.in_proj_weight"][2 * e:3 * e]
+    b_v = sd["cross_attention_fusion.cross_attn.in_proj_bias"][2 * e:3 * e]
+    v = F.linear(clip_feats.float(), w_v, b_v)
+    o = F.linear(v, sd["cross_attention_fusion.cross_attn.out_proj.weight"],
+                 sd["cross_attention_fusion.cross_attn.out_proj.bias"])
+    return o[:, :, None, None].expand(-1, -1, h, w)
+
+
+def forward_impl(state_dict, x: torch.Tensor, return_intermediates: bool = False, clip_feats=None):
+    """x: fp32 [B,3,H,W] -> logits fp32 [B,C,H,W] (activation = Identity).  Differentiable.
+    clip_feats [B,512]: ClipUnet (models/CLIP_models.py:114-131) — the bottleneck handed to dec1 is the fusion."""
     sd = {k.replace("_orig_mod.", ""): v.float() for k, v in state_dict.items()
           if v.is_floating_point()}
     n_enc = 4 if arch_of(sd) == "large" else 3
@@ -60,7 +77,10 @@ def forward_impl(state_dict, x: torch.Tensor, return_intermediates: bool = False
         h = F.max_pool2d(_double_conv(h, sd, f"enc{i}.block.0.conv"), 2, 2)
         acts[f"enc{i}"] = h
         skips.append(h)
-    h = _double_conv(h, sd, "bottleneck.conv")
+    if clip_feats is not None:
+        h = clip_fusion(sd, clip_feats, h.shape[2], h.shape[3])  # CLIP_models.py:122-124: bottleneck(enc3) is unused
+    else:
+        h = _double_conv(h, sd, "bottleneck.conv")
     acts["bottleneck"] = h
     for j in range(1, n_enc + 2):
         h = _up_skip(h, skips[n_enc + 1 - j], sd, f"dec{j}")
@@ -70,8 +90,8 @@ def forward_impl(state_dict, x: torch.Tensor, return_intermediates: bool = False
 
 
 @torch.no_grad()
-def forward(state_dict, x: torch.Tensor, return_intermediates: bool = False):
-    return forward_impl(state_dict, x, return_intermediates)
+def forward(state_dict, x: torch.Tensor, return_intermediates: bool = False, clip_feats=None):
+    return forward_impl(state_dict, x, return_intermediates, clip_feats)
 
 
 def hard_prediction(logits: torch.Tensor) -> torch.Tensor:

@@ -368,3 +368,67 @@ def test_device_resident_dataset_rows_bit_exact(dev):
     for i in range(5):
         assert np.array_equal(got[i], do.decode_mask(raw[i].numpy()))
     assert runtime.engine_for(dev).decode_masks(torch.empty((0, 8, 8), dtype=torch.uint8)).shape == (0, 8, 8)
+
+
+# ------------------------------------------------------------------ ClipUnet (the model the reference's sweep script evaluates)
+@pytest.fixture(scope="module")
+def clipunet(dev):
+    import os
+    from transformers import CLIPConfig, CLIPModel
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.CLIP_models import ClipUnet
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "clipunet_small.npz"))
+    torch.manual_seed(0)
+    m = ClipUnet(clip_model=CLIPModel(CLIPConfig()).eval()).eval()
+    own = {k: v for k, v in m.state_dict().items() if not k.startswith("clip_feature_extractor.")}
+    sd = synthetic.randomize_batchnorm(own, seed=7)
+    sd["out.bias"] = torch.from_numpy(g["out_bias"])
+    m.load_state_dict(sd, strict=False)
+    return m.to(dev), sd, g
+
+
+def test_clipunet_logits_against_reference_golden(clipunet, dev):
+    """Library path given the reference's own CLIP embedding, and the whole drop-in forward (CLIP encoder through
+    transformers on the GPU), against the reference's logits (fp32 CPU, golden)."""
+    from image_segmentation_b200 import synthetic
+    m, sd, g = clipunet
+    x = synthetic.to_float_nchw(torch.from_numpy(g["images_u8"])).to(dev)
+    ref = torch.from_numpy(g["logits"])
+    got = m.engine(dev).forward(x, clip_feats=torch.from_numpy(g["clip_feats"]).to(dev)).cpu()
+    rel = util.rel_err(got, ref)
+    feats = m.clip_feature_extractor(x).cpu()
+    frel = util.rel_err(feats, torch.from_numpy(g["clip_feats"]))
+    full = m(x).cpu()
+    print(f"ClipUnet: logits rel err {rel:.3e} (golden embedding), {util.rel_err(full, ref):.3e} (own embedding); "
+          f"CLIP embedding rel err {frel:.3e}")
+    assert frel < 1e-3
+    assert rel < 2e-2 and util.rel_err(full, ref) < 2e-2  # random-init logits of magnitude 0.08: bf16 noise floor
+    with pytest.raises(ValueError):
+        m.engine(dev).forward(x)  # the embedding is mandatory for this architecture
+
+
+def test_clipunet_evaluator_embeds_the_perturbed_image(clipunet, dev):
+    """RobustnessEvaluator on a ClipUnet: counts equal those of the explicit two-stage evaluation (perturb -> embed ->
+    evaluate), and predictions agree with the oracle evaluated on the same perturbed images and embeddings."""
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.engine import Perturbation as P
+    from image_segmentation_b200.evaluator import RobustnessEvaluator
+    m, sd, g = clipunet
+    imgs, masks = synthetic.make_dataset(11, 64, 64, seed=2)
+    ev = RobustnessEvaluator(m, imgs, masks, 4, device=dev, rank=0, world_size=1, max_microbatch=8)
+    spec = P.u8_contrast(0.6)
+    cm = ev.run_level(spec, reduce=False)[0].clone()
+    eng = ev.engine
+    x = eng.perturb(imgs.to(dev), spec)
+    want_x = po.dequantise(po.u8_contrast(imgs.permute(0, 3, 1, 2).numpy(), 0.6))
+    assert np.array_equal(x.cpu().numpy(), want_x)
+    feats = m.clip_feature_extractor(x)
+    res = eng.eval_batches(x, masks.to(dev), None, 4, want_pred=True, want_logits=True, clip_feats=feats)
+    assert int(cm.sum()) == 11 * 64 * 64
+    # the evaluator embeds chunk by chunk (8 images, then 3): the CLIP encoder's batch size may move its fp32 output
+    # by an ulp, so compare counts with a tolerance of a few pixels and predictions with the oracle
+    assert int((cm - res["cm"]).abs().sum()) <= 16
+    ref = unet_oracle.forward({k: v.to(dev) for k, v in sd.items()}, x, clip_feats=feats).cpu()
+    agree = float((unet_oracle.hard_prediction(ref) == res["pred"].cpu().long()).float().mean())
+    print(f"ClipUnet evaluator: argmax agreement with the oracle {agree:.4f}")
+    assert agree > 0.97 and util.rel_err(res["logits"].cpu(), ref) < 2e-2

@@ -146,6 +146,50 @@ def test_dataset_row_decoding_against_reference_golden():
     assert kinds[0] == {0, 1} and kinds[1] == {0, 2} and kinds[2] == {0, 2}  # cat, dog, border-only row
 
 
+def test_clip_fusion_restatement_equals_multihead_attention():
+    """oracle.unet_oracle.clip_fusion vs nn.MultiheadAttention fed the way CrossAttentionFusion feeds it
+    (processing_blocks.py:310-322): one key/value token per image -> the output ignores the queries."""
+    torch.manual_seed(3)
+    mha = torch.nn.MultiheadAttention(embed_dim=512, num_heads=1).eval()
+    sd = {"cross_attention_fusion.cross_attn." + k: v for k, v in mha.state_dict().items()}
+    feats = torch.randn(2, 512)
+    q = torch.randn(6 * 5, 2, 512)
+    with torch.no_grad():
+        ref, _ = mha(q, feats.unsqueeze(0).expand(30, -1, -1), feats.unsqueeze(0).expand(30, -1, -1))
+    ref = ref.permute(1, 2, 0).view(2, 512, 6, 5)
+    got = unet_oracle.clip_fusion(sd, feats, 6, 5)
+    assert float((got - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+
+
+def test_clipunet_tree_and_oracle_against_reference_golden():
+    """ClipUnet drop-in (reference models/CLIP_models.py:65-134): same keys/shapes/seeded init for everything but the
+    CLIP encoder, same CLIP embedding from the same seeded encoder, and the oracle reproduces the reference's logits."""
+    from transformers import CLIPConfig, CLIPModel
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.CLIP_models import ClipUnet
+    from oracle.make_golden import state_checksum
+    g = np.load(os.path.join(GOLD, "clipunet_small.npz"))
+    torch.manual_seed(0)                      # oracle/refload.py: the stand-in checkpoint is CLIPConfig() at seed 0 ...
+    clip = CLIPModel(CLIPConfig()).eval()
+    m = ClipUnet(clip_model=clip).eval()      # ... and the rest of the model draws from the same stream, as in the reference
+    own = {k: v for k, v in m.state_dict().items() if not k.startswith("clip_feature_extractor.")}
+    assert list(own.keys()) == [str(k) for k in g["keys"]]
+    assert [str(tuple(v.shape)) for v in own.values()] == [str(s) for s in g["shapes"]]
+    assert state_checksum(own) == str(g["seed42_state_sha256"])
+    sd = synthetic.randomize_batchnorm(own, seed=7)
+    sd["out.bias"] = torch.from_numpy(g["out_bias"])
+    assert state_checksum(sd) == str(g["final_state_sha256"])
+    x = synthetic.to_float_nchw(torch.from_numpy(g["images_u8"]))
+    if not torch.cuda.is_available():         # the extractor lives on the GPU when there is one
+        feats = m.clip_feature_extractor(x)
+        assert float((feats - torch.from_numpy(g["clip_feats"])).abs().max()) <= 1e-4 * float(np.abs(g["clip_feats"]).max())
+    logits = unet_oracle.forward(sd, x, clip_feats=torch.from_numpy(g["clip_feats"]))
+    ref = torch.from_numpy(g["logits"])
+    assert float((logits - ref).abs().max()) <= 2e-5 * float(ref.abs().max())
+    with pytest.raises(RuntimeError):
+        m(x)                                  # no CPU path
+
+
 def test_dice_restatement_is_self_consistent():
     """Dice is PARITY UNPINNED (smp absent): only internal consistency can be checked."""
     g = torch.Generator().manual_seed(0)
