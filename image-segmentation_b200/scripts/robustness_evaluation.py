@@ -2,9 +2,9 @@
 levels, batch 8, soft Dice per batch averaged over batches, one CSV `results/robustness_scores.csv`
 with columns perturbation_type,param_value,mean_dice ("%.4f").
 
-Differences forced by this environment, both stated in DESIGN.md: the model is `UNet` (the reference
-script hard-codes ClipUnet, whose CLIP weights need the network) and the dataset is the synthetic
-stand-in unless a dataset object is passed.  Random families use the device RNG unless
+Differences forced by this environment, both stated in DESIGN.md: `main` defaults to `UNet` (the reference
+script hard-codes ClipUnet, whose CLIP weights need the network; `run_sweep` takes either model and
+`main(model_name="ClipUnet")` builds it) and the dataset is the synthetic stand-in unless a dataset object is passed.  Random families use the device RNG unless
 `parity_rng=True`, in which case the reference's host draws are replayed (slow for salt-and-pepper,
 as in the reference).  Multi-GPU: launch under torchrun; batches are sharded over ranks and rank 0
 writes the CSV.
@@ -99,7 +99,9 @@ def run_sweep(model, images_u8, masks_u8, results_file="results/robustness_score
     return rows
 
 
-def main(n_images=3680, checkpoint="saved-models/UNet/model.pth"):
+def main(n_images=3680, checkpoint="saved-models/UNet/model.pth", model_name="UNet", clip_model=None):
+    """model_name "UNet" (BASELINE.json's metric) or "ClipUnet" (what the reference script hard-codes, :36-42; needs the
+    openai/clip-vit-base-patch32 checkpoint in the HuggingFace cache, or a CLIPModel passed as `clip_model`)."""
     from ..models.UNet import UNet
     from ..synthetic import make_dataset
     if "RANK" in os.environ and not dist.is_initialized():
@@ -107,7 +109,11 @@ def main(n_images=3680, checkpoint="saved-models/UNet/model.pth"):
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
     device = torch.device("cuda", torch.cuda.current_device())
     torch.manual_seed(42)
-    model = UNet()
+    if model_name == "ClipUnet":
+        from ..models.CLIP_models import ClipUnet
+        model = ClipUnet(clip_model=clip_model)
+    else:
+        model = UNet()
     if os.path.exists(checkpoint):
         ckpt = torch.load(checkpoint, map_location="cpu")
         model.load_state_dict({k.replace("_orig_mod.", ""): v for k, v in ckpt.items()}, strict=False)
