@@ -136,6 +136,7 @@ def cpu_time_sample(sd, images, masks, levels, n_sample, reps):
     return n_sample * reps / dt, cores, dt
 
 
+CLIP = False             # --workload clipunet256: the model the reference's sweep script hard-codes (secondary)
 LARGE = False            # --workload large512: BASELINE.json configs[2] (LargeUNet, 512x512, 64 images per GPU)
 
 
@@ -149,12 +150,36 @@ def use_large_workload(world):
     GEMM_GFLOP_PER_IMAGE = 226.123 - 2 * (H * W * 3 * 32 * 2) / 1e9  # minus the two 1x1 convs
 
 
+def use_clip_workload():
+    """Secondary workload: ClipUnet on the headline sweep.  The CLIP ViT-B/32 embedding (random-init here: the
+    checkpoint needs the network) is HuggingFace transformers on PyTorch fp32 kernels, as in the reference, and is
+    inside the timed step; the library's share is the UNet minus the (dead) bottleneck block."""
+    global CLIP, GFLOP_PER_IMAGE, GEMM_GFLOP_PER_IMAGE
+    CLIP = True
+    GFLOP_PER_IMAGE = 45.391 - 2 * 3.624          # without bottleneck.conv.0/.3 (1.208 + 2.416 GMAC)
+    GEMM_GFLOP_PER_IMAGE = 2 * (21.744 - 3.624 + 0.940)
+
+
 def net_class():
     from image_segmentation_b200.models.UNet import LargeUNet, UNet
+    if CLIP:
+        from transformers import CLIPConfig, CLIPModel
+        from image_segmentation_b200.models.CLIP_models import ClipUnet
+        dt = torch.bfloat16 if os.environ.get("UB_CLIP_DTYPE") == "bf16" else None   # default fp32, as the reference
+        return lambda: ClipUnet(clip_model=CLIPModel(CLIPConfig()).eval(), clip_autocast_dtype=dt)
     return LargeUNet if LARGE else UNet
 
 
 def base_line(args, world):
+    if CLIP:
+        return {"metric": "ClipUnet 256x256 robustness-eval images/s", "unit": "images/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "data": "synthetic",
+                "config": {"workload": "robustness_evaluation sweep levels over 3,680 synthetic 256x256 RGB images, ClipUnet "
+                                       "random-init (CLIP ViT-B/32 random-init via transformers, "
+                                       + ("bf16 autocast" if os.environ.get("UB_CLIP_DTYPE") == "bf16" else "fp32") + ", inside the step), "
+                                       "reference batch 8", "images_per_step": N_IMAGES, "ref_batch": REF_BATCH,
+                           "l2": "inputs_exceed_l2 (965 MB of images+masks per step)"}}
     if LARGE:
         return {"metric": "LargeUNet 512x512 forward+metrics images/s", "unit": "images/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
@@ -291,7 +316,7 @@ def run_gpu(args, rank, world, local_rank):
     try:
         with open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")) as f:
             tr = json.load(f)
-        if not LARGE:
+        if not LARGE and not CLIP:
             per_launch_images = ev.n_local * 2 / max(gemm_launches, 1) * 20   # images per micro-batch in this run
             roofline["traffic"] = tr["dram_bytes_per_image"] * per_launch_images / 20
             roofline["traffic_source"] = (f"profiles/r01_ncu_traffic.json: dram read+write per image from an ncu --set full "
@@ -314,7 +339,7 @@ def run_gpu(args, rank, world, local_rank):
                          "steps": k_e2e},
                  "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
                  "whole_net_tflops": value * GFLOP_PER_IMAGE / 1e3, "microbatch": eng.max_microbatch})
-    if world == 1 and not args.no_cpu:
+    if world == 1 and not args.no_cpu and not CLIP:  # (no CPU leg for the secondary ClipUnet workload)
         lv = [("contrast_increase", 1.1), ("gaussian_blur", 5), ("gaussian_noise", 10), ("occlusion", 25)]
         n_cpu = 8 if LARGE else 64
         v, cores, dt = cpu_time_sample(sd_cpu, images[:n_cpu], masks[:n_cpu], lv, n_cpu, 4)
@@ -335,8 +360,8 @@ def main():
     ap.add_argument("--microbatch", type=int, default=None)
     ap.add_argument("--layers", action="store_true", help="print the per-layer GEMM times to stderr")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--workload", default="unet256", choices=["unet256", "large512"],
-                    help="unet256 = the headline (BASELINE.json configs[1]); large512 = configs[2], secondary")
+    ap.add_argument("--workload", default="unet256", choices=["unet256", "large512", "clipunet256"],
+                    help="unet256 = the headline (BASELINE.json configs[1]); large512 = configs[2]; clipunet256: secondary")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", 0))
@@ -344,7 +369,13 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
     if args.workload == "large512":
         use_large_workload(world)
+    if args.workload == "clipunet256":
+        use_clip_workload()
     if args.impl == "reference":
+        if CLIP:
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": "no CPU arm for the secondary clipunet256 workload"}))
+            return
         run_reference(args, rank, world)
         return
     import torch.distributed as dist
