@@ -341,6 +341,13 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   const bool resident = w_tile_bytes + 2 * 24576 <= 220 * 1024;  // mirrors choose_pipeline's weight-stationary test
   { const char* d = getenv("UB_DBG"); cp->dbg = d ? atoi(d) : 0; }
   cp->cg2 = (!ctx->no_cg2 && tw == 8 && L.bk == 64 && L.block_n >= 128 && mode != ub::EPI_HEAD && mode != ub::EPI_CONVT && !resident) ? 1 : 0;
+  // ConvTranspose whose n-tile does not fit one CTA but whose halves fit a pair (dec1.up: 512 -> 4 x 256): pairs, each
+  // keeping its half of ONE n-tile resident, pair-granular tile order (ub_conv_tc.cuh) so the activations hit L2
+  if (!ctx->no_cg2 && mode == ub::EPI_CONVT && L.ksize == 1 && L.bk == 64 && L.block_n == 256 && !resident &&
+      w_tile_bytes / 2 + 2 * 16384 <= 200 * 1024 && !getenv("UB_NO_PAIRQ")) {
+    cp->cg2 = 1;
+    cp->pairq = 1;
+  }
   if (ub::is_kxs(tw)) {
     if ((rc = make_tm_w(ctx, &cp->tmB, L.w_kxs, L.cin, 9 * L.cout, 3 * L.cout, L.bk))) return rc;
   } else {
@@ -444,12 +451,25 @@ int launch_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
 template <int N, int KS>
 int launch_pair(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   ConvParams cp = cp_in;
+  int smem = 0;
+  if constexpr (N == 256 && KS == 1) {
+    if (cp.pairq) {  // weight-stationary pairs over several n-tiles: the pair count is a multiple of n_tiles
+      const int n_tiles = cp.n_total / N;
+      const int pairs_total = n_tiles * ((((cp.W + 7) / 8) + 1) / 2) * ((cp.H + 15) / 16) * cp.B;
+      int pairs = ctx->num_sms / 2;
+      if (pairs > pairs_total) pairs = pairs_total;
+      const int pw = pairs - pairs % n_tiles;
+      if (pw >= n_tiles && choose_pipeline<N, 64, KS, 8, true>(&cp, pw, !ctx->force_stream, &smem))
+        return launch_kernel<N, 64, KS, true, 8, true>(ctx, cp, 2 * pw, smem, st);
+      choose_pipeline<N, 64, KS, 8, true>(&cp, pairs, false, &smem);  // tiny launch or UB_FORCE_STREAM: same order, streamed
+      return launch_kernel<N, 64, KS, false, 8, true>(ctx, cp, 2 * pairs, smem, st);
+    }
+  }
   const int per_img = ((cp.H + 15) / 16) * ((cp.W + 7) / 8);
   const int b_pad = cp.B + ((per_img * cp.B) & 1);
   const int tiles = per_img * b_pad * (cp.n_total / N);
   const int max_grid = ctx->num_sms & ~1;
   const int grid = tiles < max_grid ? tiles : max_grid;
-  int smem = 0;
   if constexpr (N == 128 && KS == 3) {  // one n-tile and the pair's halves fit: each CTA keeps its half of the weights resident
     if (choose_pipeline<N, 64, KS, 8, true>(&cp, grid, cp.n_total == N && !ctx->force_stream, &smem))
       return launch_kernel<N, 64, KS, true, 8, true>(ctx, cp, grid, smem, st);

@@ -62,18 +62,18 @@
   };
 
   int it = grp;
-  TileIter ti = tile_iter(blockIdx.x + grp * gridDim.x, kEpiGroups * gridDim.x);
+  TileIter ti = tile_iter(t_first + grp * t_step, kEpiGroups * t_step);
   // first image of the NEXT reference batch, relative to this micro-batch (HEAD): b only grows
-  int batch_now = (p.img_base + ti.d3) / p.ref_batch;
+  int batch_now = (p.img_base + tile_b(ti)) / p.ref_batch;
   int batch_end = (batch_now + 1) * p.ref_batch - p.img_base;
 #pragma unroll 1
-  for (int t = blockIdx.x + grp * gridDim.x; t < total_tiles; t += kEpiGroups * gridDim.x, it += kEpiGroups, ti.next()) {
+  for (int t = t_first + grp * t_step; t < total_tiles; t += kEpiGroups * t_step, it += kEpiGroups, ti.next()) {
     const int acc = it % ACC;
     const uint32_t use = static_cast<uint32_t>(it / ACC);
-    const int nt = CG2 ? ti.d3 : ti.d0;
-    const int x = (CG2 ? ti.d0 : ti.d1) * kXStep - (KXS ? 1 : 0) + tx;
-    const int y = (CG2 ? ti.d1 : ti.d2) * kTileRows + ty;
-    const int b = CG2 ? ti.d2 : ti.d3;
+    const int nt = tile_nt(ti);
+    const int x = tile_tx(ti) * kXStep - (KXS ? 1 : 0) + tx;
+    const int y = tile_ty(ti) * kTileRows + ty;
+    const int b = tile_b(ti);
     const bool inb = (y < p.H) && (x < p.W) && (!KXS || (tx >= 1 && tx <= TW - 2)) && (!CG2 || b < p.B);
     const int n0 = nt * BLOCK_N;
     int tgt_pre = -1;

@@ -94,6 +94,7 @@ struct ConvParams {
   float* logits_out;       // [B,C,H,W] or null
   // pipeline shape chosen by the host (ub_api.cu: choose_pipeline)
   int dbg; // UB_DBG bit mask (experiments only): 1 = epilogue only drains, 2 = no MMAs issued
+  int pairq;  // CTA pairs: pair-granular tile order with the n-tile fastest (weight-stationary pairs, n_tiles > 1)
   int cg2; // 1 = CTA-pair kernel (host: tmB box holds N/2 rows, even grid, cluster launch)
   int tw;  // tile width chosen by the host (8 standard, 16/32 kx-stacked); the kernel has it as a template parameter
   int sa;  // A stages (activation boxes)
@@ -229,15 +230,29 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   const int n_tiles = KXS ? 1 : p.n_total / BLOCK_N;
   // Tile order.  Standard: (n-tile, column, row, image), n-tile fastest.  CTA pairs: (column, row, image, n-tile)
   // with the image count padded so that tiles 2k and 2k+1 — the two CTAs of a pair — always share the n-tile.
-  const int b_pad = CG2 ? p.B + ((tiles_x * tiles_y * p.B) & 1) : p.B;
-  const int total_tiles = b_pad * tiles_x * tiles_y * n_tiles;
+  // CTA pairs with p.pairq (weight-stationary pairs, several n-tiles): the PAIR index runs over (n-tile, column
+  // pair, row, image), n-tile fastest, and CTA r of the pair takes column 2*pair_column + r; with the pair count a
+  // multiple of n_tiles every pair keeps one n-tile (its halves of the weights stay resident) while the n-tiles of
+  // one pixel tile are worked on by neighbouring pairs at the same time (the activations hit L2).
   const uint32_t cta_rank = CG2 ? cluster_ctarank() : 0u;
+  const bool pairq = CG2 && p.pairq;
+  const int tiles_xh = (tiles_x + 1) >> 1;
+  const int b_pad = (CG2 && !pairq) ? p.B + ((tiles_x * tiles_y * p.B) & 1) : p.B;
+  const int total_tiles = pairq ? n_tiles * tiles_xh * tiles_y * p.B : b_pad * tiles_x * tiles_y * n_tiles;
+  const int t_first = pairq ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int t_step = pairq ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
   auto tile_iter = [&](int t0, int stride) {
     TileIter ti;
-    if constexpr (CG2) ti.init(t0, stride, tiles_x, tiles_y, b_pad);
+    if (pairq) ti.init(t0, stride, n_tiles, tiles_xh, tiles_y);
+    else if constexpr (CG2) ti.init(t0, stride, tiles_x, tiles_y, b_pad);
     else ti.init(t0, stride, n_tiles, tiles_x, tiles_y);
     return ti;
   };
+  // tile coordinates from the iterator's digits: n-tile, tile column, tile row, image
+  auto tile_nt = [&](const TileIter& ti) { return (CG2 && !pairq) ? ti.d3 : ti.d0; };
+  auto tile_tx = [&](const TileIter& ti) { return pairq ? 2 * ti.d1 + static_cast<int>(cta_rank) : (CG2 ? ti.d0 : ti.d1); };
+  auto tile_ty = [&](const TileIter& ti) { return (CG2 && !pairq) ? ti.d1 : ti.d2; };
+  auto tile_b = [&](const TileIter& ti) { return (CG2 && !pairq) ? ti.d2 : ti.d3; };
 
   // ---------------- one-time setup (nothing here depends on the previous kernel's output)
   for (int i = threadIdx.x; i < p.n_bias; i += kConvThreads) s_bias[i] = p.bias[i];
@@ -272,7 +287,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     if constexpr (WS) {
       // weight-stationary: with gridDim a multiple of n_tiles every tile of this CTA has the same n-tile.
       // Weights are constants of the layer: their loads may precede the wait on the previous kernel.
-      const int nt = CG2 ? 0 : blockIdx.x % n_tiles;  // pairs: the host allows WS only when there is one n-tile
+      // every tile of this CTA (pair) has the same n-tile: the host makes the CTA (pair) count a multiple of n_tiles
+      const int nt = CG2 ? static_cast<int>(blockIdx.x >> 1) % n_tiles : static_cast<int>(blockIdx.x) % n_tiles;
       if (leader) {
         if constexpr (CG2) {
           // both halves are counted on the even CTA's barrier (its MMA warp is the only reader)
@@ -295,13 +311,13 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     pdl_wait_prior_grid();  // activations of the previous layer are complete and visible from here on
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
-    TileIter ti = tile_iter(blockIdx.x, gridDim.x);
+    TileIter ti = tile_iter(t_first, t_step);
 #pragma unroll 1
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ti.next()) {
-      const int nt = CG2 ? ti.d3 : ti.d0;
-      const int x0 = (CG2 ? ti.d0 : ti.d1) * kXStep - (KXS ? 1 : 0);  // input column of tile column 0
-      const int y0 = (CG2 ? ti.d1 : ti.d2) * kTileRows;
-      const int b = CG2 ? ti.d2 : ti.d3;  // may be the padding image (== B) of a CTA pair: TMA zero-fills
+    for (int t = t_first; t < total_tiles; t += t_step, ti.next()) {
+      const int nt = tile_nt(ti);
+      const int x0 = tile_tx(ti) * kXStep - (KXS ? 1 : 0);  // input column of tile column 0 (may lie past the image: zero fill)
+      const int y0 = tile_ty(ti) * kTileRows;
+      const int b = tile_b(ti);  // may be the padding image (== B) of a CTA pair: TMA zero-fills
 #pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
         mbar_wait(&a_empty[sa], pa ^ 1u);
@@ -371,7 +387,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     uint32_t pa = 0, pb = 0;
     int it = 0;
 #pragma unroll 1
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+    for (int t = t_first; t < total_tiles; t += t_step, ++it) {
       const int acc = it % ACC;
       const uint32_t use = static_cast<uint32_t>(it / ACC);
       mbar_wait(&t_empty[acc], (use & 1u) ^ 1u);
