@@ -114,15 +114,24 @@
       tmem_ld_32x32(t_addr + static_cast<uint32_t>(CO + ch), sum);
       tmem_ld_32x32(t_addr + static_cast<uint32_t>(ch), d);
       tmem_ld_wait();
+      // the adds are packed fp32x2 (add.rn.f32x2: two IEEE adds per issue slot — these epilogues are issue-bound)
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
-        sum[j] = __float_as_uint(__uint_as_float(sum[j]) + __shfl_up_sync(0xffffffffu, __uint_as_float(d[j]), 1, TW));
+      for (int j = 0; j < 32; j += 2) {
+        const float2 nb = make_float2(__shfl_up_sync(0xffffffffu, __uint_as_float(d[j]), 1, TW),
+                                      __shfl_up_sync(0xffffffffu, __uint_as_float(d[j + 1]), 1, TW));
+        const float2 a = __fadd2_rn(make_float2(__uint_as_float(sum[j]), __uint_as_float(sum[j + 1])), nb);
+        sum[j] = __float_as_uint(a.x); sum[j + 1] = __float_as_uint(a.y);
+      }
       tmem_ld_32x32(t_addr + static_cast<uint32_t>(2 * CO + ch), d);
       tmem_ld_wait();
       if (last) release_acc();
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
-        sum[j] = __float_as_uint(__uint_as_float(sum[j]) + __shfl_down_sync(0xffffffffu, __uint_as_float(d[j]), 1, TW));
+      for (int j = 0; j < 32; j += 2) {
+        const float2 nb = make_float2(__shfl_down_sync(0xffffffffu, __uint_as_float(d[j]), 1, TW),
+                                      __shfl_down_sync(0xffffffffu, __uint_as_float(d[j + 1]), 1, TW));
+        const float2 a = __fadd2_rn(make_float2(__uint_as_float(sum[j]), __uint_as_float(sum[j + 1])), nb);
+        sum[j] = __float_as_uint(a.x); sum[j + 1] = __float_as_uint(a.y);
+      }
     };
 
     if (p.dbg & 1) {
@@ -228,24 +237,23 @@
           px = 2 * x + (q & 1);
           cg = p.out_cg0 + (bias_off >> 3);
         }
-        float v[32];
+        // bias: packed fp32x2 adds.  bf16 rounding is monotone and keeps the sign, so ReLU and max-pool commute with
+        // it: pack first, then ReLU (max with +0) and pool on the packed pairs — half the instructions, same result.
+        uint32_t pk[16];
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
           const float4 bz = *reinterpret_cast<const float4*>(s_bias + bias_off + 4 * j4);
-          v[4 * j4 + 0] = __uint_as_float(r[4 * j4 + 0]) + bz.x;
-          v[4 * j4 + 1] = __uint_as_float(r[4 * j4 + 1]) + bz.y;
-          v[4 * j4 + 2] = __uint_as_float(r[4 * j4 + 2]) + bz.z;
-          v[4 * j4 + 3] = __uint_as_float(r[4 * j4 + 3]) + bz.w;
+          const float2 a = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 0]), __uint_as_float(r[4 * j4 + 1])),
+                                      make_float2(bz.x, bz.y));
+          const float2 c = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 2]), __uint_as_float(r[4 * j4 + 3])),
+                                      make_float2(bz.z, bz.w));
+          pk[2 * j4 + 0] = pack_bf16(a.x, a.y);
+          pk[2 * j4 + 1] = pack_bf16(c.x, c.y);
         }
         if (p.relu) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+          for (int j = 0; j < 16; ++j) pk[j] = bf16x2_max(pk[j], 0u);
         }
-        // bf16 rounding is monotone, so max(bf16(a), bf16(b)) == bf16(max(a, b)): pack first, then pool the
-        // packed pairs (half the shuffles and half the max instructions of an fp32 pool, same result)
-        uint32_t pk[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
         if (p.mode == EPI_POOL) {
           // 2x2 max as a reduce-scatter over the four lanes of a pooling window: stage 1 trades HALF of the packed
           // registers with the x-partner, stage 2 a quarter with the y-partner; every lane ends with one channel
@@ -310,10 +318,15 @@
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
             const float4 bz = *reinterpret_cast<const float4*>(s_bias + cb + 4 * j4);
-            pa[2 * j4 + 0] = pack_bf16(__uint_as_float(ra[4 * j4 + 0]) + bz.x, __uint_as_float(ra[4 * j4 + 1]) + bz.y);
-            pa[2 * j4 + 1] = pack_bf16(__uint_as_float(ra[4 * j4 + 2]) + bz.z, __uint_as_float(ra[4 * j4 + 3]) + bz.w);
-            pb[2 * j4 + 0] = pack_bf16(__uint_as_float(rb[4 * j4 + 0]) + bz.x, __uint_as_float(rb[4 * j4 + 1]) + bz.y);
-            pb[2 * j4 + 1] = pack_bf16(__uint_as_float(rb[4 * j4 + 2]) + bz.z, __uint_as_float(rb[4 * j4 + 3]) + bz.w);
+            const float2 b01 = make_float2(bz.x, bz.y), b23 = make_float2(bz.z, bz.w);
+            auto add_pack = [](uint32_t r0, uint32_t r1, float2 bb) {
+              const float2 t = __fadd2_rn(make_float2(__uint_as_float(r0), __uint_as_float(r1)), bb);
+              return pack_bf16(t.x, t.y);
+            };
+            pa[2 * j4 + 0] = add_pack(ra[4 * j4 + 0], ra[4 * j4 + 1], b01);
+            pa[2 * j4 + 1] = add_pack(ra[4 * j4 + 2], ra[4 * j4 + 3], b23);
+            pb[2 * j4 + 0] = add_pack(rb[4 * j4 + 0], rb[4 * j4 + 1], b01);
+            pb[2 * j4 + 1] = add_pack(rb[4 * j4 + 2], rb[4 * j4 + 3], b23);
           }
           if (inb) {
             uint4* dst = reinterpret_cast<uint4*>(p.out) +
