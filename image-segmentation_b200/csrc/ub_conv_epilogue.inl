@@ -157,14 +157,23 @@
       float z[kMaxClasses];
 #pragma unroll
         for (int c = 0; c < kMaxClasses; ++c) z[c] = (c < C) ? p.head_b[c] : -INFINITY;
+        // packed fp32x2 arithmetic (two IEEE operations per issue slot): even and odd input channels accumulate
+        // separately and are added at the end
+        float2 z2[kMaxClasses];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float v = __uint_as_float(r[j]) + p.bias32[j];
-          v = p.relu ? fmaxf(v, 0.0f) : v;
+        for (int c = 0; c < kMaxClasses; ++c) z2[c] = make_float2(z[c], 0.0f);
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          float2 v = __fadd2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])),
+                                make_float2(p.bias32[j], p.bias32[j + 1]));
+          if (p.relu) { v.x = fmaxf(v.x, 0.0f); v.y = fmaxf(v.y, 0.0f); }
 #pragma unroll
           for (int c = 0; c < kMaxClasses; ++c)
-            if (c < C) z[c] = fmaf(p.head_w[c * 32 + j], v, z[c]);
+            if (c < C) z2[c] = __ffma2_rn(make_float2(p.head_w[c * 32 + j], p.head_w[c * 32 + j + 1]), v, z2[c]);
         }
+#pragma unroll
+        for (int c = 0; c < kMaxClasses; ++c)
+          if (c < C) z[c] = z2[c].x + z2[c].y;
         // softmax (models/losses.py:48), then first-index argmax (:50)
         float zmax = z[0];
 #pragma unroll
