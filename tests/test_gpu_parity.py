@@ -432,3 +432,26 @@ def test_clipunet_evaluator_embeds_the_perturbed_image(clipunet, dev):
     agree = float((unet_oracle.hard_prediction(ref) == res["pred"].cpu().long()).float().mean())
     print(f"ClipUnet evaluator: argmax agreement with the oracle {agree:.4f}")
     assert agree > 0.97 and util.rel_err(res["logits"].cpu(), ref) < 2e-2
+
+
+@pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_NO_CG2", "UB_NO_PDL"])
+def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
+    """The diagnostic switches select other kernels for the same layers (streamed weights, 9-tap thin layers, single
+    CTAs, plain launches); they must stay correct: same logits within bf16 accumulation-order noise, same
+    predictions except at near-ties."""
+    from image_segmentation_b200 import runtime, synthetic
+    m, sd = trained
+    imgs, _ = synthetic.make_dataset(3, 64, 128, seed=17)
+    x = synthetic.to_float_nchw(imgs).to(dev)
+    base = m.engine(dev).forward(x)
+    monkeypatch.setenv(flag, "1")
+    eng = runtime.new_engine(dev, "unet", 3, 3, 8)   # the switches are read when the context is created
+    try:
+        eng.load_state_dict(m.state_dict())
+        eng.set_layer_couts(m.layer_couts())
+        alt = eng.forward(x)
+    finally:
+        eng.close()
+    assert util.rel_err(alt.cpu(), base.cpu()) < 5e-3
+    agree = float((alt.argmax(1) == base.argmax(1)).float().mean())
+    assert agree > 0.999, (flag, agree)
