@@ -259,7 +259,7 @@
           pk[2 * j4 + 0] = pack_bf16(a.x, a.y);
           pk[2 * j4 + 1] = pack_bf16(c.x, c.y);
         }
-        if (p.relu) {
+        if (p.relu && p.mode != EPI_POOL) {  // (pooled layers: ReLU commutes with max, applied to the pooled quarter below)
 #pragma unroll
           for (int j = 0; j < 16; ++j) pk[j] = bf16x2_max(pk[j], 0u);
         }
@@ -280,6 +280,7 @@
           for (int j = 0; j < 4; ++j) {
             const uint32_t send = sy ? m[j] : m[4 + j], keep = sy ? m[4 + j] : m[j];
             q[j] = bf16x2_max(keep, __shfl_xor_sync(0xffffffffu, send, KXS ? 16 : 8));
+            if (p.relu) q[j] = bf16x2_max(q[j], 0u);
           }
           if (writer) {
             const int g = (sx ? 2 : 0) + (sy ? 1 : 0);
