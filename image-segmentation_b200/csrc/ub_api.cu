@@ -89,6 +89,8 @@ struct ub_ctx {
   // optional per-launch timing (ub_profile_begin/end): event pairs around every GEMM launch
   bool force_stream = false;  // UB_FORCE_STREAM=1: never use the weight-stationary pipeline (tests)
   bool use_pdl = true;        // UB_NO_PDL=1: plain stream-ordered launches
+  bool no_pairq = false;      // UB_NO_PAIRQ=1: the big ConvTranspose runs as single CTAs with streamed weights
+  int dbg = 0;                // UB_DBG: ablation hooks of conv_tc_kernel (1 = drain-only epilogue, 2 = no MMA)
   bool no_kxs = false;        // UB_NO_KXS=1: thin layers run the standard (9-tap) kernel
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool profiling = false;
@@ -339,12 +341,12 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   // CTA pairs (cta_group::2) for the wide layers whose weights cannot stay resident in shared memory
   const size_t w_tile_bytes = static_cast<size_t>(L.ksize) * L.ksize * L.cin * L.block_n * 2;
   const bool resident = w_tile_bytes + 2 * 24576 <= 220 * 1024;  // mirrors choose_pipeline's weight-stationary test
-  { const char* d = getenv("UB_DBG"); cp->dbg = d ? atoi(d) : 0; }
+  cp->dbg = ctx->dbg;
   cp->cg2 = (!ctx->no_cg2 && tw == 8 && L.bk == 64 && L.block_n >= 128 && mode != ub::EPI_HEAD && mode != ub::EPI_CONVT && !resident) ? 1 : 0;
   // ConvTranspose whose n-tile does not fit one CTA but whose halves fit a pair (dec1.up: 512 -> 4 x 256): pairs, each
   // keeping its half of ONE n-tile resident, pair-granular tile order (ub_conv_tc.cuh) so the activations hit L2
   if (!ctx->no_cg2 && mode == ub::EPI_CONVT && L.ksize == 1 && L.bk == 64 && L.block_n == 256 && !resident &&
-      w_tile_bytes / 2 + 2 * 16384 <= 200 * 1024 && !getenv("UB_NO_PAIRQ")) {
+      w_tile_bytes / 2 + 2 * 16384 <= 200 * 1024 && !ctx->no_pairq) {
     cp->cg2 = 1;
     cp->pairq = 1;
   }
@@ -816,6 +818,8 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   ctx->use_pdl = !(np && np[0] == '1');
   const char* nk = getenv("UB_NO_KXS");
   ctx->no_kxs = nk && nk[0] == '1';
+  { const char* e = getenv("UB_NO_PAIRQ"); ctx->no_pairq = e && e[0] == '1'; }
+  { const char* e = getenv("UB_DBG"); ctx->dbg = e ? atoi(e) : 0; }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();

@@ -434,7 +434,7 @@ def test_clipunet_evaluator_embeds_the_perturbed_image(clipunet, dev):
     assert agree > 0.97 and util.rel_err(res["logits"].cpu(), ref) < 2e-2
 
 
-@pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_NO_CG2", "UB_NO_PDL"])
+@pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL"])
 def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     """The diagnostic switches select other kernels for the same layers (streamed weights, 9-tap thin layers, single
     CTAs, plain launches); they must stay correct: same logits within bf16 accumulation-order noise, same
