@@ -18,11 +18,14 @@
   // soft-Dice partial sums); they are reduced (warp shuffle -> shared memory -> global atomics) only
   // when the reference batch changes, every kFlushTiles tiles, and once at the end.
   constexpr int kCells = kMaxClasses * kMaxClasses;
-  constexpr int kFlushTiles = 4096;
-  uint32_t cnt[kCells];
+  constexpr int kFlushTiles = 250;  // < 255: the packed 8-bit count fields cannot overflow between flushes
+  // counts of target class t live in pk[t]: kMaxClasses 8-bit fields indexed by the prediction (4 registers
+  // instead of 16, one shift and kMaxClasses predicated adds per pixel)
+  static_assert(kMaxClasses * 8 <= 32, "packed count fields");
+  uint32_t pk[kMaxClasses];
   float dsum[2 * kMaxClasses];
 #pragma unroll
-  for (int i = 0; i < kCells; ++i) cnt[i] = 0u;
+  for (int i = 0; i < kMaxClasses; ++i) pk[i] = 0u;
 #pragma unroll
   for (int i = 0; i < 2 * kMaxClasses; ++i) dsum[i] = 0.0f;
   int tiles_since_flush = 0;
@@ -30,12 +33,13 @@
     const int C = p.n_classes;
 #pragma unroll
     for (int i = 0; i < kCells; ++i) {
-      uint32_t v = cnt[i];
+      uint32_t v = (pk[i / kMaxClasses] >> (8 * (i % kMaxClasses))) & 255u;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if (lane == 0 && v) atomicAdd(&s_cm[i], static_cast<unsigned long long>(v));
-      cnt[i] = 0u;
     }
+#pragma unroll
+    for (int i = 0; i < kMaxClasses; ++i) pk[i] = 0u;
     if (p.dice) {
 #pragma unroll
       for (int i = 0; i < 2 * kMaxClasses; ++i) {
@@ -174,19 +178,41 @@
 #pragma unroll
         for (int c = 0; c < kMaxClasses; ++c)
           if (c < C) z[c] = z2[c].x + z2[c].y;
-        // softmax (models/losses.py:48), then first-index argmax (:50)
+        // argmax(softmax(z)) with the first index winning ties (models/losses.py:48,50).  When the largest logit
+        // leads the runner-up by more than 1e-4 the softmax cannot change the order: e_best = expf(0) = 1 exactly and
+        // every other e_c <= expf(-1e-4) < 1 - 9e-5, far more than the rounding of the division by the common sum, so
+        // pr_best > pr_c strictly and the prediction is the (unique) argmax of z.  Only near-ties, non-finite logits
+        // and the soft-Dice sums (which need the probabilities) evaluate the softmax itself.
         float zmax = z[0];
 #pragma unroll
         for (int c = 1; c < kMaxClasses; ++c) zmax = fmaxf(zmax, z[c]);
-        float pr[kMaxClasses], psum = 0.0f;
-#pragma unroll
-        for (int c = 0; c < kMaxClasses; ++c) { pr[c] = (c < C) ? expf(z[c] - zmax) : 0.0f; psum += pr[c]; }
         int pred = 0;
-        float best = -1.0f;
+        float second = -INFINITY;
+        if constexpr (NC == 3) {
+          const float m12 = fmaxf(z[1], z[2]), m02 = fmaxf(z[0], z[2]), m01 = fmaxf(z[0], z[1]);
+          pred = (z[0] == zmax) ? 0 : ((z[1] == zmax) ? 1 : 2);
+          second = (pred == 0) ? m12 : ((pred == 1) ? m02 : m01);
+        } else {
 #pragma unroll
-        for (int c = 0; c < kMaxClasses; ++c) {
-          pr[c] = pr[c] / psum;
-          if (c < C && pr[c] > best) { best = pr[c]; pred = c; }
+          for (int c = kMaxClasses - 1; c >= 0; --c) if (c < C && z[c] == zmax) pred = c;
+#pragma unroll
+          for (int c = 0; c < kMaxClasses; ++c) if (c < C && c != pred) second = fmaxf(second, z[c]);
+        }
+        const float gap = zmax - second;
+        const bool decisive = (gap > 1e-4f) && (gap <= 3.0e38f) && !(p.dbg & 8);  // false for NaN / infinite logits
+        float pr[kMaxClasses];
+        if (!decisive || p.dice) {
+          float psum = 0.0f;
+#pragma unroll
+          for (int c = 0; c < kMaxClasses; ++c) { pr[c] = (c < C) ? expf(z[c] - zmax) : 0.0f; psum += pr[c]; }
+          int pred_s = 0;
+          float best = -1.0f;
+#pragma unroll
+          for (int c = 0; c < kMaxClasses; ++c) {
+            pr[c] = pr[c] / psum;
+            if (c < C && pr[c] > best) { best = pr[c]; pred_s = c; }
+          }
+          pred = pred_s;
         }
         const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
         if (inb) {
@@ -199,11 +225,10 @@
         }
         if (p.targets) {
           const int tgt = (tgt_pre >= 0 && tgt_pre < C) ? tgt_pre : -1;
+          const uint32_t inc = 1u << (8 * pred);
 #pragma unroll
           for (int tc = 0; tc < kMaxClasses; ++tc)
-#pragma unroll
-            for (int pc = 0; pc < kMaxClasses; ++pc)
-              if (tc < C && pc < C) cnt[tc * kMaxClasses + pc] += (tgt == tc && pred == pc) ? 1u : 0u;
+            if (tc < C) pk[tc] += (tgt == tc) ? inc : 0u;
           if (p.dice) {
             // smp DiceLoss(from_logits=True) applies softmax again to the softmax output (losses.py:100)
             float q[kMaxClasses], qmax = pr[0], qsum = 0.0f;
