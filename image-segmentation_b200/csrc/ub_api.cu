@@ -47,7 +47,7 @@ struct GemmLayer {
 };
 
 struct Step {
-  enum Kind { GEMM, RESAMPLE, CLIP_FUSE } kind = GEMM;  // CLIP_FUSE reuses rs_out / ho / wo / c
+  enum Kind { GEMM, RESAMPLE, CLIP_FUSE, PROMPT_STEM } kind = GEMM;  // CLIP_FUSE / PROMPT_STEM reuse rs_out / ho / wo / c / out_cgs
   int layer = -1;
   ConvParams cp;   // GEMM: tensor maps + static params (B patched per launch)
   // RESAMPLE
@@ -90,14 +90,16 @@ struct ub_ctx {
   bool force_stream = false;  // UB_FORCE_STREAM=1: never use the weight-stationary pipeline (tests)
   bool use_pdl = true;        // UB_NO_PDL=1: plain stream-ordered launches
   bool no_pairq = false;      // UB_NO_PAIRQ=1: the big ConvTranspose runs as single CTAs with streamed weights
-  int dbg = 0;                // UB_DBG: ablation hooks of conv_tc_kernel (1 = drain-only epilogue, 2 = no MMA)
+  int dbg = 0;                // UB_DBG: ablation hooks of conv_tc_kernel (1 = drain-only epilogue, 2 = no MMA, 8 = head always evaluates the softmax)
   bool no_kxs = false;        // UB_NO_KXS=1: thin layers run the standard (9-tap) kernel
+  bool head_no_kxs = false;   // UB_HEAD_NO_KXS=1: only the head layer (dec4.conv.3) runs the 9-tap kernel
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool profiling = false;
   struct ProfRec { int layer; cudaEvent_t a, b; };
   std::vector<ProfRec> prof;
   std::vector<cudaEvent_t> event_pool;
   std::vector<void*> owned;  // device allocations freed in ub_destroy
+  bool has_clip() const { return arch == UB_ARCH_CLIP_UNET || arch == UB_ARCH_CLIP_UNET_PROMPT; }
 };
 
 namespace {
@@ -149,7 +151,10 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   GemmLayer L;
   L.key = conv_key;
   L.cout = static_cast<int>(w->shape[0]);
-  L.cin = static_cast<int>(w->shape[1]);
+  const int cin_w = static_cast<int>(w->shape[1]);
+  // a layer with fewer than 32 input channels (the PromptEncoder's first conv, Cin = 1) reads a zero-padded
+  // 32-channel operand: the extra weight columns are zero
+  L.cin = cin_w < 32 ? 32 : cin_w;
   L.n_total = L.cout;
   L.ksize = 3;
   L.block_n = pick_block_n(L.n_total);
@@ -157,15 +162,15 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   if (L.cin % 32 != 0 || L.cout % 32 != 0)
     return fail(ctx, UB_ERR_UNSUPPORTED, "%s: channel counts must be multiples of 32", conv_key.c_str());
   const size_t K = static_cast<size_t>(9) * L.cin;
-  std::vector<__nv_bfloat16> packed(static_cast<size_t>(L.cout) * K);
+  std::vector<__nv_bfloat16> packed(static_cast<size_t>(L.cout) * K, __float2bfloat16(0.0f));
   std::vector<float> bias(L.cout);
   for (int co = 0; co < L.cout; ++co) {
     const double s = static_cast<double>(g->data[co]) / std::sqrt(static_cast<double>(var->data[co]) + 1e-5);
     bias[co] = static_cast<float>((static_cast<double>(b->data[co]) - mu->data[co]) * s + be->data[co]);
-    for (int ci = 0; ci < L.cin; ++ci)
+    for (int ci = 0; ci < cin_w; ++ci)
       for (int t = 0; t < 9; ++t)
         packed[co * K + static_cast<size_t>(t) * L.cin + ci] =
-            __float2bfloat16(static_cast<float>(w->data[(static_cast<size_t>(co) * L.cin + ci) * 9 + t] * s));
+            __float2bfloat16(static_cast<float>(w->data[(static_cast<size_t>(co) * cin_w + ci) * 9 + t] * s));
   }
   int rc;
   if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.w), packed.size() * 2))) return rc;
@@ -224,6 +229,38 @@ int pack_convt(ub_ctx* ctx, const std::string& key) {
   return UB_OK;
 }
 
+// Plain Conv2d(k=1) with bias, no BatchNorm, no activation (prompt_segmentation.py:53 `prompt_fusion`): GEMM B operand
+// W2[co][ci], stored by the STORE epilogue.
+int pack_conv1x1(ub_ctx* ctx, const std::string& key) {
+  const HostTensor* w = find(ctx, key + ".weight");
+  const HostTensor* b = find(ctx, key + ".bias");
+  if (!w || !b) return fail(ctx, UB_ERR_INVALID, "missing state_dict entries for %s", key.c_str());
+  if (w->shape.size() != 4 || w->shape[2] != 1 || w->shape[3] != 1)
+    return fail(ctx, UB_ERR_INVALID, "%s.weight is not [Cout,Cin,1,1]", key.c_str());
+  GemmLayer L;
+  L.key = key;
+  L.cout = static_cast<int>(w->shape[0]);
+  L.cin = static_cast<int>(w->shape[1]);
+  L.n_total = L.cout;
+  L.ksize = 1;
+  L.relu = 0;
+  L.block_n = pick_block_n(L.n_total);
+  L.bk = (L.cin % 64 == 0) ? 64 : 32;
+  if (L.cin % 32 != 0 || L.cout % 32 != 0)
+    return fail(ctx, UB_ERR_UNSUPPORTED, "%s: channel counts must be multiples of 32", key.c_str());
+  std::vector<__nv_bfloat16> packed(w->data.size());
+  for (size_t i = 0; i < w->data.size(); ++i) packed[i] = __float2bfloat16(w->data[i]);
+  int rc;
+  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.w), packed.size() * 2))) return rc;
+  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), b->data.size() * 4))) return rc;
+  UB_CUDA(ctx, cudaMemcpy(L.w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
+  UB_CUDA(ctx, cudaMemcpy(L.bias, b->data.data(), b->data.size() * 4, cudaMemcpyHostToDevice));
+  L.h_bias = b->data;
+  ctx->layer_by_key[L.key] = static_cast<int>(ctx->layers.size());
+  ctx->layers.push_back(L);
+  return UB_OK;
+}
+
 int pack_all(ub_ctx* ctx) {
   int rc;
   const HostTensor* sw = find(ctx, "input.weight");
@@ -249,7 +286,18 @@ int pack_all(ub_ctx* ctx) {
     if ((rc = pack_conv(ctx, std::string(k) + ".0", std::string(k) + ".1"))) return rc;
     if ((rc = pack_conv(ctx, std::string(k) + ".3", std::string(k) + ".4"))) return rc;
   }
-  if (ctx->arch == UB_ARCH_CLIP_UNET) {
+  if (ctx->arch == UB_ARCH_CLIP_UNET_PROMPT) {
+    // PromptEncoder (prompt_segmentation.py:16-29): three ConvBlockDownsample stages and a ConvBlock, then prompt_fusion
+    for (int i = 1; i <= 3; ++i) {
+      snprintf(k, sizeof(k), "prompt_encoder.enc%d.block.0.conv", i);
+      if ((rc = pack_conv(ctx, std::string(k) + ".0", std::string(k) + ".1"))) return rc;
+      if ((rc = pack_conv(ctx, std::string(k) + ".3", std::string(k) + ".4"))) return rc;
+    }
+    if ((rc = pack_conv(ctx, "prompt_encoder.conv.conv.0", "prompt_encoder.conv.conv.1"))) return rc;
+    if ((rc = pack_conv(ctx, "prompt_encoder.conv.conv.3", "prompt_encoder.conv.conv.4"))) return rc;
+    if ((rc = pack_conv1x1(ctx, "prompt_fusion"))) return rc;
+  }
+  if (ctx->has_clip()) {
     // the bottleneck ConvBlock's output is dead in ClipUnet.forward (CLIP_models.py:124-126): its weights are not packed
     const int E = 2 * 32 * (1 << ctx->n_enc);  // bottleneck width = embed_dim of the fusion (512)
     const HostTensor* ipw = find(ctx, "cross_attention_fusion.cross_attn.in_proj_weight");
@@ -327,6 +375,7 @@ int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total,
 // Tile geometry of a layer: the thin 3x3 layers run kx-stacked (32-pixel-wide tiles, 16 when the pool is fused).
 int pick_tw(const ub_ctx* ctx, const GemmLayer& L, int mode) {
   if (ctx->no_kxs || !L.w_kxs || L.ksize != 3 || mode == ub::EPI_CONVT) return 8;
+  if (ctx->head_no_kxs && mode == ub::EPI_HEAD) return 8;
   if (L.bk == 32 && mode != ub::EPI_HEAD) return 8;  // Cin = 32: only the head layer gains (enc1.conv.0 is write-bound)
   return mode == ub::EPI_POOL ? 16 : 32;
 }
@@ -570,6 +619,19 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
     i_da[j] = want(static_cast<size_t>(MB) * hl(l) * wl(l) * skip_width(l) * 2);
     i_db[j] = want(static_cast<size_t>(MB) * hl(l) * wl(l) * skip_width(l) * 2);
   }
+  // ClipUnetPrompt: the PromptEncoder's activations (32 -> 32 -> 64 -> 128 channels at H .. H/8) and the 1024-channel
+  // concat [attention output | prompt embedding] that prompt_fusion reads
+  const bool prompt = ctx->arch == UB_ARCH_CLIP_UNET_PROMPT;
+  size_t i_p0 = 0, i_pa[4] = {0, 0, 0, 0}, i_pb[4] = {0, 0, 0, 0}, i_pcat = 0;
+  if (prompt) {
+    if (n != 3) return fail(ctx, UB_ERR_UNSUPPORTED, "ClipUnetPrompt has three encoder stages");
+    i_p0 = want(static_cast<size_t>(MB) * H * W * 32 * 2);
+    for (int i = 1; i <= 3; ++i) {
+      i_pa[i] = want(static_cast<size_t>(MB) * hl(i - 1) * wl(i - 1) * (16 << i) * 2);  // conv.0 output at the input resolution
+      i_pb[i] = want(static_cast<size_t>(MB) * hl(i) * wl(i) * (16 << i) * 2);          // pooled
+    }
+    i_pcat = want(static_cast<size_t>(MB) * hl(n) * wl(n) * 2 * cb * 2);
+  }
   const size_t img_bytes = static_cast<size_t>(MB) * 3 * H * W * 4;
   const size_t i_pert = want(img_bytes), i_bla = want(img_bytes), i_blb = want(img_bytes);
   size_t total = 0;
@@ -616,8 +678,32 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
     // ClipUnet: dec1's input is the cross-attention fusion of the CLIP embedding, broadcast over the grid
     Step s;
     s.kind = Step::CLIP_FUSE;
-    s.rs_out = bufp(i_bb); s.ho = hl(n); s.wo = wl(n); s.c = cb;
+    s.rs_out = bufp(i_bb); s.ho = hl(n); s.wo = wl(n); s.c = cb; s.out_cgs = cb / 8;
     pl->steps.push_back(s);
+  } else if (prompt) {
+    // ClipUnetPrompt (prompt_segmentation.py:76-86): PromptEncoder over the heat-map, cross-attention fusion of the CLIP
+    // embedding into planes [0, cb/8) and the prompt embedding into planes [cb/8, 2cb/8) of one buffer
+    // (= cat([attention_output, prompt_embedding], dim=1)), then the 1x1 prompt_fusion -> dec1's input
+    Step s0;
+    s0.kind = Step::PROMPT_STEM;
+    s0.rs_out = bufp(i_p0); s0.ho = H; s0.wo = W; s0.out_cgs = 4;
+    pl->steps.push_back(s0);
+    const __nv_bfloat16* px = bufp(i_p0);
+    int pc = 32;
+    for (int i = 1; i <= 3; ++i) {
+      const int co = 16 << i;
+      snprintf(k, sizeof(k), "prompt_encoder.enc%d.block.0.conv", i);
+      if ((rc = add_gemm(std::string(k) + ".0", px, pc / 8, hl(i - 1), wl(i - 1), ub::EPI_STORE, bufp(i_pa[i]), co / 8, 0))) return rc;
+      if ((rc = add_gemm(std::string(k) + ".3", bufp(i_pa[i]), co / 8, hl(i - 1), wl(i - 1), ub::EPI_POOL, bufp(i_pb[i]), co / 8, 0))) return rc;
+      px = bufp(i_pb[i]); pc = co;
+    }
+    if ((rc = add_gemm("prompt_encoder.conv.conv.0", px, pc / 8, hl(n), wl(n), ub::EPI_STORE, bufp(i_ba), cb / 8, 0))) return rc;
+    if ((rc = add_gemm("prompt_encoder.conv.conv.3", bufp(i_ba), cb / 8, hl(n), wl(n), ub::EPI_STORE, bufp(i_pcat), 2 * cb / 8, cb / 8))) return rc;
+    Step s;
+    s.kind = Step::CLIP_FUSE;
+    s.rs_out = bufp(i_pcat); s.ho = hl(n); s.wo = wl(n); s.c = cb; s.out_cgs = 2 * cb / 8;
+    pl->steps.push_back(s);
+    if ((rc = add_gemm("prompt_fusion", bufp(i_pcat), 2 * cb / 8, hl(n), wl(n), ub::EPI_STORE, bufp(i_bb), cb / 8, 0))) return rc;
   } else {
     if ((rc = add_gemm("bottleneck.conv.0", skip_half(n), 2 * skip_width(n) / 8, hl(n), wl(n), ub::EPI_STORE,
                        bufp(i_ba), cb / 8, 0))) return rc;
@@ -706,7 +792,8 @@ int run_blur(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* img, in
 struct HeadArgs {
   const void* targets = nullptr; int target_fmt = 0; int ref_batch = 1; int img_base = 0;
   unsigned long long* cm = nullptr; double* dice = nullptr; uint8_t* pred = nullptr; float* logits = nullptr;
-  const float* clip = nullptr;  // UB_ARCH_CLIP_UNET: this micro-batch's CLIP embeddings [nb, 512]
+  const float* clip = nullptr;  // UB_ARCH_CLIP_UNET(_PROMPT): this micro-batch's CLIP embeddings [nb, 512]
+  const float* prompt = nullptr;  // UB_ARCH_CLIP_UNET_PROMPT: this micro-batch's prompt heat-maps [nb, 1, H, W]
 };
 
 // One micro-batch: perturb+stem, then every planned step.
@@ -732,7 +819,15 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
     if (s.kind == Step::CLIP_FUSE) {
       if (!ha.clip) return fail(ctx, UB_ERR_INVALID, "this model needs CLIP embeddings: call ub_eval_batches_clip");
       ub::clip_fusion_broadcast_kernel<<<nb, 512, 2 * s.c * sizeof(float), st>>>(
-          ha.clip, ctx->fuse_wv_t, ctx->fuse_bv, ctx->fuse_wo_t, ctx->fuse_bo, s.rs_out, s.c, s.ho * s.wo);
+          ha.clip, ctx->fuse_wv_t, ctx->fuse_bv, ctx->fuse_wo_t, ctx->fuse_bo, s.rs_out, s.c, s.ho * s.wo, s.out_cgs);
+      UB_CUDA(ctx, cudaGetLastError());
+      ctx->launches++;
+      continue;
+    }
+    if (s.kind == Step::PROMPT_STEM) {
+      if (!ha.prompt) return fail(ctx, UB_ERR_INVALID, "this model needs a prompt heat-map: call ub_forward_prompt");
+      const size_t hw1 = static_cast<size_t>(s.ho) * s.wo;
+      ub::prompt_stem_kernel<<<blocks_for(hw1 * nb, 256), 256, 0, st>>>(ha.prompt, hw1, nb, s.rs_out, s.out_cgs);
       UB_CUDA(ctx, cudaGetLastError());
       ctx->launches++;
       continue;
@@ -791,7 +886,8 @@ int ub_make_lut(ub_perturb* p, int lut_kind, double param) {
 int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes, int max_microbatch) {
   if (!out) return UB_ERR_INVALID;
   *out = nullptr;
-  if (arch != UB_ARCH_UNET && arch != UB_ARCH_LARGE_UNET && arch != UB_ARCH_CLIP_UNET) return fail(nullptr, UB_ERR_INVALID, "unknown arch %d", arch);
+  if (arch != UB_ARCH_UNET && arch != UB_ARCH_LARGE_UNET && arch != UB_ARCH_CLIP_UNET && arch != UB_ARCH_CLIP_UNET_PROMPT)
+    return fail(nullptr, UB_ERR_INVALID, "unknown arch %d", arch);
   if (in_channels != 3) return fail(nullptr, UB_ERR_UNSUPPORTED, "only in_channels=3 is supported");
   if (n_classes < 1 || n_classes > ub::kMaxClasses) return fail(nullptr, UB_ERR_UNSUPPORTED, "n_classes must be 1..%d", ub::kMaxClasses);
   if (max_microbatch < 1 || max_microbatch > 4096) return fail(nullptr, UB_ERR_INVALID, "max_microbatch out of range");
@@ -819,6 +915,7 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   const char* nk = getenv("UB_NO_KXS");
   ctx->no_kxs = nk && nk[0] == '1';
   { const char* e = getenv("UB_NO_PAIRQ"); ctx->no_pairq = e && e[0] == '1'; }
+  { const char* e = getenv("UB_HEAD_NO_KXS"); ctx->head_no_kxs = e && e[0] == '1'; }
   { const char* e = getenv("UB_DBG"); ctx->dbg = e ? atoi(e) : 0; }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
@@ -899,13 +996,15 @@ namespace {
 int eval_impl(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, const void* targets,
               int target_format, const void* aux, const float* clip_feats, int n, int h, int w, int ref_batch,
               int64_t* cm, double* dice_sums, uint8_t* pred_out, float* logits_out, float* perturbed_out,
-              void* stream) {
+              void* stream, const float* prompt = nullptr) {
   int rc;
   if ((rc = check_ready(ctx))) return rc;
-  if (ctx->arch == UB_ARCH_CLIP_UNET && !clip_feats)
-    return fail(ctx, UB_ERR_INVALID, "UB_ARCH_CLIP_UNET needs the CLIP embeddings: call ub_eval_batches_clip");
-  if (ctx->arch != UB_ARCH_CLIP_UNET && clip_feats)
+  if (ctx->has_clip() && !clip_feats)
+    return fail(ctx, UB_ERR_INVALID, "this model needs the CLIP embeddings: call ub_eval_batches_clip / ub_forward_prompt");
+  if (!ctx->has_clip() && clip_feats)
     return fail(ctx, UB_ERR_INVALID, "clip_feats given to a model without a CLIP fusion");
+  if ((ctx->arch == UB_ARCH_CLIP_UNET_PROMPT) != (prompt != nullptr))
+    return fail(ctx, UB_ERR_INVALID, "a prompt heat-map goes with UB_ARCH_CLIP_UNET_PROMPT (ub_forward_prompt) and only with it");
   if (!images || n <= 0 || ref_batch <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
   if (image_format != UB_IMG_F32_NCHW && image_format != UB_IMG_U8_NHWC) return fail(ctx, UB_ERR_INVALID, "bad image_format");
   if (targets && !cm) return fail(ctx, UB_ERR_INVALID, "targets given without a confusion-matrix buffer");
@@ -949,6 +1048,7 @@ int eval_impl(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_fo
     ha.pred = pred_out ? pred_out + hw * i0 : nullptr;
     ha.logits = logits_out ? logits_out + hw * C * i0 : nullptr;
     ha.clip = clip_feats ? clip_feats + static_cast<size_t>(2 * 32 * (1 << ctx->n_enc)) * i0 : nullptr;
+    ha.prompt = prompt ? prompt + hw * i0 : nullptr;
     if ((rc = run_microbatch(ctx, pl, Pm, static_cast<const uint8_t*>(images) + img_stride * i0, image_format, nb, ha,
                              perturbed_out ? perturbed_out + hw * 3 * i0 : nullptr, st)))
       return rc;
@@ -978,6 +1078,14 @@ int ub_eval_batches_clip(ub_ctx* ctx, const ub_perturb* p, const void* images, i
   if (!clip_feats) return fail(ctx, UB_ERR_INVALID, "clip_feats is null");
   return eval_impl(ctx, p, images, image_format, targets, target_format, aux, clip_feats, n, h, w, ref_batch, cm,
                    dice_sums, pred_out, logits_out, perturbed_out, stream);
+}
+
+int ub_forward_prompt(ub_ctx* ctx, const float* x_nchw, const float* prompt_heatmap, const float* clip_feats,
+                      float* logits_nchw, int n, int h, int w, void* stream) {
+  if (!ctx) return UB_ERR_INVALID;
+  if (!logits_nchw || !prompt_heatmap || !clip_feats) return fail(ctx, UB_ERR_INVALID, "null argument");
+  return eval_impl(ctx, nullptr, x_nchw, UB_IMG_F32_NCHW, nullptr, UB_TGT_I64, nullptr, clip_feats, n, h, w, 1, nullptr,
+                   nullptr, nullptr, logits_nchw, nullptr, stream, prompt_heatmap);
 }
 
 int ub_forward(ub_ctx* ctx, const float* x_nchw, float* logits_nchw, int n, int h, int w, void* stream) {

@@ -214,7 +214,7 @@ __global__ void pack_dataset_kernel(const float* __restrict__ img, const long lo
 __global__ void __launch_bounds__(512)
 clip_fusion_broadcast_kernel(const float* __restrict__ clip, const float* __restrict__ w_v_t, const float* __restrict__ b_v,
                              const float* __restrict__ w_o_t, const float* __restrict__ b_o,
-                             __nv_bfloat16* __restrict__ out, int C, int hw) {
+                             __nv_bfloat16* __restrict__ out, int C, int hw, int out_cgs) {
   extern __shared__ float s_vec[];  // [2][C]
   float* s_in = s_vec;
   float* s_mid = s_vec + C;
@@ -233,7 +233,8 @@ clip_fusion_broadcast_kernel(const float* __restrict__ clip, const float* __rest
     s_in[o] = acc;  // s_in is free again
   }
   __syncthreads();
-  uint4* dst = reinterpret_cast<uint4*>(out) + static_cast<size_t>(b) * (C / 8) * hw;
+  // the destination holds out_cgs >= C/8 planes per image (ClipUnetPrompt: the fused map is the first half of a concat)
+  uint4* dst = reinterpret_cast<uint4*>(out) + static_cast<size_t>(b) * out_cgs * hw;
   for (int i = threadIdx.x; i < (C / 8) * hw; i += blockDim.x) {
     const int g = i / hw;
     __nv_bfloat162 h0 = __floats2bfloat162_rn(s_in[8 * g + 0], s_in[8 * g + 1]);
@@ -243,6 +244,19 @@ clip_fusion_broadcast_kernel(const float* __restrict__ clip, const float* __rest
     dst[i] = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
                         *reinterpret_cast<uint32_t*>(&h2), *reinterpret_cast<uint32_t*>(&h3));
   }
+}
+
+// ClipUnetPrompt (models/prompt_segmentation.py:66,79): the 1-channel prompt heat-map [n,1,H,W] fp32 becomes channel 0
+// of a channel-blocked bf16 tensor; the other 7 channels of the group are zero (the remaining planes of the padded
+// 32-channel operand are never written and stay zero from the arena's memset).  4 B read, 16 B written per pixel.
+__global__ void __launch_bounds__(256)
+prompt_stem_kernel(const float* __restrict__ heat, size_t n_px_img, int n, __nv_bfloat16* __restrict__ out, int out_cgs) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n_px_img * n) return;
+  const size_t b = i / n_px_img, px = i - b * n_px_img;
+  const __nv_bfloat16 h = __float2bfloat16(heat[i]);
+  const uint32_t lo = static_cast<uint32_t>(*reinterpret_cast<const unsigned short*>(&h));
+  reinterpret_cast<uint4*>(out)[b * out_cgs * n_px_img + px] = make_uint4(lo, 0u, 0u, 0u);
 }
 
 }  // namespace ub

@@ -93,7 +93,7 @@ struct ConvParams {
   uint8_t* pred_out;       // [B,H,W] or null
   float* logits_out;       // [B,C,H,W] or null
   // pipeline shape chosen by the host (ub_api.cu: choose_pipeline)
-  int dbg; // UB_DBG bit mask (experiments only): 1 = epilogue only drains, 2 = no MMAs issued
+  int dbg; // UB_DBG bit mask (experiments only): 1 = epilogue only drains, 2 = no MMAs issued, 8 = head always evaluates the softmax
   int pairq;  // CTA pairs: pair-granular tile order with the n-tile fastest (weight-stationary pairs, n_tiles > 1)
   int cg2; // 1 = CTA-pair kernel (host: tmB box holds N/2 rows, even grid, cluster launch)
   int tw;  // tile width chosen by the host (8 standard, 16/32 kx-stacked); the kernel has it as a template parameter

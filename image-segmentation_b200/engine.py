@@ -98,7 +98,8 @@ def _stream(device):
 
 class Engine:
     """Owns one ub_ctx.  arch: 'unet' | 'large' | 'clip' (ClipUnet: every evaluation call also takes the CLIP
-    image embeddings of the same images, `clip_feats` fp32 [n, 512])."""
+    image embeddings of the same images, `clip_feats` fp32 [n, 512]) | 'clip_prompt' (ClipUnetPrompt: forward_prompt
+    takes the embeddings and the 1-channel prompt heat-maps)."""
 
     def __init__(self, device, arch: str = "unet", in_channels: int = 3, n_classes: int = 3,
                  max_microbatch: int = 148):
@@ -111,7 +112,8 @@ class Engine:
         self.n_classes = n_classes
         self.max_microbatch = max_microbatch
         h = ctypes.c_void_p()
-        archs = {"unet": L.UB_ARCH_UNET, "large": L.UB_ARCH_LARGE_UNET, "clip": L.UB_ARCH_CLIP_UNET}
+        archs = {"unet": L.UB_ARCH_UNET, "large": L.UB_ARCH_LARGE_UNET, "clip": L.UB_ARCH_CLIP_UNET,
+                 "clip_prompt": L.UB_ARCH_CLIP_UNET_PROMPT}
         if arch not in archs:
             raise ValueError(f"unknown arch {arch!r}")
         self.arch = arch
@@ -148,6 +150,23 @@ class Engine:
         ndims = (ctypes.c_int * n)(*[v.dim() for _, v in items])
         self._check(self.lib.ub_load_weights(self.h, n, names, ptrs, shapes, ndims), "ub_load_weights")
         self.loaded = True
+
+    def forward_prompt(self, x: torch.Tensor, prompt_heatmap: torch.Tensor, clip_feats: torch.Tensor) -> torch.Tensor:
+        """ClipUnetPrompt.forward given the CLIP embedding (models/prompt_segmentation.py:63-95): -> logits [n,C,H,W]."""
+        if self.arch != "clip_prompt":
+            raise RuntimeError("forward_prompt needs an engine created with arch='clip_prompt'")
+        x = x.to(self.device, torch.float32).contiguous()
+        n, c, h, w = x.shape
+        hm = prompt_heatmap.to(self.device, torch.float32).contiguous()
+        if tuple(hm.shape) != (n, 1, h, w):
+            raise ValueError(f"prompt_heatmap must be [{n}, 1, {h}, {w}], got {tuple(hm.shape)}")
+        cf = clip_feats.to(self.device, torch.float32).contiguous()
+        if tuple(cf.shape) != (n, 512):
+            raise ValueError(f"clip_feats must be [{n}, 512], got {tuple(cf.shape)}")
+        out = torch.empty((n, self.n_classes, h, w), device=self.device, dtype=torch.float32)
+        self._check(self.lib.ub_forward_prompt(self.h, _ptr(x), _ptr(hm), _ptr(cf), _ptr(out), n, h, w,
+                                               _stream(self.device)), "ub_forward_prompt")
+        return out
 
     def forward(self, x: torch.Tensor, clip_feats: Optional[torch.Tensor] = None) -> torch.Tensor:
         x = x.to(self.device, torch.float32).contiguous()

@@ -29,6 +29,34 @@ def to_float_nchw(images_u8_nhwc: torch.Tensor) -> torch.Tensor:
     return images_u8_nhwc.permute(0, 3, 1, 2).float() / 255.0
 
 
+def prompt_heatmaps(n: int, h: int = 256, w: int = 256, seed: int = 3, sigma: float = 10.0) -> torch.Tensor:
+    """Gaussian prompt heat-maps [n,1,h,w] as customDatasets/datasets.py:599-610 builds them (exp(-d^2 / 2 sigma^2) around
+    a seeded click position)."""
+    g = torch.Generator().manual_seed(seed)
+    cy = torch.randint(0, h, (n,), generator=g).float()
+    cx = torch.randint(0, w, (n,), generator=g).float()
+    yv, xv = torch.meshgrid(torch.arange(h, dtype=torch.float32), torch.arange(w, dtype=torch.float32), indexing="ij")
+    d2 = (xv[None] - cx[:, None, None]) ** 2 + (yv[None] - cy[:, None, None]) ** 2
+    return torch.exp(-d2 / (2.0 * sigma ** 2)).unsqueeze(1)
+
+
+def amplify_bottleneck_path(state_dict, up: float = 16.0, prompt_fusion: float = 32.0, prompt_stem: float = 100.0):
+    """With default initialisation the decoder's up-sampled half carries ~1e-6 of a logit, so a test on logits would
+    not notice a wrong bottleneck (CLIP fusion, prompt encoder).  Scales `dec*.up.weight`, the prompt half of
+    `prompt_fusion.weight` and the prompt encoder's first conv so that those branches move the logits by O(0.1)."""
+    sd = dict(state_dict)
+    for k in list(sd):
+        if k.endswith(".up.weight") and k.startswith("dec"):
+            sd[k] = sd[k] * up
+    if "prompt_fusion.weight" in sd:
+        w = sd["prompt_fusion.weight"].clone()
+        w[:, w.shape[1] // 2:] *= prompt_fusion
+        sd["prompt_fusion.weight"] = w
+        k0 = "prompt_encoder.enc1.block.0.conv.0.weight"
+        sd[k0] = sd[k0] * prompt_stem
+    return sd
+
+
 def randomize_batchnorm(state_dict, seed: int = 7):
     """Give every BatchNorm non-trivial affine + running statistics so BN folding is exercised."""
     g = torch.Generator().manual_seed(seed)

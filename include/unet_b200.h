@@ -37,8 +37,10 @@ enum ub_status {
 enum ub_arch {
   UB_ARCH_UNET = 0,       /* models/UNet.py:7-76 */
   UB_ARCH_LARGE_UNET = 1, /* models/UNet.py:78-148 */
-  UB_ARCH_CLIP_UNET = 2   /* models/CLIP_models.py:89-134: UNet encoder/decoder, bottleneck = cross-attention fusion of the
+  UB_ARCH_CLIP_UNET = 2,  /* models/CLIP_models.py:89-134: UNet encoder/decoder, bottleneck = cross-attention fusion of the
                              CLIP image embedding (the embedding itself is computed by the caller) */
+  UB_ARCH_CLIP_UNET_PROMPT = 3 /* models/prompt_segmentation.py:31-95: ClipUnet plus the PromptEncoder (:16-29) over a
+                                  1-channel prompt heat-map and the 1x1 prompt_fusion of the two 512-channel maps */
 };
 
 /* Input image container. */
@@ -125,6 +127,13 @@ int ub_eval_batches_clip(ub_ctx* ctx, const ub_perturb* p, const void* images, i
                          const void* targets, int target_format, const void* aux, const float* clip_feats, int n,
                          int h, int w, int ref_batch, int64_t* cm, double* dice_sums, uint8_t* pred_out,
                          float* logits_out, float* perturbed_out, void* stream);
+
+/* Replaces ClipUnetPrompt.forward (models/prompt_segmentation.py:63-95) for UB_ARCH_CLIP_UNET_PROMPT: x fp32 [n,3,H,W],
+ * prompt_heatmap fp32 [n,1,H,W], clip_feats fp32 [n,512] (all device) -> logits fp32 [n,C,H,W] (before `activation`).
+ * The library runs stem + enc1-3 on x, the PromptEncoder on the heat-map, the cross-attention fusion of clip_feats,
+ * prompt_fusion over their channel concat, dec1-4 and the 1x1 head. */
+int ub_forward_prompt(ub_ctx* ctx, const float* x_nchw, const float* prompt_heatmap, const float* clip_feats,
+                      float* logits_nchw, int n, int h, int w, void* stream);
 
 /* Perturbation alone (the Dataset wrappers' __getitem__ / the nn.Modules' forward): out fp32 [n,3,H,W]. */
 int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,

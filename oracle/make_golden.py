@@ -11,6 +11,7 @@ through oracle/refload.py).  Run in the build container only:  python -m oracle.
                    reference IoU / PixelAccuracy on them, and a checksum of the seeded state_dict.
   dataset_rows.npz reference CustomImageDataset._deserialize_datapoint on 6 synthetic rows (trimap remap), masks +
                    a checksum of the decoded fp32 images.
+  clipunet_prompt_small.npz  reference ClipUnetPrompt (same stand-in encoder) on 2 images + Gaussian heat-maps: keys, embedding, logits
   clipunet_small.npz  reference ClipUnet with a seeded random-init CLIP encoder (the checkpoint needs the network): key
                    list, CLIP embedding and logits on the [2,3,32,64] input.
   segmodel_small.npz  reference SegmentationModel(Encoder(), SegmentationDecoderSkip(3)) (models/pre_trained.py:47-56,
@@ -220,6 +221,34 @@ def golden_clipunet():
     return out
 
 
+def golden_clipunet_prompt():
+    """Reference ClipUnetPrompt (models/prompt_segmentation.py:31-95) with the seeded stand-in CLIP encoder: key list of
+    the non-CLIP part, the CLIP embedding, the Gaussian prompt heat-maps (datasets.py:599-610 form) and the logits."""
+    from image_segmentation_b200 import synthetic
+    ns = refload.load_clip_unet(clip_seed=0)
+    torch.manual_seed(42)
+    m = ns.ClipUnetPrompt().to("cpu").eval()
+    own = {k: v for k, v in m.state_dict().items() if not k.startswith("clip_feature_extractor.")}
+    base_sum = state_checksum(own)
+    # amplified so that the prompt and the CLIP embedding visibly move the logits (see synthetic.amplify_bottleneck_path)
+    sd = synthetic.amplify_bottleneck_path(synthetic.randomize_batchnorm(own, seed=7))
+    m.load_state_dict(sd, strict=False)
+    imgs, _ = synthetic.make_dataset(2, 32, 64, seed=5)
+    x = synthetic.to_float_nchw(imgs)
+    heat = synthetic.prompt_heatmaps(2, 32, 64, seed=3, sigma=3.0)
+    with torch.no_grad():
+        feats = m.clip_feature_extractor(x.to(m.clip_feature_extractor.device)).cpu()
+        logits = m(x, heat)
+        logits_flipped = m(x, heat.flip(-1).contiguous())   # another click position: the prompt branch matters
+    keys = list(own.keys())
+    out = dict(images_u8=imgs.numpy(), heatmaps=heat.numpy(), clip_feats=feats.numpy(), logits=logits.numpy(),
+               logits_flipped_prompt=logits_flipped.numpy(),
+               keys=np.array(keys), shapes=np.array([str(tuple(own[k].shape)) for k in keys]),
+               seed42_state_sha256=np.array(base_sum), final_state_sha256=np.array(state_checksum(sd)))
+    np.savez_compressed(os.path.join(OUT, "clipunet_prompt_small.npz"), **out)
+    return out
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ns = refload.load()
@@ -229,6 +258,7 @@ def main():
     golden_segmodel(ns)
     golden_dataset_rows(ns)
     golden_clipunet()
+    golden_clipunet_prompt()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -101,4 +101,8 @@ def load_clip_unet(clip_seed: int = 0):
     ns.CLIP_models = importlib.import_module("models.CLIP_models")
     ns.SeededCLIPModel = SeededCLIPModel
     ns.ClipUnet = ns.CLIP_models.ClipUnet
+    # models/prompt_segmentation.py star-imports processing_blocks after the rebinding above, so its
+    # ClipFeatureExtractor builds the same seeded stand-in encoder
+    ns.prompt_segmentation = importlib.import_module("models.prompt_segmentation")
+    ns.ClipUnetPrompt = ns.prompt_segmentation.ClipUnetPrompt
     return ns

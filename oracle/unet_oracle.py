@@ -62,9 +62,19 @@ def clip_fusion(sd, clip_feats: torch.Tensor, h: int, w: int) -> torch.Tensor:
     return o[:, :, None, None].expand(-1, -1, h, w)
 
 
-def forward_impl(state_dict, x: torch.Tensor, return_intermediates: bool = False, clip_feats=None):
+def prompt_encoder(sd, heat: torch.Tensor) -> torch.Tensor:
+    """models/prompt_segmentation.py:16-29 (PromptEncoder.forward): three pooled double-conv stages, then a ConvBlock."""
+    h = heat.float()
+    for i in (1, 2, 3):
+        h = F.max_pool2d(_double_conv(h, sd, f"prompt_encoder.enc{i}.block.0.conv"), 2, 2)
+    return _double_conv(h, sd, "prompt_encoder.conv.conv")
+
+
+def forward_impl(state_dict, x: torch.Tensor, return_intermediates: bool = False, clip_feats=None, prompt=None):
     """x: fp32 [B,3,H,W] -> logits fp32 [B,C,H,W] (activation = Identity).  Differentiable.
-    clip_feats [B,512]: ClipUnet (models/CLIP_models.py:114-131) — the bottleneck handed to dec1 is the fusion."""
+    clip_feats [B,512]: ClipUnet (models/CLIP_models.py:114-131) — the bottleneck handed to dec1 is the fusion.
+    prompt [B,1,H,W] (with clip_feats): ClipUnetPrompt (models/prompt_segmentation.py:63-95) — dec1's input is
+    prompt_fusion(cat([fusion, prompt_encoder(prompt)]))."""
     sd = {k.replace("_orig_mod.", ""): v.float() for k, v in state_dict.items()
           if v.is_floating_point()}
     n_enc = 4 if arch_of(sd) == "large" else 3
@@ -79,6 +89,9 @@ def forward_impl(state_dict, x: torch.Tensor, return_intermediates: bool = False
         skips.append(h)
     if clip_feats is not None:
         h = clip_fusion(sd, clip_feats, h.shape[2], h.shape[3])  # CLIP_models.py:122-124: bottleneck(enc3) is unused
+        if prompt is not None:  # prompt_segmentation.py:79-86
+            cat = torch.cat([h, prompt_encoder(sd, prompt)], dim=1)
+            h = F.conv2d(cat, sd["prompt_fusion.weight"], sd["prompt_fusion.bias"])
     else:
         h = _double_conv(h, sd, "bottleneck.conv")
     acts["bottleneck"] = h
@@ -90,8 +103,8 @@ def forward_impl(state_dict, x: torch.Tensor, return_intermediates: bool = False
 
 
 @torch.no_grad()
-def forward(state_dict, x: torch.Tensor, return_intermediates: bool = False, clip_feats=None):
-    return forward_impl(state_dict, x, return_intermediates, clip_feats)
+def forward(state_dict, x: torch.Tensor, return_intermediates: bool = False, clip_feats=None, prompt=None):
+    return forward_impl(state_dict, x, return_intermediates, clip_feats, prompt)
 
 
 def hard_prediction(logits: torch.Tensor) -> torch.Tensor:

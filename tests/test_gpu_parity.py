@@ -434,6 +434,48 @@ def test_clipunet_evaluator_embeds_the_perturbed_image(clipunet, dev):
     assert agree > 0.97 and util.rel_err(res["logits"].cpu(), ref) < 2e-2
 
 
+def test_clipunet_prompt_logits_against_reference_golden(dev):
+    """ClipUnetPrompt (models/prompt_segmentation.py:31-95) through ub_forward_prompt against the reference's logits
+    (fp32 CPU, golden) given the reference's CLIP embedding; then the whole drop-in forward, and a 256x256 batch that
+    spans several micro-batches against the oracle."""
+    import os
+    from transformers import CLIPConfig, CLIPModel
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.prompt_segmentation import ClipUnetPrompt
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "clipunet_prompt_small.npz"))
+    torch.manual_seed(0)
+    m = ClipUnetPrompt(clip_model=CLIPModel(CLIPConfig()).eval()).eval()
+    own = {k: v for k, v in m.state_dict().items() if not k.startswith("clip_feature_extractor.")}
+    sd = synthetic.amplify_bottleneck_path(synthetic.randomize_batchnorm(own, seed=7))
+    m.load_state_dict(sd, strict=False)
+    m = m.to(dev)
+    x = synthetic.to_float_nchw(torch.from_numpy(g["images_u8"])).to(dev)
+    heat = torch.from_numpy(g["heatmaps"]).to(dev)
+    ref, ref_flip = torch.from_numpy(g["logits"]), torch.from_numpy(g["logits_flipped_prompt"])
+    eng = m.engine(dev)
+    got = eng.forward_prompt(x, heat, torch.from_numpy(g["clip_feats"]).to(dev)).cpu()
+    full = m(x, heat).cpu()
+    rel, rel_full = util.rel_err(got, ref), util.rel_err(full, ref)
+    print(f"ClipUnetPrompt: logits rel err {rel:.3e} (golden embedding), {rel_full:.3e} (own embedding)")
+    assert got.shape == ref.shape == (2, 1, 32, 64)
+    assert rel < 2e-2 and rel_full < 2e-2
+    # another click position: the fixture's logits move by > 10 % with the prompt, and the library follows the reference
+    other = eng.forward_prompt(x, heat.flip(-1).contiguous(), torch.from_numpy(g["clip_feats"]).to(dev)).cpu()
+    assert util.rel_err(other, ref_flip) < 2e-2 and util.rel_err(other, ref) > 10 * util.rel_err(other, ref_flip)
+    with pytest.raises(RuntimeError):
+        eng.forward(x)  # this architecture has no prompt-less forward
+    # full resolution, 5 images in micro-batches of 2
+    imgs, _ = synthetic.make_dataset(5, 256, 256, seed=11)
+    xb = synthetic.to_float_nchw(imgs).to(dev)
+    hb = synthetic.prompt_heatmaps(5, 256, 256, seed=4, sigma=10.0).to(dev)
+    feats = m.clip_feature_extractor(xb)
+    eng2 = m.engine(dev, max_microbatch=2)
+    got2 = eng2.forward_prompt(xb, hb, feats).cpu()
+    ref2 = unet_oracle.forward({k: v.to(dev) for k, v in sd.items()}, xb, clip_feats=feats, prompt=hb).cpu()
+    print(f"ClipUnetPrompt 5x256x256: logits rel err {util.rel_err(got2, ref2):.3e}")
+    assert util.rel_err(got2, ref2) < 2e-2
+
+
 @pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL"])
 def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     """The diagnostic switches select other kernels for the same layers (streamed weights, 9-tap thin layers, single

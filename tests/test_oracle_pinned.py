@@ -190,6 +190,38 @@ def test_clipunet_tree_and_oracle_against_reference_golden():
         m(x)                                  # no CPU path
 
 
+def test_clipunet_prompt_tree_and_oracle_against_reference_golden():
+    """ClipUnetPrompt drop-in (reference models/prompt_segmentation.py:16-95): same keys/shapes/seeded init as the
+    reference for everything but the CLIP encoder, and the oracle (PromptEncoder + prompt_fusion restated) reproduces the
+    reference's logits on the golden images, heat-maps and embedding."""
+    from transformers import CLIPConfig, CLIPModel
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.prompt_segmentation import ClipUnetPrompt, PromptEncoder
+    from oracle.make_golden import state_checksum
+    g = np.load(os.path.join(GOLD, "clipunet_prompt_small.npz"))
+    torch.manual_seed(0)
+    m = ClipUnetPrompt(clip_model=CLIPModel(CLIPConfig()).eval()).eval()
+    own = {k: v for k, v in m.state_dict().items() if not k.startswith("clip_feature_extractor.")}
+    assert list(own.keys()) == [str(k) for k in g["keys"]]
+    assert [str(tuple(v.shape)) for v in own.values()] == [str(s) for s in g["shapes"]]
+    assert state_checksum(own) == str(g["seed42_state_sha256"])
+    sd = synthetic.amplify_bottleneck_path(synthetic.randomize_batchnorm(own, seed=7))
+    assert state_checksum(sd) == str(g["final_state_sha256"])
+    x = synthetic.to_float_nchw(torch.from_numpy(g["images_u8"]))
+    heat = torch.from_numpy(g["heatmaps"])
+    assert torch.equal(heat, synthetic.prompt_heatmaps(2, 32, 64, seed=3, sigma=3.0))
+    ref, ref_flip = torch.from_numpy(g["logits"]), torch.from_numpy(g["logits_flipped_prompt"])
+    assert ref.shape == (2, 1, 32, 64)
+    assert float((ref - ref_flip).abs().max()) > 0.1 * float(ref.abs().max())   # the prompt branch matters in this fixture
+    for h, want in ((heat, ref), (heat.flip(-1).contiguous(), ref_flip)):
+        logits = unet_oracle.forward(sd, x, clip_feats=torch.from_numpy(g["clip_feats"]), prompt=h)
+        assert float((logits - want).abs().max()) <= 2e-5 * float(want.abs().max())
+    with pytest.raises(RuntimeError):
+        m(x, heat)                            # no CPU path
+    with pytest.raises(RuntimeError):
+        PromptEncoder()(heat)                 # runs only inside the model
+
+
 def test_dice_restatement_is_self_consistent():
     """Dice is PARITY UNPINNED (smp absent): only internal consistency can be checked."""
     g = torch.Generator().manual_seed(0)
