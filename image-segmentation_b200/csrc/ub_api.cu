@@ -47,7 +47,7 @@ struct GemmLayer {
 };
 
 struct Step {
-  enum Kind { GEMM, RESAMPLE, CLIP_FUSE, PROMPT_STEM } kind = GEMM;  // CLIP_FUSE / PROMPT_STEM reuse rs_out / ho / wo / c / out_cgs
+  enum Kind { GEMM, RESAMPLE, CLIP_FUSE, PROMPT_STEM, AE_OUT } kind = GEMM;  // CLIP_FUSE / PROMPT_STEM / AE_OUT reuse the RESAMPLE fields
   int layer = -1;
   ConvParams cp;   // GEMM: tensor maps + static params (B patched per launch)
   // RESAMPLE
@@ -270,8 +270,9 @@ int pack_all(ub_ctx* ctx) {
   if (!sw || !sb || !ow || !ob) return fail(ctx, UB_ERR_INVALID, "missing input.* / out.* entries");
   if (sw->data.size() != 32 * 3 || sb->data.size() != 32)
     return fail(ctx, UB_ERR_UNSUPPORTED, "stem must be Conv2d(3,32,1)");
-  if (static_cast<int>(ow->shape[0]) != ctx->n_classes || ow->shape[1] != 32)
-    return fail(ctx, UB_ERR_INVALID, "out.weight must be [%d,32,1,1]", ctx->n_classes);
+  const bool ae = ctx->arch == UB_ARCH_AUTOENCODER;  // Decoder.out is Conv2d(64, out_channels, 1) (autoencoder.py:34)
+  if (static_cast<int>(ow->shape[0]) != ctx->n_classes || ow->shape[1] != (ae ? 64 : 32))
+    return fail(ctx, UB_ERR_INVALID, "out.weight must be [%d,%d,1,1]", ctx->n_classes, ae ? 64 : 32);
   memcpy(ctx->stem.w, sw->data.data(), sizeof(ctx->stem.w));
   memcpy(ctx->stem.b, sb->data.data(), sizeof(ctx->stem.b));
   if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->head_w), ow->data.size() * 4))) return rc;
@@ -328,7 +329,7 @@ int pack_all(ub_ctx* ctx) {
     if ((rc = pack_conv(ctx, "bottleneck.conv.0", "bottleneck.conv.1"))) return rc;
     if ((rc = pack_conv(ctx, "bottleneck.conv.3", "bottleneck.conv.4"))) return rc;
   }
-  for (int j = 1; j <= ctx->n_enc + 1; ++j) {
+  for (int j = 1; j <= ctx->n_enc + (ae ? 0 : 1); ++j) {
     snprintf(k, sizeof(k), "dec%d", j);
     if ((rc = pack_convt(ctx, std::string(k) + ".up"))) return rc;
     if ((rc = pack_conv(ctx, std::string(k) + ".conv.conv.0", std::string(k) + ".conv.conv.1"))) return rc;
@@ -632,6 +633,14 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
     }
     i_pcat = want(static_cast<size_t>(MB) * hl(n) * wl(n) * 2 * cb * 2);
   }
+  // Autoencoder: decoder stage j (no skip) works at level n - j with 512 >> j channels: ConvT output, conv.0, conv.3
+  const bool ae = ctx->arch == UB_ARCH_AUTOENCODER;
+  std::vector<size_t> i_au(n + 1), i_aa(n + 1), i_ab(n + 1);
+  if (ae)
+    for (int j = 1; j <= n; ++j) {
+      const size_t bytes = static_cast<size_t>(MB) * hl(n - j) * wl(n - j) * (cb >> j) * 2;
+      i_au[j] = want(bytes); i_aa[j] = want(bytes); i_ab[j] = want(bytes);
+    }
   const size_t img_bytes = static_cast<size_t>(MB) * 3 * H * W * 4;
   const size_t i_pert = want(img_bytes), i_bla = want(img_bytes), i_blb = want(img_bytes);
   size_t total = 0;
@@ -712,6 +721,24 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
   // decoder (UNet.py:69-72, processing_blocks.py:105-109)
   const __nv_bfloat16* x = bufp(i_bb);
   int xc = cb, xh = hl(n), xw = wl(n);
+  if (ae) {
+    // Autoencoder decoder (autoencoder.py:36-41, processing_blocks.py:131-133): ConvT -> ConvBlock, no skip, no resize
+    for (int j = 1; j <= n; ++j) {
+      const int l = n - j, c = cb >> j;
+      snprintf(k, sizeof(k), "dec%d", j);
+      if ((rc = add_gemm(std::string(k) + ".up", x, xc / 8, xh, xw, ub::EPI_CONVT, bufp(i_au[j]), c / 8, 0))) return rc;
+      if ((rc = add_gemm(std::string(k) + ".conv.conv.0", bufp(i_au[j]), c / 8, hl(l), wl(l), ub::EPI_STORE, bufp(i_aa[j]), c / 8, 0))) return rc;
+      if ((rc = add_gemm(std::string(k) + ".conv.conv.3", bufp(i_aa[j]), c / 8, hl(l), wl(l), ub::EPI_STORE, bufp(i_ab[j]), c / 8, 0))) return rc;
+      x = bufp(i_ab[j]); xc = c; xh = hl(l); xw = wl(l);
+    }
+    Step s;
+    s.kind = Step::AE_OUT;
+    s.rs_in = x; s.c = xc; s.ho = xh; s.wo = xw;
+    pl->steps.push_back(s);
+    *out = pl.get();
+    ctx->plans[key] = std::move(pl);
+    return UB_OK;
+  }
   for (int j = 1; j <= n + 1; ++j) {
     const int l = n + 1 - j;
     snprintf(k, sizeof(k), "dec%d", j);
@@ -824,6 +851,16 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
       ctx->launches++;
       continue;
     }
+    if (s.kind == Step::AE_OUT) {
+      if (!ha.logits) return fail(ctx, UB_ERR_INVALID, "the autoencoder writes its reconstruction: call ub_forward");
+      const size_t hw1 = static_cast<size_t>(s.ho) * s.wo;
+      const int C = ctx->n_classes;
+      ub::out1x1_sigmoid_kernel<ub::kMaxClasses><<<blocks_for(hw1 * nb, 256), 256, (C * s.c + C) * sizeof(float), st>>>(
+          s.rs_in, ctx->head_w, ctx->head_b, ha.logits, nb, hw1, s.c, C, 1);
+      UB_CUDA(ctx, cudaGetLastError());
+      ctx->launches++;
+      continue;
+    }
     if (s.kind == Step::PROMPT_STEM) {
       if (!ha.prompt) return fail(ctx, UB_ERR_INVALID, "this model needs a prompt heat-map: call ub_forward_prompt");
       const size_t hw1 = static_cast<size_t>(s.ho) * s.wo;
@@ -886,7 +923,8 @@ int ub_make_lut(ub_perturb* p, int lut_kind, double param) {
 int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes, int max_microbatch) {
   if (!out) return UB_ERR_INVALID;
   *out = nullptr;
-  if (arch != UB_ARCH_UNET && arch != UB_ARCH_LARGE_UNET && arch != UB_ARCH_CLIP_UNET && arch != UB_ARCH_CLIP_UNET_PROMPT)
+  if (arch != UB_ARCH_UNET && arch != UB_ARCH_LARGE_UNET && arch != UB_ARCH_CLIP_UNET && arch != UB_ARCH_CLIP_UNET_PROMPT &&
+      arch != UB_ARCH_AUTOENCODER)
     return fail(nullptr, UB_ERR_INVALID, "unknown arch %d", arch);
   if (in_channels != 3) return fail(nullptr, UB_ERR_UNSUPPORTED, "only in_channels=3 is supported");
   if (n_classes < 1 || n_classes > ub::kMaxClasses) return fail(nullptr, UB_ERR_UNSUPPORTED, "n_classes must be 1..%d", ub::kMaxClasses);
@@ -1006,6 +1044,8 @@ int eval_impl(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_fo
   if ((ctx->arch == UB_ARCH_CLIP_UNET_PROMPT) != (prompt != nullptr))
     return fail(ctx, UB_ERR_INVALID, "a prompt heat-map goes with UB_ARCH_CLIP_UNET_PROMPT (ub_forward_prompt) and only with it");
   if (!images || n <= 0 || ref_batch <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  if (ctx->arch == UB_ARCH_AUTOENCODER && (targets || cm || dice_sums || pred_out))
+    return fail(ctx, UB_ERR_INVALID, "UB_ARCH_AUTOENCODER reconstructs images (ub_forward); it has no argmax / confusion counts");
   if (image_format != UB_IMG_F32_NCHW && image_format != UB_IMG_U8_NHWC) return fail(ctx, UB_ERR_INVALID, "bad image_format");
   if (targets && !cm) return fail(ctx, UB_ERR_INVALID, "targets given without a confusion-matrix buffer");
   if (dice_sums && !targets) return fail(ctx, UB_ERR_INVALID, "dice_sums needs targets");

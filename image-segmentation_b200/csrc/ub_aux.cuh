@@ -259,4 +259,38 @@ prompt_stem_kernel(const float* __restrict__ heat, size_t n_px_img, int n, __nv_
   reinterpret_cast<uint4*>(out)[b * out_cgs * n_px_img + px] = make_uint4(lo, 0u, 0u, 0u);
 }
 
+// Autoencoder head (models/autoencoder.py:34,40,58): Conv2d(C -> n_out, k=1) over the channel-blocked bf16 map, then
+// sigmoid, written as fp32 NCHW.  One thread per pixel; reads C*2 B (16-byte loads, coalesced per plane), writes
+// 4*n_out B.  Weights [n_out][C] + bias in shared memory.
+template <int MAX_OUT>
+__global__ void __launch_bounds__(256)
+out1x1_sigmoid_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
+                      float* __restrict__ out, int n, size_t hw, int C, int n_out, int apply_sigmoid) {
+  extern __shared__ float s_w[];  // [n_out][C] then [n_out]
+  for (int i = threadIdx.x; i < n_out * C; i += blockDim.x) s_w[i] = w[i];
+  for (int i = threadIdx.x; i < n_out; i += blockDim.x) s_w[n_out * C + i] = bias[i];
+  __syncthreads();
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= hw * n) return;
+  const size_t b = i / hw, px = i - b * hw;
+  float acc[MAX_OUT];
+#pragma unroll
+  for (int o = 0; o < MAX_OUT; ++o) acc[o] = o < n_out ? s_w[n_out * C + o] : 0.0f;
+  const uint4* src = reinterpret_cast<const uint4*>(in) + b * (C / 8) * hw + px;
+  for (int g = 0; g < C / 8; ++g) {
+    const uint4 v = src[static_cast<size_t>(g) * hw];
+    const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float lo = __uint_as_float(u[j] << 16), hi = __uint_as_float(u[j] & 0xffff0000u);
+#pragma unroll
+      for (int o = 0; o < MAX_OUT; ++o)
+        if (o < n_out) acc[o] = fmaf(s_w[o * C + 8 * g + 2 * j + 1], hi, fmaf(s_w[o * C + 8 * g + 2 * j], lo, acc[o]));
+    }
+  }
+#pragma unroll
+  for (int o = 0; o < MAX_OUT; ++o)
+    if (o < n_out) out[(b * n_out + o) * hw + px] = apply_sigmoid ? 1.0f / (1.0f + expf(-acc[o])) : acc[o];
+}
+
 }  // namespace ub

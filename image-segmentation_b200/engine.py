@@ -99,7 +99,8 @@ def _stream(device):
 class Engine:
     """Owns one ub_ctx.  arch: 'unet' | 'large' | 'clip' (ClipUnet: every evaluation call also takes the CLIP
     image embeddings of the same images, `clip_feats` fp32 [n, 512]) | 'clip_prompt' (ClipUnetPrompt: forward_prompt
-    takes the embeddings and the 1-channel prompt heat-maps)."""
+    takes the embeddings and the 1-channel prompt heat-maps) | 'autoencoder' (forward returns the sigmoid reconstruction;
+    n_classes = its output channels)."""
 
     def __init__(self, device, arch: str = "unet", in_channels: int = 3, n_classes: int = 3,
                  max_microbatch: int = 148):
@@ -113,7 +114,7 @@ class Engine:
         self.max_microbatch = max_microbatch
         h = ctypes.c_void_p()
         archs = {"unet": L.UB_ARCH_UNET, "large": L.UB_ARCH_LARGE_UNET, "clip": L.UB_ARCH_CLIP_UNET,
-                 "clip_prompt": L.UB_ARCH_CLIP_UNET_PROMPT}
+                 "clip_prompt": L.UB_ARCH_CLIP_UNET_PROMPT, "autoencoder": L.UB_ARCH_AUTOENCODER}
         if arch not in archs:
             raise ValueError(f"unknown arch {arch!r}")
         self.arch = arch

@@ -5,14 +5,21 @@ In unet-b200 the encoder is a PARAMETER CONTAINER: it computes as part of
 `pre_trained.SegmentationModel.forward`, which runs encoder and decoder in one pass of the sm_100a library
 (the same launches as `UNet`).  The stand-alone `Encoder.forward` of the reference returns the dict of
 feature maps {x0, enc1, enc2, enc3, bottleneck}; those never leave the device pipeline here, so calling it
-on its own raises.  The reconstruction `Decoder`/`Autoencoder` (:28-58, sigmoid output, no skips) is a
-training-time model outside the robustness-evaluation path and is not provided.
+on its own raises.
+
+`Decoder` (:28-42) and `Autoencoder` (:45-58) — the reconstruction model the encoder is pre-trained with: three
+`ConvBlockUpsample` stages without skips, a 1x1 conv 64 -> out_channels and a sigmoid.  `Autoencoder.forward` runs the
+whole pass in the library (`UB_ARCH_AUTOENCODER`, `ub_forward`): stem, enc1-3, bottleneck, three ConvT + double-conv
+stages on the tensor-core kernel, then `out1x1_sigmoid_kernel`.  Inference only.
 """
 from __future__ import annotations
 
 import torch.nn as nn
 
-from .processing_blocks import ConvBlock, ConvBlockDownsample, _no_standalone
+import torch
+
+from .processing_blocks import ConvBlock, ConvBlockDownsample, ConvBlockUpsample, _no_standalone
+from .UNet import _B200Net
 
 
 class Encoder(nn.Module):
@@ -28,3 +35,35 @@ class Encoder(nn.Module):
 
     def forward(self, x):
         _no_standalone("Encoder")
+
+
+class Decoder(nn.Module):
+    """dec1..3 (ConvT 2x2 -> ConvBlock, no skip) + 1x1 conv 64 -> out_channels; reference :28-42.  Container only."""
+
+    def __init__(self, out_channels=3):
+        super().__init__()
+        self.dec1 = ConvBlockUpsample(512, 256)
+        self.dec2 = ConvBlockUpsample(256, 128)
+        self.dec3 = ConvBlockUpsample(128, 64)
+        self.out = nn.Conv2d(64, out_channels, kernel_size=1, padding=0)
+
+    def forward(self, bottleneck):
+        _no_standalone("Decoder")
+
+
+class Autoencoder(_B200Net):
+    """`Autoencoder(in_channels, out_channels)(x) -> sigmoid(reconstruction)` [B,out_channels,H,W]; reference :45-58."""
+    _arch = "autoencoder"
+
+    def __init__(self, in_channels=3, out_channels=3):
+        super().__init__()
+        self.encoder = Encoder(in_channels)
+        self.decoder = Decoder(out_channels)
+        self._finish_init(out_channels, nn.Identity())  # the sigmoid is applied inside the library
+
+    @staticmethod
+    def _flat_name(key: str) -> str:
+        for prefix in ("encoder.", "decoder."):
+            if key.startswith(prefix):
+                return key[len(prefix):]
+        return key

@@ -39,8 +39,11 @@ enum ub_arch {
   UB_ARCH_LARGE_UNET = 1, /* models/UNet.py:78-148 */
   UB_ARCH_CLIP_UNET = 2,  /* models/CLIP_models.py:89-134: UNet encoder/decoder, bottleneck = cross-attention fusion of the
                              CLIP image embedding (the embedding itself is computed by the caller) */
-  UB_ARCH_CLIP_UNET_PROMPT = 3 /* models/prompt_segmentation.py:31-95: ClipUnet plus the PromptEncoder (:16-29) over a
+  UB_ARCH_CLIP_UNET_PROMPT = 3, /* models/prompt_segmentation.py:31-95: ClipUnet plus the PromptEncoder (:16-29) over a
                                   1-channel prompt heat-map and the 1x1 prompt_fusion of the two 512-channel maps */
+  UB_ARCH_AUTOENCODER = 4  /* models/autoencoder.py:5-58: Encoder -> Decoder (three ConvBlockUpsample stages without skips,
+                              1x1 conv 64 -> n_classes channels) -> sigmoid; ub_forward returns the reconstruction
+                              (after the sigmoid), the evaluation entries do not apply */
 };
 
 /* Input image container. */

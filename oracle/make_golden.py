@@ -11,6 +11,7 @@ through oracle/refload.py).  Run in the build container only:  python -m oracle.
                    reference IoU / PixelAccuracy on them, and a checksum of the seeded state_dict.
   dataset_rows.npz reference CustomImageDataset._deserialize_datapoint on 6 synthetic rows (trimap remap), masks +
                    a checksum of the decoded fp32 images.
+  autoencoder_small.npz  reference Autoencoder (models/autoencoder.py:45-58): keys, checksums, sigmoid reconstruction of [2,3,32,64]
   clipunet_prompt_small.npz  reference ClipUnetPrompt (same stand-in encoder) on 2 images + Gaussian heat-maps: keys, embedding, logits
   clipunet_small.npz  reference ClipUnet with a seeded random-init CLIP encoder (the checkpoint needs the network): key
                    list, CLIP embedding and logits on the [2,3,32,64] input.
@@ -221,6 +222,29 @@ def golden_clipunet():
     return out
 
 
+def golden_autoencoder(ns):
+    """Reference Autoencoder (models/autoencoder.py:45-58), seed 42 + randomised BatchNorm: key list, checksums and the
+    sigmoid reconstruction of the [2,3,32,64] input."""
+    from image_segmentation_b200 import synthetic
+    torch.manual_seed(42)
+    m = ns.autoencoder.Autoencoder().eval()
+    base = {k: v.clone() for k, v in m.state_dict().items()}
+    sd = synthetic.randomize_batchnorm(base, seed=7)
+    # default init leaves the pre-sigmoid output within +-0.05 (everything ~0.5): widen it so the test sees structure
+    sd["decoder.out.weight"] = sd["decoder.out.weight"] * 8.0
+    m.load_state_dict(sd)
+    imgs, _ = synthetic.make_dataset(2, 32, 64, seed=5)
+    x = synthetic.to_float_nchw(imgs)
+    with torch.no_grad():
+        recon = m(x)
+    keys = list(base.keys())
+    out = dict(images_u8=imgs.numpy(), recon=recon.numpy(), keys=np.array(keys),
+               shapes=np.array([str(tuple(base[k].shape)) for k in keys]),
+               seed42_state_sha256=np.array(state_checksum(base)), final_state_sha256=np.array(state_checksum(sd)))
+    np.savez_compressed(os.path.join(OUT, "autoencoder_small.npz"), **out)
+    return out
+
+
 def golden_clipunet_prompt():
     """Reference ClipUnetPrompt (models/prompt_segmentation.py:31-95) with the seeded stand-in CLIP encoder: key list of
     the non-CLIP part, the CLIP embedding, the Gaussian prompt heat-maps (datasets.py:599-610 form) and the logits."""
@@ -256,6 +280,7 @@ def main():
     golden_perturb_f(ns)
     golden_unet(ns)
     golden_segmodel(ns)
+    golden_autoencoder(ns)
     golden_dataset_rows(ns)
     golden_clipunet()
     golden_clipunet_prompt()

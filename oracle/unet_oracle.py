@@ -107,6 +107,22 @@ def forward(state_dict, x: torch.Tensor, return_intermediates: bool = False, cli
     return forward_impl(state_dict, x, return_intermediates, clip_feats, prompt)
 
 
+@torch.no_grad()
+def autoencoder_forward(state_dict, x: torch.Tensor) -> torch.Tensor:
+    """models/autoencoder.py:17-25,36-41,53-58 restated on the flat key names (`encoder.` / `decoder.` prefixes dropped):
+    Encoder (stem, enc1-3, bottleneck) -> three ConvBlockUpsample stages (processing_blocks.py:131-133) -> 1x1 -> sigmoid."""
+    sd = {k.replace("_orig_mod.", "").replace("encoder.", "", 1).replace("decoder.", "", 1) if k.startswith(("encoder.", "decoder."))
+          else k.replace("_orig_mod.", ""): v.float() for k, v in state_dict.items() if v.is_floating_point()}
+    h = F.conv2d(x.float(), sd["input.weight"], sd["input.bias"])
+    for i in (1, 2, 3):
+        h = F.max_pool2d(_double_conv(h, sd, f"enc{i}.block.0.conv"), 2, 2)
+    h = _double_conv(h, sd, "bottleneck.conv")
+    for j in (1, 2, 3):
+        h = F.conv_transpose2d(h, sd[f"dec{j}.up.weight"], sd[f"dec{j}.up.bias"], stride=2)
+        h = _double_conv(h, sd, f"dec{j}.conv.conv")
+    return torch.sigmoid(F.conv2d(h, sd["out.weight"], sd["out.bias"]))
+
+
 def hard_prediction(logits: torch.Tensor) -> torch.Tensor:
     """models/losses.py:48-50 — argmax taken AFTER softmax, first index on ties."""
     return torch.argmax(F.softmax(logits, dim=1), dim=1)

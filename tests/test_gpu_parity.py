@@ -434,6 +434,37 @@ def test_clipunet_evaluator_embeds_the_perturbed_image(clipunet, dev):
     assert agree > 0.97 and util.rel_err(res["logits"].cpu(), ref) < 2e-2
 
 
+def test_autoencoder_reconstruction_against_reference_golden(dev):
+    """Autoencoder (models/autoencoder.py:45-58) through ub_forward: sigmoid reconstruction against the reference's
+    (fp32 CPU, golden), then a 256x256 batch across micro-batches against the oracle."""
+    import os
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.autoencoder import Autoencoder
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "autoencoder_small.npz"))
+    torch.manual_seed(42)
+    m = Autoencoder().eval()
+    sd = synthetic.randomize_batchnorm(m.state_dict(), seed=7)
+    sd["decoder.out.weight"] = sd["decoder.out.weight"] * 8.0
+    m.load_state_dict(sd)
+    m = m.to(dev)
+    x = synthetic.to_float_nchw(torch.from_numpy(g["images_u8"])).to(dev)
+    got = m(x).cpu()
+    ref = torch.from_numpy(g["recon"])
+    err = float((got - ref).abs().max())
+    print(f"Autoencoder: reconstruction max abs err {err:.3e} (values in [{float(ref.min()):.2f}, {float(ref.max()):.2f}])")
+    assert got.shape == ref.shape == (2, 3, 32, 64)
+    assert err < 1e-2  # sigmoid outputs in (0,1): bf16 activations
+    imgs, masks = synthetic.make_dataset(5, 256, 256, seed=12)
+    xb = synthetic.to_float_nchw(imgs).to(dev)
+    got2 = m.engine(dev, max_microbatch=2).forward(xb).cpu()
+    ref2 = unet_oracle.autoencoder_forward({k: v.to(dev) for k, v in sd.items()}, xb).cpu()
+    err2 = float((got2 - ref2).abs().max())
+    print(f"Autoencoder 5x256x256: max abs err {err2:.3e}")
+    assert err2 < 1e-2
+    with pytest.raises(RuntimeError):
+        m.engine(dev).eval_batches(imgs.to(dev), masks.to(dev), None, 8)  # no argmax / counts for a reconstruction model
+
+
 def test_clipunet_prompt_logits_against_reference_golden(dev):
     """ClipUnetPrompt (models/prompt_segmentation.py:31-95) through ub_forward_prompt against the reference's logits
     (fp32 CPU, golden) given the reference's CLIP embedding; then the whole drop-in forward, and a 256x256 batch that

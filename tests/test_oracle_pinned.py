@@ -190,6 +190,31 @@ def test_clipunet_tree_and_oracle_against_reference_golden():
         m(x)                                  # no CPU path
 
 
+def test_autoencoder_tree_and_oracle_against_reference_golden():
+    """Autoencoder drop-in (reference models/autoencoder.py:28-58): same keys/shapes/seeded init, and the oracle's
+    restatement reproduces the reference's sigmoid reconstruction."""
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.models.autoencoder import Autoencoder, Decoder
+    from oracle.make_golden import state_checksum
+    g = np.load(os.path.join(GOLD, "autoencoder_small.npz"))
+    torch.manual_seed(42)
+    m = Autoencoder().eval()
+    own = m.state_dict()
+    assert list(own.keys()) == [str(k) for k in g["keys"]]
+    assert [str(tuple(v.shape)) for v in own.values()] == [str(s) for s in g["shapes"]]
+    assert state_checksum(own) == str(g["seed42_state_sha256"])
+    sd = synthetic.randomize_batchnorm(own, seed=7)
+    sd["decoder.out.weight"] = sd["decoder.out.weight"] * 8.0
+    assert state_checksum(sd) == str(g["final_state_sha256"])
+    x = synthetic.to_float_nchw(torch.from_numpy(g["images_u8"]))
+    recon = unet_oracle.autoencoder_forward(sd, x)
+    assert float((recon - torch.from_numpy(g["recon"])).abs().max()) <= 1e-6
+    with pytest.raises(RuntimeError):
+        m(x)                                  # no CPU path
+    with pytest.raises(RuntimeError):
+        Decoder()(x)                          # container only
+
+
 def test_clipunet_prompt_tree_and_oracle_against_reference_golden():
     """ClipUnetPrompt drop-in (reference models/prompt_segmentation.py:16-95): same keys/shapes/seeded init as the
     reference for everything but the CLIP encoder, and the oracle (PromptEncoder + prompt_fusion restated) reproduces the
