@@ -386,6 +386,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
     int it = 0;
+    const bool no_mma = (p.dbg & 2) != 0;  // ablation hook, hoisted out of the issue loop
 #pragma unroll 1
     for (int t = t_first; t < total_tiles; t += t_step, ++it) {
       const int acc = it % ACC;
@@ -398,42 +399,67 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
         mbar_wait(&a_full[sa], pa);
         tc_fence_after();
         const uint32_t a_lo = a_lo_ring + static_cast<uint32_t>(sa) * A_STAGE_U;
-#pragma unroll
-        for (int tap = 0; tap < TAPS; ++tap) {
-          // kx-stacked: tap = ky (one box row down); else tap = ky*3+kx (row down, pixel right)
-          const uint32_t a_tap = a_lo + static_cast<uint32_t>(KXS ? tap * Cfg::PXW : (tap / KSIZE) * Cfg::PXW + (tap % KSIZE));
-          uint32_t b_lo;
-          if constexpr (WS) {
-            b_lo = b_lo_ring + static_cast<uint32_t>(c * TAPS + tap) * B_STAGE_U;
-          } else {
-            mbar_wait(&b_full[sb], pb);
-            tc_fence_after();
-            b_lo = b_lo_ring + static_cast<uint32_t>(sb) * B_STAGE_U;
-          }
+        if constexpr (WS) {
+          // resident weights: nothing to wait for between the taps, so the elected lane issues the whole chunk
+          // (TAPS * BK/16 MMAs), frees the A stage and — after the last chunk — publishes the accumulator in ONE
+          // divergent region.  The thin layers have 6-18 MMAs per tile and were bound by this warp's own
+          // instruction stream (ncu: ~110 instructions and ~850 cycles per tile in the head layer).
           if (leader) {
+            if (!no_mma) {
 #pragma unroll
-            for (int k = 0; k < BK / 16; ++k) {
-              if (p.dbg & 2) continue;
-              const uint32_t al = a_tap + k * A_KSTEP_U, bl = b_lo + 2 * k;
-              if (tap == 0 && k == 0) {
-                if (c == 0) mma(std::false_type{}, d_tmem, al, a_hi, bl, b_hi);
-                else mma(std::true_type{}, d_tmem, al, a_hi, bl, b_hi);
-              } else {
-                mma(std::true_type{}, d_tmem, al, a_hi, bl, b_hi);
+              for (int tap = 0; tap < TAPS; ++tap) {
+                const uint32_t a_tap = a_lo + static_cast<uint32_t>(KXS ? tap * Cfg::PXW : (tap / KSIZE) * Cfg::PXW + (tap % KSIZE));
+                const uint32_t b_lo = b_lo_ring + static_cast<uint32_t>(c * TAPS + tap) * B_STAGE_U;
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                  const uint32_t al = a_tap + k * A_KSTEP_U, bl = b_lo + 2 * k;
+                  if (tap == 0 && k == 0) {
+                    if (c == 0) mma(std::false_type{}, d_tmem, al, a_hi, bl, b_hi);
+                    else mma(std::true_type{}, d_tmem, al, a_hi, bl, b_hi);
+                  } else {
+                    mma(std::true_type{}, d_tmem, al, a_hi, bl, b_hi);
+                  }
+                }
               }
             }
-            if constexpr (!WS) commit(&b_empty[sb]);
-            if (tap == TAPS - 1) commit(&a_empty[sa]);
+            commit(&a_empty[sa]);
+            if (c == k_chunks - 1) commit(&t_full[acc]);
           }
           __syncwarp();
-          if constexpr (!WS) {
+        } else {
+#pragma unroll
+          for (int tap = 0; tap < TAPS; ++tap) {
+            // kx-stacked: tap = ky (one box row down); else tap = ky*3+kx (row down, pixel right)
+            const uint32_t a_tap = a_lo + static_cast<uint32_t>(KXS ? tap * Cfg::PXW : (tap / KSIZE) * Cfg::PXW + (tap % KSIZE));
+            mbar_wait(&b_full[sb], pb);
+            tc_fence_after();
+            const uint32_t b_lo = b_lo_ring + static_cast<uint32_t>(sb) * B_STAGE_U;
+            if (leader) {
+              if (!no_mma) {
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                  const uint32_t al = a_tap + k * A_KSTEP_U, bl = b_lo + 2 * k;
+                  if (tap == 0 && k == 0) {
+                    if (c == 0) mma(std::false_type{}, d_tmem, al, a_hi, bl, b_hi);
+                    else mma(std::true_type{}, d_tmem, al, a_hi, bl, b_hi);
+                  } else {
+                    mma(std::true_type{}, d_tmem, al, a_hi, bl, b_hi);
+                  }
+                }
+              }
+              commit(&b_empty[sb]);
+              if (tap == TAPS - 1) commit(&a_empty[sa]);
+            }
+            __syncwarp();
             if (++sb == p.sb) { sb = 0; pb ^= 1u; }
           }
         }
         if (++sa == p.sa) { sa = 0; pa ^= 1u; }
       }
-      if (leader) commit(&t_full[acc]);
-      __syncwarp();
+      if constexpr (!WS) {
+        if (leader) commit(&t_full[acc]);
+        __syncwarp();
+      }
     }
   } else if (warp >= 4) {
     // ================= epilogue (kEpiGroups x 128 threads; warp w owns TMEM lanes 32*(w%4)..) =================
