@@ -92,6 +92,7 @@ struct ub_ctx {
   bool no_pairq = false;      // UB_NO_PAIRQ=1: the big ConvTranspose runs as single CTAs with streamed weights
   int dbg = 0;                // UB_DBG: ablation hooks of conv_tc_kernel (1 = drain-only epilogue, 2 = no MMA, 8 = head always evaluates the softmax)
   bool no_kxs = false;        // UB_NO_KXS=1: thin layers run the standard (9-tap) kernel
+  bool no_blur_fuse = false;  // UB_NO_BLUR_FUSE=1: blur families run one launch per pass (the path for > 12 passes)
   bool head_no_kxs = false;   // UB_HEAD_NO_KXS=1: only the head layer (dec4.conv.3) runs the 9-tap kernel
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool profiling = false;
@@ -787,6 +788,15 @@ int run_blur(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* img, in
   const int H = pl->H, W = pl->W;
   const size_t count = static_cast<size_t>(n) * 3 * H * W;
   const unsigned g = blocks_for(count, 256);
+  if (P.iparam <= ub::kBlurMaxPasses && !ctx->no_blur_fuse) {
+    // every pass of a tile in shared memory: one launch, the image read once, the fp32 result written once
+    const dim3 grid((W + ub::kBlurTW - 1) / ub::kBlurTW, (H + ub::kBlurTH - 1) / ub::kBlurTH, n * 3);
+    if (P.kind == UB_P_U8_BLUR) ub::blur_fused_kernel<false><<<grid, 256, 0, st>>>(img, fmt, H, W, P.iparam, dst);
+    else ub::blur_fused_kernel<true><<<grid, 256, 0, st>>>(img, fmt, H, W, P.iparam, dst);
+    ctx->launches++;
+    UB_CUDA(ctx, cudaGetLastError());
+    return UB_OK;
+  }
   if (P.kind == UB_P_U8_BLUR) {
     uint8_t* a = static_cast<uint8_t*>(pl->blur_a);
     uint8_t* b = static_cast<uint8_t*>(pl->blur_b);
@@ -954,6 +964,7 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   ctx->no_kxs = nk && nk[0] == '1';
   { const char* e = getenv("UB_NO_PAIRQ"); ctx->no_pairq = e && e[0] == '1'; }
   { const char* e = getenv("UB_HEAD_NO_KXS"); ctx->head_no_kxs = e && e[0] == '1'; }
+  { const char* e = getenv("UB_NO_BLUR_FUSE"); ctx->no_blur_fuse = e && e[0] == '1'; }
   { const char* e = getenv("UB_DBG"); ctx->dbg = e ? atoi(e) : 0; }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';

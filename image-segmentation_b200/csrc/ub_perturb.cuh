@@ -5,6 +5,7 @@
 // Pointwise families are evaluated inside the stem's input load (no intermediate image in HBM);
 // the two blur families need neighbours and run as short ping-pong passes first.
 #pragma once
+#include <type_traits>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -234,6 +235,97 @@ __global__ void blur_f_pass_kernel(const float* in, float* out, int planes, int 
       acc = __fadd_rn(acc, __fmul_rn(pl[static_cast<size_t>(yy) * W + xx], ninth));
     }
   out[i] = acc;
+}
+
+// ---- all blur passes of one tile in shared memory (both families, passes <= kBlurMaxPasses; more passes fall back to
+// the pass-per-launch kernels above).  One CTA = one 32x64 tile of one (image, channel) plane plus a halo of `passes`
+// pixels; pass p recomputes the region shrunk by p, so after the last pass the tile itself is exact.  The image is read
+// once (straight from its container: the quantise / load step is the tile load) and the fp32 NCHW result written once:
+// one launch instead of passes + 2, and no planar intermediates in HBM.
+//   uint8 family: positions outside the image hold 0 in every pass (conv2d zero padding, perturbations.py:108-115).
+//   float family: neighbours outside the image are mirrored (kornia reflect border) when read; same summation order as
+//   blur_f_pass_kernel.
+constexpr int kBlurTH = 32, kBlurTW = 64, kBlurMaxPasses = 12;
+constexpr int kBlurRegion = (kBlurTH + 2 * kBlurMaxPasses) * (kBlurTW + 2 * kBlurMaxPasses);
+template <bool FLOAT>
+__global__ void __launch_bounds__(256)
+blur_fused_kernel(const void* __restrict__ img, int fmt, int H, int W, int passes, float* __restrict__ out) {
+  using T = typename std::conditional<FLOAT, float, uint8_t>::type;
+  __shared__ T s_buf[2][kBlurRegion];
+  const int plane = blockIdx.z, b = plane / 3, c = plane % 3;
+  const int y0 = blockIdx.y * kBlurTH - passes, x0 = blockIdx.x * kBlurTW - passes;  // image coordinates of region (0,0)
+  const int RH = kBlurTH + 2 * passes, RW = kBlurTW + 2 * passes;
+  for (int i = threadIdx.x; i < RH * RW; i += blockDim.x) {
+    const int y = y0 + i / RW, x = x0 + i % RW;
+    const bool in = y >= 0 && y < H && x >= 0 && x < W;
+    if constexpr (FLOAT) s_buf[0][i] = in ? load_f(img, fmt, b, c, y, x, H, W) : 0.0f;
+    else s_buf[0][i] = in ? static_cast<uint8_t>(load_u8(img, fmt, b, c, y, x, H, W)) : static_cast<uint8_t>(0);
+  }
+  __syncthreads();
+  int cur = 0;
+  for (int p = 1; p <= passes; ++p) {
+    const T* src = s_buf[cur];
+    T* dst = s_buf[cur ^ 1];
+    const int h = RH - 2 * p, w = RW - 2 * p;  // region still exact after this pass
+    if constexpr (FLOAT) {
+      for (int i = threadIdx.x; i < h * w; i += blockDim.x) {
+        const int ry = p + i / w, rx = p + i % w;
+        const int y = y0 + ry, x = x0 + rx;
+        float acc = 0.0f;
+        if (y >= 0 && y < H && x >= 0 && x < W) {
+          const float ninth = 1.0f / 9.0f;
+#pragma unroll
+          for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx) {
+              int yy = y + dy, xx = x + dx;
+              yy = yy < 0 ? -yy : (yy >= H ? 2 * H - 2 - yy : yy);
+              xx = xx < 0 ? -xx : (xx >= W ? 2 * W - 2 - xx : xx);
+              acc = __fadd_rn(acc, __fmul_rn(src[(yy - y0) * RW + (xx - x0)], ninth));
+            }
+        }
+        dst[ry * RW + rx] = acc;
+      }
+    } else {
+      // integer sums are order-free: a thread walks down one column of a row segment keeping the horizontal 3-sums of
+      // the last two rows (3 shared-memory loads and one store per output instead of 9 loads)
+      const int segs = static_cast<int>(blockDim.x) / w;  // 64 <= w <= 86: 2..4 row segments per column
+      const int seg_rows = (h + segs - 1) / segs;
+      const int col = static_cast<int>(threadIdx.x) % w, seg = static_cast<int>(threadIdx.x) / w;
+      const int rx = p + col, r_begin = p + seg * seg_rows, r_end = min(p + h, r_begin + seg_rows);
+      if (seg < segs && r_begin < r_end) {
+        const int x = x0 + rx;
+        const bool x_in = x >= 0 && x < W;
+        auto hsum = [&](int ry) {
+          const uint8_t* r = src + ry * RW + rx;
+          return static_cast<int>(r[-1]) + static_cast<int>(r[0]) + static_cast<int>(r[1]);
+        };
+        int ha = hsum(r_begin - 1), hb = hsum(r_begin);
+        for (int ry = r_begin; ry < r_end; ++ry) {
+          const int hc = hsum(ry + 1);
+          const int y = y0 + ry;
+          const bool in = x_in && y >= 0 && y < H;
+          dst[ry * RW + rx] = in ? static_cast<uint8_t>((ha + hb + hc + 4) / 9) : static_cast<uint8_t>(0);
+          ha = hb;
+          hb = hc;
+        }
+      }
+    }
+    __syncthreads();
+    cur ^= 1;
+  }
+  const T* fin = s_buf[cur];
+  const size_t hw = static_cast<size_t>(H) * W;
+  for (int i = threadIdx.x; i < kBlurTH * kBlurTW; i += blockDim.x) {
+    const int ty = i / kBlurTW, tx = i % kBlurTW;
+    const int y = blockIdx.y * kBlurTH + ty, x = blockIdx.x * kBlurTW + tx;
+    if (y < H && x < W) {
+      const T v = fin[(ty + passes) * RW + tx + passes];
+      float o;
+      if constexpr (FLOAT) o = v; else o = static_cast<float>(v) / 255.0f;
+      out[(static_cast<size_t>(b) * 3 + c) * hw + static_cast<size_t>(y) * W + x] = o;
+    }
+  }
 }
 
 // ---- stem: perturbed pixel -> Conv2d(3,32,1) -> bf16, written into channel groups [cg0, cg0+4) of the

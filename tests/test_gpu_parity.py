@@ -271,6 +271,26 @@ def test_float_blur_matches_restatement(dev):
         assert np.array_equal(got, po.f_box_blur(x.numpy(), times))
 
 
+@pytest.mark.parametrize("fuse", [True, False])
+def test_blur_families_fused_and_per_pass_paths(dev, fuse, monkeypatch):
+    """Both blur families on images that span several 32x64 tiles (and do not divide into them), for pass counts on
+    either side of the fused kernel's limit (12), bit-exact against the oracle; UB_NO_BLUR_FUSE=1 selects the
+    pass-per-launch kernels for every count."""
+    from image_segmentation_b200.engine import Engine, Perturbation as P
+    if not fuse:
+        monkeypatch.setenv("UB_NO_BLUR_FUSE", "1")
+    eng = Engine(dev, "unet", 3, 3, 4)  # the switch is read when a context is created
+    g = torch.Generator().manual_seed(5)
+    u8 = torch.randint(0, 256, (3, 3, 72, 136), generator=g, dtype=torch.uint8)
+    xf = torch.rand((3, 3, 72, 136), generator=g)
+    for passes in (0, 1, 2, 9, 12, 13):
+        want = po.dequantise(po.u8_blur(u8.numpy(), passes))
+        for src in (u8.permute(0, 2, 3, 1).contiguous().to(dev), (u8.float() / 255.0).to(dev)):
+            assert np.array_equal(eng.perturb(src, P.u8_blur(passes)).cpu().numpy(), want), ("u8", passes)
+        assert np.array_equal(eng.perturb(xf.to(dev), P.f_blur(passes)).cpu().numpy(), po.f_box_blur(xf.numpy(), passes)), ("f", passes)
+    eng.close()
+
+
 def test_dropin_modules_replay_reference_rng(dev):
     """Seeded host draws + CUDA arithmetic == oracle with the same draws (Dataset wrappers)."""
     from image_segmentation_b200.customDatasets import perturbations as P
