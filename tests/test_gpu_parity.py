@@ -527,7 +527,7 @@ def test_clipunet_prompt_logits_against_reference_golden(dev):
     assert util.rel_err(got2, ref2) < 2e-2
 
 
-@pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL"])
+@pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_HEAD_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL"])
 def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     """The diagnostic switches select other kernels for the same layers (streamed weights, 9-tap thin layers, single
     CTAs, plain launches); they must stay correct: same logits within bf16 accumulation-order noise, same
@@ -548,3 +548,42 @@ def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     assert util.rel_err(alt.cpu(), base.cpu()) < 5e-3
     agree = float((alt.argmax(1) == base.argmax(1)).float().mean())
     assert agree > 0.999, (flag, agree)
+
+
+def test_head_argmax_shortcut_equals_softmax_argmax(dev, monkeypatch):
+    """The head epilogue takes the argmax straight from the logits when the lead over the runner-up exceeds 1e-4 and
+    evaluates softmax -> argmax (models/losses.py:48-50) only for near-ties.  With UB_DBG=8 every pixel goes through
+    the softmax: predictions and confusion counts must be identical bit for bit — on a default-initialised model, whose
+    logits are almost equal everywhere (a large share of near-ties), and on one with realistic margins."""
+    from image_segmentation_b200 import runtime, synthetic
+    from image_segmentation_b200.models.UNet import UNet
+    imgs, masks = synthetic.make_dataset(6, 64, 128, seed=21)
+    for randomise in (False, True):
+        torch.manual_seed(1234)
+        m = UNet().eval()
+        sd = synthetic.randomize_batchnorm(m.state_dict(), seed=7) if randomise else m.state_dict()
+        if not randomise:  # squeeze the margins further: many pixels inside the 1e-4 band, some exact ties
+            sd = {k: v.clone() for k, v in sd.items()}
+            sd["out.weight"] = sd["out.weight"] * 1e-3
+            sd["out.bias"] = torch.zeros_like(sd["out.bias"])
+        out = {}
+        for dbg in ("0", "8"):
+            monkeypatch.setenv("UB_DBG", dbg)
+            eng = runtime.new_engine(dev, "unet", 3, 3, 4)
+            try:
+                eng.load_state_dict(sd)
+                r = eng.eval_batches(imgs.to(dev), masks.to(dev), None, 4, want_pred=True, want_logits=True)
+                out[dbg] = (r["pred"].cpu(), r["cm"].cpu(), r["logits"].cpu())
+            finally:
+                eng.close()
+        assert torch.equal(out["0"][2], out["8"][2])
+        assert torch.equal(out["0"][0], out["8"][0]) and torch.equal(out["0"][1], out["8"][1])
+        if randomise:  # realistic margins: both equal the reference rule evaluated by torch on the CPU (with logits 1e-5
+            # apart, torch's CPU softmax and CUDA's expf/division differ in the last bit, which decides such ties)
+            assert torch.equal(out["0"][0].long(), unet_oracle.hard_prediction(out["0"][2]))
+        z = out["0"][2]
+        top2 = z.topk(2, dim=1).values
+        near = float(((top2[:, 0] - top2[:, 1]) <= 1e-4).float().mean())
+        print(f"head shortcut: share of pixels inside the 1e-4 band = {near:.3f} (randomised BN: {randomise})")
+        if not randomise:
+            assert near > 0.05  # the slow path is really exercised
