@@ -92,6 +92,7 @@ struct ub_ctx {
   bool no_pairq = false;      // UB_NO_PAIRQ=1: the big ConvTranspose runs as single CTAs with streamed weights
   int dbg = 0;                // UB_DBG: ablation hooks of conv_tc_kernel (1 = drain-only epilogue, 2 = no MMA, 8 = head always evaluates the softmax)
   bool no_kxs = false;        // UB_NO_KXS=1: thin layers run the standard (9-tap) kernel
+  bool stem_fold = true;      // UB_NO_STEM_FOLD=1: the 32-channel stem output is materialised (stem_kernel) instead of being folded into its readers' weights
   bool no_blur_fuse = false;  // UB_NO_BLUR_FUSE=1: blur families run one launch per pass (the path for > 12 passes)
   bool head_no_kxs = false;   // UB_HEAD_NO_KXS=1: only the head layer (dec4.conv.3) runs the 9-tap kernel
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
@@ -138,7 +139,13 @@ int pick_block_n(int n_total) { return n_total >= 256 ? 256 : n_total; }
 
 // conv3x3 + BatchNorm(eval) folded:  w' = w*g/sqrt(var+eps),  b' = (b-mean)*g/sqrt(var+eps)+beta
 // (processing_blocks.py:43-44).  Packed K order = (ky*3+kx)*Cin + ci, K contiguous per output channel.
-int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_key) {
+// fold_at >= 0: the 32 input channels [fold_at, fold_at + 32) are the stem output Conv2d(3,32,1)(x) (models/UNet.py:62,
+// no activation before the next conv).  The layer is linear in them, so they are replaced by 16 channels
+// (r, g, b, 1, r_lo, g_lo, b_lo, 0 ... 0) of the packed image with composed weights  w'[co][c][tap] = sum_ci w[co][ci][tap] * S[ci][c]  and
+// w'[co][3][tap] = sum_ci w[co][ci][tap] * b_S[ci]  (the constant-one channel is zero outside the image, exactly like the
+// zero padding of the stem output); fold_width (16 or 32) input channels are reserved for them, the rest with zero weights.
+// Stored under "<conv_key>+stem".
+int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_key, int fold_at = -1, int fold_width = 16) {
   const HostTensor* w = find(ctx, conv_key + ".weight");
   const HostTensor* b = find(ctx, conv_key + ".bias");
   const HostTensor* g = find(ctx, bn_key + ".weight");
@@ -150,17 +157,19 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   if (w->shape.size() != 4 || w->shape[2] != 3 || w->shape[3] != 3)
     return fail(ctx, UB_ERR_INVALID, "%s.weight is not [Cout,Cin,3,3]", conv_key.c_str());
   GemmLayer L;
-  L.key = conv_key;
+  L.key = fold_at >= 0 ? conv_key + "+stem" : conv_key;
   L.cout = static_cast<int>(w->shape[0]);
   const int cin_w = static_cast<int>(w->shape[1]);
+  if (fold_at >= 0 && (fold_at % 8 != 0 || fold_at + 32 != cin_w))
+    return fail(ctx, UB_ERR_UNSUPPORTED, "%s: the stem channels must be the last 32 inputs", conv_key.c_str());
   // a layer with fewer than 32 input channels (the PromptEncoder's first conv, Cin = 1) reads a zero-padded
   // 32-channel operand: the extra weight columns are zero
-  L.cin = cin_w < 32 ? 32 : cin_w;
+  L.cin = fold_at >= 0 ? fold_at + fold_width : (cin_w < 32 ? 32 : cin_w);
   L.n_total = L.cout;
   L.ksize = 3;
   L.block_n = pick_block_n(L.n_total);
-  L.bk = (L.cin % 64 == 0) ? 64 : 32;
-  if (L.cin % 32 != 0 || L.cout % 32 != 0)
+  L.bk = (L.cin % 64 == 0) ? 64 : (L.cin % 32 == 0 ? 32 : 16);
+  if (L.cin % 16 != 0 || L.cout % 32 != 0)
     return fail(ctx, UB_ERR_UNSUPPORTED, "%s: channel counts must be multiples of 32", conv_key.c_str());
   const size_t K = static_cast<size_t>(9) * L.cin;
   std::vector<__nv_bfloat16> packed(static_cast<size_t>(L.cout) * K, __float2bfloat16(0.0f));
@@ -168,10 +177,25 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   for (int co = 0; co < L.cout; ++co) {
     const double s = static_cast<double>(g->data[co]) / std::sqrt(static_cast<double>(var->data[co]) + 1e-5);
     bias[co] = static_cast<float>((static_cast<double>(b->data[co]) - mu->data[co]) * s + be->data[co]);
-    for (int ci = 0; ci < cin_w; ++ci)
+    const int n_direct = fold_at >= 0 ? fold_at : cin_w;
+    for (int ci = 0; ci < n_direct; ++ci)
       for (int t = 0; t < 9; ++t)
         packed[co * K + static_cast<size_t>(t) * L.cin + ci] =
             __float2bfloat16(static_cast<float>(w->data[(static_cast<size_t>(co) * cin_w + ci) * 9 + t] * s));
+    if (fold_at >= 0) {
+      for (int t = 0; t < 9; ++t) {
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};  // r, g, b, one
+        for (int ci = 0; ci < 32; ++ci) {
+          const double wv = w->data[(static_cast<size_t>(co) * cin_w + fold_at + ci) * 9 + t];
+          for (int c = 0; c < 3; ++c) acc[c] += wv * ctx->stem.w[ci * 3 + c];
+          acc[3] += wv * ctx->stem.b[ci];
+        }
+        for (int c = 0; c < 4; ++c)
+          packed[co * K + static_cast<size_t>(t) * L.cin + fold_at + c] = __float2bfloat16(static_cast<float>(acc[c] * s));
+        for (int c = 0; c < 3; ++c)  // channels 4-6: the bf16 rounding residue of r, g, b (image_pack_kernel), same weights
+          packed[co * K + static_cast<size_t>(t) * L.cin + fold_at + 4 + c] = __float2bfloat16(static_cast<float>(acc[c] * s));
+      }
+    }
   }
   int rc;
   if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.w), packed.size() * 2))) return rc;
@@ -330,6 +354,15 @@ int pack_all(ub_ctx* ctx) {
     if ((rc = pack_conv(ctx, "bottleneck.conv.0", "bottleneck.conv.1"))) return rc;
     if ((rc = pack_conv(ctx, "bottleneck.conv.3", "bottleneck.conv.4"))) return rc;
   }
+  // the stem's two readers, once more with the stem folded into their weights (the plain versions stay for the
+  // layer-wise debug entry and UB_NO_STEM_FOLD)
+  if ((rc = pack_conv(ctx, "enc1.block.0.conv.0", "enc1.block.0.conv.1", 0))) return rc;
+  if (!ae) {
+    snprintf(k, sizeof(k), "dec%d.conv.conv", ctx->n_enc + 1);
+    // (32 channels wide, the upper 16 with zero weights over planes nobody writes: 64 input channels keep the BK = 64
+    // kx-stacked kernel — with 48 channels as three BK = 16 chunks the layer was slower, 22.2 against 20.7 ms)
+    if ((rc = pack_conv(ctx, std::string(k) + ".0", std::string(k) + ".1", 32, 32))) return rc;
+  }
   for (int j = 1; j <= ctx->n_enc + (ae ? 0 : 1); ++j) {
     snprintf(k, sizeof(k), "dec%d", j);
     if ((rc = pack_convt(ctx, std::string(k) + ".up"))) return rc;
@@ -366,7 +399,7 @@ int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total,
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(w), dims, strides,
                                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                 bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                                 bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (bk == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B),
                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(ctx, UB_ERR_CUDA, "cuTensorMapEncodeTiled(weights) failed: %d", static_cast<int>(r));
   return UB_OK;
@@ -379,6 +412,7 @@ int pick_tw(const ub_ctx* ctx, const GemmLayer& L, int mode) {
   if (ctx->no_kxs || !L.w_kxs || L.ksize != 3 || mode == ub::EPI_CONVT) return 8;
   if (ctx->head_no_kxs && mode == ub::EPI_HEAD) return 8;
   if (L.bk == 32 && mode != ub::EPI_HEAD) return 8;  // Cin = 32: only the head layer gains (enc1.conv.0 is write-bound)
+  if (L.bk == 16 && L.cout == 64) return 8;          // enc1.conv.0 with the stem folded in: 9 small MMAs, write-bound
   return mode == ub::EPI_POOL ? 16 : 32;
 }
 
@@ -563,6 +597,7 @@ int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cuda
   if (ub::is_kxs(cp.tw)) {  // thin 3x3 layers, N = 3 * cout
     if (bk == 32 && cp.tw == 32 && cp.cout == 64) return launch_inst<192, 32, 3, 32>(ctx, cp, st);
     if (bk == 32 && cp.tw == 32 && cp.cout == 32) return launch_inst<96, 32, 3, 32>(ctx, cp, st);
+    if (bk == 16 && cp.tw == 32 && cp.cout == 32) return launch_inst<96, 16, 3, 32>(ctx, cp, st);
     if (bk != 64) return fail(ctx, UB_ERR_UNSUPPORTED, "no kx-stacked kernel for BK=%d tw=%d", bk, cp.tw);
     if (cp.tw == 32 && cp.cout == 64) return launch_inst<192, 64, 3, 32>(ctx, cp, st);
     if (cp.tw == 32 && cp.cout == 32) return launch_inst<96, 64, 3, 32>(ctx, cp, st);
@@ -584,10 +619,15 @@ int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cuda
       case 128: return launch_ks<128, 64>(ctx, cp, st);
       case 256: return launch_ks<256, 64>(ctx, cp, st);
     }
-  } else if (cp.ksize == 3) {  // the two Cin = 32 layers (enc1.conv.0, dec4.conv.3)
+  } else if (bk == 32 && cp.ksize == 3) {  // the two Cin = 32 layers (enc1.conv.0, dec4.conv.3)
     switch (block_n) {
       case 32: return launch_inst<32, 32, 3>(ctx, cp, st);
       case 64: return launch_inst<64, 32, 3>(ctx, cp, st);
+    }
+  } else if (bk == 16 && cp.ksize == 3) {  // the stem's two readers with the stem folded in (16 / 48 input channels)
+    switch (block_n) {
+      case 32: return launch_inst<32, 16, 3>(ctx, cp, st);
+      case 64: return launch_inst<64, 16, 3>(ctx, cp, st);
     }
   }
   return fail(ctx, UB_ERR_UNSUPPORTED, "no kernel for BLOCK_N=%d BK=%d ksize=%d", block_n, bk, cp.ksize);
@@ -678,7 +718,8 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
   // encoder (models/UNet.py:63-65): conv.0 -> conv.3 + MaxPool into the skip planes of the next concat buffer
   for (int i = 1; i <= n; ++i) {
     snprintf(k, sizeof(k), "enc%d.block.0.conv", i);
-    if ((rc = add_gemm(std::string(k) + ".0", skip_half(i - 1), 2 * skip_width(i - 1) / 8, hl(i - 1), wl(i - 1),
+    const bool fold = (i == 1 && ctx->stem_fold);  // reads the packed image (16 channels) through composed weights
+    if ((rc = add_gemm(std::string(k) + (fold ? ".0+stem" : ".0"), skip_half(i - 1), 2 * skip_width(i - 1) / 8, hl(i - 1), wl(i - 1),
                        ub::EPI_STORE, bufp(i_enc[i]), skip_width(i) / 8, 0))) return rc;
     if ((rc = add_gemm(std::string(k) + ".3", bufp(i_enc[i]), skip_width(i) / 8, hl(i - 1), wl(i - 1), ub::EPI_POOL,
                        bufp(i_cat[i]), 2 * skip_width(i) / 8, skip_width(i) / 8))) return rc;
@@ -755,9 +796,9 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
       s.hi = 2 * xh; s.wi = 2 * xw; s.ho = hl(l); s.wo = wl(l); s.c = sw; s.out_cgs = 2 * sw / 8; s.out_cg0 = 0;
       pl->steps.push_back(s);
     }
-    if ((rc = add_gemm(std::string(k) + ".conv.conv.0", bufp(i_cat[l]), 2 * sw / 8, hl(l), wl(l), ub::EPI_STORE,
-                       bufp(i_da[j]), sw / 8, 0))) return rc;
     const bool last = (j == n + 1);
+    if ((rc = add_gemm(std::string(k) + ((last && ctx->stem_fold) ? ".conv.conv.0+stem" : ".conv.conv.0"), bufp(i_cat[l]), 2 * sw / 8,
+                       hl(l), wl(l), ub::EPI_STORE, bufp(i_da[j]), sw / 8, 0))) return rc;
     if ((rc = add_gemm(std::string(k) + ".conv.conv.3", bufp(i_da[j]), sw / 8, hl(l), wl(l), last ? ub::EPI_HEAD : ub::EPI_STORE,
                        bufp(i_db[j]), sw / 8, 0))) return rc;
     x = bufp(i_db[j]); xc = sw; xh = hl(l); xw = wl(l);
@@ -844,8 +885,15 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
     if ((rc = run_blur(ctx, pl, P, img, fmt, nb, dst, st))) return rc;
     ub::PerturbDev none;
     memset(&none, 0, sizeof(none));
-    ub::stem_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(none, ctx->stem, dst, UB_IMG_F32_NCHW, nb, H, W, pl->stem_out,
-                                                        pl->stem_cgs, pl->stem_cg0, nullptr);
+    if (ctx->stem_fold)
+      ub::image_pack_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(none, dst, UB_IMG_F32_NCHW, nb, H, W, pl->stem_out,
+                                                                pl->stem_cgs, pl->stem_cg0, nullptr);
+    else
+      ub::stem_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(none, ctx->stem, dst, UB_IMG_F32_NCHW, nb, H, W, pl->stem_out,
+                                                          pl->stem_cgs, pl->stem_cg0, nullptr);
+  } else if (ctx->stem_fold) {
+    ub::image_pack_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(P, img, fmt, nb, H, W, pl->stem_out, pl->stem_cgs,
+                                                              pl->stem_cg0, perturbed_out);
   } else {
     ub::stem_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(P, ctx->stem, img, fmt, nb, H, W, pl->stem_out, pl->stem_cgs,
                                                         pl->stem_cg0, perturbed_out);
@@ -965,6 +1013,7 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   { const char* e = getenv("UB_NO_PAIRQ"); ctx->no_pairq = e && e[0] == '1'; }
   { const char* e = getenv("UB_HEAD_NO_KXS"); ctx->head_no_kxs = e && e[0] == '1'; }
   { const char* e = getenv("UB_NO_BLUR_FUSE"); ctx->no_blur_fuse = e && e[0] == '1'; }
+  { const char* e = getenv("UB_NO_STEM_FOLD"); ctx->stem_fold = !(e && e[0] == '1'); }
   { const char* e = getenv("UB_DBG"); ctx->dbg = e ? atoi(e) : 0; }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';

@@ -136,7 +136,7 @@ struct ConvCfg {
   static constexpr int TAIL_TMEM = TAIL_DICE + kMaxEpiGroups * kMaxClasses * 2 * 8;
   static constexpr int TAIL_BYTES = ((TAIL_TMEM + 16 + 1023) / 1024) * 1024;  // keeps the rings 1024B aligned
   static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;       // 1024 = alignment slack
-  static_assert(BK == 64 || BK == 32, "channel chunk");
+  static_assert(BK == 64 || BK == 32 || BK == 16, "channel chunk");
   static_assert(!CG2 || (TW == 8 && BLOCK_N >= 128), "CTA pairs are for the wide standard-geometry layers");
   static_assert(!KXS || (KSIZE == 3 && BLOCK_N % 48 == 0 && (TW == 16 || TW == 32)), "kx-stacked geometry");
   static_assert(TMEM_COLS >= 32 && (TMEM_COLS & (TMEM_COLS - 1)) == 0 && TMEM_COLS <= 512, "TMEM columns");

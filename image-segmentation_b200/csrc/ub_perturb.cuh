@@ -391,4 +391,50 @@ stem_kernel(const __grid_constant__ PerturbDev P, const __grid_constant__ StemWe
   }
 }
 
+// ---- stem folded into its readers (ub_api.cu: pack_conv fold_at): the perturbed pixel itself is the layer input.
+// Writes channel group cg0 of the level-0 concat buffer with (r, g, b, 1, r_lo, g_lo, b_lo, 0) in bf16 — 16 bytes per pixel; the
+// following group stays zero from the arena's memset (the layers read 16 channels).  Four pixels per thread, 64
+// contiguous bytes per thread.
+__global__ void __launch_bounds__(256)
+image_pack_kernel(const __grid_constant__ PerturbDev P, const void* __restrict__ img, int fmt, int n, int H, int W,
+                  __nv_bfloat16* __restrict__ out, int cgs, int cg0, float* __restrict__ perturbed_out) {
+  __shared__ uint8_t s_lut[256];
+  if (P.kind == UB_P_U8_LUT) {
+    s_lut[threadIdx.x] = P.lut[threadIdx.x];  // blockDim.x == 256
+    __syncthreads();
+  }
+  const size_t hw = static_cast<size_t>(H) * W;
+  const size_t total = hw * n;
+  const size_t i0 = (static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x) * kStemPx;
+  if (i0 >= total) return;
+  const int b = static_cast<int>(i0 / hw);
+  const size_t pix = i0 - static_cast<size_t>(b) * hw;
+  const int y = static_cast<int>(pix / W), x = static_cast<int>(pix % W);
+  float v[kStemPx][3];
+#pragma unroll
+  for (int k = 0; k < kStemPx; ++k) perturbed_pixel(P, s_lut, img, fmt, b, y, x + k, H, W, v[k]);
+  if (perturbed_out) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      *reinterpret_cast<float4*>(perturbed_out + (static_cast<size_t>(b) * 3 + c) * hw + pix) =
+          make_float4(v[0][c], v[1][c], v[2][c], v[3][c]);
+  }
+  uint4* dst = reinterpret_cast<uint4*>(out) + (static_cast<size_t>(b) * cgs + cg0) * hw + pix;
+  uint4 q[kStemPx];
+#pragma unroll
+  for (int k = 0; k < kStemPx; ++k) {
+    // channels 4-6 carry what bf16 rounding dropped from r, g, b (same weights as channels 0-2): the layer sees the
+    // pixel to ~16 bits instead of 8
+    const __nv_bfloat16 hr = __float2bfloat16(v[k][0]), hg = __float2bfloat16(v[k][1]), hb = __float2bfloat16(v[k][2]);
+    __nv_bfloat162 rg = __halves2bfloat162(hr, hg);
+    __nv_bfloat162 b1 = __halves2bfloat162(hb, __float2bfloat16(1.0f));
+    __nv_bfloat162 lo_rg = __floats2bfloat162_rn(v[k][0] - __bfloat162float(hr), v[k][1] - __bfloat162float(hg));
+    __nv_bfloat162 lo_b0 = __floats2bfloat162_rn(v[k][2] - __bfloat162float(hb), 0.0f);
+    q[k] = make_uint4(*reinterpret_cast<uint32_t*>(&rg), *reinterpret_cast<uint32_t*>(&b1),
+                      *reinterpret_cast<uint32_t*>(&lo_rg), *reinterpret_cast<uint32_t*>(&lo_b0));
+  }
+  st_global_256(dst, q[0], q[1]);
+  st_global_256(dst + 2, q[2], q[3]);
+}
+
 }  // namespace ub

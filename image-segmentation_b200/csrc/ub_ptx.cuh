@@ -240,11 +240,11 @@ __device__ __forceinline__ void tmem_ld_wait() {
 // Shared-memory matrix descriptor, K-major operand, 128B or 64B swizzle
 // (bit layout: cute/arch/mma_sm100_desc.hpp SmemDescriptor; PTX ISA "tcgen05 matrix descriptor").
 //   [0,14) start>>4 | [16,30) LBO>>4 (unused for swizzled K-major: 1) | [32,46) SBO>>4 = 8 rows
-//   [46,48) version=1 | [49,52) base offset=0 | [61,64) layout: 2 = SW128, 4 = SW64
+//   [46,48) version=1 | [49,52) base offset=0 | [61,64) layout: 2 = SW128, 4 = SW64, 6 = SW32
 template <int kSwizzleBytes>
 __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr) {
-  static_assert(kSwizzleBytes == 128 || kSwizzleBytes == 64, "swizzle");
-  constexpr uint64_t layout = (kSwizzleBytes == 128) ? 2ull : 4ull;
+  static_assert(kSwizzleBytes == 128 || kSwizzleBytes == 64 || kSwizzleBytes == 32, "swizzle");
+  constexpr uint64_t layout = (kSwizzleBytes == 128) ? 2ull : (kSwizzleBytes == 64 ? 4ull : 6ull);
   constexpr uint64_t sbo = (8u * kSwizzleBytes) >> 4;
   return static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (sbo << 32) |
          (1ull << 46) | (layout << 61);

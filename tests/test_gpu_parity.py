@@ -587,3 +587,38 @@ def test_head_argmax_shortcut_equals_softmax_argmax(dev, monkeypatch):
         print(f"head shortcut: share of pixels inside the 1e-4 band = {near:.3f} (randomised BN: {randomise})")
         if not randomise:
             assert near > 0.05  # the slow path is really exercised
+
+
+def test_folded_stem_and_materialised_stem_match_the_oracle(trained, dev, monkeypatch):
+    """Default plan: the stem Conv2d(3,32,1) is folded into the weights of its two readers (enc1.conv.0 over the packed
+    16-channel image, the last decoder conv.0 through the concat) — models/UNet.py:62-63,72 apply no activation in
+    between, so the composition is exact in real arithmetic.  UB_NO_STEM_FOLD=1 materialises the 32-channel stem output
+    as the reference does.  Both must match the fp32 oracle within the north-star tolerance, on images whose borders
+    exercise the zero padding of the stem OUTPUT (the constant-one channel), and agree with each other."""
+    from image_segmentation_b200 import runtime, synthetic
+    m, sd = trained
+    imgs, masks = synthetic.make_dataset(5, 64, 128, seed=31)
+    x = synthetic.to_float_nchw(imgs).to(dev)
+    ref = unet_oracle.forward({k: v.to(dev) for k, v in sd.items()}, x).cpu()
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("UB_NO_STEM_FOLD", flag)
+        eng = runtime.new_engine(dev, "unet", 3, 3, 2)
+        try:
+            eng.load_state_dict(m.state_dict())
+            r = eng.eval_batches(imgs.to(dev), masks.to(dev), None, 4, want_pred=True, want_logits=True)
+            out[flag] = (r["logits"].cpu(), r["pred"].cpu(), r["cm"].cpu())
+        finally:
+            eng.close()
+    for flag, name in (("0", "folded"), ("1", "materialised")):
+        z, pred, cm = out[flag]
+        rel = util.rel_err(z, ref)
+        agree = float((pred.long() == unet_oracle.hard_prediction(ref)).float().mean())
+        border = torch.zeros_like(pred, dtype=torch.bool)
+        border[:, :2, :] = border[:, -2:, :] = True
+        border[:, :, :2] = border[:, :, -2:] = True
+        rel_border = float((z - ref).abs().permute(0, 2, 3, 1)[border].max() / ref.abs().max())
+        print(f"stem {name}: logits rel err {rel:.3e} (border pixels {rel_border:.3e}), argmax agreement {agree:.5f}")
+        assert rel < 1e-2 and rel_border < 1e-2 and agree >= 0.999
+        assert int(cm.sum()) == 5 * 64 * 128
+    assert util.rel_err(out["0"][0], out["1"][0]) < 1e-2
