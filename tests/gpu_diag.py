@@ -1,4 +1,4 @@
-"""GPU diagnostics (run on the B200 box): per-layer and end-to-end parity numbers, printed rather than
+"""GPU diagnostics (run on the B200 box; lives under tests/ because its parity modes use the oracle): per-layer and end-to-end parity numbers, printed rather than
 asserted, so one gpurun call tells where a kernel is wrong.  Checker side uses torch on the GPU."""
 import sys
 import time
