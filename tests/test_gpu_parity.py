@@ -622,3 +622,28 @@ def test_folded_stem_and_materialised_stem_match_the_oracle(trained, dev, monkey
         assert rel < 1e-2 and rel_border < 1e-2 and agree >= 0.999
         assert int(cm.sum()) == 5 * 64 * 128
     assert util.rel_err(out["0"][0], out["1"][0]) < 1e-2
+
+
+def test_full_size_level_is_independent_of_the_microbatch_split(trained, dev):
+    """BASELINE.json's full size (3,680 images of 256x256, reference batch 8), one sweep level: size-independent
+    properties instead of an oracle run — every pixel is counted exactly once (checksum of checksums), per-batch row
+    sums equal the per-batch target histogram, and the counts do not depend on how the call is split into launches."""
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.engine import Perturbation as P
+    m, sd = trained
+    base_i, base_m = synthetic.make_dataset(46, 256, 256, seed=99)
+    imgs = base_i.repeat(80, 1, 1, 1).contiguous().to(dev)
+    masks = base_m.repeat(80, 1, 1).contiguous().to(dev)
+    assert imgs.shape[0] == 3680
+    spec = P.u8_contrast(1.1)
+    cms = []
+    for mb in (148, 61):
+        eng = m.engine(dev, max_microbatch=mb)
+        cms.append(eng.eval_batches(imgs, masks, spec, 8)["cm"].cpu())
+    assert cms[0].shape == (460, 3, 3)
+    assert torch.equal(cms[0], cms[1])
+    assert int(cms[0].sum()) == 3680 * 256 * 256
+    hist = torch.stack([(masks.view(460, -1) == c).sum(dim=1) for c in range(3)], dim=1).cpu()
+    assert torch.equal(cms[0].sum(dim=2), hist)
+    # the data repeats every 46 images = 5.75 batches, so batches 23 apart (4 periods) see the same images
+    assert torch.equal(cms[0][:23], cms[0][23:46])
