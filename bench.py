@@ -324,7 +324,7 @@ def run_gpu(args, rank, world, local_rank):
                                           f"capture at micro-batch {tr['microbatch']}, x images per launch here, mean over "
                                           f"the 20 GEMM launches of a micro-batch")
             # every layer's input read once + output written once, bf16 blocked tensors, per image
-            roofline["traffic_algorithmic"] = 91.3e6 * per_launch_images / 20   # every GEMM layer's input once + output once (enc1.conv.0 reads the 16-channel packed image)
+            roofline["traffic_algorithmic"] = 89.2e6 * per_launch_images / 20   # every GEMM layer's input once + output once (the stem's two readers read the 16-channel packed image)
     except Exception:
         pass
     if args.layers and rank == 0:

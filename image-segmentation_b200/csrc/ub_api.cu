@@ -39,6 +39,8 @@ struct HostTensor {
 struct GemmLayer {
   std::string key;  // state_dict prefix of the conv / up module
   int cin = 0, cout = 0, n_total = 0, ksize = 3, block_n = 0, bk = 64, relu = 1;
+  int cin_src = 0;  // channels that exist in the source tensor when fewer than cin (the rest of the K range meets zero weights;
+                    // the tensor map ends there, so TMA zero-fills those planes of the box without reading memory)
   bool is_convt = false;
   __nv_bfloat16* w = nullptr;  // [n_total][ksize*ksize*cin] bf16, BN folded
   __nv_bfloat16* w_kxs = nullptr;  // thin 3x3 layers: [(ky*3+kx)*cout + co][cin] for the kx-stacked kernel
@@ -165,6 +167,7 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   // a layer with fewer than 32 input channels (the PromptEncoder's first conv, Cin = 1) reads a zero-padded
   // 32-channel operand: the extra weight columns are zero
   L.cin = fold_at >= 0 ? fold_at + fold_width : (cin_w < 32 ? 32 : cin_w);
+  if (fold_at >= 0) L.cin_src = fold_at + 16;  // the packed image has two channel groups
   L.n_total = L.cout;
   L.ksize = 3;
   L.block_n = pick_block_n(L.n_total);
@@ -422,7 +425,7 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   int rc;
   const int tw = pick_tw(ctx, L, mode);
   cp->tw = tw;
-  if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin, src_cgs, W, H, B, L.ksize, L.bk, tw))) return rc;
+  if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin_src ? L.cin_src : L.cin, src_cgs, W, H, B, L.ksize, L.bk, tw))) return rc;
   // CTA pairs (cta_group::2) for the wide layers whose weights cannot stay resident in shared memory
   const size_t w_tile_bytes = static_cast<size_t>(L.ksize) * L.ksize * L.cin * L.block_n * 2;
   const bool resident = w_tile_bytes + 2 * 24576 <= 220 * 1024;  // mirrors choose_pipeline's weight-stationary test
