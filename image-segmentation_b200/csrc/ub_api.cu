@@ -443,6 +443,9 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   } else {
     if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, cp->cg2 ? L.block_n / 2 : L.block_n, L.bk))) return rc;
   }
+  // a single chunk whose tail is zero padding (the last decoder conv.0 with the stem folded in: 48 of 64 channels): the MMAs
+  // over the padding are not issued
+  cp->k_steps = (L.cin_src && L.cin == L.bk && L.cin_src < L.cin) ? (L.cin_src + 15) / 16 : 0;
   cp->B = B; cp->H = H; cp->W = W;
   cp->cin = L.cin; cp->ksize = L.ksize; cp->n_total = L.n_total;
   cp->mode = mode; cp->relu = L.relu;

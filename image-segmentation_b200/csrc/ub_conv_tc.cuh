@@ -97,6 +97,7 @@ struct ConvParams {
   int pairq;  // CTA pairs: pair-granular tile order with the n-tile fastest (weight-stationary pairs, n_tiles > 1)
   int cg2; // 1 = CTA-pair kernel (host: tmB box holds N/2 rows, even grid, cluster launch)
   int tw;  // tile width chosen by the host (8 standard, 16/32 kx-stacked); the kernel has it as a template parameter
+  int k_steps;  // MMAs (16 channels each) issued per tap and chunk; fewer than BK/16 when the tail of the chunk is zero padding
   int sa;  // A stages (activation boxes)
   int sb;  // B stages when streaming weights; unused when the kernel is the WS instantiation
 };
@@ -387,6 +388,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     uint32_t pa = 0, pb = 0;
     int it = 0;
     const bool no_mma = (p.dbg & 2) != 0;  // ablation hook, hoisted out of the issue loop
+    const int k_steps = p.k_steps > 0 ? p.k_steps : BK / 16;
 #pragma unroll 1
     for (int t = t_first; t < total_tiles; t += t_step, ++it) {
       const int acc = it % ACC;
@@ -412,6 +414,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
                 const uint32_t b_lo = b_lo_ring + static_cast<uint32_t>(c * TAPS + tap) * B_STAGE_U;
 #pragma unroll
                 for (int k = 0; k < BK / 16; ++k) {
+                  if (k >= k_steps) continue;  // zero-padded tail of the chunk (host: fill_gemm)
                   const uint32_t al = a_tap + k * A_KSTEP_U, bl = b_lo + 2 * k;
                   if (tap == 0 && k == 0) {
                     if (c == 0) mma(std::false_type{}, d_tmem, al, a_hi, bl, b_hi);
@@ -438,6 +441,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
               if (!no_mma) {
 #pragma unroll
                 for (int k = 0; k < BK / 16; ++k) {
+                  if (k >= k_steps) continue;  // zero-padded tail of the chunk (host: fill_gemm)
                   const uint32_t al = a_tap + k * A_KSTEP_U, bl = b_lo + 2 * k;
                   if (tap == 0 && k == 0) {
                     if (c == 0) mma(std::false_type{}, d_tmem, al, a_hi, bl, b_hi);
