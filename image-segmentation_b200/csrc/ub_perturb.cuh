@@ -399,8 +399,12 @@ __global__ void __launch_bounds__(256)
 image_pack_kernel(const __grid_constant__ PerturbDev P, const void* __restrict__ img, int fmt, int n, int H, int W,
                   __nv_bfloat16* __restrict__ out, int cgs, int cg0, float* __restrict__ perturbed_out) {
   __shared__ uint8_t s_lut[256];
-  if (P.kind == UB_P_U8_LUT) {
-    s_lut[threadIdx.x] = P.lut[threadIdx.x];  // blockDim.x == 256
+  __shared__ float s_flut[256];
+  const bool fast = fmt == UB_IMG_U8_NHWC && (P.kind == UB_P_NONE || P.kind == UB_P_U8_LUT);
+  if (P.kind == UB_P_U8_LUT || fast) {
+    const uint8_t u = P.kind == UB_P_U8_LUT ? P.lut[threadIdx.x] : static_cast<uint8_t>(threadIdx.x);  // blockDim.x == 256
+    s_lut[threadIdx.x] = u;
+    s_flut[threadIdx.x] = static_cast<float>(u) / 255.0f;
     __syncthreads();
   }
   const size_t hw = static_cast<size_t>(H) * W;
@@ -411,8 +415,21 @@ image_pack_kernel(const __grid_constant__ PerturbDev P, const void* __restrict__
   const size_t pix = i0 - static_cast<size_t>(b) * hw;
   const int y = static_cast<int>(pix / W), x = static_cast<int>(pix % W);
   float v[kStemPx][3];
+  if (fast) {
+    // uint8 container, value-wise family: the thread's 4 pixels are 12 contiguous bytes (three aligned words), and
+    // lut[u] / 255 comes from one table (same IEEE division as perturbed_pixel, done once per table entry)
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(img) + i0 * 3);
+    const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+    const uint32_t bytes[12] = {w0 & 255u, (w0 >> 8) & 255u, (w0 >> 16) & 255u, w0 >> 24, w1 & 255u, (w1 >> 8) & 255u,
+                                (w1 >> 16) & 255u, w1 >> 24, w2 & 255u, (w2 >> 8) & 255u, (w2 >> 16) & 255u, w2 >> 24};
 #pragma unroll
-  for (int k = 0; k < kStemPx; ++k) perturbed_pixel(P, s_lut, img, fmt, b, y, x + k, H, W, v[k]);
+    for (int k = 0; k < kStemPx; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[k][c] = s_flut[bytes[3 * k + c]];
+  } else {
+#pragma unroll
+    for (int k = 0; k < kStemPx; ++k) perturbed_pixel(P, s_lut, img, fmt, b, y, x + k, H, W, v[k]);
+  }
   if (perturbed_out) {
 #pragma unroll
     for (int c = 0; c < 3; ++c)
