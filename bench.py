@@ -6,7 +6,10 @@ perturb -> U-Net forward -> argmax -> per-batch confusion counts (+ one all-redu
 80 (family, level) pairs of scripts/robustness_evaluation.py:59-92 are visited round-robin.
 
   python bench.py [--gpus N] [--steps K] [--warmup W]            (N > 1: under torchrun, one rank per GPU)
-  python bench.py --impl reference ...    times the CPU oracle port of the same path on the host cores
+  python bench.py --impl reference ...    times the REFERENCE'S OWN modules (baseline/_ref: its Dataset-wrapper
+                                          perturbations, UNet.forward, IoU / PixelAccuracy; byte-for-byte copies made by
+                                          baseline/install_ref.py) on the host cores; the oracle port only when that
+                                          directory is absent
 
 Prints ONE JSON line on rank 0 (contract in the task description): value = device-resident throughput,
 e2e = through the public API with pinned HOST buffers (H2D of the step's images+masks and D2H of the
@@ -125,15 +128,86 @@ def oracle_step(sd, images_u8_nhwc, masks_u8, name, level, ref_batch):
     return scores
 
 
+REF_CLASS = {"gaussian_noise": "GaussianPixelNoise", "gaussian_blur": "GaussianBlur", "contrast_increase": "ContrastIncrease",
+             "contrast_decrease": "ContrastDecrease", "brightness_increase": "BrightnessIncrease",
+             "brightness_decrease": "BrightnessDecrease", "occlusion": "OcclusionIncrease",
+             "salt_pepper_noise": "SaltPepperNoise"}   # scripts/robustness_evaluation.py:59-92
+
+
+def load_reference():
+    """The reference's own modules from baseline/_ref (None when the directory did not travel)."""
+    root = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isfile(os.path.join(root, "models", "UNet.py")):
+        return None
+    from oracle import refload
+    return refload.load(root)
+
+
+class _RefBase(torch.utils.data.Dataset):
+    """Item contract of customDatasets/datasets.py:137-160: (fp32 [3,H,W] = u8/255, int64 [H,W])."""
+
+    def __init__(self, images_u8_nhwc, masks_u8):
+        self.x = images_u8_nhwc.permute(0, 3, 1, 2).float() / 255.0
+        self.t = masks_u8.long()
+
+    def __len__(self):
+        return self.x.shape[0]
+
+    def __getitem__(self, i):
+        return self.x[i], self.t[i]
+
+
+def reference_step(ns, model, images_u8_nhwc, masks_u8, name, level, ref_batch):
+    """One (family, level) pass exactly as the reference runs it (scripts/robustness_evaluation.py:105-124 with the
+    metric block of models/model_wrappers.py:456-458): its Dataset wrapper around the base set, a DataLoader of
+    `ref_batch`, UNet.forward under no_grad, IoU / PixelAccuracy / 2I/(1+I) per batch — all the reference's own code —
+    plus the restated smp Dice (the package is absent; oracle/metrics_oracle.py)."""
+    from oracle import metrics_oracle as mo
+    ds = getattr(ns.perturbations, REF_CLASS[name])(_RefBase(images_u8_nhwc, masks_u8), level)
+    loader = torch.utils.data.DataLoader(ds, batch_size=ref_batch, shuffle=False)
+    iou_fn, pa_fn = ns.losses.IoU(), ns.losses.PixelAccuracy()
+    tot = [0.0, 0.0, 0.0, 0.0]
+    for x, t in loader:
+        with torch.no_grad():
+            z = model(x)
+        iou = iou_fn(z, t)
+        tot[0] += iou.item(); tot[1] += pa_fn(z, t).item(); tot[2] += (2 * iou / (1 + iou)).item()
+        tot[3] += mo.dice_smp(z, t)
+    return [v / len(loader) for v in tot]
+
+
+def make_cpu_arm(sd):
+    """-> (step(images, masks, name, level), kind, description)"""
+    ns = load_reference()
+    if ns is not None and not LARGE:
+        model = ns.UNet().eval()
+        model.load_state_dict(sd)
+        return (lambda im, mk, name, lv: reference_step(ns, model, im, mk, name, lv, REF_BATCH), "reference",
+                "the reference's own modules (baseline/_ref: customDatasets/perturbations.py wrappers -> DataLoader -> "
+                "models/UNet.py forward fp32 -> models/losses.py IoU + PixelAccuracy, restated smp Dice)")
+    if ns is not None and LARGE:
+        model = ns.LargeUNet().eval()
+        model.load_state_dict(sd)
+
+        def step(im, mk, name, lv):
+            with torch.no_grad():
+                z = model(im.permute(0, 3, 1, 2).float() / 255.0)
+            return [ns.losses.IoU()(z, mk.long()).item(), ns.losses.PixelAccuracy()(z, mk.long()).item()]
+        return step, "reference", "the reference's own LargeUNet.forward + IoU + PixelAccuracy (baseline/_ref), fp32"
+    return (lambda im, mk, name, lv: oracle_step(sd, im, mk, name, lv, REF_BATCH), "port",
+            "oracle port of the reference path (baseline/_ref absent), torch CPU fp32")
+
+
 def cpu_time_sample(sd, images, masks, levels, n_sample, reps):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    oracle_step(sd, images[:REF_BATCH], masks[:REF_BATCH], *levels[0], REF_BATCH)  # warm-up
+    step, kind, what = make_cpu_arm(sd)
+    step(images[:REF_BATCH], masks[:REF_BATCH], *levels[0])  # warm-up
     t0 = time.perf_counter()
     for r in range(reps):
-        oracle_step(sd, images[:n_sample], masks[:n_sample], *levels[r % len(levels)], REF_BATCH)
+        step(images[:n_sample], masks[:n_sample], *levels[r % len(levels)])
     dt = time.perf_counter() - t0
-    return n_sample * reps / dt, cores, dt
+    return n_sample * reps / dt, cores, dt, kind, what
 
 
 CLIP = False             # --workload clipunet256: the model the reference's sweep script hard-codes (secondary)
@@ -201,29 +275,100 @@ def run_reference(args, rank, world):
     from image_segmentation_b200 import synthetic
     torch.manual_seed(42)
     sd = net_class()().eval().state_dict()
-    n_sample = 4 if LARGE else 16
+    n_sample = 4 if LARGE else 64
     images, masks = synthetic.make_dataset(n_sample, H, W, seed=99)
     levels = level_list()
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    step, kind, what = make_cpu_arm(sd)
     for i in range(args.warmup):
-        oracle_step(sd, images[:REF_BATCH], masks[:REF_BATCH], *levels[i % 80], REF_BATCH)
+        step(images[:REF_BATCH], masks[:REF_BATCH], *levels[i % 80])
     t0 = time.perf_counter()
     for i in range(args.steps):
-        oracle_step(sd, images, masks, *levels[i % 80], REF_BATCH)
+        step(images, masks, *levels[(args.warmup + i) % 80])
     dt = time.perf_counter() - t0
     v = n_sample * args.steps / dt
     line = base_line(args, world)
-    sample = f"each step = {n_sample} of the {N_IMAGES:,} images of one step (oracle port of the reference path, torch CPU fp32)"
+    sample = f"each step = {n_sample} of the {N_IMAGES:,} images of one (family, level) pass; {what}; {cores} threads"
     line.update({"impl": "reference", "value": v, "ms_per_step": dt / args.steps * 1e3, "dtype": "f32",
-                 "cpu_baseline": {"value": v, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+                 "cpu_baseline": {"value": v, "unit": "images/s", "cores": cores, "kind": kind, "sample": sample},
                  "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": 0})
     print(json.dumps(line), flush=True)
 
 
 # ----------------------------------------------------------------------------- GPU arm
+def timed_forward(fn, warmup=3, steps=10):
+    """ms per call of fn() by CUDA events on the current stream (secondary measurements)."""
+    for _ in range(warmup):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    e1.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def extra_measurements(dev):
+    """Short secondary measurements for the rows after the headline, run AFTER the headline's timed
+    region on the same GPU: each is a few hundred ms of device time.  Synthetic inputs, random-init weights (values do
+    not affect throughput); inputs resident on the device; images/s = images per call / mean call time."""
+    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200.evaluator import RobustnessEvaluator
+    out = {}
+    # (f1) BASELINE.json configs[2]: LargeUNet, 512x512, 64 images per GPU, forward + argmax + confusion counts
+    try:
+        from image_segmentation_b200.models.UNet import LargeUNet
+        torch.manual_seed(42)
+        m = LargeUNet().eval().to(dev)
+        bi, bm = synthetic.make_dataset(8, 512, 512, seed=3)
+        ev = RobustnessEvaluator(m, bi.repeat(8, 1, 1, 1), bm.repeat(8, 1, 1), 64, dev, rank=0, world_size=1, max_microbatch=64)
+        ms = timed_forward(lambda: ev.run_level(None))
+        out["large512"] = {"images_per_s": 64 / (ms * 1e-3), "ms_per_step": ms, "images_per_step": 64,
+                           "tflops": 64 * 226.123e9 / (ms * 1e-3) / 1e12,
+                           "what": "LargeUNet 512x512, 64 images: forward + argmax + counts (configs[2])"}
+        del ev, m
+    except Exception as e:  # a secondary line must never take the headline down
+        out["large512"] = {"error": repr(e)[:200]}
+    # (f2) configs[3]: SegmentationModel(Encoder, SegmentationDecoderSkip) at 256x256, 128 images per GPU
+    try:
+        from image_segmentation_b200.models.autoencoder import Encoder
+        from image_segmentation_b200.models.pre_trained import SegmentationDecoderSkip, SegmentationModel
+        torch.manual_seed(42)
+        m = SegmentationModel(Encoder(), SegmentationDecoderSkip(3)).eval().to(dev)
+        bi, bm = synthetic.make_dataset(16, 256, 256, seed=4)
+        ev = RobustnessEvaluator(m, bi.repeat(8, 1, 1, 1), bm.repeat(8, 1, 1), 8, dev, rank=0, world_size=1, max_microbatch=128)
+        ms = timed_forward(lambda: ev.run_level(None))
+        out["segmodel_b128"] = {"images_per_s": 128 / (ms * 1e-3), "ms_per_step": ms, "images_per_step": 128,
+                                "what": "SegmentationModel (autoencoder Encoder + skip decoder) 256x256, 128 images: "
+                                        "forward + argmax + counts (configs[3])"}
+        del ev, m
+    except Exception as e:
+        out["segmodel_b128"] = {"error": repr(e)[:200]}
+    # (f4) configs[4]: ClipUnetPrompt decoder over frozen CLIP features with the prompt heat-map channel at 224x224; the
+    # CLIP embedding is an INPUT here (precomputed, "frozen features"): the library part only
+    try:
+        from image_segmentation_b200.models.prompt_segmentation import ClipUnetPrompt
+        torch.manual_seed(42)
+        m = ClipUnetPrompt(clip_model=torch.nn.Identity()).eval().to(dev)   # (the CLIP encoder is not called)
+        eng = m.engine(dev, 128)
+        x = synthetic.to_float_nchw(synthetic.make_dataset(16, 224, 224, seed=5)[0]).repeat(8, 1, 1, 1).to(dev)
+        heat = synthetic.prompt_heatmaps(128, 224, 224, seed=6).to(dev)
+        feats = torch.randn((128, 512), device=dev)
+        ms = timed_forward(lambda: eng.forward_prompt(x, heat, feats))
+        out["clip_prompt_224"] = {"images_per_s": 128 / (ms * 1e-3), "ms_per_step": ms, "images_per_step": 128,
+                                  "what": "ClipUnetPrompt 224x224, 128 images, CLIP embeddings given: stem + enc1-3 + "
+                                          "PromptEncoder + fusion + dec1-4 + head -> logits (configs[4])"}
+    except Exception as e:
+        out["clip_prompt_224"] = {"error": repr(e)[:200]}
+    return out
+
+
 def run_gpu(args, rank, world, local_rank):
+    import hashlib
     import torch.distributed as dist
     from image_segmentation_b200 import synthetic
     from image_segmentation_b200.evaluator import RobustnessEvaluator
@@ -244,11 +389,17 @@ def run_gpu(args, rank, world, local_rank):
     eng = ev.engine
     levels = level_list()
 
-    def step(i):
+    def spec_of(i):
         if LARGE:
-            return ev.run_level(None)
+            return None
         name, lv = levels[i % len(levels)]
-        return ev.run_level(make_spec(name, lv, H * W, seed=i))
+        return make_spec(name, lv, H * W, seed=i)
+
+    def step(i):                      # synchronous form: result complete on the compute stream when it returns
+        return ev.run_level(spec_of(i))
+
+    def submit(i):                    # the all-reduce of level i stays in flight on NCCL's stream (evaluator.submit_level)
+        return ev.submit_level(spec_of(i))
 
     def barrier():
         if world > 1:
@@ -262,8 +413,23 @@ def run_gpu(args, rank, world, local_rank):
             return float(t.item())
         return x
 
+    def gather(x):
+        if world > 1:
+            t = torch.zeros((world,), device=dev, dtype=torch.float64)
+            t[rank] = x
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            return [float(v) for v in t.cpu()]
+        return [x]
+
     for i in range(args.warmup):
-        step(i)
+        submit(i).wait()
+    # N > 1: the boards of a box settle at different power-capped clocks and a sharded level ends with its slowest
+    # rank, so the reference batches are re-split once, in proportion to each rank's warm rate (untimed, part of warm-up)
+    rates = None
+    if world > 1 and not args.no_rebalance:
+        rates = ev.rebalance(images, masks, ev.local_rate(spec_of(0), steps=2))
+        for i in range(2):
+            submit(i).wait()
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -271,14 +437,25 @@ def run_gpu(args, rank, world, local_rank):
     l0 = eng.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(args.steps):
-        step(args.warmup + i)
+    pend = [submit(args.warmup + i) for i in range(args.steps)]
+    for p in pend:                     # every level's result is complete on the compute stream before the clock stops
+        p.wait()
     e1.record()
     barrier()
-    ms = max_over_ranks(e0.elapsed_time(e1))
+    my_ms = e0.elapsed_time(e1)
+    ms = max_over_ranks(my_ms)
+    per_rank_ms = gather(my_ms)
     launches = eng.launch_count - l0
     clocks = sampler.stop() if rank == 0 else None
     value = N_IMAGES * args.steps / (ms * 1e-3)
+
+    # ---- checksum of one fixed deterministic level after the all-reduce: the same at every N iff N ranks reproduce
+    # the single-GPU counts (sharding, micro-batch split and re-balancing must not change a single count)
+    cm_sha = None
+    if not LARGE and not CLIP:
+        cm_fixed, _ = ev.run_level(make_spec("contrast_increase", 1.1, H * W))
+        cm_sha = hashlib.sha256(cm_fixed.cpu().numpy().tobytes()).hexdigest()
+        assert int(cm_fixed.sum()) == N_IMAGES * H * W
 
     # ---- end to end through the public API: pinned host buffers -> H2D -> level -> D2H of the counts
     k_e2e = max(1, args.steps)   # the first upload has nothing to overlap with (pipeline fill): amortised over K steps
@@ -298,6 +475,21 @@ def run_gpu(args, rank, world, local_rank):
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e_value = N_IMAGES * k_e2e / e2e_s
+    h2d_all = sum(int(v) for v in gather(float(h2d)))
+
+    # ---- the collective alone (N > 1): mean duration of the int64 [n_batches,C,C] all-reduce, back to back, CUDA events
+    allreduce_us = None
+    if world > 1:
+        for _ in range(3):
+            dist.all_reduce(ev.cm)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a0.record()
+        for _ in range(20):
+            dist.all_reduce(ev.cm)
+        a1.record()
+        a1.synchronize()
+        allreduce_us = max_over_ranks(a0.elapsed_time(a1) / 20 * 1e3)
 
     # ---- roofline of the dominant kernel (tcgen05 implicit-GEMM conv / ConvT), per-launch CUDA events
     eng.profile_begin()
@@ -310,43 +502,58 @@ def run_gpu(args, rank, world, local_rank):
                 "achieved": gemm_tflops, "peak": peak, "unit": "TFLOP/s", "frac": gemm_tflops / peak,
                 "peak_source": pk_src + ", sustained figure (kernel timed inside a long step)",
                 "frac_of_burst_peak": gemm_tflops / pk["bf16_tflops"], "traffic": None, "traffic_unit": "bytes/launch",
-                "gemm_share_of_step": gemm_ms / 2 / (ms / args.steps),
+                "gemm_share_of_step": gemm_ms / 2 / (my_ms / args.steps),
                 "flops_per_launch": GEMM_GFLOP_PER_IMAGE * 1e9 * ev.n_local * 2 / max(gemm_launches, 1),
                 "avg_launch_ms": gemm_ms / max(gemm_launches, 1)}
-    # DRAM bytes per launch from the committed ncu --set full capture (same micro-batch, headline workload only)
+    # DRAM bytes per launch: ncu --set full capture of the same build (profiles/), headline workload only — ncu cannot
+    # run inside a timed bench, so this is the capture's per-image figure x the images per launch of THIS run
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")) as f:
+        tr_path = next(p for p in (os.path.join(ROOT, "profiles", f) for f in ("r02_ncu_traffic.json", "r01_ncu_traffic.json"))
+                       if os.path.exists(p))
+        with open(tr_path) as f:
             tr = json.load(f)
         if not LARGE and not CLIP:
-            per_launch_images = ev.n_local * 2 / max(gemm_launches, 1) * 20   # images per micro-batch in this run
-            roofline["traffic"] = tr["dram_bytes_per_image"] * per_launch_images / 20
-            roofline["traffic_source"] = (f"profiles/r01_ncu_traffic.json: dram read+write per image from an ncu --set full "
+            n_gemm = tr.get("gemm_launches_per_microbatch", 20)
+            per_launch_images = ev.n_local * 2 / max(gemm_launches, 1) * n_gemm   # images per micro-batch in this run
+            roofline["traffic"] = tr["dram_bytes_per_image"] * per_launch_images / n_gemm
+            roofline["traffic_source"] = (f"{os.path.relpath(tr_path, ROOT)}: dram read+write per image from an ncu --set full "
                                           f"capture at micro-batch {tr['microbatch']}, x images per launch here, mean over "
-                                          f"the 20 GEMM launches of a micro-batch")
+                                          f"the {n_gemm} GEMM launches of a micro-batch")
             # every layer's input read once + output written once, bf16 blocked tensors, per image
-            roofline["traffic_algorithmic"] = 89.2e6 * per_launch_images / 20   # every GEMM layer's input once + output once (the stem's two readers read the 16-channel packed image)
+            roofline["traffic_algorithmic"] = tr.get("algorithmic_bytes_per_image", 89.2e6) * per_launch_images / n_gemm
     except Exception:
         pass
     if args.layers and rank == 0:
         for k, cin, nt, ks, n, t in rows:
-            fl = 2.0 * ks * ks * cin * nt
             print(f"# layer {k:28s} cin {cin:4d} n {nt:4d} k{ks} launches {n:4d} ms {t:8.3f}", file=sys.stderr)
+
+    extra = None
+    if world == 1 and not args.no_extra and not LARGE and not CLIP:
+        del ev
+        extra = extra_measurements(dev)
 
     if rank != 0:
         return
     line = base_line(args, world)
     line.update({"value": value, "ms_per_step": ms / args.steps, "dtype": "bf16",
-                 "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
+                 "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h * world,
                          "steps": k_e2e},
                  "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
-                 "whole_net_tflops": value * GFLOP_PER_IMAGE / 1e3, "microbatch": eng.max_microbatch})
+                 "whole_net_tflops": value * GFLOP_PER_IMAGE / 1e3, "microbatch": eng.max_microbatch,
+                 "cm_sha256": cm_sha})
+    if world > 1:
+        line["multi_gpu"] = {"per_rank_ms_per_step": [v / args.steps for v in per_rank_ms], "allreduce_us": allreduce_us,
+                             "warm_rates_images_per_s": rates, "rebalanced": rates is not None,
+                             "collective": "one async int64 all-reduce of [n_batches,3,3] per level on NCCL's stream"}
+    if extra is not None:
+        line["extra"] = extra
     if world == 1 and not args.no_cpu and not CLIP:  # (no CPU leg for the secondary ClipUnet workload)
         lv = [("contrast_increase", 1.1), ("gaussian_blur", 5), ("gaussian_noise", 10), ("occlusion", 25)]
         n_cpu = 8 if LARGE else 64
-        v, cores, dt = cpu_time_sample(sd_cpu, images[:n_cpu], masks[:n_cpu], lv, n_cpu, 4)
-        line["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
+        v, cores, dt, kind, what = cpu_time_sample(sd_cpu, images[:n_cpu], masks[:n_cpu], lv, n_cpu, 4)
+        line["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": kind,
                                 "sample": f"4 levels (contrast 1.1, blur 5, noise 10, occlusion 25) x {n_cpu} images "
-                                          f"through the oracle port, {dt:.1f} s"}
+                                          f"through {what}, {dt:.1f} s"}
     else:
         line["cpu_baseline"] = None
     print(json.dumps(line), flush=True)
@@ -361,6 +568,8 @@ def main():
     ap.add_argument("--microbatch", type=int, default=None)
     ap.add_argument("--layers", action="store_true", help="print the per-layer GEMM times to stderr")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the short secondary measurements (extra)")
+    ap.add_argument("--no-rebalance", action="store_true", help="N > 1: keep the equal split of reference batches")
     ap.add_argument("--workload", default="unet256", choices=["unet256", "large512", "clipunet256"],
                     help="unet256 = the headline (BASELINE.json configs[1]); large512 = configs[2]; clipunet256: secondary")
     args = ap.parse_args()

@@ -11,6 +11,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -103,6 +104,9 @@ struct ub_ctx {
   std::vector<ProfRec> prof;
   std::vector<cudaEvent_t> event_pool;
   std::vector<void*> owned;  // device allocations freed in ub_destroy
+  // kernel instantiations whose dynamic shared-memory opt-in has been made ON THIS CONTEXT'S DEVICE (the attribute
+  // is per device and per function, so a second context on another GPU of the same process makes its own)
+  std::set<const void*> smem_opt_in;
   bool has_clip() const { return arch == UB_ARCH_CLIP_UNET || arch == UB_ARCH_CLIP_UNET_PROMPT; }
 };
 
@@ -372,6 +376,9 @@ int pack_all(ub_ctx* ctx) {
     if ((rc = pack_conv(ctx, std::string(k) + ".conv.conv.0", std::string(k) + ".conv.conv.1"))) return rc;
     if ((rc = pack_conv(ctx, std::string(k) + ".conv.conv.3", std::string(k) + ".conv.conv.4"))) return rc;
   }
+  // the uploads above are cudaMemcpy calls on the legacy default stream; the kernels run on the caller's (possibly
+  // non-blocking) stream, so make the packed weights globally visible before the first launch can be issued
+  UB_CUDA(ctx, cudaDeviceSynchronize());
   ctx->weights_ready = true;
   return UB_OK;
 }
@@ -493,11 +500,11 @@ bool choose_pipeline(ConvParams* cp, int grid, bool allow_ws, int* smem_bytes) {
 
 template <int N, int BK, int KS, bool WS, int TW, bool CG2 = false>
 int launch_kernel(ub_ctx* ctx, const ConvParams& cp, int grid, int smem, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  const void* fn = reinterpret_cast<const void*>(&ub::conv_tc_kernel<N, BK, KS, WS, TW, CG2>);
+  if (!ctx->smem_opt_in.count(fn)) {
     UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_tc_kernel<N, BK, KS, WS, TW, CG2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       ub::kSmemLimit));
-    attr_set = true;
+    ctx->smem_opt_in.insert(fn);
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -642,7 +649,7 @@ int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cuda
 // ------------------------------------------------------------------ execution plan for one resolution
 int skip_width(int level) { return level == 0 ? 32 : (32 << level); }
 
-int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
+int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out) {
   auto key = std::make_pair(H, W);
   auto it = ctx->plans.find(key);
   if (it != ctx->plans.end()) { *out = it->second.get(); return UB_OK; }
@@ -696,7 +703,9 @@ int build_plan(ub_ctx* ctx, int H, int W, Plan** out) {
   int rc;
   if ((rc = dev_alloc(ctx, &pl->arena, total))) return rc;
   pl->arena_bytes = total;
-  UB_CUDA(ctx, cudaMemset(pl->arena, 0, total));
+  // zeroed ON THE CALLER'S STREAM: the kernels that rely on the zero planes (plane 1 of the packed image, the prompt
+  // stem's padding) are launched on `st`, which need not synchronise with the legacy default stream
+  UB_CUDA(ctx, cudaMemsetAsync(pl->arena, 0, total, st));
   auto bufp = [&](size_t idx) { return reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(pl->arena) + offs[idx]); };
   pl->pert_f32 = reinterpret_cast<float*>(bufp(i_pert));
   pl->blur_a = bufp(i_bla);
@@ -1117,7 +1126,7 @@ int eval_impl(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_fo
   if (dice_sums && !targets) return fail(ctx, UB_ERR_INVALID, "dice_sums needs targets");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   Plan* pl;
-  if ((rc = build_plan(ctx, h, w, &pl))) return rc;
+  if ((rc = build_plan(ctx, h, w, st, &pl))) return rc;
   ub::PerturbDev P;
   if ((rc = to_dev_perturb(ctx, p, aux, &P))) return rc;
   const int C = ctx->n_classes;
@@ -1127,11 +1136,41 @@ int eval_impl(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_fo
   const size_t hw = static_cast<size_t>(h) * w;
   const size_t img_stride = image_format == UB_IMG_U8_NHWC ? hw * 3 : hw * 3 * 4;
   const size_t tgt_stride = target_format == UB_TGT_U8 ? hw : hw * 8;
-  // balanced micro-batches: ceil(n / max_mb) launches of (almost) equal size instead of a short last one
-  const int mb_count = (n + ctx->max_mb - 1) / ctx->max_mb;
-  const int mb_size = (n + mb_count - 1) / mb_count;
-  for (int i0 = 0; i0 < n; i0 += mb_size) {
-    const int nb = (n - i0) < mb_size ? (n - i0) : mb_size;
+  // Micro-batches.  A layer's launch is a whole number of waves only when (images x tiles per image) is a multiple of the
+  // SM count; the coarsest level has the fewest tiles per image (16 at 256x256: 2 x 4 tiles x 2 n-tiles), so its quantum
+  // q = SMs / gcd(SMs, tiles) = 37 images decides.  Sizes are multiples of q wherever the image count allows and the
+  // remainder rides on one micro-batch (a rank's share of a sharded set — 460 images on 8 GPUs — is 111+111+111+127
+  // instead of 4 x 115: the 32x32 layers then run 12 + 12 + 12 + 14 full waves instead of 4 x 12.4 -> 13).
+  std::vector<int> mb_sizes;
+  {
+    const int lv = ctx->n_enc;
+    const int tiles = (((h >> lv) + 15) / 16) * (((w >> lv) + 7) / 8) * ((64 << lv) / 256 > 0 ? (64 << lv) / 256 : 1);
+    int a = ctx->num_sms, b = tiles;
+    while (b) { const int t = a % b; a = b; b = t; }
+    const int q = ctx->num_sms / a;
+    const int mb_count = (n + ctx->max_mb - 1) / ctx->max_mb;
+    const int base = q > 1 && q <= ctx->max_mb ? (n / mb_count) / q * q : 0;
+    if (base == 0) {  // balanced: ceil(n / max_mb) launches of (almost) equal size instead of a short last one
+      const int sz = (n + mb_count - 1) / mb_count;
+      for (int i0 = 0; i0 < n; i0 += sz) mb_sizes.push_back((n - i0) < sz ? (n - i0) : sz);
+    } else {
+      mb_sizes.assign(mb_count, base);
+      int r = n - base * mb_count;
+      for (bool grew = true; grew && r >= q;) {
+        grew = false;
+        for (int i = 0; i < mb_count && r >= q; ++i)
+          if (mb_sizes[i] + q <= ctx->max_mb) { mb_sizes[i] += q; r -= q; grew = true; }
+      }
+      for (int i = mb_count - 1; i >= 0 && r > 0; --i) {
+        const int add = (ctx->max_mb - mb_sizes[i]) < r ? (ctx->max_mb - mb_sizes[i]) : r;
+        mb_sizes[i] += add; r -= add;
+      }
+      if (r > 0) mb_sizes.push_back(r);
+    }
+  }
+  int i0 = 0;
+  for (size_t mbi = 0; mbi < mb_sizes.size(); i0 += mb_sizes[mbi], ++mbi) {
+    const int nb = mb_sizes[mbi];
     ub::PerturbDev Pm = P;
     if (aux) {
       size_t per_img = 0;
@@ -1211,13 +1250,16 @@ int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int 
   if ((rc = to_dev_perturb(ctx, p, aux, &P))) return rc;
   const size_t hw = static_cast<size_t>(h) * w;
   if (P.kind == UB_P_U8_BLUR || P.kind == UB_P_F_BLUR) {
-    // needs ping-pong planes: allocate per call on the stream (not on the evaluation hot path)
+    Plan tmp;
+    tmp.H = h; tmp.W = w;
+    if (P.iparam <= ub::kBlurMaxPasses && !ctx->no_blur_fuse)  // every pass in shared memory: no planes needed
+      return run_blur(ctx, &tmp, P, images, image_format, n, out_nchw, st);
+    // pass-per-launch path: ping-pong planes, allocated per call on the stream (not on the evaluation hot path)
     void *a = nullptr, *b = nullptr;
     const size_t bytes = static_cast<size_t>(n) * 3 * hw * 4;
     UB_CUDA(ctx, cudaMallocAsync(&a, bytes, st));
     UB_CUDA(ctx, cudaMallocAsync(&b, bytes, st));
-    Plan tmp;
-    tmp.H = h; tmp.W = w; tmp.blur_a = a; tmp.blur_b = b;
+    tmp.blur_a = a; tmp.blur_b = b;
     rc = run_blur(ctx, &tmp, P, images, image_format, n, out_nchw, st);
     cudaFreeAsync(a, st);
     cudaFreeAsync(b, st);

@@ -281,6 +281,12 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
+  // Programmatic dependent launch, armed: once every CTA of this grid has got here (or exited) the next kernel of the
+  // stream may be scheduled, so its CTAs take over an SM the moment one of ours leaves it and run their prologue
+  // (barrier init, TMEM allocation, resident-weight loads) under our tail.  Safe because every consumer of another
+  // kernel's output in this file sits behind griddepcontrol.wait (warp 0), which waits for the WHOLE prior grid and its
+  // memory flush; epilogue stores only follow MMAs that follow those loads.  (UB_DBG bit 16 disarms it for A/B timing.)
+  if (!(p.dbg & 16)) pdl_launch_dependents();
 
   if (warp == 0) {
     // ================= TMA producer (whole warp runs the loop; one elected lane issues) =================

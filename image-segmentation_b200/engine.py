@@ -124,10 +124,16 @@ class Engine:
         self.h = h
         self.loaded = False
 
-    def close(self):
+    def close(self, why: str = "this engine has been closed"):
         if getattr(self, "h", None):
             self.lib.ub_destroy(self.h)
             self.h = None
+            self._closed_why = why
+
+    def _handle(self):
+        if not getattr(self, "h", None):
+            raise RuntimeError(getattr(self, "_closed_why", "this engine has been closed"))
+        return self.h
 
     def __del__(self):
         try:
@@ -149,7 +155,7 @@ class Engine:
         shapes = (ctypes.POINTER(ctypes.c_int64) * n)(*[ctypes.cast(a, ctypes.POINTER(ctypes.c_int64))
                                                         for a in shape_arrays])
         ndims = (ctypes.c_int * n)(*[v.dim() for _, v in items])
-        self._check(self.lib.ub_load_weights(self.h, n, names, ptrs, shapes, ndims), "ub_load_weights")
+        self._check(self.lib.ub_load_weights(self._handle(), n, names, ptrs, shapes, ndims), "ub_load_weights")
         self.loaded = True
 
     def forward_prompt(self, x: torch.Tensor, prompt_heatmap: torch.Tensor, clip_feats: torch.Tensor) -> torch.Tensor:
@@ -165,7 +171,7 @@ class Engine:
         if tuple(cf.shape) != (n, 512):
             raise ValueError(f"clip_feats must be [{n}, 512], got {tuple(cf.shape)}")
         out = torch.empty((n, self.n_classes, h, w), device=self.device, dtype=torch.float32)
-        self._check(self.lib.ub_forward_prompt(self.h, _ptr(x), _ptr(hm), _ptr(cf), _ptr(out), n, h, w,
+        self._check(self.lib.ub_forward_prompt(self._handle(), _ptr(x), _ptr(hm), _ptr(cf), _ptr(out), n, h, w,
                                                _stream(self.device)), "ub_forward_prompt")
         return out
 
@@ -175,7 +181,7 @@ class Engine:
         if self.arch == "clip":
             return self.eval_batches(x, None, None, 1, want_logits=True, clip_feats=clip_feats)["logits"]
         out = torch.empty((n, self.n_classes, h, w), device=self.device, dtype=torch.float32)
-        self._check(self.lib.ub_forward(self.h, _ptr(x), _ptr(out), n, h, w, _stream(self.device)), "ub_forward")
+        self._check(self.lib.ub_forward(self._handle(), _ptr(x), _ptr(out), n, h, w, _stream(self.device)), "ub_forward")
         return out
 
     def eval_batches(self, images: torch.Tensor, targets: Optional[torch.Tensor], perturbation: Optional[Perturbation],
@@ -225,7 +231,7 @@ class Engine:
                 _ptr(aux), _ptr(clip_feats), n, h, w, int(ref_batch), _ptr(cm), _ptr(dice), _ptr(pred), _ptr(logits),
                 _ptr(pert), _stream(self.device)), "ub_eval_batches_clip")
             return dict(cm=cm, dice=dice, pred=pred, logits=logits, perturbed=pert)
-        self._check(self.lib.ub_eval_batches(self.h, ctypes.byref(p.struct) if p is not None else None, _ptr(images),
+        self._check(self.lib.ub_eval_batches(self._handle(), ctypes.byref(p.struct) if p is not None else None, _ptr(images),
                                              fmt, _ptr(targets), tfmt, _ptr(aux), n, h, w, int(ref_batch), _ptr(cm),
                                              _ptr(dice), _ptr(pred), _ptr(logits), _ptr(pert),
                                              _stream(self.device)), "ub_eval_batches")
@@ -241,7 +247,7 @@ class Engine:
             n, _, h, w = images.shape
         out = torch.empty((n, 3, h, w), device=self.device, dtype=torch.float32)
         aux = perturbation.aux.to(self.device).contiguous() if perturbation.aux is not None else None
-        self._check(self.lib.ub_perturb_images(self.h, ctypes.byref(perturbation.struct), _ptr(images), fmt, _ptr(aux),
+        self._check(self.lib.ub_perturb_images(self._handle(), ctypes.byref(perturbation.struct), _ptr(images), fmt, _ptr(aux),
                                                n, h, w, _ptr(out), _stream(self.device)), "ub_perturb_images")
         return out
 
@@ -255,7 +261,7 @@ class Engine:
         nb = math.ceil(n / ref_batch)
         cm = torch.empty((nb, C, C), device=self.device, dtype=torch.int64)
         dice = torch.empty((nb, C, 3), device=self.device, dtype=torch.float64) if want_dice else None
-        self._check(self.lib.ub_metrics(self.h, _ptr(logits), _ptr(targets), tfmt, n, C, h, w, int(ref_batch), _ptr(cm),
+        self._check(self.lib.ub_metrics(self._handle(), _ptr(logits), _ptr(targets), tfmt, n, C, h, w, int(ref_batch), _ptr(cm),
                                         _ptr(dice), _stream(self.device)), "ub_metrics")
         return cm, dice
 
@@ -268,7 +274,7 @@ class Engine:
         out = torch.empty_like(raw)
         n = raw.shape[0]
         px = raw[0].numel() if n else 1
-        self._check(self.lib.ub_decode_masks(self.h, _ptr(raw), _ptr(out), n, px, _stream(self.device)),
+        self._check(self.lib.ub_decode_masks(self._handle(), _ptr(raw), _ptr(out), n, px, _stream(self.device)),
                     "ub_decode_masks")
         return out
 
@@ -284,7 +290,7 @@ class Engine:
         if masks is not None:
             masks = masks.to(self.device, torch.int64).contiguous()
             mask_u8 = torch.empty((n, h, w), device=self.device, dtype=torch.uint8)
-        self._check(self.lib.ub_pack_dataset(self.h, _ptr(images), _ptr(masks), n, h, w, _ptr(img_u8), _ptr(mask_u8),
+        self._check(self.lib.ub_pack_dataset(self._handle(), _ptr(images), _ptr(masks), n, h, w, _ptr(img_u8), _ptr(mask_u8),
                                              _stream(self.device)), "ub_pack_dataset")
         return img_u8, mask_u8
 
@@ -306,7 +312,7 @@ class Engine:
         oh, ow = (h // 2, w // 2) if pool else (h, w)
         out = torch.zeros((n, cout // 8, oh, ow, 8), device=self.device, dtype=torch.bfloat16)
         xb = self._to_blocked(x_nhwc_bf16)
-        self._check(self.lib.ub_debug_conv3x3(self.h, key.encode(), _ptr(xb), _ptr(out), n, h, w,
+        self._check(self.lib.ub_debug_conv3x3(self._handle(), key.encode(), _ptr(xb), _ptr(out), n, h, w,
                                               int(pool), _stream(self.device)), "ub_debug_conv3x3")
         return self._from_blocked(out)
 
@@ -315,7 +321,7 @@ class Engine:
         cout = self._layer_cout(key)
         out = torch.zeros((n, cout // 8, 2 * h, 2 * w, 8), device=self.device, dtype=torch.bfloat16)
         xb = self._to_blocked(x_nhwc_bf16)
-        self._check(self.lib.ub_debug_convt2x2(self.h, key.encode(), _ptr(xb), _ptr(out), n, h, w,
+        self._check(self.lib.ub_debug_convt2x2(self._handle(), key.encode(), _ptr(xb), _ptr(out), n, h, w,
                                                _stream(self.device)), "ub_debug_convt2x2")
         return self._from_blocked(out)
 
@@ -324,7 +330,7 @@ class Engine:
         n, h, w, c = x_nhwc_bf16.shape
         out = torch.zeros((n, c // 8, ho, wo, 8), device=self.device, dtype=torch.bfloat16)
         xb = self._to_blocked(x_nhwc_bf16.to(self.device))
-        self._check(self.lib.ub_debug_resample(self.h, _ptr(xb), _ptr(out), n, c, h, w, ho, wo, _stream(self.device)),
+        self._check(self.lib.ub_debug_resample(self._handle(), _ptr(xb), _ptr(out), n, c, h, w, ho, wo, _stream(self.device)),
                     "ub_debug_resample")
         return self._from_blocked(out)
 
@@ -335,13 +341,13 @@ class Engine:
         self._couts = dict(couts)
 
     def profile_begin(self):
-        self._check(self.lib.ub_profile_begin(self.h), "ub_profile_begin")
+        self._check(self.lib.ub_profile_begin(self._handle()), "ub_profile_begin")
 
     def profile_end(self):
         """-> (gemm_ms_total, gemm_launches, [(key, cin, n_total, ksize, launches, ms), ...])"""
         ms, cnt = ctypes.c_double(), ctypes.c_int64()
         buf = ctypes.create_string_buffer(16384)
-        self._check(self.lib.ub_profile_end(self.h, ctypes.byref(ms), ctypes.byref(cnt), buf, len(buf)), "ub_profile_end")
+        self._check(self.lib.ub_profile_end(self._handle(), ctypes.byref(ms), ctypes.byref(cnt), buf, len(buf)), "ub_profile_end")
         rows = []
         for line in buf.value.decode().splitlines():
             k, cin, nt, ks, n, t = line.split()
@@ -350,4 +356,4 @@ class Engine:
 
     @property
     def launch_count(self) -> int:
-        return int(self.lib.ub_launch_count(self.h))
+        return int(self.lib.ub_launch_count(self._handle()))

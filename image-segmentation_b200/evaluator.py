@@ -21,11 +21,42 @@ from . import metrics
 from .engine import Perturbation
 
 
-def batch_range(n_batches: int, rank: int, world: int):
-    """Contiguous, balanced split of reference batches: the first (n_batches % world) ranks get one more."""
-    base, extra = divmod(n_batches, world)
-    start = rank * base + min(rank, extra)
-    return start, start + base + (1 if rank < extra else 0)
+def batch_range(n_batches: int, rank: int, world: int, weights=None):
+    """Contiguous split of reference batches.  Default: balanced, the first (n_batches % world) ranks get one more.
+    `weights` (one positive number per rank, e.g. images/s measured during warm-up): shares proportional to them —
+    the boards of one box settle at different power-capped clocks, and a level ends when the slowest rank does."""
+    if weights is None:
+        base, extra = divmod(n_batches, world)
+        start = rank * base + min(rank, extra)
+        return start, start + base + (1 if rank < extra else 0)
+    w = [float(x) for x in weights]
+    if len(w) != world or min(w) <= 0:
+        raise ValueError("weights: one positive number per rank")
+    total = sum(w)
+    # largest-remainder rounding of the cumulative shares: deterministic, identical on every rank
+    edges = [0]
+    acc = 0.0
+    for r in range(world):
+        acc += w[r]
+        edges.append(int(round(n_batches * acc / total)))
+    edges[-1] = n_batches
+    for r in range(1, world + 1):
+        edges[r] = max(edges[r], edges[r - 1])
+    return edges[rank], edges[rank + 1]
+
+
+class PendingLevel:
+    """Result of `RobustnessEvaluator.submit_level`: the counts of one level, whose all-reduce may still be in flight
+    on NCCL's stream.  `wait()` orders the CURRENT stream after it and returns (cm, dice_sums or None)."""
+
+    def __init__(self, cm, dice, works):
+        self.cm, self.dice, self._works = cm, dice, works
+
+    def wait(self):
+        for w in self._works:
+            w.wait()
+        self._works = []
+        return self.cm, self.dice
 
 
 class RobustnessEvaluator:
@@ -43,15 +74,58 @@ class RobustnessEvaluator:
         self.ref_batch = int(ref_batch)
         self.n_total = images_u8.shape[0]
         self.n_batches = math.ceil(self.n_total / self.ref_batch)
-        self.b0, self.b1 = batch_range(self.n_batches, rank, world_size)
+        self.C = model._n_classes
+        self._set_range(images_u8, masks_u8, None)
+        # Precondition of the fused counts (include/unet_b200.h): every mask value is a class id.  The reference's IoU
+        # (models/losses.py:52-60) counts a prediction on a pixel with a foreign label towards the union; the [C,C]
+        # confusion tensor has no cell for that, so such a dataset is refused here instead of being scored differently.
+        if self.masks.numel() and int(self.masks.max()) >= self.C:
+            raise ValueError(f"mask values must be class ids in [0, {self.C}); found {int(self.masks.max())}")
+        self.engine = model.engine(self.device, max_microbatch)
+        # result buffers: a small ring, so that a level's all-reduce (NCCL's own stream) can still be in flight while
+        # the next levels compute into other buffers (submit_level); run_level uses slot 0 synchronously
+        self._ring = [(torch.zeros((self.n_batches, self.C, self.C), device=self.device, dtype=torch.int64),
+                       torch.zeros((self.n_batches, self.C, 3), device=self.device, dtype=torch.float64))
+                      for _ in range(3)]
+        self._ring_pending = [None] * len(self._ring)
+        self._ring_next = 0
+        self.cm, self.dice = self._ring[0]
+
+    def _set_range(self, images_u8, masks_u8, weights):
+        self.b0, self.b1 = batch_range(self.n_batches, self.rank, self.world, weights)
         i0, i1 = self.b0 * self.ref_batch, min(self.b1 * self.ref_batch, self.n_total)
         self.i0, self.i1 = i0, i1
         self.images = images_u8[i0:i1].to(self.device, non_blocking=True).contiguous()
         self.masks = masks_u8[i0:i1].to(self.device, non_blocking=True).contiguous()
-        self.C = model._n_classes
-        self.engine = model.engine(self.device, max_microbatch)
-        self.cm = torch.zeros((self.n_batches, self.C, self.C), device=self.device, dtype=torch.int64)
-        self.dice = torch.zeros((self.n_batches, self.C, 3), device=self.device, dtype=torch.float64)
+        for attr in ("_copy_stream", "_back", "_copy_done", "_front_free"):  # upload_async's buffers have the old size
+            if hasattr(self, attr):
+                delattr(self, attr)
+
+    def rebalance(self, images_u8, masks_u8, rate: float):
+        """Re-shard the reference batches in proportion to every rank's measured `rate` (images/s of its own slice,
+        e.g. from `local_rate`) and upload the new slice.  Collective: every rank must call it."""
+        if self.world == 1:
+            return [float(rate)]
+        t = torch.zeros((self.world,), device=self.device, dtype=torch.float64)
+        t[self.rank] = float(rate)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        rates = [float(v) for v in t.cpu()]
+        torch.cuda.synchronize(self.device)
+        self._set_range(images_u8, masks_u8, rates)
+        return rates
+
+    def local_rate(self, perturbation: Optional[Perturbation], steps: int = 3) -> float:
+        """Images/s of THIS rank on its current slice (no collective), by CUDA events: the input of `rebalance`."""
+        if self.n_local == 0:
+            return 1.0
+        self.run_level(perturbation, reduce=False)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            self.run_level(perturbation, reduce=False)
+        e1.record()
+        e1.synchronize()
+        return self.n_local * steps / (e0.elapsed_time(e1) * 1e-3)
 
     @property
     def n_local(self) -> int:
@@ -123,24 +197,56 @@ class RobustnessEvaluator:
                                      out_cm=out_cm[b0:b1], out_dice=out_dice[b0:b1] if out_dice is not None else None,
                                      clip_feats=feats)
 
+    def _fill(self, cm, dice, perturbation, want_dice):
+        """This rank's rows of one level into (cm, dice); the other ranks' rows are left zero for the sum."""
+        if self.world > 1:  # (one rank: the callee zeroes exactly the rows it fills — no extra memset launches)
+            cm.zero_()
+            if want_dice:
+                dice.zero_()
+        if self.n_local > 0:
+            self._eval(self.images, self.masks, self.local_aux(perturbation), want_dice, cm[self.b0:self.b1],
+                       dice[self.b0:self.b1] if want_dice else None)
+
     def run_level(self, perturbation: Optional[Perturbation], want_dice: bool = False, reduce: bool = True):
         """-> (cm int64 [n_batches,C,C], dice_sums f64 [n_batches,C,3] or None), complete on every rank."""
-        self.cm.zero_()
-        if want_dice:
-            self.dice.zero_()
-        if self.n_local > 0:
-            self._eval(self.images, self.masks, self.local_aux(perturbation), want_dice, self.cm[self.b0:self.b1],
-                       self.dice[self.b0:self.b1] if want_dice else None)
+        if self._ring_pending[0] is not None:
+            self._ring_pending[0].wait()
+            self._ring_pending[0] = None
+        self._fill(self.cm, self.dice, perturbation, want_dice)
         if reduce and self.world > 1:
             dist.all_reduce(self.cm, op=dist.ReduceOp.SUM)
             if want_dice:
                 dist.all_reduce(self.dice, op=dist.ReduceOp.SUM)
         return self.cm, (self.dice if want_dice else None)
 
+    def submit_level(self, perturbation: Optional[Perturbation], want_dice: bool = False) -> PendingLevel:
+        """Like run_level, but the all-reduce is issued with async_op=True: it runs on NCCL's stream (ordered after
+        this level's kernels) and the compute stream goes straight on to the next level, so a rank never idles at a
+        level boundary waiting for a slower board.  The result is consumed through `PendingLevel.wait()` — e.g. when
+        the level's CSV row is written.  At most len(ring) levels are in flight; an older one is waited for when its
+        buffer comes round again."""
+        slot = self._ring_next
+        self._ring_next = (slot + 1) % len(self._ring)
+        if self._ring_pending[slot] is not None:
+            self._ring_pending[slot].wait()
+        cm, dice = self._ring[slot]
+        self._fill(cm, dice, perturbation, want_dice)
+        works = []
+        if self.world > 1:
+            works.append(dist.all_reduce(cm, op=dist.ReduceOp.SUM, async_op=True))
+            if want_dice:
+                works.append(dist.all_reduce(dice, op=dist.ReduceOp.SUM, async_op=True))
+        pending = PendingLevel(cm, dice if want_dice else None, works)
+        self._ring_pending[slot] = pending
+        return pending
+
     def run_level_per_batch(self, spec_for_batch, want_dice: bool = False, chunk_batches: int = 16):
         """Like run_level, but the perturbation's random numbers are drawn batch by batch in loader
         order through `spec_for_batch(shape_probe[b,3,H,W]) -> Perturbation` (what the reference's
         nn.Module augmentations do inside the loop, model_wrappers.py:450), `chunk_batches` at a time."""
+        if self._ring_pending[0] is not None:
+            self._ring_pending[0].wait()
+            self._ring_pending[0] = None
         self.cm.zero_()
         if want_dice:
             self.dice.zero_()

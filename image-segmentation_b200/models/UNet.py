@@ -21,8 +21,7 @@ class _B200Net(nn.Module):
     def _finish_init(self, out_channels, activation):
         self.activation = activation
         self._n_classes = out_channels
-        self._engine = None
-        self._engine_key = None
+        self._engines = {}  # (device, max_microbatch) -> (weights key, Engine)
 
     def _weights_key(self):
         return tuple((p.data_ptr(), p._version) for p in list(self.parameters()) + list(self.buffers()))
@@ -32,17 +31,24 @@ class _B200Net(nn.Module):
         dev = torch.device(device) if device is not None else next(self.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("unet-b200 has no CPU path: move the model and inputs to a CUDA (sm_100a) device")
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
         mb = max_microbatch or runtime.default_microbatch()
-        key = (dev, mb, self._weights_key())
-        if self._engine is None or self._engine_key != key:
-            if self._engine is not None:
-                self._engine.close()
-            self._engine = runtime.new_engine(dev, self._arch, 3, self._n_classes, mb)
-            self._engine.load_state_dict({self._flat_name(k): v for k, v in self.state_dict().items()
-                                          if not k.startswith(self._host_side_prefixes)})
-            self._engine.set_layer_couts(self.layer_couts())
-            self._engine_key = key
-        return self._engine
+        wkey = self._weights_key()
+        slot = self._engines.get((dev, mb))
+        # one context per (device, micro-batch): asking for another micro-batch (e.g. a plain model(x) beside a
+        # RobustnessEvaluator that holds its own engine) never destroys a context somebody else is using; only a
+        # change of the WEIGHTS retires a context (its holders then get Engine's "rebuilt" error, not a stale result)
+        if slot is None or slot[0] != wkey:
+            if slot is not None:
+                slot[1].close("the model's weights changed and its engine was rebuilt: call model.engine() again")
+            eng = runtime.new_engine(dev, self._arch, 3, self._n_classes, mb)
+            eng.load_state_dict({self._flat_name(k): v for k, v in self.state_dict().items()
+                                 if not k.startswith(self._host_side_prefixes)})
+            eng.set_layer_couts(self.layer_couts())
+            self._engines[(dev, mb)] = (wkey, eng)
+            slot = self._engines[(dev, mb)]
+        return slot[1]
 
     @staticmethod
     def _flat_name(key: str) -> str:

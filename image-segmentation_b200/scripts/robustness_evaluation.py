@@ -82,17 +82,29 @@ def run_sweep(model, images_u8, masks_u8, results_file="results/robustness_score
         f = open(results_file, "w", newline="")
         writer = csv.writer(f)
         writer.writerow(["perturbation_type", "param_value", "mean_dice"])
+
+    def consume(item):
+        # the level's all-reduce (issued async on NCCL's stream) is waited for only here, when its CSV row is written
+        p_name, level, pending = item
+        _, dice = pending.wait()
+        mean_dice = RobustnessEvaluator.script_score(dice)
+        rows.append((p_name, level, mean_dice))
+        if rank0:
+            writer.writerow([p_name, level, f"{mean_dice:.4f}"])
+            if not quiet:
+                print(f"{p_name} param={level}, Dice={mean_dice:.4f}")
+
     try:
+        in_flight = None   # one level computes while the previous one's row is formatted: the GPU never waits for the host
         for li, (p_name, levels) in enumerate((perturbations or PERTURBATIONS).items()):
             for lj, level in enumerate(levels):
                 spec = parity_spec(p_name, level, n, h, w) if parity_rng else make_spec(p_name, level, h * w, seed=1000 * li + lj)
-                _, dice = ev.run_level(spec, want_dice=True)
-                mean_dice = RobustnessEvaluator.script_score(dice)
-                rows.append((p_name, level, mean_dice))
-                if rank0:
-                    writer.writerow([p_name, level, f"{mean_dice:.4f}"])
-                    if not quiet:
-                        print(f"{p_name} param={level}, Dice={mean_dice:.4f}")
+                pending = ev.submit_level(spec, want_dice=True)
+                if in_flight is not None:
+                    consume(in_flight)
+                in_flight = (p_name, level, pending)
+        if in_flight is not None:
+            consume(in_flight)
     finally:
         if f:
             f.close()

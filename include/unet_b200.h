@@ -60,12 +60,12 @@ enum ub_target_format { UB_TGT_I64 = 0 /* int64 [n,H,W], datasets.py:118-131 */,
 enum ub_perturb_kind {
   UB_P_NONE = 0,
   UB_P_U8_NOISE = 1,       /* perturbations.py:31-50;   fparam = std; aux = fp32 [n,3,H,W] N(0,std) or NULL */
-  UB_P_U8_BLUR = 2,        /* perturbations.py:85-124;  iparam = passes (0..16) */
+  UB_P_U8_BLUR = 2,        /* perturbations.py:85-124;  iparam = passes (0..64; up to 12 run fused in shared memory) */
   UB_P_U8_LUT = 3,         /* perturbations.py:140-156,182-198,222-235,262-275; lut[] filled by ub_make_lut */
   UB_P_U8_OCCLUSION = 4,   /* perturbations.py:301-327; iparam = size; aux = int32 [n,2] (y0,x0), <0 = none, or NULL */
   UB_P_U8_SALT_PEPPER = 5, /* perturbations.py:354-382; fparam = amount; aux = uint8 [n,H,W] 0 keep/1 pepper/2 salt, or NULL */
   UB_P_F_NOISE = 6,        /* processing_blocks.py:471-474; fparam = std; aux = fp32 [n,3,H,W] randn or NULL */
-  UB_P_F_BLUR = 7,         /* processing_blocks.py:493-496 (kornia box_blur, reflect); iparam = times (0..16) */
+  UB_P_F_BLUR = 7,         /* processing_blocks.py:493-496 (kornia box_blur, reflect); iparam = times (0..64) */
   UB_P_F_CONTRAST = 8,     /* processing_blocks.py:516-518; fparam = factor */
   UB_P_F_BRIGHTNESS = 9,   /* processing_blocks.py:535-539; fparam = fl32(offset/255.0) computed by the caller in double */
   UB_P_F_OCCLUSION = 10,   /* processing_blocks.py:557-563; iparam = size; aux = int32 [n,2] (y,x) or NULL */
@@ -115,7 +115,11 @@ int ub_forward(ub_ctx* ctx, const float* x_nchw, float* logits_nchw, int n, int 
  *   dice_sums double [ceil(n/ref_batch), C, 3]   (sum p*1[t=c], sum p, sum 1[t=c]), p = softmax(softmax(z))
  *                                                — the sums smp DiceLoss needs (models/losses.py:98-100); may be NULL
  *   pred_out  uint8  [n,H,W] argmax map, may be NULL;  logits_out fp32 [n,C,H,W], may be NULL
- *   perturbed_out fp32 [n,3,H,W] the perturbed network input, may be NULL */
+ *   perturbed_out fp32 [n,3,H,W] the perturbed network input, may be NULL
+ * Precondition: every target value is a class id in [0, C).  A foreign label (e.g. 255 "ignore") is dropped from every
+ * cell, whereas the reference's IoU (models/losses.py:52-60) still counts the prediction made on that pixel in the
+ * union; the reference's dataset only yields {0,1,2} (datasets.py:118-131).  The Python host checks this once when a
+ * dataset is made resident (evaluator.py). */
 int ub_eval_batches(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,
                     const void* targets, int target_format, const void* aux, int n, int h, int w,
                     int ref_batch, int64_t* cm, double* dice_sums, uint8_t* pred_out,

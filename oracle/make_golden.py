@@ -6,7 +6,8 @@ through oracle/refload.py).  Run in the build container only:  python -m oracle.
                    artefacts (noise tensors, occlusion corners, salt-pepper code maps) captured by
                    replaying random.seed(42)/torch.manual_seed(42) (robustness_evaluation.py:32-34).
   perturb_f.npz    models/processing_blocks.py float-space modules (all but RepeatedBlur, which needs
-                   kornia) on a [2,3,24,40] batch, 3 levels per family.
+                   kornia) on a [2,3,24,40] batch, EVERY level TestWrapper.test_robustness visits
+                   (models/model_wrappers.py:740-764: 69 of its 79 levels; the other 10 are RepeatedBlur).
   unet_small.npz   reference UNet (seed 42 + randomised BatchNorm) logits on a [2,3,32,64] input, the
                    reference IoU / PixelAccuracy on them, and a checksum of the seeded state_dict.
   dataset_rows.npz reference CustomImageDataset._deserialize_datapoint on 6 synthetic rows (trimap remap), masks +
@@ -39,6 +40,16 @@ SCRIPT_LEVELS = {  # scripts/robustness_evaluation.py:59-92
     "brightness_decrease": ("BrightnessDecrease", [0, 5, 10, 15, 20, 25, 30, 35, 40, 45]),
     "occlusion": ("OcclusionIncrease", [0, 5, 10, 15, 20, 25, 30, 35, 40, 45]),
     "salt_pepper_noise": ("SaltPepperNoise", [0.00, 0.02, 0.04, 0.06, 0.08, 0.10, 0.12, 0.14, 0.16, 0.18]),
+}
+
+
+WRAPPER_LEVELS = {  # models/model_wrappers.py:740-764 (class name -> every parameter value test_robustness passes)
+    "GaussianPixelNoise": [1e-6, 2, 4, 6, 8, 10, 12, 14, 16, 18],
+    "ContrastChange": [1.0, 1.01, 1.02, 1.03, 1.04, 1.05, 1.1, 1.15, 1.20, 1.25,
+                       1.0, 0.95, 0.90, 0.85, 0.80, 0.60, 0.40, 0.30, 0.20, 0.10],
+    "BrightnessChange": [0, 5, 10, 15, 20, 25, 30, 35, 40, 45, 0, -5, -10, -15, -20, -25, -30, -35, -40, -45],
+    "Occlusion": [0, 5, 10, 15, 20, 25, 30, 35, 40, 45],
+    "SaltAndPepper": [0.00, 0.02, 0.04, 0.06, 0.08, 0.10, 0.12, 0.14, 0.16],
 }
 
 
@@ -103,14 +114,7 @@ def golden_perturb_f(ns):
     u8, imgs = small_images(seed=12)
     out = {"images_u8": u8.numpy()}
     b, _, h, w = imgs.shape
-    fams = {
-        "GaussianPixelNoise": [1e-6, 8, 18],
-        "ContrastChange": [1.05, 1.25, 0.3],
-        "BrightnessChange": [15, 45, -30],
-        "Occlusion": [0, 15, 45],
-        "SaltAndPepper": [0.0, 0.06, 0.16],
-    }
-    for fam, levels in fams.items():
+    for fam, levels in WRAPPER_LEVELS.items():
         for li, level in enumerate(levels):
             random.seed(42); torch.manual_seed(42)
             mod = getattr(ns.blocks, fam)(level)

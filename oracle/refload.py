@@ -21,8 +21,8 @@ _STUBS = [
 ]
 
 
-def available() -> bool:
-    return os.path.isdir(os.path.join(REFERENCE_ROOT, "models"))
+def available(root: str = None) -> bool:
+    return os.path.isdir(os.path.join(root or REFERENCE_ROOT, "models"))
 
 
 def _install_stubs():
@@ -55,15 +55,18 @@ def _install_stubs():
         smp.losses.DiceLoss = _AbsentDiceLoss
 
 
-def load():
-    """Returns a namespace with the reference's own classes (unmodified code)."""
-    if not available():
-        raise RuntimeError(f"reference tree not found at {REFERENCE_ROOT}")
+def load(root: str = None):
+    """Returns a namespace with the reference's own classes (unmodified code).  `root`: /root/reference (build
+    container, default) or the byte-for-byte copy under baseline/_ref/ that travels to the GPU box (bench.py's CPU
+    legs only; baseline/install_ref.py makes it)."""
+    root = root or REFERENCE_ROOT
+    if not available(root):
+        raise RuntimeError(f"reference tree not found at {root}")
     _install_stubs()
     # The reference uses top-level package names `models` / `customDatasets`; make sure ours
     # (none at repo root) cannot shadow them.
-    if REFERENCE_ROOT not in sys.path:
-        sys.path.insert(0, REFERENCE_ROOT)
+    if root not in sys.path:
+        sys.path.insert(0, root)
     ns = types.SimpleNamespace()
     ns.UNet_mod = importlib.import_module("models.UNet")
     ns.blocks = importlib.import_module("models.processing_blocks")

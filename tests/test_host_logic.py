@@ -129,3 +129,22 @@ def test_rng_replay_helpers_follow_reference_order():
     random.seed(7)
     d = po.replay_salt_pepper_code(0.1, 24, 24)
     assert np.array_equal(c, d)
+
+
+def test_weighted_batch_range_partitions_every_batch_once():
+    """evaluator.batch_range with per-rank weights (re-balancing by measured rate): contiguous, complete, monotone,
+    proportional within one batch, and identical to the balanced split for equal weights up to rounding."""
+    from image_segmentation_b200.evaluator import batch_range
+    for n, w in [(460, [1.0] * 8), (460, [1, 1, 1, 1, 1, 1, 1, 0.9]), (5, [1.0, 3.0]), (3, [1.0] * 8), (0, [1.0, 2.0]),
+                 (368, [25.1, 24.2, 25.9, 23.8])]:
+        world = len(w)
+        edges = [batch_range(n, r, world, w) for r in range(world)]
+        assert edges[0][0] == 0 and edges[-1][1] == n
+        for a, b in zip(edges, edges[1:]):
+            assert a[1] == b[0] and a[0] <= a[1]
+        for r, (a, b) in enumerate(edges):
+            assert abs((b - a) - n * w[r] / sum(w)) <= 1.0
+    assert [batch_range(460, r, 8) for r in range(8)][0] == (0, 58)
+    import pytest
+    with pytest.raises(ValueError):
+        batch_range(10, 0, 2, [1.0, 0.0])

@@ -67,16 +67,21 @@ def oracle_f(fam, level, x, aux):
     raise KeyError(fam)
 
 
-def test_float_perturbations_match_golden(g_f):
+def _float_levels():
+    from oracle.make_golden import WRAPPER_LEVELS
+    return [(fam, li) for fam, levels in WRAPPER_LEVELS.items() for li in range(len(levels))]
+
+
+@pytest.mark.parametrize("fam,li", _float_levels())
+def test_float_perturbations_match_golden(g_f, fam, li):
+    """Every level TestWrapper.test_robustness visits (models/model_wrappers.py:740-764) except RepeatedBlur's."""
+    from oracle.make_golden import WRAPPER_LEVELS
     x = g_f["images_u8"].astype(np.float32) / np.float32(255.0)
-    fams = sorted({k.split("/")[0] for k in g_f.files if "/" in k})
-    assert fams == ["BrightnessChange", "ContrastChange", "GaussianPixelNoise", "Occlusion", "SaltAndPepper"]
-    for fam in fams:
-        for li in range(3):
-            level = float(g_f[f"{fam}/{li}/level"])
-            aux = g_f[f"{fam}/{li}/aux"] if f"{fam}/{li}/aux" in g_f.files else None
-            got = oracle_f(fam, level, x, aux)
-            assert np.array_equal(got, g_f[f"{fam}/{li}/out"]), (fam, level)  # bit-exact fp32
+    level = float(g_f[f"{fam}/{li}/level"])
+    assert level == float(WRAPPER_LEVELS[fam][li])
+    aux = g_f[f"{fam}/{li}/aux"] if f"{fam}/{li}/aux" in g_f.files else None
+    got = oracle_f(fam, level, x, aux)
+    assert np.array_equal(got, g_f[f"{fam}/{li}/out"]), (fam, level)  # bit-exact fp32
 
 
 def test_unet_and_metrics_match_golden():

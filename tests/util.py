@@ -30,9 +30,12 @@ def centre_head(sd, x):
     return sd
 
 
-def train_like(sd, images_f32, masks, steps=150, lr=2e-3, batch=8, crop=128, seed=0, device=None):
+def train_like(sd, images_f32, masks, steps=150, lr=2e-3, batch=8, crop=128, seed=0, device=None, clip_feats=None,
+               prompts=None, binary=False):
     """A few Adam steps of cross-entropy on the oracle network (BatchNorm kept in eval mode = fixed
-    affine) so the logits get real margins.  Checker-side only; runs on the GPU box's torch."""
+    affine) so the logits get real margins.  Checker-side only; runs on the GPU box's torch (IEEE fp32, conftest.py).
+    clip_feats [n,512] / prompts [n,1,H,W]: the ClipUnet / ClipUnetPrompt variants of the oracle network;
+    binary: 1-class head trained with BCE against (mask > 0)."""
     device = device or ("cuda" if torch.cuda.is_available() else "cpu")
     g = torch.Generator().manual_seed(seed)
     params = {k: v.clone().to(device).requires_grad_(v.is_floating_point() and "running" not in k)
@@ -40,14 +43,27 @@ def train_like(sd, images_f32, masks, steps=150, lr=2e-3, batch=8, crop=128, see
     opt = torch.optim.Adam([p for p in params.values() if p.requires_grad], lr=lr)
     n, _, h, w = images_f32.shape
     images_f32, masks = images_f32.to(device), masks.to(device).long()
+    if clip_feats is not None:
+        clip_feats = clip_feats.to(device)
+    if prompts is not None:
+        prompts = prompts.to(device)
     for _ in range(steps):
         idx = torch.randint(0, n, (batch,), generator=g)
         y0 = int(torch.randint(0, h - crop + 1, (1,), generator=g))
         x0 = int(torch.randint(0, w - crop + 1, (1,), generator=g))
         xb = images_f32[idx][:, :, y0:y0 + crop, x0:x0 + crop]
         tb = masks[idx][:, y0:y0 + crop, x0:x0 + crop]
+        kw = {}
+        if clip_feats is not None:
+            kw["clip_feats"] = clip_feats[idx.to(device)]
+        if prompts is not None:
+            kw["prompt"] = prompts[idx.to(device)][:, :, y0:y0 + crop, x0:x0 + crop]
         with torch.enable_grad():
-            loss = torch.nn.functional.cross_entropy(unet_oracle.forward_impl(params, xb), tb)
+            z = unet_oracle.forward_impl(params, xb, **kw)
+            if binary:
+                loss = torch.nn.functional.binary_cross_entropy_with_logits(z[:, 0], (tb > 0).float())
+            else:
+                loss = torch.nn.functional.cross_entropy(z, tb)
             opt.zero_grad()
             loss.backward()
             opt.step()
@@ -56,3 +72,33 @@ def train_like(sd, images_f32, masks, steps=150, lr=2e-3, batch=8, crop=128, see
         if k not in out:
             out[k] = v.clone()
     return out
+
+
+_announced = False
+
+
+def oracle_logits(sd, x, **kw):
+    """The oracle network evaluated ON THE CPU in fp32 (never cuDNN/TF32): the reference side of every logits / argmax
+    gate.  Inputs may live anywhere; the result is a CPU tensor."""
+    global _announced
+    if not _announced:
+        print(f"[oracle] unet_oracle.forward on the CPU, fp32, {torch.get_num_threads()} threads")
+        _announced = True
+    sd_cpu = {k: v.detach().cpu() for k, v in sd.items()}
+    kw_cpu = {k: (v.detach().cpu() if torch.is_tensor(v) else v) for k, v in kw.items()}
+    return unet_oracle.forward(sd_cpu, x.detach().cpu(), **kw_cpu)
+
+
+def oracle_logits_gpu_ieee(sd, x, dev, **kw):
+    """The oracle on the GPU with TF32 switched off (tests/conftest.py): IEEE fp32 through cuDNN.  Used only where the
+    CPU would take minutes (the 159-level sweep); test_gpu_sweep_parity.py checks it against oracle_logits."""
+    assert not torch.backends.cudnn.allow_tf32 and not torch.backends.cuda.matmul.allow_tf32
+    kw_dev = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in kw.items()}
+    return unet_oracle.forward({k: v.to(dev) for k, v in sd.items()}, x.to(dev), **kw_dev).cpu()
+
+
+def argmax_agreement(a: torch.Tensor, b: torch.Tensor) -> float:
+    """Share of pixels where the reference rule argmax(softmax(z)) agrees; for a 1-class head, where sign(z) agrees."""
+    if a.shape[1] == 1:
+        return float(((a > 0) == (b > 0)).float().mean())
+    return float((unet_oracle.hard_prediction(a) == unet_oracle.hard_prediction(b)).float().mean())
