@@ -69,6 +69,10 @@ struct Plan {
   void* blur_a = nullptr;      // ping-pong planes (fp32-sized)
   void* blur_b = nullptr;
   std::vector<Step> steps;
+  // the encoder's feature maps as the halves' entry points see them (ub_encoder_forward / ub_skip_decoder_forward):
+  // buffer, planes per image, first plane, channels, level (resolution H >> level)
+  struct Feat { __nv_bfloat16* buf; int cgs, cg0, c, level; };
+  std::vector<Feat> feats;
 };
 
 }  // namespace
@@ -108,6 +112,7 @@ struct ub_ctx {
   // is per device and per function, so a second context on another GPU of the same process makes its own)
   std::set<const void*> smem_opt_in;
   bool has_clip() const { return arch == UB_ARCH_CLIP_UNET || arch == UB_ARCH_CLIP_UNET_PROMPT; }
+  bool is_half() const { return arch == UB_ARCH_ENCODER || arch == UB_ARCH_SKIP_DECODER; }
 };
 
 namespace {
@@ -295,26 +300,34 @@ int pack_conv1x1(ub_ctx* ctx, const std::string& key) {
 
 int pack_all(ub_ctx* ctx) {
   int rc;
+  // the two halves of SegmentationModel hold one half of the weights each (models/autoencoder.py:5-26,
+  // models/pre_trained.py:7-24); neither folds the stem (the decoder is handed the stem OUTPUT "x0")
+  const bool enc_half = ctx->arch == UB_ARCH_ENCODER, dec_half = ctx->arch == UB_ARCH_SKIP_DECODER;
+  if (enc_half || dec_half) ctx->stem_fold = false;
   const HostTensor* sw = find(ctx, "input.weight");
   const HostTensor* sb = find(ctx, "input.bias");
   const HostTensor* ow = find(ctx, "out.weight");
   const HostTensor* ob = find(ctx, "out.bias");
-  if (!sw || !sb || !ow || !ob) return fail(ctx, UB_ERR_INVALID, "missing input.* / out.* entries");
-  if (sw->data.size() != 32 * 3 || sb->data.size() != 32)
-    return fail(ctx, UB_ERR_UNSUPPORTED, "stem must be Conv2d(3,32,1)");
+  if ((!dec_half && (!sw || !sb)) || (!enc_half && (!ow || !ob))) return fail(ctx, UB_ERR_INVALID, "missing input.* / out.* entries");
   const bool ae = ctx->arch == UB_ARCH_AUTOENCODER;  // Decoder.out is Conv2d(64, out_channels, 1) (autoencoder.py:34)
-  if (static_cast<int>(ow->shape[0]) != ctx->n_classes || ow->shape[1] != (ae ? 64 : 32))
-    return fail(ctx, UB_ERR_INVALID, "out.weight must be [%d,%d,1,1]", ctx->n_classes, ae ? 64 : 32);
-  memcpy(ctx->stem.w, sw->data.data(), sizeof(ctx->stem.w));
-  memcpy(ctx->stem.b, sb->data.data(), sizeof(ctx->stem.b));
-  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->head_w), ow->data.size() * 4))) return rc;
-  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->head_b), ob->data.size() * 4))) return rc;
-  UB_CUDA(ctx, cudaMemcpy(ctx->head_w, ow->data.data(), ow->data.size() * 4, cudaMemcpyHostToDevice));
-  UB_CUDA(ctx, cudaMemcpy(ctx->head_b, ob->data.data(), ob->data.size() * 4, cudaMemcpyHostToDevice));
-  ctx->h_head_w = ow->data;
-  ctx->h_head_b = ob->data;
+  if (!dec_half) {
+    if (sw->data.size() != 32 * 3 || sb->data.size() != 32)
+      return fail(ctx, UB_ERR_UNSUPPORTED, "stem must be Conv2d(3,32,1)");
+    memcpy(ctx->stem.w, sw->data.data(), sizeof(ctx->stem.w));
+    memcpy(ctx->stem.b, sb->data.data(), sizeof(ctx->stem.b));
+  }
+  if (!enc_half) {
+    if (static_cast<int>(ow->shape[0]) != ctx->n_classes || ow->shape[1] != (ae ? 64 : 32))
+      return fail(ctx, UB_ERR_INVALID, "out.weight must be [%d,%d,1,1]", ctx->n_classes, ae ? 64 : 32);
+    if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->head_w), ow->data.size() * 4))) return rc;
+    if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&ctx->head_b), ob->data.size() * 4))) return rc;
+    UB_CUDA(ctx, cudaMemcpy(ctx->head_w, ow->data.data(), ow->data.size() * 4, cudaMemcpyHostToDevice));
+    UB_CUDA(ctx, cudaMemcpy(ctx->head_b, ob->data.data(), ob->data.size() * 4, cudaMemcpyHostToDevice));
+    ctx->h_head_w = ow->data;
+    ctx->h_head_b = ob->data;
+  }
   char k[128];
-  for (int i = 1; i <= ctx->n_enc; ++i) {
+  for (int i = 1; i <= (dec_half ? 0 : ctx->n_enc); ++i) {
     snprintf(k, sizeof(k), "enc%d.block.0.conv", i);
     if ((rc = pack_conv(ctx, std::string(k) + ".0", std::string(k) + ".1"))) return rc;
     if ((rc = pack_conv(ctx, std::string(k) + ".3", std::string(k) + ".4"))) return rc;
@@ -357,14 +370,19 @@ int pack_all(ub_ctx* ctx) {
     UB_CUDA(ctx, cudaMemcpy(ctx->fuse_wo_t, wo_t.data(), mb, cudaMemcpyHostToDevice));
     UB_CUDA(ctx, cudaMemcpy(ctx->fuse_bv, ipb->data.data() + 2 * E, vb, cudaMemcpyHostToDevice));
     UB_CUDA(ctx, cudaMemcpy(ctx->fuse_bo, opb->data.data(), vb, cudaMemcpyHostToDevice));
-  } else {
+  } else if (!dec_half) {
     if ((rc = pack_conv(ctx, "bottleneck.conv.0", "bottleneck.conv.1"))) return rc;
     if ((rc = pack_conv(ctx, "bottleneck.conv.3", "bottleneck.conv.4"))) return rc;
   }
+  if (enc_half) {
+    UB_CUDA(ctx, cudaDeviceSynchronize());
+    ctx->weights_ready = true;
+    return UB_OK;
+  }
   // the stem's two readers, once more with the stem folded into their weights (the plain versions stay for the
   // layer-wise debug entry and UB_NO_STEM_FOLD)
-  if ((rc = pack_conv(ctx, "enc1.block.0.conv.0", "enc1.block.0.conv.1", 0))) return rc;
-  if (!ae) {
+  if (!dec_half && (rc = pack_conv(ctx, "enc1.block.0.conv.0", "enc1.block.0.conv.1", 0))) return rc;
+  if (!ae && !dec_half) {
     snprintf(k, sizeof(k), "dec%d.conv.conv", ctx->n_enc + 1);
     // (32 channels wide, the upper 16 with zero weights over planes nobody writes: 64 input channels keep the BK = 64
     // kx-stacked kernel — with 48 channels as three BK = 16 chunks the layer was slower, 22.2 against 20.7 ms)
@@ -730,8 +748,14 @@ int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out) {
     return UB_OK;
   };
   char k[128];
+  // the feature maps of Encoder.forward's dict (models/autoencoder.py:17-25): x0 and the pooled stage outputs live in
+  // the skip planes of the concat buffers, the bottleneck in its own buffer
+  for (int l = 0; l <= n; ++l)
+    pl->feats.push_back({bufp(i_cat[l]), 2 * skip_width(l) / 8, skip_width(l) / 8, skip_width(l), l});
+  pl->feats.push_back({bufp(i_bb), cb / 8, 0, cb, n});
+  const bool enc_half = ctx->arch == UB_ARCH_ENCODER, dec_half = ctx->arch == UB_ARCH_SKIP_DECODER;
   // encoder (models/UNet.py:63-65): conv.0 -> conv.3 + MaxPool into the skip planes of the next concat buffer
-  for (int i = 1; i <= n; ++i) {
+  for (int i = 1; i <= (dec_half ? 0 : n); ++i) {
     snprintf(k, sizeof(k), "enc%d.block.0.conv", i);
     const bool fold = (i == 1 && ctx->stem_fold);  // reads the packed image (16 channels) through composed weights
     if ((rc = add_gemm(std::string(k) + (fold ? ".0+stem" : ".0"), skip_half(i - 1), 2 * skip_width(i - 1) / 8, hl(i - 1), wl(i - 1),
@@ -770,10 +794,15 @@ int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out) {
     s.rs_out = bufp(i_pcat); s.ho = hl(n); s.wo = wl(n); s.c = cb; s.out_cgs = 2 * cb / 8;
     pl->steps.push_back(s);
     if ((rc = add_gemm("prompt_fusion", bufp(i_pcat), 2 * cb / 8, hl(n), wl(n), ub::EPI_STORE, bufp(i_bb), cb / 8, 0))) return rc;
-  } else {
+  } else if (!dec_half) {
     if ((rc = add_gemm("bottleneck.conv.0", skip_half(n), 2 * skip_width(n) / 8, hl(n), wl(n), ub::EPI_STORE,
                        bufp(i_ba), cb / 8, 0))) return rc;
     if ((rc = add_gemm("bottleneck.conv.3", bufp(i_ba), cb / 8, hl(n), wl(n), ub::EPI_STORE, bufp(i_bb), cb / 8, 0))) return rc;
+  }
+  if (enc_half) {  // Encoder on its own: no decoder
+    *out = pl.get();
+    ctx->plans[key] = std::move(pl);
+    return UB_OK;
   }
   // decoder (UNet.py:69-72, processing_blocks.py:105-109)
   const __nv_bfloat16* x = bufp(i_bb);
@@ -839,20 +868,37 @@ int to_dev_perturb(ub_ctx* ctx, const ub_perturb* p, const void* aux, ub::Pertur
 
 inline unsigned blocks_for(size_t n, int bs) { return static_cast<unsigned>((n + bs - 1) / bs); }
 
-// Blur families: quantise/load -> passes (ping-pong) -> fp32 NCHW in pl->pert_f32.
-int run_blur(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* img, int fmt, int n, float* dst, cudaStream_t st) {
+// Blur families.  Up to kBlurMaxPasses passes: one launch of blur_fused_kernel, which writes the packed network input
+// (`packed`, may be null) and/or the fp32 NCHW image (`dst`, may be null).  More passes (or UB_NO_BLUR_FUSE): quantise/load
+// -> one launch per pass (ping-pong planes) -> fp32 NCHW in `dst`; the caller packs it.  Returns through *did_pack
+// whether `packed` has been written.
+int run_blur(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* img, int fmt, int n, float* dst,
+             __nv_bfloat16* packed, int cgs, int cg0, bool* did_pack, cudaStream_t st) {
   const int H = pl->H, W = pl->W;
   const size_t count = static_cast<size_t>(n) * 3 * H * W;
   const unsigned g = blocks_for(count, 256);
+  if (did_pack) *did_pack = false;
   if (P.iparam <= ub::kBlurMaxPasses && !ctx->no_blur_fuse) {
-    // every pass of a tile in shared memory: one launch, the image read once, the fp32 result written once
-    const dim3 grid((W + ub::kBlurTW - 1) / ub::kBlurTW, (H + ub::kBlurTH - 1) / ub::kBlurTH, n * 3);
-    if (P.kind == UB_P_U8_BLUR) ub::blur_fused_kernel<false><<<grid, 256, 0, st>>>(img, fmt, H, W, P.iparam, dst);
-    else ub::blur_fused_kernel<true><<<grid, 256, 0, st>>>(img, fmt, H, W, P.iparam, dst);
+    // every pass of a tile in shared memory: one launch, the image read once, the result written once
+    const bool is_f = P.kind != UB_P_U8_BLUR;
+    const size_t smem = ub::blur_smem_bytes(P.iparam, is_f);
+    if (smem > 48 * 1024) {  // the float family with many passes: opt in (per device, like the conv kernels)
+      const void* fn = reinterpret_cast<const void*>(&ub::blur_fused_kernel<true>);
+      if (!ctx->smem_opt_in.count(fn)) {
+        UB_CUDA(ctx, cudaFuncSetAttribute(ub::blur_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          static_cast<int>(ub::blur_smem_bytes(ub::kBlurMaxPasses, true))));
+        ctx->smem_opt_in.insert(fn);
+      }
+    }
+    const dim3 grid((W + ub::kBlurTW - 1) / ub::kBlurTW, (H + ub::kBlurTH - 1) / ub::kBlurTH, n);
+    if (!is_f) ub::blur_fused_kernel<false><<<grid, 256, smem, st>>>(img, fmt, H, W, P.iparam, dst, packed, cgs, cg0);
+    else ub::blur_fused_kernel<true><<<grid, 256, smem, st>>>(img, fmt, H, W, P.iparam, dst, packed, cgs, cg0);
     ctx->launches++;
     UB_CUDA(ctx, cudaGetLastError());
+    if (did_pack) *did_pack = packed != nullptr;
     return UB_OK;
   }
+  if (!dst) return fail(ctx, UB_ERR_STATE, "the pass-per-launch blur path needs an fp32 destination");
   if (P.kind == UB_P_U8_BLUR) {
     uint8_t* a = static_cast<uint8_t*>(pl->blur_a);
     uint8_t* b = static_cast<uint8_t*>(pl->blur_b);
@@ -895,9 +941,19 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
   const int H = pl->H, W = pl->W;
   const size_t px = static_cast<size_t>(nb) * H * W;
   int rc;
-  if (P.kind == UB_P_U8_BLUR || P.kind == UB_P_F_BLUR) {
-    float* dst = perturbed_out ? perturbed_out : pl->pert_f32;
-    if ((rc = run_blur(ctx, pl, P, img, fmt, nb, dst, st))) return rc;
+  if (!img) {
+    // SegmentationDecoderSkip on its own: the feature maps are already in the plan's buffers (ub_skip_decoder_forward)
+  } else if (P.kind == UB_P_U8_BLUR || P.kind == UB_P_F_BLUR) {
+    // fused passes + folded stem: the blur kernel writes the packed image itself (no fp32 staging image, no second
+    // launch); perturbed_out (tests) is written by the same launch when asked for
+    const bool direct = ctx->stem_fold && P.iparam <= ub::kBlurMaxPasses && !ctx->no_blur_fuse;
+    float* dst = perturbed_out ? perturbed_out : (direct ? nullptr : pl->pert_f32);
+    bool packed_done = false;
+    if ((rc = run_blur(ctx, pl, P, img, fmt, nb, dst, direct ? pl->stem_out : nullptr, pl->stem_cgs, pl->stem_cg0, &packed_done, st)))
+      return rc;
+    if (packed_done) {
+      // (the launch below is not needed)
+    } else {
     ub::PerturbDev none;
     memset(&none, 0, sizeof(none));
     if (ctx->stem_fold)
@@ -906,15 +962,20 @@ int run_microbatch(ub_ctx* ctx, Plan* pl, const ub::PerturbDev& P, const void* i
     else
       ub::stem_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(none, ctx->stem, dst, UB_IMG_F32_NCHW, nb, H, W, pl->stem_out,
                                                           pl->stem_cgs, pl->stem_cg0, nullptr);
+    UB_CUDA(ctx, cudaGetLastError());
+    ctx->launches++;
+    }
   } else if (ctx->stem_fold) {
     ub::image_pack_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(P, img, fmt, nb, H, W, pl->stem_out, pl->stem_cgs,
                                                               pl->stem_cg0, perturbed_out);
+    UB_CUDA(ctx, cudaGetLastError());
+    ctx->launches++;
   } else {
     ub::stem_kernel<<<blocks_for(blocks_for(px, ub::kStemPx), 256), 256, 0, st>>>(P, ctx->stem, img, fmt, nb, H, W, pl->stem_out, pl->stem_cgs,
                                                         pl->stem_cg0, perturbed_out);
+    UB_CUDA(ctx, cudaGetLastError());
+    ctx->launches++;
   }
-  UB_CUDA(ctx, cudaGetLastError());
-  ctx->launches++;
   for (Step& s : pl->steps) {
     if (s.kind == Step::CLIP_FUSE) {
       if (!ha.clip) return fail(ctx, UB_ERR_INVALID, "this model needs CLIP embeddings: call ub_eval_batches_clip");
@@ -996,8 +1057,7 @@ int ub_make_lut(ub_perturb* p, int lut_kind, double param) {
 int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes, int max_microbatch) {
   if (!out) return UB_ERR_INVALID;
   *out = nullptr;
-  if (arch != UB_ARCH_UNET && arch != UB_ARCH_LARGE_UNET && arch != UB_ARCH_CLIP_UNET && arch != UB_ARCH_CLIP_UNET_PROMPT &&
-      arch != UB_ARCH_AUTOENCODER)
+  if (arch < UB_ARCH_UNET || arch > UB_ARCH_SKIP_DECODER)
     return fail(nullptr, UB_ERR_INVALID, "unknown arch %d", arch);
   if (in_channels != 3) return fail(nullptr, UB_ERR_UNSUPPORTED, "only in_channels=3 is supported");
   if (n_classes < 1 || n_classes > ub::kMaxClasses) return fail(nullptr, UB_ERR_UNSUPPORTED, "n_classes must be 1..%d", ub::kMaxClasses);
@@ -1118,6 +1178,8 @@ int eval_impl(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_fo
     return fail(ctx, UB_ERR_INVALID, "clip_feats given to a model without a CLIP fusion");
   if ((ctx->arch == UB_ARCH_CLIP_UNET_PROMPT) != (prompt != nullptr))
     return fail(ctx, UB_ERR_INVALID, "a prompt heat-map goes with UB_ARCH_CLIP_UNET_PROMPT (ub_forward_prompt) and only with it");
+  if (ctx->is_half())
+    return fail(ctx, UB_ERR_INVALID, "UB_ARCH_ENCODER / UB_ARCH_SKIP_DECODER compute through ub_encoder_forward / ub_skip_decoder_forward");
   if (!images || n <= 0 || ref_batch <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
   if (ctx->arch == UB_ARCH_AUTOENCODER && (targets || cm || dice_sums || pred_out))
     return fail(ctx, UB_ERR_INVALID, "UB_ARCH_AUTOENCODER reconstructs images (ub_forward); it has no argmax / confusion counts");
@@ -1239,6 +1301,67 @@ int ub_forward(ub_ctx* ctx, const float* x_nchw, float* logits_nchw, int n, int 
                          nullptr, logits_nchw, nullptr, stream);
 }
 
+// One micro-batch loop shared by the two halves: `encode` runs stem + encoder steps and copies the features out,
+// otherwise the features are copied in and the decoder steps run.
+static int run_half(ub_ctx* ctx, bool encode, const float* x_nchw, float* const* feats_out, const float* const* feats_in,
+                    int n_feats, float* logits, int n, int h, int w, void* stream) {
+  int rc;
+  if ((rc = check_ready(ctx))) return rc;
+  if (ctx->arch != (encode ? UB_ARCH_ENCODER : UB_ARCH_SKIP_DECODER))
+    return fail(ctx, UB_ERR_INVALID, encode ? "ub_encoder_forward needs a UB_ARCH_ENCODER context"
+                                            : "ub_skip_decoder_forward needs a UB_ARCH_SKIP_DECODER context");
+  if (n <= 0 || n_feats != ctx->n_enc + 2 || (encode ? (!x_nchw || !feats_out) : (!feats_in || !logits)))
+    return fail(ctx, UB_ERR_INVALID, "bad arguments (n_feats must be %d)", ctx->n_enc + 2);
+  for (int f = 0; f < n_feats; ++f)
+    if (!(encode ? static_cast<const void*>(feats_out[f]) : static_cast<const void*>(feats_in[f])))
+      return fail(ctx, UB_ERR_INVALID, "feature map %d is null", f);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  Plan* pl;
+  if ((rc = build_plan(ctx, h, w, st, &pl))) return rc;
+  const size_t hw = static_cast<size_t>(h) * w;
+  ub::PerturbDev none;
+  memset(&none, 0, sizeof(none));
+  for (int i0 = 0; i0 < n; i0 += ctx->max_mb) {
+    const int nb = (n - i0) < ctx->max_mb ? (n - i0) : ctx->max_mb;
+    HeadArgs ha;
+    ha.logits = logits ? logits + hw * ctx->n_classes * i0 : nullptr;
+    if (!encode) {
+      for (int f = 0; f < n_feats; ++f) {
+        const Plan::Feat& F = pl->feats[f];
+        const size_t fhw = hw >> (2 * F.level);
+        ub::block_from_nchw_kernel<<<blocks_for(static_cast<size_t>(nb) * (F.c / 8) * fhw, 256), 256, 0, st>>>(
+            feats_in[f] + static_cast<size_t>(i0) * F.c * fhw, F.c, fhw, nb, F.buf, F.cgs, F.cg0);
+        ctx->launches++;
+      }
+      UB_CUDA(ctx, cudaGetLastError());
+    }
+    if ((rc = run_microbatch(ctx, pl, none, encode ? x_nchw + hw * 3 * i0 : nullptr, UB_IMG_F32_NCHW, nb, ha, nullptr, st)))
+      return rc;
+    if (encode) {
+      for (int f = 0; f < n_feats; ++f) {
+        const Plan::Feat& F = pl->feats[f];
+        const size_t fhw = hw >> (2 * F.level);
+        ub::unblock_to_nchw_kernel<<<blocks_for(static_cast<size_t>(nb) * (F.c / 8) * fhw, 256), 256, 0, st>>>(
+            F.buf, F.cgs, F.cg0, F.c, fhw, nb, feats_out[f] + static_cast<size_t>(i0) * F.c * fhw);
+        ctx->launches++;
+      }
+      UB_CUDA(ctx, cudaGetLastError());
+    }
+  }
+  return UB_OK;
+}
+
+int ub_encoder_forward(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* const* feats, int n_feats, void* stream) {
+  if (!ctx) return UB_ERR_INVALID;
+  return run_half(ctx, true, x_nchw, feats, nullptr, n_feats, nullptr, n, h, w, stream);
+}
+
+int ub_skip_decoder_forward(ub_ctx* ctx, const float* const* feats, int n_feats, float* logits_nchw, int n, int h, int w,
+                            void* stream) {
+  if (!ctx) return UB_ERR_INVALID;
+  return run_half(ctx, false, nullptr, nullptr, feats, n_feats, logits_nchw, n, h, w, stream);
+}
+
 int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, const void* aux, int n,
                       int h, int w, float* out_nchw, void* stream) {
   if (!ctx) return UB_ERR_INVALID;
@@ -1253,14 +1376,14 @@ int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int 
     Plan tmp;
     tmp.H = h; tmp.W = w;
     if (P.iparam <= ub::kBlurMaxPasses && !ctx->no_blur_fuse)  // every pass in shared memory: no planes needed
-      return run_blur(ctx, &tmp, P, images, image_format, n, out_nchw, st);
+      return run_blur(ctx, &tmp, P, images, image_format, n, out_nchw, nullptr, 0, 0, nullptr, st);
     // pass-per-launch path: ping-pong planes, allocated per call on the stream (not on the evaluation hot path)
     void *a = nullptr, *b = nullptr;
     const size_t bytes = static_cast<size_t>(n) * 3 * hw * 4;
     UB_CUDA(ctx, cudaMallocAsync(&a, bytes, st));
     UB_CUDA(ctx, cudaMallocAsync(&b, bytes, st));
     tmp.blur_a = a; tmp.blur_b = b;
-    rc = run_blur(ctx, &tmp, P, images, image_format, n, out_nchw, st);
+    rc = run_blur(ctx, &tmp, P, images, image_format, n, out_nchw, nullptr, 0, 0, nullptr, st);
     cudaFreeAsync(a, st);
     cudaFreeAsync(b, st);
     return rc;

@@ -52,8 +52,42 @@ __global__ void resample_bilinear_kernel(const __nv_bfloat16* __restrict__ in, i
   reinterpret_cast<uint4*>(out)[((static_cast<size_t>(b) * out_cgs + out_cg0 + g) * Ho + oy) * Wo + ox] = o;
 }
 
-// Layout converters for the test hooks (NCHW fp32 <-> NHWC bf16 are done by the caller in torch);
-// nothing needed here.
+// Feature maps across the C ABI (ub_encoder_forward / ub_skip_decoder_forward; models/autoencoder.py:17-25): channel
+// planes [cg0, cg0 + C/8) of a blocked bf16 buffer [n][cgs][hw][8] <-> fp32 NCHW [n][C][hw].  One thread per (image,
+// channel group, pixel): a 16-byte access on the blocked side, 8 coalesced 4-byte accesses (one per channel plane) on the
+// NCHW side.  HBM-bound: 2 + 4 bytes per element.
+__global__ void __launch_bounds__(256)
+unblock_to_nchw_kernel(const __nv_bfloat16* __restrict__ in, int cgs, int cg0, int C, size_t hw, int n, float* __restrict__ out) {
+  const int groups = C / 8;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<size_t>(n) * groups * hw) return;
+  const size_t px = i % hw;
+  const int g = static_cast<int>((i / hw) % groups), b = static_cast<int>(i / (hw * groups));
+  const uint4 v = reinterpret_cast<const uint4*>(in)[(static_cast<size_t>(b) * cgs + cg0 + g) * hw + px];
+  const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+  float* dst = out + (static_cast<size_t>(b) * C + 8 * g) * hw + px;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    dst[static_cast<size_t>(2 * j) * hw] = __uint_as_float(u[j] << 16);
+    dst[static_cast<size_t>(2 * j + 1) * hw] = __uint_as_float(u[j] & 0xffff0000u);
+  }
+}
+__global__ void __launch_bounds__(256)
+block_from_nchw_kernel(const float* __restrict__ in, int C, size_t hw, int n, __nv_bfloat16* __restrict__ out, int cgs, int cg0) {
+  const int groups = C / 8;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<size_t>(n) * groups * hw) return;
+  const size_t px = i % hw;
+  const int g = static_cast<int>((i / hw) % groups), b = static_cast<int>(i / (hw * groups));
+  const float* src = in + (static_cast<size_t>(b) * C + 8 * g) * hw + px;
+  uint32_t u[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    __nv_bfloat162 h2 = __floats2bfloat162_rn(src[static_cast<size_t>(2 * j) * hw], src[static_cast<size_t>(2 * j + 1) * hw]);
+    u[j] = *reinterpret_cast<uint32_t*>(&h2);
+  }
+  reinterpret_cast<uint4*>(out)[(static_cast<size_t>(b) * cgs + cg0 + g) * hw + px] = make_uint4(u[0], u[1], u[2], u[3]);
+}
 
 // Metrics from materialised logits (models/losses.py:43-63, :133-154, :98-100): softmax -> argmax ->
 // warp-aggregated counts into a shared-memory int64 histogram -> one global atomic per cell per block.

@@ -48,6 +48,19 @@ __device__ __forceinline__ float normal_from(uint32_t r0, uint32_t r1) {
 
 __device__ __forceinline__ float clamp01(float v) { return fminf(fmaxf(v, 0.0f), 1.0f); }
 
+// One pixel of the packed network input (ub_api.cu: pack_conv fold_at): (r, g, b, 1, r_lo, g_lo, b_lo, 0) in bf16, 16 bytes.
+// Channels 4-6 carry what bf16 rounding dropped from r, g, b (same weights as channels 0-2): the layer sees the pixel to
+// ~16 bits instead of 8.
+__device__ __forceinline__ uint4 pack_pixel(float r, float g, float b) {
+  const __nv_bfloat16 hr = __float2bfloat16(r), hg = __float2bfloat16(g), hb = __float2bfloat16(b);
+  __nv_bfloat162 rg = __halves2bfloat162(hr, hg);
+  __nv_bfloat162 b1 = __halves2bfloat162(hb, __float2bfloat16(1.0f));
+  __nv_bfloat162 lo_rg = __floats2bfloat162_rn(r - __bfloat162float(hr), g - __bfloat162float(hg));
+  __nv_bfloat162 lo_b0 = __floats2bfloat162_rn(b - __bfloat162float(hb), 0.0f);
+  return make_uint4(*reinterpret_cast<uint32_t*>(&rg), *reinterpret_cast<uint32_t*>(&b1),
+                    *reinterpret_cast<uint32_t*>(&lo_rg), *reinterpret_cast<uint32_t*>(&lo_b0));
+}
+
 // Raw pixel channel as the dataset would hand it over: fp32 in [0,1].
 __device__ __forceinline__ float load_f(const void* img, int fmt, int b, int c, int y, int x, int H, int W) {
   if (fmt == UB_IMG_F32_NCHW)
@@ -238,93 +251,114 @@ __global__ void blur_f_pass_kernel(const float* in, float* out, int planes, int 
 }
 
 // ---- all blur passes of one tile in shared memory (both families, passes <= kBlurMaxPasses; more passes fall back to
-// the pass-per-launch kernels above).  One CTA = one 32x64 tile of one (image, channel) plane plus a halo of `passes`
-// pixels; pass p recomputes the region shrunk by p, so after the last pass the tile itself is exact.  The image is read
-// once (straight from its container: the quantise / load step is the tile load) and the fp32 NCHW result written once:
-// one launch instead of passes + 2, and no planar intermediates in HBM.
+// the pass-per-launch kernels above).  One CTA = one 32x64 tile of one IMAGE (its three channels one after the other,
+// through the same two ping-pong regions) plus a halo of `passes` pixels; pass p recomputes the region shrunk by p, so
+// after the last pass the tile itself is exact.  The image is read once (straight from its container: the quantise / load
+// step is the tile load) and the result written once — as the PACKED network input (16 bytes per pixel into the level-0
+// concat buffer, what image_pack_kernel writes for the other families: the blur levels need no fp32 staging image and
+// no second launch) and/or as fp32 NCHW (ub_perturb_images, perturbed_out, the materialised-stem path).
 //   uint8 family: positions outside the image hold 0 in every pass (conv2d zero padding, perturbations.py:108-115).
 //   float family: neighbours outside the image are mirrored (kornia reflect border) when read; same summation order as
 //   blur_f_pass_kernel.
 constexpr int kBlurTH = 32, kBlurTW = 64, kBlurMaxPasses = 12;
-constexpr int kBlurRegion = (kBlurTH + 2 * kBlurMaxPasses) * (kBlurTW + 2 * kBlurMaxPasses);
+__host__ __device__ constexpr int blur_region(int passes) { return (kBlurTH + 2 * passes) * (kBlurTW + 2 * passes); }
+__host__ __device__ constexpr size_t blur_smem_bytes(int passes, bool is_float) {
+  return (2 * static_cast<size_t>(blur_region(passes)) + 3 * kBlurTH * kBlurTW) * (is_float ? 4 : 1);
+}
 template <bool FLOAT>
 __global__ void __launch_bounds__(256)
-blur_fused_kernel(const void* __restrict__ img, int fmt, int H, int W, int passes, float* __restrict__ out) {
+blur_fused_kernel(const void* __restrict__ img, int fmt, int H, int W, int passes, float* __restrict__ out,
+                  __nv_bfloat16* __restrict__ packed, int cgs, int cg0) {
   using T = typename std::conditional<FLOAT, float, uint8_t>::type;
-  __shared__ T s_buf[2][kBlurRegion];
-  const int plane = blockIdx.z, b = plane / 3, c = plane % 3;
+  extern __shared__ __align__(16) uint8_t blur_smem[];
+  const int region = blur_region(passes);
+  T* s_buf[2] = {reinterpret_cast<T*>(blur_smem), reinterpret_cast<T*>(blur_smem) + region};
+  T* s_fin = reinterpret_cast<T*>(blur_smem) + 2 * region;  // [3][kBlurTH * kBlurTW]: the finished tile of each channel
+  const int b = blockIdx.z;
   const int y0 = blockIdx.y * kBlurTH - passes, x0 = blockIdx.x * kBlurTW - passes;  // image coordinates of region (0,0)
   const int RH = kBlurTH + 2 * passes, RW = kBlurTW + 2 * passes;
-  for (int i = threadIdx.x; i < RH * RW; i += blockDim.x) {
-    const int y = y0 + i / RW, x = x0 + i % RW;
-    const bool in = y >= 0 && y < H && x >= 0 && x < W;
-    if constexpr (FLOAT) s_buf[0][i] = in ? load_f(img, fmt, b, c, y, x, H, W) : 0.0f;
-    else s_buf[0][i] = in ? static_cast<uint8_t>(load_u8(img, fmt, b, c, y, x, H, W)) : static_cast<uint8_t>(0);
-  }
-  __syncthreads();
-  int cur = 0;
-  for (int p = 1; p <= passes; ++p) {
-    const T* src = s_buf[cur];
-    T* dst = s_buf[cur ^ 1];
-    const int h = RH - 2 * p, w = RW - 2 * p;  // region still exact after this pass
-    if constexpr (FLOAT) {
-      for (int i = threadIdx.x; i < h * w; i += blockDim.x) {
-        const int ry = p + i / w, rx = p + i % w;
-        const int y = y0 + ry, x = x0 + rx;
-        float acc = 0.0f;
-        if (y >= 0 && y < H && x >= 0 && x < W) {
-          const float ninth = 1.0f / 9.0f;
-#pragma unroll
-          for (int dy = -1; dy <= 1; ++dy)
-#pragma unroll
-            for (int dx = -1; dx <= 1; ++dx) {
-              int yy = y + dy, xx = x + dx;
-              yy = yy < 0 ? -yy : (yy >= H ? 2 * H - 2 - yy : yy);
-              xx = xx < 0 ? -xx : (xx >= W ? 2 * W - 2 - xx : xx);
-              acc = __fadd_rn(acc, __fmul_rn(src[(yy - y0) * RW + (xx - x0)], ninth));
-            }
-        }
-        dst[ry * RW + rx] = acc;
-      }
-    } else {
-      // integer sums are order-free: a thread walks down one column of a row segment keeping the horizontal 3-sums of
-      // the last two rows (3 shared-memory loads and one store per output instead of 9 loads)
-      const int segs = static_cast<int>(blockDim.x) / w;  // 64 <= w <= 86: 2..4 row segments per column
-      const int seg_rows = (h + segs - 1) / segs;
-      const int col = static_cast<int>(threadIdx.x) % w, seg = static_cast<int>(threadIdx.x) / w;
-      const int rx = p + col, r_begin = p + seg * seg_rows, r_end = min(p + h, r_begin + seg_rows);
-      if (seg < segs && r_begin < r_end) {
-        const int x = x0 + rx;
-        const bool x_in = x >= 0 && x < W;
-        auto hsum = [&](int ry) {
-          const uint8_t* r = src + ry * RW + rx;
-          return static_cast<int>(r[-1]) + static_cast<int>(r[0]) + static_cast<int>(r[1]);
-        };
-        int ha = hsum(r_begin - 1), hb = hsum(r_begin);
-        for (int ry = r_begin; ry < r_end; ++ry) {
-          const int hc = hsum(ry + 1);
-          const int y = y0 + ry;
-          const bool in = x_in && y >= 0 && y < H;
-          dst[ry * RW + rx] = in ? static_cast<uint8_t>((ha + hb + hc + 4) / 9) : static_cast<uint8_t>(0);
-          ha = hb;
-          hb = hc;
-        }
-      }
+  for (int c = 0; c < 3; ++c) {
+    for (int i = threadIdx.x; i < RH * RW; i += blockDim.x) {
+      const int y = y0 + i / RW, x = x0 + i % RW;
+      const bool in = y >= 0 && y < H && x >= 0 && x < W;
+      if constexpr (FLOAT) s_buf[0][i] = in ? load_f(img, fmt, b, c, y, x, H, W) : 0.0f;
+      else s_buf[0][i] = in ? static_cast<uint8_t>(load_u8(img, fmt, b, c, y, x, H, W)) : static_cast<uint8_t>(0);
     }
     __syncthreads();
-    cur ^= 1;
+    int cur = 0;
+    for (int p = 1; p <= passes; ++p) {
+      const T* src = s_buf[cur];
+      T* dst = s_buf[cur ^ 1];
+      const int h = RH - 2 * p, w = RW - 2 * p;  // region still exact after this pass
+      if constexpr (FLOAT) {
+        for (int i = threadIdx.x; i < h * w; i += blockDim.x) {
+          const int ry = p + i / w, rx = p + i % w;
+          const int y = y0 + ry, x = x0 + rx;
+          float acc = 0.0f;
+          if (y >= 0 && y < H && x >= 0 && x < W) {
+            const float ninth = 1.0f / 9.0f;
+#pragma unroll
+            for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+              for (int dx = -1; dx <= 1; ++dx) {
+                int yy = y + dy, xx = x + dx;
+                yy = yy < 0 ? -yy : (yy >= H ? 2 * H - 2 - yy : yy);
+                xx = xx < 0 ? -xx : (xx >= W ? 2 * W - 2 - xx : xx);
+                acc = __fadd_rn(acc, __fmul_rn(src[(yy - y0) * RW + (xx - x0)], ninth));
+              }
+          }
+          dst[ry * RW + rx] = acc;
+        }
+      } else {
+        // integer sums are order-free: a thread walks down one column of a row segment keeping the horizontal 3-sums of
+        // the last two rows (3 shared-memory loads and one store per output instead of 9 loads)
+        const int segs = static_cast<int>(blockDim.x) / w;  // 64 <= w <= 86: 2..4 row segments per column
+        const int seg_rows = (h + segs - 1) / segs;
+        const int col = static_cast<int>(threadIdx.x) % w, seg = static_cast<int>(threadIdx.x) / w;
+        const int rx = p + col, r_begin = p + seg * seg_rows, r_end = min(p + h, r_begin + seg_rows);
+        if (seg < segs && r_begin < r_end) {
+          const int x = x0 + rx;
+          const bool x_in = x >= 0 && x < W;
+          auto hsum = [&](int ry) {
+            const uint8_t* r = src + ry * RW + rx;
+            return static_cast<int>(r[-1]) + static_cast<int>(r[0]) + static_cast<int>(r[1]);
+          };
+          int ha = hsum(r_begin - 1), hb = hsum(r_begin);
+          for (int ry = r_begin; ry < r_end; ++ry) {
+            const int hc = hsum(ry + 1);
+            const int y = y0 + ry;
+            const bool in = x_in && y >= 0 && y < H;
+            dst[ry * RW + rx] = in ? static_cast<uint8_t>((ha + hb + hc + 4) / 9) : static_cast<uint8_t>(0);
+            ha = hb;
+            hb = hc;
+          }
+        }
+      }
+      __syncthreads();
+      cur ^= 1;
+    }
+    const T* fin = s_buf[cur];
+    for (int i = threadIdx.x; i < kBlurTH * kBlurTW; i += blockDim.x)
+      s_fin[c * (kBlurTH * kBlurTW) + i] = fin[(i / kBlurTW + passes) * RW + i % kBlurTW + passes];
+    __syncthreads();  // the regions are free for the next channel; s_fin[c] is complete
   }
-  const T* fin = s_buf[cur];
   const size_t hw = static_cast<size_t>(H) * W;
   for (int i = threadIdx.x; i < kBlurTH * kBlurTW; i += blockDim.x) {
-    const int ty = i / kBlurTW, tx = i % kBlurTW;
-    const int y = blockIdx.y * kBlurTH + ty, x = blockIdx.x * kBlurTW + tx;
-    if (y < H && x < W) {
-      const T v = fin[(ty + passes) * RW + tx + passes];
-      float o;
-      if constexpr (FLOAT) o = v; else o = static_cast<float>(v) / 255.0f;
-      out[(static_cast<size_t>(b) * 3 + c) * hw + static_cast<size_t>(y) * W + x] = o;
+    const int y = blockIdx.y * kBlurTH + i / kBlurTW, x = blockIdx.x * kBlurTW + i % kBlurTW;
+    if (y >= H || x >= W) continue;
+    float v[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const T t = s_fin[c * (kBlurTH * kBlurTW) + i];
+      if constexpr (FLOAT) v[c] = t; else v[c] = static_cast<float>(t) / 255.0f;
     }
+    const size_t pix = static_cast<size_t>(y) * W + x;
+    if (out) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) out[(static_cast<size_t>(b) * 3 + c) * hw + pix] = v[c];
+    }
+    if (packed)  // consecutive threads = consecutive pixels of one row: a warp stores 512 contiguous bytes
+      reinterpret_cast<uint4*>(packed)[(static_cast<size_t>(b) * cgs + cg0) * hw + pix] = pack_pixel(v[0], v[1], v[2]);
   }
 }
 
@@ -439,17 +473,7 @@ image_pack_kernel(const __grid_constant__ PerturbDev P, const void* __restrict__
   uint4* dst = reinterpret_cast<uint4*>(out) + (static_cast<size_t>(b) * cgs + cg0) * hw + pix;
   uint4 q[kStemPx];
 #pragma unroll
-  for (int k = 0; k < kStemPx; ++k) {
-    // channels 4-6 carry what bf16 rounding dropped from r, g, b (same weights as channels 0-2): the layer sees the
-    // pixel to ~16 bits instead of 8
-    const __nv_bfloat16 hr = __float2bfloat16(v[k][0]), hg = __float2bfloat16(v[k][1]), hb = __float2bfloat16(v[k][2]);
-    __nv_bfloat162 rg = __halves2bfloat162(hr, hg);
-    __nv_bfloat162 b1 = __halves2bfloat162(hb, __float2bfloat16(1.0f));
-    __nv_bfloat162 lo_rg = __floats2bfloat162_rn(v[k][0] - __bfloat162float(hr), v[k][1] - __bfloat162float(hg));
-    __nv_bfloat162 lo_b0 = __floats2bfloat162_rn(v[k][2] - __bfloat162float(hb), 0.0f);
-    q[k] = make_uint4(*reinterpret_cast<uint32_t*>(&rg), *reinterpret_cast<uint32_t*>(&b1),
-                      *reinterpret_cast<uint32_t*>(&lo_rg), *reinterpret_cast<uint32_t*>(&lo_b0));
-  }
+  for (int k = 0; k < kStemPx; ++k) q[k] = pack_pixel(v[k][0], v[k][1], v[k][2]);
   st_global_256(dst, q[0], q[1]);
   st_global_256(dst + 2, q[2], q[3]);
 }

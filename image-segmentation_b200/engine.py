@@ -114,7 +114,8 @@ class Engine:
         self.max_microbatch = max_microbatch
         h = ctypes.c_void_p()
         archs = {"unet": L.UB_ARCH_UNET, "large": L.UB_ARCH_LARGE_UNET, "clip": L.UB_ARCH_CLIP_UNET,
-                 "clip_prompt": L.UB_ARCH_CLIP_UNET_PROMPT, "autoencoder": L.UB_ARCH_AUTOENCODER}
+                 "clip_prompt": L.UB_ARCH_CLIP_UNET_PROMPT, "autoencoder": L.UB_ARCH_AUTOENCODER,
+                 "encoder": L.UB_ARCH_ENCODER, "skip_decoder": L.UB_ARCH_SKIP_DECODER}
         if arch not in archs:
             raise ValueError(f"unknown arch {arch!r}")
         self.arch = arch
@@ -173,6 +174,36 @@ class Engine:
         out = torch.empty((n, self.n_classes, h, w), device=self.device, dtype=torch.float32)
         self._check(self.lib.ub_forward_prompt(self._handle(), _ptr(x), _ptr(hm), _ptr(cf), _ptr(out), n, h, w,
                                                _stream(self.device)), "ub_forward_prompt")
+        return out
+
+    FEATURE_NAMES = ("x0", "enc1", "enc2", "enc3", "bottleneck")  # models/autoencoder.py:25
+
+    def encoder_forward(self, x: torch.Tensor) -> dict:
+        """Encoder.forward (models/autoencoder.py:17-25): x fp32 [n,3,H,W] -> {"x0","enc1","enc2","enc3","bottleneck"}."""
+        if self.arch != "encoder":
+            raise RuntimeError("encoder_forward needs an engine created with arch='encoder'")
+        x = x.to(self.device, torch.float32).contiguous()
+        n, _, h, w = x.shape
+        shapes = [(32, 0), (64, 1), (128, 2), (256, 3), (512, 3)]
+        feats = [torch.empty((n, c, h >> l, w >> l), device=self.device, dtype=torch.float32) for c, l in shapes]
+        ptrs = (ctypes.c_void_p * len(feats))(*[t.data_ptr() for t in feats])
+        self._check(self.lib.ub_encoder_forward(self._handle(), _ptr(x), n, h, w, ptrs, len(feats), _stream(self.device)),
+                    "ub_encoder_forward")
+        return dict(zip(self.FEATURE_NAMES, feats))
+
+    def skip_decoder_forward(self, features: dict) -> torch.Tensor:
+        """SegmentationDecoderSkip.forward (models/pre_trained.py:17-24): the encoder's dict -> logits fp32 [n,C,H,W]."""
+        if self.arch != "skip_decoder":
+            raise RuntimeError("skip_decoder_forward needs an engine created with arch='skip_decoder'")
+        feats = [features[k].to(self.device, torch.float32).contiguous() for k in self.FEATURE_NAMES]
+        n, _, h, w = feats[0].shape
+        for t, (c, l) in zip(feats, [(32, 0), (64, 1), (128, 2), (256, 3), (512, 3)]):
+            if tuple(t.shape) != (n, c, h >> l, w >> l):
+                raise ValueError(f"feature map of shape {tuple(t.shape)}; expected {(n, c, h >> l, w >> l)}")
+        out = torch.empty((n, self.n_classes, h, w), device=self.device, dtype=torch.float32)
+        ptrs = (ctypes.c_void_p * len(feats))(*[t.data_ptr() for t in feats])
+        self._check(self.lib.ub_skip_decoder_forward(self._handle(), ptrs, len(feats), _ptr(out), n, h, w,
+                                                     _stream(self.device)), "ub_skip_decoder_forward")
         return out
 
     def forward(self, x: torch.Tensor, clip_feats: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -1,11 +1,11 @@
 """Drop-in for the reference's models/autoencoder.py `Encoder` (:5-26): the UNet encoder half as its own
 module, so that checkpoints keyed `encoder.input.*`, `encoder.enc1.*`, ... load unchanged.
 
-In unet-b200 the encoder is a PARAMETER CONTAINER: it computes as part of
-`pre_trained.SegmentationModel.forward`, which runs encoder and decoder in one pass of the sm_100a library
-(the same launches as `UNet`).  The stand-alone `Encoder.forward` of the reference returns the dict of
-feature maps {x0, enc1, enc2, enc3, bottleneck}; those never leave the device pipeline here, so calling it
-on its own raises.
+Inside `pre_trained.SegmentationModel.forward` the encoder and the decoder run as ONE pass of the sm_100a library
+(the same launches as `UNet`, feature maps never leave the device pipeline).  On its own, `Encoder.forward(x)` returns
+the reference's dict of feature maps {x0, enc1, enc2, enc3, bottleneck} (fp32 NCHW) through `ub_encoder_forward`
+(`UB_ARCH_ENCODER`: stem, enc1-3, bottleneck on the tensor-core kernel, then an un-block kernel per map), so callers
+that take encoder features (the reference's pre-training scripts) can switch imports.
 
 `Decoder` (:28-42) and `Autoencoder` (:45-58) — the reconstruction model the encoder is pre-trained with: three
 `ConvBlockUpsample` stages without skips, a 1x1 conv 64 -> out_channels and a sigmoid.  `Autoencoder.forward` runs the
@@ -22,8 +22,11 @@ from .processing_blocks import ConvBlock, ConvBlockDownsample, ConvBlockUpsample
 from .UNet import _B200Net
 
 
-class Encoder(nn.Module):
-    """input 1x1 (3->32), enc1..3 (ConvBlock + 2x2 max-pool), bottleneck 256->512; reference :5-26."""
+class Encoder(_B200Net):
+    """input 1x1 (3->32), enc1..3 (ConvBlock + 2x2 max-pool), bottleneck 256->512; reference :5-26.
+    forward(x) -> {"x0": [B,32,H,W], "enc1": [B,64,H/2,W/2], "enc2": [B,128,H/4,W/4], "enc3": [B,256,H/8,W/8],
+    "bottleneck": [B,512,H/8,W/8]} (:17-25)."""
+    _arch = "encoder"
 
     def __init__(self, in_channels=3):
         super().__init__()
@@ -32,9 +35,16 @@ class Encoder(nn.Module):
         self.enc2 = ConvBlockDownsample(64, 128)
         self.enc3 = ConvBlockDownsample(128, 256)
         self.bottleneck = ConvBlock(256, 512)
+        self._n_classes = 3      # (unused by this half; the context wants a class count)
+        self._engines = {}
 
     def forward(self, x):
-        _no_standalone("Encoder")
+        if self.training:
+            raise RuntimeError("unet-b200 is inference-only (BatchNorm is folded): call model.eval() first")
+        if not x.is_cuda:
+            raise RuntimeError("unet-b200 has no CPU path: inputs must be CUDA tensors")
+        with torch.no_grad():
+            return self.engine(x.device).encoder_forward(x)
 
 
 class Decoder(nn.Module):

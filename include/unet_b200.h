@@ -41,9 +41,13 @@ enum ub_arch {
                              CLIP image embedding (the embedding itself is computed by the caller) */
   UB_ARCH_CLIP_UNET_PROMPT = 3, /* models/prompt_segmentation.py:31-95: ClipUnet plus the PromptEncoder (:16-29) over a
                                   1-channel prompt heat-map and the 1x1 prompt_fusion of the two 512-channel maps */
-  UB_ARCH_AUTOENCODER = 4  /* models/autoencoder.py:5-58: Encoder -> Decoder (three ConvBlockUpsample stages without skips,
+  UB_ARCH_AUTOENCODER = 4, /* models/autoencoder.py:5-58: Encoder -> Decoder (three ConvBlockUpsample stages without skips,
                               1x1 conv 64 -> n_classes channels) -> sigmoid; ub_forward returns the reconstruction
                               (after the sigmoid), the evaluation entries do not apply */
+  UB_ARCH_ENCODER = 5,      /* models/autoencoder.py:5-26 `Encoder` on its own (weights input.*, enc1-3.*, bottleneck.*):
+                              ub_encoder_forward returns its dict of feature maps */
+  UB_ARCH_SKIP_DECODER = 6  /* models/pre_trained.py:7-24 `SegmentationDecoderSkip` on its own (weights dec1-4.*, out.*):
+                              ub_skip_decoder_forward takes that dict and returns the logits */
 };
 
 /* Input image container. */
@@ -141,6 +145,18 @@ int ub_eval_batches_clip(ub_ctx* ctx, const ub_perturb* p, const void* images, i
  * prompt_fusion over their channel concat, dec1-4 and the 1x1 head. */
 int ub_forward_prompt(ub_ctx* ctx, const float* x_nchw, const float* prompt_heatmap, const float* clip_feats,
                       float* logits_nchw, int n, int h, int w, void* stream);
+
+/* The two halves of SegmentationModel as separate modules (models/pre_trained.py:47-56: `decoder(encoder(x))`), for
+ * callers that take the encoder's features (the reference's pre-training scripts do).  All tensors fp32 NCHW on the
+ * device, in the order of Encoder.forward's dict (models/autoencoder.py:17-25):
+ *   feats[0] "x0" [n,32,H,W], feats[1] "enc1" [n,64,H/2,W/2], feats[2] "enc2" [n,128,H/4,W/4],
+ *   feats[3] "enc3" [n,256,H/8,W/8], feats[4] "bottleneck" [n,512,H/8,W/8].
+ * The maps are the library's bf16 activations widened to fp32 (each within one bf16 rounding of the fp32 reference's
+ * layer output); handing them back to ub_skip_decoder_forward loses nothing (bf16 -> fp32 -> bf16 is exact). */
+int ub_encoder_forward(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* const* feats, int n_feats,
+                       void* stream);
+int ub_skip_decoder_forward(ub_ctx* ctx, const float* const* feats, int n_feats, float* logits_nchw, int n, int h,
+                            int w, void* stream);
 
 /* Perturbation alone (the Dataset wrappers' __getitem__ / the nn.Modules' forward): out fp32 [n,3,H,W]. */
 int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,

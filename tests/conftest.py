@@ -61,6 +61,6 @@ def trained(dev):
     m = UNet().eval()
     sd = synthetic.randomize_batchnorm(m.state_dict(), seed=7)
     imgs, masks = synthetic.make_dataset(48, 128, 128, seed=21)
-    sd = util.train_like(sd, synthetic.to_float_nchw(imgs), masks, steps=300, lr=1e-3, batch=8, crop=128)
+    sd = util.train_like(sd, synthetic.to_float_nchw(imgs), masks, steps=400, lr=1e-3, batch=8, crop=128, augment=True)
     m.load_state_dict(sd)
     return m.to(dev), sd

@@ -171,12 +171,11 @@ WRAPPER_FILES = [  # (csv file, class name, slice of WRAPPER_LEVELS[class]) in t
 ]
 
 
-def _oracle_f_batch(cls_name, level, x, dev):
-    """One batch through the oracle's float-space maps, drawing exactly what the reference module draws
-    (models/processing_blocks.py:471-474,557-563,586-592) from the CUDA generator / Python `random`."""
-    b, _, h, w = x.shape
+def _oracle_f_batch(cls_name, level, x, aux):
+    """One batch through the oracle's float-space maps (models/processing_blocks.py:471-474,493-496,516-518,535-539,
+    557-563,586-592), fed the numbers the drop-in module drew for this batch (`aux`: randn / corners / rand)."""
     if cls_name == "GaussianPixelNoise":
-        return po.f_gaussian_noise(x, torch.randn((b, 3, h, w), device=dev).cpu().numpy(), level)
+        return po.f_gaussian_noise(x, aux.cpu().numpy(), level)
     if cls_name == "RepeatedBlur":
         return po.f_box_blur(x, level)
     if cls_name == "ContrastChange":
@@ -184,14 +183,14 @@ def _oracle_f_batch(cls_name, level, x, dev):
     if cls_name == "BrightnessChange":
         return po.f_brightness(x, level)
     if cls_name == "Occlusion":
-        return po.f_occlusion(x, int(level), po.replay_f_occlusion_corners(b, int(level), h, w))
+        return po.f_occlusion(x, int(level), [tuple(int(v) for v in c) for c in aux.cpu().numpy()])
     if cls_name == "SaltAndPepper":
-        return po.f_salt_pepper(x, torch.rand((b, 1, h, w), device=dev).cpu().numpy(), level)
+        return po.f_salt_pepper(x, aux.cpu().numpy(), level)
     raise KeyError(cls_name)
 
 
 def test_testwrapper_robustness_all_79_levels_config1(trained, dev, data, tmp_path, monkeypatch):
-    from image_segmentation_b200 import synthetic
+    from image_segmentation_b200 import runtime, synthetic
     from image_segmentation_b200.customDatasets.datasets import CustomImageDataset
     from image_segmentation_b200.models import processing_blocks as PB
     from image_segmentation_b200.models.model_wrappers import TestWrapper
@@ -217,7 +216,9 @@ def test_testwrapper_robustness_all_79_levels_config1(trained, dev, data, tmp_pa
         csv_rows[(fname, cls_name)] = rows
     assert sum(len(r) for r in csv_rows.values()) == 79
 
-    # second pass with the same seeds: oracle and the drop-in modules draw the same numbers, level by level, batch by batch
+    # second pass with the same seeds: the drop-in modules draw, level by level and batch by batch, the numbers they drew
+    # inside test_robustness (same generators, same order — where the reference draws them); the oracle is fed exactly
+    # those numbers, so inputs can be compared bit for bit and the CSV rows against the oracle's metrics
     random.seed(7); torch.manual_seed(7)
     x_all = synthetic.to_float_nchw(imgs)
     eng = tw.model.engine(dev)
@@ -231,12 +232,14 @@ def test_testwrapper_robustness_all_79_levels_config1(trained, dev, data, tmp_pa
             got = []
             for b0 in range(0, N, 10):
                 xb = x_all[b0:b0 + 10]
-                state = (random.getstate(), torch.cuda.get_rng_state(dev))
-                want.append(_oracle_f_batch(cls_name, level, xb.numpy(), dev))
-                random.setstate(state[0]); torch.cuda.set_rng_state(state[1], dev)
-                got.append(getattr(PB, cls_name)(level)(xb.to(dev).clone()).cpu().numpy())
+                mod = getattr(PB, cls_name)(level)
+                xd = xb.to(dev).clone()
+                spec = mod.spec(xd)                                   # the module's own draws for this batch
+                got.append(runtime.engine_for(dev).perturb(xd, spec).cpu().numpy())   # = what mod.forward computes
+                want.append(_oracle_f_batch(cls_name, level, xb.numpy(), spec.aux))
             want, got = np.concatenate(want), np.concatenate(got)
-            assert np.array_equal(got, want), (cls_name, level)                            # bit-equal network input
+            assert np.array_equal(got, want), (cls_name, level, int((got != want).sum()),  # bit-equal network input
+                                               float(np.abs(got - want).max()))
             o = per_batch_scores(util.oracle_logits_gpu_ieee(sd, torch.from_numpy(want), dev), masks, 10)
             res = eng.eval_batches(torch.from_numpy(want).to(dev), dm, None, 10, want_pred=True)
             pred = res["pred"].cpu()

@@ -31,11 +31,15 @@ def centre_head(sd, x):
 
 
 def train_like(sd, images_f32, masks, steps=150, lr=2e-3, batch=8, crop=128, seed=0, device=None, clip_feats=None,
-               prompts=None, binary=False):
+               prompts=None, binary=False, augment=False):
     """A few Adam steps of cross-entropy on the oracle network (BatchNorm kept in eval mode = fixed
     affine) so the logits get real margins.  Checker-side only; runs on the GPU box's torch (IEEE fp32, conftest.py).
     clip_feats [n,512] / prompts [n,1,H,W]: the ClipUnet / ClipUnetPrompt variants of the oracle network;
-    binary: 1-class head trained with BCE against (mask > 0)."""
+    binary: 1-class head trained with BCE against (mask > 0).
+    augment: photometric jitter per step (contrast x[0.1,1.3], brightness +-0.2, pixel noise up to 18/255) — a network
+    meant for a robustness sweep keeps margins under the sweep's perturbations; without it the extreme levels
+    (contrast 0.1: a nearly black image) sit on thin margins where 0.07 % of flipped pixels move a 16-image IoU by
+    more than 0.1 point."""
     device = device or ("cuda" if torch.cuda.is_available() else "cpu")
     g = torch.Generator().manual_seed(seed)
     params = {k: v.clone().to(device).requires_grad_(v.is_floating_point() and "running" not in k)
@@ -53,6 +57,10 @@ def train_like(sd, images_f32, masks, steps=150, lr=2e-3, batch=8, crop=128, see
         x0 = int(torch.randint(0, w - crop + 1, (1,), generator=g))
         xb = images_f32[idx][:, :, y0:y0 + crop, x0:x0 + crop]
         tb = masks[idx][:, y0:y0 + crop, x0:x0 + crop]
+        if augment:
+            u = torch.rand((3,), generator=g)
+            xb = xb * float(0.1 + 1.2 * u[0]) + float(0.4 * u[1] - 0.2)
+            xb = (xb + torch.randn(xb.shape, generator=g).to(device) * float(u[2]) * (18.0 / 255.0)).clamp(0, 1)
         kw = {}
         if clip_feats is not None:
             kw["clip_feats"] = clip_feats[idx.to(device)]
