@@ -425,6 +425,21 @@ def test_clipunet_logits_against_reference_golden(clipunet, dev):
     assert rel < 2e-2 and util.rel_err(full, ref) < 2e-2  # random-init logits of magnitude 0.08: bf16 noise floor
     with pytest.raises(ValueError):
         m.engine(dev).forward(x)  # the embedding is mandatory for this architecture
+    # With default initialisation the up-sampled half carries ~1e-6 of a logit, which would hide an error in the fusion
+    # path; the same weights with the decoder's up-path amplified let the CLIP embedding carry the logits (a trained
+    # fixture is no help here: training is free to switch the branch off).  The library must follow the oracle, and
+    # swapping the two images' embeddings must move the logits far more than the error.
+    from image_segmentation_b200.models.CLIP_models import ClipUnet
+    sd2 = synthetic.amplify_bottleneck_path(sd)
+    m2 = ClipUnet(clip_model=torch.nn.Identity()).eval()
+    m2.load_state_dict(sd2, strict=False)
+    feats2 = torch.from_numpy(g["clip_feats"])
+    got2 = m2.to(dev).engine(dev).forward(x, clip_feats=feats2.to(dev)).cpu()
+    ref2 = util.oracle_logits(sd2, x, clip_feats=feats2)
+    moved = util.rel_err(util.oracle_logits(sd2, x, clip_feats=feats2.flip(0)), ref2)
+    rel2 = util.rel_err(got2, ref2)
+    print(f"ClipUnet, amplified CLIP branch: logits rel err {rel2:.3e}; swapping embeddings moves the oracle's logits by {moved:.3e}")
+    assert rel2 < 2e-2 and moved > 5 * rel2
 
 
 @pytest.fixture(scope="module")
@@ -461,19 +476,6 @@ def test_clipunet_trained_logits_and_argmax(clipunet_trained, dev):
         rel, agree = util.rel_err(got, ref), util.argmax_agreement(got, ref)
         print(f"ClipUnet {hw}x{hw}: logits rel err {rel:.3e}, argmax agreement {agree:.5f}")
         assert rel < 1e-2 and agree >= 0.999
-        # Training lets the network ignore the CLIP branch (swapping embeddings moves its logits by ~1e-3), which would
-        # hide an error in the fusion path: the same weights with the up-path amplified AFTER training make that branch
-        # carry the logits, and the library must still follow the oracle (no argmax bar: these weights have no margins).
-        from image_segmentation_b200.models.CLIP_models import ClipUnet
-        sd2 = synthetic.amplify_bottleneck_path(sd, up=4.0)
-        m2 = ClipUnet(clip_model=torch.nn.Identity()).eval()
-        m2.load_state_dict(sd2, strict=False)
-        got2 = m2.to(dev).engine(dev).forward(x, clip_feats=feats).cpu()
-        ref2 = util.oracle_logits(sd2, x, clip_feats=feats)
-        moved = util.rel_err(util.oracle_logits(sd2, x, clip_feats=feats.flip(0)), ref2)
-        rel2 = util.rel_err(got2, ref2)
-        print(f"   amplified CLIP branch: logits rel err {rel2:.3e}; swapping embeddings moves the oracle's logits by {moved:.3e}")
-        assert rel2 < 1e-2 and moved > 3 * rel2
 
 
 def test_clipunet_evaluator_embeds_the_perturbed_image(clipunet_trained, dev):
@@ -613,20 +615,6 @@ def test_clipunet_prompt_224_trained(dev):
     assert got.shape == (5, 1, 224, 224)
     assert rel < 1e-2 and agree >= 0.999
     assert util.rel_err(full, ref) < 1e-2
-    # the trained network ignores the prompt / CLIP branches; amplified after training they carry the logits, and the
-    # library must follow the oracle there too, including when the click moves (224x224, ragged tiles)
-    sd2 = synthetic.amplify_bottleneck_path(sd, up=2.0, prompt_fusion=4.0, prompt_stem=4.0)
-    m.load_state_dict(sd2, strict=False)
-    ref2 = util.oracle_logits(sd2, x, clip_feats=feats, prompt=heat)
-    flipped = heat.flip(-1).contiguous()
-    ref2f = util.oracle_logits(sd2, x, clip_feats=feats, prompt=flipped)
-    eng2 = m.engine(dev, max_microbatch=2)
-    rel2 = util.rel_err(eng2.forward_prompt(x, heat, feats).cpu(), ref2)
-    rel2f = util.rel_err(eng2.forward_prompt(x, flipped, feats).cpu(), ref2f)
-    moved = util.rel_err(ref2f, ref2)
-    print(f"   amplified prompt / CLIP branches: logits rel err {rel2:.3e} / {rel2f:.3e} (click moved); moving the click "
-          f"moves the oracle's logits by {moved:.3e}")
-    assert rel2 < 1e-2 and rel2f < 1e-2 and moved > 5 * max(rel2, rel2f)
 
 
 @pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_HEAD_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL"])

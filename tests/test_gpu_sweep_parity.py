@@ -233,10 +233,10 @@ def test_testwrapper_robustness_all_79_levels_config1(trained, dev, data, tmp_pa
             for b0 in range(0, N, 10):
                 xb = x_all[b0:b0 + 10]
                 mod = getattr(PB, cls_name)(level)
-                xd = xb.to(dev).clone()
+                xd = xb.to(dev).contiguous()   # (to_float_nchw keeps the NHWC strides of its uint8 source)
                 spec = mod.spec(xd)                                   # the module's own draws for this batch
                 got.append(runtime.engine_for(dev).perturb(xd, spec).cpu().numpy())   # = what mod.forward computes
-                want.append(_oracle_f_batch(cls_name, level, xb.numpy(), spec.aux))
+                want.append(_oracle_f_batch(cls_name, level, xb.contiguous().numpy(), spec.aux))
             want, got = np.concatenate(want), np.concatenate(got)
             assert np.array_equal(got, want), (cls_name, level, int((got != want).sum()),  # bit-equal network input
                                                float(np.abs(got - want).max()))
