@@ -18,6 +18,7 @@
 #include "../../include/unet_b200.h"
 #include "ub_aux.cuh"
 #include "ub_conv_tc.cuh"
+#include "ub_conv_rs.cuh"
 #include "ub_perturb.cuh"
 
 namespace {
@@ -45,6 +46,7 @@ struct GemmLayer {
   bool is_convt = false;
   __nv_bfloat16* w = nullptr;  // [n_total][ksize*ksize*cin] bf16, BN folded
   __nv_bfloat16* w_kxs = nullptr;  // thin 3x3 layers: [(ky*3+kx)*cout + co][cin] for the kx-stacked kernel
+  __nv_bfloat16* w_rs = nullptr;   // thin 3x3 layers: [(kx*3+(2-ky))*cout + co][cin] for the row-streaming kernel (ub_conv_rs.cuh)
   float* bias = nullptr;       // [cout]
   std::vector<float> h_bias;   // host copy (the HEAD layer passes its 32 biases by value)
 };
@@ -103,6 +105,7 @@ struct ub_ctx {
   bool no_blur_fuse = false;  // UB_NO_BLUR_FUSE=1: blur families run one launch per pass (the path for > 12 passes)
   bool head_no_kxs = false;   // UB_HEAD_NO_KXS=1: only the head layer (dec4.conv.3) runs the 9-tap kernel
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
+  bool no_rs = false;         // UB_NO_RS=1: thin layers run the kx-stacked kernel at every size (no row-streaming kernel)
   bool profiling = false;
   struct ProfRec { int layer; cudaEvent_t a, b; };
   std::vector<ProfRec> prof;
@@ -224,6 +227,16 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
           ks[(static_cast<size_t>(t) * L.cout + co) * L.cin + ci] = packed[co * K + static_cast<size_t>(t) * L.cin + ci];
     if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.w_kxs), ks.size() * 2))) return rc;
     UB_CUDA(ctx, cudaMemcpy(L.w_kxs, ks.data(), ks.size() * 2, cudaMemcpyHostToDevice));
+    // row-streaming operand: for each kx one box of 3*cout rows ordered (ky = 2, 1, 0) = the rows y'-1, y', y'+1 an
+    // input row y' contributes to
+    for (int ky = 0; ky < 3; ++ky)
+      for (int kx = 0; kx < 3; ++kx)
+        for (int co = 0; co < L.cout; ++co)
+          for (int ci = 0; ci < L.cin; ++ci)
+            ks[(static_cast<size_t>(kx * 3 + (2 - ky)) * L.cout + co) * L.cin + ci] =
+                packed[co * K + static_cast<size_t>(ky * 3 + kx) * L.cin + ci];
+    if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.w_rs), ks.size() * 2))) return rc;
+    UB_CUDA(ctx, cudaMemcpy(L.w_rs, ks.data(), ks.size() * 2, cudaMemcpyHostToDevice));
   }
   ctx->layer_by_key[L.key] = static_cast<int>(ctx->layers.size());
   ctx->layers.push_back(L);
@@ -420,6 +433,21 @@ int make_tm_act(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int cin
   if (r != CUDA_SUCCESS) return fail(ctx, UB_ERR_CUDA, "cuTensorMapEncodeTiled(activation) failed: %d", static_cast<int>(r));
   return UB_OK;
 }
+// Row-streaming kernel (ub_conv_rs.cuh): the same blocked tensor seen as {8*W, H/4 rows, 4 quarters, cin/8 planes, B};
+// one box = {32 pixels, 1 row, 4 quarters, bk/8 planes, 1 image}.
+int make_tm_act_rs(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int cin, int cgs_total, int W, int H, int B, int bk) {
+  const cuuint64_t hq = static_cast<cuuint64_t>(H / 4);
+  const cuuint64_t dims[5] = {static_cast<cuuint64_t>(8) * W, hq, 4, static_cast<cuuint64_t>(cin / 8), static_cast<cuuint64_t>(B)};
+  const cuuint64_t strides[4] = {static_cast<cuuint64_t>(W) * 16, hq * W * 16, static_cast<cuuint64_t>(H) * W * 16,
+                                 static_cast<cuuint64_t>(cgs_total) * H * W * 16};
+  const cuuint32_t box[5] = {256, 1, 4, static_cast<cuuint32_t>(bk / 8), 1};
+  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  const CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<__nv_bfloat16*>(base), dims, strides,
+                                 box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ctx, UB_ERR_CUDA, "cuTensorMapEncodeTiled(row-streaming activation) failed: %d", static_cast<int>(r));
+  return UB_OK;
+}
 int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total, int n_total, int block_n, int bk) {
   const cuuint64_t dims[2] = {static_cast<cuuint64_t>(k_total), static_cast<cuuint64_t>(n_total)};
   const cuuint64_t strides[1] = {static_cast<cuuint64_t>(k_total) * 2};
@@ -450,7 +478,15 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   int rc;
   const int tw = pick_tw(ctx, L, mode);
   cp->tw = tw;
-  if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin_src ? L.cin_src : L.cin, src_cgs, W, H, B, L.ksize, L.bk, tw))) return rc;
+  // the thin layers at the larger sizes: row-streaming kernel (a task is H/4 + 2 row tiles: worthwhile from 8 rows per
+  // stream; below that, and with UB_NO_RS=1, the kx-stacked kernel)
+  const bool rs = ub::is_kxs(tw) && !ctx->no_rs && L.w_rs && H % 8 == 0 && H >= 32 && W >= 32 && (L.cout == 32 || L.cout == 64) &&
+                  ((L.cout == 32 && (L.bk == 32 || L.bk == 64)) || (L.cout == 64 && L.bk == 64));
+  cp->rs = rs ? 1 : 0;
+  cp->hq = H / 4;
+  if (rs) {
+    if ((rc = make_tm_act_rs(ctx, &cp->tmA, src, L.cin_src ? L.cin_src : L.cin, src_cgs, W, H, B, L.bk))) return rc;
+  } else if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin_src ? L.cin_src : L.cin, src_cgs, W, H, B, L.ksize, L.bk, tw))) return rc;
   // CTA pairs (cta_group::2) for the wide layers whose weights cannot stay resident in shared memory
   const size_t w_tile_bytes = static_cast<size_t>(L.ksize) * L.ksize * L.cin * L.block_n * 2;
   const bool resident = w_tile_bytes + 2 * 24576 <= 220 * 1024;  // mirrors choose_pipeline's weight-stationary test
@@ -463,7 +499,9 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
     cp->cg2 = 1;
     cp->pairq = 1;
   }
-  if (ub::is_kxs(tw)) {
+  if (rs) {
+    if ((rc = make_tm_w(ctx, &cp->tmB, L.w_rs, L.cin, 9 * L.cout, 3 * L.cout, L.bk))) return rc;
+  } else if (ub::is_kxs(tw)) {
     if ((rc = make_tm_w(ctx, &cp->tmB, L.w_kxs, L.cin, 9 * L.cout, 3 * L.cout, L.bk))) return rc;
   } else {
     if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, cp->cg2 ? L.block_n / 2 : L.block_n, L.bk))) return rc;
@@ -597,6 +635,45 @@ int launch_pair(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   return launch_kernel<N, 64, KS, false, 8, true>(ctx, cp, grid, smem, st);
 }
 
+// Row-streaming launch: a task = (image, 30-column band); persistent CTAs walk their tasks row by row.
+template <int COUT, int BK>
+int launch_rs(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
+  using Cfg = ub::RsCfg<COUT, BK>;
+  ConvParams cp = cp_in;
+  const int bands = (cp.W + ub::kRsOut - 1) / ub::kRsOut;
+  const int tasks = cp.B * bands;
+  const int grid = tasks < ctx->num_sms ? tasks : ctx->num_sms;
+  const int w_bytes = 3 * (cp.cin / BK) * Cfg::B_STAGE_BYTES;
+  int sa = (Cfg::OPERAND_BUDGET - w_bytes) / Cfg::A_STAGE_BYTES;
+  if (sa > ub::kMaxSA) sa = ub::kMaxSA;
+  if (sa < 2) return fail(ctx, UB_ERR_UNSUPPORTED, "row-streaming kernel: the layer's weights (%d bytes) leave no room for 2 A stages", w_bytes);
+  cp.sa = sa;
+  const int smem = Cfg::TAIL_BYTES + sa * Cfg::A_STAGE_BYTES + w_bytes + 1024;
+  const void* fn = reinterpret_cast<const void*>(&ub::conv_rs_kernel<COUT, BK>);
+  if (!ctx->smem_opt_in.count(fn)) {
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_rs_kernel<COUT, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, ub::kSmemLimit));
+    ctx->smem_opt_in.insert(fn);
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(ub::rs_threads(COUT));
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  int na = 0;
+  if (ctx->use_pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_rs_kernel<COUT, BK>, cp));
+  ctx->launches++;
+  return UB_OK;
+}
+
 template <int N, int BK>
 int launch_ks(ub_ctx* ctx, const ConvParams& cp, cudaStream_t st) {
   if (cp.ksize == 3) return launch_inst<N, BK, 3>(ctx, cp, st);
@@ -625,6 +702,12 @@ int launch_gemm(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStre
 
 int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStream_t st) {
   if (cp.mode == ub::EPI_HEAD && cp.cout != 32) return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs 32 channels");
+  if (cp.rs) {  // thin 3x3 layers at the larger sizes: ky-stacked, row-streaming
+    if (cp.cout == 64 && bk == 64) return launch_rs<64, 64>(ctx, cp, st);
+    if (cp.cout == 32 && bk == 64) return launch_rs<32, 64>(ctx, cp, st);
+    if (cp.cout == 32 && bk == 32) return launch_rs<32, 32>(ctx, cp, st);
+    return fail(ctx, UB_ERR_UNSUPPORTED, "no row-streaming kernel for cout=%d BK=%d", cp.cout, bk);
+  }
   if (ub::is_kxs(cp.tw)) {  // thin 3x3 layers, N = 3 * cout
     if (bk == 32 && cp.tw == 32 && cp.cout == 64) return launch_inst<192, 32, 3, 32>(ctx, cp, st);
     if (bk == 32 && cp.tw == 32 && cp.cout == 32) return launch_inst<96, 32, 3, 32>(ctx, cp, st);
@@ -1090,6 +1173,7 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   { const char* e = getenv("UB_NO_BLUR_FUSE"); ctx->no_blur_fuse = e && e[0] == '1'; }
   { const char* e = getenv("UB_NO_STEM_FOLD"); ctx->stem_fold = !(e && e[0] == '1'); }
   { const char* e = getenv("UB_DBG"); ctx->dbg = e ? atoi(e) : 0; }
+  { const char* e = getenv("UB_NO_RS"); ctx->no_rs = e && e[0] == '1'; }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();

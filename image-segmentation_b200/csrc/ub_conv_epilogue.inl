@@ -13,57 +13,10 @@
   const int et = (threadIdx.x - 128) & 127;    // 0..127 within the group
   unsigned long long* s_cm = s_cm_all + grp * (kMaxClasses * kMaxClasses);
   double* s_dice = s_dice_all + grp * (2 * kMaxClasses);
-  int cur_batch = -1;
-  // HEAD: every thread counts its own pixels in registers (cell = target*C + prediction, and the
-  // soft-Dice partial sums); they are reduced (warp shuffle -> shared memory -> global atomics) only
-  // when the reference batch changes, every kFlushTiles tiles, and once at the end.
-  constexpr int kCells = kMaxClasses * kMaxClasses;
-  constexpr int kFlushTiles = 250;  // < 255: the packed 8-bit count fields cannot overflow between flushes
-  // counts of target class t live in pk[t]: kMaxClasses 8-bit fields indexed by the prediction (4 registers
-  // instead of 16, one shift and kMaxClasses predicated adds per pixel)
-  static_assert(kMaxClasses * 8 <= 32, "packed count fields");
-  uint32_t pk[kMaxClasses];
-  float dsum[2 * kMaxClasses];
-#pragma unroll
-  for (int i = 0; i < kMaxClasses; ++i) pk[i] = 0u;
-#pragma unroll
-  for (int i = 0; i < 2 * kMaxClasses; ++i) dsum[i] = 0.0f;
-  int tiles_since_flush = 0;
-  auto flush_counts = [&](int batch) {
-    const int C = p.n_classes;
-#pragma unroll
-    for (int i = 0; i < kCells; ++i) {
-      uint32_t v = (pk[i / kMaxClasses] >> (8 * (i % kMaxClasses))) & 255u;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0 && v) atomicAdd(&s_cm[i], static_cast<unsigned long long>(v));
-    }
-#pragma unroll
-    for (int i = 0; i < kMaxClasses; ++i) pk[i] = 0u;
-    if (p.dice) {
-#pragma unroll
-      for (int i = 0; i < 2 * kMaxClasses; ++i) {
-        float v = dsum[i];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0) atomicAdd(&s_dice[i], static_cast<double>(v));
-        dsum[i] = 0.0f;
-      }
-    }
-    epi_bar_sync(grp);  // all four warps of the group have added their share
-    if (et < C * C) {
-      const int tc = et / C, pc = et % C;
-      const unsigned long long v = atomicExch(&s_cm[tc * kMaxClasses + pc], 0ull);
-      if (v) atomicAdd(&p.cm[static_cast<size_t>(batch) * C * C + et], v);
-    } else if (p.dice && et >= 32 && et < 32 + 2 * C) {
-      const int i = et - 32;
-      const double v = s_dice[i];
-      s_dice[i] = 0.0;
-      atomicAdd(&p.dice[(static_cast<size_t>(batch) * C + (i >> 1)) * 3 + (i & 1)], v);
-    }
-    epi_bar_sync(grp);  // shared counters are zero again before the next batch is added
-    tiles_since_flush = 0;
-  };
+  // HEAD: every thread counts its own pixels in registers (ub_head.cuh); they are reduced (warp shuffle -> shared
+  // memory -> global atomics) only when the reference batch changes, every kHeadFlushTiles tiles, and once at the end.
+  HeadState hs;
+  hs.init();
 
   int it = grp;
   TileIter ti = tile_iter(t_first + grp * t_step, kEpiGroups * t_step);
@@ -86,18 +39,9 @@
       // counts accumulate in registers across tiles and go to HBM only when the reference batch
       // changes (and once at the end): <= C*C global atomics per batch per CTA instead of per tile
       while (b >= batch_end) { ++batch_now; batch_end += p.ref_batch; }
-      const int batch = batch_now;
-      if (batch != cur_batch || tiles_since_flush >= kFlushTiles) {
-        if (cur_batch >= 0) flush_counts(cur_batch);
-        cur_batch = batch;
-      }
-      ++tiles_since_flush;
+      head_begin_tile(p, hs, batch_now, grp, et, lane, s_cm, s_dice);
       // the target is fetched before waiting for the accumulator so its latency hides behind the MMAs
-      if (inb) {
-        const size_t tp = (static_cast<size_t>(b) * p.H + y) * p.W + x;
-        tgt_pre = p.target_fmt == 1 ? static_cast<int>(reinterpret_cast<const uint8_t*>(p.targets)[tp])
-                                    : static_cast<int>(reinterpret_cast<const long long*>(p.targets)[tp]);
-      }
+      if (inb) tgt_pre = head_load_target(p, b, y, x);
     }
 
     mbar_wait(&t_full[acc], use & 1u);
@@ -155,98 +99,8 @@
         release_acc();
       }
       // the per-pixel head, specialised for the usual 3 classes (NC = 0: class count known at run time only)
-      auto head_pixel = [&](auto nc_tag) {
-        constexpr int NC = decltype(nc_tag)::value;
-        const int C = NC ? NC : p.n_classes;
-      float z[kMaxClasses];
-#pragma unroll
-        for (int c = 0; c < kMaxClasses; ++c) z[c] = (c < C) ? p.head_b[c] : -INFINITY;
-        // packed fp32x2 arithmetic (two IEEE operations per issue slot): even and odd input channels accumulate
-        // separately and are added at the end
-        float2 z2[kMaxClasses];
-#pragma unroll
-        for (int c = 0; c < kMaxClasses; ++c) z2[c] = make_float2(z[c], 0.0f);
-#pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          float2 v = __fadd2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])),
-                                make_float2(p.bias32[j], p.bias32[j + 1]));
-          if (p.relu) { v.x = fmaxf(v.x, 0.0f); v.y = fmaxf(v.y, 0.0f); }
-#pragma unroll
-          for (int c = 0; c < kMaxClasses; ++c)
-            if (c < C) z2[c] = __ffma2_rn(make_float2(p.head_w[c * 32 + j], p.head_w[c * 32 + j + 1]), v, z2[c]);
-        }
-#pragma unroll
-        for (int c = 0; c < kMaxClasses; ++c)
-          if (c < C) z[c] = z2[c].x + z2[c].y;
-        // argmax(softmax(z)) with the first index winning ties (models/losses.py:48,50).  When the largest logit
-        // leads the runner-up by more than 1e-4 the softmax cannot change the order: e_best = expf(0) = 1 exactly and
-        // every other e_c <= expf(-1e-4) < 1 - 9e-5, far more than the rounding of the division by the common sum, so
-        // pr_best > pr_c strictly and the prediction is the (unique) argmax of z.  Only near-ties, non-finite logits
-        // and the soft-Dice sums (which need the probabilities) evaluate the softmax itself.
-        float zmax = z[0];
-#pragma unroll
-        for (int c = 1; c < kMaxClasses; ++c) zmax = fmaxf(zmax, z[c]);
-        int pred = 0;
-        float second = -INFINITY;
-        if constexpr (NC == 3) {
-          const float m12 = fmaxf(z[1], z[2]), m02 = fmaxf(z[0], z[2]), m01 = fmaxf(z[0], z[1]);
-          pred = (z[0] == zmax) ? 0 : ((z[1] == zmax) ? 1 : 2);
-          second = (pred == 0) ? m12 : ((pred == 1) ? m02 : m01);
-        } else {
-#pragma unroll
-          for (int c = kMaxClasses - 1; c >= 0; --c) if (c < C && z[c] == zmax) pred = c;
-#pragma unroll
-          for (int c = 0; c < kMaxClasses; ++c) if (c < C && c != pred) second = fmaxf(second, z[c]);
-        }
-        const float gap = zmax - second;
-        const bool decisive = (gap > 1e-4f) && (gap <= 3.0e38f) && !(p.dbg & 8);  // false for NaN / infinite logits
-        float pr[kMaxClasses];
-        if (!decisive || p.dice) {
-          float psum = 0.0f;
-#pragma unroll
-          for (int c = 0; c < kMaxClasses; ++c) { pr[c] = (c < C) ? expf(z[c] - zmax) : 0.0f; psum += pr[c]; }
-          int pred_s = 0;
-          float best = -1.0f;
-#pragma unroll
-          for (int c = 0; c < kMaxClasses; ++c) {
-            pr[c] = pr[c] / psum;
-            if (c < C && pr[c] > best) { best = pr[c]; pred_s = c; }
-          }
-          pred = pred_s;
-        }
-        const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
-        if (inb) {
-          if (p.pred_out) p.pred_out[pix] = static_cast<uint8_t>(pred);
-          if (p.logits_out) {
-#pragma unroll
-            for (int c = 0; c < kMaxClasses; ++c)
-              if (c < C) p.logits_out[((static_cast<size_t>(b) * C + c) * p.H + y) * p.W + x] = z[c];
-          }
-        }
-        if (p.targets) {
-          const int tgt = (tgt_pre >= 0 && tgt_pre < C) ? tgt_pre : -1;
-          const uint32_t inc = 1u << (8 * pred);
-#pragma unroll
-          for (int tc = 0; tc < kMaxClasses; ++tc)
-            if (tc < C) pk[tc] += (tgt == tc) ? inc : 0u;
-          if (p.dice) {
-            // smp DiceLoss(from_logits=True) applies softmax again to the softmax output (losses.py:100)
-            float q[kMaxClasses], qmax = pr[0], qsum = 0.0f;
-#pragma unroll
-            for (int c = 1; c < kMaxClasses; ++c) if (c < C) qmax = fmaxf(qmax, pr[c]);
-#pragma unroll
-            for (int c = 0; c < kMaxClasses; ++c) { q[c] = (c < C) ? expf(pr[c] - qmax) : 0.0f; qsum += q[c]; }
-#pragma unroll
-            for (int c = 0; c < kMaxClasses; ++c) {
-              const float pc = (inb && c < C) ? q[c] / qsum : 0.0f;
-              dsum[2 * c + 0] += (tgt == c) ? pc : 0.0f;
-              dsum[2 * c + 1] += pc;
-            }
-          }
-        }
-      };
-      if (p.n_classes == 3) head_pixel(std::integral_constant<int, 3>{});
-      else head_pixel(std::integral_constant<int, 0>{});
+      if (p.n_classes == 3) head_pixel<3>(p, hs, r, inb, b, y, x, tgt_pre);
+      else head_pixel<0>(p, hs, r, inb, b, y, x, tgt_pre);
     } else {
       // ---- STORE / POOL / CONVT: bias (+ReLU) -> bf16 -> channel-blocked global store, 32 channels at a time
       // geometry of this thread's output pixel (fixed per tile)
@@ -402,5 +256,5 @@
       }
     }
   }
-  if (kHead && p.mode == EPI_HEAD && p.targets && cur_batch >= 0) flush_counts(cur_batch);
+  if (kHead && p.mode == EPI_HEAD && p.targets && hs.cur_batch >= 0) head_flush(p, hs, hs.cur_batch, grp, et, lane, s_cm, s_dice);
 }

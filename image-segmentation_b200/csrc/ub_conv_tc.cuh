@@ -42,6 +42,7 @@
 // warps.  kAcc TMEM accumulators (up to 4): the MMA warp runs ahead of the epilogues by kAcc tiles.
 #pragma once
 #include "ub_ptx.cuh"
+#include "ub_head.cuh"
 
 namespace ub {
 
@@ -49,7 +50,7 @@ enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_CONVT = 2, EPI_HEAD = 3 };
 
 constexpr int kTileM = 128;
 constexpr int kMaxEpiGroups = 4;
-constexpr int kMaxClasses = 4;
+constexpr int kMaxClasses = kHeadMaxClasses;
 // tile geometry: TW = 8 is the standard 16-row x 8-column tile; TW = 16 / 32 are the kx-stacked variants
 __host__ __device__ constexpr bool is_kxs(int tw) { return tw != 8; }
 __host__ __device__ constexpr int tile_rows(int tw) { return kTileM / tw; }
@@ -98,6 +99,8 @@ struct ConvParams {
   int cg2; // 1 = CTA-pair kernel (host: tmB box holds N/2 rows, even grid, cluster launch)
   int tw;  // tile width chosen by the host (8 standard, 16/32 kx-stacked); the kernel has it as a template parameter
   int k_steps;  // MMAs (16 channels each) issued per tap and chunk; fewer than BK/16 when the tail of the chunk is zero padding
+  int rs;  // 1 = row-streaming kernel (ub_conv_rs.cuh): tmA is the 5-D map over (pixel, row in quarter, quarter, plane, image)
+  int hq;  // row-streaming: rows per stream = H / 4
   int sa;  // A stages (activation boxes)
   int sb;  // B stages when streaming weights; unused when the kernel is the WS instantiation
 };

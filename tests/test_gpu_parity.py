@@ -38,7 +38,9 @@ def test_every_conv_layer(base_model, dev):
         if key.endswith(".up"):
             continue
         wf, bf = folded(sd, key)
-        for (n, h, w) in [(2, 24, 40), (1, 64, 64), (3, 16, 8)]:  # ragged tiles, full tiles, odd tile count (CTA-pair padding)
+        # ragged tiles, full tiles, odd tile count (CTA-pair padding), and two sizes the thin layers run row-streaming at
+        # (H >= 32): 3 bands with a 12-pixel last one and 10 rows per stream; more tasks than SMs (5 x 64 x 900: 150)
+        for (n, h, w) in [(2, 24, 40), (1, 64, 64), (3, 16, 8), (2, 40, 72)] + ([(5, 64, 900)] if wf.shape[0] <= 64 and wf.shape[1] <= 64 else []):
             x = torch.randn((n, wf.shape[1], h, w), generator=g)
             ref = F.relu(F.conv2d(util.bf16_round(x).to(dev), util.bf16_round(wf).to(dev), bf.to(dev), padding=1))
             for pool in (False, True):
@@ -617,7 +619,7 @@ def test_clipunet_prompt_224_trained(dev):
     assert util.rel_err(full, ref) < 1e-2
 
 
-@pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_HEAD_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL"])
+@pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_NO_RS", "UB_HEAD_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL"])
 def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     """The diagnostic switches select other kernels for the same layers (streamed weights, 9-tap thin layers, single
     CTAs, plain launches); they must stay correct: same logits within bf16 accumulation-order noise, same
