@@ -433,21 +433,6 @@ int make_tm_act(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int cin
   if (r != CUDA_SUCCESS) return fail(ctx, UB_ERR_CUDA, "cuTensorMapEncodeTiled(activation) failed: %d", static_cast<int>(r));
   return UB_OK;
 }
-// Row-streaming kernel (ub_conv_rs.cuh): the same blocked tensor seen as {8*W, H/4 rows, 4 quarters, cin/8 planes, B};
-// one box = {32 pixels, 1 row, 4 quarters, bk/8 planes, 1 image}.
-int make_tm_act_rs(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int cin, int cgs_total, int W, int H, int B, int bk) {
-  const cuuint64_t hq = static_cast<cuuint64_t>(H / 4);
-  const cuuint64_t dims[5] = {static_cast<cuuint64_t>(8) * W, hq, 4, static_cast<cuuint64_t>(cin / 8), static_cast<cuuint64_t>(B)};
-  const cuuint64_t strides[4] = {static_cast<cuuint64_t>(W) * 16, hq * W * 16, static_cast<cuuint64_t>(H) * W * 16,
-                                 static_cast<cuuint64_t>(cgs_total) * H * W * 16};
-  const cuuint32_t box[5] = {256, 1, 4, static_cast<cuuint32_t>(bk / 8), 1};
-  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-  const CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<__nv_bfloat16*>(base), dims, strides,
-                                 box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                 CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return fail(ctx, UB_ERR_CUDA, "cuTensorMapEncodeTiled(row-streaming activation) failed: %d", static_cast<int>(r));
-  return UB_OK;
-}
 int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total, int n_total, int block_n, int bk) {
   const cuuint64_t dims[2] = {static_cast<cuuint64_t>(k_total), static_cast<cuuint64_t>(n_total)};
   const cuuint64_t strides[1] = {static_cast<cuuint64_t>(k_total) * 2};
@@ -484,8 +469,10 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
                   ((L.cout == 32 && (L.bk == 32 || L.bk == 64)) || (L.cout == 64 && L.bk == 64));
   cp->rs = rs ? 1 : 0;
   cp->hq = H / 4;
-  if (rs) {
-    if ((rc = make_tm_act_rs(ctx, &cp->tmA, src, L.cin_src ? L.cin_src : L.cin, src_cgs, W, H, B, L.bk))) return rc;
+  if (rs) {  // the row-streaming kernel reads the blocked tensor itself (cp.async); no activation tensor map
+    cp->a_src = src;
+    cp->a_cgs = src_cgs;
+    cp->a_planes = (L.cin_src ? L.cin_src : L.cin) / 8;
   } else if ((rc = make_tm_act(ctx, &cp->tmA, src, L.cin_src ? L.cin_src : L.cin, src_cgs, W, H, B, L.ksize, L.bk, tw))) return rc;
   // CTA pairs (cta_group::2) for the wide layers whose weights cannot stay resident in shared memory
   const size_t w_tile_bytes = static_cast<size_t>(L.ksize) * L.ksize * L.cin * L.block_n * 2;

@@ -27,11 +27,19 @@
 // Geometry.  A task = (image b, band j): output columns [30j, 30j+30), all H rows.  The 128 accumulator lanes are 4
 // streams x 32 pixels: stream q walks rows [q*H/4, (q+1)*H/4) — lanes 0 and 31 of a stream are halo columns (their
 // results are discarded), and each stream reads one extra row above and below its quarter (tiles t = 0 and H/4+1), so
-// a task is H/4 + 2 tiles.  ONE 5-D TMA box per (tile, channel chunk): {32 px * 8 ch, 1 row, 4 quarters, BK/8 planes, 1
-// image} lands as [plane][stream][32 px][8 ch] — the no-swizzle K-major UMMA layout with LBO = 2048 B (planes) and
-// SBO = 128 B (8-pixel groups, uniform across the streams).  Image borders are TMA zero fill: x = -1 / x >= W through
-// the first coordinate; the row above stream 0 and below stream 3 through the quarter coordinate (tile 0 starts the box
-// at quarter -1 with row H/4-1, the last tile at quarter +1 with row 0).
+// a task is H/4 + 2 tiles.  A stage holds [plane][stream][32 px][8 ch] — the no-swizzle K-major UMMA layout with
+// LBO = 2048 B (planes) and SBO = 128 B (8-pixel groups, uniform across the streams).
+//
+// Operand fill.  The first version used ONE 5-D TMA box per (tile, chunk) — {32 px * 8 ch, 1 row, 4 quarters, BK/8 planes}
+// — and measured no faster than the kx-stacked kernel: both sat at ~33-48 cycles per 512-byte box row (enc1.conv.3:
+// 1,600 cycles per row tile against 1,170 of MMA time; the head layer 930 against 380), i.e. the TMA unit's per-row
+// cost on these short, 16-byte-misaligned rows bounds the thin layers, not the tensor pipe or the epilogue
+// (profiles/r02_call5_*).  The A operand is therefore filled by two producer warps with cp.async (LDGSTS.128: one warp
+// instruction = the 32 pixels x 16 bytes of one (plane, stream) row, 512 contiguous bytes of the blocked tensor),
+// completion signalled on the stage's mbarrier (cp.async.mbarrier.arrive.noinc), zero fill (src-size 0) for x = -1,
+// x >= W, the row above stream 0 / below stream 3 and channel planes the view does not have.  The MMA thread orders
+// those generic-proxy writes before its async-proxy reads with fence.proxy.async after the barrier wait.  The
+// resident weights are still TMA boxes (loaded once per CTA).
 //
 // Global counters.  Each CTA numbers its tiles tau = 0, 1, ... across its tasks; rows sigma = tau - 1 become complete in
 // the same order; the two rows per task that are not outputs (the halo rows rho = 0 and rho = H/4+1) flow through the
@@ -77,13 +85,14 @@ struct RsCfg {
   static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;
 };
 
-__device__ __forceinline__ void tma_load_5d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
-                                            int c3, int c4) {
-  asm volatile(
-      "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%2, %3, %4, %5, %6}], [%7];" ::"r"(smem_u32(smem_dst)),
-      "l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4), "r"(smem_u32(bar))
-      : "memory");
+// 16-byte asynchronous copy global -> shared, bypassing L1; `ok` false: nothing is read and 16 zero bytes are written
+__device__ __forceinline__ void cp_async_16_zfill(uint32_t smem_dst, const void* gsrc, bool ok) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst), "l"(gsrc), "r"(ok ? 16 : 0) : "memory");
+}
+// the executing thread's arrival on `bar` is deferred until all of its earlier cp.async copies have completed; .noinc:
+// the arrival counts against the barrier's initial count (64 = every producer thread arrives once per stage)
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 // D[tmem] (+)= A * B with a run-time accumulate flag (the window's fresh block)
@@ -133,12 +142,9 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
   for (int i = threadIdx.x; i < COUT; i += kRsThreads) s_bias[i] = p.bias[i];
   if (threadIdx.x < G * kMaxClasses * kMaxClasses) s_cm_all[threadIdx.x] = 0ull;
   if (threadIdx.x < G * kMaxClasses * 2) s_dice_all[threadIdx.x] = 0.0;
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.tmA);
-    tma_prefetch_desc(&p.tmB);
-  }
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&p.tmB);
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < kMaxSA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < kMaxSA; ++i) { mbar_init(&a_full[i], 64); mbar_init(&a_empty[i], 1); }  // 64 = the two producer warps
     for (int i = 0; i < kRsMaxBlocks; ++i) { mbar_init(&blk_full[i], 1); mbar_init(&blk_empty[i], 128); }
     mbar_init(w_full, 1);
     fence_barrier_init();
@@ -150,40 +156,51 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
   const uint32_t tmem_base = *s_tmem;
   if (!(p.dbg & 16)) pdl_launch_dependents();  // see conv_tc_kernel
 
-  if (warp == 0) {
-    // ================= TMA producer =================
-    const bool leader = elect_one();
-    const int n_w = 3 * k_chunks;
-    if (leader) {  // weights are constants of the layer: loaded before the wait on the previous kernel
-      mbar_arrive_expect_tx(w_full, static_cast<uint32_t>(n_w * Cfg::B_STAGE_BYTES));
+  if (warp == 0 || warp == 3) {
+    // ================= producers: warp 0 (also loads the weights) and warp 3 fill the A stages with cp.async =================
+    if (warp == 0) {
+      const bool leader = elect_one();
+      const int n_w = 3 * k_chunks;
+      if (leader) {  // weights are constants of the layer: loaded before the wait on the previous kernel
+        mbar_arrive_expect_tx(w_full, static_cast<uint32_t>(n_w * Cfg::B_STAGE_BYTES));
 #pragma unroll 1
-      for (int j = 0; j < n_w; ++j) {
-        const int c = j / 3, kx = j % 3;
-        tma_load_2d(b_res + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, c * BK, kx * Cfg::N3);
+        for (int j = 0; j < n_w; ++j) {
+          const int c = j / 3, kx = j % 3;
+          tma_load_2d(b_res + j * Cfg::B_STAGE_BYTES, &p.tmB, w_full, c * BK, kx * Cfg::N3);
+        }
       }
+      __syncwarp();
     }
-    __syncwarp();
     pdl_wait_prior_grid();  // activations of the previous layer are complete and visible from here on
+    const int half = warp == 0 ? 0 : 1;      // which rows of a stage this warp copies
+    constexpr int kRows = 4 * (BK / 8);      // (plane, stream) rows of one stage, 512 bytes each
+    const size_t row_stride = static_cast<size_t>(p.W) * 8;            // elements per image row of one plane
+    const size_t plane_stride = row_stride * p.H;
+    const size_t image_stride = plane_stride * p.a_cgs;
     int sa = 0;
     uint32_t pa = 0;
 #pragma unroll 1
     for (int task = blockIdx.x; task < n_tasks; task += gridDim.x) {
       const int b = task / bands, j = task - b * bands;
-      const int x_elem = (j * kRsOut - 1) * 8;  // first lane = the band's left halo column (x = -1 for band 0: zero fill)
+      const int x = j * kRsOut - 1 + lane;   // this lane's pixel: lane 0 / 31 are the band's halo columns
+      const bool x_ok = x >= 0 && x < p.W;
+      const __nv_bfloat16* img = p.a_src + image_stride * b + static_cast<size_t>(x_ok ? x : 0) * 8;
 #pragma unroll 1
       for (int t = 0; t < tpt; ++t) {
-        // stream q reads image row q*hq - 1 + t: as (row, quarter) = (hq-1, q-1) for the row above the quarter, (t-1, q)
-        // inside it, (0, q+1) for the row below; quarter -1 / 4 are outside the tensor map: zero fill = the conv's padding
-        const int row = t == 0 ? hq - 1 : (t == tpt - 1 ? 0 : t - 1);
-        const int q0 = t == 0 ? -1 : (t == tpt - 1 ? 1 : 0);
 #pragma unroll 1
         for (int c = 0; c < k_chunks; ++c) {
           mbar_wait(&a_empty[sa], pa ^ 1u);
-          if (leader) {
-            mbar_arrive_expect_tx(&a_full[sa], static_cast<uint32_t>(Cfg::A_BOX_BYTES));
-            tma_load_5d(a_ring + sa * Cfg::A_STAGE_BYTES, &p.tmA, &a_full[sa], x_elem, row, q0, c * (BK / 8), b);
+          const uint32_t dst0 = smem_u32(a_ring + sa * Cfg::A_STAGE_BYTES) + static_cast<uint32_t>(lane) * 16u;
+#pragma unroll
+          for (int r = 0; r < kRows / 2; ++r) {
+            const int row = 2 * r + half, pl = row >> 2, q = row & 3;
+            const int y = q * hq - 1 + t;          // stream q reads image row q*hq - 1 + t (one above .. one below its quarter)
+            const int plane = c * (BK / 8) + pl;
+            const bool ok = x_ok && y >= 0 && y < p.H && plane < p.a_planes;
+            const __nv_bfloat16* src = img + plane_stride * (ok ? plane : 0) + row_stride * (ok ? y : 0);
+            cp_async_16_zfill(dst0 + static_cast<uint32_t>(row) * 512u, src, ok);
           }
-          __syncwarp();
+          cp_async_mbar_arrive_noinc(&a_full[sa]);   // arrives once this thread's copies above have landed
           if (++sa == p.sa) { sa = 0; pa ^= 1u; }
         }
       }
@@ -221,6 +238,7 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
 #pragma unroll 1
       for (int c = 0; c < k_chunks; ++c) {
         mbar_wait(&a_full[sa], pa);
+        fence_proxy_async();  // the stage was written through the generic proxy (cp.async); the MMA reads it through the async proxy
         tc_fence_after();
         if (leader) {
           const uint32_t a_stage = a_lo_ring + static_cast<uint32_t>(sa) * A_STAGE_U;

@@ -101,6 +101,10 @@ struct ConvParams {
   int k_steps;  // MMAs (16 channels each) issued per tap and chunk; fewer than BK/16 when the tail of the chunk is zero padding
   int rs;  // 1 = row-streaming kernel (ub_conv_rs.cuh): tmA is the 5-D map over (pixel, row in quarter, quarter, plane, image)
   int hq;  // row-streaming: rows per stream = H / 4
+  // row-streaming: the A operand is filled by cp.async from the raw blocked tensor (ub_conv_rs.cuh explains why not TMA)
+  const __nv_bfloat16* a_src;  // plane 0 of image 0 of the layer's input view
+  int a_cgs;                   // channel-group planes per image of that buffer
+  int a_planes;                // planes that exist in the view (cin_src / 8); planes beyond read as zero
   int sa;  // A stages (activation boxes)
   int sb;  // B stages when streaming weights; unused when the kernel is the WS instantiation
 };
