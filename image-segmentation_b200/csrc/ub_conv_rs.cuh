@@ -177,6 +177,14 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
     const size_t row_stride = static_cast<size_t>(p.W) * 8;            // elements per image row of one plane
     const size_t plane_stride = row_stride * p.H;
     const size_t image_stride = plane_stride * p.a_cgs;
+    const size_t chunk_stride = plane_stride * (BK / 8);
+    // this warp's rows: element offset of (plane pl, first row of quarter q) — the per-tile address is one 64-bit add
+    size_t off[kRows / 2];
+#pragma unroll
+    for (int r = 0; r < kRows / 2; ++r) {
+      const int row = 2 * r + half, pl = row >> 2, q = row & 3;
+      off[r] = plane_stride * pl + row_stride * hq * q;
+    }
     int sa = 0;
     uint32_t pa = 0;
 #pragma unroll 1
@@ -184,21 +192,24 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
       const int b = task / bands, j = task - b * bands;
       const int x = j * kRsOut - 1 + lane;   // this lane's pixel: lane 0 / 31 are the band's halo columns
       const bool x_ok = x >= 0 && x < p.W;
-      const __nv_bfloat16* img = p.a_src + image_stride * b + static_cast<size_t>(x_ok ? x : 0) * 8;
+      // row -1 of the image (stream 0 at t = 0) is never dereferenced: those copies have src-size 0
+      const __nv_bfloat16* img = p.a_src + image_stride * b + static_cast<size_t>(x_ok ? x : 0) * 8 - row_stride;
 #pragma unroll 1
-      for (int t = 0; t < tpt; ++t) {
+      for (int t = 0; t < tpt; ++t, img += row_stride) {
+        // stream q reads image row q*hq - 1 + t: outside the image only for (q = 0, t = 0) and (q = 3, t = last)
+        const bool top = t == 0, bottom = t == tpt - 1;
+        const __nv_bfloat16* src_c = img;
 #pragma unroll 1
-        for (int c = 0; c < k_chunks; ++c) {
+        for (int c = 0; c < k_chunks; ++c, src_c += chunk_stride) {
           mbar_wait(&a_empty[sa], pa ^ 1u);
-          const uint32_t dst0 = smem_u32(a_ring + sa * Cfg::A_STAGE_BYTES) + static_cast<uint32_t>(lane) * 16u;
+          const uint32_t dst0 = smem_u32(a_ring + sa * Cfg::A_STAGE_BYTES) + static_cast<uint32_t>(lane) * 16u +
+                                static_cast<uint32_t>(half) * 512u;
+          const int planes_left = p.a_planes - c * (BK / 8);   // planes of this chunk that exist in the view
 #pragma unroll
           for (int r = 0; r < kRows / 2; ++r) {
-            const int row = 2 * r + half, pl = row >> 2, q = row & 3;
-            const int y = q * hq - 1 + t;          // stream q reads image row q*hq - 1 + t (one above .. one below its quarter)
-            const int plane = c * (BK / 8) + pl;
-            const bool ok = x_ok && y >= 0 && y < p.H && plane < p.a_planes;
-            const __nv_bfloat16* src = img + plane_stride * (ok ? plane : 0) + row_stride * (ok ? y : 0);
-            cp_async_16_zfill(dst0 + static_cast<uint32_t>(row) * 512u, src, ok);
+            const int row = 2 * r + half, pl = row >> 2, q = row & 3;   // (pl and q are compile-time up to `half`)
+            const bool ok = x_ok && pl < planes_left && !(top && q == 0) && !(bottom && q == 3);
+            cp_async_16_zfill(dst0 + static_cast<uint32_t>(r) * 1024u, src_c + off[r], ok);
           }
           cp_async_mbar_arrive_noinc(&a_full[sa]);   // arrives once this thread's copies above have landed
           if (++sa == p.sa) { sa = 0; pa ^= 1u; }

@@ -30,23 +30,44 @@ def folded(sd, conv_key):
 
 
 # ------------------------------------------------------------------ layers (tcgen05 implicit GEMM)
-def test_every_conv_layer(base_model, dev):
-    m, sd = base_model
-    eng = m.engine()
-    g = torch.Generator().manual_seed(3)
-    for key in m.layer_couts():
-        if key.endswith(".up"):
-            continue
+def _check_conv_layers(eng, sd, keys, shapes, seed=3):
+    g = torch.Generator().manual_seed(seed)
+    dev = eng.device
+    for key in keys:
         wf, bf = folded(sd, key)
-        # ragged tiles, full tiles, odd tile count (CTA-pair padding), and two sizes the thin layers run row-streaming at
-        # (H >= 32): 3 bands with a 12-pixel last one and 10 rows per stream; more tasks than SMs (5 x 64 x 900: 150)
-        for (n, h, w) in [(2, 24, 40), (1, 64, 64), (3, 16, 8), (2, 40, 72)] + ([(5, 64, 900)] if wf.shape[0] <= 64 and wf.shape[1] <= 64 else []):
+        for (n, h, w) in shapes:
             x = torch.randn((n, wf.shape[1], h, w), generator=g)
             ref = F.relu(F.conv2d(util.bf16_round(x).to(dev), util.bf16_round(wf).to(dev), bf.to(dev), padding=1))
             for pool in (False, True):
                 got = util.nhwc_to_nchw_f32(eng.debug_conv3x3(key, util.nchw_to_nhwc_bf16(x).to(dev), pool=pool))
                 want = F.max_pool2d(ref, 2, 2) if pool else ref
                 assert util.rel_err(got, want) < 6e-3, (key, n, h, w, pool)  # one bf16 output rounding
+
+
+def test_every_conv_layer(base_model, dev):
+    m, sd = base_model
+    keys = [k for k in m.layer_couts() if not k.endswith(".up")]
+    # ragged tiles, full tiles, odd tile count (CTA-pair padding), ragged kx-stacked tiles
+    _check_conv_layers(m.engine(), sd, keys, [(2, 24, 40), (1, 64, 64), (3, 16, 8), (2, 40, 72)])
+
+
+def test_row_streaming_kernel_on_the_thin_layers(base_model, dev, monkeypatch):
+    """UB_RS=1 selects conv_rs_kernel (ky taps stacked along N, rows accumulated in a sliding window of TMEM column
+    blocks, cp.async operand fill) for the Cout <= 64 layers from 32 rows up — measured equal to the kx-stacked kernel
+    under the power cap and therefore not the default, but kept correct: every thin layer, store and pooled epilogue, on
+    a full tile grid, on 3 bands with a 12-pixel last one and 10 rows per stream, and on more tasks than SMs."""
+    from image_segmentation_b200 import runtime
+    m, sd = base_model
+    monkeypatch.setenv("UB_RS", "1")
+    eng = runtime.new_engine(dev, "unet", 3, 3, 8)
+    try:
+        eng.load_state_dict(m.state_dict())
+        eng.set_layer_couts(m.layer_couts())
+        thin = [k for k, c in m.layer_couts().items() if not k.endswith(".up") and c <= 64]
+        assert len(thin) >= 6
+        _check_conv_layers(eng, sd, thin, [(1, 64, 64), (2, 40, 72), (5, 64, 900)], seed=5)
+    finally:
+        eng.close()
 
 
 def test_every_transposed_conv(base_model, dev):
@@ -619,7 +640,8 @@ def test_clipunet_prompt_224_trained(dev):
     assert util.rel_err(full, ref) < 1e-2
 
 
-@pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_NO_RS", "UB_HEAD_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL"])
+@pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_RS", "UB_HEAD_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL",
+                                  "UB_STREAMS=2"])
 def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     """The diagnostic switches select other kernels for the same layers (streamed weights, 9-tap thin layers, single
     CTAs, plain launches); they must stay correct: same logits within bf16 accumulation-order noise, same
@@ -629,8 +651,8 @@ def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     imgs, _ = synthetic.make_dataset(3, 64, 128, seed=17)
     x = synthetic.to_float_nchw(imgs).to(dev)
     base = m.engine(dev).forward(x)
-    monkeypatch.setenv(flag, "1")
-    eng = runtime.new_engine(dev, "unet", 3, 3, 8)   # the switches are read when the context is created
+    monkeypatch.setenv(*(flag.split("=") if "=" in flag else (flag, "1")))
+    eng = runtime.new_engine(dev, "unet", 3, 3, 2 if flag.startswith("UB_STREAMS") else 8)   # switches are read at creation
     try:
         eng.load_state_dict(m.state_dict())
         eng.set_layer_couts(m.layer_couts())
