@@ -92,7 +92,7 @@ struct ub_ctx {
   float* head_b = nullptr;
   std::vector<float> h_head_w, h_head_b;  // host copies, passed by value to the HEAD epilogue
   bool weights_ready = false;
-  std::map<std::pair<int, int>, std::unique_ptr<Plan>> plans;  // key (H, W * 2 + slot): one arena per internal stream
+  std::map<std::pair<int, int>, std::unique_ptr<Plan>> plans;
   EncodeTiledFn encode = nullptr;
   int64_t launches = 0;
   // optional per-launch timing (ub_profile_begin/end): event pairs around every GEMM launch
@@ -107,12 +107,7 @@ struct ub_ctx {
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool no_rs = true;          // UB_RS=1 selects the row-streaming kernel (ub_conv_rs.cuh) for the thin layers from 32 rows up; default:
                               // kx-stacked (the two measure the same under the power cap)
-  // UB_STREAMS=2: the micro-batches of a call alternate between two internal streams, each with its own activation arena
-  // and half of the SMs per launch, so the HBM-bound layers of one micro-batch overlap the tensor-bound ones of the other
-  int n_streams = 1;
-  int grid_cap = 0;           // SMs a GEMM launch may take (num_sms / n_streams)
-  cudaStream_t side[2] = {nullptr, nullptr};
-  cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
+
   bool profiling = false;
   struct ProfRec { int layer; cudaEvent_t a, b; };
   std::vector<ProfRec> prof;
@@ -588,7 +583,7 @@ int launch_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   ConvParams cp = cp_in;
   constexpr int TH = ub::tile_rows(TW), XS = ub::tile_xstep(TW);
   const int tiles = cp.B * ((cp.H + TH - 1) / TH) * ((cp.W + XS - 1) / XS) * (ub::is_kxs(TW) ? 1 : cp.n_total / N);
-  const int grid = tiles < ctx->grid_cap ? tiles : ctx->grid_cap;
+  const int grid = tiles < ctx->num_sms ? tiles : ctx->num_sms;
   int smem = 0;
   // UB_FORCE_STREAM=1 (test hook): exercise the streaming path on layers that would be weight-stationary
   const bool ws = choose_pipeline<N, BK, KS, TW>(&cp, grid, !ctx->force_stream, &smem);
@@ -606,7 +601,7 @@ int launch_pair(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
     if (cp.pairq) {  // weight-stationary pairs over several n-tiles: the pair count is a multiple of n_tiles
       const int n_tiles = cp.n_total / N;
       const int pairs_total = n_tiles * ((((cp.W + 7) / 8) + 1) / 2) * ((cp.H + 15) / 16) * cp.B;
-      int pairs = ctx->grid_cap / 2;
+      int pairs = ctx->num_sms / 2;
       if (pairs > pairs_total) pairs = pairs_total;
       const int pw = pairs - pairs % n_tiles;
       if (pw >= n_tiles && choose_pipeline<N, 64, KS, 8, true>(&cp, pw, !ctx->force_stream, &smem))
@@ -618,7 +613,7 @@ int launch_pair(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   const int per_img = ((cp.H + 15) / 16) * ((cp.W + 7) / 8);
   const int b_pad = cp.B + ((per_img * cp.B) & 1);
   const int tiles = per_img * b_pad * (cp.n_total / N);
-  const int max_grid = ctx->grid_cap & ~1;
+  const int max_grid = ctx->num_sms & ~1;
   const int grid = tiles < max_grid ? tiles : max_grid;
   if constexpr (N == 128 && KS == 3) {  // one n-tile and the pair's halves fit: each CTA keeps its half of the weights resident
     if (choose_pipeline<N, 64, KS, 8, true>(&cp, grid, cp.n_total == N && !ctx->force_stream, &smem))
@@ -636,7 +631,7 @@ int launch_rs(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   ConvParams cp = cp_in;
   const int bands = (cp.W + ub::kRsOut - 1) / ub::kRsOut;
   const int tasks = cp.B * bands;
-  const int grid = tasks < ctx->grid_cap ? tasks : ctx->grid_cap;
+  const int grid = tasks < ctx->num_sms ? tasks : ctx->num_sms;
   const int w_bytes = 3 * (cp.cin / BK) * Cfg::B_STAGE_BYTES;
   int sa = (Cfg::OPERAND_BUDGET - w_bytes) / Cfg::A_STAGE_BYTES;
   if (sa > ub::kMaxSA) sa = ub::kMaxSA;
@@ -744,8 +739,8 @@ int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cuda
 // ------------------------------------------------------------------ execution plan for one resolution
 int skip_width(int level) { return level == 0 ? 32 : (32 << level); }
 
-int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out, int slot = 0) {
-  auto key = std::make_pair(H, W * 2 + slot);
+int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out) {
+  auto key = std::make_pair(H, W);
   auto it = ctx->plans.find(key);
   if (it != ctx->plans.end()) { *out = it->second.get(); return UB_OK; }
   const int n = ctx->n_enc, MB = ctx->max_mb;
@@ -1168,17 +1163,6 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   { const char* e = getenv("UB_NO_STEM_FOLD"); ctx->stem_fold = !(e && e[0] == '1'); }
   { const char* e = getenv("UB_DBG"); ctx->dbg = e ? atoi(e) : 0; }
   { const char* e = getenv("UB_RS"); ctx->no_rs = !(e && e[0] == '1'); }
-  { const char* e = getenv("UB_STREAMS"); ctx->n_streams = (e && e[0] == '2') ? 2 : 1; }
-  ctx->grid_cap = ctx->num_sms / ctx->n_streams;
-  if (ctx->n_streams == 2) {
-    for (int i = 0; i < 2; ++i) {
-      if (cudaStreamCreateWithFlags(&ctx->side[i], cudaStreamNonBlocking) != cudaSuccess ||
-          cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming) != cudaSuccess)
-        return fail(nullptr, UB_ERR_CUDA, "cannot create the internal streams");
-    }
-    if (cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess)
-      return fail(nullptr, UB_ERR_CUDA, "cannot create the internal streams");
-  }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();
@@ -1191,11 +1175,6 @@ void ub_destroy(ub_ctx* ctx) {
   for (void* p : ctx->owned) cudaFree(p);
   for (auto& r : ctx->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
-  for (int i = 0; i < 2; ++i) {
-    if (ctx->side[i]) cudaStreamDestroy(ctx->side[i]);
-    if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
-  }
-  if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
   delete ctx;
 }
 
@@ -1324,20 +1303,9 @@ int eval_impl(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_fo
       if (r > 0) mb_sizes.push_back(r);
     }
   }
-  // UB_STREAMS=2: fork — the internal streams start after everything already queued on the caller's stream (the memsets
-  // above included); micro-batch i runs on stream i & 1 in that stream's own arena; join at the end
-  const bool split = ctx->n_streams == 2 && mb_sizes.size() >= 2;
-  Plan* pls[2] = {pl, pl};
-  if (split) {
-    if ((rc = build_plan(ctx, h, w, ctx->side[1], &pls[1], 1))) return rc;
-    UB_CUDA(ctx, cudaEventRecord(ctx->ev_fork, st));
-    for (int i = 0; i < 2; ++i) UB_CUDA(ctx, cudaStreamWaitEvent(ctx->side[i], ctx->ev_fork, 0));
-  }
   int i0 = 0;
   for (size_t mbi = 0; mbi < mb_sizes.size(); i0 += mb_sizes[mbi], ++mbi) {
     const int nb = mb_sizes[mbi];
-    Plan* pl_mb = pls[split ? (mbi & 1) : 0];
-    cudaStream_t st_mb = split ? ctx->side[mbi & 1] : st;
     ub::PerturbDev Pm = P;
     if (aux) {
       size_t per_img = 0;
@@ -1361,15 +1329,9 @@ int eval_impl(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_fo
     ha.logits = logits_out ? logits_out + hw * C * i0 : nullptr;
     ha.clip = clip_feats ? clip_feats + static_cast<size_t>(2 * 32 * (1 << ctx->n_enc)) * i0 : nullptr;
     ha.prompt = prompt ? prompt + hw * i0 : nullptr;
-    if ((rc = run_microbatch(ctx, pl_mb, Pm, static_cast<const uint8_t*>(images) + img_stride * i0, image_format, nb, ha,
-                             perturbed_out ? perturbed_out + hw * 3 * i0 : nullptr, st_mb)))
+    if ((rc = run_microbatch(ctx, pl, Pm, static_cast<const uint8_t*>(images) + img_stride * i0, image_format, nb, ha,
+                             perturbed_out ? perturbed_out + hw * 3 * i0 : nullptr, st)))
       return rc;
-  }
-  if (split) {
-    for (int i = 0; i < 2; ++i) {
-      UB_CUDA(ctx, cudaEventRecord(ctx->ev_join[i], ctx->side[i]));
-      UB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_join[i], 0));
-    }
   }
   if (dice_sums) {
     ub::dice_tsum_kernel<<<blocks_for(static_cast<size_t>(n_batches) * C, 128), 128, 0, st>>>(

@@ -110,7 +110,8 @@ class RobustnessEvaluator:
         t[self.rank] = float(rate)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         rates = [float(v) for v in t.cpu()]
-        torch.cuda.synchronize(self.device)
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
         self._set_range(images_u8, masks_u8, rates)
         return rates
 
