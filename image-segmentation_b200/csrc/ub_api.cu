@@ -634,7 +634,8 @@ int launch_rs(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   const int grid = tasks < ctx->num_sms ? tasks : ctx->num_sms;
   const int w_bytes = 3 * (cp.cin / BK) * Cfg::B_STAGE_BYTES;
   int sa = (Cfg::OPERAND_BUDGET - w_bytes) / Cfg::A_STAGE_BYTES;
-  if (sa > ub::kMaxSA) sa = ub::kMaxSA;
+  if (sa > ub::kRsMaxSA) sa = ub::kRsMaxSA;
+  { const char* e = getenv("UB_RS_SA"); if (e && atoi(e) >= 2 && atoi(e) < sa) sa = atoi(e); }  // (experiment: ring depth)
   if (sa < 2) return fail(ctx, UB_ERR_UNSUPPORTED, "row-streaming kernel: the layer's weights (%d bytes) leave no room for 2 A stages", w_bytes);
   cp.sa = sa;
   const int smem = Cfg::TAIL_BYTES + sa * Cfg::A_STAGE_BYTES + w_bytes + 1024;

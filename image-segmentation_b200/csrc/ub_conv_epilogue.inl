@@ -1,4 +1,4 @@
-// Epilogue body of conv_tc_kernel (included inside the `warp >= 4` branch).
+// Epilogue body of conv_tc_kernel (included inside the `role < 0` branch: warps 0 .. 4*kEpiGroups-1).
 // Thread (wq, lane) owns accumulator row m = 32*wq + lane = pixel (ty = m / TW, tx = m % TW) of the
 // (128/TW) x TW tile and reads its fp32 columns from TMEM 32 at a time (double-buffered: the next
 // tcgen05.ld is in flight while the current 32 channels are converted and stored).  In the kx-stacked
@@ -7,10 +7,10 @@
 {
   constexpr bool kHead = (Cfg::COUT_T == 32);  // the fused head exists only in the 32-channel instantiations
   const int wq = warp & 3;
-  const int grp = (warp - 4) >> 2;             // tiles it with it % kEpiGroups == grp
+  const int grp = warp >> 2;                   // tiles it with it % kEpiGroups == grp
   const int ty = (32 * wq + lane) / TW;
   const int tx = (32 * wq + lane) % TW;
-  const int et = (threadIdx.x - 128) & 127;    // 0..127 within the group
+  const int et = threadIdx.x & 127;            // 0..127 within the group
   unsigned long long* s_cm = s_cm_all + grp * (kMaxClasses * kMaxClasses);
   double* s_dice = s_dice_all + grp * (2 * kMaxClasses);
   // HEAD: every thread counts its own pixels in registers (ub_head.cuh); they are reduced (warp shuffle -> shared

@@ -53,6 +53,8 @@ namespace ub {
 constexpr int kRsOut = 30;      // output columns per band (32 lanes per stream, one halo lane each side)
 constexpr int kRsMaxGroups = 4;
 constexpr int kRsMaxBlocks = 16;
+constexpr int kRsMaxSA = 24;    // A stages: a row tile is small (4-16 KB), so the ring is deep — the bytes in flight, not the
+                                // stage count, are what hides the memory latency
 // epilogue groups of 4 warps: the 32-channel layers (the head among them) have short MMA phases per row and the longest
 // per-pixel epilogue -> 4 groups; the 64-channel rows take three times as long on the tensor pipe -> 2 groups (and twice
 // the registers per thread for the held pooling row)
@@ -77,7 +79,7 @@ struct RsCfg {
   // fixed-size tail in front of the operand regions
   static constexpr int TAIL_BIAS = 0;                              // [COUT] floats
   static constexpr int TAIL_BAR = 256;                             // barriers
-  static constexpr int N_BARS = 2 * kMaxSA + 2 * kRsMaxBlocks + 1;
+  static constexpr int N_BARS = 2 * kRsMaxSA + 2 * kRsMaxBlocks + 1;
   static constexpr int TAIL_CM = TAIL_BAR + N_BARS * 8;
   static constexpr int TAIL_DICE = TAIL_CM + kRsMaxGroups * kMaxClasses * kMaxClasses * 8;
   static constexpr int TAIL_TMEM = TAIL_DICE + kRsMaxGroups * kMaxClasses * 2 * 8;
@@ -106,6 +108,56 @@ __device__ __forceinline__ void umma_bf16_lo_rt(uint32_t tmem_d, uint32_t a_lo, 
       : "memory");
 }
 
+// The MMAs of one (row tile, channel chunk), straight-line: the single issuing thread's own instruction stream bounds
+// the 32-channel layers (ncu source view of the first version: ~100 uniform-datapath instructions per row tile at
+// ~9 cycles each = the 900-cycle tile period, with 7 MMAs = 390 cycles of tensor work), so everything that can be is a
+// compile-time constant: CASE = where the three-block window sits (0: contiguous, 1: row tau+1 wraps to block 0, 2: rows
+// tau and tau+1 wrap), FIRST = this chunk carries the tile's first contribution to the fresh block (accumulate = 0).
+template <int COUT, int BK, int CASE, bool FIRST>
+__device__ __forceinline__ void rs_issue_chunk(uint32_t d0, uint32_t d_wrap, uint32_t a_stage, uint32_t a_hi, uint32_t bl_c,
+                                               uint32_t b_hi, bool skip_last_k) {
+  using Cfg = RsCfg<COUT, BK>;
+  constexpr uint32_t idesc1 = umma_idesc_bf16(kTileM, COUT);
+  constexpr uint32_t idesc2 = umma_idesc_bf16(kTileM, 2 * COUT);
+  constexpr uint32_t idesc3 = umma_idesc_bf16(kTileM, 3 * COUT);
+  constexpr uint32_t A_KSTEP_U = (2 * Cfg::A_PLANE_BYTES) >> 4;   // one MMA = 16 channels = 2 planes
+  constexpr uint32_t B_STAGE_U = Cfg::B_STAGE_BYTES >> 4;
+  constexpr uint32_t B_BLOCK_U = (COUT * Cfg::SWZ_B) >> 4;        // Cout weight rows = one ky block (whole swizzle atoms)
+#pragma unroll
+  for (int kx = 0; kx < 3; ++kx) {
+#pragma unroll
+    for (int k = 0; k < BK / 16; ++k) {
+      if (k == BK / 16 - 1 && BK / 16 > 1 && skip_last_k) continue;   // zero-padded tail of the chunk (k_steps = BK/16 - 1)
+      // tap kx reads pixel (lane + kx - 1) of the stream: the descriptor starts one 16-byte pixel earlier / later
+      const uint32_t al = a_stage + static_cast<uint32_t>(k) * A_KSTEP_U + static_cast<uint32_t>(kx) - 1u;
+      const uint32_t bl = bl_c + static_cast<uint32_t>(kx) * B_STAGE_U + 2u * static_cast<uint32_t>(k);
+      constexpr bool kFirstMma = true;
+      const bool first = FIRST && kx == 0 && k == 0;
+      (void)kFirstMma;
+      if constexpr (CASE == 0) {
+        if (!first) {
+          umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc3);
+        } else {
+          umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc2);
+          umma_bf16_lo<false>(d0 + 2 * COUT, al, a_hi, bl + 2 * B_BLOCK_U, b_hi, idesc1);
+        }
+      } else if constexpr (CASE == 1) {   // rows tau-1, tau in the last two blocks, row tau+1 in block 0
+        umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc2);
+        if (!first) umma_bf16_lo<true>(d_wrap, al, a_hi, bl + 2 * B_BLOCK_U, b_hi, idesc1);
+        else umma_bf16_lo<false>(d_wrap, al, a_hi, bl + 2 * B_BLOCK_U, b_hi, idesc1);
+      } else {                            // row tau-1 in the last block, rows tau, tau+1 in blocks 0, 1
+        umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc1);
+        if (!first) {
+          umma_bf16_lo<true>(d_wrap, al, a_hi, bl + B_BLOCK_U, b_hi, idesc2);
+        } else {
+          umma_bf16_lo<true>(d_wrap, al, a_hi, bl + B_BLOCK_U, b_hi, idesc1);
+          umma_bf16_lo<false>(d_wrap + COUT, al, a_hi, bl + 2 * B_BLOCK_U, b_hi, idesc1);
+        }
+      }
+    }
+  }
+}
+
 template <int COUT, int BK>
 __global__ void __launch_bounds__(rs_threads(COUT), 1)
 conv_rs_kernel(const __grid_constant__ ConvParams p) {
@@ -118,8 +170,8 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
   float* s_bias = reinterpret_cast<float*>(smem + Cfg::TAIL_BIAS);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::TAIL_BAR);
   uint64_t* a_full = bars;
-  uint64_t* a_empty = bars + kMaxSA;
-  uint64_t* blk_full = bars + 2 * kMaxSA;          // MMA -> epilogue: row sigma (block sigma % R) is complete
+  uint64_t* a_empty = bars + kRsMaxSA;
+  uint64_t* blk_full = bars + 2 * kRsMaxSA;        // MMA -> epilogue: row sigma (block sigma % R) is complete
   uint64_t* blk_empty = blk_full + kRsMaxBlocks;   // epilogue -> MMA: the block's columns are in registers
   uint64_t* w_full = blk_empty + kRsMaxBlocks;
   unsigned long long* s_cm_all = reinterpret_cast<unsigned long long*>(smem + Cfg::TAIL_CM);
@@ -130,6 +182,8 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
+  // epilogue warps first, the producers / MMA issuer / TMEM allocator last: the scheduler favours the highest warp id
+  const int role = warp - 4 * G;  // 0 producer (+ weights), 1 MMA issuer, 2 TMEM allocator, 3 producer; negative: epilogue
   const int k_chunks = p.cin / BK;
   const int hq = p.hq;                       // rows per stream (H / 4)
   const int tpt = hq + 2;                    // tiles per task
@@ -142,23 +196,23 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
   for (int i = threadIdx.x; i < COUT; i += kRsThreads) s_bias[i] = p.bias[i];
   if (threadIdx.x < G * kMaxClasses * kMaxClasses) s_cm_all[threadIdx.x] = 0ull;
   if (threadIdx.x < G * kMaxClasses * 2) s_dice_all[threadIdx.x] = 0.0;
-  if (warp == 0 && lane == 0) tma_prefetch_desc(&p.tmB);
-  if (warp == 1 && lane == 0) {
-    for (int i = 0; i < kMaxSA; ++i) { mbar_init(&a_full[i], 64); mbar_init(&a_empty[i], 1); }  // 64 = the two producer warps
+  if (role == 0 && lane == 0) tma_prefetch_desc(&p.tmB);
+  if (role == 1 && lane == 0) {
+    for (int i = 0; i < kRsMaxSA; ++i) { mbar_init(&a_full[i], 64); mbar_init(&a_empty[i], 1); }  // 64 = the two producer warps
     for (int i = 0; i < kRsMaxBlocks; ++i) { mbar_init(&blk_full[i], 1); mbar_init(&blk_empty[i], 128); }
     mbar_init(w_full, 1);
     fence_barrier_init();
   }
-  if (warp == 2) { tmem_alloc(s_tmem, Cfg::TMEM_COLS); tmem_relinquish(); }
+  if (role == 2) { tmem_alloc(s_tmem, Cfg::TMEM_COLS); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
   if (!(p.dbg & 16)) pdl_launch_dependents();  // see conv_tc_kernel
 
-  if (warp == 0 || warp == 3) {
+  if (role == 0 || role == 3) {
     // ================= producers: warp 0 (also loads the weights) and warp 3 fill the A stages with cp.async =================
-    if (warp == 0) {
+    if (role == 0) {
       const bool leader = elect_one();
       const int n_w = 3 * k_chunks;
       if (leader) {  // weights are constants of the layer: loaded before the wait on the previous kernel
@@ -172,7 +226,7 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
       __syncwarp();
     }
     pdl_wait_prior_grid();  // activations of the previous layer are complete and visible from here on
-    const int half = warp == 0 ? 0 : 1;      // which rows of a stage this warp copies
+    const int half = role == 0 ? 0 : 1;      // which rows of a stage this warp copies
     constexpr int kRows = 4 * (BK / 8);      // (plane, stream) rows of one stage, 512 bytes each
     const size_t row_stride = static_cast<size_t>(p.W) * 8;            // elements per image row of one plane
     const size_t plane_stride = row_stride * p.H;
@@ -216,87 +270,72 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (role == 1) {
     // ================= MMA issuer (one elected lane issues and commits) =================
     const bool leader = elect_one();
-    constexpr uint32_t idesc1 = umma_idesc_bf16(kTileM, COUT);
-    constexpr uint32_t idesc2 = umma_idesc_bf16(kTileM, 2 * COUT);
-    constexpr uint32_t idesc3 = umma_idesc_bf16(kTileM, 3 * COUT);
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint64_t desc_a = umma_smem_desc_interleaved(smem_u32(a_ring), Cfg::A_PLANE_BYTES, 128);
     const uint64_t desc_b = umma_smem_desc<Cfg::SWZ_B>(smem_u32(b_res));
     const uint32_t a_hi = static_cast<uint32_t>(desc_a >> 32), b_hi = static_cast<uint32_t>(desc_b >> 32);
     const uint32_t a_lo_ring = static_cast<uint32_t>(desc_a), b_lo_res = static_cast<uint32_t>(desc_b);
     constexpr uint32_t A_STAGE_U = Cfg::A_STAGE_BYTES >> 4;
-    constexpr uint32_t A_KSTEP_U = (2 * Cfg::A_PLANE_BYTES) >> 4;   // one MMA = 16 channels = 2 planes
-    constexpr uint32_t B_STAGE_U = Cfg::B_STAGE_BYTES >> 4;
-    constexpr uint32_t B_BLOCK_U = (COUT * Cfg::SWZ_B) >> 4;        // Cout weight rows = one ky block (whole swizzle atoms)
-    const int k_steps = p.k_steps > 0 ? p.k_steps : BK / 16;
+    constexpr uint32_t B_CHUNK_U = 3 * (Cfg::B_STAGE_BYTES >> 4);
+    const bool skip_last_k = p.k_steps > 0 && p.k_steps < BK / 16;
     mbar_wait(w_full, 0);
     tc_fence_after();
     int sa = 0;
     uint32_t pa = 0;
+    uint32_t a_stage = a_lo_ring;  // descriptor low word of stage `sa`
     int blk0 = R - 1;        // block of row tau - 1
     int fresh = 1;           // block of row tau + 1
-    uint32_t fresh_use = 0;  // how many rows have used the fresh block before: parity of its `empty` barrier
+    uint32_t fresh_par = 1;  // parity to wait for on the fresh block's `empty` barrier: (uses so far & 1) ^ 1
+    const uint32_t d_wrap = tmem_u;  // block 0
+    auto next_stage = [&]() {
+      a_stage += A_STAGE_U;
+      if (++sa == p.sa) { sa = 0; pa ^= 1u; a_stage = a_lo_ring; }
+    };
 #pragma unroll 1
     for (int tau = 0; tau < my_tiles; ++tau) {
       // the block about to be overwritten held row tau + 1 - R: its columns must be in the epilogue's registers
-      mbar_wait(&blk_empty[fresh], (fresh_use & 1u) ^ 1u);
-      tc_fence_after();
+      mbar_wait(&blk_empty[fresh], fresh_par);
       const uint32_t d0 = tmem_u + static_cast<uint32_t>(blk0 * COUT);
-      const uint32_t d_wrap = tmem_u;  // block 0
+      // chunk 0 carries the tile's first contribution to the fresh block
+      mbar_wait(&a_full[sa], pa);
+      fence_proxy_async();  // the stage was written through the generic proxy (cp.async); the MMA reads it through the async proxy
+      tc_fence_after();
+      if (leader) {
+        if (blk0 <= R - 3) rs_issue_chunk<COUT, BK, 0, true>(d0, d_wrap, a_stage, a_hi, b_lo_res, b_hi, skip_last_k);
+        else if (blk0 == R - 2) rs_issue_chunk<COUT, BK, 1, true>(d0, d_wrap, a_stage, a_hi, b_lo_res, b_hi, skip_last_k);
+        else rs_issue_chunk<COUT, BK, 2, true>(d0, d_wrap, a_stage, a_hi, b_lo_res, b_hi, skip_last_k);
+        umma_commit(&a_empty[sa]);
+        if (k_chunks == 1 && tau >= 1) umma_commit(&blk_full[blk0]);  // row tau - 1 is complete
+      }
+      __syncwarp();
+      next_stage();
 #pragma unroll 1
-      for (int c = 0; c < k_chunks; ++c) {
+      for (int c = 1; c < k_chunks; ++c) {
         mbar_wait(&a_full[sa], pa);
-        fence_proxy_async();  // the stage was written through the generic proxy (cp.async); the MMA reads it through the async proxy
+        fence_proxy_async();
         tc_fence_after();
         if (leader) {
-          const uint32_t a_stage = a_lo_ring + static_cast<uint32_t>(sa) * A_STAGE_U;
-#pragma unroll
-          for (int kx = 0; kx < 3; ++kx) {
-#pragma unroll
-            for (int k = 0; k < BK / 16; ++k) {
-              if (k >= k_steps) continue;  // zero-padded tail of the chunk
-              // tap kx reads pixel (lane + kx - 1) of the stream: the descriptor starts one 16-byte pixel earlier / later
-              const uint32_t al = a_stage + static_cast<uint32_t>(k) * A_KSTEP_U + static_cast<uint32_t>(kx) - 1u;
-              const uint32_t bl = b_lo_res + static_cast<uint32_t>(c * 3 + kx) * B_STAGE_U + 2u * static_cast<uint32_t>(k);
-              const bool first = (c == 0 && kx == 0 && k == 0);  // this tile's first contribution to the fresh block
-              if (blk0 <= R - 3) {
-                if (!first) {
-                  umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc3);
-                } else {
-                  umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc2);
-                  umma_bf16_lo<false>(d0 + 2 * COUT, al, a_hi, bl + 2 * B_BLOCK_U, b_hi, idesc1);
-                }
-              } else if (blk0 == R - 2) {   // rows tau-1, tau in the last two blocks, row tau+1 wraps to block 0
-                umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc2);
-                umma_bf16_lo_rt(d_wrap, al, a_hi, bl + 2 * B_BLOCK_U, b_hi, idesc1, first ? 0u : 1u);
-              } else {                      // row tau-1 in the last block, rows tau, tau+1 in blocks 0, 1
-                umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc1);
-                if (!first) {
-                  umma_bf16_lo<true>(d_wrap, al, a_hi, bl + B_BLOCK_U, b_hi, idesc2);
-                } else {
-                  umma_bf16_lo<true>(d_wrap, al, a_hi, bl + B_BLOCK_U, b_hi, idesc1);
-                  umma_bf16_lo<false>(d_wrap + COUT, al, a_hi, bl + 2 * B_BLOCK_U, b_hi, idesc1);
-                }
-              }
-            }
-          }
+          const uint32_t bl_c = b_lo_res + static_cast<uint32_t>(c) * B_CHUNK_U;
+          if (blk0 <= R - 3) rs_issue_chunk<COUT, BK, 0, false>(d0, d_wrap, a_stage, a_hi, bl_c, b_hi, skip_last_k);
+          else if (blk0 == R - 2) rs_issue_chunk<COUT, BK, 1, false>(d0, d_wrap, a_stage, a_hi, bl_c, b_hi, skip_last_k);
+          else rs_issue_chunk<COUT, BK, 2, false>(d0, d_wrap, a_stage, a_hi, bl_c, b_hi, skip_last_k);
           umma_commit(&a_empty[sa]);
-          if (c == k_chunks - 1 && tau >= 1) umma_commit(&blk_full[blk0]);  // row tau - 1 is complete
+          if (c == k_chunks - 1 && tau >= 1) umma_commit(&blk_full[blk0]);
         }
         __syncwarp();
-        if (++sa == p.sa) { sa = 0; pa ^= 1u; }
+        next_stage();
       }
       blk0 = blk0 + 1 == R ? 0 : blk0 + 1;
-      if (++fresh == R) { fresh = 0; ++fresh_use; }  // rows u*R .. u*R + R - 1 are the u-th occupants of their blocks
+      if (++fresh == R) { fresh = 0; fresh_par ^= 1u; }  // rows u*R .. u*R + R - 1 are the u-th occupants of their blocks
     }
-  } else if (warp >= 4) {
+  } else if (role < 0) {
     // ================= epilogue: G groups x 128 threads; thread (wq, lane) owns TMEM lane 32*wq + lane =================
     const int wq = warp & 3;                 // stream = row quarter
-    const int grp = (warp - 4) >> 2;
-    const int et = (threadIdx.x - 128) & 127;
+    const int grp = warp >> 2;
+    const int et = threadIdx.x & 127;
     unsigned long long* s_cm = s_cm_all + grp * (kMaxClasses * kMaxClasses);
     double* s_dice = s_dice_all + grp * (2 * kMaxClasses);
     HeadState hs;
@@ -417,7 +456,7 @@ conv_rs_kernel(const __grid_constant__ ConvParams p) {
   __syncwarp();
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (role == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }

@@ -38,8 +38,10 @@
 //             CTA.  Each CTA stages its own A box and HALF of every weight tile (N/2 rows); the tensor
 //             cores of both SMs read both halves.  Weight traffic from L2 and the shared-memory bytes
 //             written and read per MMA are halved — these layers were bound by exactly that.
-// Warp roles: w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, then kEpiGroups groups of 4 epilogue
-// warps.  kAcc TMEM accumulators (up to 4): the MMA warp runs ahead of the epilogues by kAcc tiles.
+// Warp roles: kEpiGroups groups of 4 epilogue warps FIRST (warps 0 .. 4*kEpiGroups-1), then the TMA producer, the MMA
+// issuer and the TMEM allocator as the LAST warps of the CTA: a scheduler that has several eligible warps picks the one
+// with the highest warp id, and the single MMA-issuing thread must never queue behind epilogue warps (or behind warps
+// spinning on a barrier).  kAcc TMEM accumulators (up to 4): the MMA warp runs ahead of the epilogues by kAcc tiles.
 #pragma once
 #include "ub_ptx.cuh"
 #include "ub_head.cuh"
@@ -232,6 +234,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   // warp index through a shuffle so the compiler treats the role branches as warp-uniform
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
+  constexpr int kEpiWarps = 4 * kEpiGroups;
+  const int role = warp - kEpiWarps;  // 0 TMA producer, 1 MMA issuer, 2 TMEM allocator, 3 spare; negative: epilogue warp
 
   const int tiles_x = (p.W + kXStep - 1) / kXStep;
   const int tiles_y = (p.H + kTileRows - 1) / kTileRows;
@@ -268,18 +272,18 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
     if (threadIdx.x < kEpiGroups * kMaxClasses * kMaxClasses) s_cm_all[threadIdx.x] = 0ull;
     if (threadIdx.x < kEpiGroups * kMaxClasses * 2) s_dice_all[threadIdx.x] = 0.0;
   }
-  if (warp == 0 && lane == 0) {
+  if (role == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
   }
-  if (warp == 1 && lane == 0) {
+  if (role == 1 && lane == 0) {
     for (int i = 0; i < kMaxSA; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
     for (int i = 0; i < kMaxSB; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
     for (int i = 0; i < kMaxAcc; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], CG2 ? 256 : 128); }
     mbar_init(w_full, 1);
     fence_barrier_init();
   }
-  if (warp == 2) {
+  if (role == 2) {
     if constexpr (CG2) { tmem_alloc_pair(s_tmem, Cfg::TMEM_COLS); tmem_relinquish_pair(); }
     else { tmem_alloc(s_tmem, Cfg::TMEM_COLS); tmem_relinquish(); }
   }
@@ -295,7 +299,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   // memory flush; epilogue stores only follow MMAs that follow those loads.  (UB_DBG bit 16 disarms it for A/B timing.)
   if (!(p.dbg & 16)) pdl_launch_dependents();
 
-  if (warp == 0) {
+  if (role == 0) {
     // ================= TMA producer (whole warp runs the loop; one elected lane issues) =================
     const bool leader = elect_one();
     if constexpr (WS) {
@@ -370,7 +374,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
         }
       }
     }
-  } else if (warp == 1 && cta_rank == 0) {
+  } else if (role == 1 && cta_rank == 0) {
     // ================= MMA issuer (whole warp runs the loop; ONE fixed lane issues and commits) =================
     // (CTA pairs: the even CTA issues M = 256 MMAs for both; the odd CTA's warp 1 has nothing to do)
     const bool leader = elect_one();
@@ -478,7 +482,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
         __syncwarp();
       }
     }
-  } else if (warp >= 4) {
+  } else if (role < 0) {
     // ================= epilogue (kEpiGroups x 128 threads; warp w owns TMEM lanes 32*(w%4)..) =================
 #include "ub_conv_epilogue.inl"
   }
@@ -488,7 +492,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   tc_fence_before();
   if constexpr (CG2) cluster_sync_all();  // the peer may still signal our barriers / read our operands until here
   else __syncthreads();
-  if (warp == 2) {
+  if (role == 2) {
     tc_fence_after();
     if constexpr (CG2) tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
     else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
