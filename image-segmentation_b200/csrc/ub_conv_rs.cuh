@@ -131,9 +131,7 @@ __device__ __forceinline__ void rs_issue_chunk(uint32_t d0, uint32_t d_wrap, uin
       // tap kx reads pixel (lane + kx - 1) of the stream: the descriptor starts one 16-byte pixel earlier / later
       const uint32_t al = a_stage + static_cast<uint32_t>(k) * A_KSTEP_U + static_cast<uint32_t>(kx) - 1u;
       const uint32_t bl = bl_c + static_cast<uint32_t>(kx) * B_STAGE_U + 2u * static_cast<uint32_t>(k);
-      constexpr bool kFirstMma = true;
       const bool first = FIRST && kx == 0 && k == 0;
-      (void)kFirstMma;
       if constexpr (CASE == 0) {
         if (!first) {
           umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc3);
