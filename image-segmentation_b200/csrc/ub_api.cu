@@ -11,6 +11,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <set>
 #include <string>
 #include <vector>
@@ -1465,6 +1466,92 @@ int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int 
   ub::perturb_kernel<<<blocks_for(hw * n, 256), 256, 0, st>>>(P, images, image_format, n, h, w, out_nchw);
   UB_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
+  return UB_OK;
+}
+
+}  // extern "C"
+
+// ---- ub_blur_images_static: the pass-per-launch blur with its ping-pong planes in a file-scope device array -----------
+// For callers that may not allocate (CUDA graph capture, tight serving loops).  No counterpart in the reference.
+// Two planes of UB_STATIC_BLUR_MAX_ELEMS fp32-sized elements each; every GPU that loads the library holds them (8 MiB)
+// until the process exits.  Every call on a device shares them: calls that overlap on the GPU race.  Nothing in them has
+// to start at zero — the load / quantise kernel writes all n*3*h*w elements of plane A before any pass reads them and
+// every pass writes all of its destination — so a call never sees what the previous one left.
+namespace {
+static __device__ __align__(256) unsigned char g_static_blur_planes[2 * sizeof(float) * UB_STATIC_BLUR_MAX_ELEMS];
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_blur_mu;
+void* g_static_blur_dev_ptr[kStaticMaxDevices] = {};  // device address of the array, per device (the symbol itself is
+                                                      // a host-side stand-in and must never reach a kernel)
+
+// Once per device, with that device current: the array's device address.
+int static_blur_planes(ub_ctx* ctx, unsigned char** out) {
+  if (ctx->device < 0 || ctx->device >= kStaticMaxDevices) return fail(ctx, UB_ERR_INVALID, "device index %d out of range", ctx->device);
+  std::lock_guard<std::mutex> lock(g_static_blur_mu);
+  void*& slot = g_static_blur_dev_ptr[ctx->device];
+  if (!slot) {
+    void* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_blur_planes);
+    if (e != cudaSuccess || !ptr)
+      return fail(ctx, UB_ERR_CUDA, "cudaGetSymbolAddress(static blur planes) on device %d: %s", ctx->device, cudaGetErrorString(e));
+    slot = ptr;
+  }
+  *out = static_cast<unsigned char*>(slot);
+  return UB_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ub_blur_images_static(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, int n, int h, int w,
+                          float* out_nchw, void* stream) {
+  if (!ctx) return UB_ERR_INVALID;
+  if (!p || !images || !out_nchw || n <= 0 || h <= 0 || w <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  if (p->kind != UB_P_U8_BLUR && p->kind != UB_P_F_BLUR)
+    return fail(ctx, UB_ERR_INVALID, "ub_blur_images_static takes the blur families only (kind %d)", p->kind);
+  const unsigned long long count = 3ull * static_cast<unsigned long long>(n) * static_cast<unsigned long long>(h) *
+                                   static_cast<unsigned long long>(w);
+  if (count > UB_STATIC_BLUR_MAX_ELEMS)
+    return fail(ctx, UB_ERR_INVALID,
+                "ub_blur_images_static: n*3*h*w = %llu elements exceeds the static planes' %llu (UB_STATIC_BLUR_MAX_ELEMS); "
+                "split the call or use ub_perturb_images",
+                count, static_cast<unsigned long long>(UB_STATIC_BLUR_MAX_ELEMS));
+  UB_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ub::PerturbDev P;
+  int rc;
+  if ((rc = to_dev_perturb(ctx, p, nullptr, &P))) return rc;
+  unsigned char* planes = nullptr;
+  if ((rc = static_blur_planes(ctx, &planes))) return rc;
+  unsigned char* plane_a = planes;
+  unsigned char* plane_b = planes + sizeof(float) * UB_STATIC_BLUR_MAX_ELEMS;
+  const unsigned g = blocks_for(static_cast<size_t>(count), 256);
+  if (P.kind == UB_P_U8_BLUR) {
+    uint8_t* a = plane_a;
+    uint8_t* b = plane_b;
+    ub::blur_u8_quantise_kernel<<<g, 256, 0, st>>>(images, image_format, n, h, w, a);
+    ctx->launches++;
+    for (int i = 0; i < P.iparam; ++i) {
+      ub::blur_u8_pass_kernel<<<g, 256, 0, st>>>(a, b, n * 3, h, w);
+      ctx->launches++;
+      std::swap(a, b);
+    }
+    ub::u8_planar_to_f32_kernel<<<g, 256, 0, st>>>(a, out_nchw, static_cast<size_t>(count));
+    ctx->launches++;
+  } else {
+    float* a = reinterpret_cast<float*>(plane_a);
+    float* b = reinterpret_cast<float*>(plane_b);
+    if (P.iparam == 0) a = out_nchw;
+    ub::blur_f_load_kernel<<<g, 256, 0, st>>>(images, image_format, n, h, w, a);
+    ctx->launches++;
+    for (int i = 0; i < P.iparam; ++i) {
+      float* o = (i == P.iparam - 1) ? out_nchw : b;
+      ub::blur_f_pass_kernel<<<g, 256, 0, st>>>(a, o, n * 3, h, w);
+      ctx->launches++;
+      b = a; a = o;
+    }
+  }
+  UB_CUDA(ctx, cudaGetLastError());
   return UB_OK;
 }
 

@@ -282,6 +282,21 @@ class Engine:
                                                n, h, w, _ptr(out), _stream(self.device)), "ub_perturb_images")
         return out
 
+    def blur_static(self, images: torch.Tensor, perturbation: Perturbation, out: torch.Tensor) -> torch.Tensor:
+        """`ub_blur_images_static`: the blur families with the library's static scratch planes — no device allocation in
+        the call, so the CALLER provides `out` (fp32 [n,3,H,W]).  No counterpart in the reference (include/unet_b200.h)."""
+        assert images.is_cuda and images.is_contiguous() and out.is_cuda and out.is_contiguous() and out.dtype == torch.float32
+        if images.dtype == torch.uint8:
+            fmt = L.UB_IMG_U8_NHWC
+            n, h, w, _ = images.shape
+        else:
+            fmt = L.UB_IMG_F32_NCHW
+            n, _, h, w = images.shape
+        assert tuple(out.shape) == (n, 3, h, w)
+        self._check(self.lib.ub_blur_images_static(self._handle(), ctypes.byref(perturbation.struct), _ptr(images), fmt,
+                                                   n, h, w, _ptr(out), _stream(self.device)), "ub_blur_images_static")
+        return out
+
     def metrics(self, logits: torch.Tensor, targets: torch.Tensor, ref_batch: int, want_dice: bool = False):
         logits = logits.to(self.device, torch.float32).contiguous()
         targets = targets.to(self.device).contiguous()

@@ -162,6 +162,22 @@ int ub_skip_decoder_forward(ub_ctx* ctx, const float* const* feats, int n_feats,
 int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,
                       const void* aux, int n, int h, int w, float* out_nchw, void* stream);
 
+/* The blur families of ub_perturb_images (UB_P_U8_BLUR / UB_P_F_BLUR, 0..64 passes) for callers that may not allocate
+ * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * NO COUNTERPART IN THE REFERENCE.  It runs the pass-per-launch blur (load /
+ * quantise, one launch per pass, result as fp32 [n,3,H,W] in out_nchw — bit-equal to ub_perturb_images) with its two
+ * ping-pong planes in a file-scope `static __device__` array instead of stream-ordered allocations: the call performs
+ * no cudaMalloc / cudaFree / cudaMallocAsync and calls no allocating library routine.
+ *   Limit: n*3*h*w <= UB_STATIC_BLUR_MAX_ELEMS (1 Mi elements: 5 images at 256x256, 1 at 512x512); larger calls
+ *   return UB_ERR_INVALID with a message naming the limit — split the call or use ub_perturb_images.
+ *   Cost: 2 x 4 MiB of device memory on every GPU that loads the library, held until the process exits.
+ *   Sharing: every call on a device uses the same planes.  Calls in one stream are ordered and safe; calls that overlap
+ *   on the GPU (different streams, no dependency) race.  The planes keep the last call's contents; nothing needs to
+ *   start at zero because each call writes every element it later reads. */
+#define UB_STATIC_BLUR_MAX_ELEMS (1u << 20)
+int ub_blur_images_static(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format, int n, int h,
+                          int w, float* out_nchw, void* stream);
+
 /* Dataset rows on the device (replaces the per-sample CPU work of customDatasets/datasets.py:92-160).
  * ub_decode_masks: raw trimap bytes [n, pixels] (38 cat / 75 dog / 255 border) -> class ids {0,1,2} with the
  *   reference's per-image rule (`_deserialize_datapoint`, datasets.py:118-131).  In place is allowed.
