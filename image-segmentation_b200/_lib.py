@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libunetb200.so")
 c_void_p, c_int, c_char_p, c_int64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_int64
 
 (UB_ARCH_UNET, UB_ARCH_LARGE_UNET, UB_ARCH_CLIP_UNET, UB_ARCH_CLIP_UNET_PROMPT,
- UB_ARCH_AUTOENCODER, UB_ARCH_ENCODER, UB_ARCH_SKIP_DECODER) = 0, 1, 2, 3, 4, 5, 6
+ UB_ARCH_AUTOENCODER, UB_ARCH_ENCODER, UB_ARCH_SKIP_DECODER, UB_ARCH_CLIP_VIT) = 0, 1, 2, 3, 4, 5, 6, 7
 UB_IMG_F32_NCHW, UB_IMG_U8_NHWC = 0, 1
 UB_TGT_I64, UB_TGT_U8 = 0, 1
 (UB_P_NONE, UB_P_U8_NOISE, UB_P_U8_BLUR, UB_P_U8_LUT, UB_P_U8_OCCLUSION, UB_P_U8_SALT_PEPPER, UB_P_F_NOISE,
@@ -46,6 +46,9 @@ SIGNATURES = {
     "ub_skip_decoder_forward": (c_int, [c_void_p, ctypes.POINTER(c_void_p), c_int, c_void_p, c_int, c_int, c_int, c_void_p]),
     "ub_perturb_images": (c_int, [c_void_p, ctypes.POINTER(ub_perturb), c_void_p, c_int, c_void_p, c_int, c_int,
                                   c_int, c_void_p, c_void_p]),
+    "ub_clip_image_features": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "ub_clip_dims": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
+    "ub_debug_clip_preprocess": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ub_blur_images_static": (c_int, [c_void_p, ctypes.POINTER(ub_perturb), c_void_p, c_int, c_int, c_int, c_int,
                                       c_void_p, c_void_p]),
     "ub_decode_masks": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),

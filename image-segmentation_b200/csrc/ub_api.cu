@@ -21,6 +21,7 @@
 #include "ub_conv_tc.cuh"
 #include "ub_conv_rs.cuh"
 #include "ub_perturb.cuh"
+#include "ub_vit.cuh"
 
 namespace {
 
@@ -42,6 +43,7 @@ struct HostTensor {
 struct GemmLayer {
   std::string key;  // state_dict prefix of the conv / up module
   int cin = 0, cout = 0, n_total = 0, ksize = 3, block_n = 0, bk = 64, relu = 1;
+  int act = 0;      // ub::EpiAct of the 1x1 STORE epilogue (the ViT's fc1: QuickGELU)
   int cin_src = 0;  // channels that exist in the source tensor when fewer than cin (the rest of the K range meets zero weights;
                     // the tensor map ends there, so TMA zero-fills those planes of the box without reading memory)
   bool is_convt = false;
@@ -61,6 +63,8 @@ struct Step {
   __nv_bfloat16* rs_out = nullptr;
   int hi = 0, wi = 0, ho = 0, wo = 0, c = 0, out_cgs = 0, out_cg0 = 0;
 };
+
+struct VitState;  // the CLIP ViT image tower (ub_vit_host.inl)
 
 struct Plan {
   int H = 0, W = 0;
@@ -117,6 +121,7 @@ struct ub_ctx {
   // kernel instantiations whose dynamic shared-memory opt-in has been made ON THIS CONTEXT'S DEVICE (the attribute
   // is per device and per function, so a second context on another GPU of the same process makes its own)
   std::set<const void*> smem_opt_in;
+  VitState* vit = nullptr;  // UB_ARCH_CLIP_VIT
   bool has_clip() const { return arch == UB_ARCH_CLIP_UNET || arch == UB_ARCH_CLIP_UNET_PROMPT; }
   bool is_half() const { return arch == UB_ARCH_ENCODER || arch == UB_ARCH_SKIP_DECODER; }
 };
@@ -314,8 +319,11 @@ int pack_conv1x1(ub_ctx* ctx, const std::string& key) {
   return UB_OK;
 }
 
+int pack_vit(ub_ctx* ctx);
+
 int pack_all(ub_ctx* ctx) {
   int rc;
+  if (ctx->arch == UB_ARCH_CLIP_VIT) return pack_vit(ctx);
   // the two halves of SegmentationModel hold one half of the weights each (models/autoencoder.py:5-26,
   // models/pre_trained.py:7-24); neither folds the stem (the decoder is handed the stem OUTPUT "x0")
   const bool enc_half = ctx->arch == UB_ARCH_ENCODER, dec_half = ctx->arch == UB_ARCH_SKIP_DECODER;
@@ -501,7 +509,7 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   cp->k_steps = (L.cin_src && L.cin == L.bk && L.cin_src < L.cin) ? (L.cin_src + 15) / 16 : 0;
   cp->B = B; cp->H = H; cp->W = W;
   cp->cin = L.cin; cp->ksize = L.ksize; cp->n_total = L.n_total;
-  cp->mode = mode; cp->relu = L.relu;
+  cp->mode = mode; cp->relu = L.relu; cp->act = L.act;
   cp->bias = L.bias; cp->n_bias = L.cout;
   cp->out = out; cp->out_cgs = out_cgs; cp->out_cg0 = out_cg0; cp->cout = L.cout;
   cp->n_classes = ctx->n_classes;
@@ -1104,6 +1112,8 @@ int check_ready(ub_ctx* ctx) {
   return UB_OK;
 }
 
+#include "ub_vit_host.inl"
+
 }  // namespace
 
 extern "C" {
@@ -1131,7 +1141,7 @@ int ub_make_lut(ub_perturb* p, int lut_kind, double param) {
 int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes, int max_microbatch) {
   if (!out) return UB_ERR_INVALID;
   *out = nullptr;
-  if (arch < UB_ARCH_UNET || arch > UB_ARCH_SKIP_DECODER)
+  if (arch < UB_ARCH_UNET || arch > UB_ARCH_CLIP_VIT)
     return fail(nullptr, UB_ERR_INVALID, "unknown arch %d", arch);
   if (in_channels != 3) return fail(nullptr, UB_ERR_UNSUPPORTED, "only in_channels=3 is supported");
   if (n_classes < 1 || n_classes > ub::kMaxClasses) return fail(nullptr, UB_ERR_UNSUPPORTED, "n_classes must be 1..%d", ub::kMaxClasses);
@@ -1177,6 +1187,7 @@ void ub_destroy(ub_ctx* ctx) {
   for (void* p : ctx->owned) cudaFree(p);
   for (auto& r : ctx->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
+  delete ctx->vit;
   delete ctx;
 }
 
@@ -1551,6 +1562,44 @@ int ub_blur_images_static(ub_ctx* ctx, const ub_perturb* p, const void* images, 
       b = a; a = o;
     }
   }
+  UB_CUDA(ctx, cudaGetLastError());
+  return UB_OK;
+}
+
+int ub_clip_image_features(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* feats, void* stream) {
+  int rc;
+  if ((rc = check_ready(ctx))) return rc;
+  if (ctx->arch != UB_ARCH_CLIP_VIT || !ctx->vit) return fail(ctx, UB_ERR_STATE, "ub_clip_image_features needs a UB_ARCH_CLIP_VIT context");
+  if (n == 0) return UB_OK;
+  if (!x_nchw || !feats || n < 0 || h <= 0 || w <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t img = static_cast<size_t>(3) * h * w;
+  for (int i0 = 0; i0 < n; i0 += ctx->max_mb) {
+    const int nb = (n - i0) < ctx->max_mb ? (n - i0) : ctx->max_mb;
+    if ((rc = vit_forward_chunk(ctx, x_nchw + img * i0, nb, h, w, feats + static_cast<size_t>(ctx->vit->E) * i0, st))) return rc;
+  }
+  return UB_OK;
+}
+
+int ub_clip_dims(const ub_ctx* ctx, int* image_size, int* embed_dim) {
+  if (!ctx || !ctx->vit) return UB_ERR_STATE;
+  if (image_size) *image_size = ctx->vit->S;
+  if (embed_dim) *embed_dim = ctx->vit->E;
+  return UB_OK;
+}
+
+int ub_debug_clip_preprocess(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* out_nchw, void* stream) {
+  int rc;
+  if ((rc = check_ready(ctx))) return rc;
+  if (ctx->arch != UB_ARCH_CLIP_VIT || !ctx->vit) return fail(ctx, UB_ERR_STATE, "ub_debug_clip_preprocess needs a UB_ARCH_CLIP_VIT context");
+  if (!x_nchw || !out_nchw || n <= 0 || h <= 0 || w <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
+  ub::ResizeTap *ry = nullptr, *rx = nullptr;
+  if ((rc = vit_taps(ctx, h, w, &ry, &rx))) return rc;
+  const int S = ctx->vit->S;
+  ub::clip_preprocess_kernel<<<blocks_for(static_cast<size_t>(n) * 3 * S * S, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x_nchw, n, h, w, ry, rx, S, kClipMean[0], kClipMean[1], kClipMean[2], 1.0f / kClipStd[0], 1.0f / kClipStd[1],
+      1.0f / kClipStd[2], out_nchw);
+  ctx->launches++;
   UB_CUDA(ctx, cudaGetLastError());
   return UB_OK;
 }

@@ -128,13 +128,21 @@
         // bias: packed fp32x2 adds.  bf16 rounding is monotone and keeps the sign, so ReLU and max-pool commute with
         // it: pack first, then ReLU (max with +0) and pool on the packed pairs — half the instructions, same result.
         uint32_t pk[16];
+        const float* bias_src = s_bias + bias_off;
+        if constexpr (KSIZE == 1) {
+          if (p.n_bias > kBiasStage) bias_src = p.bias + bias_off;  // wider than the staging area: straight from global (L1-resident)
+        }
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 bz = *reinterpret_cast<const float4*>(s_bias + bias_off + 4 * j4);
-          const float2 a = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 0]), __uint_as_float(r[4 * j4 + 1])),
-                                      make_float2(bz.x, bz.y));
-          const float2 c = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 2]), __uint_as_float(r[4 * j4 + 3])),
-                                      make_float2(bz.z, bz.w));
+          const float4 bz = *reinterpret_cast<const float4*>(bias_src + 4 * j4);
+          float2 a = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 0]), __uint_as_float(r[4 * j4 + 1])),
+                                make_float2(bz.x, bz.y));
+          float2 c = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 2]), __uint_as_float(r[4 * j4 + 3])),
+                                make_float2(bz.z, bz.w));
+          if constexpr (KSIZE == 1) {
+            // QuickGELU x * sigmoid(1.702 x) (CLIP's MLP activation; only the 1x1 instantiations carry the branch)
+            if (p.act == ACT_QUICK_GELU) { a = quick_gelu2(a); c = quick_gelu2(c); }
+          }
           pk[2 * j4 + 0] = pack_bf16(a.x, a.y);
           pk[2 * j4 + 1] = pack_bf16(c.x, c.y);
         }

@@ -49,6 +49,13 @@
 namespace ub {
 
 enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_CONVT = 2, EPI_HEAD = 3 };
+enum EpiAct : int { ACT_NONE = 0, ACT_QUICK_GELU = 1 };  // STORE epilogue of the 1x1 instantiations, after the bias (ReLU is `relu`)
+
+__device__ __forceinline__ float2 quick_gelu2(float2 v) {
+  v.x = __fdividef(v.x, 1.0f + __expf(-1.702f * v.x));
+  v.y = __fdividef(v.y, 1.0f + __expf(-1.702f * v.y));
+  return v;
+}
 
 constexpr int kTileM = 128;
 constexpr int kMaxEpiGroups = 4;
@@ -109,9 +116,11 @@ struct ConvParams {
   int a_planes;                // planes that exist in the view (cin_src / 8); planes beyond read as zero
   int sa;  // A stages (activation boxes)
   int sb;  // B stages when streaming weights; unused when the kernel is the WS instantiation
+  int act; // EpiAct (1x1 STORE only)
 };
 
 constexpr int kMaxSA = 8;
+constexpr int kBiasStage = 1024;  // biases staged in shared memory (ConvCfg::TAIL_BIAS)
 constexpr int kMaxSB = 8;
 constexpr int kMaxAcc = 4;
 constexpr int kSmemLimit = 232448;  // 227 KB, the sm_100 per-block maximum
@@ -138,7 +147,7 @@ struct ConvCfg {
   static constexpr int TMEM_COLS = ACC * ACC_STRIDE;
   // fixed-size tail in front of the two operand regions
   static constexpr int TAIL_BIAS = 0;
-  static constexpr int TAIL_HEAD = TAIL_BIAS + 1024 * 4;
+  static constexpr int TAIL_HEAD = TAIL_BIAS + kBiasStage * 4;
   static constexpr int TAIL_BAR = TAIL_HEAD + (kMaxClasses * 32 + kMaxClasses) * 4;
   static constexpr int N_BARS = 2 * kMaxSA + 2 * kMaxSB + 2 * kMaxAcc + 1;
   static constexpr int TAIL_CM = TAIL_BAR + N_BARS * 8;
@@ -267,7 +276,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p) {
   auto tile_b = [&](const TileIter& ti) { return (CG2 && !pairq) ? ti.d2 : ti.d3; };
 
   // ---------------- one-time setup (nothing here depends on the previous kernel's output)
-  for (int i = threadIdx.x; i < p.n_bias; i += kConvThreads) s_bias[i] = p.bias[i];
+  // (the staging area holds kBiasStage floats; wider 1x1 layers — the ViT's qkv and fc1 — read their bias from global memory)
+  for (int i = threadIdx.x; i < (p.n_bias < kBiasStage ? p.n_bias : kBiasStage); i += kConvThreads) s_bias[i] = p.bias[i];
   if (p.mode == EPI_HEAD) {
     if (threadIdx.x < kEpiGroups * kMaxClasses * kMaxClasses) s_cm_all[threadIdx.x] = 0ull;
     if (threadIdx.x < kEpiGroups * kMaxClasses * 2) s_dice_all[threadIdx.x] = 0.0;

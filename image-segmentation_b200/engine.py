@@ -115,7 +115,7 @@ class Engine:
         h = ctypes.c_void_p()
         archs = {"unet": L.UB_ARCH_UNET, "large": L.UB_ARCH_LARGE_UNET, "clip": L.UB_ARCH_CLIP_UNET,
                  "clip_prompt": L.UB_ARCH_CLIP_UNET_PROMPT, "autoencoder": L.UB_ARCH_AUTOENCODER,
-                 "encoder": L.UB_ARCH_ENCODER, "skip_decoder": L.UB_ARCH_SKIP_DECODER}
+                 "encoder": L.UB_ARCH_ENCODER, "skip_decoder": L.UB_ARCH_SKIP_DECODER, "clip_vit": L.UB_ARCH_CLIP_VIT}
         if arch not in archs:
             raise ValueError(f"unknown arch {arch!r}")
         self.arch = arch
@@ -280,6 +280,36 @@ class Engine:
         aux = perturbation.aux.to(self.device).contiguous() if perturbation.aux is not None else None
         self._check(self.lib.ub_perturb_images(self._handle(), ctypes.byref(perturbation.struct), _ptr(images), fmt, _ptr(aux),
                                                n, h, w, _ptr(out), _stream(self.device)), "ub_perturb_images")
+        return out
+
+    def clip_dims(self):
+        """(input size S, embedding width E) of a loaded 'clip_vit' engine."""
+        s, e = ctypes.c_int(), ctypes.c_int()
+        self._check(self.lib.ub_clip_dims(self._handle(), ctypes.byref(s), ctypes.byref(e)), "ub_clip_dims")
+        return s.value, e.value
+
+    def clip_image_features(self, x: torch.Tensor) -> torch.Tensor:
+        """ClipFeatureExtractor.forward (models/processing_blocks.py:219-233): fp32 [n,3,H,W] -> CLIP image embeddings
+        fp32 [n,E]; Resize + Normalize + ViT + projection, all in the library ('clip_vit' engines)."""
+        if self.arch != "clip_vit":
+            raise RuntimeError("clip_image_features needs an engine created with arch='clip_vit'")
+        x = x.to(self.device, torch.float32).contiguous()
+        n, c, h, w = x.shape
+        if c != 3:
+            raise ValueError("CLIP takes 3-channel images")
+        out = torch.empty((n, self.clip_dims()[1]), device=self.device, dtype=torch.float32)
+        self._check(self.lib.ub_clip_image_features(self._handle(), _ptr(x), n, h, w, _ptr(out), _stream(self.device)),
+                    "ub_clip_image_features")
+        return out
+
+    def clip_preprocess(self, x: torch.Tensor) -> torch.Tensor:
+        """CustomClipPreprocessor.forward alone (test hook): fp32 [n,3,H,W] -> fp32 [n,3,S,S]."""
+        x = x.to(self.device, torch.float32).contiguous()
+        n, _, h, w = x.shape
+        s = self.clip_dims()[0]
+        out = torch.empty((n, 3, s, s), device=self.device, dtype=torch.float32)
+        self._check(self.lib.ub_debug_clip_preprocess(self._handle(), _ptr(x), n, h, w, _ptr(out), _stream(self.device)),
+                    "ub_debug_clip_preprocess")
         return out
 
     def blur_static(self, images: torch.Tensor, perturbation: Perturbation, out: torch.Tensor) -> torch.Tensor:

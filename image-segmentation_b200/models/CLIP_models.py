@@ -22,10 +22,10 @@ class ClipUnet(_B200Net):
     _arch = "clip"
     _host_side_prefixes = ("clip_feature_extractor.",)
 
-    def __init__(self, out_channels=3, in_channels=3, activation=nn.Identity(), clip_model=None, clip_autocast_dtype=None):
+    def __init__(self, out_channels=3, in_channels=3, activation=nn.Identity(), clip_model=None, clip_autocast_dtype=None, clip_backend=None):
         super().__init__()
         self.clip_feature_extractor = ClipFeatureExtractor(train=False, clip_model=clip_model,
-                                                           autocast_dtype=clip_autocast_dtype)
+                                                           autocast_dtype=clip_autocast_dtype, backend=clip_backend)
         self.cross_attention_fusion = CrossAttentionFusion(512, num_heads=1)
         self.input = nn.Conv2d(in_channels, 32, kernel_size=1, padding=0)
         self.enc1 = ConvBlockDownsample(32, 64)

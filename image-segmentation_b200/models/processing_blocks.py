@@ -199,16 +199,24 @@ class CustomClipPreprocessor(nn.Module):
 
 
 class ClipFeatureExtractor(nn.Module):
-    """CLIP ViT-B/32 image embedding [B,512]; reference :171-233.  This is the one part of ClipUnet that is NOT
-    unet-b200 code: it runs HuggingFace `transformers`' CLIPModel with PyTorch kernels, exactly as the reference does.
+    """CLIP image embedding [B,E]; reference :171-233 (`CustomClipPreprocessor` + `CLIPModel.get_image_features`).
+
+    backend "b200" (default): Resize + Normalize + the ViT image tower + the visual projection all run in the library
+    (`ub_clip_image_features`: bf16 tensor-core GEMMs with fp32 accumulation, fp32 residual stream / LayerNorm / softmax);
+    the `clip_model` sub-module only holds the parameters (same state_dict keys as the reference, so checkpoints load).
+    backend "transformers": HuggingFace's CLIPModel on PyTorch kernels exactly as the reference runs it (fp32, or bf16
+    under CUDA autocast when `autocast_dtype` is given) — an explicit choice, never a silent fallback.
     `clip_model` lets a caller supply an already constructed CLIPModel (e.g. random-init where the
     `openai/clip-vit-base-patch32` checkpoint cannot be downloaded); the default loads the checkpoint like the
     reference (:209)."""
 
-    def __init__(self, train=False, clip_model=None, autocast_dtype=None):
-        """autocast_dtype: None = fp32 like the reference; torch.bfloat16 runs the ViT under CUDA autocast (about 7x
-        faster on B200, embedding within ~1e-2 of fp32) — an opt-in deviation, off by default."""
+    def __init__(self, train=False, clip_model=None, autocast_dtype=None, backend=None):
         super().__init__()
+        if backend is None:
+            backend = "transformers" if autocast_dtype is not None else "b200"
+        if backend not in ("b200", "transformers"):
+            raise ValueError(f"unknown CLIP backend {backend!r}")
+        self.backend = backend
         self.autocast_dtype = autocast_dtype
         self.device = torch.device('cuda' if torch.cuda.is_available() else 'cpu')
         mean = [0.48145466, 0.4578275, 0.40821073]
@@ -220,6 +228,8 @@ class ClipFeatureExtractor(nn.Module):
         self.clip_model = clip_model.to(self.device)
         self.train_clip = train
         self.set_train(train)
+        self._vit_engines = {}  # (device, max_microbatch) -> (weights key, Engine)
+        self._vit_params = None
 
     def set_train(self, value: bool):
         assert isinstance(value, bool), "Value must be a boolean"
@@ -229,7 +239,52 @@ class ClipFeatureExtractor(nn.Module):
             param.requires_grad = value
         self.train_clip = value
 
+    def _check_supported(self):
+        cfg = getattr(getattr(self.clip_model, "config", None), "vision_config", None)
+        if cfg is None:
+            raise RuntimeError("the b200 CLIP backend needs a HuggingFace CLIPModel (config.vision_config); "
+                               "pass backend='transformers' for anything else")
+        bad = []
+        if cfg.hidden_act != "quick_gelu":
+            bad.append(f"hidden_act {cfg.hidden_act!r} (quick_gelu)")
+        if abs(cfg.layer_norm_eps - 1e-5) > 1e-12:
+            bad.append(f"layer_norm_eps {cfg.layer_norm_eps} (1e-5)")
+        if cfg.num_attention_heads * 64 != cfg.hidden_size:
+            bad.append(f"head width {cfg.hidden_size // cfg.num_attention_heads} (64)")
+        if cfg.num_channels != 3:
+            bad.append(f"{cfg.num_channels} channels (3)")
+        if bad:
+            raise RuntimeError("CLIP vision tower not supported by the b200 backend: " + ", ".join(bad) +
+                               "; pass backend='transformers'")
+
+    def vit_engine(self, device, max_microbatch=None):
+        """The library context holding the packed vision tower (rebuilt when the weights change)."""
+        from .. import runtime
+        dev = torch.device(device)
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        mb = max_microbatch or runtime.default_microbatch()
+        if self._vit_params is None:
+            self._check_supported()
+            self._vit_params = [p for n, p in self.clip_model.named_parameters()
+                                if n.startswith("vision_model.") or n == "visual_projection.weight"]
+        wkey = tuple((p.data_ptr(), p._version) for p in self._vit_params)
+        slot = self._vit_engines.get((dev, mb))
+        if slot is None or slot[0] != wkey:
+            if slot is not None:
+                slot[1].close("the CLIP weights changed and the engine was rebuilt")
+            eng = runtime.new_engine(dev, "clip_vit", 3, 1, mb)
+            eng.load_state_dict({k: v for k, v in self.clip_model.state_dict().items()
+                                 if k.startswith("vision_model.") or k == "visual_projection.weight"})
+            self._vit_engines[(dev, mb)] = (wkey, eng)
+            slot = self._vit_engines[(dev, mb)]
+        return slot[1]
+
     def forward(self, X):
+        if self.backend == "b200":
+            if not X.is_cuda:
+                raise RuntimeError("unet-b200 has no CPU path: inputs must be CUDA tensors")
+            return self.vit_engine(X.device).clip_image_features(X)
         inputs = self.custom_preprocessor(X)
         with torch.no_grad(), torch.autocast("cuda", dtype=self.autocast_dtype or torch.bfloat16,
                                              enabled=self.autocast_dtype is not None and inputs.is_cuda):

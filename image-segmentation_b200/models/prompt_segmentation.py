@@ -37,11 +37,11 @@ class PromptEncoder(nn.Module):
 class ClipUnetPrompt(ClipUnet):
     _arch = "clip_prompt"
 
-    def __init__(self, out_channels=1, in_channels=3, activation=nn.Identity(), clip_model=None, clip_autocast_dtype=None):
+    def __init__(self, out_channels=1, in_channels=3, activation=nn.Identity(), clip_model=None, clip_autocast_dtype=None, clip_backend=None):
         nn.Module.__init__(self)
         # registration order follows the reference's __init__ (:33-61), so a seeded construction draws the same weights
         self.clip_feature_extractor = ClipFeatureExtractor(train=False, clip_model=clip_model,
-                                                           autocast_dtype=clip_autocast_dtype)
+                                                           autocast_dtype=clip_autocast_dtype, backend=clip_backend)
         self.cross_attention_fusion = CrossAttentionFusion(512, num_heads=1)
         self.input = nn.Conv2d(in_channels, 32, kernel_size=1, padding=0)
         self.enc1 = ConvBlockDownsample(32, 64)

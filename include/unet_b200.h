@@ -46,8 +46,12 @@ enum ub_arch {
                               (after the sigmoid), the evaluation entries do not apply */
   UB_ARCH_ENCODER = 5,      /* models/autoencoder.py:5-26 `Encoder` on its own (weights input.*, enc1-3.*, bottleneck.*):
                               ub_encoder_forward returns its dict of feature maps */
-  UB_ARCH_SKIP_DECODER = 6  /* models/pre_trained.py:7-24 `SegmentationDecoderSkip` on its own (weights dec1-4.*, out.*):
+  UB_ARCH_SKIP_DECODER = 6, /* models/pre_trained.py:7-24 `SegmentationDecoderSkip` on its own (weights dec1-4.*, out.*):
                               ub_skip_decoder_forward takes that dict and returns the logits */
+  UB_ARCH_CLIP_VIT = 7      /* models/processing_blocks.py:156-233 `ClipFeatureExtractor`: CustomClipPreprocessor (Resize +
+                              Normalize) and the CLIP ViT image tower + visual projection of HuggingFace CLIPModel
+                              (weights: its state_dict keys "vision_model.*", "visual_projection.weight");
+                              ub_clip_image_features.  ub_create's n_classes is ignored (pass 1) */
 };
 
 /* Input image container. */
@@ -157,6 +161,22 @@ int ub_encoder_forward(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, fl
                        void* stream);
 int ub_skip_decoder_forward(ub_ctx* ctx, const float* const* feats, int n_feats, float* logits_nchw, int n, int h,
                             int w, void* stream);
+
+/* Replaces ClipFeatureExtractor.forward (models/processing_blocks.py:219-233) for UB_ARCH_CLIP_VIT: x fp32 [n,3,H,W]
+ * (device; any H, W up to ~5x the CLIP input size) -> feats fp32 [n,E] (device), E = rows of visual_projection.weight.
+ *   CustomClipPreprocessor (:156-170): per image torchvision Resize((S,S)) on a tensor = bilinear with antialiasing,
+ *   align_corners=False, then Normalize with CLIP's mean / std — evaluated while the patch matrix is written;
+ *   CLIPModel.get_image_features (:228-231): patch embedding (Conv2d(3,D,P,stride P), no bias) + class token + position
+ *   embedding, pre_layrnorm, L pre-norm encoder layers (LayerNorm -> multi-head self-attention (head width 64) -> +,
+ *   LayerNorm -> fc1 -> QuickGELU -> fc2 -> +), post_layernorm of the class token, visual_projection (no bias).
+ * The linear maps run on the tensor cores in bf16 with fp32 accumulation; residual stream, LayerNorm statistics and
+ * softmax are fp32.  Supported towers: hidden size a multiple of 256 up to 1024 with heads = hidden / 64, MLP width a
+ * multiple of 256, patch size a multiple of 8, at most 64 tokens per image (ViT-B/32 at 224x224: 768 / 12 / 3072 / 32 / 50),
+ * hidden_act quick_gelu, layer_norm_eps 1e-5.  ub_clip_dims reports S and E once the weights are loaded. */
+int ub_clip_image_features(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* feats, void* stream);
+int ub_clip_dims(const ub_ctx* ctx, int* image_size, int* embed_dim);
+/* Test hook: CustomClipPreprocessor.forward alone (models/processing_blocks.py:163-170): out fp32 [n,3,S,S]. */
+int ub_debug_clip_preprocess(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* out_nchw, void* stream);
 
 /* Perturbation alone (the Dataset wrappers' __getitem__ / the nn.Modules' forward): out fp32 [n,3,H,W]. */
 int ub_perturb_images(ub_ctx* ctx, const ub_perturb* p, const void* images, int image_format,

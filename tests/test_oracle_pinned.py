@@ -186,13 +186,52 @@ def test_clipunet_tree_and_oracle_against_reference_golden():
     assert state_checksum(sd) == str(g["final_state_sha256"])
     x = synthetic.to_float_nchw(torch.from_numpy(g["images_u8"]))
     if not torch.cuda.is_available():         # the extractor lives on the GPU when there is one
-        feats = m.clip_feature_extractor(x)
+        from image_segmentation_b200.models.processing_blocks import ClipFeatureExtractor
+        feats = ClipFeatureExtractor(clip_model=clip, backend="transformers")(x)   # (the default backend is GPU-only)
         assert float((feats - torch.from_numpy(g["clip_feats"])).abs().max()) <= 1e-4 * float(np.abs(g["clip_feats"]).max())
     logits = unet_oracle.forward(sd, x, clip_feats=torch.from_numpy(g["clip_feats"]))
     ref = torch.from_numpy(g["logits"])
     assert float((logits - ref).abs().max()) <= 2e-5 * float(ref.abs().max())
     with pytest.raises(RuntimeError):
         m(x)                                  # no CPU path
+
+
+def test_clip_oracle_pinned_to_torchvision_and_the_reference_golden():
+    """oracle/clip_oracle.py (the checker of ub_clip_image_features): its Resize + Normalize restatement equals
+    torchvision's own transforms bit for bit (and the reference's CustomClipPreprocessor where /root/reference is
+    present), its embedding of the golden images equals the embedding the REFERENCE's ClipFeatureExtractor produced
+    (tests/golden/clipunet_small.npz, made by oracle/make_golden.py through the reference's class), and the tower
+    written out from the state_dict equals transformers' own forward."""
+    from torchvision import transforms
+    from transformers import CLIPConfig, CLIPModel
+    from image_segmentation_b200 import synthetic
+    from oracle import clip_oracle as co
+    gen = torch.Generator().manual_seed(3)
+    tv = transforms.Compose([transforms.Resize((224, 224)), transforms.Normalize(mean=co.CLIP_MEAN, std=co.CLIP_STD)])
+    for hw in ((256, 256), (224, 224), (200, 300), (97, 131), (512, 384)):
+        x = torch.rand((2, 3) + hw, generator=gen)
+        want = torch.stack([tv(img) for img in x])
+        assert torch.equal(co.preprocess(x), want), hw
+    if refload.available():
+        ns = refload.load()
+        ref_pre = ns.blocks.CustomClipPreprocessor(mean=list(co.CLIP_MEAN), std=list(co.CLIP_STD))
+        x = torch.rand((2, 3, 256, 256), generator=gen)
+        assert torch.equal(co.preprocess(x), ref_pre(x))
+    g = np.load(os.path.join(GOLD, "clipunet_small.npz"))
+    torch.manual_seed(0)
+    clip = CLIPModel(CLIPConfig()).eval()     # the stand-in checkpoint of oracle/refload.py: CLIPConfig() at seed 0
+    x = synthetic.to_float_nchw(torch.from_numpy(g["images_u8"]))
+    feats = co.image_features(clip, x)
+    ref = torch.from_numpy(g["clip_feats"])
+    assert float((feats - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+    cfg = clip.config.vision_config
+    restated = co.vit_restated(clip.state_dict(), co.preprocess(x), cfg.num_attention_heads, cfg.layer_norm_eps)
+    assert float((restated - ref).abs().max()) <= 1e-4 * float(ref.abs().max())
+    small = co.seeded_clip(seed=3, small=True)
+    scfg = small.config.vision_config
+    a = co.image_features(small, x)
+    b = co.vit_restated(small.state_dict(), co.preprocess(x), scfg.num_attention_heads, scfg.layer_norm_eps)
+    assert float((a - b).abs().max()) <= 1e-4 * float(a.abs().max())
 
 
 def test_autoencoder_tree_and_oracle_against_reference_golden():
