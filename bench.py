@@ -226,12 +226,19 @@ def use_large_workload(world):
 
 def use_clip_workload():
     """Secondary workload: ClipUnet on the headline sweep.  The CLIP ViT-B/32 embedding (random-init here: the
-    checkpoint needs the network) is HuggingFace transformers on PyTorch fp32 kernels, as in the reference, and is
-    inside the timed step; the library's share is the UNet minus the (dead) bottleneck block."""
+    checkpoint needs the network) is inside the timed step: the library's own ViT by default, HuggingFace transformers
+    on PyTorch kernels with UB_CLIP_BACKEND=transformers[-bf16]; the U-Net part is the UNet minus the (dead) bottleneck."""
     global CLIP, GFLOP_PER_IMAGE, GEMM_GFLOP_PER_IMAGE
     CLIP = True
     GFLOP_PER_IMAGE = 45.391 - 2 * 3.624          # without bottleneck.conv.0/.3 (1.208 + 2.416 GMAC)
     GEMM_GFLOP_PER_IMAGE = 2 * (21.744 - 3.624 + 0.940)
+
+
+def clip_backend():
+    be = os.environ.get("UB_CLIP_BACKEND", "b200")
+    if be not in ("b200", "transformers", "transformers-bf16"):
+        raise SystemExit(f"UB_CLIP_BACKEND={be!r}: b200 | transformers | transformers-bf16")
+    return be
 
 
 def net_class():
@@ -239,8 +246,12 @@ def net_class():
     if CLIP:
         from transformers import CLIPConfig, CLIPModel
         from image_segmentation_b200.models.CLIP_models import ClipUnet
-        dt = torch.bfloat16 if os.environ.get("UB_CLIP_DTYPE") == "bf16" else None   # default fp32, as the reference
-        return lambda: ClipUnet(clip_model=CLIPModel(CLIPConfig()).eval(), clip_autocast_dtype=dt)
+        # UB_CLIP_BACKEND: "b200" (default: the library's ViT), "transformers" (HuggingFace on PyTorch kernels, fp32 as the
+        # reference) or "transformers-bf16" (the same under bf16 autocast)
+        be = clip_backend()
+        return lambda: ClipUnet(clip_model=CLIPModel(CLIPConfig()).eval(),
+                                clip_autocast_dtype=torch.bfloat16 if be == "transformers-bf16" else None,
+                                clip_backend="b200" if be == "b200" else "transformers")
     return LargeUNet if LARGE else UNet
 
 
@@ -250,8 +261,9 @@ def base_line(args, world):
                 "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "data": "synthetic",
                 "config": {"workload": "robustness_evaluation sweep levels over 3,680 synthetic 256x256 RGB images, ClipUnet "
-                                       "random-init (CLIP ViT-B/32 random-init via transformers, "
-                                       + ("bf16 autocast" if os.environ.get("UB_CLIP_DTYPE") == "bf16" else "fp32") + ", inside the step), "
+                                       "random-init (CLIP ViT-B/32 random-init, "
+                                       + {"b200": "the library's ViT (bf16 GEMMs)", "transformers": "transformers fp32",
+                                          "transformers-bf16": "transformers under bf16 autocast"}[clip_backend()] + ", inside the step), "
                                        "reference batch 8", "images_per_step": N_IMAGES, "ref_batch": REF_BATCH,
                            "l2": "inputs_exceed_l2 (965 MB of images+masks per step)"}}
     if LARGE:
@@ -364,6 +376,22 @@ def extra_measurements(dev):
                                           "PromptEncoder + fusion + dec1-4 + head -> logits (configs[4])"}
     except Exception as e:
         out["clip_prompt_224"] = {"error": repr(e)[:200]}
+    # (f4) the CLIP image embedding itself (models/processing_blocks.py:156-233: Resize + Normalize + ViT-B/32 + projection)
+    # in the library, 244 images (two internal passes of 122) at 256x256, random-init tower
+    try:
+        from transformers import CLIPConfig, CLIPModel
+        from image_segmentation_b200.models.processing_blocks import ClipFeatureExtractor
+        torch.manual_seed(42)
+        ext = ClipFeatureExtractor(clip_model=CLIPModel(CLIPConfig()).eval())
+        x = synthetic.to_float_nchw(synthetic.make_dataset(61, 256, 256, seed=7)[0]).repeat(4, 1, 1, 1).to(dev)
+        ms = timed_forward(lambda: ext(x))
+        out["clip_vit_b32_256"] = {"images_per_s": 244 / (ms * 1e-3), "ms_per_step": ms, "images_per_step": 244,
+                                   "tflops": 244 * 8.74e9 / (ms * 1e-3) / 1e12,
+                                   "what": "CLIP ViT-B/32 image embedding in the library (resize 256->224 + normalise + "
+                                           "12 layers + projection), 244 images"}
+        del ext
+    except Exception as e:
+        out["clip_vit_b32_256"] = {"error": repr(e)[:200]}
     return out
 
 

@@ -47,7 +47,7 @@ SIGNATURES = {
     "ub_perturb_images": (c_int, [c_void_p, ctypes.POINTER(ub_perturb), c_void_p, c_int, c_void_p, c_int, c_int,
                                   c_int, c_void_p, c_void_p]),
     "ub_clip_image_features": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
-    "ub_clip_dims": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
+    "ub_clip_dims": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "ub_debug_clip_preprocess": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ub_blur_images_static": (c_int, [c_void_p, ctypes.POINTER(ub_perturb), c_void_p, c_int, c_int, c_int, c_int,
                                       c_void_p, c_void_p]),

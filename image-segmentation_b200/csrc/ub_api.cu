@@ -1574,17 +1574,19 @@ int ub_clip_image_features(ub_ctx* ctx, const float* x_nchw, int n, int h, int w
   if (!x_nchw || !feats || n < 0 || h <= 0 || w <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t img = static_cast<size_t>(3) * h * w;
-  for (int i0 = 0; i0 < n; i0 += ctx->max_mb) {
-    const int nb = (n - i0) < ctx->max_mb ? (n - i0) : ctx->max_mb;
+  const int chunk = ctx->vit->chunk;
+  for (int i0 = 0; i0 < n; i0 += chunk) {
+    const int nb = (n - i0) < chunk ? (n - i0) : chunk;
     if ((rc = vit_forward_chunk(ctx, x_nchw + img * i0, nb, h, w, feats + static_cast<size_t>(ctx->vit->E) * i0, st))) return rc;
   }
   return UB_OK;
 }
 
-int ub_clip_dims(const ub_ctx* ctx, int* image_size, int* embed_dim) {
+int ub_clip_dims(const ub_ctx* ctx, int* image_size, int* embed_dim, int* chunk) {
   if (!ctx || !ctx->vit) return UB_ERR_STATE;
   if (image_size) *image_size = ctx->vit->S;
   if (embed_dim) *embed_dim = ctx->vit->E;
+  if (chunk) *chunk = ctx->vit->chunk;
   return UB_OK;
 }
 

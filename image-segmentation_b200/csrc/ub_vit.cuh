@@ -39,35 +39,46 @@ __device__ __forceinline__ float clip_resized(const float* __restrict__ plane, i
 
 // Resize + Normalize written as the patch matrix of the embedding conv (Conv2d(3, D, P, stride P, bias=False)):
 //   A[kg][t][8],  k = c*P*P + py*P + px  (the conv weight's own flattening),  t = image * G*G + gy*G + gx.
-// One thread per (k group, patch token): 8 horizontally adjacent output pixels -> one 16-byte store; consecutive threads
-// are consecutive tokens of one plane (coalesced stores; the gathers hit L1/L2).
+// Block (gy, c, image): the P-row x S-column band of channel c that feeds patch row gy.  Phase 1 resamples it with lanes
+// along the output columns (coalesced reads of the input rows) into shared memory as bf16; phase 2 writes it out as
+// 16-byte items, consecutive threads on consecutive tokens of one k-group plane.
+// Dynamic shared memory: ResizeTap[S] (the column taps) | bf16[P][S].
+__host__ __device__ constexpr int clip_patch_smem_bytes(int P, int G) {
+  return G * P * static_cast<int>(sizeof(ResizeTap)) + P * G * P * 2;
+}
+
 __global__ void __launch_bounds__(256)
 clip_patch_kernel(const float* __restrict__ x, int n, int H, int W, const ResizeTap* __restrict__ ry,
                   const ResizeTap* __restrict__ rx, int P, int G, float m0, float m1, float m2, float is0, float is1,
                   float is2, __nv_bfloat16* __restrict__ out, int tp) {
-  const int tokens = n * G * G;
-  const int kgs_per_c = P * P / 8;
-  const size_t total = static_cast<size_t>(3 * kgs_per_c) * tokens;
-  const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  const int t = static_cast<int>(idx % tokens);
-  const int kg = static_cast<int>(idx / tokens);
-  const int c = kg / kgs_per_c, rem = kg % kgs_per_c;
-  const int py = rem / (P / 8), px0 = (rem % (P / 8)) * 8;
-  const int img = t / (G * G), g = t % (G * G);
-  const int oy = (g / G) * P + py, ox0 = (g % G) * P + px0;
+  extern __shared__ __align__(16) unsigned char patch_sm[];
+  const int S = G * P;
+  ResizeTap* s_rx = reinterpret_cast<ResizeTap*>(patch_sm);
+  __nv_bfloat16* band = reinterpret_cast<__nv_bfloat16*>(patch_sm + S * sizeof(ResizeTap));
+  const int gy = blockIdx.x, c = blockIdx.y, img = blockIdx.z, tid = threadIdx.x;
+  (void)n;
+  {
+    const int words = S * static_cast<int>(sizeof(ResizeTap) / 4);
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(rx);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(s_rx);
+    for (int i = tid; i < words; i += 256) dst[i] = src[i];
+  }
+  __syncthreads();
   const float mean = c == 0 ? m0 : (c == 1 ? m1 : m2), inv_std = c == 0 ? is0 : (c == 1 ? is1 : is2);
   const float* plane = x + (static_cast<size_t>(img) * 3 + c) * H * W;
-  const ResizeTap ty = ry[oy];
-  uint4 o;
-  __nv_bfloat162* op = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const float a = (clip_resized(plane, W, ty, rx[ox0 + 2 * j]) - mean) * inv_std;
-    const float b = (clip_resized(plane, W, ty, rx[ox0 + 2 * j + 1]) - mean) * inv_std;
-    op[j] = __floats2bfloat162_rn(a, b);
+  for (int i = tid; i < P * S; i += 256) {
+    const int py = i / S, ox = i % S;
+    band[i] = __float2bfloat16((clip_resized(plane, W, ry[gy * P + py], s_rx[ox]) - mean) * inv_std);
   }
-  reinterpret_cast<uint4*>(out)[static_cast<size_t>(kg) * tp + t] = o;
+  __syncthreads();
+  const int pg = P / 8;
+  for (int i = tid; i < P * pg * G; i += 256) {
+    const int gx = i % G, px8 = (i / G) % pg, py = i / (G * pg);
+    const int kg = c * (P * pg) + py * pg + px8;
+    const int t = (img * G + gy) * G + gx;
+    reinterpret_cast<uint4*>(out)[static_cast<size_t>(kg) * tp + t] =
+        *reinterpret_cast<const uint4*>(band + py * S + gx * P + px8 * 8);
+  }
 }
 
 // The same arithmetic as fp32 NCHW [n,3,S,S] (test hook: pins the resize against torchvision).
@@ -193,127 +204,133 @@ vit_ln_kernel(float* __restrict__ resid, const __nv_bfloat16* __restrict__ branc
   }
 }
 
-// ---- Multi-head self-attention of one (head, image): softmax(q k^T / sqrt(64)) v over ntok <= 64 tokens, fp32 in shared
-// memory (CLIPAttention, eager path: scores scaled, softmax in fp32, no mask in the vision tower).
-// qkv bf16 [3D/8][tp][8] with q | k | v stacked along the channels; out bf16 [D/8][tp][8].
-// Dynamic shared memory: q[ntok][65] | k[ntok][65] | v[ntok][64] | s[ntok][ntok + 1] floats.
-__host__ __device__ constexpr int vit_attn_smem_bytes(int ntok) { return 4 * (ntok * 65 * 2 + ntok * 64 + ntok * (ntok + 1)); }
+// ---- Multi-head self-attention of one (head, image): softmax(q k^T / sqrt(64)) v over ntok <= 64 tokens (CLIPAttention,
+// eager path: scores scaled, softmax in fp32, no mask in the vision tower).  qkv bf16 [3D/8][tp][8] with q | k | v
+// stacked along the channels; out bf16 [D/8][tp][8].
+// 50 x 50 x 64 per head is far below the 128-row minimum of a tcgen05 tile, so the two small products run on the
+// warp-level tensor-core path (mma.sync m16n8k16, bf16 x bf16 -> fp32): warp w owns query rows [16w, 16w+16), the scores
+// stay in registers (the accumulator fragment of q k^T IS the A fragment of p v), softmax statistics in fp32 across the
+// four lanes of a row.  Shared memory: q | k | v as [64][72] bf16 (144-byte rows: conflict-free ldmatrix), rows >= ntok zero.
+constexpr int kAttnLd = 72;
+constexpr int kAttnSmemBytes = 3 * kVitMaxTokens * kAttnLd * 2;
+
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], const void* smem_ptr) {
+  const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(smem_ptr));
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* smem_ptr) {
+  const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(smem_ptr));
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
+  const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&v);
+}
 
 __global__ void __launch_bounds__(128)
 vit_attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int D, int ntok, int tp) {
-  extern __shared__ float vit_sm[];
-  float* sq = vit_sm;
-  float* sk = sq + ntok * 65;
-  float* sv = sk + ntok * 65;
-  float* ss = sv + ntok * 64;
-  const int head = blockIdx.x, img = blockIdx.y, tid = threadIdx.x;
+  __shared__ __align__(16) __nv_bfloat16 sm[3 * kVitMaxTokens * kAttnLd];
+  __nv_bfloat16* sq = sm;
+  __nv_bfloat16* sk = sm + kVitMaxTokens * kAttnLd;
+  __nv_bfloat16* sv = sm + 2 * kVitMaxTokens * kAttnLd;
+  const int head = blockIdx.x, img = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int t0 = img * ntok;
-  const int ld_s = ntok + 1;
-  // load: 3 matrices x 8 channel groups x ntok tokens of 16 bytes
-  for (int i = tid; i < 3 * 8 * ntok; i += 128) {
-    const int tok = i % ntok, g = (i / ntok) % 8, m = i / (8 * ntok);
-    const uint4 q = reinterpret_cast<const uint4*>(qkv)[static_cast<size_t>(m * (D / 8) + head * 8 + g) * tp + t0 + tok];
-    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
-    float* dst = (m == 0 ? sq + tok * 65 : (m == 1 ? sk + tok * 65 : sv + tok * 64)) + 8 * g;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) { const float2 f = __bfloat1622float2(h[j]); dst[2 * j] = f.x; dst[2 * j + 1] = f.y; }
+  // load: 3 matrices x 8 channel groups x 64 token rows of 16 bytes (rows >= ntok: zeros)
+  for (int i = tid; i < 3 * 8 * kVitMaxTokens; i += 128) {
+    const int tok = i % kVitMaxTokens, g = (i / kVitMaxTokens) % 8, m = i / (8 * kVitMaxTokens);
+    uint4 q = make_uint4(0u, 0u, 0u, 0u);
+    if (tok < ntok) q = reinterpret_cast<const uint4*>(qkv)[static_cast<size_t>(m * (D / 8) + head * 8 + g) * tp + t0 + tok];
+    *reinterpret_cast<uint4*>(sm + (m * kVitMaxTokens + tok) * kAttnLd + 8 * g) = q;
   }
   __syncthreads();
-  // scores: 5 x 5 register tiles
-  const int nt5 = (ntok + 4) / 5;
-  for (int tile = tid; tile < nt5 * nt5; tile += 128) {
-    const int i0 = (tile / nt5) * 5, j0 = (tile % nt5) * 5;
-    float acc[5][5];
+  if (16 * warp >= ntok) return;  // (no barrier follows)
+  // scores S[16 rows][64 keys] = q k^T: 4 k-steps (16 dims each) x 8 key tiles
+  float sc[8][4];
 #pragma unroll
-    for (int a = 0; a < 5; ++a)
+  for (int nt = 0; nt < 8; ++nt)
 #pragma unroll
-      for (int b = 0; b < 5; ++b) acc[a][b] = 0.0f;
-    const float* qp[5];
-    const float* kp[5];
+    for (int j = 0; j < 4; ++j) sc[nt][j] = 0.0f;
 #pragma unroll
-    for (int a = 0; a < 5; ++a) {
-      qp[a] = sq + min(i0 + a, ntok - 1) * 65;
-      kp[a] = sk + min(j0 + a, ntok - 1) * 65;
+  for (int ks = 0; ks < 4; ++ks) {
+    uint32_t a[4];
+    ldmatrix_x4(a, sq + (16 * warp + (lane & 15)) * kAttnLd + 16 * ks + 8 * (lane >> 4));
+#pragma unroll
+    for (int np = 0; np < 4; ++np) {  // two key tiles per ldmatrix: (keys 16np..+7 | +8..+15) x (dims 16ks..+7 | +8..+15)
+      uint32_t b[4];
+      ldmatrix_x4(b, sk + (16 * np + 8 * (lane >> 4) + (lane & 7)) * kAttnLd + 16 * ks + 8 * ((lane >> 3) & 1));
+      mma_bf16_16816(sc[2 * np], a, b[0], b[1]);
+      mma_bf16_16816(sc[2 * np + 1], a, b[2], b[3]);
     }
-#pragma unroll 4
-    for (int d = 0; d < 64; ++d) {
-      float qa[5], kb[5];
-#pragma unroll
-      for (int a = 0; a < 5; ++a) { qa[a] = qp[a][d]; kb[a] = kp[a][d]; }
-#pragma unroll
-      for (int a = 0; a < 5; ++a)
-#pragma unroll
-        for (int b = 0; b < 5; ++b) acc[a][b] = fmaf(qa[a], kb[b], acc[a][b]);
-    }
-#pragma unroll
-    for (int a = 0; a < 5; ++a)
-#pragma unroll
-      for (int b = 0; b < 5; ++b)
-        if (i0 + a < ntok && j0 + b < ntok) ss[(i0 + a) * ld_s + j0 + b] = acc[a][b] * 0.125f;
   }
-  __syncthreads();
-  // softmax: one warp per row
-  for (int i = tid >> 5; i < ntok; i += 4) {
-    const int lane = tid & 31;
-    float* row = ss + i * ld_s;
-    const float a = lane < ntok ? row[lane] : -INFINITY, b = lane + 32 < ntok ? row[lane + 32] : -INFINITY;
-    float mx = fmaxf(a, b);
+  // softmax over the keys of rows r0 = lane/4 and r0 + 8 (this thread: columns 8nt + 2(lane%4) + {0,1})
+  float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    const float ea = lane < ntok ? expf(a - mx) : 0.0f, eb = lane + 32 < ntok ? expf(b - mx) : 0.0f;
-    float sum = ea + eb;
+  for (int nt = 0; nt < 8; ++nt) {
+    const int c = 8 * nt + 2 * (lane & 3);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (lane < ntok) row[lane] = ea / sum;
-    if (lane + 32 < ntok) row[lane + 32] = eb / sum;
+    for (int j = 0; j < 2; ++j) {
+      const bool ok = c + j < ntok;
+      sc[nt][j] = ok ? sc[nt][j] * 0.125f : -INFINITY;
+      sc[nt][2 + j] = ok ? sc[nt][2 + j] * 0.125f : -INFINITY;
+      mx0 = fmaxf(mx0, sc[nt][j]);
+      mx1 = fmaxf(mx1, sc[nt][2 + j]);
+    }
   }
-  __syncthreads();
-  // out = p v: 5 tokens x 8 channels (one channel group) per thread
-  for (int tile = tid; tile < nt5 * 8; tile += 128) {
-    const int i0 = (tile / 8) * 5, g = tile % 8;
-    float acc[5][8];
+  mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+  mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+  float sum0 = 0.0f, sum1 = 0.0f;
+  uint32_t pa[4][4];  // p as the A operand of p v: key block kb = score tiles 2kb, 2kb+1
 #pragma unroll
-    for (int a = 0; a < 5; ++a)
+  for (int nt = 0; nt < 8; ++nt) {
+    const float e0 = expf(sc[nt][0] - mx0), e1 = expf(sc[nt][1] - mx0), e2 = expf(sc[nt][2] - mx1), e3 = expf(sc[nt][3] - mx1);
+    sum0 += e0 + e1;
+    sum1 += e2 + e3;
+    pa[nt >> 1][(nt & 1) * 2 + 0] = pack2_bf16(e0, e1);
+    pa[nt >> 1][(nt & 1) * 2 + 1] = pack2_bf16(e2, e3);
+  }
+  sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+  sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+  // out[16 rows][64 dims] = p v: 4 key blocks x 8 dim tiles
+  float oc[8][4];
 #pragma unroll
-      for (int b = 0; b < 8; ++b) acc[a][b] = 0.0f;
-    const float* pp[5];
+  for (int nt = 0; nt < 8; ++nt)
 #pragma unroll
-    for (int a = 0; a < 5; ++a) pp[a] = ss + min(i0 + a, ntok - 1) * ld_s;
-    for (int j = 0; j < ntok; ++j) {
-      const float4 v0 = *reinterpret_cast<const float4*>(sv + j * 64 + 8 * g);
-      const float4 v1 = *reinterpret_cast<const float4*>(sv + j * 64 + 8 * g + 4);
+    for (int j = 0; j < 4; ++j) oc[nt][j] = 0.0f;
 #pragma unroll
-      for (int a = 0; a < 5; ++a) {
-        const float p = pp[a][j];
-        acc[a][0] = fmaf(p, v0.x, acc[a][0]); acc[a][1] = fmaf(p, v0.y, acc[a][1]);
-        acc[a][2] = fmaf(p, v0.z, acc[a][2]); acc[a][3] = fmaf(p, v0.w, acc[a][3]);
-        acc[a][4] = fmaf(p, v1.x, acc[a][4]); acc[a][5] = fmaf(p, v1.y, acc[a][5]);
-        acc[a][6] = fmaf(p, v1.z, acc[a][6]); acc[a][7] = fmaf(p, v1.w, acc[a][7]);
-      }
+  for (int kb = 0; kb < 4; ++kb) {
+#pragma unroll
+    for (int np = 0; np < 4; ++np) {  // (keys 16kb..+7 | +8..+15) x (dims 16np..+7 | +8..+15), transposed on load
+      uint32_t b[4];
+      ldmatrix_x4_trans(b, sv + (16 * kb + 8 * ((lane >> 3) & 1) + (lane & 7)) * kAttnLd + 16 * np + 8 * (lane >> 4));
+      mma_bf16_16816(oc[2 * np], pa[kb], b[0], b[1]);
+      mma_bf16_16816(oc[2 * np + 1], pa[kb], b[2], b[3]);
     }
+  }
+  const float inv0 = 1.0f / sum0, inv1 = 1.0f / sum1;
+  const int r0 = 16 * warp + (lane >> 2), r1 = r0 + 8;
 #pragma unroll
-    for (int a = 0; a < 5; ++a) {
-      if (i0 + a >= ntok) continue;
-      uint4 o;
-      __nv_bfloat162* op = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) op[j] = __floats2bfloat162_rn(acc[a][2 * j], acc[a][2 * j + 1]);
-      reinterpret_cast<uint4*>(out)[static_cast<size_t>(head * 8 + g) * tp + t0 + i0 + a] = o;
-    }
+  for (int nt = 0; nt < 8; ++nt) {  // dim tile nt = channel group nt of this head: a quad writes its 16 bytes
+    uint32_t* dst = reinterpret_cast<uint32_t*>(out) + (static_cast<size_t>(head * 8 + nt) * tp + t0) * 4 + (lane & 3);
+    if (r0 < ntok) dst[static_cast<size_t>(r0) * 4] = pack2_bf16(oc[nt][0] * inv0, oc[nt][1] * inv0);
+    if (r1 < ntok) dst[static_cast<size_t>(r1) * 4] = pack2_bf16(oc[nt][2] * inv1, oc[nt][3] * inv1);
   }
 }
 
-// ---- pooled output: post_layernorm of the CLS token, then visual_projection (Linear(D, E, bias=False)); one block per
-// image, fp32 throughout.  feats [n][E].  `branch`: the last encoder layer's fc2 output, not yet added to the stream.
+// ---- pooled output: post_layernorm of the CLS token, then visual_projection (Linear(D, E, bias=False)), fp32 throughout.
+// Block (image, 64-output slice): the normalised CLS vector is recomputed per slice (D values), each warp then owns 8
+// outputs.  feats [n][E].  `branch`: the last encoder layer's fc2 output, not yet added to the residual stream.
 __global__ void __launch_bounds__(256)
 vit_pool_proj_kernel(const float* __restrict__ resid, const __nv_bfloat16* __restrict__ branch, int D, int ntok, int tp,
-                     const float* __restrict__ gamma,
-                     const float* __restrict__ beta, float eps, const float* __restrict__ w_proj, int E,
-                     float* __restrict__ feats) {
+                     const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                     const float* __restrict__ w_proj, int E, float* __restrict__ feats) {
   __shared__ float pooled[kVitMaxDim];
   __shared__ float red[8];
   __shared__ float stat[2];
-  const int img = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int img = blockIdx.x, e0 = blockIdx.y * 64, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int t = img * ntok;  // the CLS token
   float loc = 0.0f;
   for (int d = tid; d < D; d += 256) {
@@ -340,7 +357,7 @@ vit_pool_proj_kernel(const float* __restrict__ resid, const __nv_bfloat16* __res
   const float rstd = stat[1];
   for (int d = tid; d < D; d += 256) pooled[d] = (pooled[d] - mean) * rstd * gamma[d] + beta[d];
   __syncthreads();
-  for (int e = warp; e < E; e += 8) {
+  for (int e = e0 + warp; e < min(e0 + 64, E); e += 8) {
     const float* wr = w_proj + static_cast<size_t>(e) * D;
     float acc = 0.0f;
     for (int d = lane; d < D; d += 32) acc = fmaf(wr[d], pooled[d], acc);

@@ -9,6 +9,7 @@ struct VitPlanN {  // everything that depends on the number of images of a chunk
 
 struct VitState {
   int D = 0, L = 0, I = 0, P = 0, G = 0, S = 0, ntok = 0, E = 0;
+  int chunk = 0;  // images per internal pass (vit_pick_chunk)
   float eps = 1e-5f;
   std::vector<int> lin;  // indices into ctx->layers, same order as VitPlanN::gemm
   float *cls = nullptr, *pos = nullptr, *pre_g = nullptr, *pre_b = nullptr, *post_g = nullptr, *post_b = nullptr,
@@ -87,6 +88,8 @@ int alloc_zeroed(ub_ctx* ctx, void** p, size_t bytes) {
   return UB_OK;
 }
 
+int vit_pick_chunk(const ub_ctx* ctx, const VitState* v);
+
 int pack_vit(ub_ctx* ctx) {
   std::unique_ptr<VitState> v(new VitState());
   const std::string vm = "vision_model.";
@@ -156,6 +159,8 @@ int pack_vit(ub_ctx* ctx) {
   if ((rc = alloc_zeroed(ctx, reinterpret_cast<void**>(&v->branch), tp * D * 2))) return rc;
   if ((rc = alloc_zeroed(ctx, reinterpret_cast<void**>(&v->mlp), tp * static_cast<size_t>(v->I) * 2))) return rc;
   UB_CUDA(ctx, cudaDeviceSynchronize());
+  v->chunk = vit_pick_chunk(ctx, v.get());
+  { const char* e = getenv("UB_VIT_CHUNK"); if (e && atoi(e) >= 1 && atoi(e) <= ctx->max_mb) v->chunk = atoi(e); }  // (experiment)
   ctx->vit = v.release();
   ctx->weights_ready = true;
   return UB_OK;
@@ -266,6 +271,26 @@ int vit_launch_ln(ub_ctx* ctx, int ns, int blocks, cudaStream_t st, float* resid
   return UB_OK;
 }
 
+// Images per chunk.  The four GEMMs of a layer are small (ViT-B/32, 122 images: 72 / 216 / 288 CTA-pair tiles), so how many
+// whole waves of the 74 CTA pairs their tile counts make decides a third of their time: 128 images give 75 tiles for the
+// two D -> D maps (two waves, the second one 1/74 full), 122 images give 72 (one wave).  Pick the chunk size <= max_mb that
+// minimises the waves spent per image, FLOP-weighted over the four shapes.
+int vit_pick_chunk(const ub_ctx* ctx, const VitState* v) {
+  const int slots = ctx->num_sms / 2 > 0 ? ctx->num_sms / 2 : 1;
+  const int nt[4] = {3 * v->D / 256, v->D / 256, v->I / 256, v->D / 256};                  // n-tiles: qkv, out_proj, fc1, fc2
+  const double kw[4] = {double(v->D), double(v->D), double(v->D), double(v->I)};           // time of one tile ~ K
+  int best = ctx->max_mb;
+  double best_cost = 1e300;
+  for (int n = ctx->max_mb; n >= 1 && n >= ctx->max_mb / 2; --n) {
+    const int pairs = (n * v->ntok + 255) / 256;
+    double cost = 0.0;
+    for (int i = 0; i < 4; ++i) cost += kw[i] * ((pairs * nt[i] + slots - 1) / slots);
+    cost /= n;
+    if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = n; }
+  }
+  return best;
+}
+
 // One chunk of at most max_mb images: x fp32 [n,3,H,W] (values as the caller's model sees them, i.e. [0,1]) -> feats [n,E].
 int vit_forward_chunk(ub_ctx* ctx, const float* x, int n, int H, int W, float* feats, cudaStream_t st) {
   VitState* v = ctx->vit;
@@ -276,10 +301,15 @@ int vit_forward_chunk(ub_ctx* ctx, const float* x, int n, int H, int W, float* f
   if ((rc = vit_plan(ctx, n, &pl))) return rc;
   const int ns = v->D / 256;
   {
-    const size_t total = static_cast<size_t>(3 * v->P * v->P / 8) * pl->ptokens;
-    ub::clip_patch_kernel<<<blocks_for(total, 256), 256, 0, st>>>(x, n, H, W, ry, rx, v->P, v->G, kClipMean[0], kClipMean[1],
-                                                                   kClipMean[2], 1.0f / kClipStd[0], 1.0f / kClipStd[1],
-                                                                   1.0f / kClipStd[2], v->patches, pl->tp_p);
+    const int smem = ub::clip_patch_smem_bytes(v->P, v->G);
+    const void* fn = reinterpret_cast<const void*>(&ub::clip_patch_kernel);
+    if (smem > 48 * 1024 && !ctx->smem_opt_in.count(fn)) {
+      UB_CUDA(ctx, cudaFuncSetAttribute(ub::clip_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      ctx->smem_opt_in.insert(fn);
+    }
+    ub::clip_patch_kernel<<<dim3(v->G, 3, n), 256, smem, st>>>(x, n, H, W, ry, rx, v->P, v->G, kClipMean[0], kClipMean[1], kClipMean[2],
+                                                             1.0f / kClipStd[0], 1.0f / kClipStd[1], 1.0f / kClipStd[2],
+                                                             v->patches, pl->tp_p);
     ctx->launches++;
     UB_CUDA(ctx, cudaGetLastError());
   }
@@ -292,22 +322,13 @@ int vit_forward_chunk(ub_ctx* ctx, const float* x, int n, int H, int W, float* f
   if ((rc = vit_launch_ln<ub::VIT_LN_EMBED>(ctx, ns, ln_blocks, st, v->resid, nullptr, v->pre_g, v->pre_b, v->eps, nullptr, pl->tokens,
                                             pl->tp, v->patch_out, pl->tp_p, v->cls, v->pos, v->ntok)))
     return rc;
-  const int attn_smem = ub::vit_attn_smem_bytes(v->ntok);
-  {
-    const void* fn = reinterpret_cast<const void*>(&ub::vit_attention_kernel);
-    if (attn_smem > 48 * 1024 && !ctx->smem_opt_in.count(fn)) {
-      UB_CUDA(ctx, cudaFuncSetAttribute(ub::vit_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        ub::vit_attn_smem_bytes(ub::kVitMaxTokens)));
-      ctx->smem_opt_in.insert(fn);
-    }
-  }
   for (int l = 0; l < v->L; ++l) {
     // layer_norm1 (the previous layer's MLP output joins the residual stream here)
     if ((rc = vit_launch_ln<ub::VIT_LN_ADD>(ctx, ns, ln_blocks, st, v->resid, l ? v->branch : nullptr, v->ln1_g[l], v->ln1_b[l], v->eps,
                                             v->ln_out, pl->tokens, pl->tp, nullptr, 0, nullptr, nullptr, v->ntok)))
       return rc;
     if ((rc = run_gemm(1 + 4 * l + 0))) return rc;
-    ub::vit_attention_kernel<<<dim3(v->D / ub::kVitHeadDim, n), 128, attn_smem, st>>>(v->qkv, v->attn, v->D, v->ntok, pl->tp);
+    ub::vit_attention_kernel<<<dim3(v->D / ub::kVitHeadDim, n), 128, 0, st>>>(v->qkv, v->attn, v->D, v->ntok, pl->tp);
     ctx->launches++;
     UB_CUDA(ctx, cudaGetLastError());
     if ((rc = run_gemm(1 + 4 * l + 1))) return rc;
@@ -317,7 +338,7 @@ int vit_forward_chunk(ub_ctx* ctx, const float* x, int n, int H, int W, float* f
     if ((rc = run_gemm(1 + 4 * l + 2))) return rc;
     if ((rc = run_gemm(1 + 4 * l + 3))) return rc;
   }
-  ub::vit_pool_proj_kernel<<<n, 256, 0, st>>>(v->resid, v->branch, v->D, v->ntok, pl->tp, v->post_g, v->post_b, v->eps, v->w_proj,
+  ub::vit_pool_proj_kernel<<<dim3(n, (v->E + 63) / 64), 256, 0, st>>>(v->resid, v->branch, v->D, v->ntok, pl->tp, v->post_g, v->post_b, v->eps, v->w_proj,
                                               v->E, feats);
   ctx->launches++;
   UB_CUDA(ctx, cudaGetLastError());

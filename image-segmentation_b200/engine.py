@@ -283,10 +283,12 @@ class Engine:
         return out
 
     def clip_dims(self):
-        """(input size S, embedding width E) of a loaded 'clip_vit' engine."""
-        s, e = ctypes.c_int(), ctypes.c_int()
-        self._check(self.lib.ub_clip_dims(self._handle(), ctypes.byref(s), ctypes.byref(e)), "ub_clip_dims")
-        return s.value, e.value
+        """(input size S, embedding width E, images per internal pass) of a loaded 'clip_vit' engine."""
+        if getattr(self, "_clip_dims", None) is None:
+            s, e, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+            self._check(self.lib.ub_clip_dims(self._handle(), ctypes.byref(s), ctypes.byref(e), ctypes.byref(c)), "ub_clip_dims")
+            self._clip_dims = (s.value, e.value, c.value)
+        return self._clip_dims
 
     def clip_image_features(self, x: torch.Tensor) -> torch.Tensor:
         """ClipFeatureExtractor.forward (models/processing_blocks.py:219-233): fp32 [n,3,H,W] -> CLIP image embeddings

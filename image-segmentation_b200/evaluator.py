@@ -182,7 +182,8 @@ class RobustnessEvaluator:
             return
         # ClipUnet (models/CLIP_models.py:114-131): the CLIP embedding is taken from the image the network sees, i.e.
         # AFTER the perturbation, so the perturbed batch is materialised, embedded, and then evaluated unperturbed.
-        step = max(1, self.engine.max_microbatch // self.ref_batch) * self.ref_batch
+        # (several micro-batches per pass: the library's ViT and U-Net split it by their own wave quanta, 122 and 148 images)
+        step = max(1, 8 * self.engine.max_microbatch // self.ref_batch) * self.ref_batch
         n = images.shape[0]
         for i0 in range(0, n, step):
             i1 = min(i0 + step, n)

@@ -172,9 +172,11 @@ int ub_skip_decoder_forward(ub_ctx* ctx, const float* const* feats, int n_feats,
  * The linear maps run on the tensor cores in bf16 with fp32 accumulation; residual stream, LayerNorm statistics and
  * softmax are fp32.  Supported towers: hidden size a multiple of 256 up to 1024 with heads = hidden / 64, MLP width a
  * multiple of 256, patch size a multiple of 8, at most 64 tokens per image (ViT-B/32 at 224x224: 768 / 12 / 3072 / 32 / 50),
- * hidden_act quick_gelu, layer_norm_eps 1e-5.  ub_clip_dims reports S and E once the weights are loaded. */
+ * hidden_act quick_gelu, layer_norm_eps 1e-5.  ub_clip_dims reports S, E and the number of images the library embeds per
+ * internal pass (chosen <= max_microbatch so that the GEMM tile counts fill whole waves of the SMs; callers that batch
+ * should hand over multiples of it) once the weights are loaded. */
 int ub_clip_image_features(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* feats, void* stream);
-int ub_clip_dims(const ub_ctx* ctx, int* image_size, int* embed_dim);
+int ub_clip_dims(const ub_ctx* ctx, int* image_size, int* embed_dim, int* chunk);
 /* Test hook: CustomClipPreprocessor.forward alone (models/processing_blocks.py:163-170): out fp32 [n,3,S,S]. */
 int ub_debug_clip_preprocess(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* out_nchw, void* stream);
 

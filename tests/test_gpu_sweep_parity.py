@@ -131,7 +131,7 @@ def test_script_sweep_all_80_levels_config1(trained, dev, data, tmp_path):
     di, dm = imgs.to(dev), masks.to(dev)
     u8 = imgs.permute(0, 3, 1, 2).numpy()
     differ = total = 0
-    worst = []
+    worst, gaps = [], []
     for fam, levels in R.PERTURBATIONS.items():
         for li, level in enumerate(levels):
             state = (random.getstate(), torch.get_rng_state())
@@ -152,10 +152,13 @@ def test_script_sweep_all_80_levels_config1(trained, dev, data, tmp_path):
             assert abs(dice - got_rows[(fam, li)]) < 1e-5, (fam, level)                    # what the CSV holds
             for name, a, b in (("IoU", iou, o["iou"]), ("PixelAccuracy", pa, o["pa"]), ("2I/(1+I)", wd, o["wdice"]),
                                ("soft Dice", dice, o["dice"])):
-                assert abs(a - b) < POINT1, (fam, level, name, a, b)
+                gaps.append((abs(a - b), fam, level, name))
     worst.sort()
+    gaps.sort(reverse=True)
     print(f"script sweep, 80 levels x {N} images: pooled argmax agreement {1 - differ / total:.6f}; lowest levels: "
-          + ", ".join(f"{f} {l}: {a:.5f}" for a, f, l in worst[:4]))
+          + ", ".join(f"{f} {l}: {a:.5f}" for a, f, l in worst[:4]) + "; largest metric gaps to the oracle: "
+          + ", ".join(f"{f} {l} {n}: {d:.2e}" for d, f, l, n in gaps[:3]))
+    assert gaps[0][0] < POINT1, gaps[:3]
     assert 1 - differ / total >= 0.999
     assert worst[0][0] >= 0.995
 
@@ -224,7 +227,7 @@ def test_testwrapper_robustness_all_79_levels_config1(trained, dev, data, tmp_pa
     eng = tw.model.engine(dev)
     dm = masks.to(dev)
     differ = total = 0
-    worst = []
+    worst, gaps = [], []
     for fname, cls_name, sl in WRAPPER_FILES:
         for row, level in zip(csv_rows[(fname, cls_name)], levels_all[cls_name][sl]):
             assert float(row["Parameter Value"]) == float(level)
@@ -247,9 +250,12 @@ def test_testwrapper_robustness_all_79_levels_config1(trained, dev, data, tmp_pa
             differ += d; total += pred.numel()
             worst.append((1.0 - d / pred.numel(), cls_name, level))
             for col, key in (("Avg IoU Loss", "iou"), ("Avg Pixel Accuracy Loss", "pa"), ("Avg Dice Loss", "wdice")):
-                assert abs(float(row[col]) - o[key]) < POINT1, (cls_name, level, col, row[col], o[key])
+                gaps.append((abs(float(row[col]) - o[key]), cls_name, level, col))
     worst.sort()
+    gaps.sort(reverse=True)
     print(f"TestWrapper.test_robustness, 79 levels x {N} images: pooled argmax agreement {1 - differ / total:.6f}; "
-          "lowest levels: " + ", ".join(f"{f} {l}: {a:.5f}" for a, f, l in worst[:4]))
+          "lowest levels: " + ", ".join(f"{f} {l}: {a:.5f}" for a, f, l in worst[:4]) + "; largest metric gaps to the oracle: "
+          + ", ".join(f"{f} {l} {n}: {d:.2e}" for d, f, l, n in gaps[:3]))
+    assert gaps[0][0] < POINT1, gaps[:3]
     assert 1 - differ / total >= 0.999
     assert worst[0][0] >= 0.995

@@ -1,5 +1,6 @@
 """Times ub_clip_image_features (the library's CLIP ViT-B/32 image tower) on one GPU: images/s for a batch of 128 at 256x256,
-next to HuggingFace transformers on the same GPU in fp32 and under bf16 autocast.  Usage: python tools/time_clip_vit.py [n]"""
+next to HuggingFace transformers on the same GPU in fp32 and under bf16 autocast.
+Usage: python tools/time_clip_vit.py [n] [ours]     ("ours": one warm-up and one timed pass of the library only — the ncu launch list)"""
 import sys
 import time
 
@@ -31,8 +32,11 @@ def main():
     ours = ClipFeatureExtractor(clip_model=m)
     hf32 = ClipFeatureExtractor(clip_model=m, backend="transformers")
     hf16 = ClipFeatureExtractor(clip_model=m, backend="transformers", autocast_dtype=torch.bfloat16)
-    for name, f in (("library ViT (bf16 GEMMs)", ours), ("transformers fp32", hf32), ("transformers bf16 autocast", hf16)):
-        ms = timed(lambda: f(x))
+    only_ours = len(sys.argv) > 2 and sys.argv[2] == "ours"
+    arms = (("library ViT (bf16 GEMMs)", ours),) if only_ours else (
+        ("library ViT (bf16 GEMMs)", ours), ("transformers fp32", hf32), ("transformers bf16 autocast", hf16))
+    for name, f in arms:
+        ms = timed(lambda: f(x), reps=1 if only_ours else 10, warm=1 if only_ours else 3)
         print(f"{name:32s} {ms:8.3f} ms per {n} images = {n / ms * 1e3:9.0f} images/s")
     eng = ours.vit_engine(dev)
     eng.profile_begin()
