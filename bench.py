@@ -454,7 +454,7 @@ def run_gpu(args, rank, world, local_rank):
     # N > 1: the boards of a box settle at different power-capped clocks and a sharded level ends with its slowest
     # rank, so the reference batches are re-split once, in proportion to each rank's warm rate (untimed, part of warm-up)
     rates = None
-    if world > 1 and not args.no_rebalance:
+    if world > 1 and args.rebalance:
         rates = ev.rebalance(images, masks, ev.local_rate(spec_of(0), steps=2))
         for i in range(2):
             submit(i).wait()
@@ -520,9 +520,15 @@ def run_gpu(args, rank, world, local_rank):
         allreduce_us = max_over_ranks(a0.elapsed_time(a1) / 20 * 1e3)
 
     # ---- roofline of the dominant kernel (tcgen05 implicit-GEMM conv / ConvT), per-launch CUDA events
+    # (the share of the step is taken against the duration of the SAME two profiled steps: with an event pair around every
+    # launch they run without launch overlap, so dividing by the un-profiled step time overstates it — 1.04 at N = 8)
     eng.profile_begin()
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record()
     step(1); step(2)
+    p1.record()
     gemm_ms, gemm_launches, rows = eng.profile_end()
+    prof_ms = p0.elapsed_time(p1)
     pk, pk_src = peaks()
     gemm_tflops = GEMM_GFLOP_PER_IMAGE * 1e9 * ev.n_local * 2 / (gemm_ms * 1e-3) / 1e12
     peak = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
@@ -530,7 +536,7 @@ def run_gpu(args, rank, world, local_rank):
                 "achieved": gemm_tflops, "peak": peak, "unit": "TFLOP/s", "frac": gemm_tflops / peak,
                 "peak_source": pk_src + ", sustained figure (kernel timed inside a long step)",
                 "frac_of_burst_peak": gemm_tflops / pk["bf16_tflops"], "traffic": None, "traffic_unit": "bytes/launch",
-                "gemm_share_of_step": gemm_ms / 2 / (my_ms / args.steps),
+                "gemm_share_of_step": gemm_ms / prof_ms, "profiled_step_ms": prof_ms / 2,
                 "flops_per_launch": GEMM_GFLOP_PER_IMAGE * 1e9 * ev.n_local * 2 / max(gemm_launches, 1),
                 "avg_launch_ms": gemm_ms / max(gemm_launches, 1)}
     # DRAM bytes per launch: ncu --set full capture of the same build (profiles/), headline workload only — ncu cannot
@@ -597,7 +603,11 @@ def main():
     ap.add_argument("--layers", action="store_true", help="print the per-layer GEMM times to stderr")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the short secondary measurements (extra)")
-    ap.add_argument("--no-rebalance", action="store_true", help="N > 1: keep the equal split of reference batches")
+    ap.add_argument("--rebalance", action="store_true",
+                    help="N > 1: re-split the reference batches in proportion to each rank's warm rate (default: equal split — on "
+                         "power-capped boards of one box the 2-step warm rates are noisier than the boards differ; measured "
+                         "-0.5 to -0.7 %% at N = 8)")
+    ap.add_argument("--no-rebalance", action="store_true", help="(accepted for older command lines; the equal split is the default)")
     ap.add_argument("--workload", default="unet256", choices=["unet256", "large512", "clipunet256"],
                     help="unet256 = the headline (BASELINE.json configs[1]); large512 = configs[2]; clipunet256: secondary")
     args = ap.parse_args()
