@@ -17,6 +17,7 @@ UB_TGT_I64, UB_TGT_U8 = 0, 1
 (UB_P_NONE, UB_P_U8_NOISE, UB_P_U8_BLUR, UB_P_U8_LUT, UB_P_U8_OCCLUSION, UB_P_U8_SALT_PEPPER, UB_P_F_NOISE,
  UB_P_F_BLUR, UB_P_F_CONTRAST, UB_P_F_BRIGHTNESS, UB_P_F_OCCLUSION, UB_P_F_SALT_PEPPER) = range(12)
 UB_LUT_CONTRAST, UB_LUT_BRIGHTNESS_INCREASE, UB_LUT_BRIGHTNESS_DECREASE = 0, 1, 2
+UB_CLIP_MAX_TAPS = 12  # ub_clip_resize_taps: weights per output coordinate
 UB_STATIC_BLUR_MAX_ELEMS = 1 << 20  # ub_blur_images_static: n*3*h*w limit of the static scratch planes
 
 
@@ -47,6 +48,7 @@ SIGNATURES = {
     "ub_perturb_images": (c_int, [c_void_p, ctypes.POINTER(ub_perturb), c_void_p, c_int, c_void_p, c_int, c_int,
                                   c_int, c_void_p, c_void_p]),
     "ub_clip_image_features": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "ub_clip_resize_taps": (c_int, [c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "ub_clip_dims": (c_int, [c_void_p, ctypes.POINTER(c_int), ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "ub_debug_clip_preprocess": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "ub_blur_images_static": (c_int, [c_void_p, ctypes.POINTER(ub_perturb), c_void_p, c_int, c_int, c_int, c_int,

@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -1578,6 +1579,19 @@ int ub_clip_image_features(ub_ctx* ctx, const float* x_nchw, int n, int h, int w
   for (int i0 = 0; i0 < n; i0 += chunk) {
     const int nb = (n - i0) < chunk ? (n - i0) : chunk;
     if ((rc = vit_forward_chunk(ctx, x_nchw + img * i0, nb, h, w, feats + static_cast<size_t>(ctx->vit->E) * i0, st))) return rc;
+  }
+  return UB_OK;
+}
+
+int ub_clip_resize_taps(int in_size, int out_size, int32_t* start, int32_t* count, float* weights) {
+  if (in_size <= 0 || out_size <= 0 || !start || !count || !weights) return UB_ERR_INVALID;
+  std::vector<ub::ResizeTap> taps;
+  const int rc = make_resize_taps(nullptr, in_size, out_size, &taps);
+  if (rc) return rc;
+  for (int i = 0; i < out_size; ++i) {
+    start[i] = taps[i].start;
+    count[i] = taps[i].count;
+    memcpy(weights + static_cast<size_t>(i) * UB_CLIP_MAX_TAPS, taps[i].w, sizeof(float) * UB_CLIP_MAX_TAPS);
   }
   return UB_OK;
 }

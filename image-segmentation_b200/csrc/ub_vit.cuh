@@ -11,12 +11,14 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/unet_b200.h"
+
 namespace ub {
 
 constexpr int kVitHeadDim = 64;     // every OpenAI CLIP ViT: hidden / heads = 64
 constexpr int kVitMaxTokens = 64;   // tokens per image the attention kernel holds in shared memory (ViT-B/32 @224: 50)
 constexpr int kVitMaxDim = 1024;    // hidden size limit of the LayerNorm kernels (4 x 256)
-constexpr int kClipMaxTaps = 12;    // antialiased-resize taps per axis (input up to ~5x the output size)
+constexpr int kClipMaxTaps = UB_CLIP_MAX_TAPS;  // antialiased-resize taps per axis (12: input up to ~5x the output size)
 
 // One output coordinate of torchvision's Resize on a tensor = F.interpolate(mode="bilinear", antialias=True,
 // align_corners=False) (ATen UpSampleKernel.cpp, _compute_indices_weights_aa): first input index, tap count, and the

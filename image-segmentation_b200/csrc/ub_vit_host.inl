@@ -205,6 +205,16 @@ int vit_taps(ub_ctx* ctx, int H, int W, ub::ResizeTap** ry, ub::ResizeTap** rx) 
   VitState* v = ctx->vit;
   auto it = v->taps.find({H, W});
   if (it == v->taps.end()) {
+    if (v->taps.size() >= 32) {  // a caller sweeping input sizes: drop the cached tables once nothing can be reading them
+      UB_CUDA(ctx, cudaDeviceSynchronize());
+      for (auto& kv : v->taps) {
+        for (void* p : {static_cast<void*>(kv.second.first), static_cast<void*>(kv.second.second)}) {
+          cudaFree(p);
+          ctx->owned.erase(std::find(ctx->owned.begin(), ctx->owned.end(), p));
+        }
+      }
+      v->taps.clear();
+    }
     std::vector<ub::ResizeTap> hy, hx;
     int rc;
     if ((rc = make_resize_taps(ctx, H, v->S, &hy))) return rc;

@@ -177,6 +177,12 @@ int ub_skip_decoder_forward(ub_ctx* ctx, const float* const* feats, int n_feats,
  * should hand over multiples of it) once the weights are loaded. */
 int ub_clip_image_features(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* feats, void* stream);
 int ub_clip_dims(const ub_ctx* ctx, int* image_size, int* embed_dim, int* chunk);
+/* Host-only helper (no GPU needed): the per-axis taps of that Resize for in_size -> out_size, as ATen's
+ * _compute_indices_weights_aa builds them for bilinear + antialias (torchvision Resize on a tensor): output coordinate i
+ * reads inputs [start[i], start[i] + count[i]) with weights[i*UB_CLIP_MAX_TAPS + j].  Arrays of out_size entries
+ * (weights: out_size * UB_CLIP_MAX_TAPS).  UB_ERR_UNSUPPORTED when an output needs more than UB_CLIP_MAX_TAPS inputs. */
+#define UB_CLIP_MAX_TAPS 12
+int ub_clip_resize_taps(int in_size, int out_size, int32_t* start, int32_t* count, float* weights);
 /* Test hook: CustomClipPreprocessor.forward alone (models/processing_blocks.py:163-170): out fp32 [n,3,S,S]. */
 int ub_debug_clip_preprocess(ub_ctx* ctx, const float* x_nchw, int n, int h, int w, float* out_nchw, void* stream);
 

@@ -148,3 +148,39 @@ def test_weighted_batch_range_partitions_every_batch_once():
     import pytest
     with pytest.raises(ValueError):
         batch_range(10, 0, 2, [1.0, 0.0])
+
+
+@pytest.mark.parametrize("n_in,n_out", [(256, 224), (224, 224), (200, 224), (300, 224), (512, 224), (100, 224), (1000, 224),
+                                        (97, 64), (131, 160)])
+def test_clip_resize_taps_reproduce_antialiased_bilinear(lib, n_in, n_out):
+    """`ub_clip_resize_taps` (host code; the tables `clip_patch_kernel` resamples with): applied separably in numpy they
+    reproduce torchvision's Resize on a tensor = F.interpolate(bilinear, antialias=True, align_corners=False)
+    (CustomClipPreprocessor, models/processing_blocks.py:156-170)."""
+    from image_segmentation_b200 import _lib
+    T = _lib.UB_CLIP_MAX_TAPS
+    start = np.zeros(n_out, dtype=np.int32)
+    count = np.zeros(n_out, dtype=np.int32)
+    w = np.zeros((n_out, T), dtype=np.float32)
+    assert lib.ub_clip_resize_taps(n_in, n_out, start.ctypes.data, count.ctypes.data, w.ctypes.data) == 0
+    assert (count >= 1).all() and (count <= T).all() and (start >= 0).all() and (start + count <= n_in).all()
+    assert np.allclose(w.sum(1), 1.0, atol=1e-6) and (w >= 0).all()
+    m = np.zeros((n_out, n_in), dtype=np.float64)            # the resampling matrix of one axis
+    for i in range(n_out):
+        m[i, start[i]:start[i] + count[i]] = w[i, :count[i]]
+    g = torch.Generator().manual_seed(n_in * 1000 + n_out)
+    x = torch.rand((1, 2, n_in, 57), generator=g)
+    want = torch.nn.functional.interpolate(x, size=(n_out, 57), mode="bilinear", antialias=True, align_corners=False)
+    got = np.einsum("oi,bciw->bcow", m, x.numpy().astype(np.float64))
+    assert np.abs(got - want.numpy()).max() < 2e-6
+    want_w = torch.nn.functional.interpolate(x.transpose(2, 3), size=(57, n_out), mode="bilinear", antialias=True, align_corners=False)
+    assert np.abs(np.einsum("oi,bcwi->bcwo", m, x.transpose(2, 3).numpy().astype(np.float64)) - want_w.numpy()).max() < 2e-6
+
+
+def test_clip_resize_taps_refuse_more_than_the_tap_limit(lib):
+    from image_segmentation_b200 import _lib
+    n_out = 224
+    start = np.zeros(n_out, dtype=np.int32); count = np.zeros(n_out, dtype=np.int32)
+    w = np.zeros((n_out, _lib.UB_CLIP_MAX_TAPS), dtype=np.float32)
+    assert lib.ub_clip_resize_taps(1400, n_out, start.ctypes.data, count.ctypes.data, w.ctypes.data) == -3   # UB_ERR_UNSUPPORTED
+    assert b"taps per axis" in lib.ub_last_error(None)
+    assert lib.ub_clip_resize_taps(0, n_out, start.ctypes.data, count.ctypes.data, w.ctypes.data) == -1
