@@ -6,12 +6,17 @@
 // Token tensors use the library's channel-blocked layout with the token index in place of the pixel index:
 //   X[d/8][tp][8]   (tp = tokens rounded up to a multiple of 8 = the "image" is tp/8 rows of 8 tokens)
 // bf16 for GEMM operands / results, fp32 for the residual stream.  Token t = image * ntok + position (position 0 = CLS).
+//
+// Programmatic dependent launch: every kernel here releases its dependents at once (the next GEMM's CTAs run their prologue —
+// barrier init, TMEM allocation, descriptor prefetch — beside these small blocks) and touches global memory only after
+// griddepcontrol.wait, i.e. after the preceding grid has completed and flushed: no read or write can overtake it.
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include "../../include/unet_b200.h"
+#include "ub_ptx.cuh"
 
 namespace ub {
 
@@ -59,13 +64,15 @@ clip_patch_kernel(const float* __restrict__ x, int n, int H, int W, const Resize
   __nv_bfloat16* band = reinterpret_cast<__nv_bfloat16*>(patch_sm + S * sizeof(ResizeTap));
   const int gy = blockIdx.x, c = blockIdx.y, img = blockIdx.z, tid = threadIdx.x;
   (void)n;
-  {
+  pdl_launch_dependents();
+  {  // (the tap tables are constants uploaded when the input size was first seen: readable before the wait)
     const int words = S * static_cast<int>(sizeof(ResizeTap) / 4);
     const uint32_t* src = reinterpret_cast<const uint32_t*>(rx);
     uint32_t* dst = reinterpret_cast<uint32_t*>(s_rx);
     for (int i = tid; i < words; i += 256) dst[i] = src[i];
   }
   __syncthreads();
+  pdl_wait_prior_grid();
   const float mean = c == 0 ? m0 : (c == 1 ? m1 : m2), inv_std = c == 0 ? is0 : (c == 1 ? is1 : is2);
   const float* plane = x + (static_cast<size_t>(img) * 3 + c) * H * W;
   for (int i = tid; i < P * S; i += 256) {
@@ -137,6 +144,8 @@ vit_ln_kernel(float* __restrict__ resid, const __nv_bfloat16* __restrict__ branc
   const int tid = threadIdx.x;
   const int t = blockIdx.x * 8 + (tid & 7);
   const bool live = t < tokens;
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
   float v[NS][8];
 #pragma unroll
   for (int k = 0; k < NS; ++k) {
@@ -241,6 +250,8 @@ vit_attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __res
   __nv_bfloat16* sv = sm + 2 * kVitMaxTokens * kAttnLd;
   const int head = blockIdx.x, img = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int t0 = img * ntok;
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
   // load: 3 matrices x 8 channel groups x 64 token rows of 16 bytes (rows >= ntok: zeros)
   for (int i = tid; i < 3 * 8 * kVitMaxTokens; i += 128) {
     const int tok = i % kVitMaxTokens, g = (i / kVitMaxTokens) % 8, m = i / (8 * kVitMaxTokens);
@@ -334,6 +345,8 @@ vit_pool_proj_kernel(const float* __restrict__ resid, const __nv_bfloat16* __res
   __shared__ float stat[2];
   const int img = blockIdx.x, e0 = blockIdx.y * 64, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int t = img * ntok;  // the CLS token
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
   float loc = 0.0f;
   for (int d = tid; d < D; d += 256) {
     const size_t at = (static_cast<size_t>(d >> 3) * tp + t) * 8 + (d & 7);

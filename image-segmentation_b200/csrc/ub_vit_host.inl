@@ -22,6 +22,28 @@ struct VitState {
   std::map<std::pair<int, int>, std::pair<ub::ResizeTap*, ub::ResizeTap*>> taps;  // (H, W) -> device tables (rows, columns)
 };
 
+// Launch with the programmatic-stream-serialization attribute (the kernels of ub_vit.cuh wait with griddepcontrol.wait
+// before their first global access); UB_NO_PDL=1: plain stream order.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(const ub_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  int na = 0;
+  if (ctx->use_pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 int upload_f32(ub_ctx* ctx, const std::vector<float>& v, float** out) {
   int rc;
   if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(out), v.size() * 4))) return rc;
@@ -270,13 +292,15 @@ template <int MODE>
 int vit_launch_ln(ub_ctx* ctx, int ns, int blocks, cudaStream_t st, float* resid, const __nv_bfloat16* branch, const float* g,
                   const float* b, float eps, __nv_bfloat16* out, int tokens, int tp, const __nv_bfloat16* patches, int tp_p,
                   const float* cls, const float* pos, int ntok) {
+  cudaError_t e = cudaSuccess;
   switch (ns) {
-    case 1: ub::vit_ln_kernel<1, MODE><<<blocks, 256, 0, st>>>(resid, branch, g, b, eps, out, tokens, tp, patches, tp_p, cls, pos, ntok); break;
-    case 2: ub::vit_ln_kernel<2, MODE><<<blocks, 256, 0, st>>>(resid, branch, g, b, eps, out, tokens, tp, patches, tp_p, cls, pos, ntok); break;
-    case 3: ub::vit_ln_kernel<3, MODE><<<blocks, 256, 0, st>>>(resid, branch, g, b, eps, out, tokens, tp, patches, tp_p, cls, pos, ntok); break;
-    case 4: ub::vit_ln_kernel<4, MODE><<<blocks, 256, 0, st>>>(resid, branch, g, b, eps, out, tokens, tp, patches, tp_p, cls, pos, ntok); break;
+    case 1: e = launch_pdl(ctx, ub::vit_ln_kernel<1, MODE>, dim3(blocks), dim3(256), 0, st, resid, branch, g, b, eps, out, tokens, tp, patches, tp_p, cls, pos, ntok); break;
+    case 2: e = launch_pdl(ctx, ub::vit_ln_kernel<2, MODE>, dim3(blocks), dim3(256), 0, st, resid, branch, g, b, eps, out, tokens, tp, patches, tp_p, cls, pos, ntok); break;
+    case 3: e = launch_pdl(ctx, ub::vit_ln_kernel<3, MODE>, dim3(blocks), dim3(256), 0, st, resid, branch, g, b, eps, out, tokens, tp, patches, tp_p, cls, pos, ntok); break;
+    case 4: e = launch_pdl(ctx, ub::vit_ln_kernel<4, MODE>, dim3(blocks), dim3(256), 0, st, resid, branch, g, b, eps, out, tokens, tp, patches, tp_p, cls, pos, ntok); break;
     default: return fail(ctx, UB_ERR_UNSUPPORTED, "hidden size %d", 256 * ns);
   }
+  UB_CUDA(ctx, e);
   ctx->launches++;
   return UB_OK;
 }
@@ -317,11 +341,10 @@ int vit_forward_chunk(ub_ctx* ctx, const float* x, int n, int H, int W, float* f
       UB_CUDA(ctx, cudaFuncSetAttribute(ub::clip_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       ctx->smem_opt_in.insert(fn);
     }
-    ub::clip_patch_kernel<<<dim3(v->G, 3, n), 256, smem, st>>>(x, n, H, W, ry, rx, v->P, v->G, kClipMean[0], kClipMean[1], kClipMean[2],
-                                                             1.0f / kClipStd[0], 1.0f / kClipStd[1], 1.0f / kClipStd[2],
-                                                             v->patches, pl->tp_p);
+    UB_CUDA(ctx, launch_pdl(ctx, ub::clip_patch_kernel, dim3(v->G, 3, n), dim3(256), smem, st, x, n, H, W, ry, rx, v->P, v->G, kClipMean[0],
+                            kClipMean[1], kClipMean[2], 1.0f / kClipStd[0], 1.0f / kClipStd[1], 1.0f / kClipStd[2], v->patches,
+                            pl->tp_p));
     ctx->launches++;
-    UB_CUDA(ctx, cudaGetLastError());
   }
   auto run_gemm = [&](size_t i) {
     const GemmLayer& L = ctx->layers[v->lin[i]];
@@ -338,9 +361,9 @@ int vit_forward_chunk(ub_ctx* ctx, const float* x, int n, int H, int W, float* f
                                             v->ln_out, pl->tokens, pl->tp, nullptr, 0, nullptr, nullptr, v->ntok)))
       return rc;
     if ((rc = run_gemm(1 + 4 * l + 0))) return rc;
-    ub::vit_attention_kernel<<<dim3(v->D / ub::kVitHeadDim, n), 128, 0, st>>>(v->qkv, v->attn, v->D, v->ntok, pl->tp);
+    UB_CUDA(ctx, launch_pdl(ctx, ub::vit_attention_kernel, dim3(v->D / ub::kVitHeadDim, n), dim3(128), 0, st, v->qkv, v->attn, v->D,
+                            v->ntok, pl->tp));
     ctx->launches++;
-    UB_CUDA(ctx, cudaGetLastError());
     if ((rc = run_gemm(1 + 4 * l + 1))) return rc;
     if ((rc = vit_launch_ln<ub::VIT_LN_ADD>(ctx, ns, ln_blocks, st, v->resid, v->branch, v->ln2_g[l], v->ln2_b[l], v->eps, v->ln_out,
                                             pl->tokens, pl->tp, nullptr, 0, nullptr, nullptr, v->ntok)))
@@ -348,9 +371,8 @@ int vit_forward_chunk(ub_ctx* ctx, const float* x, int n, int H, int W, float* f
     if ((rc = run_gemm(1 + 4 * l + 2))) return rc;
     if ((rc = run_gemm(1 + 4 * l + 3))) return rc;
   }
-  ub::vit_pool_proj_kernel<<<dim3(n, (v->E + 63) / 64), 256, 0, st>>>(v->resid, v->branch, v->D, v->ntok, pl->tp, v->post_g, v->post_b, v->eps, v->w_proj,
-                                              v->E, feats);
+  UB_CUDA(ctx, launch_pdl(ctx, ub::vit_pool_proj_kernel, dim3(n, (v->E + 63) / 64), dim3(256), 0, st, v->resid, v->branch, v->D, v->ntok,
+                          pl->tp, v->post_g, v->post_b, v->eps, v->w_proj, v->E, feats));
   ctx->launches++;
-  UB_CUDA(ctx, cudaGetLastError());
   return UB_OK;
 }
