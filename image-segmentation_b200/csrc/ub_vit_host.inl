@@ -67,6 +67,7 @@ int pack_linear(ub_ctx* ctx, const std::string& key, const std::vector<std::stri
   L.ksize = 1;
   L.relu = 0;
   L.act = act;
+  L.no_pair = true;
   std::vector<float> w, b;
   for (const std::string& k : w_keys) {
     const HostTensor* t = find(ctx, k);
@@ -87,6 +88,7 @@ int pack_linear(ub_ctx* ctx, const std::string& key, const std::vector<std::stri
   if (static_cast<int>(b.size()) != L.cout) return fail(ctx, UB_ERR_INVALID, "%s: %zu biases for %d outputs", key.c_str(), b.size(), L.cout);
   L.n_total = L.cout;
   L.block_n = pick_block_n(L.n_total);
+  { const char* e = getenv("UB_VIT_BN"); if (e && atoi(e) == 128) L.block_n = 128; }  // (experiment: 128-column tiles)
   L.bk = 64;
   if (L.cin % 64 != 0 || L.cout % 256 != 0)
     return fail(ctx, UB_ERR_UNSUPPORTED, "%s: [%d -> %d]: inputs must be a multiple of 64 and outputs of 256", key.c_str(), L.cin, L.cout);
@@ -168,7 +170,7 @@ int pack_vit(ub_ctx* ctx) {
     if ((rc = pack_linear(ctx, p + "mlp.fc2", {p + "mlp.fc2.weight"}, {p + "mlp.fc2.bias"}, ub::ACT_NONE, &idx))) return rc;
     v->lin.push_back(idx);
   }
-  // token buffers for max_mb images, rounded up to whole pairs of 128-token tiles (zeroed once: the rows after the last
+  // token buffers for max_mb images, rounded up to whole 128-token tiles (zeroed once: the rows after the last
   // token are GEMM operand rows whose results nobody reads)
   const size_t tp = (static_cast<size_t>(ctx->max_mb) * v->ntok + 255) / 256 * 256;
   const size_t tpp = (static_cast<size_t>(ctx->max_mb) * v->G * v->G + 255) / 256 * 256;
@@ -265,9 +267,9 @@ int vit_plan(ub_ctx* ctx, int n, VitPlanN** out) {
     VitPlanN pl;
     pl.n = n;
     pl.tokens = n * v->ntok;
-    pl.tp = (pl.tokens + 255) / 256 * 256;  // whole PAIRS of 128-token tiles: the CTA-pair kernel pads odd tile counts with a phantom image
+    pl.tp = (pl.tokens + 127) / 128 * 128;  // whole 128-token tiles
     pl.ptokens = n * v->G * v->G;
-    pl.tp_p = (pl.ptokens + 255) / 256 * 256;
+    pl.tp_p = (pl.ptokens + 127) / 128 * 128;
     pl.gemm.resize(v->lin.size());
     int rc;
     // the token axis as an "image" of tp/8 rows x 8 columns, one image per launch
@@ -305,20 +307,20 @@ int vit_launch_ln(ub_ctx* ctx, int ns, int blocks, cudaStream_t st, float* resid
   return UB_OK;
 }
 
-// Images per chunk.  The four GEMMs of a layer are small (ViT-B/32, 122 images: 72 / 216 / 288 CTA-pair tiles), so how many
-// whole waves of the 74 CTA pairs their tile counts make decides a third of their time: 128 images give 75 tiles for the
-// two D -> D maps (two waves, the second one 1/74 full), 122 images give 72 (one wave).  Pick the chunk size <= max_mb that
+// Images per chunk.  The four GEMMs of a layer are small (ViT-B/32, 125 images: 49 token tiles x 3 / 9 / 12 column tiles), so
+// how many whole waves of the SMs their tile counts make decides a third of their time: 128 images give 150 tiles for the two
+// D -> D maps (two waves, the second one 2/148 full), 125 images give 147 (one wave).  Pick the chunk size <= max_mb that
 // minimises the waves spent per image, FLOP-weighted over the four shapes.
 int vit_pick_chunk(const ub_ctx* ctx, const VitState* v) {
-  const int slots = ctx->num_sms / 2 > 0 ? ctx->num_sms / 2 : 1;
+  const int slots = ctx->num_sms > 0 ? ctx->num_sms : 1;
   const int nt[4] = {3 * v->D / 256, v->D / 256, v->I / 256, v->D / 256};                  // n-tiles: qkv, out_proj, fc1, fc2
   const double kw[4] = {double(v->D), double(v->D), double(v->D), double(v->I)};           // time of one tile ~ K
   int best = ctx->max_mb;
   double best_cost = 1e300;
   for (int n = ctx->max_mb; n >= 1 && n >= ctx->max_mb / 2; --n) {
-    const int pairs = (n * v->ntok + 255) / 256;
+    const int mt = (n * v->ntok + 127) / 128;
     double cost = 0.0;
-    for (int i = 0; i < 4; ++i) cost += kw[i] * ((pairs * nt[i] + slots - 1) / slots);
+    for (int i = 0; i < 4; ++i) cost += kw[i] * ((mt * nt[i] + slots - 1) / slots);
     cost /= n;
     if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = n; }
   }

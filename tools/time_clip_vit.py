@@ -50,7 +50,8 @@ def main():
         a[0] += launches; a[1] += t
     for kind, (launches, t, cin, nt) in agg.items():
         if launches:
-            fl = 2.0 * cin * nt * n * (49 if kind == "patch_embedding" else 50) * launches
+            per_layer = 1 if kind == "patch_embedding" else 12                       # launches per pass over all n images
+            fl = 2.0 * cin * nt * n * (49 if kind == "patch_embedding" else 50) * per_layer
             print(f"  {kind:16s} [{cin:4d} -> {nt:4d}] x{launches:3d}: {t:7.3f} ms  {fl / t / 1e9:7.1f} TFLOP/s")
 
 
