@@ -1611,11 +1611,21 @@ int ub_debug_clip_preprocess(ub_ctx* ctx, const float* x_nchw, int n, int h, int
   if (ctx->arch != UB_ARCH_CLIP_VIT || !ctx->vit) return fail(ctx, UB_ERR_STATE, "ub_debug_clip_preprocess needs a UB_ARCH_CLIP_VIT context");
   if (!x_nchw || !out_nchw || n <= 0 || h <= 0 || w <= 0) return fail(ctx, UB_ERR_INVALID, "bad arguments");
   ub::ResizeTap *ry = nullptr, *rx = nullptr;
-  if ((rc = vit_taps(ctx, h, w, &ry, &rx))) return rc;
+  int max_taps = ub::kClipMaxTaps;
+  if ((rc = vit_taps(ctx, h, w, &ry, &rx, &max_taps))) return rc;
   const int S = ctx->vit->S;
-  ub::clip_preprocess_kernel<<<blocks_for(static_cast<size_t>(n) * 3 * S * S, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      x_nchw, n, h, w, ry, rx, S, kClipMean[0], kClipMean[1], kClipMean[2], 1.0f / kClipStd[0], 1.0f / kClipStd[1],
-      1.0f / kClipStd[2], out_nchw);
+  const unsigned blocks = blocks_for(static_cast<size_t>(n) * 3 * S * S, 256);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define UB_PRE(T)                                                                                                              \
+  ub::clip_preprocess_kernel<T><<<blocks, 256, 0, st>>>(x_nchw, n, h, w, ry, rx, S, kClipMean[0], kClipMean[1], kClipMean[2], \
+                                                        1.0f / kClipStd[0], 1.0f / kClipStd[1], 1.0f / kClipStd[2], out_nchw)
+  if (max_taps <= 2) UB_PRE(2);  // (the same dispatch as the patch kernel: vit_forward_chunk)
+  else if (max_taps <= 3) UB_PRE(3);
+  else if (max_taps <= 4) UB_PRE(4);
+  else if (max_taps <= 6) UB_PRE(6);
+  else if (max_taps <= 8) UB_PRE(8);
+  else UB_PRE(ub::kClipMaxTaps);
+#undef UB_PRE
   ctx->launches++;
   UB_CUDA(ctx, cudaGetLastError());
   return UB_OK;

@@ -19,7 +19,8 @@ struct VitState {
                 *branch = nullptr, *mlp = nullptr;
   float* resid = nullptr;
   std::map<int, VitPlanN> plans;
-  std::map<std::pair<int, int>, std::pair<ub::ResizeTap*, ub::ResizeTap*>> taps;  // (H, W) -> device tables (rows, columns)
+  struct Taps { ub::ResizeTap *ry, *rx; int max_count; };
+  std::map<std::pair<int, int>, Taps> taps;  // (H, W) -> device tables (rows, columns) and their largest tap count
 };
 
 // Launch with the programmatic-stream-serialization attribute (the kernels of ub_vit.cuh wait with griddepcontrol.wait
@@ -225,14 +226,18 @@ int make_resize_taps(ub_ctx* ctx, int in, int out, std::vector<ub::ResizeTap>* t
   return UB_OK;
 }
 
-int vit_taps(ub_ctx* ctx, int H, int W, ub::ResizeTap** ry, ub::ResizeTap** rx) {
+// CLIP's normalisation constants (processing_blocks.py:204-205)
+constexpr float kClipMean[3] = {0.48145466f, 0.4578275f, 0.40821073f};
+constexpr float kClipStd[3] = {0.26862954f, 0.26130258f, 0.27577711f};
+
+int vit_taps(ub_ctx* ctx, int H, int W, ub::ResizeTap** ry, ub::ResizeTap** rx, int* max_count = nullptr) {
   VitState* v = ctx->vit;
   auto it = v->taps.find({H, W});
   if (it == v->taps.end()) {
     if (v->taps.size() >= 32) {  // a caller sweeping input sizes: drop the cached tables once nothing can be reading them
       UB_CUDA(ctx, cudaDeviceSynchronize());
       for (auto& kv : v->taps) {
-        for (void* p : {static_cast<void*>(kv.second.first), static_cast<void*>(kv.second.second)}) {
+        for (void* p : {static_cast<void*>(kv.second.ry), static_cast<void*>(kv.second.rx)}) {
           cudaFree(p);
           ctx->owned.erase(std::find(ctx->owned.begin(), ctx->owned.end(), p));
         }
@@ -243,22 +248,38 @@ int vit_taps(ub_ctx* ctx, int H, int W, ub::ResizeTap** ry, ub::ResizeTap** rx) 
     int rc;
     if ((rc = make_resize_taps(ctx, H, v->S, &hy))) return rc;
     if ((rc = make_resize_taps(ctx, W, v->S, &hx))) return rc;
+    int mc = 1;
+    for (const auto& t : hy) mc = t.count > mc ? t.count : mc;
+    for (const auto& t : hx) mc = t.count > mc ? t.count : mc;
     ub::ResizeTap *dy = nullptr, *dx = nullptr;
     if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&dy), hy.size() * sizeof(ub::ResizeTap)))) return rc;
     if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&dx), hx.size() * sizeof(ub::ResizeTap)))) return rc;
     UB_CUDA(ctx, cudaMemcpy(dy, hy.data(), hy.size() * sizeof(ub::ResizeTap), cudaMemcpyHostToDevice));
     UB_CUDA(ctx, cudaMemcpy(dx, hx.data(), hx.size() * sizeof(ub::ResizeTap), cudaMemcpyHostToDevice));
     UB_CUDA(ctx, cudaDeviceSynchronize());
-    it = v->taps.emplace(std::make_pair(H, W), std::make_pair(dy, dx)).first;
+    it = v->taps.emplace(std::make_pair(H, W), VitState::Taps{dy, dx, mc}).first;
   }
-  *ry = it->second.first;
-  *rx = it->second.second;
+  *ry = it->second.ry;
+  *rx = it->second.rx;
+  if (max_count) *max_count = it->second.max_count;
   return UB_OK;
 }
 
-// CLIP's normalisation constants (processing_blocks.py:204-205)
-constexpr float kClipMean[3] = {0.48145466f, 0.4578275f, 0.40821073f};
-constexpr float kClipStd[3] = {0.26862954f, 0.26130258f, 0.27577711f};
+template <int T>
+int launch_patch(ub_ctx* ctx, const VitState* v, const float* x, int n, int H, int W, const ub::ResizeTap* ry, const ub::ResizeTap* rx,
+                 int tp_p, cudaStream_t st) {
+  const int smem = ub::clip_patch_smem_bytes(v->P, v->G);
+  const void* fn = reinterpret_cast<const void*>(&ub::clip_patch_kernel<T>);
+  if (smem > 48 * 1024 && !ctx->smem_opt_in.count(fn)) {
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::clip_patch_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    ctx->smem_opt_in.insert(fn);
+  }
+  UB_CUDA(ctx, launch_pdl(ctx, ub::clip_patch_kernel<T>, dim3(v->G, 3, n), dim3(256), smem, st, x, n, H, W, ry, rx, v->P, v->G, kClipMean[0],
+                          kClipMean[1], kClipMean[2], 1.0f / kClipStd[0], 1.0f / kClipStd[1], 1.0f / kClipStd[2], v->patches, tp_p));
+  ctx->launches++;
+  return UB_OK;
+}
+
 
 int vit_plan(ub_ctx* ctx, int n, VitPlanN** out) {
   VitState* v = ctx->vit;
@@ -332,22 +353,18 @@ int vit_forward_chunk(ub_ctx* ctx, const float* x, int n, int H, int W, float* f
   VitState* v = ctx->vit;
   int rc;
   ub::ResizeTap *ry = nullptr, *rx = nullptr;
-  if ((rc = vit_taps(ctx, H, W, &ry, &rx))) return rc;
+  int max_taps = ub::kClipMaxTaps;
+  if ((rc = vit_taps(ctx, H, W, &ry, &rx, &max_taps))) return rc;
   VitPlanN* pl = nullptr;
   if ((rc = vit_plan(ctx, n, &pl))) return rc;
   const int ns = v->D / 256;
-  {
-    const int smem = ub::clip_patch_smem_bytes(v->P, v->G);
-    const void* fn = reinterpret_cast<const void*>(&ub::clip_patch_kernel);
-    if (smem > 48 * 1024 && !ctx->smem_opt_in.count(fn)) {
-      UB_CUDA(ctx, cudaFuncSetAttribute(ub::clip_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      ctx->smem_opt_in.insert(fn);
-    }
-    UB_CUDA(ctx, launch_pdl(ctx, ub::clip_patch_kernel, dim3(v->G, 3, n), dim3(256), smem, st, x, n, H, W, ry, rx, v->P, v->G, kClipMean[0],
-                            kClipMean[1], kClipMean[2], 1.0f / kClipStd[0], 1.0f / kClipStd[1], 1.0f / kClipStd[2], v->patches,
-                            pl->tp_p));
-    ctx->launches++;
-  }
+  if (max_taps <= 2) rc = launch_patch<2>(ctx, v, x, n, H, W, ry, rx, pl->tp_p, st);        // identity / enlarging
+  else if (max_taps <= 3) rc = launch_patch<3>(ctx, v, x, n, H, W, ry, rx, pl->tp_p, st);   // 256 -> 224 and other mild shrinks
+  else if (max_taps <= 4) rc = launch_patch<4>(ctx, v, x, n, H, W, ry, rx, pl->tp_p, st);
+  else if (max_taps <= 6) rc = launch_patch<6>(ctx, v, x, n, H, W, ry, rx, pl->tp_p, st);
+  else if (max_taps <= 8) rc = launch_patch<8>(ctx, v, x, n, H, W, ry, rx, pl->tp_p, st);
+  else rc = launch_patch<ub::kClipMaxTaps>(ctx, v, x, n, H, W, ry, rx, pl->tp_p, st);
+  if (rc) return rc;
   auto run_gemm = [&](size_t i) {
     const GemmLayer& L = ctx->layers[v->lin[i]];
     return launch_gemm(ctx, pl->gemm[i], L.block_n, L.bk, st, v->lin[i]);
