@@ -546,6 +546,17 @@ bool choose_pipeline(ConvParams* cp, int grid, bool allow_ws, int* smem_bytes) {
     *smem_bytes = cp->sa * Cfg::A_STAGE_BYTES + w_bytes + Cfg::TAIL_BYTES + 1024;
     return true;
   }
+  if (KS == 1) {
+    // one tap: an A box feeds only BK/16 MMAs (512 cycles at N = 256), so two A stages cannot cover a TMA round trip —
+    // the rings advance in step, equally deep (the ViT's token GEMMs: 4 + 4 stages; measured in profiles/r02_call34_*)
+    int s = budget / (Cfg::A_STAGE_BYTES + Cfg::B_STAGE_BYTES);
+    const int cap = ub::kMaxSA < ub::kMaxSB ? ub::kMaxSA : ub::kMaxSB;
+    s = s > cap ? cap : (s < 2 ? 2 : s);
+    cp->sa = cp->sb = s;
+    while (cp->sa < ub::kMaxSA && (cp->sa + 1) * Cfg::A_STAGE_BYTES + cp->sb * Cfg::B_STAGE_BYTES <= budget) cp->sa++;
+    *smem_bytes = cp->sa * Cfg::A_STAGE_BYTES + cp->sb * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES + 1024;
+    return false;
+  }
   cp->sa = Cfg::A_STAGE_BYTES >= 16384 ? 2 : 3;
   if (N <= 128) cp->sa += 1;
   int sb = (budget - cp->sa * Cfg::A_STAGE_BYTES) / Cfg::B_STAGE_BYTES;

@@ -10,6 +10,7 @@ struct VitPlanN {  // everything that depends on the number of images of a chunk
 struct VitState {
   int D = 0, L = 0, I = 0, P = 0, G = 0, S = 0, ntok = 0, E = 0;
   int chunk = 0;  // images per internal pass (vit_pick_chunk)
+  bool pair = false;  // UB_VIT_PAIR=1 (experiment): CTA-pair tiles for the token GEMMs
   float eps = 1e-5f;
   std::vector<int> lin;  // indices into ctx->layers, same order as VitPlanN::gemm
   float *cls = nullptr, *pos = nullptr, *pre_g = nullptr, *pre_b = nullptr, *post_g = nullptr, *post_b = nullptr,
@@ -68,7 +69,7 @@ int pack_linear(ub_ctx* ctx, const std::string& key, const std::vector<std::stri
   L.ksize = 1;
   L.relu = 0;
   L.act = act;
-  L.no_pair = true;
+  { const char* e = getenv("UB_VIT_PAIR"); L.no_pair = !(e && e[0] == '1'); }
   std::vector<float> w, b;
   for (const std::string& k : w_keys) {
     const HostTensor* t = find(ctx, k);
@@ -184,6 +185,7 @@ int pack_vit(ub_ctx* ctx) {
   if ((rc = alloc_zeroed(ctx, reinterpret_cast<void**>(&v->branch), tp * D * 2))) return rc;
   if ((rc = alloc_zeroed(ctx, reinterpret_cast<void**>(&v->mlp), tp * static_cast<size_t>(v->I) * 2))) return rc;
   UB_CUDA(ctx, cudaDeviceSynchronize());
+  { const char* e = getenv("UB_VIT_PAIR"); v->pair = e && e[0] == '1'; }
   v->chunk = vit_pick_chunk(ctx, v.get());
   { const char* e = getenv("UB_VIT_CHUNK"); if (e && atoi(e) >= 1 && atoi(e) <= ctx->max_mb) v->chunk = atoi(e); }  // (experiment)
   ctx->vit = v.release();
@@ -288,9 +290,10 @@ int vit_plan(ub_ctx* ctx, int n, VitPlanN** out) {
     VitPlanN pl;
     pl.n = n;
     pl.tokens = n * v->ntok;
-    pl.tp = (pl.tokens + 127) / 128 * 128;  // whole 128-token tiles
+    const int tm = v->pair ? 256 : 128;  // whole tiles (pairs: the CTA-pair kernel pads odd tile counts with a phantom image)
+    pl.tp = (pl.tokens + tm - 1) / tm * tm;
     pl.ptokens = n * v->G * v->G;
-    pl.tp_p = (pl.ptokens + 127) / 128 * 128;
+    pl.tp_p = (pl.ptokens + tm - 1) / tm * tm;
     pl.gemm.resize(v->lin.size());
     int rc;
     // the token axis as an "image" of tp/8 rows x 8 columns, one image per launch
@@ -333,13 +336,14 @@ int vit_launch_ln(ub_ctx* ctx, int ns, int blocks, cudaStream_t st, float* resid
 // D -> D maps (two waves, the second one 2/148 full), 125 images give 147 (one wave).  Pick the chunk size <= max_mb that
 // minimises the waves spent per image, FLOP-weighted over the four shapes.
 int vit_pick_chunk(const ub_ctx* ctx, const VitState* v) {
-  const int slots = ctx->num_sms > 0 ? ctx->num_sms : 1;
+  const int tile_m = v->pair ? 256 : 128;
+  const int slots = (v->pair ? ctx->num_sms / 2 : ctx->num_sms) > 0 ? (v->pair ? ctx->num_sms / 2 : ctx->num_sms) : 1;
   const int nt[4] = {3 * v->D / 256, v->D / 256, v->I / 256, v->D / 256};                  // n-tiles: qkv, out_proj, fc1, fc2
   const double kw[4] = {double(v->D), double(v->D), double(v->D), double(v->I)};           // time of one tile ~ K
   int best = ctx->max_mb;
   double best_cost = 1e300;
   for (int n = ctx->max_mb; n >= 1 && n >= ctx->max_mb / 2; --n) {
-    const int mt = (n * v->ntok + 127) / 128;
+    const int mt = (n * v->ntok + tile_m - 1) / tile_m;
     double cost = 0.0;
     for (int i = 0; i < 4; ++i) cost += kw[i] * ((mt * nt[i] + slots - 1) / slots);
     cost /= n;
