@@ -8,8 +8,16 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libunetb200.so")
 SOURCES = ["ub_api.cu"]
-DEPS = ["ub_api.cu", "ub_conv_tc.cuh", "ub_conv_epilogue.inl", "ub_ptx.cuh", "ub_perturb.cuh", "ub_aux.cuh",
-        os.path.join("..", "..", "include", "unet_b200.h")]
+
+
+
+def deps():
+    """Every source the one translation unit includes: all of csrc/ plus the C-ABI header (a fixed list went stale once:
+    edits to a header that was not on it did not rebuild the library)."""
+    here = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".inl", ".h")))
+    return here + [os.path.join("..", "..", "include", "unet_b200.h")]
+
+
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]
 
@@ -18,7 +26,7 @@ def needs_build() -> bool:
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    return any(os.path.getmtime(os.path.join(CSRC, d)) > t for d in DEPS)
+    return any(os.path.getmtime(os.path.join(CSRC, d)) > t for d in deps())
 
 
 def build(force: bool = False, verbose: bool = False) -> str:

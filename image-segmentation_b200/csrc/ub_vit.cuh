@@ -60,17 +60,19 @@ __host__ __device__ constexpr int clip_patch_smem_bytes(int P, int G) { return P
 
 // T = taps per axis the instantiation evaluates (>= the largest count in the two tables; the tables' weights beyond a
 // coordinate's count are zero and the indices are clamped into the image, so the loops unroll completely: the first
-// version with run-time tap counts spent 234 instructions per output pixel, 71 % SM-busy for 0.17 ms; this one 0.10 ms).
-// (A separable variant — rows resampled along x into shared memory first, 2.6x fewer global loads — measured the same 0.10 ms:
-// the kernel is bound by its dependent load -> FMA chains at 8 warps per block, not by L2 -> L1 traffic.  Not kept.)
-template <int T>
+// version with run-time tap counts spent 234 instructions per output pixel, 71 % SM-busy for 0.17 ms; this one 0.106 ms).
+// SEP (UB_PATCH_SEP=1, experiment): separable — each input row the band needs is resampled along x into shared memory first
+// (2.6x fewer global loads), then along y from there: 0.092 against 0.106 ms; the kernel is bound by its dependent
+// load -> FMA chains at 8 warps per block, not by L2 -> L1 traffic.
+template <int T, bool SEP = false>
 __global__ void __launch_bounds__(256)
 clip_patch_kernel(const float* __restrict__ x, int n, int H, int W, const ResizeTap* __restrict__ ry,
                   const ResizeTap* __restrict__ rx, int P, int G, float m0, float m1, float m2, float is0, float is1,
-                  float is2, __nv_bfloat16* __restrict__ out, int tp) {
+                  float is2, __nv_bfloat16* __restrict__ out, int tp, int nr_max = 0) {
   extern __shared__ __align__(16) unsigned char patch_sm[];
   const int S = G * P;
   __nv_bfloat16* band = reinterpret_cast<__nv_bfloat16*>(patch_sm);
+  float* hrow = reinterpret_cast<float*>(patch_sm + static_cast<size_t>(P) * S * 2);  // SEP: [nr_max][S]
   const int gy = blockIdx.x, c = blockIdx.y, img = blockIdx.z, tid = threadIdx.x;
   (void)n;
   pdl_launch_dependents();
@@ -85,6 +87,27 @@ clip_patch_kernel(const float* __restrict__ x, int n, int H, int W, const Resize
     for (int i = 0; i < T; ++i) {
       wx[i] = rx[ox].w[i];
       xi[i] = min(rx[ox].start + i, W - 1);
+    }
+    if (SEP) {
+      const int r0 = rows[0].start;
+      const int nr = min(min(rows[P - 1].start + T, H) - r0, nr_max);
+#pragma unroll 4
+      for (int r = 0; r < nr; ++r) {
+        const float* row = plane + static_cast<size_t>(r0 + r) * W;
+        float h = 0.0f;
+#pragma unroll
+        for (int i = 0; i < T; ++i) h = fmaf(wx[i], row[xi[i]], h);
+        hrow[r * S + ox] = h;
+      }
+#pragma unroll 4
+      for (int py = 0; py < P; ++py) {  // (same thread, same column: no barrier between the passes)
+        const int ys = rows[py].start - r0;
+        float acc = 0.0f;
+#pragma unroll
+        for (int j = 0; j < T; ++j) acc = fmaf(rows[py].w[j], hrow[min(ys + j, nr - 1) * S + ox], acc);
+        band[py * S + ox] = __float2bfloat16((acc - mean) * inv_std);
+      }
+      continue;
     }
 #pragma unroll 4
     for (int py = 0; py < P; ++py) {

@@ -271,13 +271,31 @@ template <int T>
 int launch_patch(ub_ctx* ctx, const VitState* v, const float* x, int n, int H, int W, const ub::ResizeTap* ry, const ub::ResizeTap* rx,
                  int tp_p, cudaStream_t st) {
   const int smem = ub::clip_patch_smem_bytes(v->P, v->G);
-  const void* fn = reinterpret_cast<const void*>(&ub::clip_patch_kernel<T>);
+  const void* fn = reinterpret_cast<const void*>(&ub::clip_patch_kernel<T, false>);
   if (smem > 48 * 1024 && !ctx->smem_opt_in.count(fn)) {
-    UB_CUDA(ctx, cudaFuncSetAttribute(ub::clip_patch_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::clip_patch_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     ctx->smem_opt_in.insert(fn);
   }
-  UB_CUDA(ctx, launch_pdl(ctx, ub::clip_patch_kernel<T>, dim3(v->G, 3, n), dim3(256), smem, st, x, n, H, W, ry, rx, v->P, v->G, kClipMean[0],
-                          kClipMean[1], kClipMean[2], 1.0f / kClipStd[0], 1.0f / kClipStd[1], 1.0f / kClipStd[2], v->patches, tp_p));
+  if (T == 3) {  // UB_PATCH_SEP=1 (experiment, the 256 -> 224 instantiation only): separable variant, rows resampled along x first
+    const char* e = getenv("UB_PATCH_SEP");
+    if (e && e[0] == '1') {
+      const int nr_max = 48;  // 32 output rows x 256/224 + taps
+      const int smem2 = smem + nr_max * v->G * v->P * 4;
+      const void* fn2 = reinterpret_cast<const void*>(&ub::clip_patch_kernel<3, true>);
+      if (!ctx->smem_opt_in.count(fn2)) {
+        UB_CUDA(ctx, cudaFuncSetAttribute(ub::clip_patch_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+        ctx->smem_opt_in.insert(fn2);
+      }
+      UB_CUDA(ctx, launch_pdl(ctx, ub::clip_patch_kernel<3, true>, dim3(v->G, 3, n), dim3(256), smem2, st, x, n, H, W, ry, rx, v->P, v->G,
+                              kClipMean[0], kClipMean[1], kClipMean[2], 1.0f / kClipStd[0], 1.0f / kClipStd[1], 1.0f / kClipStd[2],
+                              v->patches, tp_p, nr_max));
+      ctx->launches++;
+      return UB_OK;
+    }
+  }
+  UB_CUDA(ctx, launch_pdl(ctx, ub::clip_patch_kernel<T, false>, dim3(v->G, 3, n), dim3(256), smem, st, x, n, H, W, ry, rx, v->P, v->G,
+                          kClipMean[0], kClipMean[1], kClipMean[2], 1.0f / kClipStd[0], 1.0f / kClipStd[1], 1.0f / kClipStd[2],
+                          v->patches, tp_p, 0));
   ctx->launches++;
   return UB_OK;
 }
