@@ -21,6 +21,7 @@
 #include "ub_aux.cuh"
 #include "ub_conv_tc.cuh"
 #include "ub_conv_rs.cuh"
+#include "ub_conv_rs2.cuh"
 #include "ub_perturb.cuh"
 #include "ub_vit.cuh"
 
@@ -112,6 +113,7 @@ struct ub_ctx {
   bool no_blur_fuse = false;  // UB_NO_BLUR_FUSE=1: blur families run one launch per pass (the path for > 12 passes)
   bool head_no_kxs = false;   // UB_HEAD_NO_KXS=1: only the head layer (dec4.conv.3) runs the 9-tap kernel
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
+  bool fuse_enc1 = false;     // UB_FUSE_ENC1=1: enc1.conv.0 -> conv.3 -> pool as one kernel (ub_conv_rs2.cuh)
   bool no_rs = true;          // UB_RS=1 selects the row-streaming kernel (ub_conv_rs.cuh) for the thin layers from 32 rows up; default:
                               // kx-stacked (the two measure the same under the power cap)
 
@@ -686,6 +688,45 @@ int launch_rs(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   return UB_OK;
 }
 
+// Fused first encoder stage: a task = (image, 28-column band); persistent CTAs.
+int launch_rs2(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
+  using Cfg = ub::Rs2Cfg;
+  ConvParams cp = cp_in;
+  const int bands = (cp.W + ub::kRs2Out - 1) / ub::kRs2Out;
+  const int tasks = cp.B * bands;
+  const int grid = tasks < ctx->num_sms ? tasks : ctx->num_sms;
+  const int fixed = Cfg::B1_BYTES + Cfg::B2_BYTES;
+  cp.sa = 8;                                                               // A1 stages (4 KB)
+  int s2 = (Cfg::OPERAND_BUDGET - fixed - cp.sa * Cfg::A1_STAGE) / Cfg::A2_STAGE;   // A2 stages (16 KB)
+  if (s2 > ub::kRs2MaxSA2) s2 = ub::kRs2MaxSA2;
+  if (s2 < 3) return fail(ctx, UB_ERR_UNSUPPORTED, "fused encoder stage: no room for 3 stage-1 row buffers");
+  cp.sb = s2;
+  const int smem = Cfg::TAIL_BYTES + cp.sa * Cfg::A1_STAGE + cp.sb * Cfg::A2_STAGE + fixed + 1024;
+  const void* fn = reinterpret_cast<const void*>(&ub::conv_rs2_kernel);
+  if (!ctx->smem_opt_in.count(fn)) {
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_rs2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ub::kSmemLimit));
+    ctx->smem_opt_in.insert(fn);
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(ub::kRs2Threads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  int na = 0;
+  if (ctx->use_pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_rs2_kernel, cp));
+  ctx->launches++;
+  return UB_OK;
+}
+
 template <int N, int BK>
 int launch_ks(ub_ctx* ctx, const ConvParams& cp, cudaStream_t st) {
   if (cp.ksize == 3) return launch_inst<N, BK, 3>(ctx, cp, st);
@@ -714,6 +755,7 @@ int launch_gemm(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStre
 
 int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cudaStream_t st) {
   if (cp.mode == ub::EPI_HEAD && cp.cout != 32) return fail(ctx, UB_ERR_UNSUPPORTED, "head epilogue needs 32 channels");
+  if (cp.rs == 2) return launch_rs2(ctx, cp, st);
   if (cp.rs) {  // thin 3x3 layers at the larger sizes: ky-stacked, row-streaming
     if (cp.cout == 64 && bk == 64) return launch_rs<64, 64>(ctx, cp, st);
     if (cp.cout == 32 && bk == 64) return launch_rs<32, 64>(ctx, cp, st);
@@ -853,6 +895,32 @@ int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out) {
   for (int i = 1; i <= (dec_half ? 0 : n); ++i) {
     snprintf(k, sizeof(k), "enc%d.block.0.conv", i);
     const bool fold = (i == 1 && ctx->stem_fold);  // reads the packed image (16 channels) through composed weights
+    if (fold && ctx->fuse_enc1 && hl(0) % 8 == 0 && hl(0) >= 32 && wl(0) >= 32) {
+      // one kernel for the whole stage (ub_conv_rs2.cuh): no conv.0 output buffer is touched
+      auto l0 = ctx->layer_by_key.find(std::string(k) + ".0+stem");
+      auto l3 = ctx->layer_by_key.find(std::string(k) + ".3");
+      if (l0 == ctx->layer_by_key.end() || l3 == ctx->layer_by_key.end()) return fail(ctx, UB_ERR_STATE, "enc1 layers not packed");
+      const GemmLayer& L0 = ctx->layers[l0->second];
+      const GemmLayer& L3 = ctx->layers[l3->second];
+      if (L0.cin == 16 && L0.cout == 64 && L3.cin == 64 && L3.cout == 64 && L0.w_rs && L3.w_rs) {
+        Step s;
+        s.kind = Step::GEMM;
+        s.layer = l3->second;
+        ConvParams& cp = s.cp;
+        memset(&cp, 0, sizeof(cp));
+        if ((rc = make_tm_w(ctx, &cp.tmA, L0.w_rs, L0.cin, 9 * L0.cout, 3 * L0.cout, L0.bk))) return rc;
+        if ((rc = make_tm_w(ctx, &cp.tmB, L3.w_rs, L3.cin, 9 * L3.cout, 3 * L3.cout, L3.bk))) return rc;
+        cp.rs = 2; cp.tw = 32; cp.hq = hl(0) / 4;
+        cp.a_src = skip_half(0); cp.a_cgs = 2 * skip_width(0) / 8; cp.a_planes = (L0.cin_src ? L0.cin_src : L0.cin) / 8;
+        cp.B = MB; cp.H = hl(0); cp.W = wl(0);
+        cp.cin = L0.cin; cp.ksize = 3; cp.n_total = L3.n_total; cp.mode = ub::EPI_POOL; cp.relu = 1;
+        cp.bias1 = L0.bias; cp.bias = L3.bias; cp.n_bias = L3.cout;
+        cp.out = bufp(i_cat[1]); cp.out_cgs = 2 * skip_width(1) / 8; cp.out_cg0 = skip_width(1) / 8; cp.cout = L3.cout;
+        cp.dbg = ctx->dbg; cp.ref_batch = 1; cp.n_classes = ctx->n_classes;
+        pl->steps.push_back(s);
+        continue;
+      }
+    }
     if ((rc = add_gemm(std::string(k) + (fold ? ".0+stem" : ".0"), skip_half(i - 1), 2 * skip_width(i - 1) / 8, hl(i - 1), wl(i - 1),
                        ub::EPI_STORE, bufp(i_enc[i]), skip_width(i) / 8, 0))) return rc;
     if ((rc = add_gemm(std::string(k) + ".3", bufp(i_enc[i]), skip_width(i) / 8, hl(i - 1), wl(i - 1), ub::EPI_POOL,
@@ -1188,6 +1256,7 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   { const char* e = getenv("UB_NO_STEM_FOLD"); ctx->stem_fold = !(e && e[0] == '1'); }
   { const char* e = getenv("UB_DBG"); ctx->dbg = e ? atoi(e) : 0; }
   { const char* e = getenv("UB_RS"); ctx->no_rs = !(e && e[0] == '1'); }
+  { const char* e = getenv("UB_FUSE_ENC1"); ctx->fuse_enc1 = e && e[0] == '1'; }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();

@@ -108,7 +108,7 @@ struct ConvParams {
   int cg2; // 1 = CTA-pair kernel (host: tmB box holds N/2 rows, even grid, cluster launch)
   int tw;  // tile width chosen by the host (8 standard, 16/32 kx-stacked); the kernel has it as a template parameter
   int k_steps;  // MMAs (16 channels each) issued per tap and chunk; fewer than BK/16 when the tail of the chunk is zero padding
-  int rs;  // 1 = row-streaming kernel (ub_conv_rs.cuh): tmA is the 5-D map over (pixel, row in quarter, quarter, plane, image)
+  int rs;  // 2 = fused first encoder stage (ub_conv_rs2.cuh); 1 = row-streaming kernel (ub_conv_rs.cuh): tmA is the 5-D map over (pixel, row in quarter, quarter, plane, image)
   int hq;  // row-streaming: rows per stream = H / 4
   // row-streaming: the A operand is filled by cp.async from the raw blocked tensor (ub_conv_rs.cuh explains why not TMA)
   const __nv_bfloat16* a_src;  // plane 0 of image 0 of the layer's input view
@@ -117,6 +117,7 @@ struct ConvParams {
   int sa;  // A stages (activation boxes)
   int sb;  // B stages when streaming weights; unused when the kernel is the WS instantiation
   int act; // EpiAct (1x1 STORE only)
+  const float* bias1;  // fused first encoder stage (ub_conv_rs2.cuh, rs == 2): conv.0's bias; `bias` is conv.3's, tmA holds conv.0's weights
 };
 
 constexpr int kMaxSA = 8;
