@@ -113,7 +113,7 @@ struct ub_ctx {
   bool no_blur_fuse = false;  // UB_NO_BLUR_FUSE=1: blur families run one launch per pass (the path for > 12 passes)
   bool head_no_kxs = false;   // UB_HEAD_NO_KXS=1: only the head layer (dec4.conv.3) runs the 9-tap kernel
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
-  bool fuse_enc1 = false;     // UB_FUSE_ENC1=1: enc1.conv.0 -> conv.3 -> pool as one kernel (ub_conv_rs2.cuh)
+  bool fuse_enc1 = true;      // enc1.conv.0 -> conv.3 -> pool as one kernel (ub_conv_rs2.cuh); UB_NO_FUSE_ENC1=1 / UB_FUSE_ENC1=0: two kernels
   bool no_rs = true;          // UB_RS=1 selects the row-streaming kernel (ub_conv_rs.cuh) for the thin layers from 32 rows up; default:
                               // kx-stacked (the two measure the same under the power cap)
 
@@ -915,6 +915,8 @@ int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out) {
         cp.B = MB; cp.H = hl(0); cp.W = wl(0);
         cp.cin = L0.cin; cp.ksize = 3; cp.n_total = L3.n_total; cp.mode = ub::EPI_POOL; cp.relu = 1;
         cp.bias1 = L0.bias; cp.bias = L3.bias; cp.n_bias = L3.cout;
+        memcpy(cp.bias64[0], L0.h_bias.data(), 64 * sizeof(float));
+        memcpy(cp.bias64[1], L3.h_bias.data(), 64 * sizeof(float));
         cp.out = bufp(i_cat[1]); cp.out_cgs = 2 * skip_width(1) / 8; cp.out_cg0 = skip_width(1) / 8; cp.cout = L3.cout;
         cp.dbg = ctx->dbg; cp.ref_batch = 1; cp.n_classes = ctx->n_classes;
         pl->steps.push_back(s);
@@ -1256,7 +1258,8 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   { const char* e = getenv("UB_NO_STEM_FOLD"); ctx->stem_fold = !(e && e[0] == '1'); }
   { const char* e = getenv("UB_DBG"); ctx->dbg = e ? atoi(e) : 0; }
   { const char* e = getenv("UB_RS"); ctx->no_rs = !(e && e[0] == '1'); }
-  { const char* e = getenv("UB_FUSE_ENC1"); ctx->fuse_enc1 = e && e[0] == '1'; }
+  { const char* e = getenv("UB_FUSE_ENC1"); const char* n = getenv("UB_NO_FUSE_ENC1");   // default on
+    ctx->fuse_enc1 = !(e && e[0] == '0') && !(n && n[0] == '1'); }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();

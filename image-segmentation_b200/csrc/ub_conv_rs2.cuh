@@ -1,4 +1,4 @@
-// ub_conv_rs2.cuh — the first encoder stage as ONE kernel (opt-in, UB_FUSE_ENC1=1): enc1.conv.0 (+ folded stem) ->
+// ub_conv_rs2.cuh — the first encoder stage as ONE kernel (default; UB_NO_FUSE_ENC1=1: two kernels): enc1.conv.0 (+ folded stem) ->
 // enc1.conv.3 -> MaxPool2d(2,2), the 64-channel full-resolution tensor between the two convolutions living only in
 // shared memory.  Replaces models/processing_blocks.py:43-48 twice and :73 for that stage.
 //
@@ -24,7 +24,7 @@
 //
 // The stage-1 rows and the stage-2 rows run through the same sliding-window protocol as conv_rs_kernel (global row
 // counters across a CTA's tasks; the rows at a task's edge that take contributions from the neighbouring task are not
-// outputs and are masked), one step apart: the MMA thread issues stage 1 of step tau and stage 2 of stage-1 row tau - 2.
+// outputs and are masked); each stage has its own issuing thread, coupled only through the shared-memory row ring.
 #pragma once
 #include "ub_conv_rs.cuh"
 
@@ -34,8 +34,10 @@ constexpr int kRs2Out = 28;        // output columns per band
 constexpr int kRs2MaxSA1 = 12;     // A1 stages (4 KB each)
 constexpr int kRs2MaxSA2 = 6;      // A2 stages (16 KB each)
 constexpr int kRs2Win = 4;         // TMEM blocks per stage window
-constexpr int kRs2G2 = 2;          // stage-2 epilogue groups (stage 1 has one)
-constexpr int kRs2Threads = 128 + 128 * (1 + kRs2G2);   // 4 role warps + 4 S1-epilogue warps + 8 S2-epilogue warps
+constexpr int kRs2G2 = 2;          // stage-2 epilogue groups (row pairs)
+constexpr int kRs2G1 = 2;          // stage-1 epilogue groups (rows alternate: one group measured 1,250 cycles per row, the whole step
+                                   // has 1,440 cycles of MMA work)
+constexpr int kRs2Threads = 128 + 128 * (kRs2G1 + kRs2G2);   // 4 role warps + the epilogue warps
 
 struct Rs2Cfg {
   static constexpr int C1 = 64, C2 = 64, BK1 = 16, BK2 = 64;
@@ -59,8 +61,6 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
   constexpr int C1 = Cfg::C1, C2 = Cfg::C2, W4 = kRs2Win;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  float* s_bias1 = reinterpret_cast<float*>(smem + Cfg::TAIL_BIAS);
-  float* s_bias2 = s_bias1 + C1;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::TAIL_BAR);
   uint64_t* a1_full = bars;
   uint64_t* a1_empty = a1_full + kRs2MaxSA1;
@@ -79,8 +79,10 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  // warps 0-7: S2 epilogue (2 groups), 8-11: S1 epilogue, 12: producer (+ weights), 13: MMA, 14: TMEM allocator, 15: producer
-  const int role = warp - 12;
+  // warps 0-7: S2 epilogue (2 groups), then the S1 epilogue groups, then: producer (+ weights), stage-1 MMA, TMEM allocator +
+  // stage-2 MMA, producer
+  constexpr int kEpiWarps = 4 * (kRs2G1 + kRs2G2);
+  const int role = warp - kEpiWarps;
   const int hq = p.hq;
   const int tpt = hq + 4;                     // steps per task
   const int bands = (p.W + kRs2Out - 1) / kRs2Out;
@@ -89,8 +91,6 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
   const int my_tiles = my_tasks * tpt;        // stage-1 tiles tau = 0 .. my_tiles-1; stage-1 rows sigma1 = 0 .. my_tiles-2 (= stage-2
                                               // tiles); stage-2 rows sigma2 = 0 .. my_tiles-3
 
-  for (int i = threadIdx.x; i < C1; i += kRs2Threads) s_bias1[i] = p.bias1[i];
-  for (int i = threadIdx.x; i < C2; i += kRs2Threads) s_bias2[i] = p.bias[i];
   if (role == 0 && lane == 0) { tma_prefetch_desc(&p.tmA); tma_prefetch_desc(&p.tmB); }
   if (role == 1 && lane == 0) {
     for (int i = 0; i < kRs2MaxSA1; ++i) { mbar_init(&a1_full[i], 64); mbar_init(&a1_empty[i], 1); }
@@ -159,30 +159,25 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
         if (++sa == p.sa) { sa = 0; pa ^= 1u; }
       }
     }
-  } else if (role == 1) {
-    // ================= MMA issuer =================
+  } else if (role == 1 || role == 2) {
+    // ================= MMA issuers: warp 13 issues stage 1, warp 14 (the TMEM allocator) stage 2 =================
+    // One thread issuing both stages was the limit of the first version: ~200 instructions per step at ~9 cycles each in
+    // one warp = the 2,000-cycle step it measured, against 1,440 cycles of MMA work (15 MMAs, N = 192).  The stages share
+    // nothing but mbarriers (tcgen05.commit tracks the issuing thread's own MMAs), so they get a thread each.
     const bool leader = elect_one();
     const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint64_t d_a1 = umma_smem_desc_interleaved(smem_u32(a1_ring), Cfg::S1::A_PLANE_BYTES, 128);
-    const uint64_t d_a2 = umma_smem_desc_interleaved(smem_u32(a2_ring), Cfg::S2::A_PLANE_BYTES, 128);
-    const uint64_t d_b1 = umma_smem_desc<Cfg::S1::SWZ_B>(smem_u32(b1_res));
-    const uint64_t d_b2 = umma_smem_desc<Cfg::S2::SWZ_B>(smem_u32(b2_res));
-    const uint32_t a1_hi = static_cast<uint32_t>(d_a1 >> 32), a2_hi = static_cast<uint32_t>(d_a2 >> 32);
-    const uint32_t b1_hi = static_cast<uint32_t>(d_b1 >> 32), b2_hi = static_cast<uint32_t>(d_b2 >> 32);
-    const uint32_t a1_lo0 = static_cast<uint32_t>(d_a1), a2_lo0 = static_cast<uint32_t>(d_a2);
-    const uint32_t b1_lo = static_cast<uint32_t>(d_b1), b2_lo = static_cast<uint32_t>(d_b2);
-    const uint32_t win1 = tmem_u, win2 = tmem_u + static_cast<uint32_t>(W4 * C1);
     mbar_wait(w_full, 0);
     tc_fence_after();
-    // per stage: ring position, window position (block of row tile-1, fresh block = row tile+1 and its drain parity)
-    int sa1 = 0, sa2 = 0;
-    uint32_t pa1 = 0, pa2 = 0;
-    int blk1 = W4 - 1, fresh1 = 1, blk2 = W4 - 1, fresh2 = 1;
-    uint32_t fpar1 = 1, fpar2 = 1;
+    if (role == 1) {
+      const uint64_t d_a1 = umma_smem_desc_interleaved(smem_u32(a1_ring), Cfg::S1::A_PLANE_BYTES, 128);
+      const uint64_t d_b1 = umma_smem_desc<Cfg::S1::SWZ_B>(smem_u32(b1_res));
+      const uint32_t a1_hi = static_cast<uint32_t>(d_a1 >> 32), b1_hi = static_cast<uint32_t>(d_b1 >> 32);
+      const uint32_t a1_lo0 = static_cast<uint32_t>(d_a1), b1_lo = static_cast<uint32_t>(d_b1);
+      const uint32_t win1 = tmem_u;
+      int sa1 = 0, blk1 = W4 - 1, fresh1 = 1;   // ring position; block of row tau-1; fresh block = row tau+1 ...
+      uint32_t pa1 = 0, fpar1 = 1;              // ... and the parity of its drain barrier
 #pragma unroll 1
-    for (int step = 0; step < my_tiles + 2; ++step) {
-      if (step < my_tiles) {
-        // ---- stage 1, tile tau = step
+      for (int tau = 0; tau < my_tiles; ++tau) {
         mbar_wait(&s1_empty[fresh1], fpar1);
         mbar_wait(&a1_full[sa1], pa1);
         fence_proxy_async();
@@ -194,15 +189,23 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
           else if (blk1 == W4 - 2) rs_issue_chunk<C1, Cfg::BK1, 1, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, false);
           else rs_issue_chunk<C1, Cfg::BK1, 2, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, false);
           umma_commit(&a1_empty[sa1]);
-          if (step >= 1) umma_commit(&s1_full[blk1]);   // stage-1 row step-1 is complete
+          if (tau >= 1) umma_commit(&s1_full[blk1]);   // stage-1 row tau-1 is complete
         }
         __syncwarp();
         if (++sa1 == p.sa) { sa1 = 0; pa1 ^= 1u; }
         blk1 = blk1 + 1 == W4 ? 0 : blk1 + 1;
         if (++fresh1 == W4) { fresh1 = 0; fpar1 ^= 1u; }
       }
-      const int tau2 = step - 2;   // stage-2 tile = stage-1 row (committed at step tau2 + 1: its epilogue had one step)
-      if (tau2 >= 0 && tau2 < my_tiles - 1) {
+    } else {
+      const uint64_t d_a2 = umma_smem_desc_interleaved(smem_u32(a2_ring), Cfg::S2::A_PLANE_BYTES, 128);
+      const uint64_t d_b2 = umma_smem_desc<Cfg::S2::SWZ_B>(smem_u32(b2_res));
+      const uint32_t a2_hi = static_cast<uint32_t>(d_a2 >> 32), b2_hi = static_cast<uint32_t>(d_b2 >> 32);
+      const uint32_t a2_lo0 = static_cast<uint32_t>(d_a2), b2_lo = static_cast<uint32_t>(d_b2);
+      const uint32_t win2 = tmem_u + static_cast<uint32_t>(W4 * C1);
+      int sa2 = 0, blk2 = W4 - 1, fresh2 = 1;
+      uint32_t pa2 = 0, fpar2 = 1;
+#pragma unroll 1
+      for (int tau2 = 0; tau2 < my_tiles - 1; ++tau2) {   // stage-2 tile = stage-1 row
         mbar_wait(&s2_empty[fresh2], fpar2);
         mbar_wait(&a2_full[sa2], pa2);
         fence_proxy_async();
@@ -210,7 +213,8 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
         if (leader) {
           const uint32_t d0 = win2 + static_cast<uint32_t>(blk2 * C2);
           const uint32_t a_st = a2_lo0 + static_cast<uint32_t>(sa2) * (Cfg::A2_STAGE >> 4);
-          if (blk2 <= W4 - 3) rs_issue_chunk<C2, Cfg::BK2, 0, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
+          if (p.dbg & 64) {}  // (experiment: stage 2 issues no MMAs — timing only)
+          else if (blk2 <= W4 - 3) rs_issue_chunk<C2, Cfg::BK2, 0, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
           else if (blk2 == W4 - 2) rs_issue_chunk<C2, Cfg::BK2, 1, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
           else rs_issue_chunk<C2, Cfg::BK2, 2, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
           umma_commit(&a2_empty[sa2]);
@@ -225,12 +229,13 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
   } else if (role < 0 && warp >= 8) {
     // ================= S1 epilogue (one group): stage-1 row sigma1 -> the A2 ring =================
     const int wq = warp & 3;
+    const int g1 = (warp - 8) >> 2;   // this group takes the rows sigma % kRs2G1 == g1 (blocks g1, g1 + 2: W4 is a multiple of kRs2G1)
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(wq * 32) << 16);
     const int n_rows = my_tiles - 1;
-    int sa2 = 0;
-    uint32_t pa2 = 0;
 #pragma unroll 1
-    for (int sigma = 0; sigma < n_rows; ++sigma) {
+    for (int sigma = g1; sigma < n_rows; sigma += kRs2G1) {
+      const int sa2 = sigma % p.sb;                                   // ring slot and how often it has been used before
+      const uint32_t pa2 = static_cast<uint32_t>(sigma / p.sb) & 1u;
       const int ti = sigma / tpt, rho = sigma - ti * tpt;
       const int task = static_cast<int>(blockIdx.x) + ti * static_cast<int>(gridDim.x);
       const int j = task % bands;
@@ -243,6 +248,11 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
       tc_fence_after();
       const uint32_t t_addr = lane_addr + static_cast<uint32_t>(blk * C1);
       uint32_t pk[C1 / 2];
+      if (p.dbg & 32) {  // (experiment: no stage-1 epilogue work — timing only, results are wrong)
+        tc_fence_before(); mbar_arrive(&s1_empty[blk]);
+#pragma unroll
+        for (int i = 0; i < C1 / 2; ++i) pk[i] = 0u;
+      } else
 #pragma unroll
       for (int ch = 0; ch < C1; ch += 32) {
         uint32_t r[32];
@@ -251,7 +261,7 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
         if (ch + 32 >= C1) { tc_fence_before(); mbar_arrive(&s1_empty[blk]); }
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
-          const float4 bz = *reinterpret_cast<const float4*>(s_bias1 + ch + 4 * j4);
+          const float4 bz = make_float4(p.bias64[0][ch + 4 * j4], p.bias64[0][ch + 4 * j4 + 1], p.bias64[0][ch + 4 * j4 + 2], p.bias64[0][ch + 4 * j4 + 3]);
           const float2 a = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 0]), __uint_as_float(r[4 * j4 + 1])), make_float2(bz.x, bz.y));
           const float2 c2 = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 2]), __uint_as_float(r[4 * j4 + 3])), make_float2(bz.z, bz.w));
           pk[ch / 2 + 2 * j4 + 0] = keep ? bf16x2_max(pack_bf16(a.x, a.y), 0u) : 0u;    // ReLU on the packed pairs (monotone rounding)
@@ -264,7 +274,6 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
       for (int g = 0; g < C1 / 8; ++g) dst[g * (Cfg::S2::A_PLANE_BYTES / 16)] = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
       fence_proxy_async();          // generic-proxy stores -> visible to the tensor core's async-proxy reads
       mbar_arrive(&a2_full[sa2]);
-      if (++sa2 == p.sb) { sa2 = 0; pa2 ^= 1u; }
     }
   } else if (role < 0) {
     // ================= S2 epilogue: bias, 2x2 max-pool, ReLU, store (two groups, row pairs) =================
@@ -308,7 +317,7 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
           uint32_t pk[16];
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
-            const float4 bz = *reinterpret_cast<const float4*>(s_bias2 + ch + 4 * j4);
+            const float4 bz = make_float4(p.bias64[1][ch + 4 * j4], p.bias64[1][ch + 4 * j4 + 1], p.bias64[1][ch + 4 * j4 + 2], p.bias64[1][ch + 4 * j4 + 3]);
             const float2 a = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 0]), __uint_as_float(r[4 * j4 + 1])), make_float2(bz.x, bz.y));
             const float2 c2 = __fadd2_rn(make_float2(__uint_as_float(r[4 * j4 + 2]), __uint_as_float(r[4 * j4 + 3])), make_float2(bz.z, bz.w));
             pk[2 * j4 + 0] = pack_bf16(a.x, a.y);

@@ -118,6 +118,8 @@ struct ConvParams {
   int sb;  // B stages when streaming weights; unused when the kernel is the WS instantiation
   int act; // EpiAct (1x1 STORE only)
   const float* bias1;  // fused first encoder stage (ub_conv_rs2.cuh, rs == 2): conv.0's bias; `bias` is conv.3's, tmA holds conv.0's weights
+  float bias64[2][64]; // ... and both by value: the epilogues read them as constant-bank operands (their shared-memory reads
+                       // competed with the tensor core's operand reads: 23 % of the LSU wavefronts of the first version)
 };
 
 constexpr int kMaxSA = 8;
