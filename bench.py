@@ -542,7 +542,7 @@ def run_gpu(args, rank, world, local_rank):
     # DRAM bytes per launch: ncu --set full capture of the same build (profiles/), headline workload only — ncu cannot
     # run inside a timed bench, so this is the capture's per-image figure x the images per launch of THIS run
     try:
-        tr_path = next(p for p in (os.path.join(ROOT, "profiles", f) for f in ("r02_ncu_traffic.json", "r01_ncu_traffic.json"))
+        tr_path = next(p for p in (os.path.join(ROOT, "profiles", f) for f in ("r02_ncu_traffic_final.json", "r02_ncu_traffic.json", "r01_ncu_traffic.json"))
                        if os.path.exists(p))
         with open(tr_path) as f:
             tr = json.load(f)
