@@ -114,6 +114,7 @@ struct ub_ctx {
   bool head_no_kxs = false;   // UB_HEAD_NO_KXS=1: only the head layer (dec4.conv.3) runs the 9-tap kernel
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool fuse_enc1 = true;      // enc1.conv.0 -> conv.3 -> pool as one kernel (ub_conv_rs2.cuh); UB_NO_FUSE_ENC1=1 / UB_FUSE_ENC1=0: two kernels
+  bool fuse_dec4 = true;      // the last decoder stage's conv.0 -> conv.3 -> head as one kernel; UB_NO_FUSE_DEC4=1 / UB_FUSE_DEC4=0: two
   bool no_rs = true;          // UB_RS=1 selects the row-streaming kernel (ub_conv_rs.cuh) for the thin layers from 32 rows up; default:
                               // kx-stacked (the two measure the same under the power cap)
 
@@ -688,29 +689,30 @@ int launch_rs(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   return UB_OK;
 }
 
-// Fused first encoder stage: a task = (image, 28-column band); persistent CTAs.
-int launch_rs2(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
-  using Cfg = ub::Rs2Cfg;
+// Fused conv pairs (ub_conv_rs2.cuh): a task = (image, 28-column band); persistent CTAs.
+template <int C1, int C2, int BK1, bool HEAD>
+int launch_rs2_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
+  using Cfg = ub::Rs2Cfg<C1, C2, BK1, HEAD>;
   ConvParams cp = cp_in;
   const int bands = (cp.W + ub::kRs2Out - 1) / ub::kRs2Out;
   const int tasks = cp.B * bands;
   const int grid = tasks < ctx->num_sms ? tasks : ctx->num_sms;
   const int fixed = Cfg::B1_BYTES + Cfg::B2_BYTES;
-  cp.sa = 8;                                                               // A1 stages (4 KB)
-  int s2 = (Cfg::OPERAND_BUDGET - fixed - cp.sa * Cfg::A1_STAGE) / Cfg::A2_STAGE;   // A2 stages (16 KB)
+  cp.sa = Cfg::A1_STAGE <= 4096 ? 8 : 4;                                               // A1 stages (4 or 16 KB)
+  int s2 = (Cfg::OPERAND_BUDGET - fixed - cp.sa * Cfg::A1_STAGE) / Cfg::A2_STAGE;      // A2 stages (16 or 8 KB)
   if (s2 > ub::kRs2MaxSA2) s2 = ub::kRs2MaxSA2;
-  if (s2 < 3) return fail(ctx, UB_ERR_UNSUPPORTED, "fused encoder stage: no room for 3 stage-1 row buffers");
+  if (s2 < 3) return fail(ctx, UB_ERR_UNSUPPORTED, "fused conv pair: no room for 3 stage-1 row buffers");
   cp.sb = s2;
   const int smem = Cfg::TAIL_BYTES + cp.sa * Cfg::A1_STAGE + cp.sb * Cfg::A2_STAGE + fixed + 1024;
-  const void* fn = reinterpret_cast<const void*>(&ub::conv_rs2_kernel);
+  const void* fn = reinterpret_cast<const void*>(&ub::conv_rs2_kernel<C1, C2, BK1, HEAD>);
   if (!ctx->smem_opt_in.count(fn)) {
-    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_rs2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ub::kSmemLimit));
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_rs2_kernel<C1, C2, BK1, HEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, ub::kSmemLimit));
     ctx->smem_opt_in.insert(fn);
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(ub::kRs2Threads);
+  cfg.blockDim = dim3(Cfg::THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -722,9 +724,14 @@ int launch_rs2(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_rs2_kernel, cp));
+  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_rs2_kernel<C1, C2, BK1, HEAD>, cp));
   ctx->launches++;
   return UB_OK;
+}
+
+int launch_rs2(ub_ctx* ctx, const ConvParams& cp, cudaStream_t st) {
+  if (cp.mode == ub::EPI_HEAD) return launch_rs2_inst<32, 32, 64, true>(ctx, cp, st);   // dec4.conv.0 -> conv.3 -> head
+  return launch_rs2_inst<64, 64, 16, false>(ctx, cp, st);                              // enc1.conv.0 -> conv.3 -> pool
 }
 
 template <int N, int BK>
@@ -1006,6 +1013,38 @@ int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out) {
       pl->steps.push_back(s);
     }
     const bool last = (j == n + 1);
+    if (last && ctx->stem_fold && ctx->fuse_dec4 && hl(l) % 8 == 0 && hl(l) >= 32 && wl(l) >= 32) {
+      auto l0 = ctx->layer_by_key.find(std::string(k) + ".conv.conv.0+stem");
+      auto l3 = ctx->layer_by_key.find(std::string(k) + ".conv.conv.3");
+      if (l0 == ctx->layer_by_key.end() || l3 == ctx->layer_by_key.end()) return fail(ctx, UB_ERR_STATE, "last decoder stage not packed");
+      const GemmLayer& L0 = ctx->layers[l0->second];
+      const GemmLayer& L3 = ctx->layers[l3->second];
+      if (L0.cin == 64 && L0.cout == 32 && L3.cin == 32 && L3.cout == 32 && L0.w_rs && L3.w_rs &&
+          ctx->h_head_w.size() == static_cast<size_t>(ctx->n_classes) * 32) {
+        Step s;
+        s.kind = Step::GEMM;
+        s.layer = l3->second;
+        ConvParams& cp = s.cp;
+        memset(&cp, 0, sizeof(cp));
+        if ((rc = make_tm_w(ctx, &cp.tmA, L0.w_rs, L0.cin, 9 * L0.cout, 3 * L0.cout, L0.bk))) return rc;
+        if ((rc = make_tm_w(ctx, &cp.tmB, L3.w_rs, L3.cin, 9 * L3.cout, 3 * L3.cout, L3.bk))) return rc;
+        cp.rs = 2; cp.tw = 32; cp.hq = hl(l) / 4;
+        cp.a_src = bufp(i_cat[l]); cp.a_cgs = 2 * sw / 8; cp.a_planes = (L0.cin_src ? L0.cin_src : L0.cin) / 8;
+        cp.k_steps = (L0.cin_src && L0.cin_src < L0.cin) ? (L0.cin_src + 15) / 16 : 0;
+        cp.B = MB; cp.H = hl(l); cp.W = wl(l);
+        cp.cin = L0.cin; cp.ksize = 3; cp.n_total = L3.n_total; cp.mode = ub::EPI_HEAD; cp.relu = 1;
+        cp.bias1 = L0.bias; cp.bias = L3.bias; cp.n_bias = L3.cout; cp.cout = L3.cout;
+        memcpy(cp.bias64[0], L0.h_bias.data(), 32 * sizeof(float));
+        memcpy(cp.bias64[1], L3.h_bias.data(), 32 * sizeof(float));
+        memcpy(cp.bias32, L3.h_bias.data(), 32 * sizeof(float));
+        memcpy(cp.head_w, ctx->h_head_w.data(), ctx->h_head_w.size() * 4);
+        memcpy(cp.head_b, ctx->h_head_b.data(), ctx->h_head_b.size() * 4);
+        cp.dbg = ctx->dbg; cp.ref_batch = 1; cp.n_classes = ctx->n_classes;
+        pl->steps.push_back(s);
+        x = nullptr; xc = sw; xh = hl(l); xw = wl(l);   // (nothing follows the head)
+        continue;
+      }
+    }
     if ((rc = add_gemm(std::string(k) + ((last && ctx->stem_fold) ? ".conv.conv.0+stem" : ".conv.conv.0"), bufp(i_cat[l]), 2 * sw / 8,
                        hl(l), wl(l), ub::EPI_STORE, bufp(i_da[j]), sw / 8, 0))) return rc;
     if ((rc = add_gemm(std::string(k) + ".conv.conv.3", bufp(i_da[j]), sw / 8, hl(l), wl(l), last ? ub::EPI_HEAD : ub::EPI_STORE,
@@ -1260,6 +1299,8 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   { const char* e = getenv("UB_RS"); ctx->no_rs = !(e && e[0] == '1'); }
   { const char* e = getenv("UB_FUSE_ENC1"); const char* n = getenv("UB_NO_FUSE_ENC1");   // default on
     ctx->fuse_enc1 = !(e && e[0] == '0') && !(n && n[0] == '1'); }
+  { const char* e = getenv("UB_FUSE_DEC4"); const char* n = getenv("UB_NO_FUSE_DEC4");   // default on
+    ctx->fuse_dec4 = !(e && e[0] == '0') && !(n && n[0] == '1'); }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();

@@ -1,6 +1,9 @@
-// ub_conv_rs2.cuh — the first encoder stage as ONE kernel (default; UB_NO_FUSE_ENC1=1: two kernels): enc1.conv.0 (+ folded stem) ->
-// enc1.conv.3 -> MaxPool2d(2,2), the 64-channel full-resolution tensor between the two convolutions living only in
-// shared memory.  Replaces models/processing_blocks.py:43-48 twice and :73 for that stage.
+// ub_conv_rs2.cuh — a full-resolution conv pair as ONE kernel, the tensor between the two convolutions living only in shared
+// memory.  Two instantiations, both the default:
+//   the first encoder stage  enc1.conv.0 (+ folded stem) -> enc1.conv.3 -> MaxPool2d(2,2)   (UB_NO_FUSE_ENC1=1: two kernels)
+//   the last decoder stage   dec4.conv.0 (+ folded stem) -> dec4.conv.3 -> 1x1 head, argmax, counts   (UB_NO_FUSE_DEC4=1)
+// Replaces models/processing_blocks.py:43-48 twice per stage, :73, models/UNet.py:73 and models/losses.py:48-58.  The text below
+// describes the encoder instantiation; the decoder one differs in widths (32 channels, 8 KB rows) and in its stage-2 epilogue.
 //
 // Why.  enc1.conv.0 writes 8.4 MB per image that enc1.conv.3 reads straight back: 2.4 GB of the 12.7 GB a micro-batch of
 // 148 images moves through HBM, and conv.0 alone is bound by HBM WRITE bandwidth (1.18 GB in 359 us against a
@@ -27,38 +30,52 @@
 // outputs and are masked); each stage has its own issuing thread, coupled only through the shared-memory row ring.
 #pragma once
 #include "ub_conv_rs.cuh"
+#include "ub_head.cuh"
 
 namespace ub {
 
 constexpr int kRs2Out = 28;        // output columns per band
-constexpr int kRs2MaxSA1 = 12;     // A1 stages (4 KB each)
-constexpr int kRs2MaxSA2 = 6;      // A2 stages (16 KB each)
-constexpr int kRs2Win = 4;         // TMEM blocks per stage window
-constexpr int kRs2G2 = 2;          // stage-2 epilogue groups (row pairs)
-constexpr int kRs2G1 = 2;          // stage-1 epilogue groups (rows alternate: one group measured 1,250 cycles per row, the whole step
-                                   // has 1,440 cycles of MMA work)
-constexpr int kRs2Threads = 128 + 128 * (kRs2G1 + kRs2G2);   // 4 role warps + the epilogue warps
+constexpr int kRs2MaxSA1 = 12;     // A1 stages
+constexpr int kRs2MaxSA2 = 8;      // A2 stages
+constexpr int kRs2MaxWin = 8;      // TMEM blocks per stage window (barrier arrays)
 
+// <C1, C2, BK1, HEAD>: stage 1 = conv3x3 BK1 (-> K per tap) -> C1 channels, stage 2 = conv3x3 C1 -> C2 channels with
+//   HEAD = false: MaxPool2d(2,2) + store            (the first encoder stage: <64, 64, 16, false>)
+//   HEAD = true : 1x1 head, argmax, confusion counts (the last decoder stage, dec4.conv.0 -> conv.3 -> out: <32, 32, 64, true>)
+template <int C1_, int C2_, int BK1_, bool HEAD_>
 struct Rs2Cfg {
-  static constexpr int C1 = 64, C2 = 64, BK1 = 16, BK2 = 64;
+  static constexpr int C1 = C1_, C2 = C2_, BK1 = BK1_, BK2 = C1_;
+  static constexpr bool HEAD = HEAD_;
   using S1 = RsCfg<C1, BK1>;
   using S2 = RsCfg<C2, BK2>;
-  static constexpr int A1_STAGE = S1::A_STAGE_BYTES;   // 4 KB
-  static constexpr int A2_STAGE = S2::A_STAGE_BYTES;   // 16 KB
-  static constexpr int B1_BYTES = 3 * S1::B_STAGE_BYTES;   // 18 KB resident
-  static constexpr int B2_BYTES = 3 * S2::B_STAGE_BYTES;   // 72 KB resident
-  static constexpr int TAIL_BIAS = 0;                  // [C1 + C2] floats
-  static constexpr int TAIL_BAR = 512;
-  static constexpr int N_BARS = 2 * kRs2MaxSA1 + 2 * kRs2MaxSA2 + 4 * kRs2Win + 1;
-  static constexpr int TAIL_TMEM = TAIL_BAR + N_BARS * 8;
+  static constexpr int W1 = 256 / C1;                  // TMEM blocks of the stage-1 window (columns [0, 256))
+  static constexpr int W2 = HEAD ? 6 : 256 / C2;       // ... of the stage-2 window (from column 256); HEAD: 6 blocks for 3 groups
+  static constexpr int G1 = C1 == 64 ? 2 : 1;          // stage-1 epilogue groups (rows alternate)
+  static constexpr int G2 = HEAD ? 3 : 2;              // stage-2 epilogue groups (HEAD: rows alternate; pool: row pairs alternate)
+  static_assert(W1 % G1 == 0 && W1 <= kRs2MaxWin && W2 <= kRs2MaxWin, "a block is always drained by the same group");
+  static_assert(HEAD ? (W2 % G2 == 0) : ((W2 / 2) % G2 == 0), "a block is always drained by the same group");
+  static_assert(W1 * C1 + W2 * C2 <= 512 && W1 * C1 == 256, "TMEM columns");
+  static constexpr int THREADS = 128 + 128 * (G1 + G2);   // 4 role warps + the epilogue warps
+  static constexpr int A1_STAGE = S1::A_STAGE_BYTES;
+  static constexpr int A2_STAGE = S2::A_STAGE_BYTES;
+  static constexpr int B1_BYTES = 3 * S1::B_STAGE_BYTES;
+  static constexpr int B2_BYTES = 3 * S2::B_STAGE_BYTES;
+  static constexpr int TAIL_BAR = 0;
+  static constexpr int N_BARS = 2 * kRs2MaxSA1 + 2 * kRs2MaxSA2 + 4 * kRs2MaxWin + 1;
+  static constexpr int TAIL_CM = TAIL_BAR + N_BARS * 8;
+  static constexpr int TAIL_DICE = TAIL_CM + 4 * kMaxClasses * kMaxClasses * 8;
+  static constexpr int TAIL_TMEM = TAIL_DICE + 4 * kMaxClasses * 2 * 8;
   static constexpr int TAIL_BYTES = ((TAIL_TMEM + 16 + 1023) / 1024) * 1024;
   static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;
 };
 
-__global__ void __launch_bounds__(kRs2Threads, 1)
+template <int C1_, int C2_, int BK1_, bool HEAD_>
+__global__ void __launch_bounds__((Rs2Cfg<C1_, C2_, BK1_, HEAD_>::THREADS), 1)
 conv_rs2_kernel(const __grid_constant__ ConvParams p) {
-  using Cfg = Rs2Cfg;
-  constexpr int C1 = Cfg::C1, C2 = Cfg::C2, W4 = kRs2Win;
+  using Cfg = Rs2Cfg<C1_, C2_, BK1_, HEAD_>;
+  constexpr int C1 = Cfg::C1, C2 = Cfg::C2, W1 = Cfg::W1, W2 = Cfg::W2, G1 = Cfg::G1, G2 = Cfg::G2;
+  constexpr bool HEAD = Cfg::HEAD;
+  constexpr int kThreads = Cfg::THREADS;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::TAIL_BAR);
@@ -67,10 +84,12 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
   uint64_t* a2_full = a1_empty + kRs2MaxSA1;    // S1 epilogue -> MMA: the stage-1 row is in shared memory
   uint64_t* a2_empty = a2_full + kRs2MaxSA2;    // MMA -> S1 epilogue (tcgen05.commit)
   uint64_t* s1_full = a2_empty + kRs2MaxSA2;    // MMA -> S1 epilogue: stage-1 row complete in TMEM
-  uint64_t* s1_empty = s1_full + W4;
-  uint64_t* s2_full = s1_empty + W4;
-  uint64_t* s2_empty = s2_full + W4;
-  uint64_t* w_full = s2_empty + W4;
+  uint64_t* s1_empty = s1_full + kRs2MaxWin;
+  uint64_t* s2_full = s1_empty + kRs2MaxWin;
+  uint64_t* s2_empty = s2_full + kRs2MaxWin;
+  uint64_t* w_full = s2_empty + kRs2MaxWin;
+  unsigned long long* s_cm_all = reinterpret_cast<unsigned long long*>(smem + Cfg::TAIL_CM);
+  double* s_dice_all = reinterpret_cast<double*>(smem + Cfg::TAIL_DICE);
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + Cfg::TAIL_TMEM);
   uint8_t* a1_ring = smem + Cfg::TAIL_BYTES;
   uint8_t* a2_ring = a1_ring + p.sa * Cfg::A1_STAGE;
@@ -79,9 +98,9 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  // warps 0-7: S2 epilogue (2 groups), then the S1 epilogue groups, then: producer (+ weights), stage-1 MMA, TMEM allocator +
+  // warps [0, 4*G2): S2 epilogue groups, then the S1 epilogue groups, then: producer (+ weights), stage-1 MMA, TMEM allocator +
   // stage-2 MMA, producer
-  constexpr int kEpiWarps = 4 * (kRs2G1 + kRs2G2);
+  constexpr int kS2Warps = 4 * G2, kEpiWarps = 4 * (G1 + G2);
   const int role = warp - kEpiWarps;
   const int hq = p.hq;
   const int tpt = hq + 4;                     // steps per task
@@ -92,10 +111,12 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
                                               // tiles); stage-2 rows sigma2 = 0 .. my_tiles-3
 
   if (role == 0 && lane == 0) { tma_prefetch_desc(&p.tmA); tma_prefetch_desc(&p.tmB); }
+  if (threadIdx.x < 4 * kMaxClasses * kMaxClasses) s_cm_all[threadIdx.x] = 0ull;
+  if (threadIdx.x < 4 * kMaxClasses * 2) s_dice_all[threadIdx.x] = 0.0;
   if (role == 1 && lane == 0) {
     for (int i = 0; i < kRs2MaxSA1; ++i) { mbar_init(&a1_full[i], 64); mbar_init(&a1_empty[i], 1); }
     for (int i = 0; i < kRs2MaxSA2; ++i) { mbar_init(&a2_full[i], 128); mbar_init(&a2_empty[i], 1); }
-    for (int i = 0; i < W4; ++i) {
+    for (int i = 0; i < kRs2MaxWin; ++i) {
       mbar_init(&s1_full[i], 1); mbar_init(&s1_empty[i], 128);
       mbar_init(&s2_full[i], 1); mbar_init(&s2_empty[i], 128);
     }
@@ -124,7 +145,7 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
     }
     pdl_wait_prior_grid();
     const int half = role == 0 ? 0 : 1;
-    constexpr int kRows = 4 * (Cfg::BK1 / 8);   // 8 (plane, stream) rows of 512 bytes per stage
+    constexpr int kRows = 4 * (Cfg::BK1 / 8);   // (plane, stream) rows of 512 bytes per stage
     const size_t row_stride = static_cast<size_t>(p.W) * 8;
     const size_t plane_stride = row_stride * p.H;
     const size_t image_stride = plane_stride * p.a_cgs;
@@ -141,7 +162,8 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
       const int b = task / bands, j = task - b * bands;
       const int x = j * kRs2Out - 2 + lane;
       const bool x_ok = x >= 0 && x < p.W;
-      // rows -2, -1 (stream 0, t = 0, 1) and H, H+1 (stream 3, the last two steps) are never dereferenced (src-size 0)
+      // rows -2, -1 (stream 0, t = 0, 1) and H, H+1 (stream 3, the last two steps) are never dereferenced (src-size 0);
+      // channel planes the view does not have (dec4.conv.0: 6 of 8) are zero-filled (their MMAs are not issued)
       const __nv_bfloat16* img = p.a_src + image_stride * b + static_cast<size_t>(x_ok ? x : 0) * 8;
 #pragma unroll 1
       for (int t = 0; t < tpt; ++t) {
@@ -174,7 +196,8 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
       const uint32_t a1_hi = static_cast<uint32_t>(d_a1 >> 32), b1_hi = static_cast<uint32_t>(d_b1 >> 32);
       const uint32_t a1_lo0 = static_cast<uint32_t>(d_a1), b1_lo = static_cast<uint32_t>(d_b1);
       const uint32_t win1 = tmem_u;
-      int sa1 = 0, blk1 = W4 - 1, fresh1 = 1;   // ring position; block of row tau-1; fresh block = row tau+1 ...
+      const bool skip1 = p.k_steps > 0 && p.k_steps < Cfg::BK1 / 16;   // the tail of the chunk is zero padding (dec4.conv.0: 48 of 64)
+      int sa1 = 0, blk1 = W1 - 1, fresh1 = 1;   // ring position; block of row tau-1; fresh block = row tau+1 ...
       uint32_t pa1 = 0, fpar1 = 1;              // ... and the parity of its drain barrier
 #pragma unroll 1
       for (int tau = 0; tau < my_tiles; ++tau) {
@@ -185,24 +208,24 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
         if (leader) {
           const uint32_t d0 = win1 + static_cast<uint32_t>(blk1 * C1);
           const uint32_t a_st = a1_lo0 + static_cast<uint32_t>(sa1) * (Cfg::A1_STAGE >> 4);
-          if (blk1 <= W4 - 3) rs_issue_chunk<C1, Cfg::BK1, 0, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, false);
-          else if (blk1 == W4 - 2) rs_issue_chunk<C1, Cfg::BK1, 1, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, false);
-          else rs_issue_chunk<C1, Cfg::BK1, 2, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, false);
+          if (blk1 <= W1 - 3) rs_issue_chunk<C1, Cfg::BK1, 0, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, skip1);
+          else if (blk1 == W1 - 2) rs_issue_chunk<C1, Cfg::BK1, 1, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, skip1);
+          else rs_issue_chunk<C1, Cfg::BK1, 2, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, skip1);
           umma_commit(&a1_empty[sa1]);
           if (tau >= 1) umma_commit(&s1_full[blk1]);   // stage-1 row tau-1 is complete
         }
         __syncwarp();
         if (++sa1 == p.sa) { sa1 = 0; pa1 ^= 1u; }
-        blk1 = blk1 + 1 == W4 ? 0 : blk1 + 1;
-        if (++fresh1 == W4) { fresh1 = 0; fpar1 ^= 1u; }
+        blk1 = blk1 + 1 == W1 ? 0 : blk1 + 1;
+        if (++fresh1 == W1) { fresh1 = 0; fpar1 ^= 1u; }
       }
     } else {
       const uint64_t d_a2 = umma_smem_desc_interleaved(smem_u32(a2_ring), Cfg::S2::A_PLANE_BYTES, 128);
       const uint64_t d_b2 = umma_smem_desc<Cfg::S2::SWZ_B>(smem_u32(b2_res));
       const uint32_t a2_hi = static_cast<uint32_t>(d_a2 >> 32), b2_hi = static_cast<uint32_t>(d_b2 >> 32);
       const uint32_t a2_lo0 = static_cast<uint32_t>(d_a2), b2_lo = static_cast<uint32_t>(d_b2);
-      const uint32_t win2 = tmem_u + static_cast<uint32_t>(W4 * C1);
-      int sa2 = 0, blk2 = W4 - 1, fresh2 = 1;
+      const uint32_t win2 = tmem_u + 256u;
+      int sa2 = 0, blk2 = W2 - 1, fresh2 = 1;
       uint32_t pa2 = 0, fpar2 = 1;
 #pragma unroll 1
       for (int tau2 = 0; tau2 < my_tiles - 1; ++tau2) {   // stage-2 tile = stage-1 row
@@ -214,26 +237,26 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
           const uint32_t d0 = win2 + static_cast<uint32_t>(blk2 * C2);
           const uint32_t a_st = a2_lo0 + static_cast<uint32_t>(sa2) * (Cfg::A2_STAGE >> 4);
           if (p.dbg & 64) {}  // (experiment: stage 2 issues no MMAs — timing only)
-          else if (blk2 <= W4 - 3) rs_issue_chunk<C2, Cfg::BK2, 0, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
-          else if (blk2 == W4 - 2) rs_issue_chunk<C2, Cfg::BK2, 1, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
+          else if (blk2 <= W2 - 3) rs_issue_chunk<C2, Cfg::BK2, 0, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
+          else if (blk2 == W2 - 2) rs_issue_chunk<C2, Cfg::BK2, 1, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
           else rs_issue_chunk<C2, Cfg::BK2, 2, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
           umma_commit(&a2_empty[sa2]);
           if (tau2 >= 1) umma_commit(&s2_full[blk2]);   // stage-2 row tau2-1 is complete
         }
         __syncwarp();
         if (++sa2 == p.sb) { sa2 = 0; pa2 ^= 1u; }
-        blk2 = blk2 + 1 == W4 ? 0 : blk2 + 1;
-        if (++fresh2 == W4) { fresh2 = 0; fpar2 ^= 1u; }
+        blk2 = blk2 + 1 == W2 ? 0 : blk2 + 1;
+        if (++fresh2 == W2) { fresh2 = 0; fpar2 ^= 1u; }
       }
     }
-  } else if (role < 0 && warp >= 8) {
+  } else if (role < 0 && warp >= kS2Warps) {
     // ================= S1 epilogue (one group): stage-1 row sigma1 -> the A2 ring =================
     const int wq = warp & 3;
-    const int g1 = (warp - 8) >> 2;   // this group takes the rows sigma % kRs2G1 == g1 (blocks g1, g1 + 2: W4 is a multiple of kRs2G1)
+    const int g1 = (warp - kS2Warps) >> 2;   // this group takes the rows sigma % G1 == g1 (W1 is a multiple of G1)
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(wq * 32) << 16);
     const int n_rows = my_tiles - 1;
 #pragma unroll 1
-    for (int sigma = g1; sigma < n_rows; sigma += kRs2G1) {
+    for (int sigma = g1; sigma < n_rows; sigma += G1) {
       const int sa2 = sigma % p.sb;                                   // ring slot and how often it has been used before
       const uint32_t pa2 = static_cast<uint32_t>(sigma / p.sb) & 1u;
       const int ti = sigma / tpt, rho = sigma - ti * tpt;
@@ -242,8 +265,8 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
       const int y = wq * hq - 2 + rho, x = j * kRs2Out - 2 + lane;
       // exact only on lanes 1..30; outside the image the NEXT conv sees its zero padding
       const bool keep = lane >= 1 && lane <= 30 && x >= 0 && x < p.W && y >= 0 && y < p.H;
-      const int blk = sigma % W4;
-      const uint32_t use = static_cast<uint32_t>(sigma / W4);
+      const int blk = sigma % W1;
+      const uint32_t use = static_cast<uint32_t>(sigma / W1);
       mbar_wait(&s1_full[blk], use & 1u);
       tc_fence_after();
       const uint32_t t_addr = lane_addr + static_cast<uint32_t>(blk * C1);
@@ -276,18 +299,19 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
       mbar_arrive(&a2_full[sa2]);
     }
   } else if (role < 0) {
-    // ================= S2 epilogue: bias, 2x2 max-pool, ReLU, store (two groups, row pairs) =================
     const int wq = warp & 3;
     const int grp = warp >> 2;
+    const uint32_t lane_addr2 = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + 256u;
+    const int n_rows = my_tiles - 2;
+    if constexpr (!HEAD) {
+    // ================= S2 epilogue: bias, 2x2 max-pool, ReLU, store (row pairs alternate between the groups) =================
     uint32_t held[C2 / 2];
 #pragma unroll
     for (int i = 0; i < C2 / 2; ++i) held[i] = 0u;
-    const int n_rows = my_tiles - 2;
-    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(wq * 32) << 16) + static_cast<uint32_t>(W4 * C1);
     const int oh = p.H >> 1, ow = p.W >> 1;
     const size_t plane = static_cast<size_t>(oh) * ow;
 #pragma unroll 1
-    for (int pr = grp; 2 * pr < n_rows; pr += kRs2G2) {
+    for (int pr = grp; 2 * pr < n_rows; pr += G2) {
 #pragma unroll 1
       for (int half = 0; half < 2; ++half) {
         const int sigma = 2 * pr + half;
@@ -298,11 +322,11 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
         const int y = wq * hq - 2 + rho, x = j * kRs2Out - 2 + lane;
         const bool valid_row = rho >= 2 && rho <= hq + 1;
         const bool inb = valid_row && lane >= 2 && lane <= 29 && x < p.W;
-        const int blk = sigma % W4;
-        const uint32_t use = static_cast<uint32_t>(sigma / W4);
+        const int blk = sigma % W2;
+        const uint32_t use = static_cast<uint32_t>(sigma / W2);
         mbar_wait(&s2_full[blk], use & 1u);
         tc_fence_after();
-        const uint32_t t_addr = lane_addr + static_cast<uint32_t>(blk * C2);
+        const uint32_t t_addr = lane_addr2 + static_cast<uint32_t>(blk * C2);
         if (!valid_row) {
           tc_fence_before();
           mbar_arrive(&s2_empty[blk]);
@@ -348,6 +372,47 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
           }
         }
       }
+    }
+    } else {
+      // ================= S2 epilogue, HEAD: bias, ReLU, 1x1 head, argmax, confusion counts (rows alternate between the groups) ====
+      const int et = threadIdx.x & 127;
+      unsigned long long* s_cm = s_cm_all + grp * (kMaxClasses * kMaxClasses);
+      double* s_dice = s_dice_all + grp * (2 * kMaxClasses);
+      HeadState hs;
+      hs.init();
+#pragma unroll 1
+      for (int sigma = grp; sigma < n_rows; sigma += G2) {
+        const int ti = sigma / tpt, rho = sigma - ti * tpt;
+        const int task = static_cast<int>(blockIdx.x) + ti * static_cast<int>(gridDim.x);
+        const int b = task / bands, j = task - b * bands;
+        const int y = wq * hq - 2 + rho, x = j * kRs2Out - 2 + lane;
+        const bool valid_row = rho >= 2 && rho <= hq + 1;
+        const bool inb = valid_row && lane >= 2 && lane <= 29 && x < p.W;
+        const int blk = sigma % W2;
+        const uint32_t use = static_cast<uint32_t>(sigma / W2);
+        int tgt_pre = -1;
+        if (p.targets && valid_row) {
+          head_begin_tile(p, hs, (p.img_base + b) / p.ref_batch, grp, et, lane, s_cm, s_dice);
+          if (inb) tgt_pre = head_load_target(p, b, y, x);
+        }
+        mbar_wait(&s2_full[blk], use & 1u);
+        tc_fence_after();
+        if (!valid_row) {
+          tc_fence_before();
+          mbar_arrive(&s2_empty[blk]);
+          continue;
+        }
+        if constexpr (C2 == 32) {
+          uint32_t r[32];
+          tmem_ld_32x32(lane_addr2 + static_cast<uint32_t>(blk * C2), r);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(&s2_empty[blk]);
+          if (p.n_classes == 3) head_pixel<3>(p, hs, r, inb, b, y, x, tgt_pre);
+          else head_pixel<0>(p, hs, r, inb, b, y, x, tgt_pre);
+        }
+      }
+      if (p.targets && hs.cur_batch >= 0) head_flush(p, hs, hs.cur_batch, grp, et, lane, s_cm, s_dice);
     }
   }
 

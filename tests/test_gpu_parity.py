@@ -644,7 +644,7 @@ def test_clipunet_prompt_224_trained(dev):
 
 
 @pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_RS", "UB_HEAD_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL",
-                                  "UB_FUSE_ENC1", "UB_NO_FUSE_ENC1"])
+                                  "UB_NO_FUSE_ENC1", "UB_NO_FUSE_DEC4"])
 def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     """The diagnostic switches select other kernels for the same layers (streamed weights, 9-tap thin layers, single
     CTAs, plain launches); they must stay correct: same logits within bf16 accumulation-order noise, same
@@ -668,10 +668,10 @@ def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
 
 
 @pytest.mark.parametrize("n,hw", [(3, (32, 32)), (2, (40, 72)), (5, (64, 136)), (3, (256, 256)), (2, (264, 280))])
-def test_fused_first_encoder_stage_matches_the_two_kernel_path(trained, dev, n, hw, monkeypatch):
-    """enc1.conv.0 -> conv.3 -> pool as ONE kernel (csrc/ub_conv_rs2.cuh) against the two-kernel path, on shapes whose last
-    28-column band is ragged, whose row quarters are short (8 rows) and whose height is not a power of two; and against the
-    CPU fp32 oracle at the north-star bars."""
+def test_fused_conv_pairs_match_the_two_kernel_path(trained, dev, n, hw, monkeypatch):
+    """enc1.conv.0 -> conv.3 -> pool and dec4.conv.0 -> conv.3 -> head as ONE kernel each (csrc/ub_conv_rs2.cuh) against the
+    two-kernel paths, on shapes whose last 28-column band is ragged, whose row quarters are short (8 rows) and whose height
+    is not a power of two; and against the CPU fp32 oracle at the north-star bars."""
     from image_segmentation_b200 import runtime, synthetic
     m, sd = trained
     imgs, _ = synthetic.make_dataset(n, hw[0], hw[1], seed=23 + hw[1])
@@ -679,6 +679,7 @@ def test_fused_first_encoder_stage_matches_the_two_kernel_path(trained, dev, n, 
     out = {}
     for fused in ("1", "0"):
         monkeypatch.setenv("UB_FUSE_ENC1", fused)
+        monkeypatch.setenv("UB_FUSE_DEC4", fused)
         eng = runtime.new_engine(dev, "unet", 3, 3, 4)   # micro-batch 4: the larger cases run in several passes
         try:
             eng.load_state_dict(m.state_dict())
@@ -689,7 +690,7 @@ def test_fused_first_encoder_stage_matches_the_two_kernel_path(trained, dev, n, 
     ref = util.oracle_logits(sd, x)
     rel_f, rel_u = util.rel_err(out["1"], ref), util.rel_err(out["0"], ref)
     agree = util.argmax_agreement(out["1"], ref)
-    print(f"fused enc1 {n} x {hw}: rel err vs oracle {rel_f:.3e} (two kernels: {rel_u:.3e}), fused vs two kernels "
+    print(f"fused conv pairs {n} x {hw}: rel err vs oracle {rel_f:.3e} (two kernels: {rel_u:.3e}), fused vs two kernels "
           f"{util.rel_err(out['1'], out['0']):.3e}, argmax agreement with the oracle {agree:.5f}")
     assert util.rel_err(out["1"], out["0"]) < 5e-3
     assert rel_f < 1e-2 and agree >= 0.999
