@@ -8,7 +8,7 @@ import sys
 LAYERS = [("pack", 0.0), ("enc1 (conv.0+conv.3+pool, one kernel)", 1.208 + 2.416), ("enc2.0", 1.208), ("enc2.3", 2.416), ("enc3.0", 1.208),
           ("enc3.3", 2.416), ("bott.0", 1.208), ("bott.3", 2.416), ("dec1.up", 0.537), ("resample", 0.0), ("dec1.0", 1.208),
           ("dec1.3", 0.604), ("dec2.up", 0.134), ("dec2.0", 1.208), ("dec2.3", 0.604), ("dec3.up", 0.134), ("dec3.0", 1.208),
-          ("dec3.3", 0.604), ("dec4.up", 0.134), ("dec4.0", 1.208), ("dec4.3 (+head)", 0.604)]   # GMAC per image
+          ("dec3.3", 0.604), ("dec4.up", 0.134), ("dec4 (conv.0+conv.3+head, one kernel)", 1.208 + 0.604)]   # GMAC per image
 
 
 def main():
@@ -30,9 +30,16 @@ def main():
     for r, (name, gmac) in zip(data, LAYERS):
         t = float(r[T]) * tus
         rd, wr = float(r[RD]) * scale[units[RD]], float(r[WR]) * scale[units[WR]]
+        try:
+            tpv = float(r[TP])
+        except ValueError:
+            tpv = 0.0
         k = r[KN].replace("void ", "").replace("ub::", "").split("(")[0][:34]
-        hm = float(r[HM]) / 4 / float(r[CY]) * 100   # hmma sub-pipe cycles / 4 sub-pipes / elapsed cycles
-        print(f"{name:40s} {k:34s} {t:7.1f} {gmac * 2 * n / t * 1e3:6.0f} {float(r[TP]):7.1f} {hm:6.1f} {rd:7.1f} {wr:7.1f} "
+        try:
+            hm = float(r[HM]) / 4 / float(r[CY]) * 100   # hmma sub-pipe cycles / 4 sub-pipes / elapsed cycles
+        except ValueError:
+            hm = 0.0
+        print(f"{name:40s} {k:34s} {t:7.1f} {gmac * 2 * n / t * 1e3:6.0f} {tpv:7.1f} {hm:6.1f} {rd:7.1f} {wr:7.1f} "
               f"{(rd + wr) / t * 1e3:6.0f} {r[GH][:4]}")
         tot_t += t
         tot_b += rd + wr
@@ -40,7 +47,7 @@ def main():
             gemm_b += rd + wr
             gemms += 1
             gemm_t += t
-            w_tp += t * float(r[TP])
+            w_tp += t * tpv
             w_hm += t * hm
     print(f"total {tot_t:.1f} us per {n} images -> {n / tot_t * 1e6:.0f} img/s serialised; DRAM {tot_b / n:.2f} MB per image "
           f"({gemm_b / n:.2f} in the {gemms} tensor-core launches); time-weighted tensor-pipe activity of those launches: "
@@ -48,8 +55,9 @@ def main():
     if len(sys.argv) > 3:
         json.dump({"source": f"{sys.argv[1]} (ncu --set full, one micro-batch of {n} images, final default build of round 2)",
                    "microbatch": n, "gemm_launches_per_microbatch": gemms, "dram_bytes_per_image": gemm_b / n * 1e6,
-                   # every layer's input once + output once, minus the tensor between enc1.conv.0 and conv.3 (written + read: 2 x 8.39 MB)
-                   "algorithmic_bytes_per_image": 89.2e6 - 2 * 8388608.0}, open(sys.argv[3], "w"), indent=1)
+                   # every layer's input once + output once, minus the tensors inside the two fused conv pairs (written + read:
+                   # 2 x 8.39 MB in enc1, 2 x 4.19 MB in dec4)
+                   "algorithmic_bytes_per_image": 89.2e6 - 2 * 8388608.0 - 2 * 4194304.0}, open(sys.argv[3], "w"), indent=1)
 
 
 if __name__ == "__main__":
