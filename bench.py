@@ -483,7 +483,7 @@ def run_gpu(args, rank, world, local_rank):
     if not LARGE and not CLIP:
         cm_fixed, _ = ev.run_level(make_spec("contrast_increase", 1.1, H * W))
         cm_sha = hashlib.sha256(cm_fixed.cpu().numpy().tobytes()).hexdigest()
-        assert int(cm_fixed.sum()) == N_IMAGES * H * W
+        assert int(cm_fixed.sum()) == N_IMAGES * H * W or os.environ.get("UB_DBG")   # (UB_DBG ablations produce wrong counts on purpose)
 
     # ---- end to end through the public API: pinned host buffers -> H2D -> level -> D2H of the counts
     k_e2e = max(1, args.steps)   # the first upload has nothing to overlap with (pipeline fill): amortised over K steps

@@ -698,7 +698,8 @@ int launch_rs2_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   const int tasks = cp.B * bands;
   const int grid = tasks < ctx->num_sms ? tasks : ctx->num_sms;
   const int fixed = Cfg::B1_BYTES + Cfg::B2_BYTES;
-  cp.sa = Cfg::A1_STAGE <= 4096 ? 8 : 4;                                               // A1 stages (4 or 16 KB)
+  cp.sa = Cfg::A1_STAGE <= 4096 ? 8 : 6;                                               // A1 stages (4 or 16 KB; 6 against 4: -2 % on dec4)
+  { const char* e = getenv("UB_RS2_SA"); if (e && atoi(e) >= 2 && atoi(e) <= ub::kRs2MaxSA1) cp.sa = atoi(e); }  // (experiment)
   int s2 = (Cfg::OPERAND_BUDGET - fixed - cp.sa * Cfg::A1_STAGE) / Cfg::A2_STAGE;      // A2 stages (16 or 8 KB)
   if (s2 > ub::kRs2MaxSA2) s2 = ub::kRs2MaxSA2;
   if (s2 < 3) return fail(ctx, UB_ERR_UNSUPPORTED, "fused conv pair: no room for 3 stage-1 row buffers");

@@ -402,6 +402,11 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
           mbar_arrive(&s2_empty[blk]);
           continue;
         }
+        if (p.dbg & 128) {  // (experiment: no head arithmetic — timing only)
+          tc_fence_before();
+          mbar_arrive(&s2_empty[blk]);
+          continue;
+        }
         if constexpr (C2 == 32) {
           uint32_t r[32];
           tmem_ld_32x32(lane_addr2 + static_cast<uint32_t>(blk * C2), r);
