@@ -29,6 +29,7 @@
 // counters across a CTA's tasks; the rows at a task's edge that take contributions from the neighbouring task are not
 // outputs and are masked); each stage has its own issuing thread, coupled only through the shared-memory row ring.
 #pragma once
+#include <cstdio>
 #include "ub_conv_rs.cuh"
 #include "ub_head.cuh"
 
@@ -228,11 +229,17 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
       int sa2 = 0, blk2 = W2 - 1, fresh2 = 1;
       uint32_t pa2 = 0, fpar2 = 1;
 #pragma unroll 1
+      long long t_w1 = 0, t_w2 = 0, t_f = 0, t_i = 0;   // (UB_DBG 512: where this thread's cycles go, printed by CTA 0)
+      const bool prof = (p.dbg & 512) != 0;
       for (int tau2 = 0; tau2 < my_tiles - 1; ++tau2) {   // stage-2 tile = stage-1 row
+        const long long c0 = prof ? clock64() : 0;
         mbar_wait(&s2_empty[fresh2], fpar2);
+        const long long c1 = prof ? clock64() : 0;
         mbar_wait(&a2_full[sa2], pa2);
+        const long long c2 = prof ? clock64() : 0;
         fence_proxy_async();
         tc_fence_after();
+        const long long c3 = prof ? clock64() : 0;
         if (leader) {
           const uint32_t d0 = win2 + static_cast<uint32_t>(blk2 * C2);
           const uint32_t a_st = a2_lo0 + static_cast<uint32_t>(sa2) * (Cfg::A2_STAGE >> 4);
@@ -244,10 +251,14 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
           if (tau2 >= 1) umma_commit(&s2_full[blk2]);   // stage-2 row tau2-1 is complete
         }
         __syncwarp();
+        if (prof) { const long long c4 = clock64(); t_w1 += c1 - c0; t_w2 += c2 - c1; t_f += c3 - c2; t_i += c4 - c3; }
         if (++sa2 == p.sb) { sa2 = 0; pa2 ^= 1u; }
         blk2 = blk2 + 1 == W2 ? 0 : blk2 + 1;
         if (++fresh2 == W2) { fresh2 = 0; fpar2 ^= 1u; }
       }
+      if (prof && blockIdx.x == 0 && lane == 0)
+        printf("[rs2 C1=%d stage-2 issuer] steps %d: wait window %lld, wait row %lld, fences %lld, issue+commit %lld cycles per step\n", C1,
+               my_tiles - 1, t_w1 / (my_tiles - 1), t_w2 / (my_tiles - 1), t_f / (my_tiles - 1), t_i / (my_tiles - 1));
     }
   } else if (role < 0 && warp >= kS2Warps) {
     // ================= S1 epilogue (one group): stage-1 row sigma1 -> the A2 ring =================
