@@ -184,3 +184,21 @@ def test_clip_resize_taps_refuse_more_than_the_tap_limit(lib):
     assert lib.ub_clip_resize_taps(1400, n_out, start.ctypes.data, count.ctypes.data, w.ctypes.data) == -3   # UB_ERR_UNSUPPORTED
     assert b"taps per axis" in lib.ub_last_error(None)
     assert lib.ub_clip_resize_taps(0, n_out, start.ctypes.data, count.ctypes.data, w.ctypes.data) == -1
+
+
+def test_build_recipe_depends_on_every_source_file():
+    """The one translation unit includes every file of csrc/: the rebuild check must watch all of them (a fixed list once
+    missed the newer headers and left a stale library in place)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ub_build", os.path.join(ROOT, "image-segmentation_b200", "build.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    deps = set(b.deps())
+    csrc = os.path.join(ROOT, "image-segmentation_b200", "csrc")
+    for f in os.listdir(csrc):
+        if f.endswith((".cu", ".cuh", ".inl")):
+            assert f in deps, f
+    assert any(d.endswith("unet_b200.h") for d in deps)
+    src = open(os.path.join(csrc, "ub_api.cu")).read()
+    for inc in re.findall(r'#include "([^"]+)"', src):
+        assert os.path.basename(inc) in {os.path.basename(d) for d in deps}, inc
