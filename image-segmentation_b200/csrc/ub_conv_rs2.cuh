@@ -229,8 +229,14 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
       int sa2 = 0, blk2 = W2 - 1, fresh2 = 1;
       uint32_t pa2 = 0, fpar2 = 1;
 #pragma unroll 1
-      long long t_w1 = 0, t_w2 = 0, t_f = 0, t_i = 0;   // (UB_DBG 512: where this thread's cycles go, printed by CTA 0)
+#ifdef UB_RS2_PROFILE   // (compile with -DUB_RS2_PROFILE and run with UB_DBG=512: where this thread's cycles go, printed by CTA 0;
+                        // compiled out by default — the extra instructions sit on the issuing thread's critical path)
+      long long t_w1 = 0, t_w2 = 0, t_f = 0, t_i = 0;
       const bool prof = (p.dbg & 512) != 0;
+#else
+      constexpr bool prof = false;
+      long long t_w1 = 0, t_w2 = 0, t_f = 0, t_i = 0;
+#endif
       for (int tau2 = 0; tau2 < my_tiles - 1; ++tau2) {   // stage-2 tile = stage-1 row
         const long long c0 = prof ? clock64() : 0;
         mbar_wait(&s2_empty[fresh2], fpar2);
