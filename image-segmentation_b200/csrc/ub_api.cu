@@ -53,6 +53,7 @@ struct GemmLayer {
   __nv_bfloat16* w = nullptr;  // [n_total][ksize*ksize*cin] bf16, BN folded
   __nv_bfloat16* w_kxs = nullptr;  // thin 3x3 layers: [(ky*3+kx)*cout + co][cin] for the kx-stacked kernel
   __nv_bfloat16* w_rs = nullptr;   // thin 3x3 layers: [(kx*3+(2-ky))*cout + co][cin] for the row-streaming kernel (ub_conv_rs.cuh)
+  __nv_bfloat16* w_blend = nullptr;  // ConvTranspose: [4*co + 2a + b][cin], the four parities of a channel adjacent (EPI_CONVT_BLEND)
   float* bias = nullptr;       // [cout]
   std::vector<float> h_bias;   // host copy (the HEAD layer passes its 32 biases by value)
 };
@@ -115,6 +116,8 @@ struct ub_ctx {
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool fuse_enc1 = true;      // enc1.conv.0 -> conv.3 -> pool as one kernel (ub_conv_rs2.cuh); UB_NO_FUSE_ENC1=1 / UB_FUSE_ENC1=0: two kernels
   bool fuse_dec4 = true;      // the last decoder stage's conv.0 -> conv.3 -> head as one kernel; UB_NO_FUSE_DEC4=1 / UB_FUSE_DEC4=0: two
+  bool fuse_resize = true;    // the first decoder stage's ConvTranspose + align_corners resize as one GEMM epilogue (EPI_CONVT_BLEND);
+                              // UB_NO_FUSE_RESIZE=1: ConvTranspose to a 2H x 2W buffer, then resample_bilinear_kernel
   bool no_rs = true;          // UB_RS=1 selects the row-streaming kernel (ub_conv_rs.cuh) for the thin layers from 32 rows up; default:
                               // kx-stacked (the two measure the same under the power cap)
 
@@ -287,6 +290,13 @@ int pack_convt(ub_ctx* ctx, const std::string& key) {
   if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.bias), b->data.size() * 4))) return rc;
   UB_CUDA(ctx, cudaMemcpy(L.w, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
   UB_CUDA(ctx, cudaMemcpy(L.bias, b->data.data(), b->data.size() * 4, cudaMemcpyHostToDevice));
+  // second order for the epilogue that blends the four parity products of a pixel (ConvTranspose + resize as one step)
+  for (int ci = 0; ci < L.cin; ++ci)
+    for (int co = 0; co < L.cout; ++co)
+      for (int q = 0; q < 4; ++q)
+        packed[(static_cast<size_t>(co) * 4 + q) * L.cin + ci] = __float2bfloat16(w->data[(static_cast<size_t>(ci) * L.cout + co) * 4 + q]);
+  if ((rc = dev_alloc(ctx, reinterpret_cast<void**>(&L.w_blend), packed.size() * 2))) return rc;
+  UB_CUDA(ctx, cudaMemcpy(L.w_blend, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
   ctx->layer_by_key[L.key] = static_cast<int>(ctx->layers.size());
   ctx->layers.push_back(L);
   return UB_OK;
@@ -466,7 +476,7 @@ int make_tm_w(ub_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* w, int k_total,
 // first channel-group plane the layer reads; `src_cgs` / `out_cgs` are the planes per image of the two buffers.
 // Tile geometry of a layer: the thin 3x3 layers run kx-stacked (32-pixel-wide tiles, 16 when the pool is fused).
 int pick_tw(const ub_ctx* ctx, const GemmLayer& L, int mode) {
-  if (ctx->no_kxs || !L.w_kxs || L.ksize != 3 || mode == ub::EPI_CONVT) return 8;
+  if (ctx->no_kxs || !L.w_kxs || L.ksize != 3 || mode == ub::EPI_CONVT || mode == ub::EPI_CONVT_BLEND) return 8;
   if (ctx->head_no_kxs && mode == ub::EPI_HEAD) return 8;
   if (L.bk == 32 && mode != ub::EPI_HEAD) return 8;  // Cin = 32: only the head layer gains (enc1.conv.0 is write-bound)
   if (L.bk == 16 && L.cout == 64) return 8;          // enc1.conv.0 with the stem folded in: 9 small MMAs, write-bound
@@ -477,6 +487,8 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
               int B, int H, int W, int mode, __nv_bfloat16* out, int out_cgs, int out_cg0) {
   memset(cp, 0, sizeof(*cp));
   int rc;
+  const bool convt = mode == ub::EPI_CONVT || mode == ub::EPI_CONVT_BLEND;
+  if (convt != L.is_convt) return fail(ctx, UB_ERR_INVALID, "%s: epilogue mode %d does not fit the layer", L.key.c_str(), mode);
   const int tw = pick_tw(ctx, L, mode);
   cp->tw = tw;
   // the thin layers at the larger sizes: row-streaming kernel (a task is H/4 + 2 row tiles: worthwhile from 8 rows per
@@ -494,10 +506,10 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   const size_t w_tile_bytes = static_cast<size_t>(L.ksize) * L.ksize * L.cin * L.block_n * 2;
   const bool resident = w_tile_bytes + 2 * 24576 <= 220 * 1024;  // mirrors choose_pipeline's weight-stationary test
   cp->dbg = ctx->dbg;
-  cp->cg2 = (!ctx->no_cg2 && !L.no_pair && tw == 8 && L.bk == 64 && L.block_n >= 128 && mode != ub::EPI_HEAD && mode != ub::EPI_CONVT && !resident) ? 1 : 0;
+  cp->cg2 = (!ctx->no_cg2 && !L.no_pair && tw == 8 && L.bk == 64 && L.block_n >= 128 && mode != ub::EPI_HEAD && !convt && !resident) ? 1 : 0;
   // ConvTranspose whose n-tile does not fit one CTA but whose halves fit a pair (dec1.up: 512 -> 4 x 256): pairs, each
   // keeping its half of ONE n-tile resident, pair-granular tile order (ub_conv_tc.cuh) so the activations hit L2
-  if (!ctx->no_cg2 && mode == ub::EPI_CONVT && L.ksize == 1 && L.bk == 64 && L.block_n == 256 && !resident &&
+  if (!ctx->no_cg2 && convt && L.ksize == 1 && L.bk == 64 && L.block_n == 256 && !resident &&
       w_tile_bytes / 2 + 2 * 16384 <= 200 * 1024 && !ctx->no_pairq) {
     cp->cg2 = 1;
     cp->pairq = 1;
@@ -507,7 +519,9 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   } else if (ub::is_kxs(tw)) {
     if ((rc = make_tm_w(ctx, &cp->tmB, L.w_kxs, L.cin, 9 * L.cout, 3 * L.cout, L.bk))) return rc;
   } else {
-    if ((rc = make_tm_w(ctx, &cp->tmB, L.w, L.ksize * L.ksize * L.cin, L.n_total, cp->cg2 ? L.block_n / 2 : L.block_n, L.bk))) return rc;
+    const __nv_bfloat16* w = mode == ub::EPI_CONVT_BLEND ? L.w_blend : L.w;
+    if (!w) return fail(ctx, UB_ERR_STATE, "%s: no weights packed for epilogue mode %d", L.key.c_str(), mode);
+    if ((rc = make_tm_w(ctx, &cp->tmB, w, L.ksize * L.ksize * L.cin, L.n_total, cp->cg2 ? L.block_n / 2 : L.block_n, L.bk))) return rc;
   }
   // a single chunk whose tail is zero padding (the last decoder conv.0 with the stem folded in: 48 of 64 channels): the MMAs
   // over the padding are not issued
@@ -812,6 +826,17 @@ int launch_gemm_raw(ub_ctx* ctx, const ConvParams& cp, int block_n, int bk, cuda
 // ------------------------------------------------------------------ execution plan for one resolution
 int skip_width(int level) { return level == 0 ? 32 : (32 << level); }
 
+// True when F.interpolate(align_corners=True) from 2n back to n samples reads, for every output sample o, only the two
+// children of ConvTranspose input sample o (ub_conv_tc.cuh: convt_resample_weights, evaluated here with the kernel's own
+// fp32 arithmetic): then ConvTranspose + resize is a per-pixel blend and needs no 2n-sized tensor.
+bool convt_resize_blends(int n) {
+  for (int o = 0; o < n; ++o) {
+    float w0, w1;
+    if (!ub::convt_resample_weights(o, n, &w0, &w1)) return false;
+  }
+  return true;
+}
+
 int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out) {
   auto key = std::make_pair(H, W);
   auto it = ctx->plans.find(key);
@@ -1005,6 +1030,10 @@ int build_plan(ub_ctx* ctx, int H, int W, cudaStream_t st, Plan** out) {
     if (2 * xh == hl(l) && 2 * xw == wl(l)) {
       // F.interpolate is the identity: ConvT scatters straight into planes [0, sw/8) of the concat buffer
       if ((rc = add_gemm(std::string(k) + ".up", x, xc / 8, xh, xw, ub::EPI_CONVT, bufp(i_cat[l]), 2 * sw / 8, 0))) return rc;
+    } else if (ctx->fuse_resize && xh == hl(l) && xw == wl(l) && convt_resize_blends(xh) && convt_resize_blends(xw)) {
+      // the resize undoes the doubling (dec1: the bottleneck is not pooled): every resized pixel is a blend of the four
+      // parity products of ONE ConvTranspose input pixel -> done in the GEMM's epilogue, straight into the concat buffer
+      if ((rc = add_gemm(std::string(k) + ".up", x, xc / 8, xh, xw, ub::EPI_CONVT_BLEND, bufp(i_cat[l]), 2 * sw / 8, 0))) return rc;
     } else {
       if ((rc = add_gemm(std::string(k) + ".up", x, xc / 8, xh, xw, ub::EPI_CONVT, bufp(i_up), sw / 8, 0))) return rc;
       Step s;
@@ -1302,6 +1331,7 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
     ctx->fuse_enc1 = !(e && e[0] == '0') && !(n && n[0] == '1'); }
   { const char* e = getenv("UB_FUSE_DEC4"); const char* n = getenv("UB_NO_FUSE_DEC4");   // default on
     ctx->fuse_dec4 = !(e && e[0] == '0') && !(n && n[0] == '1'); }
+  { const char* e = getenv("UB_NO_FUSE_RESIZE"); ctx->fuse_resize = !(e && e[0] == '1'); }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();

@@ -185,7 +185,54 @@
             dst[static_cast<size_t>(g) * plane] = make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
         }
       };
-      if constexpr (KXS) {
+      bool blended = false;
+      if constexpr (KSIZE == 1 && !KXS) {
+        if (p.mode == EPI_CONVT_BLEND) {
+          // ---- ConvTranspose2d(k2,s2) + F.interpolate(align_corners) back to the input grid (dec1), as one epilogue: the
+          // weights are packed with the four parities of a channel in adjacent columns (n = 4*co + 2a + b), so 32 columns
+          // are 8 channels x 4 parity products of THIS pixel; their blend (convt_resample_weights) + bias is the resized
+          // pixel, rounded to bf16 once.  One 16-byte store per chunk; the 2H x 2W tensor never exists.
+          blended = true;
+          float wy0, wy1, wx0, wx1;
+          convt_resample_weights(y, p.H, &wy0, &wy1);
+          convt_resample_weights(x, p.W, &wx0, &wx1);
+          const float c00 = wy0 * wx0, c01 = wy0 * wx1, c10 = wy1 * wx0, c11 = wy1 * wx1;
+          uint4* dst0 = reinterpret_cast<uint4*>(p.out) +
+                        ((static_cast<size_t>(b) * p.out_cgs + p.out_cg0) * plane + static_cast<size_t>(y) * ow + x);
+          auto blend_chunk = [&](const uint32_t (&r)[32], int cb) {
+            const int c0 = (n0 + cb) >> 2;  // first of the chunk's 8 output channels
+            const float* bias_src = (p.n_bias > kBiasStage ? p.bias : s_bias) + c0;
+            const float4 b0 = *reinterpret_cast<const float4*>(bias_src), b1 = *reinterpret_cast<const float4*>(bias_src + 4);
+            const float bz[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            float o[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              o[k] = fmaf(c00, __uint_as_float(r[4 * k + 0]),
+                          fmaf(c01, __uint_as_float(r[4 * k + 1]),
+                               fmaf(c10, __uint_as_float(r[4 * k + 2]), c11 * __uint_as_float(r[4 * k + 3])))) + bz[k];
+            if (inb)
+              dst0[static_cast<size_t>(c0 >> 3) * plane] =
+                  make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+          };
+          uint32_t ra[32], rb[32];
+          tmem_ld_32x32(t_addr, ra);
+#pragma unroll 1
+          for (int cb = 0; cb < BLOCK_N; cb += 64) {
+            tmem_ld_wait();
+            if (cb + 32 < BLOCK_N) tmem_ld_32x32(t_addr + static_cast<uint32_t>(cb + 32), rb);
+            else release_acc();
+            blend_chunk(ra, cb);
+            if (cb + 32 < BLOCK_N) {
+              tmem_ld_wait();
+              if (cb + 64 < BLOCK_N) tmem_ld_32x32(t_addr + static_cast<uint32_t>(cb + 64), ra);
+              else release_acc();
+              blend_chunk(rb, cb + 32);
+            }
+          }
+        }
+      }
+      if (blended) {
+      } else if constexpr (KXS) {
         // phase 1 (needs TMEM): read the three kx blocks of every 32-channel chunk and add the neighbours'
         // shares; the accumulator is released as soon as the last block is in registers.  phase 2: bias,
         // ReLU, pool, store from registers while the MMA warp already refills the accumulator.

@@ -48,7 +48,26 @@
 
 namespace ub {
 
-enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_CONVT = 2, EPI_HEAD = 3 };
+enum EpiMode : int { EPI_STORE = 0, EPI_POOL = 1, EPI_CONVT = 2, EPI_HEAD = 3,
+                     EPI_CONVT_BLEND = 4 };  // ConvTranspose + the align_corners resample back to the input grid, in the epilogue
+
+// F.interpolate(bilinear, align_corners=True) from 2n back to n samples (models/processing_blocks.py:106-107, the first
+// decoder stage: ConvTranspose doubles the un-pooled bottleneck, the resize brings it back to the skip's size).  Output
+// sample o reads source positions i0 = floor(o * (2n-1)/(n-1)) = 2o + floor(o/(n-1)) and i0 + 1: BOTH are children of
+// ConvTranspose input sample o (its parities 0 and 1), so the two layers together are a per-pixel blend of the four
+// parity products of ONE input pixel.  Same fp32 arithmetic as resample_bilinear_kernel (ub_aux.cuh); w0 / w1 = total
+// weight on the even / odd child.  Returns false when a tap would leave input sample o (the host then keeps two kernels).
+__host__ __device__ inline bool convt_resample_weights(int o, int n, float* w0, float* w1) {
+  const int ni = 2 * n;
+  const float s = n > 1 ? static_cast<float>(ni - 1) / static_cast<float>(n - 1) : 0.0f;
+  const float f = s * static_cast<float>(o);
+  const int i0 = static_cast<int>(f);
+  const int i1 = i0 + (i0 < ni - 1 ? 1 : 0);
+  const float l = f - static_cast<float>(i0), h = 1.0f - l;
+  *w0 = ((i0 & 1) ? 0.0f : h) + ((i1 & 1) ? 0.0f : l);
+  *w1 = ((i0 & 1) ? h : 0.0f) + ((i1 & 1) ? l : 0.0f);
+  return (i0 >> 1) == o && (i1 >> 1) == o;
+}
 enum EpiAct : int { ACT_NONE = 0, ACT_QUICK_GELU = 1 };  // STORE epilogue of the 1x1 instantiations, after the bias (ReLU is `relu`)
 
 __device__ __forceinline__ float2 quick_gelu2(float2 v) {

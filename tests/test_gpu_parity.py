@@ -644,7 +644,7 @@ def test_clipunet_prompt_224_trained(dev):
 
 
 @pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_RS", "UB_HEAD_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL",
-                                  "UB_NO_FUSE_ENC1", "UB_NO_FUSE_DEC4"])
+                                  "UB_NO_FUSE_ENC1", "UB_NO_FUSE_DEC4", "UB_NO_FUSE_RESIZE"])
 def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     """The diagnostic switches select other kernels for the same layers (streamed weights, 9-tap thin layers, single
     CTAs, plain launches); they must stay correct: same logits within bf16 accumulation-order noise, same
@@ -694,6 +694,52 @@ def test_fused_conv_pairs_match_the_two_kernel_path(trained, dev, n, hw, monkeyp
           f"{util.rel_err(out['1'], out['0']):.3e}, argmax agreement with the oracle {agree:.5f}")
     assert util.rel_err(out["1"], out["0"]) < 5e-3
     assert rel_f < 1e-2 and agree >= 0.999
+
+
+def _one_vs_two_kernel_resize(m, sd, arch, dev, n, hw, monkeypatch):
+    from image_segmentation_b200 import runtime, synthetic
+    imgs, _ = synthetic.make_dataset(n, hw[0], hw[1], seed=31 + hw[1])
+    x = synthetic.to_float_nchw(imgs).to(dev)
+    out, launches = {}, {}
+    for two_kernels in ("0", "1"):
+        monkeypatch.setenv("UB_NO_FUSE_RESIZE", two_kernels)
+        eng = runtime.new_engine(dev, arch, 3, 3, 4)
+        try:
+            eng.load_state_dict(m.state_dict())
+            eng.set_layer_couts(m.layer_couts())
+            eng.forward(x[:1])                      # (plan and arena exist from here on)
+            before = eng.launch_count
+            out[two_kernels] = eng.forward(x).cpu()
+            launches[two_kernels] = eng.launch_count - before
+        finally:
+            eng.close()
+    ref = util.oracle_logits(sd, x)
+    rel_f, rel_u = util.rel_err(out["0"], ref), util.rel_err(out["1"], ref)
+    agree = util.argmax_agreement(out["0"], ref)
+    print(f"{arch} {n} x {hw}: ConvT+resize in one epilogue: rel err vs oracle {rel_f:.3e} (two kernels: {rel_u:.3e}), "
+          f"one vs two kernels {util.rel_err(out['0'], out['1']):.3e}, argmax agreement {agree:.5f}; "
+          f"launches {launches['0']} vs {launches['1']}")
+    assert launches["0"] == launches["1"] - 1
+    assert util.rel_err(out["0"], out["1"]) < 5e-3
+    assert rel_f < 1e-2 and agree >= 0.999
+
+
+@pytest.mark.parametrize("n,hw", [(3, (32, 32)), (2, (40, 72)), (3, (256, 256)), (2, (264, 280))])
+def test_convtranspose_and_resize_in_one_epilogue(trained, dev, n, hw, monkeypatch):
+    """The first decoder stage's ConvTranspose2d + F.interpolate(align_corners=True) back to the skip's size
+    (models/processing_blocks.py:106-107) as ONE GEMM whose epilogue blends the four parity products of a pixel
+    (EPI_CONVT_BLEND), against ConvTranspose -> 2H x 2W buffer -> resample kernel (UB_NO_FUSE_RESIZE=1) and against the CPU
+    fp32 oracle at the north-star bars; odd bottleneck sizes (5 x 9, 33 x 35), partial tiles, and one launch fewer."""
+    m, sd = trained
+    _one_vs_two_kernel_resize(m, sd, "unet", dev, n, hw, monkeypatch)
+
+
+@pytest.mark.parametrize("n,hw", [(2, (32, 32)), (3, (48, 80))])
+def test_convtranspose_and_resize_in_one_epilogue_large_unet(large_trained, dev, n, hw, monkeypatch):
+    """The same for LargeUNet's first decoder stage (1024 -> 512 channels: eight n-tiles of 64 channels x 4 parities on single
+    CTAs; bottleneck 2 x 2 and 3 x 5)."""
+    m, sd = large_trained
+    _one_vs_two_kernel_resize(m, sd, "large", dev, n, hw, monkeypatch)
 
 
 def test_head_argmax_shortcut_equals_softmax_argmax(dev, monkeypatch):

@@ -202,3 +202,56 @@ def test_build_recipe_depends_on_every_source_file():
     src = open(os.path.join(csrc, "ub_api.cu")).read()
     for inc in re.findall(r'#include "([^"]+)"', src):
         assert os.path.basename(inc) in {os.path.basename(d) for d in deps}, inc
+
+
+def _convt_resample_weights(o, n):
+    """numpy fp32 restatement of csrc/ub_conv_tc.cuh: convt_resample_weights (the arithmetic of resample_bilinear_kernel,
+    i.e. of F.interpolate(align_corners=True) from 2n to n samples); returns (w_even, w_odd, taps_are_children_of_o)."""
+    f32 = np.float32
+    ni = 2 * n
+    s = f32(ni - 1) / f32(n - 1) if n > 1 else f32(0)
+    f = f32(s * f32(o))
+    i0 = int(f)
+    i1 = i0 + (1 if i0 < ni - 1 else 0)
+    l = f32(f - f32(i0))
+    h = f32(f32(1) - l)
+    w0 = (f32(0) if i0 & 1 else h) + (f32(0) if i1 & 1 else l)
+    w1 = (h if i0 & 1 else f32(0)) + (l if i1 & 1 else f32(0))
+    return w0, w1, (i0 >> 1) == o and (i1 >> 1) == o
+
+
+def test_convtranspose_then_resize_reads_only_the_children_of_one_pixel():
+    """The premise of the EPI_CONVT_BLEND epilogue: output sample o of the 2n -> n align_corners resize reads the two
+    children of ConvTranspose input sample o and nothing else.  True for every n up to 2048; beyond that fp32 rounding of
+    o * (2n-1)/(n-1) can land sample n-2 exactly on an odd source index (first at n = 2082), which is why build_plan
+    evaluates the predicate per size (convt_resize_blends) and keeps the two-kernel path when it fails."""
+    for n in range(1, 2049):
+        for o in (range(n) if n <= 96 else sorted({0, 1, n // 2, n - 3, n - 2, n - 1})):
+            w0, w1, ok = _convt_resample_weights(o, n)
+            assert ok, (n, o)
+            assert abs(float(w0 + w1) - 1.0) < 1e-6
+    assert not _convt_resample_weights(2080, 2082)[2]
+
+
+@pytest.mark.parametrize("h,w", [(1, 1), (2, 3), (7, 5), (32, 32), (33, 16)])
+def test_convtranspose_plus_resize_is_a_blend_of_four_parity_products(h, w):
+    """models/processing_blocks.py:106-107 on the first decoder stage: ConvTranspose2d(k2,s2) then F.interpolate(size=skip,
+    bilinear, align_corners=True) with skip = the ConvTranspose INPUT size.  The library evaluates the pair as
+    sum_q c_q(y,x) * (W[:,:,a,b]^T x[y,x]) + bias with q = 2a+b (column 4*co + q of the re-packed weights): same result."""
+    g = torch.Generator().manual_seed(5)
+    cin, cout = 6, 4
+    x = torch.randn(2, cin, h, w, generator=g)
+    wt = torch.randn(cin, cout, 2, 2, generator=g)
+    bias = torch.randn(cout, generator=g)
+    ref = torch.nn.functional.interpolate(torch.nn.functional.conv_transpose2d(x, wt, bias, stride=2), size=(h, w),
+                                          mode="bilinear", align_corners=True)
+    wy = np.array([_convt_resample_weights(o, h)[:2] for o in range(h)], dtype=np.float32)  # [h][2]
+    wx = np.array([_convt_resample_weights(o, w)[:2] for o in range(w)], dtype=np.float32)
+    out = torch.zeros_like(ref)
+    for a in range(2):
+        for b in range(2):
+            v = torch.einsum("nihw,io->nohw", x, wt[:, :, a, b])
+            c = torch.from_numpy(np.outer(wy[:, a], wx[:, b]))
+            out += c[None, None] * v
+    out += bias[None, :, None, None]
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-5)
