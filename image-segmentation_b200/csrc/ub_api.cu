@@ -116,6 +116,7 @@ struct ub_ctx {
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool fuse_enc1 = true;      // enc1.conv.0 -> conv.3 -> pool as one kernel (ub_conv_rs2.cuh); UB_NO_FUSE_ENC1=1 / UB_FUSE_ENC1=0: two kernels
   bool fuse_dec4 = true;      // the last decoder stage's conv.0 -> conv.3 -> head as one kernel; UB_NO_FUSE_DEC4=1 / UB_FUSE_DEC4=0: two
+  bool stem_zero_plane = false;  // UB_STEM_ZERO_PLANE=1 (diagnostic): the stem's readers fetch the zero plane after the packed image
   bool fuse_resize = true;    // the first decoder stage's ConvTranspose + align_corners resize as one GEMM epilogue (EPI_CONVT_BLEND);
                               // UB_NO_FUSE_RESIZE=1: ConvTranspose to a 2H x 2W buffer, then resample_bilinear_kernel
   bool no_rs = true;          // UB_RS=1 selects the row-streaming kernel (ub_conv_rs.cuh) for the thin layers from 32 rows up; default:
@@ -195,7 +196,10 @@ int pack_conv(ub_ctx* ctx, const std::string& conv_key, const std::string& bn_ke
   // a layer with fewer than 32 input channels (the PromptEncoder's first conv, Cin = 1) reads a zero-padded
   // 32-channel operand: the extra weight columns are zero
   L.cin = fold_at >= 0 ? fold_at + fold_width : (cin_w < 32 ? 32 : cin_w);
-  if (fold_at >= 0) L.cin_src = fold_at + 16;  // the packed image has two channel groups
+  // the packed image is ONE channel group (r, g, b, 1, r_lo, g_lo, b_lo, 0); the other 8 (or 24) reserved input channels exist
+  // only as zero weights and zero-filled operand planes, never as memory reads (UB_STEM_ZERO_PLANE=1: the all-zero second plane
+  // of the buffer is read, as before)
+  if (fold_at >= 0) L.cin_src = fold_at + (ctx->stem_zero_plane ? 16 : 8);
   L.n_total = L.cout;
   L.ksize = 3;
   L.block_n = pick_block_n(L.n_total);
@@ -1332,6 +1336,7 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   { const char* e = getenv("UB_FUSE_DEC4"); const char* n = getenv("UB_NO_FUSE_DEC4");   // default on
     ctx->fuse_dec4 = !(e && e[0] == '0') && !(n && n[0] == '1'); }
   { const char* e = getenv("UB_NO_FUSE_RESIZE"); ctx->fuse_resize = !(e && e[0] == '1'); }
+  { const char* e = getenv("UB_STEM_ZERO_PLANE"); ctx->stem_zero_plane = e && e[0] == '1'; }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();
