@@ -9,6 +9,15 @@ LAYERS = [("pack", 0.0), ("enc1 (conv.0+conv.3+pool, one kernel)", 1.208 + 2.416
           ("enc3.3", 2.416), ("bott.0", 1.208), ("bott.3", 2.416), ("dec1.up", 0.537), ("resample", 0.0), ("dec1.0", 1.208),
           ("dec1.3", 0.604), ("dec2.up", 0.134), ("dec2.0", 1.208), ("dec2.3", 0.604), ("dec3.up", 0.134), ("dec3.0", 1.208),
           ("dec3.3", 0.604), ("dec4.up", 0.134), ("dec4 (conv.0+conv.3+head, one kernel)", 1.208 + 0.604)]   # GMAC per image
+# every layer's input once + output once, minus the tensors inside the two fused conv pairs (written + read: 2 x 8.39 MB in
+# enc1, 2 x 4.19 MB in dec4)
+ALGORITHMIC = 89.2e6 - 2 * 8388608.0 - 2 * 4194304.0
+# builds from r02 call 69 on: ConvTranspose + resize of dec1 in one epilogue (19 launches: no resample; dec1.up writes the
+# 32 x 32 x 256 tensor instead of 64 x 64 x 256: -1.57 MB per image) and the stem's readers fetch one plane of the packed image
+# instead of two (enc1 and dec4: -1.05 MB per image each)
+LAYERS_19 = [l for l in LAYERS if l[0] != "resample"]
+LAYERS_19[8] = ("dec1.up (+resize in the epilogue)", 0.537)
+ALGORITHMIC_19 = ALGORITHMIC - (2097152.0 - 524288.0) - 2 * 1048576.0
 
 
 def main():
@@ -22,12 +31,13 @@ def main():
     GH, KN = col("sm__cycles_elapsed.avg.per_second"), col("Kernel Name")
     scale = {"Mbyte": 1.0, "Kbyte": 1e-3, "Gbyte": 1e3, "byte": 1e-6}
     tus = {"us": 1.0, "ns": 1e-3, "ms": 1e3}[units[T]]
-    assert len(data) == len(LAYERS), (len(data), len(LAYERS))
+    layers, algorithmic = (LAYERS_19, ALGORITHMIC_19) if len(data) == 19 else (LAYERS, ALGORITHMIC)
+    assert len(data) == len(layers), (len(data), len(layers))
     print(f"# ncu --set full, one micro-batch of {n} images (cold cache, serialised)")
     print(f"{'layer':40s} {'kernel':34s} {'t_us':>7s} {'TF/s':>6s} {'tensor%':>7s} {'hmma%':>6s} {'rdMB':>7s} {'wrMB':>7s} {'GB/s':>6s} GHz")
     tot_t = tot_b = gemm_b = gemm_t = w_tp = w_hm = 0.0
     gemms = 0
-    for r, (name, gmac) in zip(data, LAYERS):
+    for r, (name, gmac) in zip(data, layers):
         t = float(r[T]) * tus
         rd, wr = float(r[RD]) * scale[units[RD]], float(r[WR]) * scale[units[WR]]
         try:
@@ -55,9 +65,7 @@ def main():
     if len(sys.argv) > 3:
         json.dump({"source": f"{sys.argv[1]} (ncu --set full, one micro-batch of {n} images, final default build of round 2)",
                    "microbatch": n, "gemm_launches_per_microbatch": gemms, "dram_bytes_per_image": gemm_b / n * 1e6,
-                   # every layer's input once + output once, minus the tensors inside the two fused conv pairs (written + read:
-                   # 2 x 8.39 MB in enc1, 2 x 4.19 MB in dec4)
-                   "algorithmic_bytes_per_image": 89.2e6 - 2 * 8388608.0 - 2 * 4194304.0}, open(sys.argv[3], "w"), indent=1)
+                   "algorithmic_bytes_per_image": algorithmic}, open(sys.argv[3], "w"), indent=1)
 
 
 if __name__ == "__main__":
