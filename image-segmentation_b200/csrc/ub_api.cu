@@ -116,6 +116,7 @@ struct ub_ctx {
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool fuse_enc1 = true;      // enc1.conv.0 -> conv.3 -> pool as one kernel (ub_conv_rs2.cuh); UB_NO_FUSE_ENC1=1 / UB_FUSE_ENC1=0: two kernels
   bool fuse_dec4 = true;      // the last decoder stage's conv.0 -> conv.3 -> head as one kernel; UB_NO_FUSE_DEC4=1 / UB_FUSE_DEC4=0: two
+  bool rs2_no_spare = false;     // UB_RS2_NO_SPARE=1 (diagnostic): the fused last decoder stage with circular TMEM windows (split MMAs at the wrap)
   bool stem_zero_plane = false;  // UB_STEM_ZERO_PLANE=1 (diagnostic): the stem's readers fetch the zero plane after the packed image
   bool fuse_resize = true;    // the first decoder stage's ConvTranspose + align_corners resize as one GEMM epilogue (EPI_CONVT_BLEND);
                               // UB_NO_FUSE_RESIZE=1: ConvTranspose to a 2H x 2W buffer, then resample_bilinear_kernel
@@ -708,9 +709,9 @@ int launch_rs(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
 }
 
 // Fused conv pairs (ub_conv_rs2.cuh): a task = (image, 28-column band); persistent CTAs.
-template <int C1, int C2, int BK1, bool HEAD>
+template <int C1, int C2, int BK1, bool HEAD, bool SPARE = false>
 int launch_rs2_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
-  using Cfg = ub::Rs2Cfg<C1, C2, BK1, HEAD>;
+  using Cfg = ub::Rs2Cfg<C1, C2, BK1, HEAD, SPARE>;
   ConvParams cp = cp_in;
   const int bands = (cp.W + ub::kRs2Out - 1) / ub::kRs2Out;
   const int tasks = cp.B * bands;
@@ -723,9 +724,9 @@ int launch_rs2_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   if (s2 < 3) return fail(ctx, UB_ERR_UNSUPPORTED, "fused conv pair: no room for 3 stage-1 row buffers");
   cp.sb = s2;
   const int smem = Cfg::TAIL_BYTES + cp.sa * Cfg::A1_STAGE + cp.sb * Cfg::A2_STAGE + fixed + 1024;
-  const void* fn = reinterpret_cast<const void*>(&ub::conv_rs2_kernel<C1, C2, BK1, HEAD>);
+  const void* fn = reinterpret_cast<const void*>(&ub::conv_rs2_kernel<C1, C2, BK1, HEAD, SPARE>);
   if (!ctx->smem_opt_in.count(fn)) {
-    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_rs2_kernel<C1, C2, BK1, HEAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, ub::kSmemLimit));
+    UB_CUDA(ctx, cudaFuncSetAttribute(ub::conv_rs2_kernel<C1, C2, BK1, HEAD, SPARE>, cudaFuncAttributeMaxDynamicSharedMemorySize, ub::kSmemLimit));
     ctx->smem_opt_in.insert(fn);
   }
   cudaLaunchConfig_t cfg;
@@ -743,13 +744,15 @@ int launch_rs2_inst(ub_ctx* ctx, const ConvParams& cp_in, cudaStream_t st) {
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_rs2_kernel<C1, C2, BK1, HEAD>, cp));
+  UB_CUDA(ctx, cudaLaunchKernelEx(&cfg, ub::conv_rs2_kernel<C1, C2, BK1, HEAD, SPARE>, cp));
   ctx->launches++;
   return UB_OK;
 }
 
 int launch_rs2(ub_ctx* ctx, const ConvParams& cp, cudaStream_t st) {
-  if (cp.mode == ub::EPI_HEAD) return launch_rs2_inst<32, 32, 64, true>(ctx, cp, st);   // dec4.conv.0 -> conv.3 -> head
+  if (cp.mode == ub::EPI_HEAD)                                                           // dec4.conv.0 -> conv.3 -> head
+    return ctx->rs2_no_spare ? launch_rs2_inst<32, 32, 64, true, false>(ctx, cp, st)     // (UB_RS2_NO_SPARE=1: circular TMEM windows)
+                             : launch_rs2_inst<32, 32, 64, true, true>(ctx, cp, st);
   return launch_rs2_inst<64, 64, 16, false>(ctx, cp, st);                              // enc1.conv.0 -> conv.3 -> pool
 }
 
@@ -1337,6 +1340,7 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
     ctx->fuse_dec4 = !(e && e[0] == '0') && !(n && n[0] == '1'); }
   { const char* e = getenv("UB_NO_FUSE_RESIZE"); ctx->fuse_resize = !(e && e[0] == '1'); }
   { const char* e = getenv("UB_STEM_ZERO_PLANE"); ctx->stem_zero_plane = e && e[0] == '1'; }
+  { const char* e = getenv("UB_RS2_NO_SPARE"); ctx->rs2_no_spare = e && e[0] == '1'; }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();

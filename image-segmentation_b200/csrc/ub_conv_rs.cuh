@@ -112,7 +112,7 @@ __device__ __forceinline__ void umma_bf16_lo_rt(uint32_t tmem_d, uint32_t a_lo, 
 // the 32-channel layers (ncu source view of the first version: ~100 uniform-datapath instructions per row tile at
 // ~9 cycles each = the 900-cycle tile period, with 7 MMAs = 390 cycles of tensor work), so everything that can be is a
 // compile-time constant: CASE = where the three-block window sits (0: contiguous, 1: row tau+1 wraps to block 0, 2: rows
-// tau and tau+1 wrap), FIRST = this chunk carries the tile's first contribution to the fresh block (accumulate = 0).
+// tau and tau+1 wrap, 3: contiguous and every block untouched so far), FIRST = this chunk carries the tile's first contribution to the fresh block (accumulate = 0).
 template <int COUT, int BK, int CASE, bool FIRST>
 __device__ __forceinline__ void rs_issue_chunk(uint32_t d0, uint32_t d_wrap, uint32_t a_stage, uint32_t a_hi, uint32_t bl_c,
                                                uint32_t b_hi, bool skip_last_k) {
@@ -143,6 +143,9 @@ __device__ __forceinline__ void rs_issue_chunk(uint32_t d0, uint32_t d_wrap, uin
         umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc2);
         if (!first) umma_bf16_lo<true>(d_wrap, al, a_hi, bl + 2 * B_BLOCK_U, b_hi, idesc1);
         else umma_bf16_lo<false>(d_wrap, al, a_hi, bl + 2 * B_BLOCK_U, b_hi, idesc1);
+      } else if constexpr (CASE == 3) {   // linear window (ub_conv_rs2.cuh, overflow blocks): all three blocks are first touches
+        if (!first) umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc3);
+        else umma_bf16_lo<false>(d0, al, a_hi, bl, b_hi, idesc3);
       } else {                            // row tau-1 in the last block, rows tau, tau+1 in blocks 0, 1
         umma_bf16_lo<true>(d0, al, a_hi, bl, b_hi, idesc1);
         if (!first) {

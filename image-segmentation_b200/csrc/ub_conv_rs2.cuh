@@ -43,19 +43,28 @@ constexpr int kRs2MaxWin = 8;      // TMEM blocks per stage window (barrier arra
 // <C1, C2, BK1, HEAD>: stage 1 = conv3x3 BK1 (-> K per tap) -> C1 channels, stage 2 = conv3x3 C1 -> C2 channels with
 //   HEAD = false: MaxPool2d(2,2) + store            (the first encoder stage: <64, 64, 16, false>)
 //   HEAD = true : 1x1 head, argmax, confusion counts (the last decoder stage, dec4.conv.0 -> conv.3 -> out: <32, 32, 64, true>)
-template <int C1_, int C2_, int BK1_, bool HEAD_>
+// SPARE: two overflow blocks behind each stage's ring of W TMEM blocks ("linear window").  Input row tau adds to the output rows
+//   tau-1, tau, tau+1 = ring blocks h, h+1, h+2 (h = (tau-1) mod W) with ONE N = 3C MMA per k-step.  Without overflow blocks
+//   the two positions per lap where that span crosses the end of the ring split every MMA in two (N = 2C + C, 48 cycles each
+//   instead of 56 for N = 96: 29 % of the last decoder stage's tensor-pipe time).  With them the span simply runs on into
+//   blocks W, W+1: a row whose home is block 0 (1) collects its first two (one) contributions in overflow block W (W+1) and
+//   the rest at home, and its epilogue adds the two.  Barriers are unchanged: an overflow block is drained together with its
+//   home block, by the same thread, before that thread arrives on the home block's `empty` barrier.
+template <int C1_, int C2_, int BK1_, bool HEAD_, bool SPARE_ = false>
 struct Rs2Cfg {
   static constexpr int C1 = C1_, C2 = C2_, BK1 = BK1_, BK2 = C1_;
-  static constexpr bool HEAD = HEAD_;
+  static constexpr bool HEAD = HEAD_, SPARE = SPARE_;
   using S1 = RsCfg<C1, BK1>;
   using S2 = RsCfg<C2, BK2>;
-  static constexpr int W1 = 256 / C1;                  // TMEM blocks of the stage-1 window (columns [0, 256))
+  static constexpr int W1 = 256 / C1 - (SPARE ? 2 : 0);  // TMEM ring blocks of the stage-1 window (columns [0, 256), overflow blocks included)
   static constexpr int W2 = HEAD ? 6 : 256 / C2;       // ... of the stage-2 window (from column 256); HEAD: 6 blocks for 3 groups
   static constexpr int G1 = C1 == 64 ? 2 : 1;          // stage-1 epilogue groups (rows alternate)
   static constexpr int G2 = HEAD ? 3 : 2;              // stage-2 epilogue groups (HEAD: rows alternate; pool: row pairs alternate)
   static_assert(W1 % G1 == 0 && W1 <= kRs2MaxWin && W2 <= kRs2MaxWin, "a block is always drained by the same group");
   static_assert(HEAD ? (W2 % G2 == 0) : ((W2 / 2) % G2 == 0), "a block is always drained by the same group");
-  static_assert(W1 * C1 + W2 * C2 <= 512 && W1 * C1 == 256, "TMEM columns");
+  static_assert((W1 + (SPARE ? 2 : 0)) * C1 == 256 && 256 + (W2 + (SPARE ? 2 : 0)) * C2 <= 512, "TMEM columns");
+  static_assert(!SPARE || (W1 >= 4 && W2 >= 4), "three open rows and one being drained");
+  static_assert(!SPARE || HEAD, "the pooling epilogue does not read overflow blocks (C = 64 leaves no TMEM columns for them)");
   static constexpr int THREADS = 128 + 128 * (G1 + G2);   // 4 role warps + the epilogue warps
   static constexpr int A1_STAGE = S1::A_STAGE_BYTES;
   static constexpr int A2_STAGE = S2::A_STAGE_BYTES;
@@ -70,12 +79,12 @@ struct Rs2Cfg {
   static constexpr int OPERAND_BUDGET = kSmemLimit - 1024 - TAIL_BYTES;
 };
 
-template <int C1_, int C2_, int BK1_, bool HEAD_>
-__global__ void __launch_bounds__((Rs2Cfg<C1_, C2_, BK1_, HEAD_>::THREADS), 1)
+template <int C1_, int C2_, int BK1_, bool HEAD_, bool SPARE_ = false>
+__global__ void __launch_bounds__((Rs2Cfg<C1_, C2_, BK1_, HEAD_, SPARE_>::THREADS), 1)
 conv_rs2_kernel(const __grid_constant__ ConvParams p) {
-  using Cfg = Rs2Cfg<C1_, C2_, BK1_, HEAD_>;
+  using Cfg = Rs2Cfg<C1_, C2_, BK1_, HEAD_, SPARE_>;
   constexpr int C1 = Cfg::C1, C2 = Cfg::C2, W1 = Cfg::W1, W2 = Cfg::W2, G1 = Cfg::G1, G2 = Cfg::G2;
-  constexpr bool HEAD = Cfg::HEAD;
+  constexpr bool HEAD = Cfg::HEAD, SPARE = Cfg::SPARE;
   constexpr int kThreads = Cfg::THREADS;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -209,7 +218,10 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
         if (leader) {
           const uint32_t d0 = win1 + static_cast<uint32_t>(blk1 * C1);
           const uint32_t a_st = a1_lo0 + static_cast<uint32_t>(sa1) * (Cfg::A1_STAGE >> 4);
-          if (blk1 <= W1 - 3) rs_issue_chunk<C1, Cfg::BK1, 0, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, skip1);
+          if constexpr (SPARE) {   // blocks blk1 .. blk1+2 are physically contiguous (W1, W1+1: overflow); at blk1 = 0 all are first touches
+            if (blk1 == 0) rs_issue_chunk<C1, Cfg::BK1, 3, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, skip1);
+            else rs_issue_chunk<C1, Cfg::BK1, 0, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, skip1);
+          } else if (blk1 <= W1 - 3) rs_issue_chunk<C1, Cfg::BK1, 0, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, skip1);
           else if (blk1 == W1 - 2) rs_issue_chunk<C1, Cfg::BK1, 1, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, skip1);
           else rs_issue_chunk<C1, Cfg::BK1, 2, true>(d0, win1, a_st, a1_hi, b1_lo, b1_hi, skip1);
           umma_commit(&a1_empty[sa1]);
@@ -251,7 +263,10 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
           const uint32_t d0 = win2 + static_cast<uint32_t>(blk2 * C2);
           const uint32_t a_st = a2_lo0 + static_cast<uint32_t>(sa2) * (Cfg::A2_STAGE >> 4);
           if (p.dbg & 64) {}  // (experiment: stage 2 issues no MMAs — timing only)
-          else if (blk2 <= W2 - 3) rs_issue_chunk<C2, Cfg::BK2, 0, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
+          else if constexpr (SPARE) {
+            if (blk2 == 0) rs_issue_chunk<C2, Cfg::BK2, 3, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
+            else rs_issue_chunk<C2, Cfg::BK2, 0, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
+          } else if (blk2 <= W2 - 3) rs_issue_chunk<C2, Cfg::BK2, 0, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
           else if (blk2 == W2 - 2) rs_issue_chunk<C2, Cfg::BK2, 1, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
           else rs_issue_chunk<C2, Cfg::BK2, 2, true>(d0, win2, a_st, a2_hi, b2_lo, b2_hi, false);
           umma_commit(&a2_empty[sa2]);
@@ -298,6 +313,19 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
       for (int ch = 0; ch < C1; ch += 32) {
         uint32_t r[32];
         tmem_ld_32x32(t_addr + static_cast<uint32_t>(ch), r);
+        if constexpr (SPARE) {
+          if (blk < 2) {   // the row's first contributions sit in its overflow block
+            uint32_t o[32];
+            tmem_ld_32x32(lane_addr + static_cast<uint32_t>((W1 + blk) * C1 + ch), o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const float2 a = __fadd2_rn(make_float2(__uint_as_float(r[i]), __uint_as_float(r[i + 1])),
+                                          make_float2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])));
+              r[i] = __float_as_uint(a.x); r[i + 1] = __float_as_uint(a.y);
+            }
+          }
+        }
         tmem_ld_wait();
         if (ch + 32 >= C1) { tc_fence_before(); mbar_arrive(&s1_empty[blk]); }
 #pragma unroll
@@ -428,6 +456,19 @@ conv_rs2_kernel(const __grid_constant__ ConvParams p) {
         if constexpr (C2 == 32) {
           uint32_t r[32];
           tmem_ld_32x32(lane_addr2 + static_cast<uint32_t>(blk * C2), r);
+          if constexpr (SPARE) {
+            if (blk < 2) {   // the row's first contributions sit in its overflow block
+              uint32_t o[32];
+              tmem_ld_32x32(lane_addr2 + static_cast<uint32_t>((W2 + blk) * C2), o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; i += 2) {
+                const float2 a = __fadd2_rn(make_float2(__uint_as_float(r[i]), __uint_as_float(r[i + 1])),
+                                            make_float2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])));
+                r[i] = __float_as_uint(a.x); r[i + 1] = __float_as_uint(a.y);
+              }
+            }
+          }
           tmem_ld_wait();
           tc_fence_before();
           mbar_arrive(&s2_empty[blk]);

@@ -644,7 +644,7 @@ def test_clipunet_prompt_224_trained(dev):
 
 
 @pytest.mark.parametrize("flag", ["UB_FORCE_STREAM", "UB_NO_KXS", "UB_RS", "UB_HEAD_NO_KXS", "UB_NO_CG2", "UB_NO_PAIRQ", "UB_NO_PDL",
-                                  "UB_NO_FUSE_ENC1", "UB_NO_FUSE_DEC4", "UB_NO_FUSE_RESIZE", "UB_STEM_ZERO_PLANE"])
+                                  "UB_NO_FUSE_ENC1", "UB_NO_FUSE_DEC4", "UB_NO_FUSE_RESIZE", "UB_STEM_ZERO_PLANE", "UB_RS2_NO_SPARE"])
 def test_diagnostic_code_paths_agree(trained, dev, flag, monkeypatch):
     """The diagnostic switches select other kernels for the same layers (streamed weights, 9-tap thin layers, single
     CTAs, plain launches); they must stay correct: same logits within bf16 accumulation-order noise, same

@@ -2,7 +2,7 @@
 # One short GPU session: selected parity tests, then the default bench line with and without one diagnostic switch.
 # usage: gpu_call_ab.sh TAG ENVVAR "pytest -k expression"
 tag=${1:-cXX}; var=$2; kexpr=$3
-timeout 420 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -s -k "$kexpr" > gpurun_out/${tag}_tests.log 2>&1; rc=$?
+timeout 240 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -s -k "$kexpr" > gpurun_out/${tag}_tests.log 2>&1; rc=$?
 echo "rc=$rc" >> gpurun_out/${tag}_tests.log
 grep -E "passed|failed|rc=|Error|assert" gpurun_out/${tag}_tests.log | tail -12
 [ $rc -eq 0 ] || exit 1
