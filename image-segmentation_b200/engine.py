@@ -258,7 +258,7 @@ class Engine:
             if tuple(clip_feats.shape) != (n, 512):
                 raise ValueError(f"clip_feats must be [n, 512], got {tuple(clip_feats.shape)}")
             self._check(self.lib.ub_eval_batches_clip(
-                self.h, ctypes.byref(p.struct) if p is not None else None, _ptr(images), fmt, _ptr(targets), tfmt,
+                self._handle(), ctypes.byref(p.struct) if p is not None else None, _ptr(images), fmt, _ptr(targets), tfmt,
                 _ptr(aux), _ptr(clip_feats), n, h, w, int(ref_batch), _ptr(cm), _ptr(dice), _ptr(pred), _ptr(logits),
                 _ptr(pert), _stream(self.device)), "ub_eval_batches_clip")
             return dict(cm=cm, dice=dice, pred=pred, logits=logits, perturbed=pert)
