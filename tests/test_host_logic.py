@@ -255,3 +255,58 @@ def test_convtranspose_plus_resize_is_a_blend_of_four_parity_products(h, w):
             out += c[None, None] * v
     out += bias[None, :, None, None]
     torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-5)
+
+
+def _simulate_row_window(W, n_tiles, spare):
+    """Bookkeeping model of the sliding TMEM window of csrc/ub_conv_rs2.cuh (the issuing thread's loop + rs_issue_chunk's
+    CASE table + the epilogue's reads), one k-step per tile.  A block holds a set of (input row, ky) contributions; a
+    non-accumulating MMA replaces the set.  Returns (what the epilogue read per output row, MMAs issued per tile)."""
+    blocks = {b: {"garbage"} for b in range(W + 2)}
+    read, mmas = {}, []
+
+    def mma(first_block, n_blocks, tau, ky_of_first, accumulate):
+        for i in range(n_blocks):
+            contrib = (tau, ky_of_first - i)          # B rows are ordered ky = 2, 1, 0 = output rows tau-1, tau, tau+1
+            b = first_block + i
+            blocks[b] = (blocks[b] | {contrib}) if accumulate else {contrib}
+
+    blk = W - 1                                        # home of row tau-1
+    for tau in range(n_tiles):
+        issued = 0
+        if spare:                                      # linear window: blocks blk..blk+2 physically contiguous (W, W+1: overflow)
+            if blk == 0:
+                mma(0, 3, tau, 2, False); issued += 1                       # CASE 3: all three are first touches
+            else:
+                mma(blk, 2, tau, 2, True); mma(blk + 2, 1, tau, 0, False); issued += 2   # CASE 0, first k-step
+        elif blk <= W - 3:
+            mma(blk, 2, tau, 2, True); mma(blk + 2, 1, tau, 0, False); issued += 2
+        elif blk == W - 2:                             # CASE 1: row tau+1 wraps to block 0
+            mma(blk, 2, tau, 2, True); mma(0, 1, tau, 0, False); issued += 2
+        else:                                          # CASE 2: rows tau, tau+1 wrap to blocks 0, 1
+            mma(blk, 1, tau, 2, True); mma(0, 1, tau, 1, True); mma(1, 1, tau, 0, False); issued += 3
+        mmas.append(issued)
+        if tau >= 1:                                   # row tau-1 is complete: its epilogue reads home (+ overflow)
+            sigma = tau - 1
+            home = sigma % W
+            got = set(blocks[home])
+            if spare and home < 2:
+                got |= blocks[W + home]
+            read[sigma] = got
+        blk = (blk + 1) % W
+    return read, mmas
+
+
+@pytest.mark.parametrize("W,spare", [(4, False), (6, False), (8, False), (6, True), (4, True)])
+def test_sliding_tmem_window_gives_every_row_its_three_contributions(W, spare):
+    """Every output row sigma >= 1 must be read as exactly {(sigma-1, ky=0), (sigma, ky=1), (sigma+1, ky=2)} — in the circular
+    window (split MMAs where the span wraps) and in the linear one with two overflow blocks (Rs2Cfg::SPARE: the first
+    contributions of the rows whose home is block 0 / 1 sit in blocks W / W+1 and the epilogue adds them)."""
+    read, mmas = _simulate_row_window(W, 5 * W + 3, spare)
+    for sigma, got in read.items():
+        if sigma == 0:
+            continue                                   # the first row of a CTA has no tile -1: masked in the kernel (rho = 0)
+        assert got == {(sigma - 1, 0), (sigma, 1), (sigma + 1, 2)}, (sigma, got)
+    if spare:                                          # never more than the first k-step's split; one MMA when all blocks are fresh
+        assert set(mmas) == {1, 2} and mmas.count(1) == len([t for t in range(len(mmas)) if (W - 1 + t) % W == 0])
+    else:
+        assert 3 in mmas                               # the wrap costs extra MMAs on every lap
