@@ -116,6 +116,7 @@ struct ub_ctx {
   bool no_cg2 = false;        // UB_NO_CG2=1: wide layers run one CTA per tile (no cta_group::2 pairs)
   bool fuse_enc1 = true;      // enc1.conv.0 -> conv.3 -> pool as one kernel (ub_conv_rs2.cuh); UB_NO_FUSE_ENC1=1 / UB_FUSE_ENC1=0: two kernels
   bool fuse_dec4 = true;      // the last decoder stage's conv.0 -> conv.3 -> head as one kernel; UB_NO_FUSE_DEC4=1 / UB_FUSE_DEC4=0: two
+  bool pair_resident = false;    // UB_PAIR_RESIDENT=1 (experiment): CTA pairs for enc2.conv.0 as well
   bool rs2_no_spare = false;     // UB_RS2_NO_SPARE=1 (diagnostic): the fused last decoder stage with circular TMEM windows (split MMAs at the wrap)
   bool stem_zero_plane = false;  // UB_STEM_ZERO_PLANE=1 (diagnostic): the stem's readers fetch the zero plane after the packed image
   bool fuse_resize = true;    // the first decoder stage's ConvTranspose + align_corners resize as one GEMM epilogue (EPI_CONVT_BLEND);
@@ -511,7 +512,10 @@ int fill_gemm(ub_ctx* ctx, ConvParams* cp, const GemmLayer& L, const __nv_bfloat
   const size_t w_tile_bytes = static_cast<size_t>(L.ksize) * L.ksize * L.cin * L.block_n * 2;
   const bool resident = w_tile_bytes + 2 * 24576 <= 220 * 1024;  // mirrors choose_pipeline's weight-stationary test
   cp->dbg = ctx->dbg;
-  cp->cg2 = (!ctx->no_cg2 && !L.no_pair && tw == 8 && L.bk == 64 && L.block_n >= 128 && mode != ub::EPI_HEAD && !convt && !resident) ? 1 : 0;
+  // (UB_PAIR_RESIDENT=1, experiment: also the one 3x3 layer whose whole n-tile fits a single CTA — enc2.conv.0, 64 -> 128 — runs as pairs)
+  const bool pair_anyway = ctx->pair_resident && L.ksize == 3 && L.block_n == 128 && L.n_total == 128;
+  cp->cg2 = (!ctx->no_cg2 && !L.no_pair && tw == 8 && L.bk == 64 && L.block_n >= 128 && mode != ub::EPI_HEAD && !convt &&
+             (!resident || pair_anyway)) ? 1 : 0;
   // ConvTranspose whose n-tile does not fit one CTA but whose halves fit a pair (dec1.up: 512 -> 4 x 256): pairs, each
   // keeping its half of ONE n-tile resident, pair-granular tile order (ub_conv_tc.cuh) so the activations hit L2
   if (!ctx->no_cg2 && convt && L.ksize == 1 && L.bk == 64 && L.block_n == 256 && !resident &&
@@ -1341,6 +1345,7 @@ int ub_create(ub_ctx** out, int device, int arch, int in_channels, int n_classes
   { const char* e = getenv("UB_NO_FUSE_RESIZE"); ctx->fuse_resize = !(e && e[0] == '1'); }
   { const char* e = getenv("UB_STEM_ZERO_PLANE"); ctx->stem_zero_plane = e && e[0] == '1'; }
   { const char* e = getenv("UB_RS2_NO_SPARE"); ctx->rs2_no_spare = e && e[0] == '1'; }
+  { const char* e = getenv("UB_PAIR_RESIDENT"); ctx->pair_resident = e && e[0] == '1'; }
   const char* nc = getenv("UB_NO_CG2");
   ctx->no_cg2 = nc && nc[0] == '1';
   *out = ctx.release();
